@@ -1,0 +1,113 @@
+// common.cuh -- shared device helpers for the B200 (sm_100a) quantized forward-pass kernels.
+// Block formats follow the GGUF spec the reference defines in ggml/src/ggml-common.h:167-326;
+// written from the format description, not copied.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+namespace b200 {
+
+// ggml type ids (reference ggml/include/ggml.h:352-366)
+enum : int { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q8_0 = 8, T_Q8_1 = 9, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14, T_I32 = 26 };
+
+template <int TYPE> struct fmt;   // bytes per block, elements per block
+template <> struct fmt<T_Q4_0> { static constexpr int BB = 18,  BE = 32;  };
+template <> struct fmt<T_Q8_0> { static constexpr int BB = 34,  BE = 32;  };
+template <> struct fmt<T_Q8_1> { static constexpr int BB = 36,  BE = 32;  };
+template <> struct fmt<T_Q4_K> { static constexpr int BB = 144, BE = 256; };
+template <> struct fmt<T_Q5_K> { static constexpr int BB = 176, BE = 256; };
+template <> struct fmt<T_Q6_K> { static constexpr int BB = 210, BE = 256; };
+
+__host__ __device__ inline int block_bytes(int t) {
+    switch (t) { case T_Q4_0: return 18; case T_Q8_0: return 34; case T_Q8_1: return 36; case T_Q4_K: return 144;
+                 case T_Q5_K: return 176; case T_Q6_K: return 210; case T_F32: return 4; case T_F16: return 2; case T_I32: return 4; }
+    return 0;
+}
+__host__ __device__ inline int block_elems(int t) {
+    switch (t) { case T_Q4_0: case T_Q8_0: case T_Q8_1: return 32; case T_Q4_K: case T_Q5_K: case T_Q6_K: return 256;
+                 case T_F32: case T_F16: case T_I32: return 1; }
+    return 0;
+}
+
+// ---- shared-memory access at 2-byte alignment ------------------------------------------------
+// GGUF blocks are only 2-byte aligned (18/34/210-byte strides).  A 32-bit value at a 2-byte
+// aligned shared address = funnel shift of the two aligned words that cover it.
+__device__ __forceinline__ uint32_t lds32(uint32_t saddr) {
+    uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr)); return v;
+}
+__device__ __forceinline__ uint32_t lds16(uint32_t saddr) {
+    uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(saddr)); return v;
+}
+__device__ __forceinline__ int4 lds128(uint32_t saddr) {
+    int4 v; asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr)); return v;
+}
+// N consecutive 32-bit words starting at a 2-byte aligned shared address
+template <int N> __device__ __forceinline__ void lds_words_a2(uint32_t saddr, int (&out)[N]) {
+    const uint32_t base = saddr & ~3u, sh = (saddr & 2u) * 8u;
+    uint32_t w[N + 1];
+#pragma unroll
+    for (int i = 0; i <= N; ++i) w[i] = lds32(base + 4 * i);
+#pragma unroll
+    for (int i = 0; i < N; ++i) out[i] = (int)__funnelshift_r(w[i], w[i + 1], sh);
+}
+
+__device__ __forceinline__ float half_bits_to_float(uint32_t h16) {
+    return __half2float(__ushort_as_half((unsigned short)h16));
+}
+
+// ---- mbarrier + bulk async copy (TMA 1-D) ----------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" :: "r"(bar), "r"(parity) : "memory");
+}
+// global -> shared bulk copy, completion signalled on an mbarrier (SASS: UBLKCP).  src/dst 16-byte
+// aligned, bytes a multiple of 16.
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void * src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+// same, with an L2 evict-first policy: weights are streamed once per token
+__device__ __forceinline__ void bulk_g2s_stream(uint32_t dst, const void * src, uint32_t bytes, uint32_t bar, uint64_t pol) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 :: "r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(pol) : "memory");
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t p; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p;
+}
+// programmatic dependent launch: wait for the producer grid / allow the dependent grid to start
+__device__ __forceinline__ void pdl_wait()    { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+extern int g_launches;   // kernels launched by this library (bench.py gpu_launches)
+
+}  // namespace b200
+
+#define B200_CUDA_CHECK(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) return (int)e_; } while (0)

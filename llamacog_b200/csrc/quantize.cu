@@ -1,0 +1,120 @@
+// quantize.cu -- stand-alone activation quantisation and weight dequantisation.
+// Element-wise, HBM-bound helpers; the hot path fuses the q8_1 step into the GEMV/GEMM prologues.
+#include "common.cuh"
+#include "../../include/b200_ops.h"
+
+namespace b200 {
+
+
+// One warp per q8_1 block, exactly the arithmetic of reference ggml-cuda/quantize.cu:4-49:
+// d = amax/127, q = roundf(x/d), s = xor-butterfly sum of the unquantised x, both stored as half.
+__global__ void quantize_q8_1_kernel(const float * __restrict__ x, int64_t xs, uint8_t * __restrict__ y,
+                                     int64_t k, int64_t k_pad, int64_t nrows) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nb = k_pad >> 5;
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (wid >= nb * nrows) return;
+    const int64_t row = wid / nb, ib = wid - row * nb, i = ib * 32 + lane;
+    const float v = i < k ? x[row * xs + i] : 0.0f;
+    const float amax = warp_max(fabsf(v));
+    const float sum = warp_sum(v);
+    const float d = __fdiv_rn(amax, 127.0f);
+    const int8_t q = amax == 0.0f ? 0 : (int8_t)roundf(__fdiv_rn(v, d));
+    uint8_t * blk = y + (row * nb + ib) * 36;
+    blk[4 + lane] = (uint8_t)q;
+    if (lane == 0) {
+        reinterpret_cast<__half *>(blk)[0] = __float2half_rn(d);
+        reinterpret_cast<__half *>(blk)[1] = __float2half_rn(sum);
+    }
+}
+
+// 6-bit scale/min unpack (reference ggml-quants.c:625-632)
+__device__ __forceinline__ void scale_min_k4(int j, const uint8_t * q, int & sc, int & mn) {
+    if (j < 4) { sc = q[j] & 63; mn = q[j + 4] & 63; }
+    else { sc = (q[j + 4] & 0x0F) | ((q[j - 4] >> 6) << 4); mn = (q[j + 4] >> 4) | ((q[j] >> 6) << 4); }
+}
+
+__device__ __forceinline__ float ldh(const uint8_t * p) {   // 2-byte aligned half load
+    return __half2float(__ushort_as_half(*reinterpret_cast<const unsigned short *>(p)));
+}
+
+// One element per thread; every product/difference is an explicit single rounding so the result is
+// bit-identical to the reference's unfused CPU arithmetic (ggml-quants.c dequantize_row_*).
+template <int TYPE> __device__ __forceinline__ float dequant_elem(const uint8_t * row, int64_t e) {
+    if constexpr (TYPE == T_Q4_0) {
+        const uint8_t * b = row + (e >> 5) * 18; const int j = e & 31;
+        const int q = j < 16 ? (b[2 + j] & 0xF) : (b[2 + j - 16] >> 4);
+        return __fmul_rn((float)(q - 8), ldh(b));
+    } else if constexpr (TYPE == T_Q8_0) {
+        const uint8_t * b = row + (e >> 5) * 34;
+        return __fmul_rn((float)(int8_t)b[2 + (e & 31)], ldh(b));
+    } else if constexpr (TYPE == T_Q4_K || TYPE == T_Q5_K) {
+        constexpr int BB = TYPE == T_Q4_K ? 144 : 176, QS = TYPE == T_Q4_K ? 16 : 48;
+        const uint8_t * b = row + (e >> 8) * BB; const int r = e & 255, s = r >> 5, l = r & 31, p = s >> 1;
+        int sc, mn; scale_min_k4(s, b + 4, sc, mn);
+        const uint8_t qb = b[QS + 32 * p + l];
+        int q = (s & 1) ? (qb >> 4) : (qb & 0xF);
+        if constexpr (TYPE == T_Q5_K) q += ((b[16 + l] >> s) & 1) ? 16 : 0;
+        const float d = __fmul_rn(ldh(b), (float)sc), m = __fmul_rn(ldh(b + 2), (float)mn);
+        return __fsub_rn(__fmul_rn(d, (float)q), m);
+    } else {  // Q6_K
+        const uint8_t * b = row + (e >> 8) * 210; const int r0 = e & 255, h = r0 >> 7, r = r0 & 127, g = r >> 5, l = r & 31;
+        const uint8_t lo = b[64 * h + 32 * (g & 1) + l];
+        const int nib = g < 2 ? (lo & 0xF) : (lo >> 4);
+        const int hi = (b[128 + 32 * h + l] >> (2 * g)) & 3;
+        const int q = (int)(int8_t)(nib | (hi << 4)) - 32;
+        const float ds = __fmul_rn(ldh(b + 208), (float)(int8_t)b[192 + (r0 >> 4)]);
+        return __fmul_rn(ds, (float)q);
+    }
+}
+
+template <int TYPE, typename OUT>
+__global__ void dequantize_rows_kernel(const uint8_t * __restrict__ src, int64_t src_nb1, OUT * __restrict__ dst,
+                                       int64_t dst_stride, int64_t k, int64_t nrows) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= k * nrows) return;
+    const int64_t row = i / k, e = i - row * k;
+    const float v = dequant_elem<TYPE>(src + row * src_nb1, e);
+    if constexpr (sizeof(OUT) == 2) dst[row * dst_stride + e] = __float2half_rn(v);
+    else dst[row * dst_stride + e] = v;
+}
+
+template <int TYPE> static int dequant_launch(const void * src, int64_t nb1, void * dst, int dst_type, int64_t ds,
+                                              int64_t k, int64_t nrows, cudaStream_t st) {
+    const int64_t n = k * nrows;
+    const int threads = 256;
+    const unsigned blocks = (unsigned)((n + threads - 1) / threads);
+    if (dst_type == T_F16) dequantize_rows_kernel<TYPE, __half><<<blocks, threads, 0, st>>>((const uint8_t *)src, nb1, (__half *)dst, ds, k, nrows);
+    else dequantize_rows_kernel<TYPE, float><<<blocks, threads, 0, st>>>((const uint8_t *)src, nb1, (float *)dst, ds, k, nrows);
+    ++g_launches;
+    return (int)cudaGetLastError();
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_quantize_q8_1(const float * x, int64_t xs, void * y, int64_t k, int64_t k_pad, int64_t nrows, void * stream) {
+    if (k_pad % 32 || k > k_pad || nrows <= 0) return -1;
+    const int64_t warps = (k_pad / 32) * nrows;
+    const int threads = 256;
+    const unsigned blocks = (unsigned)((warps * 32 + threads - 1) / threads);
+    quantize_q8_1_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(x, xs, (uint8_t *)y, k, k_pad, nrows);
+    ++g_launches;
+    return (int)cudaGetLastError();
+}
+
+extern "C" int b200_dequantize_rows(int type, const void * src, int64_t src_nb1, void * dst, int dst_type, int64_t dst_stride,
+                                    int64_t k, int64_t nrows, void * stream) {
+    if (dst_type != T_F32 && dst_type != T_F16) return -1;
+    if (k <= 0 || nrows <= 0 || k % block_elems(type)) return -1;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (type) {
+        case T_Q4_0: return dequant_launch<T_Q4_0>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);
+        case T_Q8_0: return dequant_launch<T_Q8_0>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);
+        case T_Q4_K: return dequant_launch<T_Q4_K>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);
+        case T_Q5_K: return dequant_launch<T_Q5_K>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);
+        case T_Q6_K: return dequant_launch<T_Q6_K>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);
+    }
+    return -1;
+}

@@ -1,0 +1,96 @@
+"""ctypes bindings of libb200ops.so (include/b200_ops.h) over torch CUDA tensors.
+
+Mirrors the reference operator semantics: `mul_mat(type, W, X)` is GGML_OP_MUL_MAT with a quantised
+src0 (reference ggml-cuda/mmvq.cu:491-561), etc.  torch is used for device memory and streams only.
+"""
+import ctypes as C
+import os
+
+import torch
+
+from . import build as _build
+
+F32, F16, Q4_0, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K, I32 = 0, 1, 2, 8, 9, 12, 13, 14, 26
+BLOCK_BYTES = {Q4_0: 18, Q8_0: 34, Q8_1: 36, Q4_K: 144, Q5_K: 176, Q6_K: 210, F32: 4, F16: 2}
+BLOCK_ELEMS = {Q4_0: 32, Q8_0: 32, Q8_1: 32, Q4_K: 256, Q5_K: 256, Q6_K: 256, F32: 1, F16: 1}
+
+
+class MmvqArgs(C.Structure):
+    _fields_ = [("type", C.c_int), ("W", C.c_void_p), ("nb1", C.c_int64), ("X", C.c_void_p), ("xs", C.c_int64),
+                ("dst", C.c_void_p), ("ds", C.c_int64), ("N", C.c_int), ("K", C.c_int), ("M", C.c_int),
+                ("nchannels", C.c_int), ("w_ch_stride", C.c_int64), ("x_ch_stride", C.c_int64),
+                ("d_ch_stride", C.c_int64), ("ids", C.c_void_p), ("x_ch_mod", C.c_int), ("w_ch_div", C.c_int),
+                ("pdl", C.c_int), ("dbg_sumi", C.c_void_p)]
+
+
+_lib = None
+
+
+def lib():
+    """Load the CUDA library; fail loudly when it is missing (no CPU fallback exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_build.OPS_LIB):
+            raise RuntimeError("libb200ops.so is not built: run `python -m llamacog_b200.build` "
+                               "(or __graft_entry__.build()); there is no CPU fallback")
+        _lib = C.CDLL(_build.OPS_LIB)
+        _lib.b200_mul_mat_vec_q_ex.argtypes = [C.POINTER(MmvqArgs), C.c_void_p]
+        for name in EXPORTS:
+            getattr(_lib, name).restype = C.c_int
+    return _lib
+
+
+# every symbol include/b200_ops.h declares (tests/test_capi_symbols.py keeps this in sync)
+EXPORTS = ["b200_mul_mat_vec_q_ex", "b200_mul_mat_vec_q", "b200_mmvq_supported_type", "b200_quantize_q8_1",
+           "b200_dequantize_rows", "b200_kernel_launch_count"]
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise RuntimeError("%s failed: rc=%d" % (what, rc))
+
+
+def row_bytes(t, k):
+    assert k % BLOCK_ELEMS[t] == 0
+    return k // BLOCK_ELEMS[t] * BLOCK_BYTES[t]
+
+
+def mul_mat_vec_q(t, W, X, N, K, nb1=None, dbg=False, pdl=-1):
+    """W: uint8 CUDA tensor of N quantised rows; X: float32 [M, K].  Returns dst [M, N]
+    (and the int32 block sums [M, N, K/32] when dbg)."""
+    assert W.is_cuda and X.is_cuda and X.dtype == torch.float32 and X.stride(-1) == 1
+    M = X.shape[0]
+    dst = torch.empty((M, N), dtype=torch.float32, device=X.device)
+    sums = torch.zeros((M, N, K // 32), dtype=torch.int32, device=X.device) if dbg else None
+    a = MmvqArgs(type=t, W=W.data_ptr(), nb1=nb1 or row_bytes(t, K), X=X.data_ptr(), xs=X.stride(0),
+                 dst=dst.data_ptr(), ds=N, N=N, K=K, M=M, nchannels=1, w_ch_stride=0, x_ch_stride=0, d_ch_stride=0,
+                 ids=None, x_ch_mod=0, w_ch_div=0, pdl=pdl, dbg_sumi=sums.data_ptr() if dbg else None)
+    _check(lib().b200_mul_mat_vec_q_ex(C.byref(a), _stream()), "b200_mul_mat_vec_q_ex")
+    return (dst, sums) if dbg else dst
+
+
+def quantize_q8_1(X, k_pad=None):
+    assert X.is_cuda and X.dtype == torch.float32 and X.dim() == 2 and X.stride(1) == 1
+    rows, k = X.shape
+    k_pad = k_pad or (k + 31) // 32 * 32
+    y = torch.empty((rows, k_pad // 32 * 36), dtype=torch.uint8, device=X.device)
+    _check(lib().b200_quantize_q8_1(C.c_void_p(X.data_ptr()), C.c_int64(X.stride(0)), C.c_void_p(y.data_ptr()),
+                                    C.c_int64(k), C.c_int64(k_pad), C.c_int64(rows), _stream()), "b200_quantize_q8_1")
+    return y
+
+
+def dequantize_rows(t, W, nrows, k, out_dtype=torch.float32):
+    assert W.is_cuda and W.dtype == torch.uint8
+    dst = torch.empty((nrows, k), dtype=out_dtype, device=W.device)
+    _check(lib().b200_dequantize_rows(C.c_int(t), C.c_void_p(W.data_ptr()), C.c_int64(row_bytes(t, k)),
+                                      C.c_void_p(dst.data_ptr()), C.c_int(F16 if out_dtype == torch.float16 else F32),
+                                      C.c_int64(k), C.c_int64(k), C.c_int64(nrows), _stream()), "b200_dequantize_rows")
+    return dst
+
+
+def kernel_launch_count():
+    return lib().b200_kernel_launch_count()

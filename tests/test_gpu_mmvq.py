@@ -1,0 +1,150 @@
+"""GPU parity of the decode GEMV (through the C ABI) against the CPU oracle.
+
+Bars: int32 block dot products bit-exact; fp32 outputs within 2e-5 of the oracle's double
+accumulation relative to the output RMS (fp32 summation-order noise only); NMSE against the
+dequantise-then-f32 matmul <= 5e-4 (reference tests/test-backend-ops.cpp:1990-1992)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle as O
+
+pytestmark = pytest.mark.gpu
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "quant_golden.npz"))
+NAMES = list(O.QUANT_TYPES)
+
+
+def _ops():
+    from llamacog_b200 import ops
+    return ops
+
+
+def _run(t, Wnp, Xnp, N, K, dbg=False):
+    ops = _ops()
+    W = torch.from_numpy(np.ascontiguousarray(Wnp).reshape(-1)).cuda()
+    X = torch.from_numpy(np.ascontiguousarray(Xnp)).cuda()
+    out = ops.mul_mat_vec_q(t, W, X, N, K, dbg=dbg)
+    torch.cuda.synchronize()
+    return out
+
+
+def _close(got, want, tol=2e-5):
+    rms = float(np.sqrt((want.astype(np.float64) ** 2).mean())) + 1e-30
+    err = float(np.abs(got.astype(np.float64) - want).max()) / rms
+    assert err < tol, "max err / rms = %g" % err
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_golden_block_sums_bit_exact(name):
+    """The reference-derived golden int32 sums (tests/golden) out of the production kernel."""
+    t = O.QUANT_TYPES[name]
+    dst, sums = _run(t, G["W_" + name], G["X"], 4, 512, dbg=True)
+    assert np.array_equal(sums.cpu().numpy(), G["sumi_" + name])
+    _close(dst.cpu().numpy(), O.mul_mat_vec_q(t, G["W_" + name], G["X"], 4, 512, 2))
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("M", [1, 2, 3, 4, 5, 8])
+def test_small_shapes_vs_oracle(name, M):
+    """m=16,k=256 n=1..8: the reference's own MUL_MAT grid (tests/test-backend-ops.cpp:4246-4250)."""
+    t = O.QUANT_TYPES[name]
+    rng = np.random.default_rng(100 + M)
+    N, K = 16, 256
+    W = O.random_quant_bytes(t, N, K, rng)
+    X = rng.uniform(-1, 1, (M, K)).astype(np.float32)
+    dst, sums = _run(t, W, X, N, K, dbg=True)
+    for m in range(M):
+        q = O.quantize_row_q8_1_cuda(X[m], K)
+        for n in range(N):
+            si, _ = O.block_sums(t, W[n], q, K)
+            assert np.array_equal(sums[m, n].cpu().numpy(), si)
+    _close(dst.cpu().numpy(), O.mul_mat_vec_q(t, W, X, N, K, M))
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("N,K,M", [(257, 4096, 1), (130, 14336, 1), (96, 4096, 4), (64, 2048, 8), (40, 1024, 7),
+                                   (33, 8192, 2), (1, 512, 1), (7, 28672, 1)])
+def test_model_shapes_vs_oracle(name, N, K, M):
+    t = O.QUANT_TYPES[name]
+    rng = np.random.default_rng(N * 7 + K + M)
+    W = O.random_quant_bytes(t, N, K, rng)
+    X = rng.uniform(-1, 1, (M, K)).astype(np.float32)
+    X[0, :32] = 0.0                      # an all-zero q8_1 block (d == 0 path)
+    dst = _run(t, W, X, N, K).cpu().numpy()
+    want = O.mul_mat_vec_q(t, W, X, N, K, M)
+    _close(dst, want)
+    f32 = O.mul_mat_f32(t, W, X, N, K, M)
+    nmse = float(((dst - f32) ** 2).sum() / (f32 ** 2).sum())
+    assert nmse < 5e-4, nmse
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_strided_unaligned_rows(name):
+    """Rows of a non-contiguous view (row stride > row bytes, 2-byte-aligned start), the layout
+    test-backend-ops exercises with v=1 (tests/test-backend-ops.cpp:2043-2055)."""
+    ops = _ops()
+    t = O.QUANT_TYPES[name]
+    rng = np.random.default_rng(5)
+    N, K, M = 19, 512, 2
+    rb = O.row_bytes(t, K)
+    nb1 = rb + O.BLOCK_BYTES[t] * 3
+    off = O.BLOCK_BYTES[t]              # start one block in: only 2-byte aligned for 18/34/210-byte blocks
+    Wrows = O.random_quant_bytes(t, N, K, rng)
+    buf = np.zeros(off + N * nb1 + 64, dtype=np.uint8)
+    for n in range(N):
+        buf[off + n * nb1: off + n * nb1 + rb] = Wrows[n]
+    X = rng.uniform(-1, 1, (M, K)).astype(np.float32)
+    Wd = torch.from_numpy(buf).cuda()
+    dst = ops.mul_mat_vec_q(t, Wd[off:], torch.from_numpy(X).cuda(), N, K, nb1=nb1)
+    torch.cuda.synchronize()
+    _close(dst.cpu().numpy(), O.mul_mat_vec_q(t, Wrows, X, N, K, M))
+
+
+@pytest.mark.parametrize("name", ["q4_K", "q6_K"])
+def test_full_size_linearity(name):
+    """BASELINE sizes (ffn_down 4096x14336): too big for the scalar oracle in seconds, so check a
+    size-independent property -- the GEMV is linear in the weights' row order: permuting rows
+    permutes outputs exactly (bit-for-bit), and 64 sampled rows match the oracle."""
+    ops = _ops()
+    t = O.QUANT_TYPES[name]
+    rng = np.random.default_rng(11)
+    N, K = 4096, 14336
+    W = O.random_quant_bytes(t, N, K, rng)
+    X = rng.uniform(-1, 1, (1, K)).astype(np.float32)
+    Xd = torch.from_numpy(X).cuda()
+    d0 = ops.mul_mat_vec_q(t, torch.from_numpy(W.reshape(-1)).cuda(), Xd, N, K).cpu().numpy()
+    perm = rng.permutation(N)
+    d1 = ops.mul_mat_vec_q(t, torch.from_numpy(np.ascontiguousarray(W[perm]).reshape(-1)).cuda(), Xd, N, K).cpu().numpy()
+    assert np.array_equal(d1[0], d0[0][perm])
+    rows = rng.choice(N, 64, replace=False)
+    want = O.mul_mat_vec_q(t, np.ascontiguousarray(W[rows]), X, 64, K, 1)
+    _close(d0[:, rows], want)
+
+
+def test_quantize_q8_1_bit_exact():
+    ops = _ops()
+    rng = np.random.default_rng(3)
+    X = rng.uniform(-1, 1, (5, 200)).astype(np.float32)
+    X[2, 32:64] = 0
+    X[3, 7] = 1e4
+    y = ops.quantize_q8_1(torch.from_numpy(X).cuda(), 512).cpu().numpy()
+    for r in range(5):
+        assert np.array_equal(y[r], O.quantize_row_q8_1_cuda(X[r], 512))
+    for m in range(2):
+        y = ops.quantize_q8_1(torch.from_numpy(G["X"][m:m + 1].copy()).cuda(), 512).cpu().numpy()
+        assert np.array_equal(y[0], G["q81cuda"][m])
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_dequantize_bit_exact(name):
+    ops = _ops()
+    t = O.QUANT_TYPES[name]
+    for src, ref in (("W_", "deq_"), ("R_", "rdeq_")):
+        got = ops.dequantize_rows(t, torch.from_numpy(G[src + name].reshape(-1).copy()).cuda(), 4, 512).cpu().numpy()
+        assert np.array_equal(got.view(np.uint32), G[ref + name])
+    rng = np.random.default_rng(9)
+    raw = O.random_quant_bytes(t, 8, 4096, rng)
+    got = ops.dequantize_rows(t, torch.from_numpy(raw.reshape(-1).copy()).cuda(), 8, 4096).cpu().numpy()
+    assert np.array_equal(got.view(np.uint32), O.dequantize(t, raw, 8, 4096).view(np.uint32))
