@@ -217,10 +217,27 @@ def main():
 
     import ctypes as C
 
-    def launch(t, W, X, dst, N, K):
+    # where the q8_1 quantisation of the activations runs: "none" = fused prologue of every GEMV;
+    # "down" = one quantise kernel in front of ffn_down (K=14336), "all" = one per distinct activation
+    # vector (q/k/v share one, gate/up share one), the GEMVs then copy the quantised vector
+    xq_mode = os.environ.get("B200_BENCH_XQ", "all")
+    xq_bufs = {}
+
+    def launch(t, W, X, dst, N, K, name="", src=""):
+        xq = None
+        if xq_mode == "all" or (xq_mode == "down" and K > 8192):
+            fresh = name in ("wq", "wo", "gate", "down", "output")     # first consumer of a new activation vector
+            if fresh or src not in xq_bufs:
+                if src not in xq_bufs:
+                    xq_bufs[src] = torch.empty(((K + 255) // 256 * 400,), dtype=torch.uint8, device=dev)
+                rc = ops.lib().b200_quantize_acts(C.c_void_p(X.data_ptr()), C.c_int64(K), C.c_void_p(xq_bufs[src].data_ptr()),
+                                                  C.c_int(K), C.c_int(1), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+                if rc:
+                    raise RuntimeError("b200_quantize_acts rc=%d" % rc)
+            xq = xq_bufs[src].data_ptr()
         a = ops.MmvqArgs(type=t, W=W.data_ptr(), nb1=ops.row_bytes(t, K), X=X.data_ptr(), xs=K, dst=dst.data_ptr(), ds=N,
                          N=N, K=K, M=1, nchannels=1, w_ch_stride=0, x_ch_stride=0, d_ch_stride=0, ids=None,
-                         x_ch_mod=0, w_ch_div=0, pdl=-1, dbg_sumi=None)
+                         x_ch_mod=0, w_ch_div=0, pdl=-1, dbg_sumi=None, Xq=xq, xq_ch_stride=0)
         rc = ops.lib().b200_mul_mat_vec_q_ex(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream))
         if rc:
             raise RuntimeError("b200_mul_mat_vec_q_ex rc=%d" % rc)
@@ -230,7 +247,7 @@ def main():
             if only is not None and t != only:
                 continue
             X = first_input if (first_input is not None and name == "wq" and W is weights[0]) else bufs[i]
-            launch(t, W, X, bufs[o], N, K)
+            launch(t, W, X, bufs[o], N, K, name, i)
 
     st = torch.cuda.Stream()
     graphs = {}
@@ -312,7 +329,7 @@ def main():
                 "dtype": "q4_K/q6_K x q8 (int8 dot, f32 accumulate)", "data": "synthetic",
                 "config": {"workload": "llama3-8b-q4_k_m-decode-b1: 225 quantised MUL_MAT GEMVs per token (4.616 GB weights, "
                                        "Q4_K_M type mix), fused q8_1 prologue; non-matmul glue ops not yet in the timed step",
-                           "l2": "inputs larger than L2 (4.6 GB streamed per step)", "parallelism": "replicas x%d" % world},
+                           "l2": "inputs larger than L2 (4.6 GB streamed per step)", "activation_quantise": xq_mode, "parallelism": "replicas x%d" % world},
                 "clocks": clocks,
                 "e2e": {"value": e2e_val, "unit": "tokens/s", "h2d_bytes_per_step": N_EMBD * 4, "d2h_bytes_per_step": N_VOCAB * 4},
                 "gpu_launches": launches_per_step * args.steps,

@@ -55,6 +55,10 @@ typedef struct b200_mmvq_args {
     int pdl;                /* 1: launch with programmatic dependent launch, 0: off, -1: env B200_PDL */
     int32_t * dbg_sumi;     /* optional device [M][N][K/32] zero-initialised: receives the exact int32
                                block dot products (reference vecdotq.cuh sumi/dot1) for parity tests */
+    const void * Xq;        /* optional: activations already quantised by b200_quantize_acts (then X may be
+                               NULL): [channels][M][ceil(K/256)] items of 400 bytes; the kernel then copies
+                               them instead of quantising X itself (better when K is large and N small) */
+    int64_t xq_ch_stride;   /* bytes between channels of Xq */
 } b200_mmvq_args;
 
 int b200_mul_mat_vec_q_ex(const b200_mmvq_args * args, void * stream);
@@ -66,6 +70,12 @@ int b200_mmvq_supported_type(int type);
  * Replaces quantize_row_q8_1_cuda (ggml/src/ggml-cuda/quantize.cu:4-49,145-157): x fp32 [nrows][k]
  * (row stride xs floats) -> block_q8_1 rows of k_pad/32 blocks, zero padded beyond k. */
 int b200_quantize_q8_1(const float * x, int64_t xs, void * y, int64_t k, int64_t k_pad, int64_t nrows, void * stream);
+
+/* The same quantisation in the shared-memory layout of the GEMV (per 32 values: 32 int8, fp32 d,
+ * d*sum(q), -32*sum(q[0..15]), -32*sum(q[16..31]); 400 bytes per 256 values), for b200_mmvq_args.Xq.
+ * x fp32 [M][K] (column stride xs floats) -> out [M][ceil(K/256)*400 bytes]. */
+int b200_quantize_acts(const float * x, int64_t xs, void * out, int K, int M, void * stream);
+int64_t b200_quantized_acts_bytes(int K, int M);
 
 /* ---- dequantisation ---------------------------------------------------------------------------
  * Replaces dequantize_row_<type> (ggml/src/ggml-quants.c:249,343,1274,1480,1684; GPU analogue

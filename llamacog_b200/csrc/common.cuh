@@ -107,6 +107,7 @@ __device__ __forceinline__ float warp_max(float v) {
 }
 
 extern int g_launches;   // kernels launched by this library (bench.py gpu_launches)
+int pdl_default();       // env B200_PDL (default 1): launch kernels with programmatic dependent launch
 
 }  // namespace b200
 

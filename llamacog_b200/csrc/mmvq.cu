@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <cstdlib>
+#include <cstdint>
 
 namespace b200 {
 
@@ -24,63 +25,97 @@ static int num_sms() {
     return n[dev] > 0 ? n[dev] : 148;
 }
 
-static const size_t SMEM_MAX = 232448 - 1024;   // 227 KB opt-in limit minus static/alignment slack
+static const size_t SMEM_1CTA = 232448 - 1024;   // 227 KB opt-in limit minus static/alignment slack
+static const size_t SMEM_2CTA = 115712 - 1024;   // half an SM: two CTAs (or two kernels under PDL) co-reside
 
-// Largest number of activation columns one launch can take for this K (register budget:
-// CPT*M <= 8 unit-columns per thread, team <= 15 warps).
+static int env_int(const char * name, int dflt) { const char * e = getenv(name); return e ? atoi(e) : dflt; }
+
+// Largest number of activation columns one launch can take for this K: the quantised activations
+// of all columns live in shared memory (400 B per 256 elements per column), at most ~96 KB.
 static int max_cols_per_launch(int K) {
-    const int U = K / 32;
-    for (int m = 8; m >= 1; --m) {
-        for (int cpt = 1; cpt * m <= 8; cpt <<= 1) {
-            if ((U + cpt - 1) / cpt <= 32 * 15) return m;
-        }
-    }
+    const int bpr = (K + 255) / 256;
+    const int m = (int)((96 * 1024) / ((size_t)bpr * ACT_ITEM));
+    return std::max(0, std::min(8, m));
+}
+
+static int item_bytes(int type) {
+    switch (type) { case T_Q4_0: return 144; case T_Q8_0: return 272; case T_Q4_K: return 144; case T_Q5_K: return 176; case T_Q6_K: return 210; }
     return 0;
 }
 
 // Choose geometry.  Returns 0 on success.
 static int configure(int type, int N, int K, int M, const b200_mmvq_args & a, mmvq_params & p, mmvq_launch_cfg & c) {
-    const int U = K / 32;
     const int rb = K / block_elems(type) * block_bytes(type);
-    // units per thread: smallest CPT that brings a team to <= 7 warps, within the register budget
-    int cpt = 1;
-    while (cpt * 2 * M <= 8 && (U + cpt - 1) / cpt > 224) cpt <<= 1;
-    const int team_threads = (U + cpt - 1) / cpt;
-    const int wpt = (team_threads + 31) / 32;
-    if (wpt > 15) return -2;
-    int nt = std::max(1, std::min(4, 16 / wpt));
+    const int bpr = (K + 255) / 256;
+    int G = 1;
+    while (G < 32 && bpr % (2 * G) == 0) G <<= 1;
+    const int nseg = bpr / G;
     const int sms = num_sms();
-    // CTAs: one per SM at most, and at least ~one row per team
-    int gx = std::min(sms, std::max(1, (N + nt - 1) / nt));
-    const int rows_per_cta = (N + gx - 1) / gx;
-    nt = std::max(1, std::min(nt, rows_per_cta));
 
     const bool w_aligned = (((uintptr_t)a.W | (uintptr_t)a.nb1 | (uintptr_t)a.w_ch_stride) & 15) == 0;
     const bool contig = w_aligned && a.nb1 == rb && (rb % 16) == 0;
     const int pitch = contig ? rb : ((rb + 16 + 15) & ~15);
-    // rows per stage: aim at ~32 KB per bulk transaction group, a multiple of NT, no more than the CTA has
-    int x = std::max(1, (32 * 1024) / (nt * pitch));
-    x = std::min(x, std::max(1, (rows_per_cta + nt - 1) / nt));
-    int R = nt * x, stage_bytes = 0, nstages = 0;
-    for (;;) {
-        stage_bytes = ((R * pitch + 15) & ~15) + 16;
-        const size_t per_stage = (size_t)stage_bytes + (size_t)wpt * nt * (R / nt) * M * 4 + 16;
-        nstages = (int)std::min<size_t>(8, SMEM_MAX / per_stage);
-        if (nstages >= 2 || R == 1) break;
-        if (x > 1) { x = (x + 1) / 2; R = nt * x; }
-        else if (nt > 1) { nt = nt / 2; R = nt; }
-        else break;
+    const size_t act_bytes = (size_t)M * bpr * ACT_ITEM;
+
+    // static knobs for tuning runs
+    static const int eR = env_int("B200_MMVQ_R", 0), eCW = env_int("B200_MMVQ_CW", 0), eNG = env_int("B200_MMVQ_NG", 0),
+                     eNS = env_int("B200_MMVQ_NS", 0), eCPS = env_int("B200_MMVQ_CPS", 0), eSB = env_int("B200_MMVQ_STAGE_KB", 32);
+
+    int cps = eCPS > 0 ? eCPS : (M <= 4 ? 2 : 1);                  // CTAs per SM the kernel is sized for
+    if (act_bytes + 2 * (size_t)pitch + 4096 > SMEM_2CTA) cps = 1;
+    const int nct_max = sms * cps;
+    const int rows_per_cta = (N + nct_max - 1) / nct_max;
+
+    // search rows-per-stage R and consumer geometry (CW warps per group x NG groups)
+    int bR = 1, bCW = 1, bNG = 1; double best = -1.0;
+    const int stage_cap = eSB * 1024;
+    for (int R = 1; R <= std::min(rows_per_cta, 256); ++R) {
+        if (R > 1 && (size_t)R * pitch > (size_t)stage_cap) break;
+        const int items = R * bpr;
+        const int stages_per_cta = (rows_per_cta + R - 1) / R;
+        for (int CW = 1; CW <= 8; ++CW) {
+            const int passes = (items + 32 * CW - 1) / (32 * CW);
+            const double util = (double)items / (passes * 32.0 * CW);
+            const int NG = std::max(1, std::min(8 / CW, stages_per_cta));
+            const int warps = CW * NG;
+            // tail efficiency: the last stage of a CTA is partially filled
+            const double fill = (double)rows_per_cta / (stages_per_cta * R);
+            const double bytes = std::min(1.0, (double)R * pitch / 16384.0);
+            const double score = util * fill * (0.5 + 0.5 * std::min(1.0, warps / 8.0)) * (0.75 + 0.25 * bytes);
+            if (score > best + 1e-9) { best = score; bR = R; bCW = CW; bNG = NG; }
+        }
     }
-    if (nstages < 1) return -3;    // a single row does not fit in shared memory
+    if (eR > 0) bR = eR;
+    if (eCW > 0) bCW = std::min(8, eCW);
+    if (eNG > 0) bNG = eNG;
+    if (bCW * bNG > 8) bNG = std::max(1, 8 / bCW);
+
+    const int R = bR;
+    const int stage_bytes = (((size_t)R * pitch + 15) & ~(size_t)15) + 288;   // slack: a partial tail item over-reads
     const int groups_per_cta = (rows_per_cta + R - 1) / R;
-    nstages = std::max(1, std::min(nstages, groups_per_cta));
+    const size_t fixed = act_bytes + (size_t)4 * R * nseg * M * 4 + 8 + 8 * 16 + 256;
+    auto stages_for = [&](size_t budget) -> int {
+        if (budget <= fixed) return 0;
+        return (int)std::min<size_t>(8, (budget - fixed) / ((size_t)stage_bytes + (size_t)R * nseg * M * 4));
+    };
+    int want = std::min(eNS > 0 ? eNS : 4, std::max(1, groups_per_cta));
+    want = std::max(want, std::min(bNG, groups_per_cta));
+    int nstages = std::min(want, stages_for(cps == 2 ? SMEM_2CTA : SMEM_1CTA));
+    if (nstages < std::min(2, want) && cps == 2) { cps = 1; nstages = std::min(want, stages_for(SMEM_1CTA)); }
+    if (nstages < 1) return -3;    // a single stage does not fit in shared memory
+    if (bNG > nstages) bNG = nstages;
+
+    static const int eGPS = env_int("B200_MMVQ_GRID_PER_SM", 0);
+    int gx = std::min(sms * (eGPS > 0 ? eGPS : cps), (N + R - 1) / R);
+    gx = std::max(gx, 1);
 
     p.R = R; p.nstages = nstages; p.pitch = pitch; p.stage_bytes = stage_bytes; p.contig = contig ? 1 : 0;
-    p.WPT = wpt; p.NT = nt;
-    c.M = M; c.CPT = cpt; c.A16 = (contig || w_aligned) ? 1 : 0;
+    p.CW = bCW; p.NG = bNG; p.BPR = bpr; p.G = G; p.act_bytes = (int)act_bytes;
+    p.rows_q = N / gx; p.rows_rem = N % gx;
+    c.M = M; c.A16 = (w_aligned && item_bytes(type) % 16 == 0) ? 1 : 0;
     c.grid = dim3(gx, std::max(1, a.nchannels), 1);
-    c.block = dim3(32 * (1 + wpt * nt), 1, 1);
-    c.smem = (size_t)nstages * stage_bytes + (((size_t)nstages * wpt * nt * (R / nt) * M + 1) & ~(size_t)1) * 4 + (size_t)nstages * 16;
+    c.block = dim3(288, 1, 1);   // producer warp + 8 warps (all quantise; CW*NG of them consume)
+    c.smem = (size_t)nstages * stage_bytes + act_bytes + (((size_t)nstages * R * nseg * M + 1) & ~(size_t)1) * 4 + (size_t)nstages * 16 + 8;
     return 0;
 }
 
@@ -96,6 +131,7 @@ static int mmvq_dispatch(int type, const mmvq_params & p, const mmvq_launch_cfg 
 }
 
 int g_launches = 0;
+int pdl_default() { static const int v = [] { const char * e = getenv("B200_PDL"); return e ? atoi(e) : 1; }(); return v; }
 
 }  // namespace b200
 
@@ -112,12 +148,13 @@ extern "C" int b200_mul_mat_vec_q_ex(const b200_mmvq_args * a, void * stream) {
     if (a->K <= 0 || a->K % block_elems(a->type) || a->N <= 0 || a->M <= 0) return -1;
     const int mmax = max_cols_per_launch(a->K);
     if (mmax <= 0) return -2;
-    static const int pdl_env = [] { const char * e = getenv("B200_PDL"); return e ? atoi(e) : 0; }();
+    const int pdl_env = pdl_default();
     for (int m0 = 0; m0 < a->M; m0 += mmax) {
         const int mc = std::min(mmax, a->M - m0);
         mmvq_params p = {};
         p.W = (const uint8_t *)a->W; p.nb1 = a->nb1;
-        p.X = a->X + (int64_t)m0 * a->xs; p.xs = a->xs;
+        p.X = a->X ? a->X + (int64_t)m0 * a->xs : nullptr; p.xs = a->xs;
+        p.Xq = a->Xq ? (const uint8_t *)a->Xq + (size_t)m0 * ((a->K + 255) / 256) * ACT_ITEM : nullptr; p.xq_ch_stride = a->xq_ch_stride;
         p.dst = a->dst + (int64_t)m0 * a->ds; p.ds = a->ds;
         p.N = a->N; p.K = a->K;
         p.w_ch_stride = a->w_ch_stride; p.x_ch_stride = a->x_ch_stride; p.d_ch_stride = a->d_ch_stride;

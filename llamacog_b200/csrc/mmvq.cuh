@@ -1,19 +1,26 @@
-// mmvq.cuh -- decode GEMV / skinny GEMM over GGUF block formats for B200 (sm_100a).
+// mmvq.cuh -- decode GEMV / skinny GEMM over GGUF block formats for B200 (sm_100a), v2.
 //
 // Replaces the reference's two-kernel path  quantize_q8_1 -> mul_mat_vec_q
 // (ggml-cuda/mmvq.cu:491-561, :140-224; quantize.cu:4-49) with ONE warp-specialised kernel:
 //
-//   warp 0      producer + epilogue: streams whole weight rows HBM -> shared memory with 1-D TMA
-//               bulk copies (cp.async.bulk, mbarrier complete_tx) through a ring of stages, and,
-//               when all consumers have released a stage, adds their per-warp partials in a fixed
-//               order and stores dst.
-//   warps 1..   consumers, organised in NT teams of WPT warps.  A team covers one row: thread t of
-//               the team owns units t, t+T, ... (T = 32*WPT) and keeps the q8_1-quantised
-//               activations of those units in REGISTERS for the whole kernel (fused prologue).
-//               Row r of a stage belongs to team r % NT.
+//   warp 0      producer + epilogue.  Streams whole weight rows HBM -> shared memory with 1-D TMA
+//               bulk copies (cp.async.bulk, mbarrier complete_tx, L2 evict-first) through a ring
+//               of stages of R rows; it starts BEFORE the programmatic-dependent-launch wait, so
+//               the first stages of this GEMV are in flight while the previous kernel drains.
+//               When the consumers release a stage it adds their partial sums in a fixed order
+//               and stores dst.
+//   warps 1..   consumers, NG groups of CW warps; group j owns stages j, j+NG, ...  They first
+//               quantise the M activation columns ONCE per CTA into shared memory (fused q8_1
+//               prologue, mmvq_units.cuh), then every thread takes 256-weight items
+//               (row, b) of its stage: lanes are consecutive items, so a row is a run of
+//               consecutive lanes and the row sum is a segmented xor-shuffle over G lanes
+//               (G = largest power of two dividing the items per row, <= 32) followed by
+//               BPR/G partials per row in shared memory.
 //
-// Weights are read exactly once, in 16-byte-aligned bulk transactions; activations are re-read
-// (fp32, from L2) once per team per CTA.  No __syncthreads after setup: all hand-offs are mbarriers.
+// Weights are read exactly once, in 16-byte-aligned bulk transactions.  The kernel is sized so
+// that two CTAs (this GEMV's, or this one and the next kernel's) fit one SM: <= 113 KB of shared
+// memory and 288 threads, which is what lets consecutive kernels of a decode step overlap under
+// PDL instead of leaving HBM idle at every kernel boundary.
 #pragma once
 #include "mmvq_units.cuh"
 
@@ -23,6 +30,8 @@ struct mmvq_params {
     const uint8_t * W;       // weight rows
     int64_t nb1;             // bytes between rows
     const float * X;         // activations, column m at X + m*xs
+    const uint8_t * Xq;      // optional: activations already quantised (mmvq_units.cuh layout, column stride BPR*400)
+    int64_t xq_ch_stride;    // bytes between channels of Xq
     int64_t xs;
     float * dst;             // dst[m*ds + row]
     int64_t ds;
@@ -38,81 +47,59 @@ struct mmvq_params {
     int R;                   // rows per stage
     int nstages;
     int pitch;               // bytes between rows inside a stage (== row bytes in contiguous mode)
-    int stage_bytes;         // R*pitch + 16 slack, multiple of 16
+    int stage_bytes;         // multiple of 16, >= R*pitch + 16
     int contig;              // 1: one bulk copy per stage (rows back to back, 16 B aligned)
-    int WPT, NT;             // warps per team, teams
+    int CW, NG;              // consumer warps per group, groups
+    int BPR;                 // items (256 weights) per row = ceil(K/256)
+    int G;                   // lanes per reduction segment (power of two dividing BPR)
+    int rows_q, rows_rem;    // N / gridDim.x, N % gridDim.x
+    int act_bytes;           // shared bytes of the activation area (M columns)
     int vec_ok;              // X columns 16-byte aligned -> float4 loads
-    int32_t * dbg_sumi;      // parity hook: when non-null, int32 block sums [M][N][K/32] are accumulated here
+    int32_t * dbg_sumi;      // parity hook: when non-null, int32 block sums [M][N][K/32] are stored here
 };
 
-// Multi-value warp reduction: NV values per lane (NV a power of two <= 32).  After the call lane l
-// holds the full sum of value index reduce_index<NV>(l) in v[0].  NV-1 + (5-log2 NV) shuffles.
-template <int NV> __device__ __forceinline__ void warp_reduce_multi(float (&v)[NV], int lane) {
-    int off = 16;
-#pragma unroll
-    for (int n = NV; n > 1; n >>= 1, off >>= 1) {
-        const bool up = lane & off;
-#pragma unroll
-        for (int i = 0; i < n / 2; ++i) {
-            const float send = up ? v[i] : v[i + n / 2];
-            const float keep = up ? v[i + n / 2] : v[i];
-            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-        }
-    }
-    for (; off > 0; off >>= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], off);
-}
-template <int NV> __device__ __forceinline__ int reduce_index(int lane) {
-    int idx = 0, off = 16;
-#pragma unroll
-    for (int n = NV; n > 1; n >>= 1, off >>= 1) if (lane & off) idx += n / 2;
-    return idx;
-}
-
-constexpr int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
-
-// rows a team accumulates before one multi-value reduction
-template <int M> struct row_batch { static constexpr int RB = M == 1 ? 4 : (M == 2 ? 2 : 1); };
-
-template <int TYPE, int M, int CPT, bool A16>
-__global__ void __launch_bounds__(544, 1) mmvq_kernel(const mmvq_params p) {
-    constexpr int G = unit_traits<TYPE>::G;
-    constexpr int RB = row_batch<M>::RB;
-    constexpr int NV = next_pow2(RB * M);
+template <int TYPE, int M, bool A16, bool DBG>
+__global__ void __launch_bounds__(288, (M <= 4 ? 2 : 1)) mmvq_kernel(const mmvq_params p) {
+    constexpr int IB = item_traits<TYPE>::BYTES;
     extern __shared__ __align__(128) uint8_t smem_raw[];
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int U = p.K >> 5;                        // units per row
-    const int T = 32 * p.WPT;                      // threads per team
-    const int ncw = p.WPT * p.NT;                  // consumer warps
-    const int rows_pt = p.R / p.NT;                // rows per team per stage (R is a multiple of NT*RB)
+    const int ncw = p.CW * p.NG;                   // consumer warps
+    const int nb32 = p.K >> 5;
+    const int nseg = p.BPR / p.G;
+    const uint32_t acs = (uint32_t)p.BPR * ACT_ITEM;   // bytes between activation columns
 
-    // shared memory carve-up: [stages][partials][barriers]
+    // shared memory: [stages][activations][partials][barriers]
     uint8_t * stages = smem_raw;
-    float * partials = reinterpret_cast<float *>(smem_raw + (size_t)p.nstages * p.stage_bytes);   // [nstages][ncw][rows_pt*M]
-    // mbarriers need 8-byte alignment: round the partials area up to an even number of floats
-    uint64_t * bars = reinterpret_cast<uint64_t *>(partials + (((size_t)p.nstages * ncw * rows_pt * M + 1) & ~(size_t)1));
-    const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * p.nstages;
-    const int part_stage = ncw * rows_pt * M;
+    uint8_t * act = smem_raw + (size_t)p.nstages * p.stage_bytes;
+    float * partials = reinterpret_cast<float *>(act + p.act_bytes);          // [nstages][R][nseg][M]
+    const int part_stage = p.R * nseg * M;
+    uint64_t * bars = reinterpret_cast<uint64_t *>(partials + (((size_t)p.nstages * part_stage + 1) & ~(size_t)1));
+    const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * p.nstages, actbar = empty0 + 8 * p.nstages;
 
     // channel (batch / expert) addressing
     const int ch = blockIdx.y;
-    const int wsel = p.ids ? p.ids[ch] : ch / p.w_ch_div;
+    int wsel = 0, xch = 0;
+    if (gridDim.y > 1 || p.ids) { wsel = p.ids ? p.ids[ch] : ch / p.w_ch_div; xch = ch % p.x_ch_mod; }
     const uint8_t * Wc = p.W + (int64_t)wsel * p.w_ch_stride;
-    const float * Xc = p.X + (int64_t)(ch % p.x_ch_mod) * p.x_ch_stride;
+    const float * Xc = p.X + (int64_t)xch * p.x_ch_stride;
     float * Dc = p.dst + (int64_t)ch * p.d_ch_stride;
 
-    // balanced contiguous row range of this CTA
-    const int nct = gridDim.x, cta = blockIdx.x;
-    const int row_lo = (int)(((int64_t)p.N * cta) / nct), row_hi = (int)(((int64_t)p.N * (cta + 1)) / nct);
-    const int nrows = row_hi - row_lo;
+    // balanced contiguous row range of this CTA: the first rows_rem CTAs take one extra row
+    const int cta = blockIdx.x;
+    const int row_lo = cta * p.rows_q + min(cta, p.rows_rem);
+    const int nrows = p.rows_q + (cta < p.rows_rem ? 1 : 0);
+    const int row_hi = row_lo + nrows;
     const int ngroups = (nrows + p.R - 1) / p.R;
     const int rb = (p.K / fmt<TYPE>::BE) * fmt<TYPE>::BB;   // payload bytes per row
 
     if (tid == 0) {
-        for (int s = 0; s < p.nstages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, ncw); }
+        for (int s = 0; s < p.nstages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, p.CW); }
+        mbar_init(actbar, 1);
         mbar_fence_init();
     }
     __syncthreads();
+    pdl_trigger();            // dependents may start their own prologue (weight prefetch) now
 
     if (warp == 0) {
         // ================= producer + epilogue warp =================
@@ -141,7 +128,12 @@ __global__ void __launch_bounds__(544, 1) mmvq_kernel(const mmvq_params p) {
         };
         // weights do not depend on the previous kernel: start streaming before the PDL wait
         if (lane == 0) for (int g = 0; g < min(ngroups, p.nstages); ++g) issue(g);
-        pdl_wait();   // dst may still be read by the previous grid
+        pdl_wait();   // dst may still be read by the previous grid; Xq is written by it
+        if (p.Xq && lane == 0) {
+            const uint8_t * xq = p.Xq + (int64_t)xch * p.xq_ch_stride;
+            mbar_expect_tx(actbar, (uint32_t)M * acs);
+            for (int m = 0; m < M; ++m) bulk_g2s(smem_u32(act) + m * acs, xq + (size_t)m * acs, acs, actbar);
+        }
         for (int g = 0; g < ngroups; ++g) {
             const int slot = g % p.nstages;
             mbar_wait(empty0 + 8 * slot, (g / p.nstages) & 1);
@@ -149,70 +141,65 @@ __global__ void __launch_bounds__(544, 1) mmvq_kernel(const mmvq_params p) {
             const float * ps = partials + (size_t)slot * part_stage;
             for (int o = lane; o < nr * M; o += 32) {
                 const int r = o / M, m = o - r * M;
-                const int team = r % p.NT, rt = r / p.NT;       // row rt of that team's share
                 float s = 0.0f;
-                for (int w = 0; w < p.WPT; ++w) s += ps[((team * p.WPT + w) * rows_pt + rt) * M + m];
+                for (int sg = 0; sg < nseg; ++sg) s += ps[(r * nseg + sg) * M + m];
                 Dc[(int64_t)m * p.ds + r0 + r] = s;
             }
             __syncwarp();
             if (lane == 0 && g + p.nstages < ngroups) issue(g + p.nstages);
         }
-        pdl_trigger();
-    } else if (warp <= ncw) {
+    } else {
         // ================= consumer warps =================
-        const int cw = warp - 1, team = cw / p.WPT, tt = (cw % p.WPT) * 32 + lane;   // thread index inside team
-        pdl_wait();   // activations come from the previous kernel
-        act_regs<G> a[CPT][M];
-#pragma unroll
-        for (int c = 0; c < CPT; ++c) {
-            const int u = tt + c * T;
-#pragma unroll
-            for (int m = 0; m < M; ++m) quantize_unit<TYPE>(Xc + (int64_t)m * p.xs, u, u < U, p.vec_ok, a[c][m]);
+        // all eight take part in the activation prologue; CW*NG of them go on to the dot products
+        const int cw = warp - 1, grp = cw / p.CW, wig = cw - grp * p.CW;   // warp inside its group
+        const int T = 32 * p.CW;
+        if (p.Xq) {
+            if (cw >= ncw) return;
+            mbar_wait(actbar, 0);
+        } else {
+            pdl_wait();   // activations come from the previous kernel
+            quantize_acts(Xc, p.xs, M, nb32, p.vec_ok, act, acs, tid - 32, 256);
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (cw >= ncw) return;
         }
-        const int ridx = reduce_index<NV>(lane);
-        for (int g = 0; g < ngroups; ++g) {
+        const uint32_t act0 = smem_u32(act);
+        const int dT_row = T / p.BPR, dT_b = T - dT_row * p.BPR;       // item-index step per pass
+        for (int g = grp; g < ngroups; g += p.NG) {
             const int slot = g % p.nstages;
             const int r0 = row_lo + g * p.R, nr = min(p.R, row_hi - r0);
+            const int nitems = nr * p.BPR;
             mbar_wait(full0 + 8 * slot, (g / p.nstages) & 1);
             const uint32_t sbase = smem_u32(stages + (size_t)slot * p.stage_bytes);
-            float * pw = partials + (size_t)slot * part_stage + (size_t)cw * rows_pt * M;
-            for (int rt0 = 0; rt0 < rows_pt; rt0 += RB) {
-                float v[NV];
+            float * pw = partials + (size_t)slot * part_stage;
+            int i = wig * 32 + lane;
+            int row = i / p.BPR, b = i - row * p.BPR;
+            for (int i0 = wig * 32; i0 < nitems; i0 += T) {
+                float acc[M];
 #pragma unroll
-                for (int i = 0; i < NV; ++i) v[i] = 0.0f;
+                for (int m = 0; m < M; ++m) acc[m] = 0.0f;
+                const bool valid = i < nitems;
+                if (valid) {
+                    uint32_t wp = sbase + (uint32_t)row * p.pitch + (uint32_t)b * IB;
+                    if (!p.contig) wp += (uint32_t)((uint64_t)(Wc + (int64_t)(r0 + row) * p.nb1) & 15);
+                    const int nblk = min(8, nb32 - 8 * b);
+                    int32_t * dbg = DBG ? p.dbg_sumi + (int64_t)(r0 + row) * nb32 + 8 * b : nullptr;
+                    item_dot<TYPE, M, A16, DBG>(wp, act0 + (uint32_t)b * ACT_ITEM, acs, nblk, acc, dbg, (int64_t)p.N * nb32);
+                }
+                // segmented row sum over G consecutive lanes (G is warp-uniform)
 #pragma unroll
-                for (int rbi = 0; rbi < RB; ++rbi) {
-                    const int r = (rt0 + rbi) * p.NT + team;     // row inside the stage
-                    if (r < nr) {
-                        uint32_t rowp = sbase + (uint32_t)r * p.pitch;
-                        if (!p.contig) rowp += (uint32_t)((uint64_t)(Wc + (int64_t)(r0 + r) * p.nb1) & 15);
-                        float acc[M];
+                for (int o = 1; o < 32; o <<= 1) {
+                    if (o < p.G) {
 #pragma unroll
-                        for (int m = 0; m < M; ++m) acc[m] = 0.0f;
-#pragma unroll
-                        for (int c = 0; c < CPT; ++c) {
-                            const int u = tt + c * T;
-                            if (u < U) {
-                                if (p.dbg_sumi) {
-                                    unit_ints<G> ints[M];
-                                    unit_dot<TYPE, M, A16>(rowp, u, a[c], acc, ints);
-                                    for (int m = 0; m < M; ++m) for (int gg = 0; gg < G; ++gg)
-                                        atomicAdd(p.dbg_sumi + ((int64_t)m * p.N + r0 + r) * U + unit_group_elem0<TYPE>(u, gg) / 32, ints[m].dot[gg]);
-                                } else {
-                                    unit_dot<TYPE, M, A16>(rowp, u, a[c], acc);
-                                }
-                            }
-                        }
-#pragma unroll
-                        for (int m = 0; m < M; ++m) v[rbi * M + m] = acc[m];
+                        for (int m = 0; m < M; ++m) acc[m] += __shfl_xor_sync(0xffffffffu, acc[m], o);
                     }
                 }
-                warp_reduce_multi<NV>(v, lane);
-                // lane l holds value index ridx = rbi*M + m (lanes with equal ridx hold the same sum)
-                if (ridx < RB * M && (lane & (32 / NV - 1)) == 0) {
-                    const int rbi = ridx / M, m = ridx - rbi * M;
-                    if (rt0 + rbi < rows_pt) pw[(rt0 + rbi) * M + m] = v[0];
+                if (valid && (lane & (p.G - 1)) == 0) {
+                    float * dstp = pw + (row * nseg + b / p.G) * M;
+#pragma unroll
+                    for (int m = 0; m < M; ++m) dstp[m] = acc[m];
                 }
+                i += T; row += dT_row; b += dT_b;
+                if (b >= p.BPR) { b -= p.BPR; ++row; }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(empty0 + 8 * slot);

@@ -6,7 +6,7 @@
 namespace b200 {
 
 struct mmvq_launch_cfg {
-    int M, CPT, A16;
+    int M, A16;
     dim3 grid, block;
     size_t smem;
     int pdl;
@@ -14,9 +14,9 @@ struct mmvq_launch_cfg {
 
 template <int TYPE> int mmvq_launch_type(const mmvq_params & p, const mmvq_launch_cfg & c, cudaStream_t stream);
 
-template <int TYPE, int M, int CPT, bool A16>
+template <int TYPE, int M, bool A16, bool DBG>
 static int mmvq_launch_one(const mmvq_params & p, const mmvq_launch_cfg & c, cudaStream_t stream) {
-    auto kern = mmvq_kernel<TYPE, M, CPT, A16>;
+    auto kern = mmvq_kernel<TYPE, M, A16, DBG>;
     static int smem_set[16] = {0};   // per device
     int dev = 0;
     B200_CUDA_CHECK(cudaGetDevice(&dev));
@@ -34,19 +34,17 @@ static int mmvq_launch_one(const mmvq_params & p, const mmvq_launch_cfg & c, cud
     return 0;
 }
 
-#define B200_MMVQ_CASE(MM, CC) \
-    if (c.M == MM && c.CPT == CC) return c.A16 ? mmvq_launch_one<TYPE, MM, CC, A16_OK>(p, c, stream) : mmvq_launch_one<TYPE, MM, CC, false>(p, c, stream);
+#define B200_MMVQ_CASE(MM) \
+    if (c.M == MM) return p.dbg_sumi ? mmvq_launch_one<TYPE, MM, false, true>(p, c, stream) : \
+        c.A16 ? mmvq_launch_one<TYPE, MM, A16_OK, false>(p, c, stream) : mmvq_launch_one<TYPE, MM, false, false>(p, c, stream);
 
-// A16 only changes code for the 16-byte-multiple block formats (Q4_K, Q5_K)
+// A16 (16-byte aligned items, LDS.128) exists for every format whose item size is a multiple of 16
 #define B200_MMVQ_DEFINE(TYPE_) \
     template <> int mmvq_launch_type<TYPE_>(const mmvq_params & p, const mmvq_launch_cfg & c, cudaStream_t stream) { \
         constexpr int TYPE = TYPE_; \
-        constexpr bool A16_OK = (TYPE_ == T_Q4_K || TYPE_ == T_Q5_K); \
-        B200_MMVQ_CASE(1, 1) B200_MMVQ_CASE(1, 2) B200_MMVQ_CASE(1, 4) B200_MMVQ_CASE(1, 8) \
-        B200_MMVQ_CASE(2, 1) B200_MMVQ_CASE(2, 2) B200_MMVQ_CASE(2, 4) \
-        B200_MMVQ_CASE(3, 1) B200_MMVQ_CASE(3, 2) \
-        B200_MMVQ_CASE(4, 1) B200_MMVQ_CASE(4, 2) \
-        B200_MMVQ_CASE(5, 1) B200_MMVQ_CASE(6, 1) B200_MMVQ_CASE(7, 1) B200_MMVQ_CASE(8, 1) \
+        constexpr bool A16_OK = (TYPE_ != T_Q6_K); \
+        B200_MMVQ_CASE(1) B200_MMVQ_CASE(2) B200_MMVQ_CASE(3) B200_MMVQ_CASE(4) \
+        B200_MMVQ_CASE(5) B200_MMVQ_CASE(6) B200_MMVQ_CASE(7) B200_MMVQ_CASE(8) \
         return -1; \
     }
 

@@ -1,224 +1,296 @@
-// mmvq_units.cuh -- per-format "unit" arithmetic of the decode GEMV.
+// mmvq_units.cuh -- per-format arithmetic of the decode GEMV (v2: one 256-weight ITEM per thread).
 //
-// A UNIT is 32 weights of one row that one thread multiplies with 32 activations it keeps in
-// registers.  Every format has 8 units per 256 weights, so a row of K weights has K/32 units:
-//   Q4_0/Q8_0 : unit u = block u                      -> 1 group of 32 consecutive elements
-//   Q4_K/Q5_K : unit u = 16-byte chunk c=u%8 of qs    -> 2 groups of 16 (low / high nibbles)
-//   Q6_K      : unit u = (half h, 8 lanes l0) of ql/qh -> 4 groups of 8
+// An ITEM is 256 consecutive weights of one row: one K-quant super-block (Q4_K 144 B, Q5_K 176 B,
+// Q6_K 210 B) or eight consecutive 32-blocks (Q4_0 144 B, Q8_0 272 B; the last item of a row may
+// hold fewer when K % 256 != 0).  One thread multiplies one item with the matching 256 activations
+// of M columns, so the K-quant header (fp16 scales, 6-bit sub-scales) is unpacked once per 256
+// weights, and 144/176/272-byte items are read with conflict-free LDS.128 (odd multiples of 16 B).
+//
 // Activations are quantised to q8_1 semantics (d = amax/127, q = roundf(x/d); reference
-// ggml-cuda/quantize.cu:4-49) directly into registers -- the fused prologue of north-star item (2).
+// ggml-cuda/quantize.cu:4-49) ONCE per CTA into shared memory -- the fused prologue of north-star
+// item (2) -- in this layout, per column, per 32-block: 48 bytes
+//     q[32] int8 | d8 (fp32 value of the fp16-rounded scale) | dsq | m32a | m32b
+// and 400 bytes per item (8 x 48 + 16 pad: an odd multiple of 16 B, so that lanes reading
+// consecutive items with LDS.128 hit distinct banks).  The tail serves every weight format:
+//     dsq  = d8 * sum q (fp32)            Q4_K, Q5_K: the dmin term (vecdotq.cuh:376,437)
+//     m32a = -32 * sum q[0..15]  (int)    Q6_K: folds __vsubss4(., 32) (vecdotq.cuh:492)
+//     m32b = -32 * sum q[16..31] (int)    Q4_0: (m32a + m32b) >> 2 = -8 * sum q (vecdotq.cuh:43)
+// The same layout is produced in global memory by quantize_acts_kernel (quantize.cu) for GEMVs that
+// take pre-quantised activations (large K, small N: per-CTA re-quantisation would cost more than
+// the dot products there).
 // The integer dot products are those of reference ggml-cuda/vecdotq.cuh:25-44 (q4_0), 153-165
-// (q8_0), 359-381 (q4_K), 415-444 (q5_K), 478-498 (q6_K); they are order independent and therefore
-// bit-exact; the fp32 combination order is ours.
+// (q8_0), 359-381 (q4_K), 415-444 (q5_K), 478-498 (q6_K); integer sums are order independent and
+// therefore bit-exact; the fp32 combination order is ours.
 #pragma once
 #include "common.cuh"
 
 namespace b200 {
 
-template <int TYPE> struct unit_traits;
-template <> struct unit_traits<T_Q4_0> { static constexpr int G = 1; };
-template <> struct unit_traits<T_Q8_0> { static constexpr int G = 1; };
-template <> struct unit_traits<T_Q4_K> { static constexpr int G = 2; };
-template <> struct unit_traits<T_Q5_K> { static constexpr int G = 2; };
-template <> struct unit_traits<T_Q6_K> { static constexpr int G = 4; };
+template <int TYPE> struct item_traits;
+template <> struct item_traits<T_Q4_0> { static constexpr int BYTES = 144; };
+template <> struct item_traits<T_Q8_0> { static constexpr int BYTES = 272; };
+template <> struct item_traits<T_Q4_K> { static constexpr int BYTES = 144; };
+template <> struct item_traits<T_Q5_K> { static constexpr int BYTES = 176; };
+template <> struct item_traits<T_Q6_K> { static constexpr int BYTES = 210; };
 
-// element index (within the row) of the first element of group g of unit u
-template <int TYPE> __device__ __forceinline__ int unit_group_elem0(int u, int g) {
-    if constexpr (TYPE == T_Q4_0 || TYPE == T_Q8_0) { return 32 * u; }
-    else if constexpr (TYPE == T_Q4_K || TYPE == T_Q5_K) {
-        const int b = u >> 3, c = u & 7;
-        return 256 * b + 64 * (c >> 1) + 16 * (c & 1) + 32 * g;
-    } else {  // Q6_K
-        const int b = u >> 3, c = u & 7;
-        return 256 * b + 128 * (c >> 2) + 8 * (c & 3) + 32 * g;
-    }
-}
-
-// quantised activations of one unit for one activation column
-template <int G> struct act_regs {
-    int   q[8];     // 32 int8, group-major
-    float d8[G];    // q8_1 scale of the 32-block each group belongs to
-    int   sq[G];    // sum of this unit's q inside each group (exact int; the "dot2" of vecdotq.cuh:376)
-};
-
-// Quantise the 32 activations of unit u (column pointer x, K valid elements) into registers.
-// Threads of the same q8_1 block are G adjacent lanes, so amax is completed with xor-shuffles.
-// Must be called by all 32 lanes (inactive units pass valid=false and contribute zeros).
-template <int TYPE> __device__ __forceinline__ void quantize_unit(
-        const float * __restrict__ x, int u, bool valid, bool vec_ok, act_regs<unit_traits<TYPE>::G> & a) {
-    constexpr int G = unit_traits<TYPE>::G, E = 32 / G;   // elements per group
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-        float v[E];
-        if (valid) {
-            const float * src = x + unit_group_elem0<TYPE>(u, g);
-            if (vec_ok) {
-#pragma unroll
-                for (int i = 0; i < E / 4; ++i) {
-                    const float4 t = __ldg(reinterpret_cast<const float4 *>(src) + i);
-                    v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < E; ++i) v[i] = __ldg(src + i);
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < E; ++i) v[i] = 0.0f;
-        }
-        float amax = 0.0f;
-#pragma unroll
-        for (int i = 0; i < E; ++i) amax = fmaxf(amax, fabsf(v[i]));
-#pragma unroll
-        for (int o = 1; o < G; o <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-        const float d = __fdiv_rn(amax, 127.0f);
-        int sq = 0;
-#pragma unroll
-        for (int i = 0; i < E / 4; ++i) {
-            int packed = 0;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int qi = amax == 0.0f ? 0 : (int)roundf(__fdiv_rn(v[4 * i + j], d));
-                sq += qi;
-                packed |= (qi & 0xFF) << (8 * j);
-            }
-            a.q[g * (E / 4) + i] = packed;
-        }
-        a.d8[g] = __half2float(__float2half_rn(d));   // q8_1 stores d as binary16 (reference quantize.cu:47)
-        a.sq[g] = sq;
-    }
-}
+constexpr int ACT_BLK = 48;      // bytes per 32-block of quantised activations in shared memory
+constexpr int ACT_ITEM = 400;    // bytes per 256-element item (8 * 48 + 16)
 
 // exact int -> float for |i| < 2^22 on the FMA/ALU pipes (avoids the quarter-rate I2F path)
 __device__ __forceinline__ float i2f_small(int i) {
     return __int_as_float(0x4B400000 + i) - 12582912.0f;
 }
+// byte k of x -> float, exact (PRMT + FADD)
+__device__ __forceinline__ float byte2f(uint32_t x, int k) {
+    return __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7440 + k)) - 8388608.0f;
+}
+// unsigned bytes x signed bytes dot product (the x16 nibble trick needs u8 weights)
+__device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {
+    int d; asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
+}
+__device__ __forceinline__ int dp4a_ss(int a, int b, int c) { return __dp4a(a, b, c); }
 
-// 6-bit (scale,min) pairs of sub-blocks 2j and 2j+1 of a K-quant header (reference
-// ggml-quants.c:625-632), both at once: returns sc = {sc[2j], sc[2j+1]} and mn likewise as bytes
-// 0 and 1 of the outputs.  w0,w1,w2 are the three 32-bit words of scales[12].
-__device__ __forceinline__ void k4_scales_pair(uint32_t w0, uint32_t w1, uint32_t w2, int j, uint32_t & sc2, uint32_t & mn2) {
-    const int sh = 16 * (j & 1);
-    const uint32_t h0 = (w0 >> sh) & 0xFFFFu, h1 = (w1 >> sh) & 0xFFFFu, h2 = (w2 >> sh) & 0xFFFFu;
-    const uint32_t sc_lo = h0 & 0x3F3Fu, mn_lo = h1 & 0x3F3Fu;
-    const uint32_t sc_hi = (h2 & 0x0F0Fu) | ((h0 >> 2) & 0x3030u);
-    const uint32_t mn_hi = ((h2 >> 4) & 0x0F0Fu) | ((h1 >> 2) & 0x3030u);
-    sc2 = j < 2 ? sc_lo : sc_hi;
-    mn2 = j < 2 ? mn_lo : mn_hi;
+// N consecutive 32-bit words from shared memory; A16: address is 16-byte aligned and N % 4 == 0
+template <int N, bool A16> __device__ __forceinline__ void lds_words(uint32_t saddr, int (&w)[N]) {
+    if constexpr (A16 && N % 4 == 0) {
+#pragma unroll
+        for (int i = 0; i < N / 4; ++i) {
+            const int4 t = lds128(saddr + 16 * i);
+            w[4 * i] = t.x; w[4 * i + 1] = t.y; w[4 * i + 2] = t.z; w[4 * i + 3] = t.w;
+        }
+    } else {
+        lds_words_a2<N>(saddr, w);
+    }
 }
 
-// Result of the integer part of one unit x one column, kept so that the parity tests can read
-// the exact int32 sums out of the very code the production kernel runs.
-template <int G> struct unit_ints { int dot[G]; };
+// activations of one 32-block of one column: 8 words of int8 + (d8, aux0, aux1)
+struct act_blk { int q[8]; float d8, dsq; int m32a, m32b; };
+__device__ __forceinline__ void lds_act(uint32_t ap, act_blk & a) {
+    const int4 t0 = lds128(ap), t1 = lds128(ap + 16), t2 = lds128(ap + 32);
+    a.q[0] = t0.x; a.q[1] = t0.y; a.q[2] = t0.z; a.q[3] = t0.w;
+    a.q[4] = t1.x; a.q[5] = t1.y; a.q[6] = t1.z; a.q[7] = t1.w;
+    a.d8 = __int_as_float(t2.x); a.dsq = __int_as_float(t2.y); a.m32a = t2.z; a.m32b = t2.w;
+}
 
-// ---- the per-format unit dot products -------------------------------------------------------
-// rowp: shared-memory byte address of the row (2-byte aligned; 16-byte aligned when A16).
-// Adds this unit's contribution for M columns to acc[M]; optionally exports the int sums.
-template <int TYPE, int M, bool A16>
-__device__ __forceinline__ void unit_dot(uint32_t rowp, int u, const act_regs<unit_traits<TYPE>::G> (&a)[M],
-                                         float (&acc)[M], unit_ints<unit_traits<TYPE>::G> * ints = nullptr) {
+// halfword h (static index) of a register array of words
+template <int NW> __device__ __forceinline__ uint32_t halfword(const int (&w)[NW], int h) {
+    return (h & 1) ? ((uint32_t)w[h >> 1] >> 16) : ((uint32_t)w[h >> 1] & 0xFFFFu);
+}
+// 32-bit word starting at halfword h (static index)
+template <int NW> __device__ __forceinline__ int word_at_half(const int (&w)[NW], int h) {
+    return (h & 1) ? (int)__funnelshift_r((uint32_t)w[h >> 1], (uint32_t)w[(h >> 1) + 1], 16) : w[h >> 1];
+}
+
+// ---- the per-format item dot products ---------------------------------------------------------
+// wp: shared byte address of the item (2-byte aligned; 16-byte aligned when A16)
+// ap: shared byte address of the item's activations of column 0; acs: bytes between columns
+// nblk: valid 32-blocks in this item (8 except the tail item of Q4_0/Q8_0 rows)
+// dbg: optional global pointer to this item's 8 int32 block sums of column 0; dms: ints between columns
+template <int TYPE, int M, bool A16, bool DBG>
+__device__ __forceinline__ void item_dot(uint32_t wp, uint32_t ap, uint32_t acs, int nblk, float (&acc)[M],
+                                         int32_t * dbg, int64_t dms) {
     if constexpr (TYPE == T_Q4_0) {
-        const uint32_t bp = rowp + 18u * u;
-        int w[4];
-        const float d = half_bits_to_float(lds16(bp));
-        lds_words_a2<4>(bp + 2, w);
-        int lo[4], hi[4];
+        int w[36];
+        lds_words<36, A16>(wp, w);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { lo[i] = w[i] & 0x0F0F0F0F; hi[i] = (w[i] >> 4) & 0x0F0F0F0F; }
+        for (int i = 0; i < 8; ++i) {
+            if (i < nblk) {
+                const float dw = half_bits_to_float(halfword<36>(w, 9 * i));
+                uint32_t lo[4], hi[4];
 #pragma unroll
-        for (int m = 0; m < M; ++m) {
-            int s = 0;
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t q = (uint32_t)word_at_half<36>(w, 9 * i + 1 + 2 * j);
+                    lo[j] = q & 0x0F0F0F0Fu; hi[j] = q & 0xF0F0F0F0u;
+                }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) { s = __dp4a(lo[i], a[m].q[i], s); s = __dp4a(hi[i], a[m].q[4 + i], s); }
-            if (ints) ints[m].dot[0] = s;
-            acc[m] = fmaf(d * a[m].d8[0], i2f_small(s - 8 * a[m].sq[0]), acc[m]);
+                for (int m = 0; m < M; ++m) {
+                    act_blk a; lds_act(ap + m * acs + i * ACT_BLK, a);
+                    int s0 = 0, s1 = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { s0 = dp4a_us(lo[j], a.q[j], s0); s1 = dp4a_us(hi[j], a.q[4 + j], s1); }
+                    const int s = s0 + (s1 >> 4);
+                    if constexpr (DBG) dbg[m * dms + i] = s;
+                    acc[m] = fmaf(dw * a.d8, i2f_small(s + ((a.m32a + a.m32b) >> 2)), acc[m]);
+                }
+            }
         }
     } else if constexpr (TYPE == T_Q8_0) {
-        const uint32_t bp = rowp + 34u * u;
-        int w[8];
-        const float d = half_bits_to_float(lds16(bp));
-        lds_words_a2<8>(bp + 2, w);
+        int w[68];
+        lds_words<68, A16>(wp, w);
 #pragma unroll
-        for (int m = 0; m < M; ++m) {
-            int s = 0;
+        for (int i = 0; i < 8; ++i) {
+            if (i < nblk) {
+                const float dw = half_bits_to_float(halfword<68>(w, 17 * i));
+                int q[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) s = __dp4a(w[i], a[m].q[i], s);
-            if (ints) ints[m].dot[0] = s;
-            acc[m] = fmaf(d * a[m].d8[0], i2f_small(s), acc[m]);
+                for (int j = 0; j < 8; ++j) q[j] = word_at_half<68>(w, 17 * i + 1 + 2 * j);
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    act_blk a; lds_act(ap + m * acs + i * ACT_BLK, a);
+                    int s = 0;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) s = dp4a_ss(q[j], a.q[j], s);
+                    if constexpr (DBG) dbg[m * dms + i] = s;
+                    acc[m] = fmaf(dw * a.d8, i2f_small(s), acc[m]);
+                }
+            }
         }
     } else if constexpr (TYPE == T_Q4_K || TYPE == T_Q5_K) {
-        constexpr int BB = fmt<TYPE>::BB, QS0 = (TYPE == T_Q4_K) ? 16 : 48;
-        const int c = u & 7, j = c >> 1;
-        const uint32_t bp = rowp + (uint32_t)BB * (u >> 3);
-        int hd[4], w[4];
-        if constexpr (A16) {
-            const int4 t = lds128(bp); hd[0] = t.x; hd[1] = t.y; hd[2] = t.z; hd[3] = t.w;
-            const int4 q = lds128(bp + QS0 + 16 * c); w[0] = q.x; w[1] = q.y; w[2] = q.z; w[3] = q.w;
-        } else {
-            lds_words_a2<4>(bp, hd);
-            lds_words_a2<4>(bp + QS0 + 16 * c, w);
-        }
-        int lo[4], hi[4];
+        constexpr int QS0 = (TYPE == T_Q4_K) ? 16 : 48;
+        int hd[4];
+        lds_words<4, A16>(wp, hd);
+        const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&hd[0]));
+        // 6-bit (scale, min) pairs, reference ggml-quants.c:625-632, four at a time as packed bytes
+        const uint32_t h1 = (uint32_t)hd[1], h2 = (uint32_t)hd[2], h3 = (uint32_t)hd[3];
+        const uint32_t sc4[2] = { h1 & 0x3F3F3F3Fu, (h3 & 0x0F0F0F0Fu) | ((h1 >> 2) & 0x30303030u) };
+        const uint32_t mn4[2] = { h2 & 0x3F3F3F3Fu, ((h3 >> 4) & 0x0F0F0F0Fu) | ((h2 >> 2) & 0x30303030u) };
+        int qh[8];
+        if constexpr (TYPE == T_Q5_K) lds_words<8, A16>(wp + 16, qh);
+        float accd[M], accm[M];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { lo[i] = w[i] & 0x0F0F0F0F; hi[i] = (w[i] >> 4) & 0x0F0F0F0F; }
-        if constexpr (TYPE == T_Q5_K) {
-            int qh[4];
-            if constexpr (A16) { const int4 t = lds128(bp + 16 + 16 * (c & 1)); qh[0] = t.x; qh[1] = t.y; qh[2] = t.z; qh[3] = t.w; }
-            else { lds_words_a2<4>(bp + 16 + 16 * (c & 1), qh); }
+        for (int m = 0; m < M; ++m) { accd[m] = 0.0f; accm[m] = 0.0f; }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                lo[i] |= ((qh[i] >> (2 * j)) & 0x01010101) << 4;
-                hi[i] |= ((qh[i] >> (2 * j + 1)) & 0x01010101) << 4;
+        for (int p = 0; p < 4; ++p) {
+            int w[8];
+            lds_words<8, A16>(wp + QS0 + 32 * p, w);
+            uint32_t lo[8], hi[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if constexpr (TYPE == T_Q4_K) {
+                    lo[j] = (uint32_t)w[j] & 0x0F0F0F0Fu;
+                    hi[j] = (uint32_t)w[j] & 0xF0F0F0F0u;           // 16 x nibble, divided out after the dot
+                } else {
+                    const uint32_t b0 = (p < 2 ? ((uint32_t)qh[j] << (4 - 2 * p)) : ((uint32_t)qh[j] >> (2 * p - 4))) & 0x10101010u;
+                    const uint32_t b1 = (p < 2 ? ((uint32_t)qh[j] << (3 - 2 * p)) : ((uint32_t)qh[j] >> (2 * p - 3))) & 0x10101010u;
+                    lo[j] = ((uint32_t)w[j] & 0x0F0F0F0Fu) | b0;
+                    hi[j] = (((uint32_t)w[j] >> 4) & 0x0F0F0F0Fu) | b1;
+                }
+            }
+            const float sc0 = byte2f(sc4[p >> 1], 2 * (p & 1)), sc1 = byte2f(sc4[p >> 1], 2 * (p & 1) + 1);
+            const float mn0 = byte2f(mn4[p >> 1], 2 * (p & 1)), mn1 = byte2f(mn4[p >> 1], 2 * (p & 1) + 1);
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+                act_blk a0, a1;
+                lds_act(ap + m * acs + (2 * p) * ACT_BLK, a0);
+                lds_act(ap + m * acs + (2 * p + 1) * ACT_BLK, a1);
+                int s0 = 0, s1 = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { s0 = dp4a_us(lo[j], a0.q[j], s0); s1 = dp4a_us(hi[j], a1.q[j], s1); }
+                if constexpr (TYPE == T_Q4_K) s1 >>= 4;
+                if constexpr (DBG) { dbg[m * dms + 2 * p] = s0; dbg[m * dms + 2 * p + 1] = s1; }
+                accd[m] = fmaf(a0.d8, i2f_small(s0) * sc0, accd[m]);
+                accd[m] = fmaf(a1.d8, i2f_small(s1) * sc1, accd[m]);
+                accm[m] = fmaf(a0.dsq, mn0, accm[m]);
+                accm[m] = fmaf(a1.dsq, mn1, accm[m]);
             }
         }
-        uint32_t sc2, mn2;
-        k4_scales_pair((uint32_t)hd[1], (uint32_t)hd[2], (uint32_t)hd[3], j, sc2, mn2);
-        const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&hd[0]));
-        const int sc0 = sc2 & 0xFF, sc1 = sc2 >> 8, mn0 = mn2 & 0xFF, mn1 = mn2 >> 8;
 #pragma unroll
-        for (int m = 0; m < M; ++m) {
-            int s0 = 0, s1 = 0;
+        for (int m = 0; m < M; ++m) acc[m] += dm.x * accd[m] - dm.y * accm[m];
+    } else {  // Q6_K: ql[128] qh[64] scales[16] d
+        const float d = half_bits_to_float(lds16(wp + 208));
+        float acc6[M];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) { s0 = __dp4a(lo[i], a[m].q[i], s0); s1 = __dp4a(hi[i], a[m].q[4 + i], s1); }
-            if (ints) { ints[m].dot[0] = s0; ints[m].dot[1] = s1; }
-            const float pd = a[m].d8[0] * i2f_small(s0 * sc0) + a[m].d8[1] * i2f_small(s1 * sc1);
-            const float pm = a[m].d8[0] * i2f_small(a[m].sq[0] * mn0) + a[m].d8[1] * i2f_small(a[m].sq[1] * mn1);
-            acc[m] += dm.x * pd - dm.y * pm;
-        }
-    } else {  // Q6_K
-        const int c = u & 7, h = c >> 2, l0 = 8 * (c & 3);
-        const uint32_t bp = rowp + 210u * (u >> 3);
-        int qa[2], qb[2], qh[2];
-        lds_words_a2<2>(bp + 64 * h + l0, qa);
-        lds_words_a2<2>(bp + 64 * h + 32 + l0, qb);
-        lds_words_a2<2>(bp + 128 + 32 * h + l0, qh);
-        // scales[8h + (l0>>4) + {0,2,4,6}] : 7 consecutive bytes starting at an arbitrary byte
-        const uint32_t sa = bp + 192 + 8 * h + (l0 >> 4);
-        const uint32_t sbase = sa & ~3u, ssh = (sa & 3u) * 8u;
-        const uint32_t s0w = lds32(sbase), s1w = lds32(sbase + 4), s2w = lds32(sbase + 8);
-        const uint32_t sw0 = __funnelshift_r(s0w, s1w, ssh), sw1 = __funnelshift_r(s1w, s2w, ssh);
-        const int sc[4] = { (int)(int8_t)(sw0 & 0xFF), (int)(int8_t)((sw0 >> 16) & 0xFF),
-                            (int)(int8_t)(sw1 & 0xFF), (int)(int8_t)((sw1 >> 16) & 0xFF) };
-        const float d = half_bits_to_float(lds16(bp + 208));
-        int v[4][2];
+        for (int m = 0; m < M; ++m) acc6[m] = 0.0f;
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            v[0][i] = (qa[i] & 0x0F0F0F0F)        | ((qh[i] << 4) & 0x30303030);
-            v[1][i] = (qb[i] & 0x0F0F0F0F)        | ((qh[i] << 2) & 0x30303030);
-            v[2][i] = ((qa[i] >> 4) & 0x0F0F0F0F) | ( qh[i]       & 0x30303030);
-            v[3][i] = ((qb[i] >> 4) & 0x0F0F0F0F) | ((qh[i] >> 2) & 0x30303030);
-        }
-#pragma unroll
-        for (int m = 0; m < M; ++m) {
-            float p = 0.0f;
+        for (int h = 0; h < 2; ++h) {
+            int ql[16], qh[8], scw[2];
+            lds_words_a2<16>(wp + 64 * h, ql);
+            lds_words_a2<8>(wp + 128 + 32 * h, qh);
+            lds_words_a2<2>(wp + 192 + 8 * h, scw);
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
-                // sum (v-32)*q = sum v*q - 32*sum q : same int32 as the __vsubss4 form (vecdotq.cuh:492)
-                int s = __dp4a(v[g][0], a[m].q[2 * g], __dp4a(v[g][1], a[m].q[2 * g + 1], -32 * a[m].sq[g]));
-                if (ints) ints[m].dot[g] = s;
-                p = fmaf(a[m].d8[g], i2f_small(s * sc[g]), p);
+                uint32_t v[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t l4 = (uint32_t)ql[8 * (g & 1) + j], h4 = (uint32_t)qh[j];
+                    const uint32_t nib = (g < 2 ? l4 : (l4 >> 4)) & 0x0F0F0F0Fu;
+                    const uint32_t top = (g == 0 ? (h4 << 4) : g == 1 ? (h4 << 2) : g == 2 ? h4 : (h4 >> 2)) & 0x30303030u;
+                    v[j] = nib | top;
+                }
+                const int sca = (int)(int8_t)((uint32_t)scw[g >> 1] >> (16 * (g & 1)));
+                const int scb = (int)(int8_t)((uint32_t)scw[g >> 1] >> (16 * (g & 1) + 8));
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    act_blk a; lds_act(ap + m * acs + (4 * h + g) * ACT_BLK, a);
+                    int sa = a.m32a, sb = a.m32b;       // -32 * sum q: folds the -32 offset of the 6-bit code
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { sa = dp4a_us(v[j], a.q[j], sa); sb = dp4a_us(v[4 + j], a.q[4 + j], sb); }
+                    if constexpr (DBG) dbg[m * dms + 4 * h + g] = sa + sb;
+                    acc6[m] = fmaf(a.d8, (float)(sa * sca + sb * scb), acc6[m]);
+                }
             }
-            acc[m] = fmaf(d, p, acc[m]);
+        }
+#pragma unroll
+        for (int m = 0; m < M; ++m) acc[m] = fmaf(d, acc6[m], acc[m]);
+    }
+}
+
+// ---- fused prologue: quantise M activation columns into shared memory ---------------------------
+// q = roundf(x / d) with d = amax / 127, bit-identical to the reference (quantize.cu:38-47), at a
+// fraction of the IEEE-division cost: r' = x * rcp(d) is within 3e-5 of x/d, so unless r' lies
+// within 1e-4 of a rounding boundary (k + 0.5) its nearest integer IS roundf(x/d); the rare
+// boundary cases (and denormal scales) take the exact division.
+__device__ __forceinline__ int q8_round(float x, float d, float inv, bool exact_only) {
+    const float r = x * inv;
+    const float fm = r + 12582912.0f;              // 1.5 * 2^23: the mantissa now holds rint(r)
+    const float u = r - (fm - 12582912.0f);
+    if (exact_only || !(fabsf(u) <= 0.4999f)) return (int)roundf(__fdiv_rn(x, d));
+    return __float_as_int(fm) - 0x4B400000;
+}
+
+// Eight lanes per 32-block (a float4 each); nthreads threads (a multiple of 32) cooperate.  Must be
+// called by all of them.  nb32 = K/32 blocks per column.
+__device__ __forceinline__ void quantize_acts(const float * __restrict__ X, int64_t xs, int M, int nb32, bool vec_ok,
+                                              uint8_t * act, uint32_t acs, int tid, int nthreads) {
+    const int sub = tid & 7, grp = tid >> 3, ngrp = nthreads >> 3;
+    constexpr int UN = 4;                                    // independent loads in flight per lane
+    for (int m = 0; m < M; ++m) {
+        const float * xm = X + (int64_t)m * xs + 4 * sub;
+        uint8_t * am = act + (size_t)m * acs;
+        for (int base = 0; base < nb32; base += UN * ngrp) {
+            float4 xv[UN];
+#pragma unroll
+            for (int u = 0; u < UN; ++u) {
+                const int jb = base + u * ngrp + grp;
+                xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (jb < nb32) {
+                    const float * src = xm + 32 * jb;
+                    if (vec_ok) xv[u] = __ldg(reinterpret_cast<const float4 *>(src));
+                    else { xv[u].x = __ldg(src); xv[u].y = __ldg(src + 1); xv[u].z = __ldg(src + 2); xv[u].w = __ldg(src + 3); }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UN; ++u) {
+                const int jb = base + u * ngrp + grp;         // uniform across the 8 lanes of a group
+                const float4 x = xv[u];
+                float amax = fmaxf(fmaxf(fabsf(x.x), fabsf(x.y)), fmaxf(fabsf(x.z), fabsf(x.w)));
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+                const float d = __fdiv_rn(amax, 127.0f);
+                int q0 = 0, q1 = 0, q2 = 0, q3 = 0;
+                if (amax != 0.0f) {
+                    const bool tiny = amax < 1e-20f;
+                    float inv; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(d));
+                    q0 = q8_round(x.x, d, inv, tiny); q1 = q8_round(x.y, d, inv, tiny);
+                    q2 = q8_round(x.z, d, inv, tiny); q3 = q8_round(x.w, d, inv, tiny);
+                }
+                const int word = (int)__byte_perm(__byte_perm(q0, q1, 0x0040), __byte_perm(q2, q3, 0x0040), 0x5410);
+                int s = __dp4a(word, 0x01010101, 0);
+                s += __shfl_xor_sync(0xffffffffu, s, 1);
+                s += __shfl_xor_sync(0xffffffffu, s, 2);          // sum of 16 elements (lanes 0-3 / 4-7)
+                const int s16 = s;
+                s += __shfl_xor_sync(0xffffffffu, s, 4);          // sum of the 32-block
+                const int s16b = __shfl_down_sync(0xffffffffu, s16, 4);
+                if (jb < nb32) {
+                    uint8_t * blk = am + (size_t)(jb >> 3) * ACT_ITEM + (jb & 7) * ACT_BLK;
+                    reinterpret_cast<int *>(blk)[sub] = word;
+                    if (sub == 0) {
+                        const float d8 = __half2float(__float2half_rn(d));   // q8_1 stores d as binary16 (quantize.cu:47)
+                        int4 t; t.x = __float_as_int(d8); t.y = __float_as_int(d8 * (float)s); t.z = -32 * s16; t.w = -32 * s16b;
+                        *reinterpret_cast<int4 *>(blk + 32) = t;
+                    }
+                }
+            }
         }
     }
 }

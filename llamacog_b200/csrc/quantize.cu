@@ -1,7 +1,8 @@
 // quantize.cu -- stand-alone activation quantisation and weight dequantisation.
 // Element-wise, HBM-bound helpers; the hot path fuses the q8_1 step into the GEMV/GEMM prologues.
-#include "common.cuh"
+#include "mmvq_units.cuh"
 #include "../../include/b200_ops.h"
+#include <algorithm>
 
 namespace b200 {
 
@@ -26,6 +27,15 @@ __global__ void quantize_q8_1_kernel(const float * __restrict__ x, int64_t xs, u
         reinterpret_cast<__half *>(blk)[0] = __float2half_rn(d);
         reinterpret_cast<__half *>(blk)[1] = __float2half_rn(sum);
     }
+}
+
+// the GEMV's activation layout, written to global memory (pre-quantised path of mmvq.cuh)
+__global__ void __launch_bounds__(256) quantize_acts_kernel(const float * __restrict__ x, int64_t xs, uint8_t * __restrict__ out,
+                                                            int K, int M, int vec_ok) {
+    pdl_trigger();
+    pdl_wait();
+    const uint32_t acs = (uint32_t)((K + 255) / 256) * ACT_ITEM;
+    quantize_acts(x, xs, M, K >> 5, vec_ok != 0, out, acs, blockIdx.x * 256 + threadIdx.x, gridDim.x * 256);
 }
 
 // 6-bit scale/min unpack (reference ggml-quants.c:625-632)
@@ -102,6 +112,24 @@ extern "C" int b200_quantize_q8_1(const float * x, int64_t xs, void * y, int64_t
     quantize_q8_1_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(x, xs, (uint8_t *)y, k, k_pad, nrows);
     ++g_launches;
     return (int)cudaGetLastError();
+}
+
+extern "C" int64_t b200_quantized_acts_bytes(int K, int M) { return (int64_t)M * ((K + 255) / 256) * ACT_ITEM; }
+
+extern "C" int b200_quantize_acts(const float * x, int64_t xs, void * out, int K, int M, void * stream) {
+    if (K <= 0 || K % 32 || M <= 0) return -1;
+    const int vec_ok = ((((uintptr_t)x) | ((uintptr_t)xs * 4)) & 15) == 0;
+    const int groups = (K / 32) * M;                       // one 8-lane group per 32-block, 4 blocks per group
+    const unsigned blocks = (unsigned)std::max(1, std::min(2 * 148, (groups / 4 + 31) / 32));
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3(blocks); lc.blockDim = dim3(256); lc.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+    B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, quantize_acts_kernel, x, xs, (uint8_t *)out, K, M, vec_ok));
+    ++g_launches;
+    return 0;
 }
 
 extern "C" int b200_dequantize_rows(int type, const void * src, int64_t src_nb1, void * dst, int dst_type, int64_t dst_stride,

@@ -20,7 +20,7 @@ class MmvqArgs(C.Structure):
                 ("dst", C.c_void_p), ("ds", C.c_int64), ("N", C.c_int), ("K", C.c_int), ("M", C.c_int),
                 ("nchannels", C.c_int), ("w_ch_stride", C.c_int64), ("x_ch_stride", C.c_int64),
                 ("d_ch_stride", C.c_int64), ("ids", C.c_void_p), ("x_ch_mod", C.c_int), ("w_ch_div", C.c_int),
-                ("pdl", C.c_int), ("dbg_sumi", C.c_void_p)]
+                ("pdl", C.c_int), ("dbg_sumi", C.c_void_p), ("Xq", C.c_void_p), ("xq_ch_stride", C.c_int64)]
 
 
 _lib = None
@@ -37,12 +37,13 @@ def lib():
         _lib.b200_mul_mat_vec_q_ex.argtypes = [C.POINTER(MmvqArgs), C.c_void_p]
         for name in EXPORTS:
             getattr(_lib, name).restype = C.c_int
+        _lib.b200_quantized_acts_bytes.restype = C.c_int64
     return _lib
 
 
 # every symbol include/b200_ops.h declares (tests/test_capi_symbols.py keeps this in sync)
 EXPORTS = ["b200_mul_mat_vec_q_ex", "b200_mul_mat_vec_q", "b200_mmvq_supported_type", "b200_quantize_q8_1",
-           "b200_dequantize_rows", "b200_kernel_launch_count"]
+           "b200_dequantize_rows", "b200_kernel_launch_count", "b200_quantize_acts", "b200_quantized_acts_bytes"]
 
 
 def _stream():
@@ -59,16 +60,28 @@ def row_bytes(t, k):
     return k // BLOCK_ELEMS[t] * BLOCK_BYTES[t]
 
 
-def mul_mat_vec_q(t, W, X, N, K, nb1=None, dbg=False, pdl=-1):
+def quantize_acts(X):
+    """X float32 [M, K] -> the GEMV's pre-quantised activation layout (uint8 [M, ceil(K/256)*400])."""
+    assert X.is_cuda and X.dtype == torch.float32 and X.dim() == 2 and X.stride(1) == 1
+    M, K = X.shape
+    out = torch.empty((M, (K + 255) // 256 * 400), dtype=torch.uint8, device=X.device)
+    _check(lib().b200_quantize_acts(C.c_void_p(X.data_ptr()), C.c_int64(X.stride(0)), C.c_void_p(out.data_ptr()),
+                                    C.c_int(K), C.c_int(M), _stream()), "b200_quantize_acts")
+    return out
+
+
+def mul_mat_vec_q(t, W, X, N, K, nb1=None, dbg=False, pdl=-1, Xq=None):
     """W: uint8 CUDA tensor of N quantised rows; X: float32 [M, K].  Returns dst [M, N]
-    (and the int32 block sums [M, N, K/32] when dbg)."""
+    (and the int32 block sums [M, N, K/32] when dbg).  Xq: activations pre-quantised by
+    quantize_acts (the kernel then skips its fused prologue)."""
     assert W.is_cuda and X.is_cuda and X.dtype == torch.float32 and X.stride(-1) == 1
     M = X.shape[0]
     dst = torch.empty((M, N), dtype=torch.float32, device=X.device)
     sums = torch.zeros((M, N, K // 32), dtype=torch.int32, device=X.device) if dbg else None
     a = MmvqArgs(type=t, W=W.data_ptr(), nb1=nb1 or row_bytes(t, K), X=X.data_ptr(), xs=X.stride(0),
                  dst=dst.data_ptr(), ds=N, N=N, K=K, M=M, nchannels=1, w_ch_stride=0, x_ch_stride=0, d_ch_stride=0,
-                 ids=None, x_ch_mod=0, w_ch_div=0, pdl=pdl, dbg_sumi=sums.data_ptr() if dbg else None)
+                 ids=None, x_ch_mod=0, w_ch_div=0, pdl=pdl, dbg_sumi=sums.data_ptr() if dbg else None,
+                 Xq=Xq.data_ptr() if Xq is not None else None, xq_ch_stride=0)
     _check(lib().b200_mul_mat_vec_q_ex(C.byref(a), _stream()), "b200_mul_mat_vec_q_ex")
     return (dst, sums) if dbg else dst
 

@@ -148,3 +148,48 @@ def test_dequantize_bit_exact(name):
     raw = O.random_quant_bytes(t, 8, 4096, rng)
     got = ops.dequantize_rows(t, torch.from_numpy(raw.reshape(-1).copy()).cuda(), 8, 4096).cpu().numpy()
     assert np.array_equal(got.view(np.uint32), O.dequantize(t, raw, 8, 4096).view(np.uint32))
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("N,K,M", [(64, 4096, 1), (37, 14336, 2), (16, 512, 4)])
+def test_prequantised_path_matches_fused(name, N, K, M):
+    """b200_quantize_acts + Xq (pre-quantised activations) must give the same int32 block sums and the
+    same fp32 result, bit for bit, as the fused prologue: both run the same quantiser."""
+    ops = _ops()
+    t = O.QUANT_TYPES[name]
+    rng = np.random.default_rng(K + M)
+    W = torch.from_numpy(O.random_quant_bytes(t, N, K, rng).reshape(-1)).cuda()
+    X = torch.from_numpy(rng.uniform(-1, 1, (M, K)).astype(np.float32)).cuda()
+    d0, s0 = ops.mul_mat_vec_q(t, W, X, N, K, dbg=True)
+    d1, s1 = ops.mul_mat_vec_q(t, W, X, N, K, dbg=True, Xq=ops.quantize_acts(X))
+    torch.cuda.synchronize()
+    assert torch.equal(s0, s1)
+    assert torch.equal(d0, d1)
+
+
+def test_fused_quantiser_rounding_boundaries():
+    """The prologue replaces x/d by x*rcp(d) away from rounding boundaries; values placed on and next
+    to every k+0.5 boundary (where the shortcut must fall back to the exact division) have to
+    reproduce roundf(x/d) of the reference quantiser (quantize.cu:38-47) exactly."""
+    ops = _ops()
+    rng = np.random.default_rng(17)
+    K = 4096
+    X = np.empty((8, K), dtype=np.float32)
+    for m in range(8):
+        for b in range(K // 32):
+            amax = np.float32(rng.uniform(0.01, 50.0))
+            d = np.float32(amax / np.float32(127.0))
+            k = rng.integers(-126, 126, 32).astype(np.float32) + np.float32(0.5)
+            x = (k * d).astype(np.float32)
+            step = rng.integers(-3, 4, 32).astype(np.int32)
+            x = (x.view(np.int32) + step).view(np.float32)      # a few ulps around the boundary
+            x[0] = amax
+            X[m, 32 * b: 32 * b + 32] = x
+    Wnp = O.random_quant_bytes(O.Q8_0, 4, K, rng)
+    _, sums = ops.mul_mat_vec_q(O.Q8_0, torch.from_numpy(Wnp.reshape(-1)).cuda(), torch.from_numpy(X).cuda(), 4, K, dbg=True)
+    torch.cuda.synchronize()
+    for m in range(8):
+        q = O.quantize_row_q8_1_cuda(X[m], K)
+        for n in range(4):
+            si, _ = O.block_sums(O.Q8_0, Wnp[n], q, K)
+            assert np.array_equal(sums[m, n].cpu().numpy(), si)

@@ -51,12 +51,20 @@ def main():
     Ms = [int(a) for a in sys.argv[1:]] or [1]
     for M in Ms:
         for name, t, N, K in SHAPES:
+            if os.environ.get('MICRO_SHAPES') and not any(k in name for k in os.environ['MICRO_SHAPES'].split(',')):
+                continue
             wbytes = N * ops.row_bytes(t, K)
             copies = max(2, int(400e6 // wbytes) + 1)
             pool = [rand_weights(t, wbytes, dev) for _ in range(min(copies, 48))]
             X = torch.rand((M, K), device=dev) * 2 - 1
+            prequant = os.environ.get("MICRO_XQ", "0") == "1"
+
+            def run(Wm):
+                if prequant:   # separate quantise kernel + GEMV on pre-quantised activations
+                    return ops.mul_mat_vec_q(t, Wm, X, N, K, Xq=ops.quantize_acts(X))
+                return ops.mul_mat_vec_q(t, Wm, X, N, K)
             for i in range(3):
-                ops.mul_mat_vec_q(t, pool[i % len(pool)], X, N, K)
+                run(pool[i % len(pool)])
             torch.cuda.synchronize()
             # one CUDA graph of `iters` back-to-back launches: removes host launch latency from the
             # measurement (decode runs from a graph too); each launch still reads a different matrix
@@ -66,7 +74,7 @@ def main():
             with torch.cuda.stream(st):
                 with torch.cuda.graph(g, stream=st):
                     for i in range(iters):
-                        ops.mul_mat_vec_q(t, pool[i % len(pool)], X, N, K)
+                        run(pool[i % len(pool)])
             ts = []
             for rep in range(6):
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
