@@ -236,8 +236,7 @@ def main():
                     raise RuntimeError("b200_quantize_acts rc=%d" % rc)
             xq = xq_bufs[src].data_ptr()
         a = ops.MmvqArgs(type=t, W=W.data_ptr(), nb1=ops.row_bytes(t, K), X=X.data_ptr(), xs=K, dst=dst.data_ptr(), ds=N,
-                         N=N, K=K, M=1, nchannels=1, w_ch_stride=0, x_ch_stride=0, d_ch_stride=0, ids=None,
-                         x_ch_mod=0, w_ch_div=0, pdl=-1, dbg_sumi=None, Xq=xq, xq_ch_stride=0)
+                         N=N, K=K, M=1, ny=1, nz=1, pdl=-1, dbg_sumi=None, Xq=xq)
         rc = ops.lib().b200_mul_mat_vec_q_ex(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream))
         if rc:
             raise RuntimeError("b200_mul_mat_vec_q_ex rc=%d" % rc)

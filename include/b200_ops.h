@@ -45,20 +45,26 @@ typedef struct b200_mmvq_args {
     float * dst;
     int64_t ds;             /* floats between dst columns */
     int N, K, M;
-    int nchannels;          /* >= 1: batch / expert-slot channels (grid.y) */
-    int64_t w_ch_stride;    /* bytes between weight matrices */
-    int64_t x_ch_stride;    /* floats */
-    int64_t d_ch_stride;    /* floats */
-    const int32_t * ids;    /* optional device array [nchannels]: weight matrix per channel */
-    int x_ch_mod;           /* channel c reads X channel c % x_ch_mod (0: no wrap) */
-    int w_ch_div;           /* without ids: channel c reads weight matrix c / w_ch_div (0: 1) */
-    int pdl;                /* 1: launch with programmatic dependent launch, 0: off, -1: env B200_PDL */
-    int32_t * dbg_sumi;     /* optional device [M][N][K/32] zero-initialised: receives the exact int32
-                               block dot products (reference vecdotq.cuh sumi/dot1) for parity tests */
+    /* batch / expert-slot channels: a (ny x nz) grid of independent GEMVs.  Channel (y, z) uses
+     *   weight matrix  W + ids[z*ids_sz + y] * w_sy                    when ids != NULL (MUL_MAT_ID), else
+     *                  W + (y / w_div_y) * w_sy + (z / w_div_z) * w_sz   (ne02/ne03 broadcast of MUL_MAT)
+     *   activations    X + (y % x_mod_y) * x_sy + z * x_sz  (floats)    (ne11 broadcast of MUL_MAT_ID)
+     *   output         dst + y * d_sy + z * d_sz  (floats) */
+    int ny, nz;             /* 0 is treated as 1 */
+    int64_t w_sy, w_sz;     /* bytes */
+    int w_div_y, w_div_z;   /* 0 is treated as 1 */
+    int64_t x_sy, x_sz;     /* floats */
+    int x_mod_y;            /* 0: no wrap */
+    int64_t d_sy, d_sz;     /* floats */
+    const int32_t * ids;    /* optional device array */
+    int64_t ids_sz;         /* ints between z rows of ids */
+    int pdl;                /* 1: launch with programmatic dependent launch, 0: off, -1: env B200_PDL (default on) */
+    int32_t * dbg_sumi;     /* optional device [M][N][K/32]: receives the exact int32 block dot products
+                               (reference vecdotq.cuh sumi/dot1) for parity tests; single channel only */
     const void * Xq;        /* optional: activations already quantised by b200_quantize_acts (then X may be
-                               NULL): [channels][M][ceil(K/256)] items of 400 bytes; the kernel then copies
+                               NULL): per channel [M][ceil(K/256)] items of 400 bytes; the kernel then copies
                                them instead of quantising X itself (better when K is large and N small) */
-    int64_t xq_ch_stride;   /* bytes between channels of Xq */
+    int64_t xq_sy, xq_sz;   /* bytes between channels of Xq (same y wrap as X) */
 } b200_mmvq_args;
 
 int b200_mul_mat_vec_q_ex(const b200_mmvq_args * args, void * stream);
@@ -84,6 +90,81 @@ int64_t b200_quantized_acts_bytes(int K, int M);
  * reference for fp32 output. */
 int b200_dequantize_rows(int type, const void * src, int64_t src_nb1, void * dst, int dst_type, int64_t dst_stride,
                          int64_t k, int64_t nrows, void * stream);
+
+
+/* ==== tensor-level operators (the non-matmul nodes of the Llama / Mixtral graphs and the MUL_MAT
+ * dispatch).  A b200_tensor mirrors the fields of ggml_tensor that an op needs (reference
+ * ggml/include/ggml.h:569-604): device data pointer, ggml type id, ne[4] elements and nb[4] byte
+ * strides.  Every function is asynchronous on `stream`, returns 0 on success, -1 when the argument
+ * combination is not supported (the plugin's supports_op asks the matching *_supported predicate
+ * first) or a positive cudaError_t. ============================================================ */
+typedef struct b200_tensor {
+    void *  data;
+    int     type;
+    int64_t ne[4];
+    int64_t nb[4];
+} b200_tensor;
+
+#define B200_TYPE_BF16 30
+
+enum b200_binary_op { B200_ADD = 0, B200_SUB = 1, B200_MUL = 2, B200_DIV = 3 };
+/* unary op ids = ggml_unary_op (reference ggml/include/ggml.h:525-543) */
+enum b200_unary_op { B200_UNARY_ABS = 0, B200_UNARY_SGN, B200_UNARY_NEG, B200_UNARY_STEP, B200_UNARY_TANH, B200_UNARY_ELU,
+                     B200_UNARY_RELU, B200_UNARY_SIGMOID, B200_UNARY_GELU, B200_UNARY_GELU_QUICK, B200_UNARY_SILU,
+                     B200_UNARY_HARDSWISH, B200_UNARY_HARDSIGMOID, B200_UNARY_EXP, B200_UNARY_GELU_ERF };
+
+/* dst = a (op) b with b broadcast over a; f32.  Replaces ggml_cuda_op_add/sub/mul/div (ggml-cuda/binbcast.cu:26-). */
+int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, void * stream);
+/* element-wise f32 on contiguous tensors.  Replaces ggml-cuda/unary.cu:87-. */
+int b200_op_unary(int op, const b200_tensor * src, const b200_tensor * dst, void * stream);
+/* dst = src * scale.  Replaces ggml-cuda/scale.cu:3-. */
+int b200_op_scale(const b200_tensor * src, const b200_tensor * dst, float scale, void * stream);
+/* row-wise x / sqrt(mean(x^2) + eps).  Replaces ggml_cuda_op_rms_norm (ggml-cuda/norm.cu:108-). */
+int b200_op_rms_norm(const b200_tensor * src, const b200_tensor * dst, float eps, void * stream);
+/* rotary embedding, modes normal (0) and neox (2), f32 or f16 data, optional frequency factors.
+ * Replaces ggml_cuda_op_rope (ggml-cuda/rope.cu:41,85-); parameters as ggml_rope_ext packs them
+ * into op_params (reference ggml/src/ggml-cpu/ops.cpp:5187-5202). */
+typedef struct b200_rope_params {
+    int n_dims, mode, n_ctx_orig;
+    float freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow;
+} b200_rope_params;
+int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst,
+                 const b200_rope_params * prm, void * stream);
+/* copy with type conversion and arbitrary strides (CPY / CONT / DUP): f32,f16,bf16 -> f32,f16,bf16; f32 -> q8_0 (the
+ * KV-cache store; bit-exact to quantize_row_q8_0_ref, ggml-quants.c:191-212); same-type block copies of quantised
+ * data.  Replaces ggml_cuda_cpy (ggml-cuda/cpy.cu:303-). */
+int b200_op_cpy(const b200_tensor * src, const b200_tensor * dst, void * stream);
+int b200_op_cpy_supported(int src_type, int dst_type);
+/* dst[:, i] = dequant(src[:, ids[i]]), dst f32.  Replaces ggml_cuda_op_get_rows (ggml-cuda/getrows.cu:42-). */
+int b200_op_get_rows(const b200_tensor * src, const b200_tensor * ids, const b200_tensor * dst, void * stream);
+/* soft_max(src * scale + slope * mask) over rows; mask f16 or f32 or NULL.  Replaces ggml-cuda/softmax.cu:23-. */
+int b200_op_soft_max(const b200_tensor * src, const b200_tensor * mask, const b200_tensor * dst, float scale, float max_bias,
+                     void * stream);
+/* row-wise argsort (order 0 ascending, 1 descending), dst i32; ne0 <= 1024.  Replaces ggml-cuda/argsort.cu:11-. */
+int b200_op_argsort(const b200_tensor * src, const b200_tensor * dst, int order, void * stream);
+/* dst[0, r] = sum over row r.  Replaces ggml-cuda/sumrows.cu. */
+int b200_op_sum_rows(const b200_tensor * src, const b200_tensor * dst, void * stream);
+/* softmax(scale * Q K^T + slope * mask [softcap]) V with online softmax and GQA broadcast; Q f32 [D, n_batch, n_head],
+ * K/V f16 or q8_0 [D, n_kv, n_head_kv] (strided views of the KV cache), mask f16 [n_kv, >= n_batch], dst f32
+ * [D, n_head, n_batch].  Replaces ggml_cuda_flash_attn_ext (ggml-cuda/fattn.cu:271-346); op contract
+ * ggml/include/ggml.h:1848-1870.  scratch: device memory of b200_flash_attn_scratch_bytes() for the split-KV partials. */
+int b200_op_flash_attn_ext(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
+                           const b200_tensor * dst, float scale, float max_bias, float logit_softcap,
+                           void * scratch, int64_t scratch_bytes, void * stream);
+int64_t b200_flash_attn_scratch_bytes(const b200_tensor * q, const b200_tensor * k);
+int b200_flash_attn_supported(int k_type, int v_type, int64_t dk, int64_t dv);
+/* MUL_MAT: dst[N, M, b2, b3] = src0[K, N, a2, a3] x src1[K, M, b2, b3], src0 broadcast over dims 2,3.
+ * Quantised src0 (Q4_0, Q8_0, Q4_K, Q5_K, Q6_K) with f32 src1 goes to the MMVQ GEMV for M <= 8 and to the MMQ GEMM
+ * beyond; f16/bf16/f32 src0 to a plain tiled kernel.  Replaces ggml_cuda_mul_mat (ggml-cuda/ggml-cuda.cu:1936-2005).
+ * scratch: device memory for the quantised activations (b200_mul_mat_scratch_bytes). */
+int b200_op_mul_mat(const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst,
+                    void * scratch, int64_t scratch_bytes, void * stream);
+int64_t b200_mul_mat_scratch_bytes(const b200_tensor * src0, const b200_tensor * src1);
+int b200_mul_mat_supported(const b200_tensor * src0, const b200_tensor * src1);
+/* MUL_MAT_ID: dst[:, e, t] = as[:, :, ids[e, t]] x b[:, e % ne11, t]; ids i32 read on the device (no host sync).
+ * Replaces ggml_cuda_mul_mat_id (ggml-cuda/ggml-cuda.cu:2007-2148) and the MoE branch of mmq.cu:141-223. */
+int b200_op_mul_mat_id(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * dst,
+                       void * scratch, int64_t scratch_bytes, void * stream);
 
 /* number of kernels launched by this library so far in this process (bench.py gpu_launches) */
 int b200_kernel_launch_count(void);

@@ -36,7 +36,7 @@ def _newer(src_files, target):
 
 def _compile(src, extra=()):
     obj = os.path.join(OBJ, os.path.basename(src) + ".o")
-    deps = glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(CSRC, "backend", "*.h")) + \
+    deps = glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(CSRC, "backend", "*.h")) + glob.glob(os.path.join(CSRC, "backend", "*.inc")) + \
         glob.glob(os.path.join(ROOT, "include", "*.h")) + [src]
     if _newer(deps, obj):
         cmd = [NVCC] + NVCC_FLAGS + list(extra) + ["-c", src, "-o", obj]

@@ -9,7 +9,7 @@
 namespace b200 {
 
 // ggml type ids (reference ggml/include/ggml.h:352-366)
-enum : int { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q8_0 = 8, T_Q8_1 = 9, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14, T_I32 = 26 };
+enum : int { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q8_0 = 8, T_Q8_1 = 9, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14, T_I32 = 26, T_BF16 = 30 };
 
 template <int TYPE> struct fmt;   // bytes per block, elements per block
 template <> struct fmt<T_Q4_0> { static constexpr int BB = 18,  BE = 32;  };
@@ -21,12 +21,12 @@ template <> struct fmt<T_Q6_K> { static constexpr int BB = 210, BE = 256; };
 
 __host__ __device__ inline int block_bytes(int t) {
     switch (t) { case T_Q4_0: return 18; case T_Q8_0: return 34; case T_Q8_1: return 36; case T_Q4_K: return 144;
-                 case T_Q5_K: return 176; case T_Q6_K: return 210; case T_F32: return 4; case T_F16: return 2; case T_I32: return 4; }
+                 case T_Q5_K: return 176; case T_Q6_K: return 210; case T_F32: return 4; case T_F16: return 2; case T_I32: return 4; case T_BF16: return 2; }
     return 0;
 }
 __host__ __device__ inline int block_elems(int t) {
     switch (t) { case T_Q4_0: case T_Q8_0: case T_Q8_1: return 32; case T_Q4_K: case T_Q5_K: case T_Q6_K: return 256;
-                 case T_F32: case T_F16: case T_I32: return 1; }
+                 case T_F32: case T_F16: case T_I32: case T_BF16: return 1; }
     return 0;
 }
 

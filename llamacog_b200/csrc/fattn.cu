@@ -1,0 +1,278 @@
+// fattn.cu -- GGML_OP_FLASH_ATTN_EXT over an f16 / q8_0 KV cache (vector form: decode and small batches).
+//
+// Replaces ggml_cuda_flash_attn_ext's vec kernels (ggml-cuda/fattn.cu:271-346, fattn-vec-f32.cuh,
+// fattn-common.cuh:237-268,312-354,451-468) with one split-KV kernel + a combine kernel:
+//   grid (q rows, heads, KV splits), 4 warps per CTA; a warp walks tiles of 32 KV positions.
+//   scores: lane j owns position j of the tile and runs the whole dot product q . k_j (Q lives in
+//           shared memory and is read as a broadcast; for q8_0 K, Q is quantised to int8 per 32
+//           values once per CTA and the dot is dp4a, as the reference does on both CPU and GPU);
+//   online softmax per tile with warp reductions (reference ggml-cpu/ops.cpp:7141-7209);
+//   P.V:    lanes own D/32 output dims, V rows are read coalesced, p_j arrives by shuffle.
+// K and V are strided views of the cache (nb1/nb2/nb3 honoured); GQA by index division.
+#include "common.cuh"
+#include "../../include/b200_ops.h"
+
+#include <algorithm>
+#include <cmath>
+
+namespace b200 {
+
+struct fa_params {
+    const char * q; const char * k; const char * v; const char * mask; char * dst;
+    float * part;                          // [rows][heads][nsplit][2 + DV] when nsplit > 1
+    int64_t nbq1, nbq2, nbq3, nbk1, nbk2, nbk3, nbv1, nbv2, nbv3, nbm1, nbd1;
+    int N, n_head, ne3, n_kv, rk2, rk3, rv2, rv3;
+    int nsplit, tiles_per_split;
+    float scale, max_bias, softcap, m0, m1;
+    unsigned n_head_log2;
+};
+
+__device__ __forceinline__ uint32_t ldg_u16(const void * p) { return *reinterpret_cast<const unsigned short *>(p); }
+
+// dot product of one K row with Q (shared memory); D elements
+template <int KT, int D>
+__device__ __forceinline__ float k_dot(const char * krow, const float * qf, const int * qi, const float * qd) {
+    float s = 0.0f;
+    if constexpr (KT == T_F16) {
+        const uint4 * kp = reinterpret_cast<const uint4 *>(krow);      // rows of the cache are 16-byte aligned
+#pragma unroll 4
+        for (int i = 0; i < D / 8; ++i) {
+            const uint4 u = __ldg(kp + i);
+            const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+            const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&u.z)), d = __half22float2(*reinterpret_cast<const __half2 *>(&u.w));
+            const float4 q0 = *reinterpret_cast<const float4 *>(qf + 8 * i), q1 = *reinterpret_cast<const float4 *>(qf + 8 * i + 4);
+            s = fmaf(a.x, q0.x, s); s = fmaf(a.y, q0.y, s); s = fmaf(b.x, q0.z, s); s = fmaf(b.y, q0.w, s);
+            s = fmaf(c.x, q1.x, s); s = fmaf(c.y, q1.y, s); s = fmaf(d.x, q1.z, s); s = fmaf(d.y, q1.w, s);
+        }
+    } else {   // q8_0: blocks of {half d; int8 q[32]}, 2-byte aligned
+#pragma unroll
+        for (int b = 0; b < D / 32; ++b) {
+            const char * blk = krow + 34 * b;
+            const float dk = __half2float(__ushort_as_half((unsigned short)ldg_u16(blk)));
+            int acc = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int w = (int)(ldg_u16(blk + 2 + 4 * i) | (ldg_u16(blk + 4 + 4 * i) << 16));
+                acc = __dp4a(w, qi[8 * b + i], acc);
+            }
+            s = fmaf(dk * qd[b], (float)acc, s);
+        }
+    }
+    return s;
+}
+
+// lanes own DV/32 consecutive output dims: acc[] += p * V[row][dims]
+template <int VT, int DV>
+__device__ __forceinline__ void v_accum(const char * vrow, int lane, float p, float (&acc)[DV / 32]) {
+    constexpr int E = DV / 32;
+    if constexpr (VT == T_F16) {
+        const __half * vp = reinterpret_cast<const __half *>(vrow) + E * lane;
+        if constexpr (E == 4) {
+            const uint2 u = __ldg(reinterpret_cast<const uint2 *>(vp));
+            const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+            acc[0] = fmaf(p, a.x, acc[0]); acc[1] = fmaf(p, a.y, acc[1]); acc[2] = fmaf(p, b.x, acc[2]); acc[3] = fmaf(p, b.y, acc[3]);
+        } else {
+#pragma unroll
+            for (int e = 0; e < E; ++e) acc[e] = fmaf(p, __half2float(vp[e]), acc[e]);
+        }
+    } else {
+        const int d0 = E * lane;
+        const char * blk = vrow + 34 * (d0 >> 5);
+        const float dv = __half2float(__ushort_as_half((unsigned short)ldg_u16(blk)));
+        const float pd = p * dv;
+#pragma unroll
+        for (int e = 0; e < E; e += 2) {
+            const uint32_t w = ldg_u16(blk + 2 + (d0 & 31) + e);
+            acc[e] = fmaf(pd, (float)(int)(int8_t)(w & 0xFF), acc[e]);
+            acc[e + 1] = fmaf(pd, (float)(int)(int8_t)(w >> 8), acc[e + 1]);
+        }
+    }
+}
+
+template <int KT, int VT, int DK, int DV>
+__global__ void __launch_bounds__(128) fattn_vec_kernel(const fa_params p) {
+    pdl_trigger(); pdl_wait();
+    constexpr int EV = DV / 32, NW = 4;
+    __shared__ __align__(16) float qf[DK];
+    __shared__ int qi[DK / 4];
+    __shared__ float qd[DK / 32];
+    __shared__ float wm[NW], wl[NW];
+    __shared__ float wacc[NW][DV];
+
+    const int iq1 = blockIdx.x, iq2 = blockIdx.y % p.n_head, iq3 = blockIdx.y / p.n_head, split = blockIdx.z;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float * qrow = reinterpret_cast<const float *>(p.q + iq1 * p.nbq1 + iq2 * p.nbq2 + iq3 * p.nbq3);
+    for (int i = tid; i < DK; i += 128) qf[i] = qrow[i];
+    __syncthreads();
+    if constexpr (KT == T_Q8_0) {
+        // quantise Q per 32 values (q8_0 arithmetic of the CPU path: d = amax/127, q = roundf(x/d))
+        for (int b = warp; b < DK / 32; b += NW) {
+            const float x = qf[32 * b + lane];
+            const float amax = warp_max(fabsf(x));
+            const float d = amax / 127.0f;
+            const int q = amax == 0.0f ? 0 : (int)roundf(x / d);
+            reinterpret_cast<int8_t *>(qi)[32 * b + lane] = (int8_t)q;
+            if (lane == 0) qd[b] = d;
+        }
+        __syncthreads();
+    }
+
+    const unsigned h = iq2;
+    const float slope = p.max_bias > 0.0f ? (h < p.n_head_log2 ? powf(p.m0, (float)(h + 1)) : powf(p.m1, (float)(2 * (h - p.n_head_log2) + 1))) : 1.0f;
+    const char * kbase = p.k + (iq2 / p.rk2) * p.nbk2 + (iq3 / p.rk3) * p.nbk3;
+    const char * vbase = p.v + (iq2 / p.rv2) * p.nbv2 + (iq3 / p.rv3) * p.nbv3;
+    const __half * mrow = p.mask ? reinterpret_cast<const __half *>(p.mask + iq1 * p.nbm1) : nullptr;
+
+    float M = -INFINITY, L = 0.0f, acc[EV];
+#pragma unroll
+    for (int e = 0; e < EV; ++e) acc[e] = 0.0f;
+
+    const int ntiles = (p.n_kv + 31) / 32;
+    const int t0 = split * p.tiles_per_split, t1 = min(ntiles, t0 + p.tiles_per_split);
+    for (int t = t0 + warp; t < t1; t += NW) {
+        const int ic = 32 * t + lane;
+        float s = -INFINITY;
+        if (ic < p.n_kv) {
+            const float mv = mrow ? slope * __half2float(mrow[ic]) : 0.0f;
+            if (mv != -INFINITY) {
+                s = k_dot<KT, DK>(kbase + (int64_t)ic * p.nbk1, qf, qi, qd) * p.scale;
+                if (p.softcap != 0.0f) s = p.softcap * tanhf(s);
+                s += mv;
+            }
+        }
+        const float tmax = warp_max(s);
+        if (tmax == -INFINITY) continue;            // whole tile masked (warp-uniform)
+        const float Mn = fmaxf(M, tmax);
+        const float corr = expf(M - Mn);            // M = -inf -> 0
+        const float pj = expf(s - Mn);              // s = -inf -> 0
+        L = L * corr + warp_sum(pj);
+#pragma unroll
+        for (int e = 0; e < EV; ++e) acc[e] *= corr;
+        M = Mn;
+        const int nvalid = min(32, p.n_kv - 32 * t);
+        for (int j = 0; j < nvalid; ++j) {
+            const float pv = __shfl_sync(0xffffffffu, pj, j);
+            if (pv != 0.0f) v_accum<VT, DV>(vbase + (int64_t)(32 * t + j) * p.nbv1, lane, pv, acc);
+        }
+    }
+
+    // combine the four warps
+    if (lane == 0) { wm[warp] = M; wl[warp] = L; }
+#pragma unroll
+    for (int e = 0; e < EV; ++e) wacc[warp][EV * lane + e] = acc[e];
+    __syncthreads();
+    float Mc = wm[0];
+    for (int w = 1; w < NW; ++w) Mc = fmaxf(Mc, wm[w]);
+    float Lc = 0.0f;
+    for (int w = 0; w < NW; ++w) Lc += wm[w] == -INFINITY ? 0.0f : wl[w] * expf(wm[w] - Mc);
+    const int64_t orow = ((int64_t)iq3 * p.N + iq1) * p.n_head + iq2;
+    for (int d = tid; d < DV; d += 128) {
+        float a = 0.0f;
+        for (int w = 0; w < NW; ++w) a += wm[w] == -INFINITY ? 0.0f : wacc[w][d] * expf(wm[w] - Mc);
+        if (p.nsplit == 1) reinterpret_cast<float *>(p.dst + orow * p.nbd1)[d] = a / Lc;
+        else p.part[(orow * p.nsplit + split) * (2 + DV) + 2 + d] = a;
+    }
+    if (p.nsplit > 1 && tid == 0) {
+        p.part[(orow * p.nsplit + split) * (2 + DV)] = Mc;
+        p.part[(orow * p.nsplit + split) * (2 + DV) + 1] = Lc;
+    }
+}
+
+// merge the split-KV partials: one warp per output row
+template <int DV>
+__global__ void __launch_bounds__(128) fattn_combine_kernel(const float * __restrict__ part, char * __restrict__ dst, int64_t nbd1, int64_t nrows, int nsplit) {
+    pdl_trigger(); pdl_wait();
+    const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (r >= nrows) return;
+    const float * pr = part + r * nsplit * (2 + DV);
+    float Mc = -INFINITY;
+    for (int s = 0; s < nsplit; ++s) Mc = fmaxf(Mc, pr[s * (2 + DV)]);
+    float Lc = 0.0f, a[DV / 32];
+#pragma unroll
+    for (int e = 0; e < DV / 32; ++e) a[e] = 0.0f;
+    for (int s = 0; s < nsplit; ++s) {
+        const float m = pr[s * (2 + DV)];
+        if (m == -INFINITY) continue;
+        const float w = expf(m - Mc);
+        Lc += pr[s * (2 + DV) + 1] * w;
+#pragma unroll
+        for (int e = 0; e < DV / 32; ++e) a[e] += pr[s * (2 + DV) + 2 + (DV / 32) * lane + e] * w;
+    }
+    float * out = reinterpret_cast<float *>(dst + r * nbd1);
+#pragma unroll
+    for (int e = 0; e < DV / 32; ++e) out[(DV / 32) * lane + e] = a[e] / Lc;
+}
+
+static int fa_splits(int64_t rows_heads, int ntiles) {
+    // enough CTAs for ~2 per SM, at least 4 tiles (one per warp) per CTA
+    int ns = (int)std::min<int64_t>(std::max<int64_t>(1, (2 * 148 + rows_heads - 1) / rows_heads), std::max(1, ntiles / 4));
+    return std::max(1, std::min(ns, 64));
+}
+
+template <int KT, int VT, int D>
+static int fa_launch(const fa_params & p, dim3 grid, cudaStream_t st) {
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = grid; lc.blockDim = dim3(128); lc.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+    B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_vec_kernel<KT, VT, D, D>, p));
+    ++g_launches;
+    if (p.nsplit > 1) {
+        const int64_t nrows = (int64_t)p.N * p.n_head * p.ne3;
+        lc.gridDim = dim3((unsigned)((nrows * 32 + 127) / 128));
+        B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_combine_kernel<D>, (const float *)p.part, p.dst, p.nbd1, nrows, p.nsplit));
+        ++g_launches;
+    }
+    return 0;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_flash_attn_supported(int k_type, int v_type, int64_t dk, int64_t dv) {
+    if (dk != dv || (dk != 64 && dk != 128)) return 0;
+    if (k_type != v_type) return 0;
+    return k_type == T_F16 || k_type == T_Q8_0;
+}
+
+extern "C" int64_t b200_flash_attn_scratch_bytes(const b200_tensor * q, const b200_tensor * k) {
+    const int64_t rows_heads = q->ne[1] * q->ne[2] * q->ne[3];
+    const int ns = fa_splits(rows_heads, (int)((k->ne[1] + 31) / 32));
+    return ns > 1 ? rows_heads * ns * (2 + q->ne[0]) * 4 : 0;
+}
+
+extern "C" int b200_op_flash_attn_ext(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
+                                      const b200_tensor * dst, float scale, float max_bias, float logit_softcap,
+                                      void * scratch, int64_t scratch_bytes, void * stream) {
+    if (!b200_flash_attn_supported(k->type, v->type, k->ne[0], v->ne[0]) || q->type != T_F32 || dst->type != T_F32) return -1;
+    if (q->ne[0] != k->ne[0] || q->nb[0] != 4 || dst->nb[0] != 4 || k->ne[1] != v->ne[1]) return -1;
+    if (mask && (mask->type != T_F16 || mask->nb[0] != 2 || mask->ne[0] < k->ne[1])) return -1;
+    if (k->type == T_F16 && ((((uintptr_t)k->data | k->nb[1] | k->nb[2] | k->nb[3]) & 15) || (((uintptr_t)v->data | v->nb[1] | v->nb[2] | v->nb[3]) & 7))) return -1;
+    if (q->ne[1] == 0 || k->ne[1] == 0) return 0;
+    fa_params p = {};
+    p.q = (const char *)q->data; p.k = (const char *)k->data; p.v = (const char *)v->data; p.mask = mask ? (const char *)mask->data : nullptr;
+    p.dst = (char *)dst->data;
+    p.nbq1 = q->nb[1]; p.nbq2 = q->nb[2]; p.nbq3 = q->nb[3]; p.nbk1 = k->nb[1]; p.nbk2 = k->nb[2]; p.nbk3 = k->nb[3];
+    p.nbv1 = v->nb[1]; p.nbv2 = v->nb[2]; p.nbv3 = v->nb[3]; p.nbm1 = mask ? mask->nb[1] : 0; p.nbd1 = dst->nb[1];
+    p.N = (int)q->ne[1]; p.n_head = (int)q->ne[2]; p.ne3 = (int)q->ne[3]; p.n_kv = (int)k->ne[1];
+    p.rk2 = (int)(q->ne[2] / k->ne[2]); p.rk3 = (int)(q->ne[3] / k->ne[3]); p.rv2 = (int)(q->ne[2] / v->ne[2]); p.rv3 = (int)(q->ne[3] / v->ne[3]);
+    if (logit_softcap != 0.0f) scale /= logit_softcap;
+    p.scale = scale; p.max_bias = max_bias; p.softcap = logit_softcap;
+    p.n_head_log2 = 1u << (unsigned)floorf(log2f((float)p.n_head));
+    p.m0 = powf(2.0f, -max_bias / p.n_head_log2); p.m1 = powf(2.0f, -(max_bias / 2.0f) / p.n_head_log2);
+    const int ntiles = (p.n_kv + 31) / 32;
+    const int64_t rows_heads = q->ne[1] * q->ne[2] * q->ne[3];
+    p.nsplit = fa_splits(rows_heads, ntiles);
+    if (p.nsplit > 1 && (!scratch || scratch_bytes < rows_heads * p.nsplit * (2 + q->ne[0]) * 4)) p.nsplit = 1;
+    p.tiles_per_split = (ntiles + p.nsplit - 1) / p.nsplit;
+    p.part = (float *)scratch;
+    const dim3 grid((unsigned)q->ne[1], (unsigned)(q->ne[2] * q->ne[3]), (unsigned)p.nsplit);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int D = (int)q->ne[0];
+    if (k->type == T_F16) return D == 128 ? fa_launch<T_F16, T_F16, 128>(p, grid, st) : fa_launch<T_F16, T_F16, 64>(p, grid, st);
+    return D == 128 ? fa_launch<T_Q8_0, T_Q8_0, 128>(p, grid, st) : fa_launch<T_Q8_0, T_Q8_0, 64>(p, grid, st);
+}

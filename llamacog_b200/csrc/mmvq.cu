@@ -52,7 +52,7 @@ static int configure(int type, int N, int K, int M, const b200_mmvq_args & a, mm
     const int nseg = bpr / G;
     const int sms = num_sms();
 
-    const bool w_aligned = (((uintptr_t)a.W | (uintptr_t)a.nb1 | (uintptr_t)a.w_ch_stride) & 15) == 0;
+    const bool w_aligned = (((uintptr_t)a.W | (uintptr_t)a.nb1 | (uintptr_t)a.w_sy | (uintptr_t)a.w_sz) & 15) == 0;
     const bool contig = w_aligned && a.nb1 == rb && (rb % 16) == 0;
     const int pitch = contig ? rb : ((rb + 16 + 15) & ~15);
     const size_t act_bytes = (size_t)M * bpr * ACT_ITEM;
@@ -113,7 +113,7 @@ static int configure(int type, int N, int K, int M, const b200_mmvq_args & a, mm
     p.CW = bCW; p.NG = bNG; p.BPR = bpr; p.G = G; p.act_bytes = (int)act_bytes;
     p.rows_q = N / gx; p.rows_rem = N % gx;
     c.M = M; c.A16 = (w_aligned && item_bytes(type) % 16 == 0) ? 1 : 0;
-    c.grid = dim3(gx, std::max(1, a.nchannels), 1);
+    c.grid = dim3(gx, std::max(1, a.ny), std::max(1, a.nz));
     c.block = dim3(288, 1, 1);   // producer warp + 8 warps (all quantise; CW*NG of them consume)
     c.smem = (size_t)nstages * stage_bytes + act_bytes + (((size_t)nstages * R * nseg * M + 1) & ~(size_t)1) * 4 + (size_t)nstages * 16 + 8;
     return 0;
@@ -154,12 +154,14 @@ extern "C" int b200_mul_mat_vec_q_ex(const b200_mmvq_args * a, void * stream) {
         mmvq_params p = {};
         p.W = (const uint8_t *)a->W; p.nb1 = a->nb1;
         p.X = a->X ? a->X + (int64_t)m0 * a->xs : nullptr; p.xs = a->xs;
-        p.Xq = a->Xq ? (const uint8_t *)a->Xq + (size_t)m0 * ((a->K + 255) / 256) * ACT_ITEM : nullptr; p.xq_ch_stride = a->xq_ch_stride;
+        p.Xq = a->Xq ? (const uint8_t *)a->Xq + (size_t)m0 * ((a->K + 255) / 256) * ACT_ITEM : nullptr;
         p.dst = a->dst + (int64_t)m0 * a->ds; p.ds = a->ds;
         p.N = a->N; p.K = a->K;
-        p.w_ch_stride = a->w_ch_stride; p.x_ch_stride = a->x_ch_stride; p.d_ch_stride = a->d_ch_stride;
-        p.ids = a->ids; p.x_ch_mod = a->x_ch_mod > 0 ? a->x_ch_mod : 1 << 30; p.w_ch_div = a->w_ch_div > 0 ? a->w_ch_div : 1;
-        p.vec_ok = ((((uintptr_t)p.X) | ((uintptr_t)a->xs * 4) | ((uintptr_t)a->x_ch_stride * 4)) & 15) == 0;
+        p.w_sy = a->w_sy; p.w_sz = a->w_sz; p.w_div_y = std::max(1, a->w_div_y); p.w_div_z = std::max(1, a->w_div_z);
+        p.x_sy = a->x_sy; p.x_sz = a->x_sz; p.x_mod_y = a->x_mod_y > 0 ? a->x_mod_y : 1 << 30;
+        p.d_sy = a->d_sy; p.d_sz = a->d_sz; p.ids = a->ids; p.ids_sz = a->ids_sz;
+        p.xq_sy = a->xq_sy; p.xq_sz = a->xq_sz;
+        p.vec_ok = ((((uintptr_t)p.X) | ((uintptr_t)a->xs * 4) | ((uintptr_t)a->x_sy * 4) | ((uintptr_t)a->x_sz * 4)) & 15) == 0;
         p.dbg_sumi = a->dbg_sumi ? a->dbg_sumi + (int64_t)m0 * a->N * (a->K / 32) : nullptr;
         mmvq_launch_cfg c = {};
         int rc = configure(a->type, a->N, a->K, mc, *a, p, c);
@@ -176,6 +178,6 @@ extern "C" int b200_mul_mat_vec_q(int type, const void * W, int64_t nb1, const f
                                   float * dst, int64_t ds, int N, int K, int M, void * stream) {
     b200_mmvq_args a = {};
     a.type = type; a.W = W; a.nb1 = nb1; a.X = X; a.xs = xs; a.dst = dst; a.ds = ds; a.N = N; a.K = K; a.M = M;
-    a.nchannels = 1; a.pdl = -1;
+    a.ny = 1; a.nz = 1; a.pdl = -1;
     return b200_mul_mat_vec_q_ex(&a, stream);
 }

@@ -31,18 +31,18 @@ struct mmvq_params {
     int64_t nb1;             // bytes between rows
     const float * X;         // activations, column m at X + m*xs
     const uint8_t * Xq;      // optional: activations already quantised (mmvq_units.cuh layout, column stride BPR*400)
-    int64_t xq_ch_stride;    // bytes between channels of Xq
     int64_t xs;
     float * dst;             // dst[m*ds + row]
     int64_t ds;
     int N, K;
-    // batch/expert channels (blockIdx.y): per-channel offsets; ids selects the weight matrix
-    int64_t w_ch_stride;     // bytes between weight matrices (experts / broadcast dims)
-    int64_t x_ch_stride;     // floats
-    int64_t d_ch_stride;     // floats
-    const int32_t * ids;     // optional [nchannels]: expert index per channel (MUL_MAT_ID decode)
-    int x_ch_mod;            // channel c reads X channel (c % x_ch_mod) (ne11 broadcast of MUL_MAT_ID)
-    int w_ch_div;            // channel c reads W matrix (c / w_ch_div) when ids == nullptr (ne02 broadcast)
+    // batch/expert channels: blockIdx.y = y, blockIdx.z = z (see b200_mmvq_args)
+    int64_t w_sy, w_sz;      // bytes
+    int w_div_y, w_div_z;
+    int64_t x_sy, x_sz;      // floats
+    int x_mod_y;
+    int64_t d_sy, d_sz;      // floats
+    const int32_t * ids; int64_t ids_sz;
+    int64_t xq_sy, xq_sz;    // bytes
     // launch geometry
     int R;                   // rows per stage
     int nstages;
@@ -78,12 +78,19 @@ __global__ void __launch_bounds__(288, (M <= 4 ? 2 : 1)) mmvq_kernel(const mmvq_
     const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * p.nstages, actbar = empty0 + 8 * p.nstages;
 
     // channel (batch / expert) addressing
-    const int ch = blockIdx.y;
-    int wsel = 0, xch = 0;
-    if (gridDim.y > 1 || p.ids) { wsel = p.ids ? p.ids[ch] : ch / p.w_ch_div; xch = ch % p.x_ch_mod; }
-    const uint8_t * Wc = p.W + (int64_t)wsel * p.w_ch_stride;
-    const float * Xc = p.X + (int64_t)xch * p.x_ch_stride;
-    float * Dc = p.dst + (int64_t)ch * p.d_ch_stride;
+    const uint8_t * Wc = p.W;
+    const float * Xc = p.X;
+    const uint8_t * Xqc = p.Xq;
+    float * Dc = p.dst;
+    if (gridDim.y > 1 || gridDim.z > 1 || p.ids) {
+        const int y = blockIdx.y, z = blockIdx.z;
+        if (p.ids) Wc += (int64_t)p.ids[z * p.ids_sz + y] * p.w_sy;
+        else Wc += (int64_t)(y / p.w_div_y) * p.w_sy + (int64_t)(z / p.w_div_z) * p.w_sz;
+        const int xy = y % p.x_mod_y;
+        if (Xc) Xc += (int64_t)xy * p.x_sy + (int64_t)z * p.x_sz;
+        if (Xqc) Xqc += (int64_t)xy * p.xq_sy + (int64_t)z * p.xq_sz;
+        Dc += (int64_t)y * p.d_sy + (int64_t)z * p.d_sz;
+    }
 
     // balanced contiguous row range of this CTA: the first rows_rem CTAs take one extra row
     const int cta = blockIdx.x;
@@ -130,7 +137,7 @@ __global__ void __launch_bounds__(288, (M <= 4 ? 2 : 1)) mmvq_kernel(const mmvq_
         if (lane == 0) for (int g = 0; g < min(ngroups, p.nstages); ++g) issue(g);
         pdl_wait();   // dst may still be read by the previous grid; Xq is written by it
         if (p.Xq && lane == 0) {
-            const uint8_t * xq = p.Xq + (int64_t)xch * p.xq_ch_stride;
+            const uint8_t * xq = Xqc;
             mbar_expect_tx(actbar, (uint32_t)M * acs);
             for (int m = 0; m < M; ++m) bulk_g2s(smem_u32(act) + m * acs, xq + (size_t)m * acs, acs, actbar);
         }

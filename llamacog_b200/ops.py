@@ -18,9 +18,10 @@ BLOCK_ELEMS = {Q4_0: 32, Q8_0: 32, Q8_1: 32, Q4_K: 256, Q5_K: 256, Q6_K: 256, F3
 class MmvqArgs(C.Structure):
     _fields_ = [("type", C.c_int), ("W", C.c_void_p), ("nb1", C.c_int64), ("X", C.c_void_p), ("xs", C.c_int64),
                 ("dst", C.c_void_p), ("ds", C.c_int64), ("N", C.c_int), ("K", C.c_int), ("M", C.c_int),
-                ("nchannels", C.c_int), ("w_ch_stride", C.c_int64), ("x_ch_stride", C.c_int64),
-                ("d_ch_stride", C.c_int64), ("ids", C.c_void_p), ("x_ch_mod", C.c_int), ("w_ch_div", C.c_int),
-                ("pdl", C.c_int), ("dbg_sumi", C.c_void_p), ("Xq", C.c_void_p), ("xq_ch_stride", C.c_int64)]
+                ("ny", C.c_int), ("nz", C.c_int), ("w_sy", C.c_int64), ("w_sz", C.c_int64), ("w_div_y", C.c_int),
+                ("w_div_z", C.c_int), ("x_sy", C.c_int64), ("x_sz", C.c_int64), ("x_mod_y", C.c_int),
+                ("d_sy", C.c_int64), ("d_sz", C.c_int64), ("ids", C.c_void_p), ("ids_sz", C.c_int64),
+                ("pdl", C.c_int), ("dbg_sumi", C.c_void_p), ("Xq", C.c_void_p), ("xq_sy", C.c_int64), ("xq_sz", C.c_int64)]
 
 
 _lib = None
@@ -79,9 +80,8 @@ def mul_mat_vec_q(t, W, X, N, K, nb1=None, dbg=False, pdl=-1, Xq=None):
     dst = torch.empty((M, N), dtype=torch.float32, device=X.device)
     sums = torch.zeros((M, N, K // 32), dtype=torch.int32, device=X.device) if dbg else None
     a = MmvqArgs(type=t, W=W.data_ptr(), nb1=nb1 or row_bytes(t, K), X=X.data_ptr(), xs=X.stride(0),
-                 dst=dst.data_ptr(), ds=N, N=N, K=K, M=M, nchannels=1, w_ch_stride=0, x_ch_stride=0, d_ch_stride=0,
-                 ids=None, x_ch_mod=0, w_ch_div=0, pdl=pdl, dbg_sumi=sums.data_ptr() if dbg else None,
-                 Xq=Xq.data_ptr() if Xq is not None else None, xq_ch_stride=0)
+                 dst=dst.data_ptr(), ds=N, N=N, K=K, M=M, ny=1, nz=1, pdl=pdl, dbg_sumi=sums.data_ptr() if dbg else None,
+                 Xq=Xq.data_ptr() if Xq is not None else None)
     _check(lib().b200_mul_mat_vec_q_ex(C.byref(a), _stream()), "b200_mul_mat_vec_q_ex")
     return (dst, sums) if dbg else dst
 
