@@ -1,27 +1,25 @@
 #!/usr/bin/env python
 """bench.py -- headline measurement of the hot path.
 
-Workload (BASELINE.json configs[1]): Llama-3-8B Q4_K_M, batch-1 decode.  One STEP = one token = every
-quantised MUL_MAT of the model (32 layers x {wq,wk,wv,wo,gate,up,down} + lm_head, 225 GEMVs, 4.616 GB
-of weights in the Q4_K_M tensor-type mix of reference src/llama-quant.cpp:185-224,291-353), run through
-the C ABI of include/b200_ops.h from one CUDA graph, the way the backend's graph_compute replays a
-decode step.  Weights are synthetic random-init blocks (random payload bits, sane fp16 scales), every
-matrix a distinct allocation, so a step streams 4.6 GB from HBM (inputs >> 126 MB L2; no L2 flush
-needed).
+Workload (BASELINE.json configs[1]): Llama-3-8B Q4_K_M, batch-1 decode (tg), flash attention on, f16 KV cache.
+One STEP = one decoded token = one pass of the whole quantised forward graph (32 layers + lm_head, 4.616 GB of
+Q4_K/Q6_K weights streamed from HBM, ~420 kernels) through the reference's own front end: the UNMODIFIED
+llama-bench of the reference (baseline/_ref/bin) loads the plugin libggml-b200.so through GGML_BACKEND_PATH
+(ggml/src/ggml-backend-reg.cpp:586-590) and drives libllama -> ggml_backend_sched -> our graph_compute.
+The model is a random-init GGUF of that architecture written by tools/make_gguf.py (reference quantiser).
 
-  value   tokens/s, everything resident in HBM, CUDA events on the launching stream, max over ranks
-  e2e     tokens/s through the same C-ABI calls with HOST buffers: each step copies the activation
-          vector from pinned host memory, replays the step and reads the logits back
-  roofline  the dominant kernel (mmvq_kernel<Q4_K>): algorithmic bytes (N*K*144/256 per launch) over its
-          mean launch duration, timed live with CUDA events on a graph holding only those launches
-  cpu_baseline  the oracle port (single thread, scalar C) on a bounded sample of the same GEMVs
+  e2e     llama-bench's own tokens/s: every step copies token id / positions / mask from host memory, runs the
+          graph on the GPU and reads the 128256 logits back to the host (the call a user makes)
+  value   tokens / device time of the graph_compute calls of the same run, taken with CUDA events on the backend's
+          stream (B200_TIMING=1 makes the plugin accumulate them); inputs are resident in HBM at that point
+  roofline  the dominant kernel, mmvq_kernel<Q4_K>: algorithmic bytes (N*K*144/256 per launch) over its mean launch
+          duration, timed live in this process with CUDA events on a CUDA graph holding exactly the 192 Q4_K
+          GEMVs of one token (distinct weight matrices, 3.36 GB > L2), through the C ABI of include/b200_ops.h
+  cpu_baseline  the reference CPU backend on the same GGUF (llama-bench -ngl 0, all host threads), bounded to tg16
 
-`--impl reference` times the reference's own CPU code for the path on the host cores: the unmodified
-ggml CPU backend from baseline/_ref (test-backend-ops perf -b CPU, all threads) when it is present,
-else the oracle port.
-
-N > 1 (torchrun): the path shards by weight rows with no data-path collective at this level (each
-rank holds its own replica of the step: weak scaling, value = sum of ranks' tokens / max time).
+`--impl reference` times the reference's own CPU implementation (same llama-bench, no plugin) on the same model.
+N > 1 (torchrun): the decode path of an 8B model does not shard at this level (row split is SURVEY 8e, next):
+replicas only -- every rank runs the same workload on its own GPU, value = tokens of all ranks / max time.
 """
 import argparse
 import json
@@ -35,6 +33,12 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+REF_BIN = os.path.join(ROOT, "baseline", "_ref", "bin")
+REF_LIB = os.path.join(ROOT, "baseline", "_ref", "lib")
+PLUGIN = os.path.join(ROOT, "llamacog_b200", "libggml-b200.so")
+MODEL_DIR = os.environ.get("B200_MODEL_DIR", "/tmp/b200_models")
+METRIC = "llama-bench tg tokens/s, Llama-3-8B Q4_K_M (batch-1 decode)"
+
 N_EMBD, N_FF, N_LAYER, N_KV, N_VOCAB = 4096, 14336, 32, 1024, 128256
 Q4_K, Q6_K = 12, 14
 BPW = {Q4_K: 144 / 256, Q6_K: 210 / 256}
@@ -45,7 +49,7 @@ def use_more_bits(i, n):   # reference src/llama-quant.cpp:185-187
 
 
 def step_plan():
-    """[(name, type, N, K, input, output)] of one decode token, Q4_K_M mix."""
+    """[(name, type, N, K, input, output)] of the quantised MUL_MATs of one decode token, Q4_K_M mix."""
     plan = []
     for il in range(N_LAYER):
         more = use_more_bits(il, N_LAYER)
@@ -85,24 +89,26 @@ class ClockSampler(threading.Thread):
                     rs = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
                 except Exception:
                     rs = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                self.samples.append((time.time(), mhz, rs))
+                util = self.nv.nvmlDeviceGetUtilizationRates(self.h).gpu
+                self.samples.append((time.time(), mhz, rs, util))
             except Exception:
                 pass
-            time.sleep(0.004)
+            time.sleep(0.01)
 
     def summary(self, t0, t1):
         if not self.ok:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable"]}
-        inside = [s for s in self.samples if t0 <= s[0] <= t1] or self.samples[-3:]
-        mhz = sorted(s[1] for s in inside)
+        inside = [s for s in self.samples if t0 <= s[0] <= t1]
+        loaded = [s for s in inside if s[3] > 0] or inside or self.samples[-3:]
+        mhz = sorted(s[1] for s in loaded)
         bits = 0
-        for s in inside:
+        for s in loaded:
             bits |= s[2]
-        names = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
-                 0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
-                 0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+        names = {0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x10: "sync_boost",
+                 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown",
+                 0x100: "display_clock_setting"}
         return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": self.max_mhz,
-                "reasons": [n for b, n in names.items() if bits & b and n != "gpu_idle"], "samples": len(inside)}
+                "reasons": [n for b, n in names.items() if bits & b], "samples": len(loaded)}
 
 
 def measured_peak():
@@ -113,233 +119,212 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def cpu_port_baseline(budget_s=12.0):
-    """Oracle port, 1 thread, on a bounded sample: rows of the ffn_down Q4_K and Q6_K GEMVs."""
-    import numpy as np
-    import oracle as O
-    rng = np.random.default_rng(0)
-    K = N_EMBD
-    done_bytes, t_used, rows = 0, 0.0, 256
-    x = rng.uniform(-1, 1, (1, K)).astype(np.float32)
-    for t in (O.Q4_K, O.Q6_K):
-        W = O.random_quant_bytes(t, rows, K, rng)
-        O.mul_mat_vec_q(t, W[:8], x, 8, K, 1)
-        reps, t0 = 0, time.perf_counter()
-        while time.perf_counter() - t0 < budget_s / 2:
-            O.mul_mat_vec_q(t, W, x, rows, K, 1)
-            reps += 1
-        t_used += time.perf_counter() - t0
-        done_bytes += reps * rows * O.row_bytes(t, K)
-    tok_s = (done_bytes / t_used) / plan_bytes(step_plan())
-    return {"value": tok_s, "unit": "tokens/s", "cores": 1, "kind": "port",
-            "sample": "%d-row slices of 4096-wide Q4_K and Q6_K GEMVs (fused q8_1 quantise + int dot), %.0f s, "
-                      "scaled by bytes to the 4.616 GB token" % (rows, t_used)}
+def ensure_model(preset="llama3-8b", ftype="q4_k_m"):
+    os.makedirs(MODEL_DIR, exist_ok=True)
+    path = os.path.join(MODEL_DIR, "%s-%s.gguf" % (preset, ftype))
+    if not os.path.exists(path):
+        tmp = path + ".tmp.%d" % os.getpid()
+        subprocess.check_call([sys.executable, os.path.join(ROOT, "tools", "make_gguf.py"), preset, ftype, tmp],
+                              stdout=subprocess.DEVNULL)
+        os.replace(tmp, path)
+    return path
+
+
+def llama_bench(model, extra, plugin, timing=False, device=None, timeout=1800):
+    """Run the reference's llama-bench; returns (list of json results, stats dict from the plugin)."""
+    exe = os.path.join(REF_BIN, "llama-bench")
+    if not os.path.exists(exe):
+        raise RuntimeError("baseline/_ref/bin/llama-bench is missing: run __graft_entry__.build() where /root/reference exists")
+    env = dict(os.environ)
+    env["LD_LIBRARY_PATH"] = REF_LIB + ":" + os.path.join(ROOT, "llamacog_b200") + ":" + env.get("LD_LIBRARY_PATH", "")
+    env.pop("GGML_BACKEND_PATH", None)
+    if plugin:
+        if not os.path.exists(PLUGIN):
+            raise RuntimeError("llamacog_b200/libggml-b200.so is not built; there is no CPU fallback")
+        env["GGML_BACKEND_PATH"] = PLUGIN
+        if timing:
+            env["B200_TIMING"] = "1"
+        if device is not None:
+            env["CUDA_VISIBLE_DEVICES"] = str(device)
+    r = subprocess.run([exe, "-m", model, "-o", "json"] + extra, capture_output=True, text=True, env=env, timeout=timeout)
+    if r.returncode != 0:
+        raise RuntimeError("llama-bench failed (%d): %s" % (r.returncode, r.stderr[-2000:]))
+    res = json.loads(r.stdout[r.stdout.index("["):])
+    stats = {}
+    m = re.search(r"ggml-b200: stats graphs=(\d+) device_ms=([0-9.]+) kernel_launches=(\d+)", r.stderr)
+    if m:
+        stats = {"graphs": int(m.group(1)), "device_ms": float(m.group(2)), "launches": int(m.group(3))}
+    if plugin and "B200" not in r.stdout + r.stderr:
+        raise RuntimeError("llama-bench did not load the B200 backend: " + r.stderr[-1000:])
+    return res, stats
+
+
+def kernel_roofline(steps, warmup, dev_index):
+    """Dominant kernel timed live: the 192 Q4_K GEMVs of one token from a CUDA graph, CUDA events on its stream."""
+    import ctypes as C
+    import torch
+    from llamacog_b200 import ops
+    from tools.mmvq_micro import rand_weights
+    torch.cuda.set_device(dev_index)
+    dev = torch.device("cuda", dev_index)
+    ops.lib()
+    plan = [p for p in step_plan() if p[1] == Q4_K]
+    weights = [rand_weights(t, N * ops.row_bytes(t, K), dev) for _, t, N, K, _, _ in plan]
+    X = {4096: torch.rand(1, 4096, device=dev) * 2 - 1, 14336: torch.rand(1, 14336, device=dev) * 2 - 1}
+    out = {N: torch.zeros(1, N, device=dev) for N in (4096, 1024, 14336)}
+    xq = {K: ops.quantize_acts(x) for K, x in X.items()}
+
+    def run():
+        for (_, t, N, K, _, _), W in zip(plan, weights):
+            a = ops.MmvqArgs(type=t, W=W.data_ptr(), nb1=ops.row_bytes(t, K), X=X[K].data_ptr(), xs=K, dst=out[N].data_ptr(),
+                             ds=N, N=N, K=K, M=1, ny=1, nz=1, pdl=-1, dbg_sumi=None, Xq=xq[K].data_ptr())
+            rc = ops.lib().b200_mul_mat_vec_q_ex(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+            if rc:
+                raise RuntimeError("b200_mul_mat_vec_q_ex rc=%d" % rc)
+
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        run()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=st):
+            run()
+        for _ in range(max(3, warmup)):
+            g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        for _ in range(steps):
+            g.replay()
+        e1.record(st)
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    nbytes = plan_bytes(plan)
+    return {"launches": len(plan), "us_per_launch": ms * 1e3 / len(plan), "bytes": nbytes, "gbps": nbytes / (ms * 1e-3) / 1e9}
+
+
+def cpu_reference_run(model, n_tokens, threads):
+    res, _ = llama_bench(model, ["-ngl", "0", "-p", "0", "-n", str(n_tokens), "-r", "1", "-t", str(threads)], plugin=False)
+    return float(res[-1]["avg_ts"])
 
 
 def reference_arm(args):
-    """The reference's own CPU implementation of the path on the host cores."""
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+    """The reference's own CPU implementation of the path on the host cores (unmodified llama-bench, no plugin)."""
+    if int(os.environ.get("RANK", "0")) != 0:
         return
-    plan = step_plan()
-    tbo = os.path.join(ROOT, "baseline", "_ref", "bin", "test-backend-ops")
-    cores = os.cpu_count() or 1
-    out = None
-    if os.path.exists(tbo):
-        # unmodified reference CPU backend: MUL_MAT m=4096,k=14336,n=1 perf cases of its own test tool
-        # (tests/test-backend-ops.cpp:4622-4628), all host threads
-        try:
-            env = dict(os.environ)
-            env["LD_LIBRARY_PATH"] = os.path.join(ROOT, "baseline", "_ref", "lib") + ":" + env.get("LD_LIBRARY_PATH", "")
-            r = subprocess.run([tbo, "perf", "-b", "CPU", "-o", "MUL_MAT", "-p", "type_a=(q4_K|q6_K),type_b=f32,m=4096,n=1,k=14336"], capture_output=True, text=True, timeout=900, env=env)
-            us = {}
-            for line in r.stdout.splitlines():
-                m = re.search(r"MUL_MAT\(type_a=(q4_K|q6_K),type_b=f32,m=4096,n=1,k=14336.*?([0-9.]+) us/run", line)
-                if m:
-                    us[m.group(1)] = float(m.group(2))
-            if "q4_K" in us and "q6_K" in us:
-                b4, b6 = 4096 * 14336 * BPW[Q4_K], 4096 * 14336 * BPW[Q6_K]
-                t_tok = plan_bytes(plan, Q4_K) / b4 * us["q4_K"] * 1e-6 + plan_bytes(plan, Q6_K) / b6 * us["q6_K"] * 1e-6
-                out = {"value": 1.0 / t_tok, "kind": "reference", "cores": cores,
-                       "sample": "reference test-backend-ops perf -b CPU -o MUL_MAT, m=4096 k=14336 n=1: q4_K %.0f us, q6_K %.0f us "
-                                 "per GEMV, scaled by bytes to the 4.616 GB token" % (us["q4_K"], us["q6_K"])}
-        except Exception as e:  # noqa: BLE001
-            sys.stderr.write("reference tool failed (%s); falling back to the oracle port\n" % e)
-    if out is None:
-        b = cpu_port_baseline(20.0)
-        out = {"value": b["value"], "kind": "port", "cores": 1, "sample": b["sample"]}
-    line = {"impl": "reference", "metric": "llama3-8b-q4_k_m tg (batch-1 decode) tokens/s", "value": out["value"],
-            "unit": "tokens/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 / out["value"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "q4_K/q6_K x q8 (int8 dot, f32 accumulate)", "data": "synthetic",
-            "config": {"workload": "llama3-8b-q4_k_m-decode-b1: 225 quantised MUL_MAT GEMVs per token"},
-            "cpu_baseline": {"value": out["value"], "unit": "tokens/s", "cores": out["cores"], "kind": out["kind"], "sample": out["sample"]},
-            "e2e": {"value": out["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    model = ensure_model()
+    threads = os.cpu_count() or 1
+    n = max(4, min(args.steps, 64))
+    v = cpu_reference_run(model, n, threads)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "tokens/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 / v, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "q4_K/q6_K weights x q8_K activations (int8 dot, f32 accumulate)", "data": "synthetic",
+            "config": {"workload": "llama3-8b-q4_k_m tg, batch 1, reference ggml CPU backend via llama-bench -ngl 0"},
+            "cpu_baseline": {"value": v, "unit": "tokens/s", "cores": threads, "kind": "reference",
+                             "sample": "llama-bench -ngl 0 -p 0 -n %d -r 1 -t %d (after its 1-token warm-up)" % (n, threads)},
+            "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=128)
+    ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
         return reference_arm(args)
 
-    import torch
-    import torch.distributed as dist
-    from llamacog_b200 import ops
-    from tools.mmvq_micro import rand_weights
-
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
+    dist = None
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    ops.lib()
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if rank == 0:
+        model = ensure_model()
+    if world > 1:
+        dist.barrier()
+    model = ensure_model()
 
-    plan = step_plan()
-    torch.manual_seed(1234 + rank)
-    weights = [rand_weights(t, N * ops.row_bytes(t, K), dev) for _, t, N, K, _, _ in plan]
-    bufs = {"h": torch.rand(1, N_EMBD, device=dev) * 2 - 1}
-    for _, _, N, _, _, o in plan:
-        if o not in bufs:
-            bufs[o] = torch.zeros(1, N, device=dev)
-    host_x = torch.rand(1, N_EMBD).pin_memory()
-    host_logits = torch.empty(1, N_VOCAB).pin_memory()
-    x_in = torch.empty(1, N_EMBD, device=dev)
-
-    import ctypes as C
-
-    # where the q8_1 quantisation of the activations runs: "none" = fused prologue of every GEMV;
-    # "down" = one quantise kernel in front of ffn_down (K=14336), "all" = one per distinct activation
-    # vector (q/k/v share one, gate/up share one), the GEMVs then copy the quantised vector
-    xq_mode = os.environ.get("B200_BENCH_XQ", "all")
-    xq_bufs = {}
-
-    def launch(t, W, X, dst, N, K, name="", src=""):
-        xq = None
-        if xq_mode == "all" or (xq_mode == "down" and K > 8192):
-            fresh = name in ("wq", "wo", "gate", "down", "output")     # first consumer of a new activation vector
-            if fresh or src not in xq_bufs:
-                if src not in xq_bufs:
-                    xq_bufs[src] = torch.empty(((K + 255) // 256 * 400,), dtype=torch.uint8, device=dev)
-                rc = ops.lib().b200_quantize_acts(C.c_void_p(X.data_ptr()), C.c_int64(K), C.c_void_p(xq_bufs[src].data_ptr()),
-                                                  C.c_int(K), C.c_int(1), C.c_void_p(torch.cuda.current_stream().cuda_stream))
-                if rc:
-                    raise RuntimeError("b200_quantize_acts rc=%d" % rc)
-            xq = xq_bufs[src].data_ptr()
-        a = ops.MmvqArgs(type=t, W=W.data_ptr(), nb1=ops.row_bytes(t, K), X=X.data_ptr(), xs=K, dst=dst.data_ptr(), ds=N,
-                         N=N, K=K, M=1, ny=1, nz=1, pdl=-1, dbg_sumi=None, Xq=xq)
-        rc = ops.lib().b200_mul_mat_vec_q_ex(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream))
-        if rc:
-            raise RuntimeError("b200_mul_mat_vec_q_ex rc=%d" % rc)
-
-    def run_step(only=None, first_input=None):
-        for (name, t, N, K, i, o), W in zip(plan, weights):
-            if only is not None and t != only:
-                continue
-            X = first_input if (first_input is not None and name == "wq" and W is weights[0]) else bufs[i]
-            launch(t, W, X, bufs[o], N, K, name, i)
-
-    st = torch.cuda.Stream()
-    graphs = {}
-    with torch.cuda.stream(st):
-        for _ in range(2):
-            run_step()
-        torch.cuda.synchronize()
-        for key, only, first in (("all", None, None), ("q4k", Q4_K, None), ("e2e", None, x_in)):
-            g = torch.cuda.CUDAGraph()
-            n0 = ops.kernel_launch_count()
-            with torch.cuda.graph(g, stream=st):
-                run_step(only, first)
-            graphs[key] = (g, ops.kernel_launch_count() - n0)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps, warmup):
-        with torch.cuda.stream(st):
-            for _ in range(warmup):
-                fn()
-            barrier()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            t0 = time.time()
-            e0.record(st)
-            for _ in range(steps):
-                fn()
-            e1.record(st)
-            barrier()
-            t1 = time.time()
-        ms = e0.elapsed_time(e1)
-        if world > 1:
-            tt = torch.tensor([ms], device=dev)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            ms = float(tt.item())
-        return ms, t0, t1
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    device = vis.split(",")[local] if vis else str(local)
+    lb = ["-ngl", "99", "-fa", "1", "-p", "0", "-n", "%d,%d" % (args.warmup, args.steps), "-r", "1"]
 
     sampler = ClockSampler(local)
     sampler.start()
-    g_all, launches_per_step = graphs["all"]
-    ms, t0, t1 = timed(g_all.replay, args.steps, args.warmup)
+    if world > 1:
+        dist.barrier()
+    t0 = time.time()
+    res, _ = llama_bench(model, lb, plugin=True, device=device)                       # e2e: host buffers in and out
+    t1 = time.time()
     clocks = sampler.summary(t0, t1)
-    ms_step = ms / args.steps
-    value = world * 1e3 / ms_step
-
-    # dominant kernel, timed live: a graph with only the Q4_K launches of the step
-    g_q4, n_q4 = graphs["q4k"]
-    ms_q4, _, _ = timed(g_q4.replay, args.steps, args.warmup)
-    q4_bytes = plan_bytes(plan, Q4_K)
-    ach = q4_bytes / (ms_q4 / args.steps * 1e-3) / 1e9
-    peak, how = measured_peak()
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "r01_mmvq_q4k_traffic.json")
-    if os.path.exists(tpath):
-        try:
-            traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
-        except Exception:
-            traffic = None
-
-    # end to end: host buffers in, logits out, every step
-    g_e2e, _ = graphs["e2e"]
-
-    def e2e_step():
-        x_in.copy_(host_x, non_blocking=True)
-        g_e2e.replay()
-        host_logits.copy_(bufs["logits"], non_blocking=True)
-        st.synchronize()
-
-    ms_e2e, _, _ = timed(e2e_step, args.steps, args.warmup)
+    res_t, stats = llama_bench(model, lb, plugin=True, timing=True, device=device)    # device time of graph_compute
     sampler.stop_flag = True
-    e2e_val = world * 1e3 / (ms_e2e / args.steps)
+    e2e_rank = float(res[-1]["avg_ts"])
+    n_tok = args.warmup + args.steps + 2            # llama-bench decodes one warm-up token in front of each test
+    if not stats or stats["graphs"] <= 0:
+        raise RuntimeError("the plugin reported no graph_compute calls: the CUDA path did not run")
+    dev_ms_per_graph = stats["device_ms"] / stats["graphs"]
+    graphs_per_tok = stats["graphs"] / n_tok
+    ms_step = dev_ms_per_graph * graphs_per_tok
+    launches_per_step = stats["launches"] / n_tok
+
+    if world > 1:
+        import torch
+        tt = torch.tensor([ms_step, 1e3 / e2e_rank], device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_step, e2e_ms = float(tt[0]), float(tt[1])
+    else:
+        e2e_ms = 1e3 / e2e_rank
+    value = world * 1e3 / ms_step
+    e2e_val = world * 1e3 / e2e_ms
 
     if rank == 0:
-        line = {"metric": "llama3-8b-q4_k_m tg (batch-1 decode) tokens/s", "value": value, "unit": "tokens/s",
-                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "q4_K/q6_K x q8 (int8 dot, f32 accumulate)", "data": "synthetic",
-                "config": {"workload": "llama3-8b-q4_k_m-decode-b1: 225 quantised MUL_MAT GEMVs per token (4.616 GB weights, "
-                                       "Q4_K_M type mix), fused q8_1 prologue; non-matmul glue ops not yet in the timed step",
-                           "l2": "inputs larger than L2 (4.6 GB streamed per step)", "activation_quantise": xq_mode, "parallelism": "replicas x%d" % world},
+        n_kv = 256
+        line = {"metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "q4_K/q6_K weights x q8_1 activations (int8 dp4a, f32 accumulate), f16 KV", "data": "synthetic",
+                "config": {"workload": "llama3-8b-q4_k_m tg%d: unmodified reference llama-bench -ngl 99 -fa 1 -p 0 over the "
+                                       "libggml-b200.so plugin; random-init GGUF (tools/make_gguf.py, reference quantiser, no_vocab)" % args.steps,
+                           "l2": "inputs larger than L2 (4.6 GB of weights streamed per step)",
+                           "parallelism": "replicas x%d" % world, "graph_compute_calls_per_token": graphs_per_tok},
                 "clocks": clocks,
-                "e2e": {"value": e2e_val, "unit": "tokens/s", "h2d_bytes_per_step": N_EMBD * 4, "d2h_bytes_per_step": N_VOCAB * 4},
-                "gpu_launches": launches_per_step * args.steps,
-                "roofline": {"bound": "hbm", "kernel": "mmvq_kernel<Q4_K>", "achieved": ach, "peak": peak, "unit": "GB/s",
-                             "frac": ach / peak, "traffic": traffic, "peak_source": how,
-                             "launches": n_q4, "algorithmic_bytes_per_step": q4_bytes,
-                             "whole_step_GBps": plan_bytes(plan) / (ms_step * 1e-3) / 1e9}}
+                "e2e": {"value": e2e_val, "unit": "tokens/s", "h2d_bytes_per_step": 12 + n_kv * 64 * 4, "d2h_bytes_per_step": N_VOCAB * 4},
+                "gpu_launches": int(round(launches_per_step * args.steps))}
+        if not args.no_roofline:
+            try:
+                k = kernel_roofline(max(20, min(args.steps, 200)), args.warmup, local)
+                peak, how = measured_peak()
+                traffic = None
+                tpath = os.path.join(ROOT, "profiles", "r01_mmvq_q4k_traffic.json")
+                if os.path.exists(tpath):
+                    traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+                line["roofline"] = {"bound": "hbm", "kernel": "mmvq_kernel<Q4_K> (192 launches per token: wq wk wv wo gate up down)",
+                                    "achieved": k["gbps"], "peak": peak, "unit": "GB/s", "frac": k["gbps"] / peak, "traffic": traffic,
+                                    "peak_source": how, "launches": k["launches"], "us_per_launch": k["us_per_launch"],
+                                    "algorithmic_bytes_per_launch": k["bytes"] / k["launches"],
+                                    "whole_step_GBps": plan_bytes(step_plan()) / (ms_step * 1e-3) / 1e9}
+            except Exception as e:  # noqa: BLE001
+                line["roofline"] = {"error": str(e)[:200]}
         if not args.no_cpu_baseline and world == 1:
-            line["cpu_baseline"] = cpu_port_baseline()
+            threads = os.cpu_count() or 1
+            try:
+                v = cpu_reference_run(model, 16, threads)
+                line["cpu_baseline"] = {"value": v, "unit": "tokens/s", "cores": threads, "kind": "reference",
+                                        "sample": "reference llama-bench -ngl 0 -p 0 -n 16 -r 1 -t %d on the same GGUF" % threads}
+            except Exception as e:  # noqa: BLE001
+                line["cpu_baseline"] = {"error": str(e)[:200]}
         print(json.dumps(line), flush=True)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 

@@ -206,7 +206,9 @@ __global__ void __launch_bounds__(128) fattn_combine_kernel(const float * __rest
 
 static int fa_splits(int64_t rows_heads, int ntiles) {
     // enough CTAs for ~2 per SM, at least 4 tiles (one per warp) per CTA
-    int ns = (int)std::min<int64_t>(std::max<int64_t>(1, (2 * 148 + rows_heads - 1) / rows_heads), std::max(1, ntiles / 4));
+    // short contexts: one CTA per (row, head) walks all tiles (no combine launch); long: split for occupancy
+    if (ntiles <= 32) return 1;
+    int ns = (int)std::min<int64_t>(std::max<int64_t>(1, (2 * 148 + rows_heads - 1) / rows_heads), std::max(1, ntiles / 8));
     return std::max(1, std::min(ns, 64));
 }
 

@@ -118,7 +118,37 @@ __global__ void __launch_bounds__(256) scale_kernel(const float * __restrict__ x
 }
 
 // ---- rms_norm (reference ggml-cpu/ops.cpp:3285-3312): one CTA per row ----
-__global__ void __launch_bounds__(256) rms_norm_kernel(const tens src, const tens dst, float eps) {
+// The row is read once with independent 128-bit loads (all in flight together: a decode step has a
+// single row, so the kernel is pure load latency) and kept in registers for the scaling pass.
+template <int VPT>      // float4 per thread
+__global__ void __launch_bounds__(1024) rms_norm_kernel(const tens src, const tens dst, float eps) {
+    pdl_enter();
+    const int64_t r = blockIdx.x;
+    const int64_t i1 = r % src.ne[1], i2 = (r / src.ne[1]) % src.ne[2], i3 = r / (src.ne[1] * src.ne[2]);
+    const float4 * x = (const float4 *)(src.d + i1 * src.nb[1] + i2 * src.nb[2] + i3 * src.nb[3]);
+    float4 * y = (float4 *)(dst.d + i1 * dst.nb[1] + i2 * dst.nb[2] + i3 * dst.nb[3]);
+    const int n4 = (int)(src.ne[0] >> 2);
+    float4 v[VPT];
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) { const int i = threadIdx.x + k * blockDim.x; v[k] = i < n4 ? x[i] : make_float4(0.f, 0.f, 0.f, 0.f); }
+    float s = 0.0f;
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) s += v[k].x * v[k].x + v[k].y * v[k].y + v[k].z * v[k].z + v[k].w * v[k].w;
+    s = warp_sum(s);
+    __shared__ float part[32];
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
+    __syncthreads();
+    float tot = 0.0f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += part[w];
+    const float scale = rsqrtf(tot / (float)src.ne[0] + eps);
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+        const int i = threadIdx.x + k * blockDim.x;
+        if (i < n4) y[i] = make_float4(v[k].x * scale, v[k].y * scale, v[k].z * scale, v[k].w * scale);
+    }
+}
+// generic fallback (unaligned rows or very long rows)
+__global__ void __launch_bounds__(256) rms_norm_generic_kernel(const tens src, const tens dst, float eps) {
     pdl_enter();
     const int64_t r = blockIdx.x;
     const int64_t i1 = r % src.ne[1], i2 = (r / src.ne[1]) % src.ne[2], i3 = r / (src.ne[1] * src.ne[2]);
@@ -292,8 +322,24 @@ extern "C" int b200_op_rms_norm(const b200_tensor * src, const b200_tensor * dst
     if (src->type != T_F32 || dst->type != T_F32 || !same_shape(src, dst) || src->nb[0] != 4 || dst->nb[0] != 4) return -1;
     const int64_t r = nrows(src);
     if (r == 0 || src->ne[0] == 0) return 0;
-    const int threads = src->ne[0] >= 1024 ? 256 : (src->ne[0] >= 256 ? 128 : 32);
-    return launch(rms_norm_kernel, (unsigned)r, threads, 0, (cudaStream_t)stream, mk(src), mk(dst), eps);
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool al = src->ne[0] % 4 == 0 && ((((uintptr_t)src->data | (uintptr_t)dst->data | src->nb[1] | src->nb[2] | src->nb[3] |
+                                              dst->nb[1] | dst->nb[2] | dst->nb[3]) & 15) == 0);
+    const int64_t n4 = src->ne[0] / 4;
+    if (al && n4 <= 4096) {
+        // few rows (decode): many threads, one float4 each; many rows (prefill): 256 threads, up to 4 float4 each
+        if (r <= 8 || n4 > 1024) {
+            const int threads = (int)std::min<int64_t>(1024, (n4 + 31) / 32 * 32);
+            if (n4 <= threads) return launch(rms_norm_kernel<1>, (unsigned)r, threads, 0, st, mk(src), mk(dst), eps);
+            if (n4 <= 2 * threads) return launch(rms_norm_kernel<2>, (unsigned)r, threads, 0, st, mk(src), mk(dst), eps);
+            return launch(rms_norm_kernel<4>, (unsigned)r, threads, 0, st, mk(src), mk(dst), eps);
+        }
+        const int threads = (int)std::min<int64_t>(256, (n4 + 31) / 32 * 32);
+        if (n4 <= threads) return launch(rms_norm_kernel<1>, (unsigned)r, threads, 0, st, mk(src), mk(dst), eps);
+        if (n4 <= 2 * threads) return launch(rms_norm_kernel<2>, (unsigned)r, threads, 0, st, mk(src), mk(dst), eps);
+        return launch(rms_norm_kernel<4>, (unsigned)r, threads, 0, st, mk(src), mk(dst), eps);
+    }
+    return launch(rms_norm_generic_kernel, (unsigned)r, 256, 0, st, mk(src), mk(dst), eps);
 }
 
 extern "C" int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, const b200_tensor * ffac, const b200_tensor * dst,
