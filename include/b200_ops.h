@@ -161,6 +161,16 @@ int b200_op_mul_mat(const b200_tensor * src0, const b200_tensor * src1, const b2
                     void * scratch, int64_t scratch_bytes, void * stream);
 int64_t b200_mul_mat_scratch_bytes(const b200_tensor * src0, const b200_tensor * src1);
 int b200_mul_mat_supported(const b200_tensor * src0, const b200_tensor * src1);
+/* MMQ: dst[m*ds + n] = sum_k dequant(W[n][k]) * X[m*xs + k] for M > 8 tokens on the tcgen05 tensor cores (weights dequantised
+ * to bf16 in shared memory, activations converted to bf16 once into `scratch`, f32 accumulation in TMEM).
+ * Replaces ggml_cuda_mul_mat_q / mul_mat_q<type> (ggml/src/ggml-cuda/mmq.cu:1-140, mmq.cuh:3390-3760) for the dense
+ * (non-MoE) case.  Requires K % 256 == 0, W and nb1 16-byte aligned (b200_mul_mat_q_supported); scratch of
+ * b200_mul_mat_q_scratch_bytes(K, M) bytes.  Weight rows may be read up to 30 bytes past a row's end (never past
+ * row N-1's stride), which ggml buffers pad for (get_alloc_size). */
+int b200_mul_mat_q(int type, const void * W, int64_t nb1, const float * X, int64_t xs, float * dst, int64_t ds,
+                   int N, int K, int M, void * scratch, int64_t scratch_bytes, void * stream);
+int64_t b200_mul_mat_q_scratch_bytes(int K, int M);
+int b200_mul_mat_q_supported(int type, const void * W, int64_t nb1, int K);
 /* MUL_MAT_ID: dst[:, e, t] = as[:, :, ids[e, t]] x b[:, e % ne11, t]; ids i32 read on the device (no host sync).
  * Replaces ggml_cuda_mul_mat_id (ggml-cuda/ggml-cuda.cu:2007-2148) and the MoE branch of mmq.cu:141-223. */
 int b200_op_mul_mat_id(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * dst,

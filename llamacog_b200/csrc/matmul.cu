@@ -68,6 +68,12 @@ static int mm_dense_launch(const mm_params & p, int nz, cudaStream_t st) {
 static bool is_quant(int t) { return t == T_Q4_0 || t == T_Q8_0 || t == T_Q4_K || t == T_Q5_K || t == T_Q6_K; }
 static bool is_dense(int t) { return t == T_F32 || t == T_F16 || t == T_BF16; }
 
+static int mmq_min_m() { static const int v = [] { const char * e = getenv("B200_MMQ_MIN_M"); return e ? atoi(e) : 9; }(); return v; }
+// the tensor-core path takes quantised weights x one plane of more than 8 token columns
+static bool use_mmq(const b200_tensor * a, const b200_tensor * b) {
+    return is_quant(a->type) && b->ne[2] * b->ne[3] == 1 && b->ne[1] >= mmq_min_m() && b->ne[1] > 8 &&
+           b200_mul_mat_q_supported(a->type, a->data, a->nb[1], (int)a->ne[0]);
+}
 static int xq_min_k() { static const int v = [] { const char * e = getenv("B200_XQ_MIN_K"); return e ? atoi(e) : 8192; }(); return v; }
 
 }  // namespace b200
@@ -89,6 +95,7 @@ extern "C" int b200_mul_mat_supported(const b200_tensor * a, const b200_tensor *
 }
 
 extern "C" int64_t b200_mul_mat_scratch_bytes(const b200_tensor * a, const b200_tensor * b) {
+    if (use_mmq(a, b)) return b200_mul_mat_q_scratch_bytes((int)a->ne[0], (int)b->ne[1]);
     if (!is_quant(a->type) || b->ne[2] * b->ne[3] != 1 || a->ne[0] < xq_min_k()) return 0;
     return b200_quantized_acts_bytes((int)a->ne[0], (int)b->ne[1]);
 }
@@ -99,6 +106,9 @@ extern "C" int b200_op_mul_mat(const b200_tensor * a, const b200_tensor * b, con
     const int K = (int)a->ne[0], N = (int)a->ne[1], M = (int)b->ne[1];
     if (dst->ne[0] != N || dst->ne[1] != M || dst->ne[2] != b->ne[2] || dst->ne[3] != b->ne[3]) return -1;
     if (K == 0 || N == 0 || M == 0 || b->ne[2] * b->ne[3] == 0) return 0;
+    if (use_mmq(a, b) && scratch && scratch_bytes >= b200_mul_mat_q_scratch_bytes(K, M))
+        return b200_mul_mat_q(a->type, a->data, a->nb[1], (const float *)b->data, b->nb[1] / 4, (float *)dst->data, dst->nb[1] / 4,
+                              N, K, M, scratch, scratch_bytes, stream);
     if (is_quant(a->type)) {
         b200_mmvq_args g = {};
         g.type = a->type; g.W = a->data; g.nb1 = a->nb[1];
@@ -109,7 +119,7 @@ extern "C" int b200_op_mul_mat(const b200_tensor * a, const b200_tensor * b, con
         g.w_sy = a->nb[2]; g.w_sz = a->nb[3]; g.w_div_y = (int)(b->ne[2] / a->ne[2]); g.w_div_z = (int)(b->ne[3] / a->ne[3]);
         g.x_sy = b->nb[2] / 4; g.x_sz = b->nb[3] / 4; g.d_sy = dst->nb[2] / 4; g.d_sz = dst->nb[3] / 4;
         g.pdl = -1;
-        const int64_t need = b200_mul_mat_scratch_bytes(a, b);
+        const int64_t need = use_mmq(a, b) ? 0 : b200_mul_mat_scratch_bytes(a, b);
         if (need > 0 && scratch && scratch_bytes >= need) {
             const int rc = b200_quantize_acts(g.X, g.xs, scratch, K, M, stream);
             if (rc) return rc;

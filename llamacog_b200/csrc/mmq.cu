@@ -1,0 +1,578 @@
+// mmq.cu -- batched quantized matmul for prefill (reference ggml-cuda/mmq.cu:1-366,
+// mmq.cuh tile loaders + mma.sync; reference dispatch ggml-cuda.cu:1936-2005) rebuilt for sm_100a:
+//
+//   dst[m][n] = sum_k dequant(W[n][k]) * X[m][k]          W: GGUF blocks, X: f32 activations, dst: f32
+//
+// One CTA owns a 128-weight-row x TN-token output tile whose f32 accumulator lives in TMEM.  Per 256-K
+// block:  warp 0 TMA-loads the raw GGUF bytes of the 128 rows (2-D tensor map over the weight bytes),
+// warp 3 TMA-loads the bf16 activation tiles (2-D tensor map, 128-byte swizzle), eight dequantiser warps
+// expand the blocks to bf16 straight into the 128B-swizzled K-major layout tcgen05 reads, and one thread
+// of warp 1 issues tcgen05.mma (kind::f16, bf16 x bf16 -> f32, M=128, N=TN, K=16).  Raw bytes are read
+// from HBM exactly once per tile row; dequantisation overlaps the tensor pipe through a 4-slot ring.
+// Activations are converted f32 -> bf16 once per mat-mul by a small pre-pass (the reference quantises
+// them to q8_1 there instead, ggml-cuda/quantize.cu).
+#include "common.cuh"
+#include "../../include/b200_ops.h"
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cstdlib>
+#include <cstring>
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------------
+// PTX wrappers: TMA tensor copies, tcgen05
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap * map, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 :: "r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap * map) {
+    asm volatile("prefetch.tensormap [%0];" :: "l"(map) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(dst_smem), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish() { asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]
+__device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                   "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr) : "memory");
+}
+// bounded mbarrier wait: a pipeline bug traps (launch failure) instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait_b(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    const long long t0 = clock64();
+    while (true) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (done) return;
+        if (clock64() - t0 > 4000000000ll) __trap();
+    }
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" :: "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint2 lds64(uint32_t saddr) {
+    uint2 v; asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(saddr)); return v;
+}
+__device__ __forceinline__ uint32_t fma_bf16x2(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d; asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
+}
+// {f, f} as packed bf16 (round to nearest even)
+__device__ __forceinline__ uint32_t pack_bf16_dup(float f) {
+    uint32_t d; asm("cvt.rn.bf16x2.f32 %0, %1, %1;" : "=r"(d) : "f"(f)); return d;
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    uint32_t d; asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo)); return d;
+}
+__device__ __forceinline__ float bf16lo_to_float(uint32_t packed) { return __uint_as_float(packed << 16); }
+
+// shared-memory matrix descriptor of a K-major bf16 tile stored with the 128-byte swizzle: rows of 64
+// elements (128 B), groups of 8 rows 1024 B apart
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+// instruction descriptor: D f32, A/B bf16, both K-major, M = 128, N = tn
+__device__ __forceinline__ uint32_t umma_idesc_bf16(int tn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(tn >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Dequantisers.  A dequantiser thread owns one weight row r of the tile and one half h of each 256-K
+// block (h = 0: K 0..127, h = 1: K 128..255), i.e. the two 64-K sub-chunks c = 2h, 2h+1.  For each it
+// writes the row's 8 16-byte chunks (8 bf16 each) of the A tile:  chunk u of row r lives at
+// r*128 + ((u ^ (r & 7)) << 4)  (the 128-byte swizzle tcgen05 and TMA use).
+//
+// Integer codes become bf16 without conversions: a byte 0x80|(q << s) under a 0x3F high byte is the
+// bf16 value 1 + q/2^(7-s), so  w = q*scale - offset  is one packed fma  x*S + B  with S = 2^(7-s)*scale
+// and B = -(S + offset); S is rounded to bf16 first and B is computed from the rounded S, so q = 0 maps
+// to -offset up to one bf16 rounding.  (Values follow dequantize_row_*, reference ggml-quants.c; the
+// result is rounded to bf16 -- the op's parity bar is NMSE <= 5e-4, tests/test-backend-ops.cpp.)
+// ------------------------------------------------------------------------------------------------
+#define PRMT_01 0x4140u   // {b0, 0x3F, b1, 0x3F}
+#define PRMT_23 0x4342u   // {b2, 0x3F, b3, 0x3F}
+
+// four code bytes (already shifted, 0x80 set) -> two packed bf16 pairs, scaled
+__device__ __forceinline__ void expand4(uint32_t codes, uint32_t s2, uint32_t b2, uint32_t & o01, uint32_t & o23) {
+    o01 = fma_bf16x2(__byte_perm(codes, 0x3F3F3F3Fu, PRMT_01), s2, b2);
+    o23 = fma_bf16x2(__byte_perm(codes, 0x3F3F3F3Fu, PRMT_23), s2, b2);
+}
+// scale pair from S (float): s2 = {S,S} bf16, b2 = {-(Sr*bm + off)} with Sr the rounded S
+__device__ __forceinline__ void make_sb(float S, float bm, float off, uint32_t & s2, uint32_t & b2) {
+    s2 = pack_bf16_dup(S);
+    b2 = pack_bf16_dup(-fmaf(bf16lo_to_float(s2), bm, off));
+}
+__device__ __forceinline__ float ubyte_f(uint32_t w, int i) { return (float)((w >> (8 * i)) & 0xFFu); }
+
+template <int TYPE> struct dq;
+
+// ---- Q4_K: d, dmin (f16) | scales[12] (6-bit sc/mn x 8) | qs[128]; sub-block j (32 elems): nibble (j&1) of qs[32*(j/2) + l]
+template <> struct dq<T_Q4_K> {
+    static constexpr int PITCH = 144;      // bytes of one row's block in the raw stage
+    static constexpr int STEP16 = 72;      // block stride in 16-bit elements (tensor-map coordinate)
+    uint32_t s2[4], b2[4];
+    __device__ __forceinline__ void prep(uint32_t row, int h) {
+        const int4 hd = lds128(row);
+        const float d = half_bits_to_float(hd.x & 0xFFFF), dmin = half_bits_to_float((uint32_t)hd.x >> 16);
+        uint32_t SC, MN;
+        if (h == 0) { SC = hd.y & 0x3F3F3F3Fu; MN = hd.z & 0x3F3F3F3Fu; }
+        else { SC = (hd.w & 0x0F0F0F0Fu) | (((uint32_t)hd.y >> 2) & 0x30303030u); MN = (((uint32_t)hd.w >> 4) & 0x0F0F0F0Fu) | (((uint32_t)hd.z >> 2) & 0x30303030u); }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) make_sb(16.0f * d * ubyte_f(SC, j), 1.0f, dmin * ubyte_f(MN, j), s2[j], b2[j]);
+    }
+    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t dst, int rx) const {
+        const uint32_t qs = row + 16 + 32 * (2 * h + t);
+        const int4 q0 = lds128(qs), q1 = lds128(qs + 16);
+        const uint32_t w[8] = {(uint32_t)q0.x, (uint32_t)q0.y, (uint32_t)q0.z, (uint32_t)q0.w, (uint32_t)q1.x, (uint32_t)q1.y, (uint32_t)q1.z, (uint32_t)q1.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {      // low nibbles -> chunks 0..3 (sub-block 2t), high -> 4..7 (sub-block 2t+1)
+            uint32_t o[4], p[4];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const uint32_t x = w[2 * u + i];
+                expand4(((x << 3) & 0x78787878u) | 0x80808080u, s2[2 * t], b2[2 * t], o[2 * i], o[2 * i + 1]);
+                expand4(((x >> 1) & 0x78787878u) | 0x80808080u, s2[2 * t + 1], b2[2 * t + 1], p[2 * i], p[2 * i + 1]);
+            }
+            sts128(dst + ((u ^ rx) << 4), o[0], o[1], o[2], o[3]);
+            sts128(dst + (((u + 4) ^ rx) << 4), p[0], p[1], p[2], p[3]);
+        }
+    }
+};
+
+// ---- Q5_K: d, dmin | scales[12] | qh[32] | qs[128]; as Q4_K plus bit j of qh[l] as the code's fifth bit
+template <> struct dq<T_Q5_K> {
+    static constexpr int PITCH = 176;
+    static constexpr int STEP16 = 88;
+    uint32_t s2[4], b2[4], qh[8];
+    __device__ __forceinline__ void prep(uint32_t row, int h) {
+        const int4 hd = lds128(row);
+        const float d = half_bits_to_float(hd.x & 0xFFFF), dmin = half_bits_to_float((uint32_t)hd.x >> 16);
+        uint32_t SC, MN;
+        if (h == 0) { SC = hd.y & 0x3F3F3F3Fu; MN = hd.z & 0x3F3F3F3Fu; }
+        else { SC = (hd.w & 0x0F0F0F0Fu) | (((uint32_t)hd.y >> 2) & 0x30303030u); MN = (((uint32_t)hd.w >> 4) & 0x0F0F0F0Fu) | (((uint32_t)hd.z >> 2) & 0x30303030u); }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) make_sb(32.0f * d * ubyte_f(SC, j), 1.0f, dmin * ubyte_f(MN, j), s2[j], b2[j]);
+        const int4 a = lds128(row + 16), b = lds128(row + 32);
+        const int sh = 4 * h;              // this half's four sub-block bits move to bits 0..3
+        qh[0] = (uint32_t)a.x >> sh; qh[1] = (uint32_t)a.y >> sh; qh[2] = (uint32_t)a.z >> sh; qh[3] = (uint32_t)a.w >> sh;
+        qh[4] = (uint32_t)b.x >> sh; qh[5] = (uint32_t)b.y >> sh; qh[6] = (uint32_t)b.z >> sh; qh[7] = (uint32_t)b.w >> sh;
+    }
+    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t dst, int rx) const {
+        const uint32_t qs = row + 48 + 32 * (2 * h + t);
+        const int4 q0 = lds128(qs), q1 = lds128(qs + 16);
+        const uint32_t w[8] = {(uint32_t)q0.x, (uint32_t)q0.y, (uint32_t)q0.z, (uint32_t)q0.w, (uint32_t)q1.x, (uint32_t)q1.y, (uint32_t)q1.z, (uint32_t)q1.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            uint32_t o[4], p[4];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const uint32_t x = w[2 * u + i], hb = qh[2 * u + i];
+                // code byte = 0x80 | q5 << 2 : nibble at bits 2..5, fifth bit at bit 6
+                const uint32_t lo = ((x << 2) & 0x3C3C3C3Cu) | 0x80808080u | ((hb << (6 - 2 * t)) & 0x40404040u);
+                const uint32_t hi = ((x >> 2) & 0x3C3C3C3Cu) | 0x80808080u | ((hb << (5 - 2 * t)) & 0x40404040u);
+                expand4(lo, s2[2 * t], b2[2 * t], o[2 * i], o[2 * i + 1]);
+                expand4(hi, s2[2 * t + 1], b2[2 * t + 1], p[2 * i], p[2 * i + 1]);
+            }
+            sts128(dst + ((u ^ rx) << 4), o[0], o[1], o[2], o[3]);
+            sts128(dst + (((u + 4) ^ rx) << 4), p[0], p[1], p[2], p[3]);
+        }
+    }
+};
+
+// ---- Q6_K: ql[128] | qh[64] | scales int8[16] | d (f16).  Element e: half hh = e/128, g = (e%128)/32, l = e%32:
+//      nibble (g/2) of ql[64hh + 32(g&1) + l], bits 2g..2g+1 of qh[32hh + l]; value (q6 - 32) * d * scales[e/16]
+template <> struct dq<T_Q6_K> {
+    static constexpr int PITCH = 240;      // 210 bytes + 30 of the next block (ignored); keeps 16-byte loads conflict-free
+    static constexpr int STEP16 = 105;
+    uint32_t s2[8], b2[8];                 // 8 x 16-element scale groups of this half
+    __device__ __forceinline__ void prep(uint32_t row, int h) {
+        const float d = half_bits_to_float(lds16(row + 208));
+        const uint2 sc = lds64(row + 192 + 8 * h);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int s = (int)(int8_t)(((j < 4 ? sc.x : sc.y) >> (8 * (j & 3))) & 0xFF);
+            make_sb(64.0f * d * (float)s, 1.5f, 0.0f, s2[j], b2[j]);      // (q6 - 32) * ds = (1 + q6/64) * 64ds - 1.5 * 64ds
+        }
+    }
+    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t dst, int rx) const {
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {      // 32 elements each; sub-chunk c = 2h + t holds groups 2t, 2t+1 of half h
+            const uint32_t ql = row + 64 * h + 32 * g, qhp = row + 128 + 32 * h;
+            const int4 q0 = lds128(ql), q1 = lds128(ql + 16), h0 = lds128(qhp), h1 = lds128(qhp + 16);
+            const uint32_t w[8] = {(uint32_t)q0.x, (uint32_t)q0.y, (uint32_t)q0.z, (uint32_t)q0.w, (uint32_t)q1.x, (uint32_t)q1.y, (uint32_t)q1.z, (uint32_t)q1.w};
+            const uint32_t hb[8] = {(uint32_t)h0.x, (uint32_t)h0.y, (uint32_t)h0.z, (uint32_t)h0.w, (uint32_t)h1.x, (uint32_t)h1.y, (uint32_t)h1.z, (uint32_t)h1.w};
+            const int gg = 2 * t + g;      // bit pair 2gg of qh
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                uint32_t o[4];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const uint32_t x = w[2 * u + i], y = hb[2 * u + i];
+                    // code byte = 0x80 | q6 << 1 : nibble at bits 1..4, high pair at bits 5..6
+                    const uint32_t nib = t == 0 ? (x << 1) : (x >> 3);
+                    const uint32_t hi2 = 2 * gg <= 5 ? (y << (5 - 2 * gg)) : (y >> (2 * gg - 5));
+                    const uint32_t code = (nib & 0x1E1E1E1Eu) | 0x80808080u | (hi2 & 0x60606060u);
+                    const int si = 4 * t + 2 * g + (u >> 1);
+                    expand4(code, s2[si], b2[si], o[2 * i], o[2 * i + 1]);
+                }
+                sts128(dst + (((4 * g + u) ^ rx) << 4), o[0], o[1], o[2], o[3]);
+            }
+        }
+    }
+};
+
+// ---- Q4_0: 8 blocks of {d (f16), qs[16]} per 256 K; element j of a block: nibble (j/16) of qs[j%16]; (q - 8) * d
+template <> struct dq<T_Q4_0> {
+    static constexpr int PITCH = 144;
+    static constexpr int STEP16 = 72;
+    __device__ __forceinline__ void prep(uint32_t, int) {}
+    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t dst, int rx) const {
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            const uint32_t blk = row + 18 * (2 * (2 * h + t) + b);
+            uint32_t s2, b2;
+            make_sb(16.0f * half_bits_to_float(lds16(blk)), 1.5f, 0.0f, s2, b2);      // (q - 8) d = (1 + q/16) 16d - 1.5 * 16d
+            int w[4]; lds_words_a2<4>(blk + 2, w);
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                uint32_t o[4], p[4];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const uint32_t x = (uint32_t)w[2 * u + i];
+                    expand4(((x << 3) & 0x78787878u) | 0x80808080u, s2, b2, o[2 * i], o[2 * i + 1]);
+                    expand4(((x >> 1) & 0x78787878u) | 0x80808080u, s2, b2, p[2 * i], p[2 * i + 1]);
+                }
+                sts128(dst + (((4 * b + u) ^ rx) << 4), o[0], o[1], o[2], o[3]);
+                sts128(dst + (((4 * b + u + 2) ^ rx) << 4), p[0], p[1], p[2], p[3]);
+            }
+        }
+    }
+};
+
+// ---- Q8_0: 8 blocks of {d (f16), qs int8[32]} per 256 K; q * d.  Codes go through f16 (1024 + (q ^ 0x80) is
+//      exact, minus 1152 gives q, times the f16 scale) and are then rounded to bf16.
+template <> struct dq<T_Q8_0> {
+    static constexpr int PITCH = 272;
+    static constexpr int STEP16 = 136;
+    __device__ __forceinline__ void prep(uint32_t, int) {}
+    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t dst, int rx) const {
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            const uint32_t blk = row + 34 * (2 * (2 * h + t) + b);
+            const __half dh = __ushort_as_half((unsigned short)lds16(blk));
+            const __half2 d2 = __half2half2(dh), off = __float2half2_rn(1152.0f);
+            int w[8]; lds_words_a2<8>(blk + 2, w);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                uint32_t o[4];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const uint32_t x = (uint32_t)w[2 * u + i] ^ 0x80808080u;
+                    const uint32_t a = __byte_perm(x, 0x64646464u, PRMT_01), c = __byte_perm(x, 0x64646464u, PRMT_23);
+                    const float2 fa = __half22float2(__hmul2(__hsub2(*reinterpret_cast<const __half2 *>(&a), off), d2));
+                    const float2 fc = __half22float2(__hmul2(__hsub2(*reinterpret_cast<const __half2 *>(&c), off), d2));
+                    o[2 * i] = pack_bf16(fa.x, fa.y); o[2 * i + 1] = pack_bf16(fc.x, fc.y);
+                }
+                sts128(dst + (((4 * b + u) ^ rx) << 4), o[0], o[1], o[2], o[3]);
+            }
+        }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// The kernel.  Step i = 4*kb + j covers the 64-K sub-chunk c = {0,2,1,3}[j] of block kb, so that the two
+// dequantiser groups (h = 0: sub-chunks 0,1; h = 1: sub-chunks 2,3) alternate: A slot = j, group = j & 1.
+// ------------------------------------------------------------------------------------------------
+struct mmq_params {
+    float * dst; int64_t ds;     // dst[m*ds + n]
+    int N, M, K;
+    int tn;                      // tokens per tile: 32, 64, 128 or 256
+    int nb;                      // depth of the activation-tile ring (<= 4)
+};
+
+constexpr int MMQ_THREADS = 384;
+constexpr int A_SLOT = 128 * 128;            // 128 rows x 64 bf16
+constexpr int A_SLOTS = 4;
+constexpr int NB_MAX = 4;
+
+template <int TYPE>
+__global__ void __launch_bounds__(MMQ_THREADS, 1)
+mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUtensorMap xmap, const mmq_params p) {
+    using DQ = dq<TYPE>;
+    constexpr int RAW = 128 * DQ::PITCH;
+    extern __shared__ uint8_t smem_dyn[];
+    const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
+    const int tn = p.tn, nb = p.nb;
+    const uint32_t b_slot = (uint32_t)tn * 128u;
+    const uint32_t sA = base, sB = sA + A_SLOTS * A_SLOT, sR = sB + (uint32_t)nb * b_slot, sBar = sR + 2 * RAW;
+    const uint32_t raw_full = sBar, raw_empty = sBar + 16, a_full = sBar + 32, a_empty = sBar + 64,
+                   b_full = sBar + 96, b_empty = sBar + 128, tmem_full = sBar + 160, tmem_slot = sBar + 168;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * tn, n0 = blockIdx.y * 128;
+    const int nkb = p.K >> 8, nsteps = nkb * 4;
+    const uint32_t ncols = tn < 32 ? 32u : (uint32_t)tn;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) { mbar_init(raw_full + 8 * i, 1); mbar_init(raw_empty + 8 * i, 8); }
+        for (int i = 0; i < A_SLOTS; ++i) { mbar_init(a_full + 8 * i, 4); mbar_init(a_empty + 8 * i, 1); }
+        for (int i = 0; i < NB_MAX; ++i) { mbar_init(b_full + 8 * i, 1); mbar_init(b_empty + 8 * i, 1); }
+        mbar_init(tmem_full, 1);
+        mbar_fence_init();
+        tma_prefetch_desc(&wmap); tma_prefetch_desc(&xmap);
+    }
+    if (warp == 2) { tmem_alloc(tmem_slot, ncols); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = lds32(tmem_slot);
+    pdl_trigger();
+    pdl_wait();                                  // the bf16 activations come from the preceding kernel
+
+    if (warp == 0) {
+        if (lane == 0) {                         // raw weight blocks: one 128-row box per 256-K block
+            for (int kb = 0; kb < nkb; ++kb) {
+                const int s = kb & 1;
+                mbar_wait_b(raw_empty + 8 * s, ((kb >> 1) & 1) ^ 1);
+                mbar_expect_tx(raw_full + 8 * s, RAW);
+                tma_load_2d(sR + s * RAW, &wmap, kb * DQ::STEP16, n0, raw_full + 8 * s);
+            }
+        }
+    } else if (warp == 3) {
+        if (lane == 0) {                         // bf16 activation tiles [tn][64], 128-byte swizzle
+            for (int i = 0; i < nsteps; ++i) {
+                const int j = i & 3, c = ((j & 1) << 1) | (j >> 1), s = i % nb;
+                mbar_wait_b(b_empty + 8 * s, ((i / nb) & 1) ^ 1);
+                mbar_expect_tx(b_full + 8 * s, b_slot);
+                tma_load_2d(sB + s * b_slot, &xmap, (i >> 2) * 256 + c * 64, m0, b_full + 8 * s);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {                         // tensor-core issue
+            const uint32_t idesc = umma_idesc_bf16(tn);
+            for (int i = 0; i < nsteps; ++i) {
+                const int sa = i & 3, sb = i % nb;
+                mbar_wait_b(a_full + 8 * sa, (i >> 2) & 1);
+                mbar_wait_b(b_full + 8 * sb, (i / nb) & 1);
+                tc_fence_after();
+                const uint64_t ad = umma_desc_sw128(sA + sa * A_SLOT), bd = umma_desc_sw128(sB + sb * b_slot);
+#pragma unroll
+                for (int k = 0; k < 4; ++k)      // K = 16 per instruction: 32 bytes along the swizzled row
+                    tc_mma_f16(tmem_base, ad + 2 * k, bd + 2 * k, idesc, (uint32_t)((i | k) != 0));
+                tc_commit(a_empty + 8 * sa);
+                tc_commit(b_empty + 8 * sb);
+            }
+            tc_commit(tmem_full);
+        }
+    } else if (warp >= 4) {
+        const int dw = warp - 4, h = dw >> 2, r = (dw & 3) * 32 + lane, rx = r & 7;
+        DQ q;
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb & 1;
+            mbar_wait_b(raw_full + 8 * s, (kb >> 1) & 1);
+            const uint32_t row = sR + s * RAW + r * DQ::PITCH;
+            q.prep(row, h);
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                const int slot = 2 * t + h;
+                mbar_wait_b(a_empty + 8 * slot, (kb & 1) ^ 1);
+                q.emit(row, h, t, sA + slot * A_SLOT + r * 128, rx);
+                fence_proxy_async();             // generic-proxy stores -> visible to the tensor core's async proxy
+                __syncwarp();
+                if (lane == 0) mbar_arrive(a_full + 8 * slot);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(raw_empty + 8 * s);
+        }
+        // epilogue: TMEM lane = weight row (this warp's quarter), column = token; group h takes every other 32 columns
+        mbar_wait_b(tmem_full, 0);
+        tc_fence_after();
+        const int n = n0 + r;
+        for (int c0 = h * 32; c0 < tn; c0 += 64) {
+            uint32_t v[32];
+            tmem_ld32(tmem_base + ((uint32_t)((dw & 3) * 32) << 16) + (uint32_t)c0, v);
+            tmem_ld_wait();
+            if (n < p.N) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int m = m0 + c0 + j;
+                    if (m < p.M) p.dst[(int64_t)m * p.ds + n] = __uint_as_float(v[j]);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) { tc_fence_after(); tmem_dealloc(tmem_base, ncols); }
+}
+
+// ---- activations f32 -> bf16 [M][K] (contiguous) ----
+__global__ void __launch_bounds__(256) x_to_bf16_kernel(const float * __restrict__ X, int64_t xs, uint32_t * __restrict__ out, int K, int M, int vec) {
+    pdl_trigger(); pdl_wait();
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;      // one group of 8 elements
+    const int kg = K >> 3;
+    if (i >= (int64_t)M * kg) return;
+    const int m = (int)(i / kg), k = (int)(i % kg) * 8;
+    const float * src = X + (int64_t)m * xs + k;
+    float f[8];
+    if (vec) {
+        const float4 a = *reinterpret_cast<const float4 *>(src), b = *reinterpret_cast<const float4 *>(src + 4);
+        f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = src[j];
+    }
+    uint4 o; o.x = pack_bf16(f[0], f[1]); o.y = pack_bf16(f[2], f[3]); o.z = pack_bf16(f[4], f[5]); o.w = pack_bf16(f[6], f[7]);
+    *reinterpret_cast<uint4 *>(out + ((int64_t)m * K + k) / 2) = o;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                    const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static encode_tiled_fn encode_tiled() {
+    static encode_tiled_fn fn = [] {
+        void * p = nullptr; cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+        return (encode_tiled_fn)p;
+    }();
+    return fn;
+}
+
+static int env_int(const char * name, int def) { const char * e = getenv(name); return e ? atoi(e) : def; }
+
+template <int TYPE> static int pitch_of() { return dq<TYPE>::PITCH; }
+static int raw_pitch(int type) {
+    switch (type) { case T_Q4_0: return pitch_of<T_Q4_0>(); case T_Q8_0: return pitch_of<T_Q8_0>(); case T_Q4_K: return pitch_of<T_Q4_K>();
+                    case T_Q5_K: return pitch_of<T_Q5_K>(); case T_Q6_K: return pitch_of<T_Q6_K>(); }
+    return 0;
+}
+static size_t mmq_smem(int type, int tn, int nb) { return 1024 + (size_t)A_SLOTS * A_SLOT + (size_t)nb * tn * 128 + 2 * 128 * (size_t)raw_pitch(type) + 256; }
+
+// tokens per tile: fill the 148 SMs first, then prefer the wider tile (weights are dequantised once per tile)
+static int choose_tn(int N, int M) {
+    const int forced = env_int("B200_MMQ_TN", 0);
+    if (forced == 32 || forced == 64 || forced == 128 || forced == 256) return forced;
+    if (M <= 32) return 32;
+    if (M <= 64) return 64;
+    if (M <= 128) return 128;
+    const int rows = (N + 127) / 128;
+    double best = 1e30; int best_tn = 128;
+    for (int tn : {256, 128}) {
+        const int tiles = rows * ((M + tn - 1) / tn);
+        const double cost = (double)((tiles + 147) / 148) * (tn == 256 ? 2.0 : 1.25);      // per-tile time: tensor pipe, or dequantiser for narrow tiles
+        if (cost < best) { best = cost; best_tn = tn; }
+    }
+    return best_tn;
+}
+
+template <int TYPE>
+static int mmq_launch(const CUtensorMap & wmap, const CUtensorMap & xmap, const mmq_params & p, size_t smem, cudaStream_t st) {
+    static size_t configured = 0;
+    if (smem > configured) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(mmq_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((p.M + p.tn - 1) / p.tn, (p.N + 127) / 128, 1); lc.blockDim = dim3(MMQ_THREADS); lc.dynamicSmemBytes = smem; lc.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+    B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, mmq_kernel<TYPE>, wmap, xmap, p));
+    ++g_launches;
+    return 0;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_mul_mat_q_supported(int type, const void * W, int64_t nb1, int K) {
+    if (!raw_pitch(type) || K <= 0 || K % 256) return 0;
+    if (((uintptr_t)W & 15) || (nb1 & 15)) return 0;              // TMA: 16-byte aligned base and row stride
+    if (nb1 < (int64_t)(K / block_elems(type)) * block_bytes(type)) return 0;
+    return encode_tiled() != nullptr;
+}
+
+extern "C" int64_t b200_mul_mat_q_scratch_bytes(int K, int M) { return (int64_t)K * M * 2 + 256; }
+
+extern "C" int b200_mul_mat_q(int type, const void * W, int64_t nb1, const float * X, int64_t xs, float * dst, int64_t ds,
+                              int N, int K, int M, void * scratch, int64_t scratch_bytes, void * stream) {
+    if (!b200_mul_mat_q_supported(type, W, nb1, K) || N <= 0 || M <= 0) return -1;
+    if (!scratch || scratch_bytes < b200_mul_mat_q_scratch_bytes(K, M)) return -2;
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t * xb = (uint8_t *)(((uintptr_t)scratch + 127) & ~(uintptr_t)127);
+
+    const int vec = (((uintptr_t)X & 15) == 0 && (xs & 3) == 0) ? 1 : 0;
+    {
+        const int64_t groups = (int64_t)M * (K / 8);
+        cudaLaunchConfig_t lc = {};
+        lc.gridDim = dim3((unsigned)((groups + 255) / 256)); lc.blockDim = dim3(256); lc.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+        B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, x_to_bf16_kernel, X, xs, (uint32_t *)xb, K, M, vec));
+        ++g_launches;
+    }
+
+    mmq_params p = {};
+    p.dst = dst; p.ds = ds; p.N = N; p.M = M; p.K = K;
+    p.tn = choose_tn(N, M);
+    p.nb = NB_MAX;
+    while (p.nb > 2 && mmq_smem(type, p.tn, p.nb) > 232448) --p.nb;
+    if (mmq_smem(type, p.tn, p.nb) > 232448) return -3;
+    const size_t smem = mmq_smem(type, p.tn, p.nb);
+
+    CUtensorMap wmap, xmap;
+    {   // weights as a [N][nb1/2] array of 16-bit words; box = one 256-K block (padded to the raw pitch) x 128 rows
+        const cuuint64_t dims[2] = {(cuuint64_t)((int64_t)(K / block_elems(type)) * block_bytes(type) / 2), (cuuint64_t)N};
+        const cuuint64_t strides[1] = {(cuuint64_t)nb1};
+        const cuuint32_t box[2] = {(cuuint32_t)(raw_pitch(type) / 2), 128};
+        const cuuint32_t es[2] = {1, 1};
+        if (encode_tiled()(&wmap, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void *>(W), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return -4;
+    }
+    {   // activations bf16 [M][K]; box = 64 K x tn tokens, 128-byte swizzle
+        const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)M};
+        const cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+        const cuuint32_t box[2] = {64, (cuuint32_t)p.tn};
+        const cuuint32_t es[2] = {1, 1};
+        if (encode_tiled()(&xmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, xb, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return -5;
+    }
+    switch (type) {
+        case T_Q4_0: return mmq_launch<T_Q4_0>(wmap, xmap, p, smem, st);
+        case T_Q8_0: return mmq_launch<T_Q8_0>(wmap, xmap, p, smem, st);
+        case T_Q4_K: return mmq_launch<T_Q4_K>(wmap, xmap, p, smem, st);
+        case T_Q5_K: return mmq_launch<T_Q5_K>(wmap, xmap, p, smem, st);
+        case T_Q6_K: return mmq_launch<T_Q6_K>(wmap, xmap, p, smem, st);
+    }
+    return -1;
+}

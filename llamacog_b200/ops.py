@@ -39,6 +39,7 @@ def lib():
         for name in EXPORTS:
             getattr(_lib, name).restype = C.c_int
         _lib.b200_quantized_acts_bytes.restype = C.c_int64
+        _lib.b200_mul_mat_q_scratch_bytes.restype = C.c_int64
     return _lib
 
 
@@ -48,7 +49,8 @@ EXPORTS = ["b200_mul_mat_vec_q_ex", "b200_mul_mat_vec_q", "b200_mmvq_supported_t
            "b200_op_binary", "b200_op_unary", "b200_op_scale", "b200_op_rms_norm", "b200_op_rope", "b200_op_cpy", "b200_op_cpy_supported",
            "b200_op_get_rows", "b200_op_soft_max", "b200_op_argsort", "b200_op_sum_rows", "b200_op_flash_attn_ext",
            "b200_flash_attn_scratch_bytes", "b200_flash_attn_supported", "b200_op_mul_mat", "b200_mul_mat_scratch_bytes",
-           "b200_mul_mat_supported", "b200_op_mul_mat_id"]
+           "b200_mul_mat_supported", "b200_op_mul_mat_id", "b200_mul_mat_q", "b200_mul_mat_q_scratch_bytes",
+           "b200_mul_mat_q_supported"]
 
 
 def _stream():
@@ -88,6 +90,24 @@ def mul_mat_vec_q(t, W, X, N, K, nb1=None, dbg=False, pdl=-1, Xq=None):
                  Xq=Xq.data_ptr() if Xq is not None else None)
     _check(lib().b200_mul_mat_vec_q_ex(C.byref(a), _stream()), "b200_mul_mat_vec_q_ex")
     return (dst, sums) if dbg else dst
+
+
+def mul_mat_q(t, W, X, N, K, nb1=None):
+    """Batched quantised mat-mul on the tensor cores (GGML_OP_MUL_MAT, quantised src0, M > 8 tokens).
+    W: uint8 CUDA tensor of N quantised rows (16-byte aligned, a few bytes of slack after the last row);
+    X: float32 [M, K].  Returns dst [M, N]."""
+    assert W.is_cuda and X.is_cuda and X.dtype == torch.float32 and X.stride(-1) == 1
+    M = X.shape[0]
+    nb1 = nb1 or row_bytes(t, K)
+    if not lib().b200_mul_mat_q_supported(C.c_int(t), C.c_void_p(W.data_ptr()), C.c_int64(nb1), C.c_int(K)):
+        raise RuntimeError("b200_mul_mat_q: unsupported type/shape/alignment")
+    need = lib().b200_mul_mat_q_scratch_bytes(C.c_int(K), C.c_int(M))
+    scratch = torch.empty(need, dtype=torch.uint8, device=X.device)
+    dst = torch.empty((M, N), dtype=torch.float32, device=X.device)
+    _check(lib().b200_mul_mat_q(C.c_int(t), C.c_void_p(W.data_ptr()), C.c_int64(nb1), C.c_void_p(X.data_ptr()), C.c_int64(X.stride(0)),
+                                C.c_void_p(dst.data_ptr()), C.c_int64(N), C.c_int(N), C.c_int(K), C.c_int(M),
+                                C.c_void_p(scratch.data_ptr()), C.c_int64(need), _stream()), "b200_mul_mat_q")
+    return dst
 
 
 def quantize_q8_1(X, k_pad=None):

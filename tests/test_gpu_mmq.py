@@ -1,0 +1,117 @@
+"""GPU parity of the tensor-core prefill mat-mul (b200_mul_mat_q, through the C ABI) against the CPU oracle.
+
+Bar: NMSE <= 5e-4 against dequantise-then-f32 matmul, the reference's own bar for MUL_MAT
+(tests/test-backend-ops.cpp:1990-1992); the tests hold the kernel to 1e-4.  One-hot activations read the
+dequantised weights back through the MMA and are checked element-wise against dequantize_row_* (oracle)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle as O
+
+pytestmark = pytest.mark.gpu
+NAMES = list(O.QUANT_TYPES)
+NMSE_BAR = 1e-4
+
+
+def _ops():
+    from llamacog_b200 import ops
+    return ops
+
+
+def _dev(Wnp):
+    flat = np.ascontiguousarray(Wnp).reshape(-1)
+    buf = torch.zeros(flat.size + 256, dtype=torch.uint8, device="cuda")      # slack: the Q6_K box reads 30 bytes past a block
+    buf[:flat.size] = torch.from_numpy(flat).cuda()
+    return buf
+
+
+def _k_for(name, k):
+    return (k + 2047) // 2048 * 2048 if name == "q6_k" else k       # Q6_K rows must be a multiple of 16 bytes for TMA
+
+
+def _nmse(got, ref):
+    return float(((got.astype(np.float64) - ref) ** 2).sum() / (ref.astype(np.float64) ** 2).sum())
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("tn", [32, 64, 128, 256])
+def test_one_hot_reads_back_dequantised_weights(name, tn, monkeypatch):
+    t = O.QUANT_TYPES[name]
+    N, K = 130, _k_for(name, 512)
+    rng = np.random.default_rng(11)
+    W = O.random_quant_bytes(t, N, K, rng)
+    want = O.dequantize(t, W, N, K)
+    monkeypatch.setenv("B200_MMQ_TN", str(tn))
+    got = _ops().mul_mat_q(t, _dev(W), torch.eye(K, dtype=torch.float32, device="cuda"), N, K).cpu().numpy().T
+    tol = np.abs(want) * 2.0 ** -6 + np.abs(want).max() * 2.0 ** -7
+    assert (np.abs(got - want) <= tol).all(), float(np.abs(got - want).max())
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("N,K,M", [(16, 256, 9), (16, 256, 16), (16, 256, 32), (128, 512, 33), (257, 1024, 100), (129, 4096, 129),
+                                   (512, 2048, 300), (96, 14336, 64)])
+def test_shapes_vs_oracle(name, N, K, M):
+    """n = 9..32 at m=16,k=256 is the reference's own grid (tests/test-backend-ops.cpp:4246-4266); the rest are ragged tiles."""
+    t = O.QUANT_TYPES[name]
+    K = _k_for(name, K)
+    rng = np.random.default_rng(N * 3 + K + M)
+    W = O.random_quant_bytes(t, N, K, rng)
+    X = rng.uniform(-1, 1, (M, K)).astype(np.float32)
+    got = _ops().mul_mat_q(t, _dev(W), torch.from_numpy(X).cuda(), N, K).cpu().numpy()
+    ref = O.mul_mat_f32(t, W, X, N, K, M)
+    assert _nmse(got, ref) < NMSE_BAR, _nmse(got, ref)
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_strided_activations_and_padded_rows(name):
+    """src1 rows with a stride (a view) and weight rows with a larger nb1."""
+    t = O.QUANT_TYPES[name]
+    N, K, M = 70, _k_for(name, 768), 40
+    rng = np.random.default_rng(3)
+    W = O.random_quant_bytes(t, N, K, rng)
+    rb = W.shape[1]
+    nb1 = rb + 64
+    Wp = np.zeros((N, nb1), dtype=np.uint8); Wp[:, :rb] = W
+    Xfull = rng.uniform(-1, 1, (M, K + 12)).astype(np.float32)
+    Xd = torch.from_numpy(Xfull).cuda()[:, 4:4 + K]                    # 16-byte aligned start, row stride K+12
+    got = _ops().mul_mat_q(t, _dev(Wp), Xd, N, K, nb1=nb1).cpu().numpy()
+    ref = O.mul_mat_f32(t, W, np.ascontiguousarray(Xfull[:, 4:4 + K]), N, K, M)
+    assert _nmse(got, ref) < NMSE_BAR
+    Xu = torch.from_numpy(Xfull).cuda()[:, 1:1 + K]                    # unaligned start: scalar conversion path
+    got = _ops().mul_mat_q(t, _dev(Wp), Xu, N, K, nb1=nb1).cpu().numpy()
+    ref = O.mul_mat_f32(t, W, np.ascontiguousarray(Xfull[:, 1:1 + K]), N, K, M)
+    assert _nmse(got, ref) < NMSE_BAR
+
+
+@pytest.mark.parametrize("name", ["q4_k", "q6_k"])
+def test_model_size_properties(name):
+    """Llama-3-8B FFN shape at pp512: agreement with the GEMV path (itself oracle-checked), exact scaling by a
+    power of two, and determinism."""
+    ops = _ops()
+    t = O.QUANT_TYPES[name]
+    N, K, M = 14336, 4096, 512
+    rng = np.random.default_rng(9)
+    one = O.random_quant_bytes(t, 256, K, rng)
+    W = _dev(np.tile(one, (N // 256, 1)))
+    X = torch.randn(M, K, device="cuda")
+    a = ops.mul_mat_q(t, W, X, N, K)
+    b = ops.mul_mat_q(t, W, X, N, K)
+    assert torch.equal(a, b)
+    assert torch.equal(ops.mul_mat_q(t, W, X * 4.0, N, K), a * 4.0)
+    assert torch.equal(a[:, :256], a[:, 256:512])                       # tiled weights -> tiled outputs
+    gemv = torch.cat([ops.mul_mat_vec_q(t, W, X[i:i + 8].contiguous(), N, K) for i in range(0, 64, 8)])
+    num = ((a[:64] - gemv) ** 2).sum().item(); den = (gemv ** 2).sum().item()
+    assert num / den < 2e-4, num / den
+
+
+def test_unsupported_shapes_are_refused():
+    ops = _ops()
+    W = torch.zeros(4096, dtype=torch.uint8, device="cuda")
+    X = torch.zeros(16, 128, device="cuda")
+    with pytest.raises(RuntimeError):
+        ops.mul_mat_q(O.QUANT_TYPES["q4_0"], W, X, 4, 128)              # K % 256 != 0
+    with pytest.raises(RuntimeError):
+        ops.mul_mat_q(O.QUANT_TYPES["q6_k"], W, torch.zeros(16, 256, device="cuda"), 4, 256)      # 210-byte row stride
