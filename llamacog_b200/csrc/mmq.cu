@@ -6,9 +6,12 @@
 // One CTA owns a 128-weight-row x TN-token output tile whose f32 accumulator lives in TMEM.  Per 256-K
 // block:  warp 0 TMA-loads the raw GGUF bytes of the 128 rows (2-D tensor map over the weight bytes),
 // warp 3 TMA-loads the bf16 activation tiles (2-D tensor map, 128-byte swizzle), eight dequantiser warps
-// expand the blocks to bf16 straight into the 128B-swizzled K-major layout tcgen05 reads, and one thread
-// of warp 1 issues tcgen05.mma (kind::f16, bf16 x bf16 -> f32, M=128, N=TN, K=16).  Raw bytes are read
-// from HBM exactly once per tile row; dequantisation overlaps the tensor pipe through a 4-slot ring.
+// expand the blocks to bf16 and store them with tcgen05.st into a ring of A-operand slots in TENSOR
+// MEMORY (thread = weight row = TMEM lane), and one thread of warp 1 issues tcgen05.mma with A from TMEM
+// and B from shared memory (kind::f16, bf16 x bf16 -> f32, M=128, N=TN, K=16).  Keeping A out of shared
+// memory matters: an SS-mode MMA reads A and B from shared memory at 96 B/clk of the SM's 128 B/clk, which
+// left the first version of this kernel shared-memory bound at 37 % tensor-pipe utilisation
+// (profiles/r01_mmq_notes.md).  Raw bytes are read from HBM exactly once per tile row.
 // Activations are converted f32 -> bf16 once per mat-mul by a small pre-pass (the reference quantises
 // them to q8_1 there instead, ggml-cuda/quantize.cu).
 #include "common.cuh"
@@ -18,6 +21,7 @@
 #include <cuda_bf16.h>
 #include <cstdlib>
 #include <cstring>
+#include <type_traits>
 
 namespace b200 {
 
@@ -50,6 +54,24 @@ __device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t adesc, uint
                  "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
                  :: "r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// same with A read from tensor memory (lane = row, two bf16 per 32-bit column)
+__device__ __forceinline__ void tc_mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                 :: "r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 32 consecutive 32-bit columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+                 "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+                 :: "r"(taddr),
+                    "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+                    "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+                    "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+                    "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
                  "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
@@ -62,12 +84,11 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 // bounded mbarrier wait: a pipeline bug traps (launch failure) instead of hanging the GPU
 __device__ __forceinline__ void mbar_wait_b(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
-    const long long t0 = clock64();
-    while (true) {
+    for (uint32_t spins = 0; ; ++spins) {
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
                      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
         if (done) return;
-        if (clock64() - t0 > 4000000000ll) __trap();
+        if (spins > (1u << 26)) __trap();
     }
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
@@ -103,8 +124,8 @@ __device__ __forceinline__ uint32_t umma_idesc_bf16(int tn) {
 // ------------------------------------------------------------------------------------------------
 // Dequantisers.  A dequantiser thread owns one weight row r of the tile and one half h of each 256-K
 // block (h = 0: K 0..127, h = 1: K 128..255), i.e. the two 64-K sub-chunks c = 2h, 2h+1.  For each it
-// writes the row's 8 16-byte chunks (8 bf16 each) of the A tile:  chunk u of row r lives at
-// r*128 + ((u ^ (r & 7)) << 4)  (the 128-byte swizzle tcgen05 and TMA use).
+// produces the row's 64 bf16 as 32 packed registers (chunk u = elements 8u..8u+7 = out[4u..4u+3]), which
+// one tcgen05.st writes to the 32 columns of the thread's TMEM lane.
 //
 // Integer codes become bf16 without conversions: a byte 0x80|(q << s) under a 0x3F high byte is the
 // bf16 value 1 + q/2^(7-s), so  w = q*scale - offset  is one packed fma  x*S + B  with S = 2^(7-s)*scale
@@ -120,6 +141,19 @@ __device__ __forceinline__ void expand4(uint32_t codes, uint32_t s2, uint32_t b2
     o01 = fma_bf16x2(__byte_perm(codes, 0x3F3F3F3Fu, PRMT_01), s2, b2);
     o23 = fma_bf16x2(__byte_perm(codes, 0x3F3F3F3Fu, PRMT_23), s2, b2);
 }
+// symmetric formats (no per-block minimum): remove the code offset exactly first ((1 + q/2^n) - off is exact in bf16),
+// then one multiply -- a single rounding per weight
+__device__ __forceinline__ uint32_t add_bf16x2(uint32_t a, uint32_t b) {
+    uint32_t d; asm("add.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d;
+}
+__device__ __forceinline__ uint32_t mul_bf16x2(uint32_t a, uint32_t b) {
+    uint32_t d; asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d;
+}
+__device__ __forceinline__ void expand4_sym(uint32_t codes, uint32_t s2, uint32_t & o01, uint32_t & o23) {
+    constexpr uint32_t M15 = 0xBFC0BFC0u;      // {-1.5, -1.5} bf16
+    o01 = mul_bf16x2(add_bf16x2(__byte_perm(codes, 0x3F3F3F3Fu, PRMT_01), M15), s2);
+    o23 = mul_bf16x2(add_bf16x2(__byte_perm(codes, 0x3F3F3F3Fu, PRMT_23), M15), s2);
+}
 // scale pair from S (float): s2 = {S,S} bf16, b2 = {-(Sr*bm + off)} with Sr the rounded S
 __device__ __forceinline__ void make_sb(float S, float bm, float off, uint32_t & s2, uint32_t & b2) {
     s2 = pack_bf16_dup(S);
@@ -133,8 +167,9 @@ template <int TYPE> struct dq;
 template <> struct dq<T_Q4_K> {
     static constexpr int PITCH = 144;      // bytes of one row's block in the raw stage
     static constexpr int STEP16 = 72;      // block stride in 16-bit elements (tensor-map coordinate)
+    static constexpr bool SHIFTED = false;
     uint32_t s2[4], b2[4];
-    __device__ __forceinline__ void prep(uint32_t row, int h) {
+    template <int S> __device__ __forceinline__ void prep(uint32_t row, int h) {
         const int4 hd = lds128(row);
         const float d = half_bits_to_float(hd.x & 0xFFFF), dmin = half_bits_to_float((uint32_t)hd.x >> 16);
         uint32_t SC, MN;
@@ -143,7 +178,7 @@ template <> struct dq<T_Q4_K> {
 #pragma unroll
         for (int j = 0; j < 4; ++j) make_sb(16.0f * d * ubyte_f(SC, j), 1.0f, dmin * ubyte_f(MN, j), s2[j], b2[j]);
     }
-    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t dst, int rx) const {
+    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t (&out)[32]) const {
         const uint32_t qs = row + 16 + 32 * (2 * h + t);
         const int4 q0 = lds128(qs), q1 = lds128(qs + 16);
         const uint32_t w[8] = {(uint32_t)q0.x, (uint32_t)q0.y, (uint32_t)q0.z, (uint32_t)q0.w, (uint32_t)q1.x, (uint32_t)q1.y, (uint32_t)q1.z, (uint32_t)q1.w};
@@ -156,8 +191,8 @@ template <> struct dq<T_Q4_K> {
                 expand4(((x << 3) & 0x78787878u) | 0x80808080u, s2[2 * t], b2[2 * t], o[2 * i], o[2 * i + 1]);
                 expand4(((x >> 1) & 0x78787878u) | 0x80808080u, s2[2 * t + 1], b2[2 * t + 1], p[2 * i], p[2 * i + 1]);
             }
-            sts128(dst + ((u ^ rx) << 4), o[0], o[1], o[2], o[3]);
-            sts128(dst + (((u + 4) ^ rx) << 4), p[0], p[1], p[2], p[3]);
+            { out[4 * (u)] = o[0]; out[4 * (u) + 1] = o[1]; out[4 * (u) + 2] = o[2]; out[4 * (u) + 3] = o[3]; }
+            { out[4 * ((u + 4))] = p[0]; out[4 * ((u + 4)) + 1] = p[1]; out[4 * ((u + 4)) + 2] = p[2]; out[4 * ((u + 4)) + 3] = p[3]; }
         }
     }
 };
@@ -166,8 +201,9 @@ template <> struct dq<T_Q4_K> {
 template <> struct dq<T_Q5_K> {
     static constexpr int PITCH = 176;
     static constexpr int STEP16 = 88;
+    static constexpr bool SHIFTED = false;
     uint32_t s2[4], b2[4], qh[8];
-    __device__ __forceinline__ void prep(uint32_t row, int h) {
+    template <int S> __device__ __forceinline__ void prep(uint32_t row, int h) {
         const int4 hd = lds128(row);
         const float d = half_bits_to_float(hd.x & 0xFFFF), dmin = half_bits_to_float((uint32_t)hd.x >> 16);
         uint32_t SC, MN;
@@ -180,7 +216,7 @@ template <> struct dq<T_Q5_K> {
         qh[0] = (uint32_t)a.x >> sh; qh[1] = (uint32_t)a.y >> sh; qh[2] = (uint32_t)a.z >> sh; qh[3] = (uint32_t)a.w >> sh;
         qh[4] = (uint32_t)b.x >> sh; qh[5] = (uint32_t)b.y >> sh; qh[6] = (uint32_t)b.z >> sh; qh[7] = (uint32_t)b.w >> sh;
     }
-    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t dst, int rx) const {
+    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t (&out)[32]) const {
         const uint32_t qs = row + 48 + 32 * (2 * h + t);
         const int4 q0 = lds128(qs), q1 = lds128(qs + 16);
         const uint32_t w[8] = {(uint32_t)q0.x, (uint32_t)q0.y, (uint32_t)q0.z, (uint32_t)q0.w, (uint32_t)q1.x, (uint32_t)q1.y, (uint32_t)q1.z, (uint32_t)q1.w};
@@ -196,49 +232,66 @@ template <> struct dq<T_Q5_K> {
                 expand4(lo, s2[2 * t], b2[2 * t], o[2 * i], o[2 * i + 1]);
                 expand4(hi, s2[2 * t + 1], b2[2 * t + 1], p[2 * i], p[2 * i + 1]);
             }
-            sts128(dst + ((u ^ rx) << 4), o[0], o[1], o[2], o[3]);
-            sts128(dst + (((u + 4) ^ rx) << 4), p[0], p[1], p[2], p[3]);
+            { out[4 * (u)] = o[0]; out[4 * (u) + 1] = o[1]; out[4 * (u) + 2] = o[2]; out[4 * (u) + 3] = o[3]; }
+            { out[4 * ((u + 4))] = p[0]; out[4 * ((u + 4)) + 1] = p[1]; out[4 * ((u + 4)) + 2] = p[2]; out[4 * ((u + 4)) + 3] = p[3]; }
         }
     }
 };
 
+// NW 32-bit words at byte offset S (even, < 16, compile time) past a 16-byte aligned shared address
+template <int NW, int S> __device__ __forceinline__ void lds_shifted(uint32_t a16, uint32_t (&out)[NW]) {
+    constexpr int NV = (S + 4 * NW + 15) / 16, WO = S >> 2, SH = (S & 2) * 8;
+    uint32_t w[4 * NV + 1];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        const int4 t = lds128(a16 + 16 * v);
+        w[4 * v] = (uint32_t)t.x; w[4 * v + 1] = (uint32_t)t.y; w[4 * v + 2] = (uint32_t)t.z; w[4 * v + 3] = (uint32_t)t.w;
+    }
+    w[4 * NV] = 0;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) out[i] = SH ? __funnelshift_r(w[WO + i], w[WO + i + 1], SH) : w[WO + i];
+}
+
 // ---- Q6_K: ql[128] | qh[64] | scales int8[16] | d (f16).  Element e: half hh = e/128, g = (e%128)/32, l = e%32:
-//      nibble (g/2) of ql[64hh + 32(g&1) + l], bits 2g..2g+1 of qh[32hh + l]; value (q6 - 32) * d * scales[e/16]
+//      nibble (g/2) of ql[64hh + 32(g&1) + l], bits 2g..2g+1 of qh[32hh + l]; value (q6 - 32) * d * scales[e/16].
+//      A 210-byte block is not a multiple of 16: TMA fetches the enclosing 16-byte aligned 240-byte window, so block
+//      kb starts S = (210 kb) mod 16 = 2 (kb mod 8) bytes into its row of the raw stage (compile-time per unrolled kb).
 template <> struct dq<T_Q6_K> {
-    static constexpr int PITCH = 240;      // 210 bytes + 30 of the next block (ignored); keeps 16-byte loads conflict-free
+    static constexpr int PITCH = 240;
     static constexpr int STEP16 = 105;
-    uint32_t s2[8], b2[8];                 // 8 x 16-element scale groups of this half
-    __device__ __forceinline__ void prep(uint32_t row, int h) {
-        const float d = half_bits_to_float(lds16(row + 208));
-        const uint2 sc = lds64(row + 192 + 8 * h);
+    static constexpr bool SHIFTED = true;
+    uint32_t s2[8];                        // 8 x 16-element scale groups of this half
+    uint32_t ql[16], qh[8];                // this half's 64 low-nibble bytes and 32 high-bit bytes
+    template <int S> __device__ __forceinline__ void prep(uint32_t row, int h) {
+        const float d = half_bits_to_float(lds16(row + 208 + S));
+        uint32_t sc[4]; lds_shifted<4, S>(row + 192, sc);
+        const uint32_t sx = h ? sc[2] : sc[0], sy = h ? sc[3] : sc[1];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const int s = (int)(int8_t)(((j < 4 ? sc.x : sc.y) >> (8 * (j & 3))) & 0xFF);
-            make_sb(64.0f * d * (float)s, 1.5f, 0.0f, s2[j], b2[j]);      // (q6 - 32) * ds = (1 + q6/64) * 64ds - 1.5 * 64ds
+            const int v = (int)(int8_t)(((j < 4 ? sx : sy) >> (8 * (j & 3))) & 0xFF);
+            s2[j] = pack_bf16_dup(64.0f * d * (float)v);                  // (q6 - 32) * ds = ((1 + q6/64) - 1.5) * 64ds
         }
+        lds_shifted<16, S>(row + 64 * h, ql);
+        lds_shifted<8, S>(row + 128 + 32 * h, qh);
     }
-    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t dst, int rx) const {
+    __device__ __forceinline__ void emit(uint32_t, int, int t, uint32_t (&out)[32]) const {
 #pragma unroll
         for (int g = 0; g < 2; ++g) {      // 32 elements each; sub-chunk c = 2h + t holds groups 2t, 2t+1 of half h
-            const uint32_t ql = row + 64 * h + 32 * g, qhp = row + 128 + 32 * h;
-            const int4 q0 = lds128(ql), q1 = lds128(ql + 16), h0 = lds128(qhp), h1 = lds128(qhp + 16);
-            const uint32_t w[8] = {(uint32_t)q0.x, (uint32_t)q0.y, (uint32_t)q0.z, (uint32_t)q0.w, (uint32_t)q1.x, (uint32_t)q1.y, (uint32_t)q1.z, (uint32_t)q1.w};
-            const uint32_t hb[8] = {(uint32_t)h0.x, (uint32_t)h0.y, (uint32_t)h0.z, (uint32_t)h0.w, (uint32_t)h1.x, (uint32_t)h1.y, (uint32_t)h1.z, (uint32_t)h1.w};
             const int gg = 2 * t + g;      // bit pair 2gg of qh
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 uint32_t o[4];
 #pragma unroll
                 for (int i = 0; i < 2; ++i) {
-                    const uint32_t x = w[2 * u + i], y = hb[2 * u + i];
+                    const uint32_t x = ql[8 * g + 2 * u + i], y = qh[2 * u + i];
                     // code byte = 0x80 | q6 << 1 : nibble at bits 1..4, high pair at bits 5..6
                     const uint32_t nib = t == 0 ? (x << 1) : (x >> 3);
                     const uint32_t hi2 = 2 * gg <= 5 ? (y << (5 - 2 * gg)) : (y >> (2 * gg - 5));
                     const uint32_t code = (nib & 0x1E1E1E1Eu) | 0x80808080u | (hi2 & 0x60606060u);
                     const int si = 4 * t + 2 * g + (u >> 1);
-                    expand4(code, s2[si], b2[si], o[2 * i], o[2 * i + 1]);
+                    expand4_sym(code, s2[si], o[2 * i], o[2 * i + 1]);
                 }
-                sts128(dst + (((4 * g + u) ^ rx) << 4), o[0], o[1], o[2], o[3]);
+                { out[4 * ((4 * g + u))] = o[0]; out[4 * ((4 * g + u)) + 1] = o[1]; out[4 * ((4 * g + u)) + 2] = o[2]; out[4 * ((4 * g + u)) + 3] = o[3]; }
             }
         }
     }
@@ -248,13 +301,13 @@ template <> struct dq<T_Q6_K> {
 template <> struct dq<T_Q4_0> {
     static constexpr int PITCH = 144;
     static constexpr int STEP16 = 72;
-    __device__ __forceinline__ void prep(uint32_t, int) {}
-    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t dst, int rx) const {
+    static constexpr bool SHIFTED = false;
+    template <int S> __device__ __forceinline__ void prep(uint32_t, int) {}
+    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t (&out)[32]) const {
 #pragma unroll
         for (int b = 0; b < 2; ++b) {
             const uint32_t blk = row + 18 * (2 * (2 * h + t) + b);
-            uint32_t s2, b2;
-            make_sb(16.0f * half_bits_to_float(lds16(blk)), 1.5f, 0.0f, s2, b2);      // (q - 8) d = (1 + q/16) 16d - 1.5 * 16d
+            const uint32_t s2 = pack_bf16_dup(16.0f * half_bits_to_float(lds16(blk)));      // (q - 8) d = ((1 + q/16) - 1.5) * 16d
             int w[4]; lds_words_a2<4>(blk + 2, w);
 #pragma unroll
             for (int u = 0; u < 2; ++u) {
@@ -262,11 +315,11 @@ template <> struct dq<T_Q4_0> {
 #pragma unroll
                 for (int i = 0; i < 2; ++i) {
                     const uint32_t x = (uint32_t)w[2 * u + i];
-                    expand4(((x << 3) & 0x78787878u) | 0x80808080u, s2, b2, o[2 * i], o[2 * i + 1]);
-                    expand4(((x >> 1) & 0x78787878u) | 0x80808080u, s2, b2, p[2 * i], p[2 * i + 1]);
+                    expand4_sym(((x << 3) & 0x78787878u) | 0x80808080u, s2, o[2 * i], o[2 * i + 1]);
+                    expand4_sym(((x >> 1) & 0x78787878u) | 0x80808080u, s2, p[2 * i], p[2 * i + 1]);
                 }
-                sts128(dst + (((4 * b + u) ^ rx) << 4), o[0], o[1], o[2], o[3]);
-                sts128(dst + (((4 * b + u + 2) ^ rx) << 4), p[0], p[1], p[2], p[3]);
+                { out[4 * ((4 * b + u))] = o[0]; out[4 * ((4 * b + u)) + 1] = o[1]; out[4 * ((4 * b + u)) + 2] = o[2]; out[4 * ((4 * b + u)) + 3] = o[3]; }
+                { out[4 * ((4 * b + u + 2))] = p[0]; out[4 * ((4 * b + u + 2)) + 1] = p[1]; out[4 * ((4 * b + u + 2)) + 2] = p[2]; out[4 * ((4 * b + u + 2)) + 3] = p[3]; }
             }
         }
     }
@@ -277,8 +330,9 @@ template <> struct dq<T_Q4_0> {
 template <> struct dq<T_Q8_0> {
     static constexpr int PITCH = 272;
     static constexpr int STEP16 = 136;
-    __device__ __forceinline__ void prep(uint32_t, int) {}
-    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t dst, int rx) const {
+    static constexpr bool SHIFTED = false;
+    template <int S> __device__ __forceinline__ void prep(uint32_t, int) {}
+    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t (&out)[32]) const {
 #pragma unroll
         for (int b = 0; b < 2; ++b) {
             const uint32_t blk = row + 34 * (2 * (2 * h + t) + b);
@@ -296,7 +350,7 @@ template <> struct dq<T_Q8_0> {
                     const float2 fc = __half22float2(__hmul2(__hsub2(*reinterpret_cast<const __half2 *>(&c), off), d2));
                     o[2 * i] = pack_bf16(fa.x, fa.y); o[2 * i + 1] = pack_bf16(fc.x, fc.y);
                 }
-                sts128(dst + (((4 * b + u) ^ rx) << 4), o[0], o[1], o[2], o[3]);
+                { out[4 * ((4 * b + u))] = o[0]; out[4 * ((4 * b + u)) + 1] = o[1]; out[4 * ((4 * b + u)) + 2] = o[2]; out[4 * ((4 * b + u)) + 3] = o[3]; }
             }
         }
     }
@@ -304,19 +358,22 @@ template <> struct dq<T_Q8_0> {
 
 // ------------------------------------------------------------------------------------------------
 // The kernel.  Step i = 4*kb + j covers the 64-K sub-chunk c = {0,2,1,3}[j] of block kb, so that the two
-// dequantiser groups (h = 0: sub-chunks 0,1; h = 1: sub-chunks 2,3) alternate: A slot = j, group = j & 1.
+// dequantiser groups (h = 0: sub-chunks 0,1; h = 1: sub-chunks 2,3) alternate: group = i & 1.
+// Tensor memory: columns [0, tn) hold the f32 accumulator, columns [a_col0, a_col0 + 32*na) the ring of
+// `na` A slots (128 lanes x 32 columns = 128 rows x 64 bf16 each).
 // ------------------------------------------------------------------------------------------------
 struct mmq_params {
     float * dst; int64_t ds;     // dst[m*ds + n]
     int N, M, K;
     int tn;                      // tokens per tile: 32, 64, 128 or 256
-    int nb;                      // depth of the activation-tile ring (<= 4)
+    int nb;                      // depth of the activation-tile ring in shared memory (<= NB_MAX)
+    int na;                      // depth of the A ring in tensor memory: 4 or 8 (even)
+    int tmem_cols;               // 256 or 512
 };
 
 constexpr int MMQ_THREADS = 384;
-constexpr int A_SLOT = 128 * 128;            // 128 rows x 64 bf16
-constexpr int A_SLOTS = 4;
-constexpr int NB_MAX = 4;
+constexpr int NA_MAX = 8;
+constexpr int NB_MAX = 6;
 
 template <int TYPE>
 __global__ void __launch_bounds__(MMQ_THREADS, 1)
@@ -325,26 +382,26 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
     constexpr int RAW = 128 * DQ::PITCH;
     extern __shared__ uint8_t smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
-    const int tn = p.tn, nb = p.nb;
+    const int tn = p.tn, nb = p.nb, na = p.na;
     const uint32_t b_slot = (uint32_t)tn * 128u;
-    const uint32_t sA = base, sB = sA + A_SLOTS * A_SLOT, sR = sB + (uint32_t)nb * b_slot, sBar = sR + 2 * RAW;
-    const uint32_t raw_full = sBar, raw_empty = sBar + 16, a_full = sBar + 32, a_empty = sBar + 64,
-                   b_full = sBar + 96, b_empty = sBar + 128, tmem_full = sBar + 160, tmem_slot = sBar + 168;
+    const uint32_t sB = base, sR = sB + (uint32_t)nb * b_slot, sBar = sR + 2 * RAW;
+    const uint32_t raw_full = sBar, raw_empty = sBar + 16, a_full = sBar + 32, a_empty = a_full + 8 * NA_MAX,
+                   b_full = a_empty + 8 * NA_MAX, b_empty = b_full + 8 * NB_MAX, tmem_full = b_empty + 8 * NB_MAX, tmem_slot = tmem_full + 8;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.x * tn, n0 = blockIdx.y * 128;
     const int nkb = p.K >> 8, nsteps = nkb * 4;
-    const uint32_t ncols = tn < 32 ? 32u : (uint32_t)tn;
+    const uint32_t a_col0 = (uint32_t)p.tmem_cols - 32u * (uint32_t)na;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) { mbar_init(raw_full + 8 * i, 1); mbar_init(raw_empty + 8 * i, 8); }
-        for (int i = 0; i < A_SLOTS; ++i) { mbar_init(a_full + 8 * i, 4); mbar_init(a_empty + 8 * i, 1); }
+        for (int i = 0; i < NA_MAX; ++i) { mbar_init(a_full + 8 * i, 4); mbar_init(a_empty + 8 * i, 1); }
         for (int i = 0; i < NB_MAX; ++i) { mbar_init(b_full + 8 * i, 1); mbar_init(b_empty + 8 * i, 1); }
         mbar_init(tmem_full, 1);
         mbar_fence_init();
         tma_prefetch_desc(&wmap); tma_prefetch_desc(&xmap);
     }
-    if (warp == 2) { tmem_alloc(tmem_slot, ncols); tmem_relinquish(); }
+    if (warp == 2) { tmem_alloc(tmem_slot, (uint32_t)p.tmem_cols); tmem_relinquish(); }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -358,7 +415,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
                 const int s = kb & 1;
                 mbar_wait_b(raw_empty + 8 * s, ((kb >> 1) & 1) ^ 1);
                 mbar_expect_tx(raw_full + 8 * s, RAW);
-                tma_load_2d(sR + s * RAW, &wmap, kb * DQ::STEP16, n0, raw_full + 8 * s);
+                tma_load_2d(sR + s * RAW, &wmap, (kb * DQ::STEP16) & ~7, n0, raw_full + 8 * s);     // 16-byte aligned start
             }
         }
     } else if (warp == 3) {
@@ -374,38 +431,55 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
         if (lane == 0) {                         // tensor-core issue
             const uint32_t idesc = umma_idesc_bf16(tn);
             for (int i = 0; i < nsteps; ++i) {
-                const int sa = i & 3, sb = i % nb;
-                mbar_wait_b(a_full + 8 * sa, (i >> 2) & 1);
+                const int sa = i % na, sb = i % nb;
+                mbar_wait_b(a_full + 8 * sa, (i / na) & 1);
                 mbar_wait_b(b_full + 8 * sb, (i / nb) & 1);
                 tc_fence_after();
-                const uint64_t ad = umma_desc_sw128(sA + sa * A_SLOT), bd = umma_desc_sw128(sB + sb * b_slot);
+                const uint32_t at = tmem_base + a_col0 + 32u * (uint32_t)sa;
+                const uint64_t bd = umma_desc_sw128(sB + sb * b_slot);
 #pragma unroll
-                for (int k = 0; k < 4; ++k)      // K = 16 per instruction: 32 bytes along the swizzled row
-                    tc_mma_f16(tmem_base, ad + 2 * k, bd + 2 * k, idesc, (uint32_t)((i | k) != 0));
+                for (int k = 0; k < 4; ++k)      // K = 16 per instruction: 8 TMEM columns of A, 32 bytes along B's swizzled row
+                    tc_mma_f16_ts(tmem_base, at + 8 * k, bd + 2 * k, idesc, (uint32_t)((i | k) != 0));
                 tc_commit(a_empty + 8 * sa);
                 tc_commit(b_empty + 8 * sb);
             }
             tc_commit(tmem_full);
         }
     } else if (warp >= 4) {
-        const int dw = warp - 4, h = dw >> 2, r = (dw & 3) * 32 + lane, rx = r & 7;
+        const int dw = warp - 4, h = dw >> 2, r = (dw & 3) * 32 + lane;
+        const uint32_t lane_base = tmem_base + ((uint32_t)((dw & 3) * 32) << 16);      // this warp's TMEM lane quarter
         DQ q;
-        for (int kb = 0; kb < nkb; ++kb) {
+        auto block = [&](auto shift, int kb) {
+            constexpr int S = decltype(shift)::value;
             const int s = kb & 1;
             mbar_wait_b(raw_full + 8 * s, (kb >> 1) & 1);
             const uint32_t row = sR + s * RAW + r * DQ::PITCH;
-            q.prep(row, h);
+            q.template prep<S>(row, h);
 #pragma unroll
             for (int t = 0; t < 2; ++t) {
-                const int slot = 2 * t + h;
-                mbar_wait_b(a_empty + 8 * slot, (kb & 1) ^ 1);
-                q.emit(row, h, t, sA + slot * A_SLOT + r * 128, rx);
-                fence_proxy_async();             // generic-proxy stores -> visible to the tensor core's async proxy
+                const int i = 4 * kb + 2 * t + h, slot = i % na;
+                uint32_t out[32];
+                q.emit(row, h, t, out);
+                mbar_wait_b(a_empty + 8 * slot, ((i / na) & 1) ^ 1);
+                tc_fence_after();
+                tmem_st32(lane_base + a_col0 + 32u * (uint32_t)slot, out);
+                tmem_st_wait();
+                tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(a_full + 8 * slot);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(raw_empty + 8 * s);
+        };
+        if constexpr (DQ::SHIFTED) {             // block kb sits 2*(kb % 8) bytes into its raw row: unroll the period
+            for (int kb = 0; kb < nkb; kb += 8) {
+                block(std::integral_constant<int, 0>{}, kb);      block(std::integral_constant<int, 2>{}, kb + 1);
+                block(std::integral_constant<int, 4>{}, kb + 2);  block(std::integral_constant<int, 6>{}, kb + 3);
+                block(std::integral_constant<int, 8>{}, kb + 4);  block(std::integral_constant<int, 10>{}, kb + 5);
+                block(std::integral_constant<int, 12>{}, kb + 6); block(std::integral_constant<int, 14>{}, kb + 7);
+            }
+        } else {
+            for (int kb = 0; kb < nkb; ++kb) block(std::integral_constant<int, 0>{}, kb);
         }
         // epilogue: TMEM lane = weight row (this warp's quarter), column = token; group h takes every other 32 columns
         mbar_wait_b(tmem_full, 0);
@@ -413,7 +487,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
         const int n = n0 + r;
         for (int c0 = h * 32; c0 < tn; c0 += 64) {
             uint32_t v[32];
-            tmem_ld32(tmem_base + ((uint32_t)((dw & 3) * 32) << 16) + (uint32_t)c0, v);
+            tmem_ld32(lane_base + (uint32_t)c0, v);
             tmem_ld_wait();
             if (n < p.N) {
 #pragma unroll
@@ -426,7 +500,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 2) { tc_fence_after(); tmem_dealloc(tmem_base, ncols); }
+    if (warp == 2) { tc_fence_after(); tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols); }
 }
 
 // ---- activations f32 -> bf16 [M][K] (contiguous) ----
@@ -472,7 +546,7 @@ static int raw_pitch(int type) {
                     case T_Q5_K: return pitch_of<T_Q5_K>(); case T_Q6_K: return pitch_of<T_Q6_K>(); }
     return 0;
 }
-static size_t mmq_smem(int type, int tn, int nb) { return 1024 + (size_t)A_SLOTS * A_SLOT + (size_t)nb * tn * 128 + 2 * 128 * (size_t)raw_pitch(type) + 256; }
+static size_t mmq_smem(int type, int tn, int nb) { return 1024 + (size_t)nb * tn * 128 + 2 * 128 * (size_t)raw_pitch(type) + 512; }
 
 // tokens per tile: fill the 148 SMs first, then prefer the wider tile (weights are dequantised once per tile)
 static int choose_tn(int N, int M) {
@@ -515,6 +589,7 @@ using namespace b200;
 
 extern "C" int b200_mul_mat_q_supported(int type, const void * W, int64_t nb1, int K) {
     if (!raw_pitch(type) || K <= 0 || K % 256) return 0;
+    if (type == T_Q6_K && K % 2048) return 0;                     // the 210-byte blocks realign with 16 bytes every 8 blocks
     if (((uintptr_t)W & 15) || (nb1 & 15)) return 0;              // TMA: 16-byte aligned base and row stride
     if (nb1 < (int64_t)(K / block_elems(type)) * block_bytes(type)) return 0;
     return encode_tiled() != nullptr;
@@ -547,6 +622,9 @@ extern "C" int b200_mul_mat_q(int type, const void * W, int64_t nb1, const float
     p.tn = choose_tn(N, M);
     p.nb = NB_MAX;
     while (p.nb > 2 && mmq_smem(type, p.tn, p.nb) > 232448) --p.nb;
+    // tensor memory: accumulator columns + A ring; narrow tiles take half of it so that two CTAs can share an SM
+    p.na = p.tn <= 128 ? 4 : NA_MAX;
+    p.tmem_cols = p.tn <= 128 ? 256 : 512;
     if (mmq_smem(type, p.tn, p.nb) > 232448) return -3;
     const size_t smem = mmq_smem(type, p.tn, p.nb);
 

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(288, (M <= 4 ? 2 : 1)) mmvq_kernel(const mmvq_
     float * Dc = p.dst;
     if (gridDim.y > 1 || gridDim.z > 1 || p.ids) {
         const int y = blockIdx.y, z = blockIdx.z;
-        if (p.ids) Wc += (int64_t)p.ids[z * p.ids_sz + y] * p.w_sy;
+        if (p.ids) { pdl_wait(); Wc += (int64_t)p.ids[z * p.ids_sz + y] * p.w_sy; }      // the expert ids come from the previous kernels
         else Wc += (int64_t)(y / p.w_div_y) * p.w_sy + (int64_t)(z / p.w_div_z) * p.w_sz;
         const int xy = y % p.x_mod_y;
         if (Xc) Xc += (int64_t)xy * p.x_sy + (int64_t)z * p.x_sz;

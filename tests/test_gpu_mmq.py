@@ -29,7 +29,7 @@ def _dev(Wnp):
 
 
 def _k_for(name, k):
-    return (k + 2047) // 2048 * 2048 if name == "q6_k" else k       # Q6_K rows must be a multiple of 16 bytes for TMA
+    return (k + 2047) // 2048 * 2048 if name == "q6_K" else k       # Q6_K rows must be a multiple of 16 bytes for TMA
 
 
 def _nmse(got, ref):
@@ -86,7 +86,7 @@ def test_strided_activations_and_padded_rows(name):
     assert _nmse(got, ref) < NMSE_BAR
 
 
-@pytest.mark.parametrize("name", ["q4_k", "q6_k"])
+@pytest.mark.parametrize("name", ["q4_K", "q6_K"])
 def test_model_size_properties(name):
     """Llama-3-8B FFN shape at pp512: agreement with the GEMV path (itself oracle-checked), exact scaling by a
     power of two, and determinism."""
@@ -114,4 +114,4 @@ def test_unsupported_shapes_are_refused():
     with pytest.raises(RuntimeError):
         ops.mul_mat_q(O.QUANT_TYPES["q4_0"], W, X, 4, 128)              # K % 256 != 0
     with pytest.raises(RuntimeError):
-        ops.mul_mat_q(O.QUANT_TYPES["q6_k"], W, torch.zeros(16, 256, device="cuda"), 4, 256)      # 210-byte row stride
+        ops.mul_mat_q(O.QUANT_TYPES["q6_K"], W, torch.zeros(16, 256, device="cuda"), 4, 256)      # 210-byte row stride

@@ -5,7 +5,7 @@ timeout 300 python tools/mmq_debug.py check > gpurun_out/mmq_check.log 2>&1; ech
 tail -5 gpurun_out/mmq_check.log
 timeout 600 python -m pytest tests/test_gpu_mmq.py -q -x > gpurun_out/mmq_pytest.log 2>&1; echo "exit $?" >> gpurun_out/mmq_pytest.log
 tail -5 gpurun_out/mmq_pytest.log
-timeout 300 python tools/mmq_debug.py time q4_k q6_k > gpurun_out/mmq_time.log 2>&1; echo "exit $?" >> gpurun_out/mmq_time.log
+timeout 300 python tools/mmq_debug.py time q4_K q6_K > gpurun_out/mmq_time.log 2>&1; echo "exit $?" >> gpurun_out/mmq_time.log
 cat gpurun_out/mmq_time.log
 timeout 900 python -m pytest tests -m gpu -q -x --deselect tests/test_gpu_mmq.py > gpurun_out/pytest_gpu.log 2>&1; echo "exit $?" >> gpurun_out/pytest_gpu.log
 tail -5 gpurun_out/pytest_gpu.log

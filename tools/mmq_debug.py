@@ -87,11 +87,11 @@ def timing(name, N, K, M, iters=20):
 
 def main():
     mode = sys.argv[1] if len(sys.argv) > 1 else "check"
-    names = sys.argv[2:] or ["q4_k", "q6_k", "q5_k", "q4_0", "q8_0"]
+    names = sys.argv[2:] or ["q4_K", "q6_K", "q5_K", "q4_0", "q8_0"]
     ok = True
     if mode == "check":
         for name in names:
-            K = 2048 if name == "q6_k" else 256
+            K = 2048 if name == "q6_K" else 256
             for tn in (32, 128, 256):
                 ok &= onehot(name, 128, K, tn)
             os.environ.pop("B200_MMQ_TN", None)
