@@ -171,6 +171,9 @@ int b200_mul_mat_q(int type, const void * W, int64_t nb1, const float * X, int64
                    int N, int K, int M, void * scratch, int64_t scratch_bytes, void * stream);
 int64_t b200_mul_mat_q_scratch_bytes(int K, int M);
 int b200_mul_mat_q_supported(int type, const void * W, int64_t nb1, int K);
+/* debug hook: device buffer of (return value) int64 slots that CTA (0,0) of later b200_mul_mat_q launches fills with
+ * clock64 stamps of its pipeline events (tools/mmq_debug.py trace); NULL switches it off. */
+int b200_mmq_debug_trace(void * dev_buf);
 /* MUL_MAT_ID: dst[:, e, t] = as[:, :, ids[e, t]] x b[:, e % ne11, t]; ids i32 read on the device (no host sync).
  * Replaces ggml_cuda_mul_mat_id (ggml-cuda/ggml-cuda.cu:2007-2148) and the MoE branch of mmq.cu:141-223. */
 int b200_op_mul_mat_id(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * dst,

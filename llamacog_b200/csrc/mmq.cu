@@ -369,7 +369,16 @@ struct mmq_params {
     int nb;                      // depth of the activation-tile ring in shared memory (<= NB_MAX)
     int na;                      // depth of the A ring in tensor memory: 4 or 8 (even)
     int tmem_cols;               // 256 or 512
+    long long * trace;           // debug: clock64 stamps of CTA (0,0), [event][index] (b200_mmq_debug_trace)
 };
+constexpr int TRACE_N = 512;
+#ifdef B200_MMQ_TRACE
+__device__ __forceinline__ void trace(const mmq_params & p, int ev, int idx) {
+    if (p.trace && blockIdx.x == 0 && blockIdx.y == 0 && idx < TRACE_N) p.trace[ev * TRACE_N + idx] = clock64();
+}
+#else
+__device__ __forceinline__ void trace(const mmq_params &, int, int) {}
+#endif
 
 constexpr int MMQ_THREADS = 384;
 constexpr int NA_MAX = 8;
@@ -414,57 +423,78 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
             for (int kb = 0; kb < nkb; ++kb) {
                 const int s = kb & 1;
                 mbar_wait_b(raw_empty + 8 * s, ((kb >> 1) & 1) ^ 1);
+                trace(p, 0, kb);
                 mbar_expect_tx(raw_full + 8 * s, RAW);
                 tma_load_2d(sR + s * RAW, &wmap, (kb * DQ::STEP16) & ~7, n0, raw_full + 8 * s);     // 16-byte aligned start
             }
         }
     } else if (warp == 3) {
         if (lane == 0) {                         // bf16 activation tiles [tn][64], 128-byte swizzle
+            int s = 0; uint32_t ph = 1;
             for (int i = 0; i < nsteps; ++i) {
-                const int j = i & 3, c = ((j & 1) << 1) | (j >> 1), s = i % nb;
-                mbar_wait_b(b_empty + 8 * s, ((i / nb) & 1) ^ 1);
+                const int j = i & 3, c = ((j & 1) << 1) | (j >> 1);
+                mbar_wait(b_empty + 8 * s, ph);
+                trace(p, 1, i);
                 mbar_expect_tx(b_full + 8 * s, b_slot);
                 tma_load_2d(sB + s * b_slot, &xmap, (i >> 2) * 256 + c * 64, m0, b_full + 8 * s);
+                if (++s == nb) { s = 0; ph ^= 1; }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {                         // tensor-core issue
+        if (lane == 0) {                         // tensor-core issue: one thread, so every instruction between two MMAs counts
             const uint32_t idesc = umma_idesc_bf16(tn);
+            const uint32_t a0 = tmem_base + a_col0;
+            const uint64_t bd0 = umma_desc_sw128(sB);
+            const uint32_t bd_step = b_slot >> 4;
+            int sa = 0, sb = 0; uint32_t pa = 0, pb = 0, acc = 0;
             for (int i = 0; i < nsteps; ++i) {
-                const int sa = i % na, sb = i % nb;
-                mbar_wait_b(a_full + 8 * sa, (i / na) & 1);
-                mbar_wait_b(b_full + 8 * sb, (i / nb) & 1);
+                trace(p, 2, i);
+                mbar_wait(a_full + 8 * sa, pa);
+                mbar_wait(b_full + 8 * sb, pb);
+                trace(p, 4, i);
                 tc_fence_after();
-                const uint32_t at = tmem_base + a_col0 + 32u * (uint32_t)sa;
-                const uint64_t bd = umma_desc_sw128(sB + sb * b_slot);
-#pragma unroll
-                for (int k = 0; k < 4; ++k)      // K = 16 per instruction: 8 TMEM columns of A, 32 bytes along B's swizzled row
-                    tc_mma_f16_ts(tmem_base, at + 8 * k, bd + 2 * k, idesc, (uint32_t)((i | k) != 0));
+                const uint32_t at = a0 + 32u * (uint32_t)sa;
+                const uint64_t bd = bd0 + (uint64_t)(bd_step * (uint32_t)sb);
+                tc_mma_f16_ts(tmem_base, at, bd, idesc, acc);      // K = 16 per instruction: 8 TMEM columns of A, 32 bytes along B's swizzled row
+                tc_mma_f16_ts(tmem_base, at + 8, bd + 2, idesc, 1);
+                tc_mma_f16_ts(tmem_base, at + 16, bd + 4, idesc, 1);
+                tc_mma_f16_ts(tmem_base, at + 24, bd + 6, idesc, 1);
+                acc = 1;
                 tc_commit(a_empty + 8 * sa);
                 tc_commit(b_empty + 8 * sb);
+                trace(p, 5, i);
+                if (++sa == na) { sa = 0; pa ^= 1; }
+                if (++sb == nb) { sb = 0; pb ^= 1; }
             }
             tc_commit(tmem_full);
         }
     } else if (warp >= 4) {
         const int dw = warp - 4, h = dw >> 2, r = (dw & 3) * 32 + lane;
         const uint32_t lane_base = tmem_base + ((uint32_t)((dw & 3) * 32) << 16);      // this warp's TMEM lane quarter
+        const int na_shift = na == 8 ? 3 : 2;
         DQ q;
         auto block = [&](auto shift, int kb) {
             constexpr int S = decltype(shift)::value;
             const int s = kb & 1;
+            const bool tr = lane == 0 && (dw & 3) == 0;
+            if (tr) trace(p, 8 + 8 * h, kb);
             mbar_wait_b(raw_full + 8 * s, (kb >> 1) & 1);
+            if (tr) trace(p, 9 + 8 * h, kb);
             const uint32_t row = sR + s * RAW + r * DQ::PITCH;
             q.template prep<S>(row, h);
 #pragma unroll
             for (int t = 0; t < 2; ++t) {
-                const int i = 4 * kb + 2 * t + h, slot = i % na;
+                const int i = 4 * kb + 2 * t + h, slot = i & (na - 1);
                 uint32_t out[32];
                 q.emit(row, h, t, out);
-                mbar_wait_b(a_empty + 8 * slot, ((i / na) & 1) ^ 1);
+                if (tr) trace(p, 10 + 8 * h + 3 * t, kb);
+                mbar_wait_b(a_empty + 8 * slot, ((i >> na_shift) & 1) ^ 1);
+                if (tr) trace(p, 11 + 8 * h + 3 * t, kb);
                 tc_fence_after();
                 tmem_st32(lane_base + a_col0 + 32u * (uint32_t)slot, out);
                 tmem_st_wait();
                 tc_fence_before();
+                if (tr) trace(p, 12 + 8 * h + 3 * t, kb);
                 __syncwarp();
                 if (lane == 0) mbar_arrive(a_full + 8 * slot);
             }
@@ -484,6 +514,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
         // epilogue: TMEM lane = weight row (this warp's quarter), column = token; group h takes every other 32 columns
         mbar_wait_b(tmem_full, 0);
         tc_fence_after();
+        if (lane == 0 && dw == 0) trace(p, 6, 0);
         const int n = n0 + r;
         for (int c0 = h * 32; c0 < tn; c0 += 64) {
             uint32_t v[32];
@@ -500,6 +531,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
     }
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) trace(p, 7, 0);
     if (warp == 2) { tc_fence_after(); tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols); }
 }
 
@@ -595,6 +627,15 @@ extern "C" int b200_mul_mat_q_supported(int type, const void * W, int64_t nb1, i
     return encode_tiled() != nullptr;
 }
 
+static long long * g_mmq_trace = nullptr;
+extern "C" int b200_mmq_debug_trace(void * dev_buf) {
+#ifdef B200_MMQ_TRACE
+    g_mmq_trace = (long long *)dev_buf; return 24 * TRACE_N;
+#else
+    (void)dev_buf; return 0;      // compiled without -DB200_MMQ_TRACE
+#endif
+}
+
 extern "C" int64_t b200_mul_mat_q_scratch_bytes(int K, int M) { return (int64_t)K * M * 2 + 256; }
 
 extern "C" int b200_mul_mat_q(int type, const void * W, int64_t nb1, const float * X, int64_t xs, float * dst, int64_t ds,
@@ -620,6 +661,7 @@ extern "C" int b200_mul_mat_q(int type, const void * W, int64_t nb1, const float
     mmq_params p = {};
     p.dst = dst; p.ds = ds; p.N = N; p.M = M; p.K = K;
     p.tn = choose_tn(N, M);
+    p.trace = g_mmq_trace;
     p.nb = NB_MAX;
     while (p.nb > 2 && mmq_smem(type, p.tn, p.nb) > 232448) --p.nb;
     // tensor memory: accumulator columns + A ring; narrow tiles take half of it so that two CTAs can share an SM

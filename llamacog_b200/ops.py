@@ -50,7 +50,7 @@ EXPORTS = ["b200_mul_mat_vec_q_ex", "b200_mul_mat_vec_q", "b200_mmvq_supported_t
            "b200_op_get_rows", "b200_op_soft_max", "b200_op_argsort", "b200_op_sum_rows", "b200_op_flash_attn_ext",
            "b200_flash_attn_scratch_bytes", "b200_flash_attn_supported", "b200_op_mul_mat", "b200_mul_mat_scratch_bytes",
            "b200_mul_mat_supported", "b200_op_mul_mat_id", "b200_mul_mat_q", "b200_mul_mat_q_scratch_bytes",
-           "b200_mul_mat_q_supported"]
+           "b200_mul_mat_q_supported", "b200_mmq_debug_trace"]
 
 
 def _stream():

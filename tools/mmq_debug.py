@@ -85,6 +85,39 @@ def timing(name, N, K, M, iters=20):
     print("%-5s N=%5d K=%5d M=%4d tn=%s: %.3f ms  %.1f TFLOP/s" % (name, N, K, M, os.environ.get("B200_MMQ_TN", "auto"), ms, 2.0 * N * K * M / ms / 1e9))
 
 
+def trace(name, N, K, M):
+    """clock64 timeline of CTA (0,0): per 256-K block, when each role passed its waits (cycles since kernel start)."""
+    import ctypes as C
+    t = O.QUANT_TYPES[name]
+    rb = ops.row_bytes(t, K)
+    rng = np.random.default_rng(1)
+    one = O.random_quant_bytes(t, 128, K, rng).reshape(-1)
+    W = torch.from_numpy(np.tile(one, (N + 127) // 128)[: N * rb]).cuda()
+    W = torch.cat([W, torch.zeros(256, dtype=torch.uint8, device="cuda")])
+    X = torch.randn(M, K, device="cuda")
+    for _ in range(2):
+        ops.mul_mat_q(t, W, X, N, K)
+    n = ops.lib().b200_mmq_debug_trace(None)
+    buf = torch.zeros(n, dtype=torch.int64, device="cuda")
+    ops.lib().b200_mmq_debug_trace(C.c_void_p(buf.data_ptr()))
+    ops.mul_mat_q(t, W, X, N, K)
+    torch.cuda.synchronize()
+    ops.lib().b200_mmq_debug_trace(None)
+    T = buf.cpu().numpy().reshape(24, -1)
+    nkb = K // 256
+    t0 = T[0, 0]
+    rel = lambda v: int(v - t0) if v else -1
+    print("trace %s N=%d K=%d M=%d tn=%s  (cycles since first W issue)" % (name, N, K, M, os.environ.get("B200_MMQ_TN", "auto")))
+    print("kb | Wissue | g0: start rawfull emit0 aempty0 st0 emit1 aempty1 st1 | g1: start rawfull emit0 aempty0 st0 emit1 aempty1 st1")
+    for kb in range(min(nkb, 16)):
+        g = lambda h: " ".join("%6d" % rel(T[e + 8 * h, kb]) for e in (8, 9, 10, 11, 12, 13, 14, 15))
+        print("%2d | %6d | %s | %s" % (kb, rel(T[0, kb]), g(0), g(1)))
+    print("step | Xissue | mma: loop afull bfull issued")
+    for i in range(min(4 * nkb, 48)):
+        print("%3d | %6d | %6d %6d %6d %6d" % (i, rel(T[1, i]), rel(T[2, i]), rel(T[3, i]), rel(T[4, i]), rel(T[5, i])))
+    print("tmem_full seen %d, kernel end %d" % (rel(T[6, 0]), rel(T[7, 0])))
+
+
 def main():
     mode = sys.argv[1] if len(sys.argv) > 1 else "check"
     names = sys.argv[2:] or ["q4_K", "q6_K", "q5_K", "q4_0", "q8_0"]
@@ -100,6 +133,11 @@ def main():
             ok &= nmse_case(name, 1024, 2048, 512)
         print("ALL OK" if ok else "FAILURES")
         sys.exit(0 if ok else 1)
+    elif mode == "trace":
+        for name in names:
+            for tn in ("256", "128"):
+                os.environ["B200_MMQ_TN"] = tn
+                trace(name, 14336, 4096, 512)
     else:
         for name in names:
             for (N, K, M) in [(4096, 4096, 512), (14336, 4096, 512), (4096, 14336, 512), (4096, 4096, 128), (14336, 4096, 2048)]:
