@@ -171,6 +171,13 @@ int b200_mul_mat_q(int type, const void * W, int64_t nb1, const float * X, int64
                    int N, int K, int M, void * scratch, int64_t scratch_bytes, void * stream);
 int64_t b200_mul_mat_q_scratch_bytes(int K, int M);
 int b200_mul_mat_q_supported(int type, const void * W, int64_t nb1, int K);
+/* The two halves of b200_mul_mat_q, for callers that multiply several weight matrices by the same activations
+ * (q/k/v, gate/up): convert once (out: b200_acts_bf16_bytes(K, M) bytes, 128-byte aligned), then one
+ * b200_mul_mat_q_bf16 per weight matrix.  The reference quantises src1 once per MUL_MAT (ggml-cuda/mmq.cu:118-140). */
+int64_t b200_acts_bf16_bytes(int K, int M);
+int b200_convert_acts_bf16(const float * X, int64_t xs, void * out, int K, int M, void * stream);
+int b200_mul_mat_q_bf16(int type, const void * W, int64_t nb1, const void * Xb, float * dst, int64_t ds,
+                        int N, int K, int M, void * stream);
 /* debug hook: device buffer of (return value) int64 slots that CTA (0,0) of later b200_mul_mat_q launches fills with
  * clock64 stamps of its pipeline events (tools/mmq_debug.py trace); NULL switches it off. */
 int b200_mmq_debug_trace(void * dev_buf);

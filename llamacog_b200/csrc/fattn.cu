@@ -231,6 +231,10 @@ static int fa_launch(const fa_params & p, dim3 grid, cudaStream_t st) {
     return 0;
 }
 
+// tensor-core kernel for batches of query rows (fattn_tc.cu); returns 0 when the shape is not its to take
+int fattn_tc_try(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst,
+                 float scale, float max_bias, float logit_softcap, cudaStream_t st, int * rc);
+
 }  // namespace b200
 
 using namespace b200;
@@ -255,6 +259,10 @@ extern "C" int b200_op_flash_attn_ext(const b200_tensor * q, const b200_tensor *
     if (mask && (mask->type != T_F16 || mask->nb[0] != 2 || mask->ne[0] < k->ne[1])) return -1;
     if (k->type == T_F16 && ((((uintptr_t)k->data | k->nb[1] | k->nb[2] | k->nb[3]) & 15) || (((uintptr_t)v->data | v->nb[1] | v->nb[2] | v->nb[3]) & 7))) return -1;
     if (q->ne[1] == 0 || k->ne[1] == 0) return 0;
+    {
+        int rc = 0;
+        if (fattn_tc_try(q, k, v, mask, dst, scale, max_bias, logit_softcap, (cudaStream_t)stream, &rc)) return rc;
+    }
     fa_params p = {};
     p.q = (const char *)q->data; p.k = (const char *)k->data; p.v = (const char *)v->data; p.mask = mask ? (const char *)mask->data : nullptr;
     p.dst = (char *)dst->data;

@@ -14,7 +14,7 @@
 // (profiles/r01_mmq_notes.md).  Raw bytes are read from HBM exactly once per tile row.
 // Activations are converted f32 -> bf16 once per mat-mul by a small pre-pass (the reference quantises
 // them to q8_1 there instead, ggml-cuda/quantize.cu).
-#include "common.cuh"
+#include "tc.cuh"
 #include "../../include/b200_ops.h"
 
 #include <cuda.h>
@@ -25,80 +25,6 @@
 
 namespace b200 {
 
-// ------------------------------------------------------------------------------------------------
-// PTX wrappers: TMA tensor copies, tcgen05
-// ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap * map, int c0, int c1, uint32_t bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                 :: "r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap * map) {
-    asm volatile("prefetch.tensormap [%0];" :: "l"(map) : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(dst_smem), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void tmem_relinquish() { asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(taddr), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
-}
-// D[tmem] (+)= A[smem desc] * B[smem desc]
-__device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-                 :: "r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-// same with A read from tensor memory (lane = row, two bf16 per 32-bit column)
-__device__ __forceinline__ void tc_mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-                 :: "r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-// 32 consecutive 32-bit columns of this thread's TMEM lane
-__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-                 "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
-                 :: "r"(taddr),
-                    "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
-                    "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
-                    "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
-                    "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
-                 : "memory");
-}
-__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                 "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-                   "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                 : "r"(taddr) : "memory");
-}
-// bounded mbarrier wait: a pipeline bug traps (launch failure) instead of hanging the GPU
-__device__ __forceinline__ void mbar_wait_b(uint32_t bar, uint32_t parity) {
-    uint32_t done = 0;
-    for (uint32_t spins = 0; ; ++spins) {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
-                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-        if (done) return;
-        if (spins > (1u << 26)) __trap();
-    }
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" :: "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-__device__ __forceinline__ uint2 lds64(uint32_t saddr) {
-    uint2 v; asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(saddr)); return v;
-}
 __device__ __forceinline__ uint32_t fma_bf16x2(uint32_t a, uint32_t b, uint32_t c) {
     uint32_t d; asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
 }
@@ -110,16 +36,6 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     uint32_t d; asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo)); return d;
 }
 __device__ __forceinline__ float bf16lo_to_float(uint32_t packed) { return __uint_as_float(packed << 16); }
-
-// shared-memory matrix descriptor of a K-major bf16 tile stored with the 128-byte swizzle: rows of 64
-// elements (128 B), groups of 8 rows 1024 B apart
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
-    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
-}
-// instruction descriptor: D f32, A/B bf16, both K-major, M = 128, N = tn
-__device__ __forceinline__ uint32_t umma_idesc_bf16(int tn) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(tn >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-}
 
 // ------------------------------------------------------------------------------------------------
 // Dequantisers.  A dequantiser thread owns one weight row r of the tile and one half h of each 256-K
@@ -442,7 +358,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
         }
     } else if (warp == 1) {
         if (lane == 0) {                         // tensor-core issue: one thread, so every instruction between two MMAs counts
-            const uint32_t idesc = umma_idesc_bf16(tn);
+            const uint32_t idesc = umma_idesc(1, tn, 0);
             const uint32_t a0 = tmem_base + a_col0;
             const uint64_t bd0 = umma_desc_sw128(sB);
             const uint32_t bd_step = b_slot >> 4;
@@ -558,10 +474,7 @@ __global__ void __launch_bounds__(256) x_to_bf16_kernel(const float * __restrict
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
-typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
-                                    const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static encode_tiled_fn encode_tiled() {
+encode_tiled_fn encode_tiled() {
     static encode_tiled_fn fn = [] {
         void * p = nullptr; cudaDriverEntryPointQueryResult q;
         if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
@@ -638,25 +551,30 @@ extern "C" int b200_mmq_debug_trace(void * dev_buf) {
 
 extern "C" int64_t b200_mul_mat_q_scratch_bytes(int K, int M) { return (int64_t)K * M * 2 + 256; }
 
-extern "C" int b200_mul_mat_q(int type, const void * W, int64_t nb1, const float * X, int64_t xs, float * dst, int64_t ds,
-                              int N, int K, int M, void * scratch, int64_t scratch_bytes, void * stream) {
-    if (!b200_mul_mat_q_supported(type, W, nb1, K) || N <= 0 || M <= 0) return -1;
-    if (!scratch || scratch_bytes < b200_mul_mat_q_scratch_bytes(K, M)) return -2;
-    cudaStream_t st = (cudaStream_t)stream;
-    uint8_t * xb = (uint8_t *)(((uintptr_t)scratch + 127) & ~(uintptr_t)127);
+extern "C" int64_t b200_acts_bf16_bytes(int K, int M) { return (int64_t)K * M * 2; }
 
+// activations f32 [M][xs] -> bf16 [M][K] contiguous (out 128-byte aligned)
+extern "C" int b200_convert_acts_bf16(const float * X, int64_t xs, void * out, int K, int M, void * stream) {
+    if (K <= 0 || M <= 0 || K % 8 || ((uintptr_t)out & 127)) return -1;
     const int vec = (((uintptr_t)X & 15) == 0 && (xs & 3) == 0) ? 1 : 0;
-    {
-        const int64_t groups = (int64_t)M * (K / 8);
-        cudaLaunchConfig_t lc = {};
-        lc.gridDim = dim3((unsigned)((groups + 255) / 256)); lc.blockDim = dim3(256); lc.stream = st;
-        cudaLaunchAttribute at[1];
-        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        at[0].val.programmaticStreamSerializationAllowed = 1;
-        lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
-        B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, x_to_bf16_kernel, X, xs, (uint32_t *)xb, K, M, vec));
-        ++g_launches;
-    }
+    const int64_t groups = (int64_t)M * (K / 8);
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)((groups + 255) / 256)); lc.blockDim = dim3(256); lc.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+    B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, x_to_bf16_kernel, X, xs, (uint32_t *)out, K, M, vec));
+    ++g_launches;
+    return 0;
+}
+
+// dst = W x Xb^T with Xb the bf16 [M][K] activations made by b200_convert_acts_bf16
+extern "C" int b200_mul_mat_q_bf16(int type, const void * W, int64_t nb1, const void * Xb, float * dst, int64_t ds,
+                                   int N, int K, int M, void * stream) {
+    if (!b200_mul_mat_q_supported(type, W, nb1, K) || N <= 0 || M <= 0 || ((uintptr_t)Xb & 127)) return -1;
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t * xb = (uint8_t *)Xb;
 
     mmq_params p = {};
     p.dst = dst; p.ds = ds; p.N = N; p.M = M; p.K = K;
@@ -695,4 +613,14 @@ extern "C" int b200_mul_mat_q(int type, const void * W, int64_t nb1, const float
         case T_Q6_K: return mmq_launch<T_Q6_K>(wmap, xmap, p, smem, st);
     }
     return -1;
+}
+
+extern "C" int b200_mul_mat_q(int type, const void * W, int64_t nb1, const float * X, int64_t xs, float * dst, int64_t ds,
+                              int N, int K, int M, void * scratch, int64_t scratch_bytes, void * stream) {
+    if (!b200_mul_mat_q_supported(type, W, nb1, K) || N <= 0 || M <= 0) return -1;
+    if (!scratch || scratch_bytes < b200_mul_mat_q_scratch_bytes(K, M)) return -2;
+    uint8_t * xb = (uint8_t *)(((uintptr_t)scratch + 127) & ~(uintptr_t)127);
+    const int rc = b200_convert_acts_bf16(X, xs, xb, K, M, stream);
+    if (rc) return rc;
+    return b200_mul_mat_q_bf16(type, W, nb1, xb, dst, ds, N, K, M, stream);
 }

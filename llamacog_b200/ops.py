@@ -40,6 +40,8 @@ def lib():
             getattr(_lib, name).restype = C.c_int
         _lib.b200_quantized_acts_bytes.restype = C.c_int64
         _lib.b200_mul_mat_q_scratch_bytes.restype = C.c_int64
+        _lib.b200_acts_bf16_bytes.restype = C.c_int64
+        _lib.b200_flash_attn_scratch_bytes.restype = C.c_int64
     return _lib
 
 
@@ -50,7 +52,8 @@ EXPORTS = ["b200_mul_mat_vec_q_ex", "b200_mul_mat_vec_q", "b200_mmvq_supported_t
            "b200_op_get_rows", "b200_op_soft_max", "b200_op_argsort", "b200_op_sum_rows", "b200_op_flash_attn_ext",
            "b200_flash_attn_scratch_bytes", "b200_flash_attn_supported", "b200_op_mul_mat", "b200_mul_mat_scratch_bytes",
            "b200_mul_mat_supported", "b200_op_mul_mat_id", "b200_mul_mat_q", "b200_mul_mat_q_scratch_bytes",
-           "b200_mul_mat_q_supported", "b200_mmq_debug_trace"]
+           "b200_mul_mat_q_supported", "b200_mmq_debug_trace", "b200_acts_bf16_bytes",
+           "b200_convert_acts_bf16", "b200_mul_mat_q_bf16"]
 
 
 def _stream():
@@ -131,3 +134,41 @@ def dequantize_rows(t, W, nrows, k, out_dtype=torch.float32):
 
 def kernel_launch_count():
     return lib().b200_kernel_launch_count()
+
+
+class B200Tensor(C.Structure):
+    """b200_tensor of include/b200_ops.h: data pointer, ggml type id, ne[4], nb[4] (bytes)."""
+    _fields_ = [("data", C.c_void_p), ("type", C.c_int), ("ne", C.c_int64 * 4), ("nb", C.c_int64 * 4)]
+
+
+_GGML_OF = {torch.float32: 0, torch.float16: 1, torch.int32: 26, torch.bfloat16: 30}
+
+
+def as_b200(t):
+    """A torch tensor (up to 4-D, torch order = ggml order reversed) as a b200_tensor view."""
+    assert t.is_cuda and t.dim() <= 4
+    shape = list(t.shape)[::-1] + [1] * (4 - t.dim())
+    es = t.element_size()
+    strides = [s * es for s in list(t.stride())[::-1]]
+    while len(strides) < 4:
+        strides.append(strides[-1] * shape[len(strides) - 1])
+    r = B200Tensor()
+    r.data = t.data_ptr(); r.type = _GGML_OF[t.dtype]
+    for i in range(4):
+        r.ne[i] = shape[i]; r.nb[i] = strides[i]
+    return r
+
+
+def flash_attn_ext(q, k, v, mask=None, scale=1.0, max_bias=0.0, logit_softcap=0.0):
+    """GGML_OP_FLASH_ATTN_EXT.  q: f32 [ne3, n_head, N, D]; k, v: f16 [ne3, n_head_kv, n_kv, D]; mask: f16 [N_pad, n_kv_pad] or
+    None.  Returns f32 [ne3, N, n_head, D] (the op's output layout)."""
+    ne3, n_head, N, D = q.shape
+    dst = torch.empty((ne3, N, n_head, D), dtype=torch.float32, device=q.device)
+    tq, tk, tv, td = as_b200(q), as_b200(k), as_b200(v), as_b200(dst)
+    tm = as_b200(mask) if mask is not None else None
+    need = lib().b200_flash_attn_scratch_bytes(C.byref(tq), C.byref(tk))
+    scratch = torch.empty(max(int(need), 16), dtype=torch.uint8, device=q.device)
+    _check(lib().b200_op_flash_attn_ext(C.byref(tq), C.byref(tk), C.byref(tv), C.byref(tm) if tm is not None else None, C.byref(td),
+                                        C.c_float(scale), C.c_float(max_bias), C.c_float(logit_softcap),
+                                        C.c_void_p(scratch.data_ptr()), C.c_int64(scratch.numel()), _stream()), "b200_op_flash_attn_ext")
+    return dst
