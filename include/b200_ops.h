@@ -134,6 +134,10 @@ int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, const b200_te
  * KV-cache store; bit-exact to quantize_row_q8_0_ref, ggml-quants.c:191-212); same-type block copies of quantised
  * data.  Replaces ggml_cuda_cpy (ggml-cuda/cpy.cu:303-). */
 int b200_op_cpy(const b200_tensor * src, const b200_tensor * dst, void * stream);
+/* same, with the destination base address read on the device from *dst_slot when the kernel runs (dst->data is ignored):
+ * lets a captured CUDA graph of a decode step be replayed while the KV-cache cell it writes moves (the reference's
+ * ggml_cuda_cpy_dest_ptrs_copy indirection, ggml-cuda/cpy.cu:360-372,591-612, ggml-cuda.cu:2502-2564). */
+int b200_op_cpy_indirect(const b200_tensor * src, const b200_tensor * dst, void * const * dst_slot, void * stream);
 int b200_op_cpy_supported(int src_type, int dst_type);
 /* dst[:, i] = dequant(src[:, ids[i]]), dst f32.  Replaces ggml_cuda_op_get_rows (ggml-cuda/getrows.cu:42-). */
 int b200_op_get_rows(const b200_tensor * src, const b200_tensor * ids, const b200_tensor * dst, void * stream);
@@ -188,6 +192,8 @@ int b200_op_mul_mat_id(const b200_tensor * as, const b200_tensor * b, const b200
 
 /* number of kernels launched by this library so far in this process (bench.py gpu_launches) */
 int b200_kernel_launch_count(void);
+/* account for kernels launched through a replayed CUDA graph (the plugin captures decode steps) */
+int b200_kernel_launch_add(int n);
 
 #ifdef __cplusplus
 }

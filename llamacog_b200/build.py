@@ -84,9 +84,26 @@ def build_plugin():
     return PLUGIN_LIB
 
 
+HOST_TEST = os.path.join(ROOT, "tests", "host", "build", "logits_check")
+
+
+def build_host_tests():
+    """tests/host/logits_check: libllama harness for the end-to-end logits parity test (needs the reference headers)."""
+    src = os.path.join(ROOT, "tests", "host", "logits_check.cpp")
+    if not os.path.isdir(os.path.join(REF, "include")):
+        return HOST_TEST if os.path.exists(HOST_TEST) else None
+    if _newer([src], HOST_TEST):
+        os.makedirs(os.path.dirname(HOST_TEST), exist_ok=True)
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-I", os.path.join(REF, "include"), "-I", os.path.join(REF, "ggml", "include"),
+                               src, "-o", HOST_TEST, "-L", os.path.join(HOST, "lib"), "-lllama", "-lggml", "-lggml-base",
+                               "-Wl,-rpath,$ORIGIN/../../../baseline/_ref/lib"])
+    return HOST_TEST
+
+
 def build_all(verbose=False):
     build_ops(verbose)
     build_plugin()
+    build_host_tests()
 
 
 if __name__ == "__main__":

@@ -218,15 +218,17 @@ __device__ __forceinline__ int64_t flat_off(const tens & t, int64_t i) {
     return i0 * t.nb[0] + i1 * t.nb[1] + (r2 % t.ne[2]) * t.nb[2] + (r2 / t.ne[2]) * t.nb[3];
 }
 template <typename S, typename D>
-__global__ void __launch_bounds__(256) cpy_kernel(const tens src, const tens dst, int64_t n) {
+__global__ void __launch_bounds__(256) cpy_kernel(const tens src, const tens dst, int64_t n, char * const * dslot) {
     pdl_enter();
+    char * dd = dslot ? *dslot : dst.d;          // CUDA-graph replay: the destination (KV cache cell) comes from a pointer table
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-        *(D *)(dst.d + flat_off(dst, i)) = from_f32<D>(to_f32<S>(*(const S *)(src.d + flat_off(src, i))));
+        *(D *)(dd + flat_off(dst, i)) = from_f32<D>(to_f32<S>(*(const S *)(src.d + flat_off(src, i))));
 }
 // f32 -> q8_0 blocks: one warp per block of 32 consecutive source elements (the same flat order);
 // arithmetic of quantize_row_q8_0_ref (ggml-quants.c:191-212): d = amax/127, id = 1/d, q = roundf(x*id)
-__global__ void __launch_bounds__(256) cpy_f32_q8_0_kernel(const tens src, const tens dst, int64_t nblocks) {
+__global__ void __launch_bounds__(256) cpy_f32_q8_0_kernel(const tens src, const tens dst, int64_t nblocks, char * const * dslot) {
     pdl_enter();
+    char * dd = dslot ? *dslot : dst.d;
     const int lane = threadIdx.x & 31;
     for (int64_t b = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < nblocks; b += ((int64_t)gridDim.x * blockDim.x) >> 5) {
         const float x = *(const float *)(src.d + flat_off(src, b * 32 + lane));
@@ -237,21 +239,22 @@ __global__ void __launch_bounds__(256) cpy_f32_q8_0_kernel(const tens src, const
         // destination block: dst is laid out in blocks along ne[0]
         const int64_t bpr = dst.ne[0] / 32, i0 = b % bpr, r = b / bpr;
         const int64_t i1 = r % dst.ne[1], r2 = r / dst.ne[1];
-        uint8_t * blk = (uint8_t *)(dst.d + i0 * dst.nb[0] + i1 * dst.nb[1] + (r2 % dst.ne[2]) * dst.nb[2] + (r2 / dst.ne[2]) * dst.nb[3]);
+        uint8_t * blk = (uint8_t *)(dd + i0 * dst.nb[0] + i1 * dst.nb[1] + (r2 % dst.ne[2]) * dst.nb[2] + (r2 / dst.ne[2]) * dst.nb[3]);
         blk[2 + lane] = (uint8_t)(int8_t)q;
         if (lane == 0) *reinterpret_cast<__half *>(blk) = __float2half_rn(d);
     }
 }
 // same-type copy of block data (quantised or not) between strided tensors of identical shape
-__global__ void __launch_bounds__(256) cpy_blocks_kernel(const tens src, const tens dst, int64_t nblocks, int bb, int be) {
+__global__ void __launch_bounds__(256) cpy_blocks_kernel(const tens src, const tens dst, int64_t nblocks, int bb, int be, char * const * dslot) {
     pdl_enter();
+    char * dd = dslot ? *dslot : dst.d;
     for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < nblocks; b += (int64_t)gridDim.x * blockDim.x) {
         const int64_t bps = src.ne[0] / be, s0 = b % bps, sr = b / bps;
         const int64_t s1 = sr % src.ne[1], sr2 = sr / src.ne[1];
         const char * sp = src.d + s0 * src.nb[0] + s1 * src.nb[1] + (sr2 % src.ne[2]) * src.nb[2] + (sr2 / src.ne[2]) * src.nb[3];
         const int64_t bpd = dst.ne[0] / be, d0 = b % bpd, dr = b / bpd;
         const int64_t d1 = dr % dst.ne[1], dr2 = dr / dst.ne[1];
-        char * dp = dst.d + d0 * dst.nb[0] + d1 * dst.nb[1] + (dr2 % dst.ne[2]) * dst.nb[2] + (dr2 / dst.ne[2]) * dst.nb[3];
+        char * dp = dd + d0 * dst.nb[0] + d1 * dst.nb[1] + (dr2 % dst.ne[2]) * dst.nb[2] + (dr2 / dst.ne[2]) * dst.nb[3];
         for (int k = 0; k < bb; k += 2) *(uint16_t *)(dp + k) = *(const uint16_t *)(sp + k);
     }
 }
@@ -370,13 +373,15 @@ extern "C" int b200_op_cpy_supported(int s, int d) {
     return 0;
 }
 
-#define B200_CPY_CASE(ST, SC, DT, DC) if (src->type == ST && dst->type == DT) return launch(cpy_kernel<SC, DC>, grid_for(n, 256), 256, 0, st, mk(src), mk(dst), n);
-extern "C" int b200_op_cpy(const b200_tensor * src, const b200_tensor * dst, void * stream) {
+#define B200_CPY_CASE(ST, SC, DT, DC) if (src->type == ST && dst->type == DT) return launch(cpy_kernel<SC, DC>, grid_for(n, 256), 256, 0, st, mk(src), mk(dst), n, dslot);
+extern "C" int b200_op_cpy(const b200_tensor * src, const b200_tensor * dst, void * stream) { return b200_op_cpy_indirect(src, dst, nullptr, stream); }
+extern "C" int b200_op_cpy_indirect(const b200_tensor * src, const b200_tensor * dst, void * const * dst_slot, void * stream) {
     if (!b200_op_cpy_supported(src->type, dst->type) || nelem(src) != nelem(dst)) return -1;
     cudaStream_t st = (cudaStream_t)stream;
+    char * const * dslot = (char * const *)dst_slot;
     const int64_t n = nelem(src);
     if (n == 0) return 0;
-    if (src->type == dst->type && is_contig(src) && is_contig(dst)) {
+    if (!dslot && src->type == dst->type && is_contig(src) && is_contig(dst)) {
         const size_t bytes = (size_t)(n / block_elems(src->type)) * block_bytes(src->type);
         B200_CUDA_CHECK(cudaMemcpyAsync(dst->data, src->data, bytes, cudaMemcpyDeviceToDevice, st));
         return 0;
@@ -384,12 +389,12 @@ extern "C" int b200_op_cpy(const b200_tensor * src, const b200_tensor * dst, voi
     if (src->type == T_F32 && dst->type == T_Q8_0) {
         if (src->ne[0] % 32 || dst->ne[0] % 32) return -1;
         const int64_t nb = n / 32;
-        return launch(cpy_f32_q8_0_kernel, grid_for(nb, 8), 256, 0, st, mk(src), mk(dst), nb);
+        return launch(cpy_f32_q8_0_kernel, grid_for(nb, 8), 256, 0, st, mk(src), mk(dst), nb, dslot);
     }
     if (src->type == dst->type && block_elems(src->type) > 1) {
         const int be = block_elems(src->type);
         if (src->ne[0] % be || dst->ne[0] % be) return -1;
-        return launch(cpy_blocks_kernel, grid_for(n / be, 256), 256, 0, st, mk(src), mk(dst), n / be, block_bytes(src->type), be);
+        return launch(cpy_blocks_kernel, grid_for(n / be, 256), 256, 0, st, mk(src), mk(dst), n / be, block_bytes(src->type), be, dslot);
     }
     B200_CPY_CASE(T_F32, float, T_F32, float) B200_CPY_CASE(T_F32, float, T_F16, __half) B200_CPY_CASE(T_F32, float, B200_TYPE_BF16, __nv_bfloat16)
     B200_CPY_CASE(T_F16, __half, T_F32, float) B200_CPY_CASE(T_F16, __half, T_F16, __half) B200_CPY_CASE(T_F16, __half, B200_TYPE_BF16, __nv_bfloat16)

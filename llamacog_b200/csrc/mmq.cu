@@ -44,18 +44,26 @@ __device__ __forceinline__ float bf16lo_to_float(uint32_t packed) { return __uin
 // one tcgen05.st writes to the 32 columns of the thread's TMEM lane.
 //
 // Integer codes become bf16 without conversions: a byte 0x80|(q << s) under a 0x3F high byte is the
-// bf16 value 1 + q/2^(7-s), so  w = q*scale - offset  is one packed fma  x*S + B  with S = 2^(7-s)*scale
-// and B = -(S + offset); S is rounded to bf16 first and B is computed from the rounded S, so q = 0 maps
-// to -offset up to one bf16 rounding.  (Values follow dequantize_row_*, reference ggml-quants.c; the
-// result is rounded to bf16 -- the op's parity bar is NMSE <= 5e-4, tests/test-backend-ops.cpp.)
+// bf16 value 1 + q/2^n (n = 7-s).  Subtracting 1.5 is exact and centres the code, (q - 2^(n-1))/2^n, so
+//   w = q*scale - offset = ((1 + q/2^n) - 1.5) * S + C,   S = 2^n*scale,  C = S/2 - offset
+// costs one packed add and one packed fma per two weights; formats without an offset (Q6_K, Q4_0: the
+// centring IS their zero point) need only a multiply.  S and C are rounded to bf16 once per sub-block and
+// C is computed from the rounded S.  (Values follow dequantize_row_*, reference ggml-quants.c; the result
+// is rounded to bf16 -- the op's parity bar is NMSE <= 5e-4, tests/test-backend-ops.cpp.)
 // ------------------------------------------------------------------------------------------------
 #define PRMT_01 0x4140u   // {b0, 0x3F, b1, 0x3F}
 #define PRMT_23 0x4342u   // {b2, 0x3F, b3, 0x3F}
 
-// four code bytes (already shifted, 0x80 set) -> two packed bf16 pairs, scaled
-__device__ __forceinline__ void expand4(uint32_t codes, uint32_t s2, uint32_t b2, uint32_t & o01, uint32_t & o23) {
-    o01 = fma_bf16x2(__byte_perm(codes, 0x3F3F3F3Fu, PRMT_01), s2, b2);
-    o23 = fma_bf16x2(__byte_perm(codes, 0x3F3F3F3Fu, PRMT_23), s2, b2);
+// four code bytes (already shifted, 0x80 set) -> two packed bf16 pairs:  ((1 + q/2^n) - 1.5) * S + C.  The subtraction is exact
+// (it centres the code: (q - 2^(n-1)) / 2^n), so the only roundings are those of S, C and the result; C = S/2 - offset is small
+// for the roughly symmetric blocks a quantiser produces, which keeps its rounding error far below one code step.
+__device__ __forceinline__ void expand4(uint32_t codes, uint32_t s2, uint32_t c2, uint32_t & o01, uint32_t & o23) {
+    constexpr uint32_t M15 = 0xBFC0BFC0u;      // {-1.5, -1.5} bf16
+    uint32_t a, b;
+    asm("add.rn.bf16x2 %0, %1, %2;" : "=r"(a) : "r"(__byte_perm(codes, 0x3F3F3F3Fu, PRMT_01)), "r"(M15));
+    asm("add.rn.bf16x2 %0, %1, %2;" : "=r"(b) : "r"(__byte_perm(codes, 0x3F3F3F3Fu, PRMT_23)), "r"(M15));
+    o01 = fma_bf16x2(a, s2, c2);
+    o23 = fma_bf16x2(b, s2, c2);
 }
 // symmetric formats (no per-block minimum): remove the code offset exactly first ((1 + q/2^n) - off is exact in bf16),
 // then one multiply -- a single rounding per weight
@@ -70,10 +78,10 @@ __device__ __forceinline__ void expand4_sym(uint32_t codes, uint32_t s2, uint32_
     o01 = mul_bf16x2(add_bf16x2(__byte_perm(codes, 0x3F3F3F3Fu, PRMT_01), M15), s2);
     o23 = mul_bf16x2(add_bf16x2(__byte_perm(codes, 0x3F3F3F3Fu, PRMT_23), M15), s2);
 }
-// scale pair from S (float): s2 = {S,S} bf16, b2 = {-(Sr*bm + off)} with Sr the rounded S
-__device__ __forceinline__ void make_sb(float S, float bm, float off, uint32_t & s2, uint32_t & b2) {
+// scale pair from S (float): s2 = {S,S} bf16, c2 = {Sr/2 - off} with Sr the rounded S
+__device__ __forceinline__ void make_sb(float S, float off, uint32_t & s2, uint32_t & c2) {
     s2 = pack_bf16_dup(S);
-    b2 = pack_bf16_dup(-fmaf(bf16lo_to_float(s2), bm, off));
+    c2 = pack_bf16_dup(fmaf(bf16lo_to_float(s2), 0.5f, -off));
 }
 __device__ __forceinline__ float ubyte_f(uint32_t w, int i) { return (float)((w >> (8 * i)) & 0xFFu); }
 
@@ -92,7 +100,7 @@ template <> struct dq<T_Q4_K> {
         if (h == 0) { SC = hd.y & 0x3F3F3F3Fu; MN = hd.z & 0x3F3F3F3Fu; }
         else { SC = (hd.w & 0x0F0F0F0Fu) | (((uint32_t)hd.y >> 2) & 0x30303030u); MN = (((uint32_t)hd.w >> 4) & 0x0F0F0F0Fu) | (((uint32_t)hd.z >> 2) & 0x30303030u); }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) make_sb(16.0f * d * ubyte_f(SC, j), 1.0f, dmin * ubyte_f(MN, j), s2[j], b2[j]);
+        for (int j = 0; j < 4; ++j) make_sb(16.0f * d * ubyte_f(SC, j), dmin * ubyte_f(MN, j), s2[j], b2[j]);
     }
     __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t (&out)[32]) const {
         const uint32_t qs = row + 16 + 32 * (2 * h + t);
@@ -126,7 +134,7 @@ template <> struct dq<T_Q5_K> {
         if (h == 0) { SC = hd.y & 0x3F3F3F3Fu; MN = hd.z & 0x3F3F3F3Fu; }
         else { SC = (hd.w & 0x0F0F0F0Fu) | (((uint32_t)hd.y >> 2) & 0x30303030u); MN = (((uint32_t)hd.w >> 4) & 0x0F0F0F0Fu) | (((uint32_t)hd.z >> 2) & 0x30303030u); }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) make_sb(32.0f * d * ubyte_f(SC, j), 1.0f, dmin * ubyte_f(MN, j), s2[j], b2[j]);
+        for (int j = 0; j < 4; ++j) make_sb(32.0f * d * ubyte_f(SC, j), dmin * ubyte_f(MN, j), s2[j], b2[j]);
         const int4 a = lds128(row + 16), b = lds128(row + 32);
         const int sh = 4 * h;              // this half's four sub-block bits move to bits 0..3
         qh[0] = (uint32_t)a.x >> sh; qh[1] = (uint32_t)a.y >> sh; qh[2] = (uint32_t)a.z >> sh; qh[3] = (uint32_t)a.w >> sh;

@@ -142,6 +142,7 @@ extern "C" int b200_mmvq_supported_type(int type) {
 }
 
 extern "C" int b200_kernel_launch_count(void) { return g_launches; }
+extern "C" int b200_kernel_launch_add(int n) { g_launches += n; return g_launches; }
 
 extern "C" int b200_mul_mat_vec_q_ex(const b200_mmvq_args * a, void * stream) {
     if (!a || !b200_mmvq_supported_type(a->type)) return -1;
