@@ -238,6 +238,38 @@ __device__ __forceinline__ int q8_round(float x, float d, float inv, bool exact_
     return __float_as_int(fm) - 0x4B400000;
 }
 
+// One 32-block held by 8 consecutive lanes (lane `sub` of the group has elements 4*sub..4*sub+3): quantise it with q8_1
+// arithmetic and store it as block jb of the activation layout at `am` (see ACT_ITEM / ACT_BLK).  All 8 lanes must call.
+__device__ __forceinline__ void quant_block_store(const float4 x, int jb, int sub, bool in_range, uint8_t * am) {
+    float amax = fmaxf(fmaxf(fabsf(x.x), fabsf(x.y)), fmaxf(fabsf(x.z), fabsf(x.w)));
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    const float d = __fdiv_rn(amax, 127.0f);
+    int q0 = 0, q1 = 0, q2 = 0, q3 = 0;
+    if (amax != 0.0f) {
+        const bool tiny = amax < 1e-20f;
+        float inv; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(d));
+        q0 = q8_round(x.x, d, inv, tiny); q1 = q8_round(x.y, d, inv, tiny);
+        q2 = q8_round(x.z, d, inv, tiny); q3 = q8_round(x.w, d, inv, tiny);
+    }
+    const int word = (int)__byte_perm(__byte_perm(q0, q1, 0x0040), __byte_perm(q2, q3, 0x0040), 0x5410);
+    int s = __dp4a(word, 0x01010101, 0);
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);          // sum of 16 elements (lanes 0-3 / 4-7)
+    const int s16 = s;
+    s += __shfl_xor_sync(0xffffffffu, s, 4);          // sum of the 32-block
+    const int s16b = __shfl_down_sync(0xffffffffu, s16, 4);
+    if (in_range) {
+        uint8_t * blk = am + (size_t)(jb >> 3) * ACT_ITEM + (jb & 7) * ACT_BLK;
+        reinterpret_cast<int *>(blk)[sub] = word;
+        if (sub == 0) {
+            const float d8 = __half2float(__float2half_rn(d));   // q8_1 stores d as binary16 (quantize.cu:47)
+            int4 t; t.x = __float_as_int(d8); t.y = __float_as_int(d8 * (float)s); t.z = -32 * s16; t.w = -32 * s16b;
+            *reinterpret_cast<int4 *>(blk + 32) = t;
+        }
+    }
+}
+
 // Eight lanes per 32-block (a float4 each); nthreads threads (a multiple of 32) cooperate.  Must be
 // called by all of them.  nb32 = K/32 blocks per column.
 __device__ __forceinline__ void quantize_acts(const float * __restrict__ X, int64_t xs, int M, int nb32, bool vec_ok,
@@ -262,34 +294,7 @@ __device__ __forceinline__ void quantize_acts(const float * __restrict__ X, int6
 #pragma unroll
             for (int u = 0; u < UN; ++u) {
                 const int jb = base + u * ngrp + grp;         // uniform across the 8 lanes of a group
-                const float4 x = xv[u];
-                float amax = fmaxf(fmaxf(fabsf(x.x), fabsf(x.y)), fmaxf(fabsf(x.z), fabsf(x.w)));
-#pragma unroll
-                for (int o = 1; o < 8; o <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-                const float d = __fdiv_rn(amax, 127.0f);
-                int q0 = 0, q1 = 0, q2 = 0, q3 = 0;
-                if (amax != 0.0f) {
-                    const bool tiny = amax < 1e-20f;
-                    float inv; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(d));
-                    q0 = q8_round(x.x, d, inv, tiny); q1 = q8_round(x.y, d, inv, tiny);
-                    q2 = q8_round(x.z, d, inv, tiny); q3 = q8_round(x.w, d, inv, tiny);
-                }
-                const int word = (int)__byte_perm(__byte_perm(q0, q1, 0x0040), __byte_perm(q2, q3, 0x0040), 0x5410);
-                int s = __dp4a(word, 0x01010101, 0);
-                s += __shfl_xor_sync(0xffffffffu, s, 1);
-                s += __shfl_xor_sync(0xffffffffu, s, 2);          // sum of 16 elements (lanes 0-3 / 4-7)
-                const int s16 = s;
-                s += __shfl_xor_sync(0xffffffffu, s, 4);          // sum of the 32-block
-                const int s16b = __shfl_down_sync(0xffffffffu, s16, 4);
-                if (jb < nb32) {
-                    uint8_t * blk = am + (size_t)(jb >> 3) * ACT_ITEM + (jb & 7) * ACT_BLK;
-                    reinterpret_cast<int *>(blk)[sub] = word;
-                    if (sub == 0) {
-                        const float d8 = __half2float(__float2half_rn(d));   // q8_1 stores d as binary16 (quantize.cu:47)
-                        int4 t; t.x = __float_as_int(d8); t.y = __float_as_int(d8 * (float)s); t.z = -32 * s16; t.w = -32 * s16b;
-                        *reinterpret_cast<int4 *>(blk + 32) = t;
-                    }
-                }
+                quant_block_store(xv[u], jb, sub, jb < nb32, am);
             }
         }
     }

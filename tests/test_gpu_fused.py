@@ -1,0 +1,83 @@
+"""GPU parity of the decode-step fusions (fused.cu) through the C ABI: every output of a fused launch must be bit-identical
+to the outputs of the separate operators it replaces (b200_op_binary / rms_norm / unary / quantize_acts), which are themselves
+checked against the reference by test-backend-ops and the oracle."""
+import ctypes as C
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ops():
+    from llamacog_b200 import ops
+    return ops
+
+
+def _st(ops):
+    return ops._stream()
+
+
+def _same_acts(q, q_ref):
+    """the activation layout is 400 bytes per 256 values, of which the last 16 are padding"""
+    M = q.shape[0]
+    return torch.equal(q.view(M, -1, 400)[:, :, :384], q_ref.view(M, -1, 400)[:, :, :384])
+
+
+@pytest.mark.parametrize("M", [1, 3, 8])
+@pytest.mark.parametrize("K", [256, 2048, 4096, 8192, 14336])
+@pytest.mark.parametrize("with_add", [False, True])
+def test_add_rms_norm_mul_matches_separate_ops(M, K, with_add):
+    ops = _ops(); L = ops.lib()
+    torch.manual_seed(K + M)
+    a = torch.randn(M, K, device="cuda"); b = torch.randn(M, K, device="cuda"); w = torch.randn(K, device="cuda")
+    eps = 1e-5
+    # separate operators
+    s_ref = torch.empty_like(a); n_ref = torch.empty_like(a); o_ref = torch.empty_like(a)
+    x = a
+    if with_add:
+        assert L.b200_op_binary(C.c_int(0), C.byref(ops.as_b200(a)), C.byref(ops.as_b200(b)), C.byref(ops.as_b200(s_ref)), _st(ops)) == 0
+        x = s_ref
+    assert L.b200_op_rms_norm(C.byref(ops.as_b200(x)), C.byref(ops.as_b200(n_ref)), C.c_float(eps), _st(ops)) == 0
+    assert L.b200_op_binary(C.c_int(2), C.byref(ops.as_b200(n_ref)), C.byref(ops.as_b200(w)), C.byref(ops.as_b200(o_ref)), _st(ops)) == 0
+    q_ref = ops.quantize_acts(o_ref)
+    # fused
+    s = torch.empty_like(a); n = torch.empty_like(a); o = torch.empty_like(a); q = torch.zeros_like(q_ref)
+    rc = L.b200_op_add_rms_norm_mul(C.byref(ops.as_b200(a)), C.byref(ops.as_b200(b)) if with_add else None,
+                                    C.byref(ops.as_b200(s)) if with_add else None, C.byref(ops.as_b200(n)), C.byref(ops.as_b200(w)),
+                                    C.byref(ops.as_b200(o)), C.c_float(eps), C.c_void_p(q.data_ptr()), _st(ops))
+    assert rc == 0
+    torch.cuda.synchronize()
+    if with_add:
+        assert torch.equal(s, s_ref)
+    assert torch.equal(n, n_ref) and torch.equal(o, o_ref)
+    assert _same_acts(q, q_ref)
+    # and against plain PyTorch fp32 (tolerance: fp32 summation order of the mean square)
+    xx = (a + b) if with_add else a
+    want = xx * torch.rsqrt((xx.double() ** 2).mean(dim=1, keepdim=True).float() + eps) * w
+    assert torch.allclose(o, want, rtol=2e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("M", [1, 5, 8])
+@pytest.mark.parametrize("K", [512, 14336, 28672])
+def test_silu_mul_matches_separate_ops(M, K):
+    ops = _ops(); L = ops.lib()
+    torch.manual_seed(K * 3 + M)
+    g = torch.randn(M, K, device="cuda") * 3; u = torch.randn(M, K, device="cuda")
+    a_ref = torch.empty_like(g); o_ref = torch.empty_like(g)
+    assert L.b200_op_unary(C.c_int(10), C.byref(ops.as_b200(g)), C.byref(ops.as_b200(a_ref)), _st(ops)) == 0      # GGML_UNARY_OP_SILU
+    assert L.b200_op_binary(C.c_int(2), C.byref(ops.as_b200(a_ref)), C.byref(ops.as_b200(u)), C.byref(ops.as_b200(o_ref)), _st(ops)) == 0
+    q_ref = ops.quantize_acts(o_ref)
+    a = torch.empty_like(g); o = torch.empty_like(g); q = torch.zeros_like(q_ref)
+    assert L.b200_op_unary_mul(C.c_int(10), C.byref(ops.as_b200(g)), C.byref(ops.as_b200(a)), C.byref(ops.as_b200(u)), C.byref(ops.as_b200(o)),
+                               C.c_void_p(q.data_ptr()), _st(ops)) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(a, a_ref) and torch.equal(o, o_ref) and _same_acts(q, q_ref)
+    assert torch.allclose(o, torch.nn.functional.silu(g) * u, rtol=1e-5, atol=1e-6)
+
+
+def test_shapes_the_fusion_does_not_take_are_refused():
+    ops = _ops(); L = ops.lib()
+    a = torch.randn(9, 256, device="cuda"); w = torch.randn(256, device="cuda"); n = torch.empty_like(a); o = torch.empty_like(a)
+    assert L.b200_op_add_rms_norm_mul(C.byref(ops.as_b200(a)), None, None, C.byref(ops.as_b200(n)), C.byref(ops.as_b200(w)),
+                                      C.byref(ops.as_b200(o)), C.c_float(1e-5), None, _st(ops)) == -1       # more than 8 rows
