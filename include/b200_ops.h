@@ -70,6 +70,11 @@ typedef struct b200_mmvq_args {
 int b200_mul_mat_vec_q_ex(const b200_mmvq_args * args, void * stream);
 int b200_mul_mat_vec_q(int type, const void * W, int64_t nb1, const float * X, int64_t xs,
                        float * dst, int64_t ds, int N, int K, int M, void * stream);
+/* ng <= 3 weight matrices of one type, K and row stride times the same activations (args: type, nb1, X / Xq, xs, K, M <= 8, pdl)
+ * in ONE launch: matrix g has N[g] rows at W[g] and writes dst[g][m*ds[g] + n].  The q/k/v and gate/up projections of a decode
+ * step (the reference launches them separately: one mul_mat_vec_q per MUL_MAT node, ggml-cuda/mmvq.cu:491-561). */
+int b200_mul_mat_vec_q_group(const b200_mmvq_args * args, int ng, const void * const * W, float * const * dst, const int * N,
+                             const int64_t * ds, void * stream);
 int b200_mmvq_supported_type(int type);
 
 /* ---- activation quantisation as a stand-alone op ---------------------------------------------
@@ -200,6 +205,20 @@ int b200_op_add_rms_norm_mul(const b200_tensor * a, const b200_tensor * b, const
                              const b200_tensor * w, const b200_tensor * out, float eps, void * xq, void * stream);
 int b200_op_unary_mul(int op, const b200_tensor * g, const b200_tensor * act, const b200_tensor * u, const b200_tensor * out,
                       void * xq, void * stream);
+
+/* Up to 4 rope / KV-store nodes of a decode step in one launch.
+ *   kind 0: dst = rope(src)          kind 1: dst = rope(src) and dst2 = cpy(dst)  (the K row going into the cache)
+ *   kind 2: dst2 = cpy(src)           (the V row going into the cache);  src, dst f32; dst2 f32 / f16 / bf16
+ * dst2_slot (optional): device address of a pointer that replaces dst2->data when the kernel runs (see b200_op_cpy_indirect).
+ * Outputs are bit-identical to b200_op_rope followed by b200_op_cpy. */
+typedef struct b200_ew_desc {
+    int kind;
+    const b200_tensor * src, * dst, * dst2, * pos, * ffac;
+    const b200_rope_params * rope;
+    void * const * dst2_slot;
+} b200_ew_desc;
+int b200_op_rope_cpy_batch(const b200_ew_desc * tasks, int n, void * stream);
+int b200_op_rope_cpy_batch_check(const b200_ew_desc * tasks, int n);      /* 0 when the batch would be accepted; launches nothing */
 
 /* number of kernels launched by this library so far in this process (bench.py gpu_launches) */
 int b200_kernel_launch_count(void);

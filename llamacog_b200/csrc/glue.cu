@@ -8,6 +8,8 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cuda_bf16.h>
 
 namespace b200 {
@@ -169,6 +171,18 @@ __global__ void __launch_bounds__(256) rms_norm_generic_kernel(const tens src, c
 
 // ---- rope (reference ggml-cpu/ops.cpp:5080-5118, 5178-5360): modes normal and neox ----
 struct rope_dev { int n_dims, neox; float freq_scale, ext_factor, attn_factor, theta_scale, corr0, corr1; };
+// rotation of pair ip of a row at position p: returns cos/sin (already scaled)
+__device__ __forceinline__ void rope_cs(const rope_dev & p, int64_t ip, int32_t posv, const float * __restrict__ ff, float & c, float & sn) {
+    const float theta_extrap = (float)posv * powf(p.theta_scale, (float)ip) / (ff ? ff[ip] : 1.0f);
+    float theta = p.freq_scale * theta_extrap, mscale = p.attn_factor;
+    if (p.ext_factor != 0.0f) {
+        const float y = ((float)ip - p.corr0) / fmaxf(0.001f, p.corr1 - p.corr0);
+        const float ramp = (1.0f - fminf(1.0f, fmaxf(0.0f, y))) * p.ext_factor;
+        theta = theta * (1.0f - ramp) + theta_extrap * ramp;
+        mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
+    }
+    c = cosf(theta) * mscale; sn = sinf(theta) * mscale;
+}
 template <typename T>
 __global__ void __launch_bounds__(256) rope_kernel(const tens src, const tens dst, const int32_t * __restrict__ pos,
                                                    const float * __restrict__ ff, const rope_dev p) {
@@ -185,15 +199,7 @@ __global__ void __launch_bounds__(256) rope_kernel(const tens src, const tens ds
             ((T *)d)[i0] = ((const T *)s)[i0]; ((T *)d)[i0 + 1] = ((const T *)s)[i0 + 1];
             continue;
         }
-        const float theta_extrap = (float)pos[i2] * powf(p.theta_scale, (float)ip) / (ff ? ff[ip] : 1.0f);
-        float theta = p.freq_scale * theta_extrap, mscale = p.attn_factor;
-        if (p.ext_factor != 0.0f) {
-            const float y = ((float)ip - p.corr0) / fmaxf(0.001f, p.corr1 - p.corr0);
-            const float ramp = (1.0f - fminf(1.0f, fmaxf(0.0f, y))) * p.ext_factor;
-            theta = theta * (1.0f - ramp) + theta_extrap * ramp;
-            mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
-        }
-        const float c = cosf(theta) * mscale, sn = sinf(theta) * mscale;
+        float c, sn; rope_cs(p, ip, pos[i2], ff, c, sn);
         const int64_t ia = p.neox ? ip : i0, ib = p.neox ? ip + p.n_dims / 2 : i0 + 1;
         const float x0 = (float)((const T *)s)[ia], x1 = (float)((const T *)s)[ib];
         ((T *)d)[ia] = (T)(x0 * c - x1 * sn);
@@ -256,6 +262,47 @@ __global__ void __launch_bounds__(256) cpy_blocks_kernel(const tens src, const t
         const int64_t d1 = dr % dst.ne[1], dr2 = dr / dst.ne[1];
         char * dp = dd + d0 * dst.nb[0] + d1 * dst.nb[1] + (dr2 % dst.ne[2]) * dst.nb[2] + (dr2 / dst.ne[2]) * dst.nb[3];
         for (int k = 0; k < bb; k += 2) *(uint16_t *)(dp + k) = *(const uint16_t *)(sp + k);
+    }
+}
+
+// ---- several rope / KV-store nodes of a decode step in one launch (blockIdx.y = task) ----
+// kind 0: dst = rope(src);  kind 1: dst = rope(src) and dst2 = convert(dst) in cpy's flat element order;  kind 2: dst2 = convert(src)
+struct ew_task { int kind, d2type; tens src, dst, dst2; const int32_t * pos; const float * ff; rope_dev rp; char * const * dslot; int64_t n; };
+struct ew_batch { ew_task t[4]; };
+__device__ __forceinline__ void store_conv(char * base, const tens & d2, int d2type, int64_t flat, float v) {
+    char * p = base + flat_off(d2, flat);
+    if (d2type == T_F16) *(__half *)p = __float2half_rn(v);
+    else if (d2type == T_BF16) *(__nv_bfloat16 *)p = __float2bfloat16_rn(v);
+    else *(float *)p = v;
+}
+__global__ void __launch_bounds__(256) ew_batch_kernel(const __grid_constant__ ew_batch b) {
+    pdl_enter();
+    const ew_task & t = b.t[blockIdx.y];
+    char * d2 = t.kind ? (t.dslot ? *t.dslot : t.dst2.d) : nullptr;
+    if (t.kind == 2) {
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < t.n; i += (int64_t)gridDim.x * blockDim.x)
+            store_conv(d2, t.dst2, t.d2type, i, *(const float *)(t.src.d + flat_off(t.src, i)));
+        return;
+    }
+    const tens & src = t.src; const tens & dst = t.dst; const rope_dev & p = t.rp;
+    const int64_t half0 = src.ne[0] / 2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < t.n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t ip = i % half0, r = i / half0;
+        const int64_t i1 = r % src.ne[1], i2 = (r / src.ne[1]) % src.ne[2], i3 = r / (src.ne[1] * src.ne[2]);
+        const float * s = (const float *)(src.d + i1 * src.nb[1] + i2 * src.nb[2] + i3 * src.nb[3]);
+        float * d = (float *)(dst.d + i1 * dst.nb[1] + i2 * dst.nb[2] + i3 * dst.nb[3]);
+        const int64_t row0 = r * src.ne[0];          // flat index of the row's first element (cpy order)
+        const int64_t i0 = 2 * ip;
+        int64_t ia, ib; float ya, yb;
+        if (i0 >= p.n_dims) { ia = i0; ib = i0 + 1; ya = s[ia]; yb = s[ib]; }
+        else {
+            float c, sn; rope_cs(p, ip, t.pos[i2], t.ff, c, sn);
+            ia = p.neox ? ip : i0; ib = p.neox ? ip + p.n_dims / 2 : i0 + 1;
+            const float x0 = s[ia], x1 = s[ib];
+            ya = x0 * c - x1 * sn; yb = x0 * sn + x1 * c;
+        }
+        d[ia] = ya; d[ib] = yb;
+        if (t.kind == 1) { store_conv(d2, t.dst2, t.d2type, row0 + ia, ya); store_conv(d2, t.dst2, t.d2type, row0 + ib, yb); }
     }
 }
 
@@ -401,4 +448,50 @@ extern "C" int b200_op_cpy_indirect(const b200_tensor * src, const b200_tensor *
     B200_CPY_CASE(B200_TYPE_BF16, __nv_bfloat16, T_F32, float) B200_CPY_CASE(B200_TYPE_BF16, __nv_bfloat16, T_F16, __half)
     B200_CPY_CASE(B200_TYPE_BF16, __nv_bfloat16, B200_TYPE_BF16, __nv_bfloat16)
     return -1;
+}
+
+#define EW_FAIL() do { if (getenv("B200_DEBUG")) fprintf(stderr, "b200_op_rope_cpy_batch: refused at line %d\n", __LINE__); return -1; } while (0)
+static int ew_build(const b200_ew_desc * tasks, int n, ew_batch & b, int64_t & nmax) {
+    if (n < 1 || n > 4) EW_FAIL();
+    nmax = 0;
+    for (int i = 0; i < n; ++i) {
+        const b200_ew_desc & d = tasks[i];
+        ew_task & t = b.t[i];
+        t.kind = d.kind;
+        if (d.kind < 0 || d.kind > 2 || !d.src || d.src->type != T_F32 || (d.kind != 2 && d.src->nb[0] != 4)) EW_FAIL();
+        t.src = mk(d.src);
+        if (d.kind != 2) {
+            const b200_rope_params * prm = d.rope;
+            if (!d.dst || !prm || !d.pos || d.dst->type != T_F32 || d.dst->nb[0] != 4 || !same_shape(d.src, d.dst) || d.pos->type != T_I32) EW_FAIL();
+            if ((prm->mode != 0 && prm->mode != 2) || prm->n_dims % 2 || prm->n_dims > d.src->ne[0] || d.src->ne[0] % 2) EW_FAIL();
+            t.dst = mk(d.dst);
+            t.pos = (const int32_t *)d.pos->data; t.ff = d.ffac ? (const float *)d.ffac->data : nullptr;
+            rope_dev & p = t.rp;
+            p.n_dims = prm->n_dims; p.neox = prm->mode == 2; p.freq_scale = prm->freq_scale; p.ext_factor = prm->ext_factor;
+            p.attn_factor = prm->attn_factor; p.theta_scale = powf(prm->freq_base, -2.0f / prm->n_dims);
+            auto corr_dim = [&](float n_rot) { return prm->n_dims * logf(prm->n_ctx_orig / (n_rot * 2 * 3.14159265358979323846f)) / (2 * logf(prm->freq_base)); };
+            p.corr0 = std::max(0.0f, floorf(corr_dim(prm->beta_fast)));
+            p.corr1 = std::min((float)prm->n_dims - 1, ceilf(corr_dim(prm->beta_slow)));
+            t.n = nelem(d.src) / 2;
+        } else t.n = nelem(d.src);
+        if (d.kind != 0) {
+            if (!d.dst2 || nelem(d.dst2) != nelem(d.src)) EW_FAIL();
+            if (d.dst2->type != T_F16 && d.dst2->type != T_F32 && d.dst2->type != T_BF16) EW_FAIL();
+            if (d.dst2->nb[0] != type_size(d.dst2->type)) EW_FAIL();
+            t.dst2 = mk(d.dst2); t.d2type = d.dst2->type; t.dslot = (char * const *)d.dst2_slot;
+        }
+        nmax = std::max(nmax, t.n);
+    }
+    return 0;
+}
+extern "C" int b200_op_rope_cpy_batch_check(const b200_ew_desc * tasks, int n) {
+    ew_batch b = {}; int64_t nmax;
+    return ew_build(tasks, n, b, nmax);
+}
+extern "C" int b200_op_rope_cpy_batch(const b200_ew_desc * tasks, int n, void * stream) {
+    ew_batch b = {}; int64_t nmax;
+    const int rc = ew_build(tasks, n, b, nmax);
+    if (rc) return rc;
+    if (nmax == 0) return 0;
+    return launch(ew_batch_kernel, dim3(grid_for(nmax, 256), (unsigned)n), 256, 0, (cudaStream_t)stream, b);
 }

@@ -175,6 +175,50 @@ extern "C" int b200_mul_mat_vec_q_ex(const b200_mmvq_args * a, void * stream) {
     return 0;
 }
 
+// Several weight matrices (same type, K and row stride) times the same activations in one launch: q/k/v, gate/up.
+extern "C" int b200_mul_mat_vec_q_group(const b200_mmvq_args * a, int ng, const void * const * W, float * const * dst, const int * N,
+                                        const int64_t * ds, void * stream) {
+    if (!a || ng < 1 || ng > 3 || !b200_mmvq_supported_type(a->type)) return -1;
+    if (a->K <= 0 || a->K % block_elems(a->type) || a->M <= 0 || a->M > max_cols_per_launch(a->K)) return -1;
+    if (std::max(1, a->ny) != 1 || std::max(1, a->nz) != 1 || a->ids || a->dbg_sumi) return -1;
+    int ntot = 0;
+    for (int g = 0; g < ng; ++g) { if (N[g] <= 0) return -1; ntot += N[g]; }
+    mmvq_params p = {};
+    p.W = (const uint8_t *)W[0]; p.nb1 = a->nb1;
+    p.X = a->X; p.xs = a->xs; p.Xq = (const uint8_t *)a->Xq;
+    p.dst = dst[0]; p.ds = ds[0];
+    p.N = ntot; p.K = a->K;
+    p.w_div_y = 1; p.w_div_z = 1; p.x_mod_y = 1 << 30;
+    p.vec_ok = ((((uintptr_t)p.X) | ((uintptr_t)a->xs * 4)) & 15) == 0;
+    b200_mmvq_args cfg = *a;
+    uintptr_t align = 0;
+    for (int g = 0; g < ng; ++g) align |= (uintptr_t)W[g];
+    cfg.W = (const void *)align;                     // configure() only looks at the alignment bits
+    cfg.ny = 1; cfg.nz = 1;
+    mmvq_launch_cfg c = {};
+    int rc = configure(a->type, ntot, a->K, a->M, cfg, p, c);
+    if (rc) return rc;
+    // split the CTAs over the matrices in proportion to their rows (at least one each)
+    const int gx = (int)c.grid.x;
+    int used = 0;
+    p.ngroup = ng;
+    for (int g = 0; g < ng; ++g) {
+        int share = g + 1 == ng ? std::max(1, gx - used) : std::max(1, (int)((int64_t)gx * N[g] / ntot));
+        share = std::min(share, (N[g] + p.R - 1) / p.R);
+        share = std::max(share, 1);
+        p.cta0[g] = used; used += share;
+        p.Wg[g] = (const uint8_t *)W[g]; p.Dg[g] = dst[g]; p.dsg[g] = ds[g];
+        p.rows_qg[g] = N[g] / share; p.rows_remg[g] = N[g] % share;
+    }
+    p.cta0[ng] = used;
+    c.grid = dim3(used, 1, 1);
+    c.pdl = a->pdl >= 0 ? a->pdl : pdl_default();
+    rc = mmvq_dispatch(a->type, p, c, (cudaStream_t)stream);
+    if (rc) return rc;
+    ++g_launches;
+    return 0;
+}
+
 extern "C" int b200_mul_mat_vec_q(int type, const void * W, int64_t nb1, const float * X, int64_t xs,
                                   float * dst, int64_t ds, int N, int K, int M, void * stream) {
     b200_mmvq_args a = {};

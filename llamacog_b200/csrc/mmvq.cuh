@@ -56,6 +56,11 @@ struct mmvq_params {
     int act_bytes;           // shared bytes of the activation area (M columns)
     int vec_ok;              // X columns 16-byte aligned -> float4 loads
     int32_t * dbg_sumi;      // parity hook: when non-null, int32 block sums [M][N][K/32] are stored here
+    // group mode (b200_mul_mat_vec_q_group): up to 3 weight matrices of one type and K read the same activations in one
+    // launch; CTAs [cta0[g], cta0[g+1]) work on matrix g with their own balanced row split
+    int ngroup;
+    const uint8_t * Wg[3]; float * Dg[3]; int64_t dsg[3];
+    int cta0[4], rows_qg[3], rows_remg[3];
 };
 
 template <int TYPE, int M, bool A16, bool DBG>
@@ -93,9 +98,15 @@ __global__ void __launch_bounds__(288, (M <= 4 ? 2 : 1)) mmvq_kernel(const mmvq_
     }
 
     // balanced contiguous row range of this CTA: the first rows_rem CTAs take one extra row
-    const int cta = blockIdx.x;
-    const int row_lo = cta * p.rows_q + min(cta, p.rows_rem);
-    const int nrows = p.rows_q + (cta < p.rows_rem ? 1 : 0);
+    int cta = blockIdx.x, rows_q = p.rows_q, rows_rem = p.rows_rem;
+    int64_t ds = p.ds;
+    if (p.ngroup) {
+        int g = 0;
+        while (g + 1 < p.ngroup && cta >= p.cta0[g + 1]) ++g;
+        cta -= p.cta0[g]; Wc = p.Wg[g]; Dc = p.Dg[g]; ds = p.dsg[g]; rows_q = p.rows_qg[g]; rows_rem = p.rows_remg[g];
+    }
+    const int row_lo = cta * rows_q + min(cta, rows_rem);
+    const int nrows = rows_q + (cta < rows_rem ? 1 : 0);
     const int row_hi = row_lo + nrows;
     const int ngroups = (nrows + p.R - 1) / p.R;
     const int rb = (p.K / fmt<TYPE>::BE) * fmt<TYPE>::BB;   // payload bytes per row
@@ -150,7 +161,7 @@ __global__ void __launch_bounds__(288, (M <= 4 ? 2 : 1)) mmvq_kernel(const mmvq_
                 const int r = o / M, m = o - r * M;
                 float s = 0.0f;
                 for (int sg = 0; sg < nseg; ++sg) s += ps[(r * nseg + sg) * M + m];
-                Dc[(int64_t)m * p.ds + r0 + r] = s;
+                Dc[(int64_t)m * ds + r0 + r] = s;
             }
             __syncwarp();
             if (lane == 0 && g + p.nstages < ngroups) issue(g + p.nstages);
