@@ -203,6 +203,37 @@ def kernel_roofline(steps, warmup, dev_index):
     return {"launches": len(plan), "us_per_launch": ms * 1e3 / len(plan), "bytes": nbytes, "gbps": nbytes / (ms * 1e-3) / 1e9}
 
 
+def mmq_roofline(steps, warmup, dev_index):
+    """Prefill MMQ (tcgen05) on the seven Q4_K_M projection shapes of one layer at 512 tokens, through the C ABI: TFLOP/s
+    (2*N*K*M per mat-mul, activation conversion included) against the measured dense bf16 peak."""
+    import torch
+    from llamacog_b200 import ops
+    from tools.mmvq_micro import rand_weights
+    dev = torch.device("cuda", dev_index)
+    M = 512
+    shapes = [(Q4_K, N_EMBD, N_EMBD), (Q4_K, N_KV, N_EMBD), (Q6_K, N_KV, N_EMBD), (Q4_K, N_EMBD, N_EMBD),
+              (Q4_K, N_FF, N_EMBD), (Q4_K, N_FF, N_EMBD), (Q6_K, N_EMBD, N_FF)]
+    with torch.cuda.device(dev):
+        Ws = [rand_weights(t, N * ops.row_bytes(t, K) + 256, dev) for t, N, K in shapes]
+        Xs = {K: torch.randn(M, K, device=dev) for K in (N_EMBD, N_FF)}
+
+        def run():
+            for (t, N, K), W in zip(shapes, Ws):
+                ops.mul_mat_q(t, W, Xs[K], N, K)
+        for _ in range(max(3, warmup)):
+            run()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            run()
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    flops = sum(2.0 * N * K * M for _, N, K in shapes)
+    return {"tflops": flops / (ms * 1e-3) / 1e12, "ms_per_layer": ms, "flops_per_layer": flops}
+
+
 def cpu_reference_run(model, n_tokens, threads):
     res, _ = llama_bench(model, ["-ngl", "0", "-p", "0", "-n", str(n_tokens), "-r", "1", "-t", str(threads)], plugin=False)
     return float(res[-1]["avg_ts"])
@@ -314,6 +345,22 @@ def main():
                                     "whole_step_GBps": plan_bytes(step_plan()) / (ms_step * 1e-3) / 1e9}
             except Exception as e:  # noqa: BLE001
                 line["roofline"] = {"error": str(e)[:200]}
+        if not args.no_roofline and world == 1:
+            # the prefill side of the headline metric: pp512 through the same unmodified llama-bench, and the MMQ tensor-pipe fraction
+            try:
+                resp, _ = llama_bench(model, ["-ngl", "99", "-fa", "1", "-p", "512", "-n", "0", "-r", "3"], plugin=True, device=device)
+                pre = {"pp512_tokens_per_s": float(resp[-1]["avg_ts"]),
+                       "workload": "llama3-8b-q4_k_m pp512, llama-bench -ngl 99 -fa 1 (MMQ tcgen05 + tensor-core flash attention)"}
+                m = mmq_roofline(20, args.warmup, local)
+                peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+                tpeak = float(peaks.get("bf16_tflops", 1590.0))
+                pre["mmq_roofline"] = {"bound": "tensor", "kernel": "mmq_kernel (7 projections of one layer, M=512)", "achieved": m["tflops"],
+                                       "peak": tpeak, "unit": "TFLOP/s", "frac": m["tflops"] / tpeak,
+                                       "peak_source": "measured bf16 burst (MEASURED_PEAKS.json)" if peaks else "fallback 1.59 PFLOP/s",
+                                       "ms_per_layer": m["ms_per_layer"]}
+                line["prefill"] = pre
+            except Exception as e:  # noqa: BLE001
+                line["prefill"] = {"error": str(e)[:200]}
         if not args.no_cpu_baseline and world == 1:
             threads = os.cpu_count() or 1
             try:

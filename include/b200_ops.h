@@ -195,16 +195,17 @@ int b200_mmq_debug_trace(void * dev_buf);
 int b200_op_mul_mat_id(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * dst,
                        void * scratch, int64_t scratch_bytes, void * stream);
 
-/* Decode-step fusions (at most 8 rows of K floats, K % 32 == 0, rows 16-byte aligned; -1 = shape not taken, run the nodes
+/* Fusions of adjacent graph nodes over rows of K floats (K % 32 == 0, rows 16-byte aligned; -1 = shape not taken, run the nodes
  * one by one).  Every intermediate tensor is written exactly as the separate operators write it.
  *   add_rms_norm_mul:  sum = a + b (skipped when b == NULL);  norm = rms_norm(sum or a, eps);  out = norm * w  (w: [K])
  *   unary_mul:         act = silu|gelu(g);  out = act * u
- * xq (optional): the GEMV's pre-quantised activation layout of `out` (b200_quantized_acts_bytes), written by the same launch.
+ * xq (optional): `out` once more in the form the following mat-mul reads, written by the same launch: xq_kind 0 = the GEMV's
+ * pre-quantised activation layout (b200_quantized_acts_bytes; at most 8 rows), 1 = bf16 [M][K] for the MMQ (b200_acts_bf16_bytes).
  * Reference: the RMS_NORM+MUL(+ADD) and GLU fusions of ggml-cuda (ggml-cuda.cu ggml_cuda_can_fuse / norm.cu rms_norm_mul). */
 int b200_op_add_rms_norm_mul(const b200_tensor * a, const b200_tensor * b, const b200_tensor * sum, const b200_tensor * norm,
-                             const b200_tensor * w, const b200_tensor * out, float eps, void * xq, void * stream);
+                             const b200_tensor * w, const b200_tensor * out, float eps, void * xq, int xq_kind, void * stream);
 int b200_op_unary_mul(int op, const b200_tensor * g, const b200_tensor * act, const b200_tensor * u, const b200_tensor * out,
-                      void * xq, void * stream);
+                      void * xq, int xq_kind, void * stream);
 
 /* Up to 4 rope / KV-store nodes of a decode step in one launch.
  *   kind 0: dst = rope(src)          kind 1: dst = rope(src) and dst2 = cpy(dst)  (the K row going into the cache)

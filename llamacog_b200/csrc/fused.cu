@@ -1,12 +1,13 @@
-// fused.cu -- decode-step fusions of adjacent graph nodes (batch <= 8 rows).  A decode step of an 8B model is ~800
-// kernels of a few microseconds each; these kernels do the work of 3-4 nodes in one launch and hand the next GEMV its
-// activations already quantised.  Every intermediate tensor of the original nodes is still written, with the same
-// arithmetic in the same order as the separate kernels (glue.cu), so results are bit-identical with and without fusion
-// and nothing needs to be known about other consumers of the intermediates.
-//   b200_op_add_rms_norm_mul : [ADD] -> RMS_NORM -> MUL(weight)   (+ q8_1 activations of the result for the GEMV)
-//   b200_op_unary_mul        : UNARY(silu|gelu) -> MUL(other)     (+ q8_1 activations of the result)
-// Reference: the same chains are fused in ggml-cuda (ggml_cuda_op_rms_norm_fused, ggml-cuda.cu fusion of RMS_NORM+MUL; GLU
-// kernels in unary.cu); semantics of each step follow ggml-cpu/ops.cpp (rms_norm 3285-3312, silu unary-ops.cpp).
+// fused.cu -- fusions of adjacent graph nodes.  A decode step of an 8B model is ~800 kernels of a few microseconds each and
+// a prefill pass spends a quarter of its time in element-wise glue; these kernels do the work of 3-4 nodes in one launch and
+// hand the next mat-mul its activations in the form it reads (q8_1 blocks for the GEMV, bf16 rows for the MMQ).  Every
+// intermediate tensor of the original nodes is still written, with the same arithmetic in the same order as the separate
+// kernels (glue.cu), so results are bit-identical with and without fusion and nothing needs to be known about other
+// consumers of the intermediates.
+//   b200_op_add_rms_norm_mul : [ADD] -> RMS_NORM -> MUL(weight)   (+ activations of the result for the next mat-mul)
+//   b200_op_unary_mul        : UNARY(silu|gelu) -> MUL(other)     (+ activations of the result)
+// Reference: the same chains are fused in ggml-cuda (RMS_NORM+MUL in norm.cu / ggml-cuda.cu graph fusion; GLU kernels in
+// unary.cu); semantics of each step follow ggml-cpu/ops.cpp (rms_norm 3285-3312) and unary-ops.cpp (silu, gelu).
 #include "mmvq_units.cuh"
 #include "../../include/b200_ops.h"
 
@@ -14,12 +15,13 @@
 
 namespace b200 {
 
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi);
 // one CTA per row, thread t holds float4 t, t + blockDim, ... of the row (8 consecutive threads = one 32-block)
 template <int VPT>
 __global__ void __launch_bounds__(1024) add_rms_norm_mul_kernel(const float * __restrict__ a, int64_t as, const float * __restrict__ b, int64_t bs,
                                                                 float * __restrict__ sum, int64_t ss, float * __restrict__ norm, int64_t ns,
                                                                 const float * __restrict__ w, float * __restrict__ out, int64_t os,
-                                                                uint8_t * __restrict__ xq, int K, float eps) {
+                                                                uint8_t * __restrict__ xq, int xkind, int K, float eps) {
     pdl_trigger(); pdl_wait();
     const int r = blockIdx.x, n4 = K >> 2;
     const float4 * a4 = reinterpret_cast<const float4 *>(a + (int64_t)r * as);
@@ -59,10 +61,14 @@ __global__ void __launch_bounds__(1024) add_rms_norm_mul_kernel(const float * __
             y = make_float4(nv.x * ww.x, nv.y * ww.y, nv.z * ww.z, nv.w * ww.w);
             n4p[i] = nv; o4[i] = y;
         }
-        if (xq) quant_block_store(y, i >> 3, threadIdx.x & 7, i < n4, xq + (size_t)r * acs);
+        if (xq && xkind == 0) quant_block_store(y, i >> 3, threadIdx.x & 7, i < n4, xq + (size_t)r * acs);
+        if (xq && xkind == 1 && i < n4) reinterpret_cast<uint2 *>(xq + (size_t)r * K * 2)[i] = make_uint2(pack_bf16x2(y.x, y.y), pack_bf16x2(y.z, y.w));
     }
 }
 
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    uint32_t d; asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo)); return d;
+}
 template <int OP> __device__ __forceinline__ float act_fn(float x) {
     if constexpr (OP == B200_UNARY_SILU) return x / (1.0f + expf(-x));
     else { const float c = 0.044715f, s = 0.79788456080286535587989211986876f; return 0.5f * x * (1.0f + tanhf(s * x * (1.0f + c * x * x))); }
@@ -71,7 +77,7 @@ template <int OP> __device__ __forceinline__ float act_fn(float x) {
 template <int OP>
 __global__ void __launch_bounds__(256) unary_mul_kernel(const float * __restrict__ g, int64_t gs, float * __restrict__ act, int64_t as,
                                                         const float * __restrict__ u, int64_t us, float * __restrict__ out, int64_t os,
-                                                        uint8_t * __restrict__ xq, int K, int M) {
+                                                        uint8_t * __restrict__ xq, int xkind, int K, int M) {
     pdl_trigger(); pdl_wait();
     const int n4 = K >> 2;
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -86,10 +92,11 @@ __global__ void __launch_bounds__(256) unary_mul_kernel(const float * __restrict
         reinterpret_cast<float4 *>(act + (int64_t)r * as)[i] = a;
         reinterpret_cast<float4 *>(out + (int64_t)r * os)[i] = y;
     }
-    if (xq) {
+    if (xq && xkind == 0) {
         const uint32_t acs = (uint32_t)((K + 255) / 256) * ACT_ITEM;
         quant_block_store(y, i >> 3, threadIdx.x & 7, in, xq + (size_t)r * acs);
     }
+    if (xq && xkind == 1 && in) reinterpret_cast<uint2 *>(xq + (size_t)r * K * 2)[i] = make_uint2(pack_bf16x2(y.x, y.y), pack_bf16x2(y.z, y.w));
 }
 
 template <typename... KArgs, typename... Args>
@@ -120,21 +127,23 @@ static bool rows_of(const b200_tensor * t, int K, int M, int64_t * stride) {
 using namespace b200;
 
 extern "C" int b200_op_add_rms_norm_mul(const b200_tensor * a, const b200_tensor * b, const b200_tensor * sum, const b200_tensor * norm,
-                                        const b200_tensor * w, const b200_tensor * out, float eps, void * xq, void * stream) {
+                                        const b200_tensor * w, const b200_tensor * out, float eps, void * xq, int xq_kind, void * stream) {
     const int K = (int)a->ne[0];
     const int64_t M64 = a->ne[1] * a->ne[2] * a->ne[3];
-    if (K <= 0 || K % 32 || K > 16384 || M64 < 1 || M64 > 8) return -1;
+    if (K <= 0 || K % 32 || K > 16384 || M64 < 1 || M64 > 65535 || (xq && xq_kind == 0 && M64 > 8) || (xq_kind != 0 && xq_kind != 1)) return -1;
     const int M = (int)M64;
+    if (xq && ((uintptr_t)xq & 15)) return -1;
     int64_t as, bs = 0, ss = 0, ns, os;
     if (!rows_of(a, K, M, &as) || !rows_of(norm, K, M, &ns) || !rows_of(out, K, M, &os)) return -1;
     if (b && (!sum || !rows_of(b, K, M, &bs) || !rows_of(sum, K, M, &ss))) return -1;
     if (w->type != T_F32 || w->ne[0] != K || w->ne[1] * w->ne[2] * w->ne[3] != 1 || w->nb[0] != 4 || ((uintptr_t)w->data & 15)) return -1;
     const int n4 = K / 4;
-    const int threads = std::min(1024, (n4 + 31) / 32 * 32);
+    // few rows (decode): as many threads as float4s, one each (pure latency); many rows (prefill): 256 threads, up to 4 each
+    const int threads = M <= 8 || n4 > 1024 ? std::min(1024, (n4 + 31) / 32 * 32) : std::min(256, (n4 + 31) / 32 * 32);
     cudaStream_t st = (cudaStream_t)stream;
     const float * bp = b ? (const float *)b->data : nullptr;
     float * sp = b ? (float *)sum->data : nullptr;
-#define B200_NORM_ARGS (const float *)a->data, as, bp, bs, sp, ss, (float *)norm->data, ns, (const float *)w->data, (float *)out->data, os, (uint8_t *)xq, K, eps
+#define B200_NORM_ARGS (const float *)a->data, as, bp, bs, sp, ss, (float *)norm->data, ns, (const float *)w->data, (float *)out->data, os, (uint8_t *)xq, xq_kind, K, eps
     if (n4 <= threads) return flaunch(add_rms_norm_mul_kernel<1>, M, threads, st, B200_NORM_ARGS);
     if (n4 <= 2 * threads) return flaunch(add_rms_norm_mul_kernel<2>, M, threads, st, B200_NORM_ARGS);
     return flaunch(add_rms_norm_mul_kernel<4>, M, threads, st, B200_NORM_ARGS);
@@ -142,10 +151,11 @@ extern "C" int b200_op_add_rms_norm_mul(const b200_tensor * a, const b200_tensor
 }
 
 extern "C" int b200_op_unary_mul(int op, const b200_tensor * g, const b200_tensor * act, const b200_tensor * u, const b200_tensor * out,
-                                 void * xq, void * stream) {
+                                 void * xq, int xq_kind, void * stream) {
     const int K = (int)g->ne[0];
     const int64_t M64 = g->ne[1] * g->ne[2] * g->ne[3];
-    if (K <= 0 || K % 32 || M64 < 1 || M64 > 8 || (op != B200_UNARY_SILU && op != B200_UNARY_GELU)) return -1;
+    if (K <= 0 || K % 32 || M64 < 1 || M64 > 65535 || (op != B200_UNARY_SILU && op != B200_UNARY_GELU)) return -1;
+    if ((xq && xq_kind == 0 && M64 > 8) || (xq_kind != 0 && xq_kind != 1)) return -1;
     const int M = (int)M64;
     int64_t gs, as, us, os;
     if (!rows_of(g, K, M, &gs) || !rows_of(act, K, M, &as) || !rows_of(u, K, M, &us) || !rows_of(out, K, M, &os)) return -1;
@@ -154,7 +164,7 @@ extern "C" int b200_op_unary_mul(int op, const b200_tensor * g, const b200_tenso
     cudaStream_t st = (cudaStream_t)stream;
     if (op == B200_UNARY_SILU)
         return flaunch(unary_mul_kernel<B200_UNARY_SILU>, grid, 256, st, (const float *)g->data, gs, (float *)act->data, as, (const float *)u->data, us,
-                       (float *)out->data, os, (uint8_t *)xq, K, M);
+                       (float *)out->data, os, (uint8_t *)xq, xq_kind, K, M);
     return flaunch(unary_mul_kernel<B200_UNARY_GELU>, grid, 256, st, (const float *)g->data, gs, (float *)act->data, as, (const float *)u->data, us,
-                   (float *)out->data, os, (uint8_t *)xq, K, M);
+                   (float *)out->data, os, (uint8_t *)xq, xq_kind, K, M);
 }

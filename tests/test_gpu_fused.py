@@ -45,7 +45,7 @@ def test_add_rms_norm_mul_matches_separate_ops(M, K, with_add):
     s = torch.empty_like(a); n = torch.empty_like(a); o = torch.empty_like(a); q = torch.zeros_like(q_ref)
     rc = L.b200_op_add_rms_norm_mul(C.byref(ops.as_b200(a)), C.byref(ops.as_b200(b)) if with_add else None,
                                     C.byref(ops.as_b200(s)) if with_add else None, C.byref(ops.as_b200(n)), C.byref(ops.as_b200(w)),
-                                    C.byref(ops.as_b200(o)), C.c_float(eps), C.c_void_p(q.data_ptr()), _st(ops))
+                                    C.byref(ops.as_b200(o)), C.c_float(eps), C.c_void_p(q.data_ptr()), C.c_int(0), _st(ops))
     assert rc == 0
     torch.cuda.synchronize()
     if with_add:
@@ -70,7 +70,7 @@ def test_silu_mul_matches_separate_ops(M, K):
     q_ref = ops.quantize_acts(o_ref)
     a = torch.empty_like(g); o = torch.empty_like(g); q = torch.zeros_like(q_ref)
     assert L.b200_op_unary_mul(C.c_int(10), C.byref(ops.as_b200(g)), C.byref(ops.as_b200(a)), C.byref(ops.as_b200(u)), C.byref(ops.as_b200(o)),
-                               C.c_void_p(q.data_ptr()), _st(ops)) == 0
+                               C.c_void_p(q.data_ptr()), C.c_int(0), _st(ops)) == 0
     torch.cuda.synchronize()
     assert torch.equal(a, a_ref) and torch.equal(o, o_ref) and _same_acts(q, q_ref)
     assert torch.allclose(o, torch.nn.functional.silu(g) * u, rtol=1e-5, atol=1e-6)
@@ -79,5 +79,34 @@ def test_silu_mul_matches_separate_ops(M, K):
 def test_shapes_the_fusion_does_not_take_are_refused():
     ops = _ops(); L = ops.lib()
     a = torch.randn(9, 256, device="cuda"); w = torch.randn(256, device="cuda"); n = torch.empty_like(a); o = torch.empty_like(a)
+    q = torch.zeros(9 * 400, dtype=torch.uint8, device="cuda")
     assert L.b200_op_add_rms_norm_mul(C.byref(ops.as_b200(a)), None, None, C.byref(ops.as_b200(n)), C.byref(ops.as_b200(w)),
-                                      C.byref(ops.as_b200(o)), C.c_float(1e-5), None, _st(ops)) == -1       # more than 8 rows
+                                      C.byref(ops.as_b200(o)), C.c_float(1e-5), C.c_void_p(q.data_ptr()), C.c_int(0), _st(ops)) == -1   # q8 layout: at most 8 rows
+    a = torch.randn(4, 250, device="cuda"); w = torch.randn(250, device="cuda"); n = torch.empty_like(a); o = torch.empty_like(a)
+    assert L.b200_op_add_rms_norm_mul(C.byref(ops.as_b200(a)), None, None, C.byref(ops.as_b200(n)), C.byref(ops.as_b200(w)),
+                                      C.byref(ops.as_b200(o)), C.c_float(1e-5), None, C.c_int(0), _st(ops)) == -1       # K % 32 != 0
+
+
+@pytest.mark.parametrize("M,K", [(9, 256), (100, 4096), (512, 4096), (300, 14336)])
+def test_prefill_rows_with_bf16_activations(M, K):
+    """many rows: the fused kernels also hand the MMQ its bf16 activations (bit-identical to b200_convert_acts_bf16 of the f32 output)"""
+    ops = _ops(); L = ops.lib()
+    torch.manual_seed(M + K)
+    a = torch.randn(M, K, device="cuda"); b = torch.randn(M, K, device="cuda"); w = torch.randn(K, device="cuda")
+    s = torch.empty_like(a); n = torch.empty_like(a); o = torch.empty_like(a); xb = torch.zeros(M, K, dtype=torch.bfloat16, device="cuda")
+    assert L.b200_op_add_rms_norm_mul(C.byref(ops.as_b200(a)), C.byref(ops.as_b200(b)), C.byref(ops.as_b200(s)), C.byref(ops.as_b200(n)),
+                                      C.byref(ops.as_b200(w)), C.byref(ops.as_b200(o)), C.c_float(1e-5), C.c_void_p(xb.data_ptr()), C.c_int(1), _st(ops)) == 0
+    s_ref = torch.empty_like(a); n_ref = torch.empty_like(a); o_ref = torch.empty_like(a)
+    assert L.b200_op_binary(C.c_int(0), C.byref(ops.as_b200(a)), C.byref(ops.as_b200(b)), C.byref(ops.as_b200(s_ref)), _st(ops)) == 0
+    assert L.b200_op_rms_norm(C.byref(ops.as_b200(s_ref)), C.byref(ops.as_b200(n_ref)), C.c_float(1e-5), _st(ops)) == 0
+    assert L.b200_op_binary(C.c_int(2), C.byref(ops.as_b200(n_ref)), C.byref(ops.as_b200(w)), C.byref(ops.as_b200(o_ref)), _st(ops)) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(s, s_ref) and torch.equal(n, n_ref) and torch.equal(o, o_ref)
+    assert torch.equal(xb, o_ref.to(torch.bfloat16))
+    g = torch.randn(M, K, device="cuda") * 2; u = torch.randn(M, K, device="cuda")
+    act = torch.empty_like(g); out = torch.empty_like(g); xb2 = torch.zeros(M, K, dtype=torch.bfloat16, device="cuda")
+    assert L.b200_op_unary_mul(C.c_int(10), C.byref(ops.as_b200(g)), C.byref(ops.as_b200(act)), C.byref(ops.as_b200(u)), C.byref(ops.as_b200(out)),
+                               C.c_void_p(xb2.data_ptr()), C.c_int(1), _st(ops)) == 0
+    torch.cuda.synchronize()
+    assert torch.allclose(out, torch.nn.functional.silu(g) * u, rtol=1e-5, atol=1e-6)
+    assert torch.equal(xb2, out.to(torch.bfloat16))
