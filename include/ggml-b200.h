@@ -12,7 +12,11 @@
  *   "ggml_backend_b200_device_time_ms"     -> double (*)(long * n_graphs): device time spent inside
  *                                             graph_compute since load when B200_TIMING=1 (bench.py)
  *   "ggml_backend_b200_kernel_launches"    -> int (*)(void): kernels launched so far
- *   "ggml_backend_split_buffer_type"       -> NULL in this round (row split: SURVEY 8e, next round)
+ *   "ggml_backend_split_buffer_type"       -> ggml_backend_buffer_type_t (*)(int main_device, const float * tensor_split):
+ *                                             the row-split buffer type of `--split-mode row` (reference
+ *                                             ggml-cuda.cu:753-1084, :3476-3478; consumer src/llama-model.cpp:342-360).
+ *                                             Weight rows are sharded over the devices in proportion to tensor_split,
+ *                                             boundaries rounded down to 128 rows; MUL_MAT is the only op accepted on it.
  */
 #ifndef GGML_B200_H
 #define GGML_B200_H
@@ -27,6 +31,9 @@ struct ggml_backend_reg;
 struct ggml_backend_reg * ggml_backend_init(void);
 /* optional: 0 means "do not load" (no sm_100 device visible) */
 int ggml_backend_score(void);
+/* row boundaries the split buffer type uses for an n_rows matrix over n_dev devices (row0: n_dev + 1 entries);
+ * needs no GPU.  Mirrors get_row_split of the reference (ggml-cuda.cu:768-781). */
+void ggml_backend_b200_split_rows(long long n_rows, int n_dev, const float * tensor_split, long long * row0);
 
 #ifdef __cplusplus
 }

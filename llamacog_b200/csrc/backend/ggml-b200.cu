@@ -21,6 +21,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -181,5 +182,6 @@ bool host_buft_is_host(ggml_backend_buffer_type_t) { return true; }
 
 }  // namespace
 
+#include "ggml-b200-split.inc"
 #include "ggml-b200-compute.inc"
 #include "ggml-b200-device.inc"

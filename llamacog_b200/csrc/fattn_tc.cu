@@ -287,11 +287,13 @@ template <int D> static size_t fat_smem() { return 1024 + 5 * (size_t)(D / 64) *
 
 template <int D>
 static int fat_launch(const CUtensorMap & kmap, const CUtensorMap & vmap, const fat_params & p, dim3 grid, cudaStream_t st) {
-    static bool configured = false;
+    static bool configured[16] = {false};   // per device
     const size_t smem = fat_smem<D>();
-    if (!configured) {
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev)); dev &= 15;
+    if (!configured[dev]) {
         B200_CUDA_CHECK(cudaFuncSetAttribute(fattn_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
+        configured[dev] = true;
     }
     cudaLaunchConfig_t lc = {};
     lc.gridDim = grid; lc.blockDim = dim3(FAT_THREADS); lc.dynamicSmemBytes = smem; lc.stream = st;

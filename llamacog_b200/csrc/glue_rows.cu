@@ -169,9 +169,11 @@ extern "C" int b200_op_soft_max(const b200_tensor * src, const b200_tensor * mas
     cudaStream_t st = (cudaStream_t)stream;
     const size_t smem = (size_t)nc * 4;
     if (smem > 48 * 1024) {
-        static bool set[2] = {false, false};
-        if (!set[0]) { cudaFuncSetAttribute(soft_max_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-                       cudaFuncSetAttribute(soft_max_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); set[0] = true; }
+        static bool set[16] = {false};   // per device
+        int dev = 0;
+        cudaGetDevice(&dev); dev &= 15;
+        if (!set[dev]) { cudaFuncSetAttribute(soft_max_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+                       cudaFuncSetAttribute(soft_max_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); set[dev] = true; }
     }
     if (mask && mask->type == T_F16)
         return rlaunch(soft_max_kernel<__half>, (unsigned)nr, threads, smem, st, (const float *)src->data, (const __half *)mask->data,

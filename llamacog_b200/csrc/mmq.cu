@@ -520,10 +520,12 @@ static int choose_tn(int N, int M) {
 
 template <int TYPE>
 static int mmq_launch(const CUtensorMap & wmap, const CUtensorMap & xmap, const mmq_params & p, size_t smem, cudaStream_t st) {
-    static size_t configured = 0;
-    if (smem > configured) {
+    static size_t configured[16] = {0};  // per device
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    if (smem > configured[dev & 15]) {
         B200_CUDA_CHECK(cudaFuncSetAttribute(mmq_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+        configured[dev & 15] = smem;
     }
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3((p.M + p.tn - 1) / p.tn, (p.N + 127) / 128, 1); lc.blockDim = dim3(MMQ_THREADS); lc.dynamicSmemBytes = smem; lc.stream = st;

@@ -3,16 +3,17 @@
 // GGML_BACKEND_PATH=libggml-b200.so: the B200 plugin) and writes the logits of the last prompt token and of
 // every teacher-forced decode step to a file.  tests/test_gpu_plugin.py runs it once per backend and compares.
 //
-// usage: logits_check <model.gguf> <out.bin> <ngl> <flash_attn 0|1> <n_prompt> <n_decode> [n_ubatch]
+// usage: logits_check <model.gguf> <out.bin> <ngl> <flash_attn 0|1> <n_prompt> <n_decode> [n_ubatch] [none|layer|row]
 #include "llama.h"
 #include "ggml-backend.h"
 
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 int main(int argc, char ** argv) {
-    if (argc < 7) { fprintf(stderr, "usage: %s model out ngl fa n_prompt n_decode [n_ubatch]\n", argv[0]); return 2; }
+    if (argc < 7) { fprintf(stderr, "usage: %s model out ngl fa n_prompt n_decode [n_ubatch] [none|layer|row]\n", argv[0]); return 2; }
     const char * path = argv[1]; const char * out = argv[2];
     const int ngl = atoi(argv[3]), fa = atoi(argv[4]), n_prompt = atoi(argv[5]), n_decode = atoi(argv[6]);
     const int n_ubatch = argc > 7 ? atoi(argv[7]) : 512;
@@ -20,6 +21,12 @@ int main(int argc, char ** argv) {
     ggml_backend_load_all();
     llama_model_params mp = llama_model_default_params();
     mp.n_gpu_layers = ngl;
+    if (argc > 8) {      // how the model is spread over several GPUs (src/llama-model.cpp:337-366, :1505-1600)
+        if (strcmp(argv[8], "none") == 0) mp.split_mode = LLAMA_SPLIT_MODE_NONE;
+        else if (strcmp(argv[8], "layer") == 0) mp.split_mode = LLAMA_SPLIT_MODE_LAYER;
+        else if (strcmp(argv[8], "row") == 0) mp.split_mode = LLAMA_SPLIT_MODE_ROW;
+        else { fprintf(stderr, "unknown split mode %s\n", argv[8]); return 2; }
+    }
     llama_model * model = llama_model_load_from_file(path, mp);
     if (!model) { fprintf(stderr, "cannot load %s\n", path); return 1; }
     llama_context_params cp = llama_context_default_params();
