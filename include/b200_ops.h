@@ -226,6 +226,20 @@ int b200_kernel_launch_count(void);
 /* account for kernels launched through a replayed CUDA graph (the plugin captures decode steps) */
 int b200_kernel_launch_add(int n);
 
+/* ---- hand-over between devices through flags in peer memory (csrc/peer.cu) ----------------------------------
+ * Replaces the cudaEventRecord / cudaStreamWaitEvent fork-join and the peer memcpys of the reference's split
+ * MUL_MAT (ggml-cuda/ggml-cuda.cu:1605-1608, :1628-1630, :1701-1745).  All pointers are device pointers that the
+ * launching device can reach (its own memory or peer-mapped memory); flags are 32-bit words, zero when idle.
+ *   b200_peer_bcast : copy `bytes` (multiple of 16) from src to each dsts[p], then raise flags[p] (p < n_peers <=
+ *                     B200_PEER_MAX); counter = one zeroed 32-bit word in the launching device's memory
+ *   b200_peer_wait  : for every bit t of mask, wait until flags[t * stride] is raised and lower it (t < 32)
+ *   b200_peer_signal: make this stream's earlier stores visible system-wide, then raise *remote_flag */
+#define B200_PEER_MAX 15
+int b200_peer_bcast(const void * src, void * const * dsts, uint32_t * const * flags, int n_peers, int64_t bytes,
+                    unsigned * counter, void * stream);
+int b200_peer_wait(uint32_t * flags, int stride, uint32_t mask, void * stream);
+int b200_peer_signal(uint32_t * remote_flag, void * stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -65,15 +65,17 @@ def test_llama_bench_tiny_model_runs_on_plugin(tmp_path):
             assert all(x["avg_ts"] > 0 for x in res)
 
 
-def _logits(model, out, ngl, fa, n_prompt, n_decode, plugin):
+def _logits(model, out, ngl, fa, n_prompt, n_decode, plugin, split=None, extra_env=None):
     import numpy as np
     env = _env()
+    env.update(extra_env or {})
     if not plugin:
         env.pop("GGML_BACKEND_PATH", None)
     exe = os.path.join(ROOT, "tests", "host", "build", "logits_check")
     if not os.path.exists(exe):
         pytest.fail("tests/host/build/logits_check missing: run __graft_entry__.build() in the build container")
-    r = subprocess.run([exe, model, out, str(ngl), str(fa), str(n_prompt), str(n_decode)], capture_output=True, text=True, env=env, timeout=600)
+    cmd = [exe, model, out, str(ngl), str(fa), str(n_prompt), str(n_decode)] + (["512", split] if split else [])
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     raw = np.fromfile(out, dtype=np.uint8)
     n_vocab = int(raw[:4].view(np.int32)[0])
@@ -102,3 +104,23 @@ def test_logits_match_reference_cpu_backend(tmp_path, preset, fa, n_prompt):
     for i in range(ref.shape[0]):
         bar = 4.0 * nmse(self_[i], ref[i]) + 1e-3
         assert nmse(got[i], ref[i]) < bar, (i, nmse(got[i], ref[i]), bar)
+
+
+@pytest.mark.parametrize("mode,env", [("layer", {}), ("row", {}), ("row", {"B200_SPLIT_FLAGS": "0"}), ("row", {"B200_SPLIT_P2P": "0"}),
+                                      ("row", {"B200_CUDA_GRAPHS": "0"})])
+def test_row_split_logits_equal_single_gpu(tmp_path, mode, env):
+    """--split-mode layer / row over every visible B200 against the single-GPU run of the same model: prefill + 8 decode steps.
+    A weight row's dot product does not depend on which device holds it, so the logits must be bit-identical -- through the
+    flag hand-over in peer memory (default), the event fork/join (B200_SPLIT_FLAGS=0), the staged path without peer mappings
+    (B200_SPLIT_P2P=0) and without CUDA graphs.  The reference has no test for its split buffers: this is the pin."""
+    import numpy as np
+    import torch
+    _need()
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    model = str(tmp_path / "l1b.gguf")
+    subprocess.check_call([sys.executable, os.path.join(ROOT, "tools", "make_gguf.py"), "llama3.2-1b", "q4_k_m", model], stdout=subprocess.DEVNULL)
+    one = _logits(model, str(tmp_path / "none.bin"), 99, 1, 40, 8, plugin=True, split="none")
+    got = _logits(model, str(tmp_path / "split.bin"), 99, 1, 40, 8, plugin=True, split=mode, extra_env=env)
+    assert one.shape == got.shape and one.shape[0] == 9
+    assert np.array_equal(one.view(np.uint32), got.view(np.uint32))

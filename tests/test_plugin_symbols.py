@@ -24,7 +24,7 @@ def test_plugin_exports_loader_symbols():
     src = open(os.path.join(ROOT, "include", "ggml-b200.h")).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     names = sorted(set(re.findall(r"\b(ggml_backend_[a-z0-9_]+)\s*\(", src)))
-    assert names == ["ggml_backend_init", "ggml_backend_score"]
+    assert names == ["ggml_backend_b200_split_rows", "ggml_backend_init", "ggml_backend_score"]
     for n in names:
         assert hasattr(lib, n)
 
