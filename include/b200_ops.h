@@ -194,6 +194,19 @@ int b200_mmq_debug_trace(void * dev_buf);
  * Replaces ggml_cuda_mul_mat_id (ggml-cuda/ggml-cuda.cu:2007-2148) and the MoE branch of mmq.cu:141-223. */
 int b200_op_mul_mat_id(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * dst,
                        void * scratch, int64_t scratch_bytes, void * stream);
+/* scratch the call above wants for these operands (0: the per-pair GEMV path needs none).  From 9 tokens on
+ * (B200_MMQ_ID_MIN_T) the rows are sorted by expert on the device and multiplied by the tensor-core MMQ: */
+int64_t b200_mul_mat_id_scratch_bytes(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids);
+/* the batched path itself.  W: n_expert matrices [N][K] of one quantised type, rows nb1 bytes apart, experts N * nb1 apart.
+ * X: f32 activations of token t / slot u at X + t * x_sz + (u % x_ne1) * x_sy (floats).  ids: int32 [T][ids_s1], n_used
+ * per token.  The result row of (t, u) goes to dst + t * d_sz + u * d_sy (floats).  Three launches: routing tables (counts,
+ * offsets, (token, slot) pairs in expert order), gather + bf16 conversion, one MMQ grid over (token tiles, row tiles,
+ * experts) whose CTAs leave when their expert has fewer tokens.  -1: shape not taken.  The reference sorts on the host after
+ * a device->host copy of ids and a stream synchronisation (ggml-cuda.cu:2050-2075). */
+int64_t b200_mul_mat_id_q_scratch_bytes(int K, int n_used, int T, int n_expert);
+int b200_mul_mat_id_q(int type, const void * W, int64_t nb1, int n_expert, const float * X, int64_t x_sy, int64_t x_sz, int x_ne1,
+                      const int32_t * ids, int64_t ids_s1, int n_used, int T, float * dst, int64_t d_sy, int64_t d_sz,
+                      int N, int K, void * scratch, int64_t scratch_bytes, void * stream);
 
 /* Fusions of adjacent graph nodes over rows of K floats (K % 32 == 0, rows 16-byte aligned; -1 = shape not taken, run the nodes
  * one by one).  Every intermediate tensor is written exactly as the separate operators write it.

@@ -145,9 +145,19 @@ extern "C" int b200_op_mul_mat(const b200_tensor * a, const b200_tensor * b, con
     return -1;
 }
 
+// batches: rows sorted by expert + tensor-core MMQ (mmq.cu); a few tokens: one GEMV per (token, expert) pair
+static int mmq_id_min_t() { static const int v = [] { const char * e = getenv("B200_MMQ_ID_MIN_T"); return e ? atoi(e) : 9; }(); return v; }
+static bool use_mmq_id(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids) {
+    if (ids->ne[1] < mmq_id_min_t() || as->nb[2] != as->ne[1] * as->nb[1] || as->ne[2] > 4096 || (ids->nb[1] & 3) || ids->nb[0] != 4) return false;
+    return b200_mul_mat_q_supported(as->type, as->data, as->nb[1], (int)as->ne[0]) != 0 && (b->nb[1] & 3) == 0 && (b->nb[2] & 3) == 0;
+}
+extern "C" int64_t b200_mul_mat_id_scratch_bytes(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids) {
+    if (!is_quant(as->type) || !use_mmq_id(as, b, ids)) return 0;
+    return b200_mul_mat_id_q_scratch_bytes((int)as->ne[0], (int)ids->ne[0], (int)ids->ne[1], (int)as->ne[2]);
+}
+
 extern "C" int b200_op_mul_mat_id(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * dst,
                                   void * scratch, int64_t scratch_bytes, void * stream) {
-    (void)scratch; (void)scratch_bytes;
     if (!is_quant(as->type) || b->type != T_F32 || ids->type != T_I32 || dst->type != T_F32) return -1;
     if (as->ne[0] != b->ne[0] || b->nb[0] != 4 || dst->nb[0] != 4 || as->nb[0] != block_bytes(as->type)) return -1;
     if (as->ne[0] % block_elems(as->type) || as->ne[3] != 1 || b->ne[3] != 1) return -1;
@@ -158,6 +168,12 @@ extern "C" int b200_op_mul_mat_id(const b200_tensor * as, const b200_tensor * b,
     }
     if (T > 65535 || n_used > 65535) return -1;
     if (K == 0 || N == 0 || n_used == 0 || T == 0) return 0;
+    if (use_mmq_id(as, b, ids) && scratch && scratch_bytes >= b200_mul_mat_id_q_scratch_bytes(K, n_used, T, (int)as->ne[2])) {
+        const int rc = b200_mul_mat_id_q(as->type, as->data, as->nb[1], (int)as->ne[2], (const float *)b->data, b->nb[1] / 4, b->nb[2] / 4, (int)b->ne[1],
+                                         (const int32_t *)ids->data, ids->nb[1] / 4, n_used, T, (float *)dst->data, dst->nb[1] / 4, dst->nb[2] / 4,
+                                         N, K, scratch, scratch_bytes, stream);
+        if (rc != -1) return rc;
+    }
     b200_mmvq_args g = {};
     g.type = as->type; g.W = as->data; g.nb1 = as->nb[1];
     g.X = (const float *)b->data; g.xs = K;

@@ -294,6 +294,9 @@ struct mmq_params {
     int na;                      // depth of the A ring in tensor memory: 4 or 8 (even)
     int tmem_cols;               // 256 or 512
     long long * trace;           // debug: clock64 stamps of CTA (0,0), [event][index] (b200_mmq_debug_trace)
+    // MUL_MAT_ID (expert = blockIdx.z): activation rows sorted by expert; rows [off[e], off[e] + cnt[e]) belong to expert e,
+    // row m of the sorted list goes to dst + row_off[m]; the weight map stacks the experts' matrices (N rows each)
+    const int * moe_cnt; const int * moe_off; const int64_t * moe_row;
 };
 constexpr int TRACE_N = 512;
 #ifdef B200_MMQ_TRACE
@@ -322,7 +325,15 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
                    b_full = a_empty + 8 * NA_MAX, b_empty = b_full + 8 * NB_MAX, tmem_full = b_empty + 8 * NB_MAX, tmem_slot = tmem_full + 8;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * tn, n0 = blockIdx.y * 128;
+    int m0 = blockIdx.x * tn, m_end = p.M, w_row0 = blockIdx.y * 128;
+    const int n0 = blockIdx.y * 128;
+    if (p.moe_cnt) {                             // (launched without PDL: the routing tables are complete)
+        const int cnt = p.moe_cnt[blockIdx.z];
+        if (m0 >= cnt) return;                   // this expert has fewer tokens than the worst case the grid was sized for
+        m0 += p.moe_off[blockIdx.z];
+        m_end = p.moe_off[blockIdx.z] + cnt;
+        w_row0 += blockIdx.z * p.N;
+    }
     const int nkb = p.K >> 8, nsteps = nkb * 4;
     const uint32_t a_col0 = (uint32_t)p.tmem_cols - 32u * (uint32_t)na;
 
@@ -349,7 +360,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
                 mbar_wait_b(raw_empty + 8 * s, ((kb >> 1) & 1) ^ 1);
                 trace(p, 0, kb);
                 mbar_expect_tx(raw_full + 8 * s, RAW);
-                tma_load_2d(sR + s * RAW, &wmap, (kb * DQ::STEP16) & ~7, n0, raw_full + 8 * s);     // 16-byte aligned start
+                tma_load_2d(sR + s * RAW, &wmap, (kb * DQ::STEP16) & ~7, w_row0, raw_full + 8 * s);     // 16-byte aligned start
             }
         }
     } else if (warp == 3) {
@@ -448,7 +459,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const int m = m0 + c0 + j;
-                    if (m < p.M) p.dst[(int64_t)m * p.ds + n] = __uint_as_float(v[j]);
+                    if (m < m_end) p.dst[(p.moe_row ? p.moe_row[m] : (int64_t)m * p.ds) + n] = __uint_as_float(v[j]);
                 }
             }
         }
@@ -477,6 +488,45 @@ __global__ void __launch_bounds__(256) x_to_bf16_kernel(const float * __restrict
     }
     uint4 o; o.x = pack_bf16(f[0], f[1]); o.y = pack_bf16(f[2], f[3]); o.z = pack_bf16(f[4], f[5]); o.w = pack_bf16(f[6], f[7]);
     *reinterpret_cast<uint4 *>(out + ((int64_t)m * K + k) / 2) = o;
+}
+
+// ---- MUL_MAT_ID routing (reference ggml-cuda/ggml-cuda.cu:2010-2140 sorts the rows on the host after a
+// device->host copy of ids and a stream synchronisation; here the tables never leave the device) ----
+// One CTA: counts per expert, exclusive prefix, then the (token, slot) pairs in expert order.
+__global__ void __launch_bounds__(1024) moe_sort_kernel(const int32_t * __restrict__ ids, int64_t ids_s1, int n_used, int T, int n_expert,
+                                                        int * __restrict__ cnt, int * __restrict__ off, int2 * __restrict__ pairs) {
+    extern __shared__ int sm_moe[];              // [n_expert] counters, [n_expert] cursors
+    int * c = sm_moe, * cur = sm_moe + n_expert;
+    pdl_trigger(); pdl_wait();
+    for (int e = threadIdx.x; e < n_expert; e += blockDim.x) c[e] = 0;
+    __syncthreads();
+    const int total = n_used * T;
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+        const int e = ids[(int64_t)(i / n_used) * ids_s1 + i % n_used];
+        if (e >= 0 && e < n_expert) atomicAdd(&c[e], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int run = 0;
+        for (int e = 0; e < n_expert; ++e) { cur[e] = run; off[e] = run; cnt[e] = c[e]; run += c[e]; }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+        const int t = i / n_used, u = i % n_used;
+        const int e = ids[(int64_t)t * ids_s1 + u];
+        if (e >= 0 && e < n_expert) pairs[atomicAdd(&cur[e], 1)] = make_int2(t, u);
+    }
+}
+// One CTA per sorted row: its activations f32 -> bf16, and where its result goes.
+__global__ void __launch_bounds__(256) moe_gather_kernel(const float * __restrict__ X, int64_t x_sy, int64_t x_sz, int x_ne1, const int2 * __restrict__ pairs,
+                                                         const int * __restrict__ cnt, const int * __restrict__ off, int n_expert,
+                                                         uint32_t * __restrict__ out, int64_t * __restrict__ row_off, int64_t d_sy, int64_t d_sz, int K) {
+    const int slot = blockIdx.x;
+    if (slot >= off[n_expert - 1] + cnt[n_expert - 1]) return;        // ids outside [0, n_expert) leave the tail unused
+    const int2 tu = pairs[slot];
+    const float * src = X + (int64_t)tu.x * x_sz + (int64_t)(tu.y % x_ne1) * x_sy;
+    for (int k = threadIdx.x * 2; k < K; k += 512) out[((int64_t)slot * K + k) >> 1] = pack_bf16(src[k], src[k + 1]);
+    if (threadIdx.x == 0) row_off[slot] = (int64_t)tu.x * d_sz + (int64_t)tu.y * d_sy;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -519,7 +569,7 @@ static int choose_tn(int N, int M) {
 }
 
 template <int TYPE>
-static int mmq_launch(const CUtensorMap & wmap, const CUtensorMap & xmap, const mmq_params & p, size_t smem, cudaStream_t st) {
+static int mmq_launch(const CUtensorMap & wmap, const CUtensorMap & xmap, const mmq_params & p, size_t smem, cudaStream_t st, int n_expert = 0) {
     static size_t configured[16] = {0};  // per device
     int dev = 0;
     B200_CUDA_CHECK(cudaGetDevice(&dev));
@@ -528,11 +578,11 @@ static int mmq_launch(const CUtensorMap & wmap, const CUtensorMap & xmap, const 
         configured[dev & 15] = smem;
     }
     cudaLaunchConfig_t lc = {};
-    lc.gridDim = dim3((p.M + p.tn - 1) / p.tn, (p.N + 127) / 128, 1); lc.blockDim = dim3(MMQ_THREADS); lc.dynamicSmemBytes = smem; lc.stream = st;
+    lc.gridDim = dim3((p.M + p.tn - 1) / p.tn, (p.N + 127) / 128, n_expert > 0 ? n_expert : 1); lc.blockDim = dim3(MMQ_THREADS); lc.dynamicSmemBytes = smem; lc.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
-    lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+    lc.attrs = at; lc.numAttrs = pdl_default() && n_expert == 0 ? 1 : 0;       // the expert tables are read before griddepcontrol.wait
     B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, mmq_kernel<TYPE>, wmap, xmap, p));
     ++g_launches;
     return 0;
@@ -633,4 +683,74 @@ extern "C" int b200_mul_mat_q(int type, const void * W, int64_t nb1, const float
     const int rc = b200_convert_acts_bf16(X, xs, xb, K, M, stream);
     if (rc) return rc;
     return b200_mul_mat_q_bf16(type, W, nb1, xb, dst, ds, N, K, M, stream);
+}
+
+// ---- MUL_MAT_ID for batches: rows sorted by expert on the device, one MMQ grid over (token tiles, row tiles, experts) ----
+static int64_t align256(int64_t x) { return (x + 255) & ~(int64_t)255; }
+extern "C" int64_t b200_mul_mat_id_q_scratch_bytes(int K, int n_used, int T, int n_expert) {
+    const int64_t total = (int64_t)n_used * T;
+    return align256(2 * (int64_t)n_expert * 4) + align256(total * 8) + align256(total * 8) + align256(total * K * 2 + 256 * (int64_t)K * 2) + 256;
+}
+// W: n_expert matrices [N][K] of one quantised type, nb1 bytes between rows, experts N * nb1 apart.  X: f32 activations of
+// token t / slot u at X + t * x_sz + (u % x_ne1) * x_sy (floats).  ids: int32 [T][ids_s1], n_used per token.  dst row of
+// (t, u) at dst + t * d_sz + u * d_sy (floats).  Returns -1 for shapes this path does not take (the caller falls back).
+extern "C" int b200_mul_mat_id_q(int type, const void * W, int64_t nb1, int n_expert, const float * X, int64_t x_sy, int64_t x_sz, int x_ne1,
+                                 const int32_t * ids, int64_t ids_s1, int n_used, int T, float * dst, int64_t d_sy, int64_t d_sz,
+                                 int N, int K, void * scratch, int64_t scratch_bytes, void * stream) {
+    if (!b200_mul_mat_q_supported(type, W, nb1, K) || N <= 0 || T <= 0 || n_used <= 0 || n_expert <= 0 || n_expert > 4096 || x_ne1 <= 0) return -1;
+    if (!scratch || scratch_bytes < b200_mul_mat_id_q_scratch_bytes(K, n_used, T, n_expert)) return -2;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t total = (int64_t)n_used * T;
+    uint8_t * sp = (uint8_t *)(((uintptr_t)scratch + 255) & ~(uintptr_t)255);
+    int * cnt = (int *)sp; int * off = cnt + n_expert; sp += align256(2 * (int64_t)n_expert * 4);
+    int2 * pairs = (int2 *)sp; sp += align256(total * 8);
+    int64_t * row_off = (int64_t *)sp; sp += align256(total * 8);
+    uint8_t * xb = sp;                                                 // bf16 [total (+ one tile of slack)][K]
+
+    moe_sort_kernel<<<1, 1024, 2 * n_expert * sizeof(int), st>>>(ids, ids_s1, n_used, T, n_expert, cnt, off, pairs);
+    B200_CUDA_CHECK(cudaGetLastError());
+    moe_gather_kernel<<<(unsigned)total, 256, 0, st>>>(X, x_sy, x_sz, x_ne1, pairs, cnt, off, n_expert, (uint32_t *)xb, row_off, d_sy, d_sz, K);
+    B200_CUDA_CHECK(cudaGetLastError());
+    g_launches += 2;
+
+    mmq_params p = {};
+    p.dst = dst; p.ds = 0; p.N = N; p.K = K;
+    p.M = (int)total;                                                  // worst case per expert: every row routes to it (CTAs past the real count leave at once)
+    const int64_t avg = (total + n_expert - 1) / n_expert;
+    p.tn = env_int("B200_MMQ_ID_TN", 0);
+    if (p.tn != 32 && p.tn != 64 && p.tn != 128 && p.tn != 256) p.tn = avg <= 32 ? 32 : avg <= 64 ? 64 : avg <= 192 ? 128 : 256;
+    p.trace = nullptr;
+    p.nb = NB_MAX;
+    while (p.nb > 2 && mmq_smem(type, p.tn, p.nb) > 232448) --p.nb;
+    p.na = p.tn <= 128 ? 4 : NA_MAX;
+    p.tmem_cols = p.tn <= 128 ? 256 : 512;
+    if (mmq_smem(type, p.tn, p.nb) > 232448) return -3;
+    const size_t smem = mmq_smem(type, p.tn, p.nb);
+    p.moe_cnt = cnt; p.moe_off = off; p.moe_row = row_off;
+
+    CUtensorMap wmap, xmap;
+    {   // the experts' matrices stacked: [n_expert * N][nb1 / 2] 16-bit words
+        const cuuint64_t dims[2] = {(cuuint64_t)((int64_t)(K / block_elems(type)) * block_bytes(type) / 2), (cuuint64_t)N * (cuuint64_t)n_expert};
+        const cuuint64_t strides[1] = {(cuuint64_t)nb1};
+        const cuuint32_t box[2] = {(cuuint32_t)(raw_pitch(type) / 2), 128};
+        const cuuint32_t es[2] = {1, 1};
+        if (encode_tiled()(&wmap, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void *>(W), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return -4;
+    }
+    {   // sorted bf16 rows [total][K]
+        const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)total};
+        const cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+        const cuuint32_t box[2] = {64, (cuuint32_t)p.tn};
+        const cuuint32_t es[2] = {1, 1};
+        if (encode_tiled()(&xmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, xb, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return -5;
+    }
+    switch (type) {
+        case T_Q4_0: return mmq_launch<T_Q4_0>(wmap, xmap, p, smem, st, n_expert);
+        case T_Q8_0: return mmq_launch<T_Q8_0>(wmap, xmap, p, smem, st, n_expert);
+        case T_Q4_K: return mmq_launch<T_Q4_K>(wmap, xmap, p, smem, st, n_expert);
+        case T_Q5_K: return mmq_launch<T_Q5_K>(wmap, xmap, p, smem, st, n_expert);
+        case T_Q6_K: return mmq_launch<T_Q6_K>(wmap, xmap, p, smem, st, n_expert);
+    }
+    return -1;
 }

@@ -40,13 +40,15 @@ def lib():
             getattr(_lib, name).restype = C.c_int
         _lib.b200_quantized_acts_bytes.restype = C.c_int64
         _lib.b200_mul_mat_q_scratch_bytes.restype = C.c_int64
+        _lib.b200_mul_mat_id_q_scratch_bytes.restype = C.c_int64
+        _lib.b200_mul_mat_id_scratch_bytes.restype = C.c_int64
         _lib.b200_acts_bf16_bytes.restype = C.c_int64
         _lib.b200_flash_attn_scratch_bytes.restype = C.c_int64
     return _lib
 
 
 # every symbol include/b200_ops.h declares (tests/test_capi_symbols.py keeps this in sync)
-EXPORTS = ["b200_mul_mat_vec_q_ex", "b200_mul_mat_vec_q", "b200_mul_mat_vec_q_group", "b200_mmvq_supported_type", "b200_quantize_q8_1",
+EXPORTS = ["b200_mul_mat_id_q", "b200_peer_bcast", "b200_peer_wait", "b200_peer_signal", "b200_mul_mat_vec_q_ex", "b200_mul_mat_vec_q", "b200_mul_mat_vec_q_group", "b200_mmvq_supported_type", "b200_quantize_q8_1",
            "b200_dequantize_rows", "b200_kernel_launch_count", "b200_kernel_launch_add", "b200_quantize_acts", "b200_quantized_acts_bytes",
            "b200_op_binary", "b200_op_unary", "b200_op_scale", "b200_op_rms_norm", "b200_op_rope", "b200_op_cpy", "b200_op_cpy_indirect", "b200_op_cpy_supported",
            "b200_op_get_rows", "b200_op_soft_max", "b200_op_argsort", "b200_op_sum_rows", "b200_op_flash_attn_ext",
@@ -110,6 +112,25 @@ def mul_mat_q(t, W, X, N, K, nb1=None):
     _check(lib().b200_mul_mat_q(C.c_int(t), C.c_void_p(W.data_ptr()), C.c_int64(nb1), C.c_void_p(X.data_ptr()), C.c_int64(X.stride(0)),
                                 C.c_void_p(dst.data_ptr()), C.c_int64(N), C.c_int(N), C.c_int(K), C.c_int(M),
                                 C.c_void_p(scratch.data_ptr()), C.c_int64(need), _stream()), "b200_mul_mat_q")
+    return dst
+
+
+def mul_mat_id(t, W, X, ids, N, K, n_expert):
+    """GGML_OP_MUL_MAT_ID (quantised experts).  W: uint8 CUDA tensor holding n_expert matrices of N quantised rows each;
+    X: float32 [T, x_ne1, K] with x_ne1 = 1 (shared by the token's experts) or n_used; ids: int32 [T, n_used].
+    Returns dst [T, n_used, N].  From 9 tokens on the rows are sorted by expert and go through the tensor-core MMQ."""
+    assert W.is_cuda and X.is_cuda and ids.is_cuda and X.dtype == torch.float32 and ids.dtype == torch.int32
+    T, n_used = ids.shape
+    nb1 = row_bytes(t, K)
+    dst = torch.empty((T, n_used, N), dtype=torch.float32, device=X.device)
+    a = B200Tensor(); a.data = W.data_ptr(); a.type = t
+    a.ne[0], a.ne[1], a.ne[2], a.ne[3] = K, N, n_expert, 1
+    a.nb[0], a.nb[1], a.nb[2], a.nb[3] = nb1 // (K // {2: 32, 8: 32}.get(t, 256)), nb1, nb1 * N, nb1 * N * n_expert
+    b, i, d = as_b200(X), as_b200(ids), as_b200(dst)
+    need = lib().b200_mul_mat_id_scratch_bytes(C.byref(a), C.byref(b), C.byref(i))
+    scratch = torch.empty(max(need, 1), dtype=torch.uint8, device=X.device)
+    _check(lib().b200_op_mul_mat_id(C.byref(a), C.byref(b), C.byref(i), C.byref(d), C.c_void_p(scratch.data_ptr() if need else None),
+                                    C.c_int64(need), _stream()), "b200_op_mul_mat_id")
     return dst
 
 
