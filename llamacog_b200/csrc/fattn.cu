@@ -233,7 +233,11 @@ static int fa_launch(const fa_params & p, dim3 grid, cudaStream_t st) {
 
 // tensor-core kernel for batches of query rows (fattn_tc.cu); returns 0 when the shape is not its to take
 int fattn_tc_try(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst,
-                 float scale, float max_bias, float logit_softcap, cudaStream_t st, int * rc);
+                 float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc);
+int64_t fattn_tc_flag_bytes(const b200_tensor * q, const b200_tensor * k);
+int64_t fattn_tc_q8_scratch(const b200_tensor * q, const b200_tensor * k);
+int fattn_tc_try_q8(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst,
+                    float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc);
 
 }  // namespace b200
 
@@ -248,7 +252,10 @@ extern "C" int b200_flash_attn_supported(int k_type, int v_type, int64_t dk, int
 extern "C" int64_t b200_flash_attn_scratch_bytes(const b200_tensor * q, const b200_tensor * k) {
     const int64_t rows_heads = q->ne[1] * q->ne[2] * q->ne[3];
     const int ns = fa_splits(rows_heads, (int)((k->ne[1] + 31) / 32));
-    return ns > 1 ? rows_heads * ns * (2 + q->ne[0]) * 4 : 0;
+    const int64_t part = ns > 1 ? rows_heads * ns * (2 + q->ne[0]) * 4 : 0;
+    int64_t deq = fattn_tc_q8_scratch(q, k);                  // prefill over a q8_0 cache: f16 copies of K and V (+ mask tile flags)
+    if (deq == 0) deq = fattn_tc_flag_bytes(q, k);            // tensor-core kernel: one byte per 128 x 128 mask tile
+    return part > deq ? part : deq;
 }
 
 extern "C" int b200_op_flash_attn_ext(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
@@ -261,7 +268,8 @@ extern "C" int b200_op_flash_attn_ext(const b200_tensor * q, const b200_tensor *
     if (q->ne[1] == 0 || k->ne[1] == 0) return 0;
     {
         int rc = 0;
-        if (fattn_tc_try(q, k, v, mask, dst, scale, max_bias, logit_softcap, (cudaStream_t)stream, &rc)) return rc;
+        if (fattn_tc_try(q, k, v, mask, dst, scale, max_bias, logit_softcap, scratch, scratch_bytes, (cudaStream_t)stream, &rc)) return rc;
+        if (k->type == T_Q8_0 && fattn_tc_try_q8(q, k, v, mask, dst, scale, max_bias, logit_softcap, scratch, scratch_bytes, (cudaStream_t)stream, &rc)) return rc;
     }
     fa_params p = {};
     p.q = (const char *)q->data; p.k = (const char *)k->data; p.v = (const char *)v->data; p.mask = mask ? (const char *)mask->data : nullptr;

@@ -27,7 +27,39 @@ struct fat_params {
     int N, n_head, n_kv, rk2, rk3, mask_vec;
     float scale, softcap, max_bias, m0, m1;
     unsigned n_head_log2;
+    const uint8_t * flags;       // [q tiles][kv tiles] from mask_classify_kernel: 0 nothing to attend, 1 mixed, 2 mask is all zero
 };
+
+// ---- one pass over the mask for all heads: which 128 x 128 tiles are empty, which need no mask at all ----
+// (the attention kernel used to scan its 128 mask rows per CTA, once per head, with one thread per row: at 32k context
+// that scan and the per-element mask loads were most of the kernel's time)
+__global__ void __launch_bounds__(256) mask_classify_kernel(const char * __restrict__ mask, int64_t nbm1, int N, int n_kv, int nt, int vec,
+                                                            uint8_t * __restrict__ flags) {
+    pdl_trigger(); pdl_wait();
+    const int j = blockIdx.x, qt = blockIdx.y;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int lim = min(128, n_kv - 128 * j);
+    int any = 0, nz = 0;
+    for (int r = warp; r < 128; r += 8) {
+        const int qi = 128 * qt + r;
+        if (qi >= N) break;
+        const __half * row = reinterpret_cast<const __half *>(mask + (int64_t)qi * nbm1) + 128 * j;
+        if (vec && lim == 128) {
+            const uint2 u = __ldg(reinterpret_cast<const uint2 *>(row) + lane);
+            any |= (u.x != 0xFC00FC00u) | (u.y != 0xFC00FC00u);
+            nz |= ((u.x | u.y) & 0x7FFF7FFFu) != 0u;
+        } else {
+            for (int i = lane; i < lim; i += 32) {
+                const unsigned short h = __half_as_ushort(row[i]);
+                any |= h != 0xFC00u; nz |= (h & 0x7FFFu) != 0;
+            }
+        }
+    }
+    any = __syncthreads_or(any);
+    nz = __syncthreads_or(nz);
+    if (threadIdx.x == 0) flags[(int64_t)qt * nt + j] = !any ? 0 : ((nz || lim < 128) ? 1 : 2);
+}
+
 
 constexpr int FAT_THREADS = 192;
 constexpr int FAT_MAX_TILES = 512;
@@ -68,7 +100,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
         tma_prefetch_desc(&kmap); tma_prefetch_desc(&vmap);
     }
     if (warp == 1) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
-    for (int j = threadIdx.x; j < nt; j += FAT_THREADS) act[j] = p.mask ? 0 : 1;
+    for (int j = threadIdx.x; j < nt; j += FAT_THREADS) act[j] = p.mask ? 0 : (128 * (j + 1) <= p.n_kv ? 2 : 1);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -95,7 +127,9 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
         }
         fence_proxy_async();
         // ---- which KV tiles have anything to attend to? ----
-        if (p.mask) {
+        if (p.mask && p.flags) {
+            for (int j = threadIdx.x - 64; j < nt; j += FAT_THREADS - 64) act[j] = p.flags[(int64_t)blockIdx.x * nt + j];
+        } else if (p.mask) {
             for (int j = 0; j < nt; ++j) {
                 bool any = false;
                 if (mrow) {
@@ -118,7 +152,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
     __syncthreads();
     if (threadIdx.x == 0) {
         int n = 0;
-        for (int j = 0; j < nt; ++j) if (act[j]) tiles[n++] = (unsigned short)j;
+        for (int j = 0; j < nt; ++j) if (act[j]) tiles[n++] = (unsigned short)(j | (act[j] == 2 ? 0x8000 : 0));      // bit 15: no mask needed
         *nact_p = n;
     }
     __syncthreads();
@@ -128,7 +162,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
         if (lane == 0) {                         // TMA producer: K and V tiles of the active KV tiles, two stages each
             const int ik2 = iq2 / p.rk2, ik3 = iq3 / p.rk3;
             for (int jj = 0; jj < nact; ++jj) {
-                const int j = tiles[jj], st = jj & 1;
+                const int j = tiles[jj] & 0x7FFF, st = jj & 1;
                 const uint32_t ph = ((jj >> 1) & 1) ^ 1;
                 mbar_wait_b(k_empty + 8 * st, ph);
                 mbar_expect_tx(k_full + 8 * st, TILE);
@@ -179,7 +213,8 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
         const float sc2 = p.softcap != 0.0f ? p.scale : p.scale * LOG2E, ms2 = slope * LOG2E;
         float m = -INFINITY, l = 0.0f;           // running max (log2 domain) and sum
         for (int jj = 0; jj < nact; ++jj) {
-            const int j = tiles[jj], st = jj & 1;
+            const int j = tiles[jj] & 0x7FFF, st = jj & 1;
+            const bool nomask = (tiles[jj] & 0x8000) != 0;
             mbar_wait_b(s_full + 8 * st, (jj >> 1) & 1);
             tc_fence_after();
             float s[128];
@@ -197,6 +232,16 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
             // scale, softcap, mask (all in the log2 domain), positions past n_kv and rows past N are -inf
             const int lim = p.n_kv - 128 * j;
             float rmax = -INFINITY;
+            if (nomask) {                        // a whole tile, every row attends to every position: scale (and softcap) only
+#pragma unroll
+                for (int i = 0; i < 128; ++i) {
+                    float x = s[i] * sc2;
+                    if (p.softcap != 0.0f) x = p.softcap * LOG2E * tanhf(x);
+                    x = valid ? x : -INFINITY;
+                    s[i] = x;
+                    rmax = fmaxf(rmax, x);
+                }
+            } else
 #pragma unroll
             for (int g = 0; g < 16; ++g) {
                 float mv[8];
@@ -309,8 +354,12 @@ static int fat_launch(const CUtensorMap & kmap, const CUtensorMap & vmap, const 
 static int fat_min_rows() { static const int v = [] { const char * e = getenv("B200_FATTN_TC_MIN_ROWS"); return e ? atoi(e) : 9; }(); return v; }
 
 // 1 = launched, 0 = not applicable (the caller uses the vector kernel), < 0 / > 0 = error
+int64_t fattn_tc_flag_bytes(const b200_tensor * q, const b200_tensor * k) {
+    if (q->ne[1] < fat_min_rows() || k->ne[1] > 128 * FAT_MAX_TILES || (k->type != T_F16 && k->type != T_Q8_0)) return 0;
+    return ((((q->ne[1] + 127) / 128) * ((k->ne[1] + 127) / 128) + 255) & ~(int64_t)255) + 256;
+}
 int fattn_tc_try(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst,
-                 float scale, float max_bias, float logit_softcap, cudaStream_t st, int * rc) {
+                 float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc) {
     *rc = 0;
     const int D = (int)q->ne[0];
     if (k->type != T_F16 || v->type != T_F16 || (D != 64 && D != 128) || v->ne[0] != D) return 0;
@@ -339,8 +388,81 @@ int fattn_tc_try(const b200_tensor * q, const b200_tensor * k, const b200_tensor
     p.n_head_log2 = 1u << (unsigned)floorf(log2f((float)p.n_head));
     p.m0 = powf(2.0f, -max_bias / p.n_head_log2); p.m1 = powf(2.0f, -(max_bias / 2.0f) / p.n_head_log2);
     const dim3 grid((unsigned)((q->ne[1] + 127) / 128), (unsigned)(q->ne[2] * q->ne[3]));
+    const int64_t fbytes = fattn_tc_flag_bytes(q, k);
+    if (mask && scratch && fbytes > 0 && scratch_bytes >= fbytes) {
+        uint8_t * flags = reinterpret_cast<uint8_t *>(((uintptr_t)scratch + 255) & ~(uintptr_t)255);
+        const int nt = (int)((k->ne[1] + 127) / 128);
+        cudaLaunchConfig_t lc = {};
+        lc.gridDim = dim3((unsigned)nt, grid.x); lc.blockDim = dim3(256); lc.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+        if (cudaLaunchKernelEx(&lc, mask_classify_kernel, (const char *)mask->data, (int64_t)mask->nb[1], (int)q->ne[1], (int)k->ne[1], nt, (int)p.mask_vec, flags) != cudaSuccess) { *rc = -100; return 1; }
+        ++g_launches;
+        p.flags = flags;
+    }
     *rc = D == 128 ? fat_launch<128>(kmap, vmap, p, grid, st) : fat_launch<64>(kmap, vmap, p, grid, st);
     return 1;
+}
+
+// ---- q8_0 KV cache -> f16 for the tensor-core kernel (prefill over a quantised cache) ----
+// The reference dequantises K/V to f16 the same way before its tensor-core attention (ggml-cuda/fattn-common.cuh:700-760,
+// launch_fattn with need_f16_K / need_f16_V).  One thread per 32-element block.
+__global__ void __launch_bounds__(256) kv_q8_0_to_f16_kernel(const char * __restrict__ src, int64_t nb1, int64_t nb2, int64_t nb3,
+                                                             __half * __restrict__ dst, int D, int n_kv, int n_head) {
+    pdl_trigger(); pdl_wait();
+    const int bpr = D >> 5;
+    const int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (idx >= (int64_t)n_kv * bpr) return;
+    const int pos = (int)(idx / bpr), b = (int)(idx % bpr);
+    const int h = blockIdx.y % n_head, i3 = blockIdx.y / n_head;
+    const unsigned short * blk = reinterpret_cast<const unsigned short *>(src + (int64_t)pos * nb1 + (int64_t)h * nb2 + (int64_t)i3 * nb3 + (int64_t)b * 34);
+    const float d = __half2float(__ushort_as_half(blk[0]));
+    uint32_t out[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const unsigned short w = blk[1 + i];
+        const float lo = d * (float)(signed char)(w & 0xFF), hi = d * (float)(signed char)(w >> 8);
+        out[i] = (uint32_t)__half_as_ushort(__float2half_rn(lo)) | ((uint32_t)__half_as_ushort(__float2half_rn(hi)) << 16);
+    }
+    uint4 * o = reinterpret_cast<uint4 *>(dst + ((((int64_t)i3 * n_head + h) * n_kv + pos) * D + b * 32));
+#pragma unroll
+    for (int i = 0; i < 4; ++i) o[i] = make_uint4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
+}
+
+int64_t fattn_tc_q8_scratch(const b200_tensor * q, const b200_tensor * k) {
+    if (k->type != T_Q8_0 || q->ne[1] < fat_min_rows() || k->ne[1] > 128 * FAT_MAX_TILES || !encode_tiled()) return 0;
+    return 2 * ((k->ne[0] * k->ne[1] * k->ne[2] * k->ne[3] * 2 + 255) & ~(int64_t)255) + 256 + fattn_tc_flag_bytes(q, k);
+}
+
+// q8_0 K and V: dequantise into scratch, then the f16 kernel.  Returns 1 when it ran (rc = its status).
+int fattn_tc_try_q8(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst,
+                    float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc) {
+    *rc = 0;
+    const int64_t need = fattn_tc_q8_scratch(q, k);
+    if (need == 0 || v->type != T_Q8_0 || !scratch || scratch_bytes < need || v->ne[0] != k->ne[0] || v->ne[1] != k->ne[1] || v->ne[2] != k->ne[2] || v->ne[3] != k->ne[3]) return 0;
+    if (((k->nb[1] | k->nb[2] | k->nb[3] | v->nb[1] | v->nb[2] | v->nb[3]) & 1) || ((uintptr_t)k->data & 1) || ((uintptr_t)v->data & 1)) return 0;
+    const int D = (int)k->ne[0], n_kv = (int)k->ne[1], n_head = (int)k->ne[2];
+    b200_tensor kv[2];
+    for (int which = 0; which < 2; ++which) {
+        const b200_tensor * t = which ? v : k;
+        const int64_t fb = fattn_tc_flag_bytes(q, k);               // the mask flags sit in front
+        __half * out = reinterpret_cast<__half *>((((uintptr_t)scratch + 255) & ~(uintptr_t)255) + (uintptr_t)fb + (uintptr_t)which * (uintptr_t)((need - fb - 256) / 2));
+        cudaLaunchConfig_t lc = {};
+        lc.gridDim = dim3((unsigned)(((int64_t)n_kv * (D / 32) + 255) / 256), (unsigned)(t->ne[2] * t->ne[3])); lc.blockDim = dim3(256); lc.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+        if (cudaLaunchKernelEx(&lc, kv_q8_0_to_f16_kernel, (const char *)t->data, t->nb[1], t->nb[2], t->nb[3], out, D, n_kv, n_head) != cudaSuccess) { *rc = -100; return 1; }
+        ++g_launches;
+        b200_tensor & f = kv[which];
+        f.data = out; f.type = T_F16;
+        f.ne[0] = D; f.ne[1] = n_kv; f.ne[2] = t->ne[2]; f.ne[3] = t->ne[3];
+        f.nb[0] = 2; f.nb[1] = 2 * D; f.nb[2] = f.nb[1] * n_kv; f.nb[3] = f.nb[2] * t->ne[2];
+    }
+    return fattn_tc_try(q, &kv[0], &kv[1], mask, dst, scale, max_bias, logit_softcap, scratch, fattn_tc_flag_bytes(q, k), st, rc);
 }
 
 }  // namespace b200

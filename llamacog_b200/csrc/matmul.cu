@@ -52,8 +52,47 @@ __global__ void __launch_bounds__(256) mm_dense_kernel(const mm_params p) {
     }
 }
 
+// ---- few token columns (M <= 8): one CTA per weight row, K spread over the threads ----
+// (the router of a MoE layer: [n_embd] x [n_expert] in f32; K.Q and V.P of the non-flash attention path at decode)
+template <typename TA, typename TB>
+__global__ void __launch_bounds__(128) mv_dense_kernel(const mm_params p) {
+    pdl_trigger(); pdl_wait();
+    const int i12 = blockIdx.z % p.ne12, i13 = blockIdx.z / p.ne12;
+    const char * A = p.a + (int64_t)(i12 / p.r2) * p.nba2 + (int64_t)(i13 / p.r3) * p.nba3 + (int64_t)blockIdx.x * p.nba1;
+    const char * B = p.b + (int64_t)i12 * p.nbb2 + (int64_t)i13 * p.nbb3;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int k = threadIdx.x; k < p.K; k += 128) {
+        const float av = ld_f<TA>(A + (int64_t)k * p.nba0);
+#pragma unroll
+        for (int m = 0; m < 8; ++m) if (m < p.M) acc[m] = fmaf(av, ld_f<TB>(B + (int64_t)m * p.nbb1 + (int64_t)k * p.nbb0), acc[m]);
+    }
+    __shared__ float part[4][8];
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+        float v = acc[m];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5][m] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < p.M)
+        *(float *)(p.d + (int64_t)threadIdx.x * p.nbd1 + (int64_t)i12 * p.nbd2 + (int64_t)i13 * p.nbd3 + (int64_t)blockIdx.x * 4) =
+            part[0][threadIdx.x] + part[1][threadIdx.x] + part[2][threadIdx.x] + part[3][threadIdx.x];
+}
+
 template <typename TA, typename TB>
 static int mm_dense_launch(const mm_params & p, int nz, cudaStream_t st) {
+    if (p.M <= 8 && p.N <= 2147483647 / 1) {
+        cudaLaunchConfig_t lc = {};
+        lc.gridDim = dim3(p.N, 1, nz); lc.blockDim = dim3(128); lc.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+        B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, mv_dense_kernel<TA, TB>, p));
+        ++g_launches;
+        return 0;
+    }
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3((p.N + 31) / 32, (p.M + 31) / 32, nz); lc.blockDim = dim3(256); lc.stream = st;
     cudaLaunchAttribute at[1];

@@ -162,7 +162,7 @@ class B200Tensor(C.Structure):
     _fields_ = [("data", C.c_void_p), ("type", C.c_int), ("ne", C.c_int64 * 4), ("nb", C.c_int64 * 4)]
 
 
-_GGML_OF = {torch.float32: 0, torch.float16: 1, torch.int32: 26, torch.bfloat16: 30}
+_GGML_OF = {torch.float32: 0, torch.float16: 1, torch.int32: 26, torch.bfloat16: 30, torch.uint8: 24}       # uint8: raw blocks (I8 id as a placeholder; the caller sets the quantised type)
 
 
 def as_b200(t):
@@ -186,6 +186,9 @@ def flash_attn_ext(q, k, v, mask=None, scale=1.0, max_bias=0.0, logit_softcap=0.
     ne3, n_head, N, D = q.shape
     dst = torch.empty((ne3, N, n_head, D), dtype=torch.float32, device=q.device)
     tq, tk, tv, td = as_b200(q), as_b200(k), as_b200(v), as_b200(dst)
+    for t, x in ((tk, k), (tv, v)):
+        if x.dtype == torch.uint8:                   # q8_0 cache: uint8 [ne3, n_head_kv, n_kv, D / 32 * 34] holding block_q8_0 rows
+            t.type = 8; t.ne[0] = D; t.nb[0] = 34
     tm = as_b200(mask) if mask is not None else None
     need = lib().b200_flash_attn_scratch_bytes(C.byref(tq), C.byref(tk))
     scratch = torch.empty(max(int(need), 16), dtype=torch.uint8, device=q.device)

@@ -84,3 +84,28 @@ def test_kv_cache_view_layout():
     mask[:, 0] = 0
     out = _ops().flash_attn_ext(q, k, v, mask, 0.09)
     assert _nmse(out, _ref(q, k, v, mask, 0.09)) < 1e-5
+
+
+@pytest.mark.parametrize("D", [64, 128])
+@pytest.mark.parametrize("N,n_kv,n_past", [(1, 300, 299), (8, 512, 504), (9, 256, 247), (64, 512, 448), (130, 700, 570), (512, 2048, 1536)])
+def test_q8_0_kv_cache(D, N, n_kv, n_past):
+    """K and V stored as q8_0 (-ctk q8_0 -ctv q8_0): decode rows take the vector kernel (q8_1 x q8_0 integer dot products), 9 rows and
+    more dequantise the cache to f16 and take the tensor-core kernel.  Reference: fattn-vec-f32.cuh:72-126, fattn-common.cuh:700-760;
+    the oracle quantises with quantize_row_q8_0_ref (ggml-quants.c:198-231) and the expectation attends over the dequantised values."""
+    import numpy as np
+    import oracle as O
+    torch.manual_seed(N + n_kv + D + 1)
+    n_head, n_head_kv = 8, 2
+    q = torch.randn(1, n_head, N, D, device="cuda")
+    kf = torch.randn(1, n_head_kv, n_kv, D)
+    vf = torch.randn(1, n_head_kv, n_kv, D)
+    kq = O.quantize_row_q8_0_ref(kf.numpy().reshape(-1)); vq = O.quantize_row_q8_0_ref(vf.numpy().reshape(-1))
+    kd = torch.from_numpy(O.dequantize(O.QUANT_TYPES["q8_0"], kq, n_head_kv * n_kv, D)).reshape(1, n_head_kv, n_kv, D).cuda()
+    vd = torch.from_numpy(O.dequantize(O.QUANT_TYPES["q8_0"], vq, n_head_kv * n_kv, D)).reshape(1, n_head_kv, n_kv, D).cuda()
+    k8 = torch.from_numpy(kq).reshape(1, n_head_kv, n_kv, D // 32 * 34).cuda()
+    v8 = torch.from_numpy(vq).reshape(1, n_head_kv, n_kv, D // 32 * 34).cuda()
+    mask = _causal_mask(N, n_kv, n_past)
+    scale = 1.0 / math.sqrt(D)
+    out = _ops().flash_attn_ext(q, k8, v8, mask, scale)
+    ref = _ref(q, kd, vd, mask, scale)
+    assert _nmse(out, ref) < 5e-4, _nmse(out, ref)
