@@ -178,6 +178,200 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fa_params p) {
     }
 }
 
+// ---- grouped form: G query vectors that share one KV head (GQA heads x the rows of a small batch) per CTA ----
+// At long context the kernel above reads the cache once per (row, head): rk2 x N times more L2 traffic than the cache
+// holds.  Here lane j still owns KV position j of a 32-position tile, but its K row is loaded once and dotted with all G
+// queries (Q in shared memory, broadcast reads), and every V row chunk is loaded once and accumulated into G outputs.
+// Query g of CTA x: flat index x * G + g over (row, head-in-group), row-major.
+template <int KT, int VT, int D, int G>
+__global__ void __launch_bounds__(128) fattn_vec_gqa_kernel(const fa_params p) {
+    pdl_trigger(); pdl_wait();
+    constexpr int EV = D / 32, NW = 4;
+    __shared__ __align__(16) float qf[G][D];
+    __shared__ int qi[G][D / 4];
+    __shared__ float qd[G][D / 32];
+    __shared__ float wm[NW][G], wl[NW][G];
+    __shared__ float wacc[NW][G][D];
+
+    const int ikv = blockIdx.y % (p.n_head / p.rk2), iq3 = blockIdx.y / (p.n_head / p.rk2), split = blockIdx.z;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int ngq = p.N * p.rk2;                                  // queries that share this KV head
+    const int g0 = blockIdx.x * G;
+    for (int i = tid; i < G * D; i += 128) {
+        const int g = i / D, d = i % D, gq = g0 + g;
+        float x = 0.0f;
+        if (gq < ngq) x = reinterpret_cast<const float *>(p.q + (int64_t)(gq / p.rk2) * p.nbq1 + (int64_t)(ikv * p.rk2 + gq % p.rk2) * p.nbq2 + (int64_t)iq3 * p.nbq3)[d];
+        qf[g][d] = x;
+    }
+    __syncthreads();
+    if constexpr (KT == T_Q8_0) {
+        for (int b = warp; b < G * (D / 32); b += NW) {
+            const int g = b / (D / 32), bb = b % (D / 32);
+            const float x = qf[g][32 * bb + lane];
+            const float amax = warp_max(fabsf(x));
+            const float d = amax / 127.0f;
+            const int q = amax == 0.0f ? 0 : (int)roundf(x / d);
+            reinterpret_cast<int8_t *>(qi[g])[32 * bb + lane] = (int8_t)q;
+            if (lane == 0) qd[g][bb] = d;
+        }
+        __syncthreads();
+    }
+    float slope[G];
+    const __half * mrow[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const int gq = min(g0 + g, ngq - 1);
+        const unsigned h = (unsigned)(ikv * p.rk2 + gq % p.rk2);
+        slope[g] = p.max_bias > 0.0f ? (h < p.n_head_log2 ? powf(p.m0, (float)(h + 1)) : powf(p.m1, (float)(2 * (h - p.n_head_log2) + 1))) : 1.0f;
+        mrow[g] = p.mask ? reinterpret_cast<const __half *>(p.mask + (int64_t)(gq / p.rk2) * p.nbm1) : nullptr;
+    }
+    const char * kbase = p.k + (int64_t)ikv * p.nbk2 + (int64_t)(iq3 / p.rk3) * p.nbk3;
+    const char * vbase = p.v + (int64_t)ikv * p.nbv2 + (int64_t)(iq3 / p.rv3) * p.nbv3;
+
+    float M[G], L[G], acc[G][EV];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        M[g] = -INFINITY; L[g] = 0.0f;
+#pragma unroll
+        for (int e = 0; e < EV; ++e) acc[g][e] = 0.0f;
+    }
+    const int ntiles = (p.n_kv + 31) / 32;
+    const int t0 = split * p.tiles_per_split, t1 = min(ntiles, t0 + p.tiles_per_split);
+    for (int t = t0 + warp; t < t1; t += NW) {
+        const int ic = 32 * t + lane;
+        float s[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) s[g] = 0.0f;
+        const bool in = ic < p.n_kv;
+        if (in) {
+            const char * krow = kbase + (int64_t)ic * p.nbk1;
+            if constexpr (KT == T_F16) {
+                const uint4 * kp = reinterpret_cast<const uint4 *>(krow);
+#pragma unroll 4
+                for (int i = 0; i < D / 8; ++i) {
+                    const uint4 u = __ldg(kp + i);
+                    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+                    const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&u.z)), d = __half22float2(*reinterpret_cast<const __half2 *>(&u.w));
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        const float4 q0 = *reinterpret_cast<const float4 *>(&qf[g][8 * i]), q1 = *reinterpret_cast<const float4 *>(&qf[g][8 * i + 4]);
+                        float x = s[g];
+                        x = fmaf(a.x, q0.x, x); x = fmaf(a.y, q0.y, x); x = fmaf(b.x, q0.z, x); x = fmaf(b.y, q0.w, x);
+                        x = fmaf(c.x, q1.x, x); x = fmaf(c.y, q1.y, x); x = fmaf(d.x, q1.z, x); x = fmaf(d.y, q1.w, x);
+                        s[g] = x;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int b = 0; b < D / 32; ++b) {
+                    const char * blk = krow + 34 * b;
+                    const float dk = __half2float(__ushort_as_half((unsigned short)ldg_u16(blk)));
+                    int w[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) w[i] = (int)(ldg_u16(blk + 2 + 4 * i) | (ldg_u16(blk + 4 + 4 * i) << 16));
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        int a = 0;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) a = __dp4a(w[i], qi[g][8 * b + i], a);
+                        s[g] = fmaf(dk * qd[g][b], (float)a, s[g]);
+                    }
+                }
+            }
+        }
+        float pj[G];
+        bool any = false;
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            float x = -INFINITY;
+            if (in) {
+                const float mv = mrow[g] ? slope[g] * __half2float(mrow[g][ic]) : 0.0f;
+                if (mv != -INFINITY) {
+                    x = s[g] * p.scale;
+                    if (p.softcap != 0.0f) x = p.softcap * tanhf(x);
+                    x += mv;
+                }
+            }
+            const float tmax = warp_max(x);
+            if (tmax == -INFINITY) { pj[g] = 0.0f; continue; }          // this query sees nothing in the tile (warp-uniform)
+            any = true;
+            const float Mn = fmaxf(M[g], tmax);
+            const float corr = expf(M[g] - Mn);
+            pj[g] = expf(x - Mn);
+            L[g] = L[g] * corr + warp_sum(pj[g]);
+#pragma unroll
+            for (int e = 0; e < EV; ++e) acc[g][e] *= corr;
+            M[g] = Mn;
+        }
+        if (!any) continue;
+        const int nvalid = min(32, p.n_kv - 32 * t);
+        auto vstep = [&](int j) {
+            float vv[EV];
+            const char * vrow = vbase + (int64_t)(32 * t + j) * p.nbv1;
+            if constexpr (VT == T_F16) {
+                const __half * vp = reinterpret_cast<const __half *>(vrow) + EV * lane;
+                if constexpr (EV == 4) {
+                    const uint2 u = __ldg(reinterpret_cast<const uint2 *>(vp));
+                    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+                    vv[0] = a.x; vv[1] = a.y; vv[2] = b.x; vv[3] = b.y;
+                } else {
+#pragma unroll
+                    for (int e = 0; e < EV; ++e) vv[e] = __half2float(vp[e]);
+                }
+            } else {
+                const int d0 = EV * lane;
+                const char * blk = vrow + 34 * (d0 >> 5);
+                const float dv = __half2float(__ushort_as_half((unsigned short)ldg_u16(blk)));
+#pragma unroll
+                for (int e = 0; e < EV; e += 2) {
+                    const uint32_t w = ldg_u16(blk + 2 + (d0 & 31) + e);
+                    vv[e] = dv * (float)(int)(int8_t)(w & 0xFF); vv[e + 1] = dv * (float)(int)(int8_t)(w >> 8);
+                }
+            }
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                const float pv = __shfl_sync(0xffffffffu, pj[g], j);
+#pragma unroll
+                for (int e = 0; e < EV; ++e) acc[g][e] = fmaf(pv, vv[e], acc[g][e]);
+            }
+        };
+        if (nvalid == 32) {
+#pragma unroll 8
+            for (int j = 0; j < 32; ++j) vstep(j);
+        } else {
+            for (int j = 0; j < nvalid; ++j) vstep(j);
+        }
+    }
+
+    // combine the four warps, one query at a time
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        if (lane == 0) { wm[warp][g] = M[g]; wl[warp][g] = L[g]; }
+#pragma unroll
+        for (int e = 0; e < EV; ++e) wacc[warp][g][EV * lane + e] = acc[g][e];
+    }
+    __syncthreads();
+    for (int i = tid; i < G * D; i += 128) {
+        const int g = i / D, d = i % D, gq = g0 + g;
+        if (gq >= ngq) continue;
+        float Mc = wm[0][g];
+        for (int w = 1; w < NW; ++w) Mc = fmaxf(Mc, wm[w][g]);
+        float Lc = 0.0f, a = 0.0f;
+        for (int w = 0; w < NW; ++w) {
+            if (wm[w][g] == -INFINITY) continue;
+            const float f = expf(wm[w][g] - Mc);
+            Lc += wl[w][g] * f; a += wacc[w][g][d] * f;
+        }
+        const int64_t orow = ((int64_t)iq3 * p.N + gq / p.rk2) * p.n_head + ikv * p.rk2 + gq % p.rk2;
+        if (p.nsplit == 1) reinterpret_cast<float *>(p.dst + orow * p.nbd1)[d] = a / Lc;
+        else {
+            float * pr = p.part + (orow * p.nsplit + split) * (2 + D);
+            pr[2 + d] = a;
+            if (d == 0) { pr[0] = Mc; pr[1] = Lc; }
+        }
+    }
+}
+
 // merge the split-KV partials: one warp per output row
 template <int DV>
 __global__ void __launch_bounds__(128) fattn_combine_kernel(const float * __restrict__ part, char * __restrict__ dst, int64_t nbd1, int64_t nrows, int nsplit) {
@@ -231,6 +425,26 @@ static int fa_launch(const fa_params & p, dim3 grid, cudaStream_t st) {
     return 0;
 }
 
+template <int KT, int VT, int D, int G>
+static int fa_launch_gqa(const fa_params & p, dim3 grid, cudaStream_t st) {
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = grid; lc.blockDim = dim3(128); lc.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+    B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_vec_gqa_kernel<KT, VT, D, G>, p));
+    ++g_launches;
+    if (p.nsplit > 1) {
+        const int64_t nrows = (int64_t)p.N * p.n_head * p.ne3;
+        lc.gridDim = dim3((unsigned)((nrows * 32 + 127) / 128));
+        B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_combine_kernel<D>, (const float *)p.part, p.dst, p.nbd1, nrows, p.nsplit));
+        ++g_launches;
+    }
+    return 0;
+}
+static int fa_gqa_min_kv() { static const int v = [] { const char * e = getenv("B200_FATTN_GQA_MIN_KV"); return e ? atoi(e) : 512; }();  return v; }
+
 // tensor-core kernel for batches of query rows (fattn_tc.cu); returns 0 when the shape is not its to take
 int fattn_tc_try(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst,
                  float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc);
@@ -252,7 +466,8 @@ extern "C" int b200_flash_attn_supported(int k_type, int v_type, int64_t dk, int
 extern "C" int64_t b200_flash_attn_scratch_bytes(const b200_tensor * q, const b200_tensor * k) {
     const int64_t rows_heads = q->ne[1] * q->ne[2] * q->ne[3];
     const int ns = fa_splits(rows_heads, (int)((k->ne[1] + 31) / 32));
-    const int64_t part = ns > 1 ? rows_heads * ns * (2 + q->ne[0]) * 4 : 0;
+    int64_t part = ns > 1 ? rows_heads * ns * (2 + q->ne[0]) * 4 : 0;
+    if (k->ne[1] >= fa_gqa_min_kv() && q->ne[1] <= 64) part = std::max<int64_t>(part, rows_heads * 128 * (2 + q->ne[0]) * 4);      // grouped kernel: up to 128 splits
     int64_t deq = fattn_tc_q8_scratch(q, k);                  // prefill over a q8_0 cache: f16 copies of K and V (+ mask tile flags)
     if (deq == 0) deq = fattn_tc_flag_bytes(q, k);            // tensor-core kernel: one byte per 128 x 128 mask tile
     return part > deq ? part : deq;
@@ -284,6 +499,29 @@ extern "C" int b200_op_flash_attn_ext(const b200_tensor * q, const b200_tensor *
     p.m0 = powf(2.0f, -max_bias / p.n_head_log2); p.m1 = powf(2.0f, -(max_bias / 2.0f) / p.n_head_log2);
     const int ntiles = (p.n_kv + 31) / 32;
     const int64_t rows_heads = q->ne[1] * q->ne[2] * q->ne[3];
+    // long context, several queries per KV head (GQA and / or a few rows): the grouped kernel reads the cache once per group
+    if (p.n_kv >= fa_gqa_min_kv() && p.N * p.rk2 >= 2 && p.rk2 == p.rv2 && p.rk3 == p.rv3 && q->ne[2] % p.rk2 == 0) {
+        const int ngq = p.N * p.rk2;
+        const int G = ngq <= 4 ? 4 : 8;
+        const int nx = (ngq + G - 1) / G;
+        const int64_t ctas = (int64_t)nx * (q->ne[2] / p.rk2) * q->ne[3];
+        int ns = (int)std::min<int64_t>(std::max<int64_t>(1, (4 * 148 + ctas - 1) / ctas), std::max(1, ntiles / 4));
+        ns = std::max(1, std::min(ns, 128));
+        if (ns > 1 && (!scratch || scratch_bytes < rows_heads * ns * (2 + q->ne[0]) * 4)) ns = 1;
+        p.nsplit = ns;
+        p.tiles_per_split = (ntiles + ns - 1) / ns;
+        p.part = (float *)scratch;
+        const dim3 grid((unsigned)nx, (unsigned)((q->ne[2] / p.rk2) * q->ne[3]), (unsigned)ns);
+        cudaStream_t st = (cudaStream_t)stream;
+        const int D = (int)q->ne[0];
+        const bool f16 = k->type == T_F16;
+        if (G == 4) {
+            if (D == 128) return f16 ? fa_launch_gqa<T_F16, T_F16, 128, 4>(p, grid, st) : fa_launch_gqa<T_Q8_0, T_Q8_0, 128, 4>(p, grid, st);
+            return f16 ? fa_launch_gqa<T_F16, T_F16, 64, 4>(p, grid, st) : fa_launch_gqa<T_Q8_0, T_Q8_0, 64, 4>(p, grid, st);
+        }
+        if (D == 128) return f16 ? fa_launch_gqa<T_F16, T_F16, 128, 8>(p, grid, st) : fa_launch_gqa<T_Q8_0, T_Q8_0, 128, 8>(p, grid, st);
+        return f16 ? fa_launch_gqa<T_F16, T_F16, 64, 8>(p, grid, st) : fa_launch_gqa<T_Q8_0, T_Q8_0, 64, 8>(p, grid, st);
+    }
     p.nsplit = fa_splits(rows_heads, ntiles);
     if (p.nsplit > 1 && (!scratch || scratch_bytes < rows_heads * p.nsplit * (2 + q->ne[0]) * 4)) p.nsplit = 1;
     p.tiles_per_split = (ntiles + p.nsplit - 1) / p.nsplit;

@@ -43,7 +43,8 @@ def _causal_mask(N, n_kv, n_past, pad_q=64, pad_kv=256):
 
 @pytest.mark.parametrize("D", [64, 128])
 @pytest.mark.parametrize("N,n_kv,n_past", [(1, 300, 299), (8, 512, 504), (9, 256, 247), (32, 512, 480), (35, 1024, 100), (128, 128, 0),
-                                            (200, 200, 0), (512, 512, 0), (130, 700, 570), (512, 2048, 1536)])
+                                            (200, 200, 0), (512, 512, 0), (130, 700, 570), (512, 2048, 1536), (1, 4100, 4099), (3, 2000, 1990),
+                                            (5, 1500, 700)])
 def test_causal_gqa(D, N, n_kv, n_past):
     torch.manual_seed(N + n_kv + D)
     n_head, n_head_kv = 8, 2
@@ -87,7 +88,8 @@ def test_kv_cache_view_layout():
 
 
 @pytest.mark.parametrize("D", [64, 128])
-@pytest.mark.parametrize("N,n_kv,n_past", [(1, 300, 299), (8, 512, 504), (9, 256, 247), (64, 512, 448), (130, 700, 570), (512, 2048, 1536)])
+@pytest.mark.parametrize("N,n_kv,n_past", [(1, 300, 299), (8, 512, 504), (9, 256, 247), (64, 512, 448), (130, 700, 570), (512, 2048, 1536),
+                                            (1, 4100, 4099), (3, 2000, 1990)])
 def test_q8_0_kv_cache(D, N, n_kv, n_past):
     """K and V stored as q8_0 (-ctk q8_0 -ctv q8_0): decode rows take the vector kernel (q8_1 x q8_0 integer dot products), 9 rows and
     more dequantise the cache to f16 and take the tensor-core kernel.  Reference: fattn-vec-f32.cuh:72-126, fattn-common.cuh:700-760;
