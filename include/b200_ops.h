@@ -65,6 +65,12 @@ typedef struct b200_mmvq_args {
                                NULL): per channel [M][ceil(K/256)] items of 400 bytes; the kernel then copies
                                them instead of quantising X itself (better when K is large and N small) */
     int64_t xq_sy, xq_sz;   /* bytes between channels of Xq (same y wrap as X) */
+    /* optional hint: byte ranges (the next matmul's weights) that the CTAs pull into L2 with cp.async.bulk.prefetch
+     * once they have issued their own last weight load, so that HBM keeps streaming through the kernel's tail and the
+     * small kernels that follow.  No effect on results. */
+    int pf_n;               /* 0..3 */
+    const void * pf_ptr[3];
+    int64_t pf_bytes[3];
 } b200_mmvq_args;
 
 int b200_mul_mat_vec_q_ex(const b200_mmvq_args * args, void * stream);

@@ -144,6 +144,7 @@ extern "C" int b200_mmvq_supported_type(int type) {
 extern "C" int b200_kernel_launch_count(void) { return g_launches; }
 extern "C" int b200_kernel_launch_add(int n) { g_launches += n; return g_launches; }
 
+static void set_prefetch(mmvq_params & p, const b200_mmvq_args * a);
 extern "C" int b200_mul_mat_vec_q_ex(const b200_mmvq_args * a, void * stream) {
     if (!a || !b200_mmvq_supported_type(a->type)) return -1;
     if (a->K <= 0 || a->K % block_elems(a->type) || a->N <= 0 || a->M <= 0) return -1;
@@ -164,6 +165,7 @@ extern "C" int b200_mul_mat_vec_q_ex(const b200_mmvq_args * a, void * stream) {
         p.xq_sy = a->xq_sy; p.xq_sz = a->xq_sz;
         p.vec_ok = ((((uintptr_t)p.X) | ((uintptr_t)a->xs * 4) | ((uintptr_t)a->x_sy * 4) | ((uintptr_t)a->x_sz * 4)) & 15) == 0;
         p.dbg_sumi = a->dbg_sumi ? a->dbg_sumi + (int64_t)m0 * a->N * (a->K / 32) : nullptr;
+        if (m0 + mmax >= a->M) set_prefetch(p, a);
         mmvq_launch_cfg c = {};
         int rc = configure(a->type, a->N, a->K, mc, *a, p, c);
         if (rc) return rc;
@@ -173,6 +175,16 @@ extern "C" int b200_mul_mat_vec_q_ex(const b200_mmvq_args * a, void * stream) {
         ++g_launches;
     }
     return 0;
+}
+
+static void set_prefetch(mmvq_params & p, const b200_mmvq_args * a) {
+    p.pf_n = 0;
+    for (int i = 0; i < a->pf_n && i < 3; ++i) {
+        const uintptr_t q = ((uintptr_t)a->pf_ptr[i] + 15) & ~(uintptr_t)15;
+        const int64_t bytes = a->pf_bytes[i] - (int64_t)(q - (uintptr_t)a->pf_ptr[i]);
+        if (!a->pf_ptr[i] || bytes < 16) continue;
+        p.pf_ptr[p.pf_n] = (const uint8_t *)q; p.pf_bytes[p.pf_n] = bytes; ++p.pf_n;
+    }
 }
 
 // Several weight matrices (same type, K and row stride) times the same activations in one launch: q/k/v, gate/up.
@@ -190,6 +202,7 @@ extern "C" int b200_mul_mat_vec_q_group(const b200_mmvq_args * a, int ng, const 
     p.N = ntot; p.K = a->K;
     p.w_div_y = 1; p.w_div_z = 1; p.x_mod_y = 1 << 30;
     p.vec_ok = ((((uintptr_t)p.X) | ((uintptr_t)a->xs * 4)) & 15) == 0;
+    set_prefetch(p, a);
     b200_mmvq_args cfg = *a;
     uintptr_t align = 0;
     for (int g = 0; g < ng; ++g) align |= (uintptr_t)W[g];

@@ -61,6 +61,8 @@ struct mmvq_params {
     int ngroup;
     const uint8_t * Wg[3]; float * Dg[3]; int64_t dsg[3];
     int cta0[4], rows_qg[3], rows_remg[3];
+    // trailing L2 prefetch of the next matmul's weights (b200_mmvq_args.pf_*)
+    int pf_n; const uint8_t * pf_ptr[3]; int64_t pf_bytes[3];
 };
 
 template <int TYPE, int M, bool A16, bool DBG>
@@ -144,8 +146,25 @@ __global__ void __launch_bounds__(288, (M <= 4 ? 2 : 1)) mmvq_kernel(const mmvq_
                 }
             }
         };
+        // once this CTA's last weight load is queued: its share of the next matmul's weights -> L2 (hint only)
+        auto prefetch_next = [&]() {   // lane 0 only
+            const long long nct = (long long)gridDim.x * gridDim.y * gridDim.z;
+            const long long cta = blockIdx.x + (long long)gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
+            for (int r = 0; r < p.pf_n; ++r) {
+                const long long per = ((p.pf_bytes[r] + nct - 1) / nct + 15) & ~15ll;
+                long long lo = cta * per;
+                const long long hi = min(p.pf_bytes[r] & ~15ll, lo + per);
+                for (; lo < hi; lo += 16384) {
+                    const unsigned size = (unsigned)min(16384ll, hi - lo);
+                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p.pf_ptr[r] + lo), "r"(size) : "memory");
+                }
+            }
+        };
         // weights do not depend on the previous kernel: start streaming before the PDL wait
-        if (lane == 0) for (int g = 0; g < min(ngroups, p.nstages); ++g) issue(g);
+        if (lane == 0) {
+            for (int g = 0; g < min(ngroups, p.nstages); ++g) issue(g);
+            if (p.pf_n && ngroups <= p.nstages) prefetch_next();
+        }
         pdl_wait();   // dst may still be read by the previous grid; Xq is written by it
         if (p.Xq && lane == 0) {
             const uint8_t * xq = Xqc;
@@ -164,7 +183,10 @@ __global__ void __launch_bounds__(288, (M <= 4 ? 2 : 1)) mmvq_kernel(const mmvq_
                 Dc[(int64_t)m * ds + r0 + r] = s;
             }
             __syncwarp();
-            if (lane == 0 && g + p.nstages < ngroups) issue(g + p.nstages);
+            if (lane == 0 && g + p.nstages < ngroups) {
+                issue(g + p.nstages);
+                if (p.pf_n && g + p.nstages == ngroups - 1) prefetch_next();
+            }
         }
     } else {
         // ================= consumer warps =================

@@ -21,7 +21,8 @@ class MmvqArgs(C.Structure):
                 ("ny", C.c_int), ("nz", C.c_int), ("w_sy", C.c_int64), ("w_sz", C.c_int64), ("w_div_y", C.c_int),
                 ("w_div_z", C.c_int), ("x_sy", C.c_int64), ("x_sz", C.c_int64), ("x_mod_y", C.c_int),
                 ("d_sy", C.c_int64), ("d_sz", C.c_int64), ("ids", C.c_void_p), ("ids_sz", C.c_int64),
-                ("pdl", C.c_int), ("dbg_sumi", C.c_void_p), ("Xq", C.c_void_p), ("xq_sy", C.c_int64), ("xq_sz", C.c_int64)]
+                ("pdl", C.c_int), ("dbg_sumi", C.c_void_p), ("Xq", C.c_void_p), ("xq_sy", C.c_int64), ("xq_sz", C.c_int64),
+                ("pf_n", C.c_int), ("pf_ptr", C.c_void_p * 3), ("pf_bytes", C.c_int64 * 3)]
 
 
 _lib = None
@@ -48,7 +49,7 @@ def lib():
 
 
 # every symbol include/b200_ops.h declares (tests/test_capi_symbols.py keeps this in sync)
-EXPORTS = ["b200_mul_mat_id_q", "b200_peer_bcast", "b200_peer_wait", "b200_peer_signal", "b200_mul_mat_vec_q_ex", "b200_mul_mat_vec_q", "b200_mul_mat_vec_q_group", "b200_mmvq_supported_type", "b200_quantize_q8_1",
+EXPORTS = ["b200_mul_mat_id_q", "b200_mul_mat_id_q_scratch_bytes", "b200_mul_mat_id_scratch_bytes", "b200_peer_bcast", "b200_peer_wait", "b200_peer_signal", "b200_mul_mat_vec_q_ex", "b200_mul_mat_vec_q", "b200_mul_mat_vec_q_group", "b200_mmvq_supported_type", "b200_quantize_q8_1",
            "b200_dequantize_rows", "b200_kernel_launch_count", "b200_kernel_launch_add", "b200_quantize_acts", "b200_quantized_acts_bytes",
            "b200_op_binary", "b200_op_unary", "b200_op_scale", "b200_op_rms_norm", "b200_op_rope", "b200_op_cpy", "b200_op_cpy_indirect", "b200_op_cpy_supported",
            "b200_op_get_rows", "b200_op_soft_max", "b200_op_argsort", "b200_op_sum_rows", "b200_op_flash_attn_ext",
