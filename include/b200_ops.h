@@ -166,6 +166,13 @@ int b200_op_sum_rows(const b200_tensor * src, const b200_tensor * dst, void * st
 int b200_op_flash_attn_ext(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
                            const b200_tensor * dst, float scale, float max_bias, float logit_softcap,
                            void * scratch, int64_t scratch_bytes, void * stream);
+/* same, and (xq != NULL) the result also as the pre-quantised activations of the GEMV that consumes it (b200_quantize_acts
+ * layout for K = D * n_head, row m at xq + m * ceil(K / 256) * 400): saves the quantisation launch of a decode step.
+ * Only for shapes b200_flash_attn_xq_supported accepts (decode rows, D = 128, one sequence). */
+int b200_flash_attn_xq_supported(const b200_tensor * q, const b200_tensor * k);
+int b200_op_flash_attn_ext_xq(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
+                              const b200_tensor * dst, float scale, float max_bias, float logit_softcap,
+                              void * scratch, int64_t scratch_bytes, void * xq, void * stream);
 int64_t b200_flash_attn_scratch_bytes(const b200_tensor * q, const b200_tensor * k);
 int b200_flash_attn_supported(int k_type, int v_type, int64_t dk, int64_t dv);
 /* MUL_MAT: dst[N, M, b2, b3] = src0[K, N, a2, a3] x src1[K, M, b2, b3], src0 broadcast over dims 2,3.

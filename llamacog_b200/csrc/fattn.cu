@@ -9,7 +9,7 @@
 //   online softmax per tile with warp reductions (reference ggml-cpu/ops.cpp:7141-7209);
 //   P.V:    lanes own D/32 output dims, V rows are read coalesced, p_j arrives by shuffle.
 // K and V are strided views of the cache (nb1/nb2/nb3 honoured); GQA by index division.
-#include "common.cuh"
+#include "mmvq_units.cuh"
 #include "../../include/b200_ops.h"
 
 #include <algorithm>
@@ -25,6 +25,7 @@ struct fa_params {
     int nsplit, tiles_per_split;
     float scale, max_bias, softcap, m0, m1;
     unsigned n_head_log2;
+    uint8_t * xq; uint32_t xq_acs;         // optional (DV = 128, ne3 = 1): the result also as q8 activations of the next GEMV, acs bytes per row
 };
 
 __device__ __forceinline__ uint32_t ldg_u16(const void * p) { return *reinterpret_cast<const unsigned short *>(p); }
@@ -166,11 +167,18 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fa_params p) {
     float Lc = 0.0f;
     for (int w = 0; w < NW; ++w) Lc += wm[w] == -INFINITY ? 0.0f : wl[w] * expf(wm[w] - Mc);
     const int64_t orow = ((int64_t)iq3 * p.N + iq1) * p.n_head + iq2;
+    __shared__ __align__(16) float fin[DV];
     for (int d = tid; d < DV; d += 128) {
         float a = 0.0f;
         for (int w = 0; w < NW; ++w) a += wm[w] == -INFINITY ? 0.0f : wacc[w][d] * expf(wm[w] - Mc);
-        if (p.nsplit == 1) reinterpret_cast<float *>(p.dst + orow * p.nbd1)[d] = a / Lc;
+        if (p.nsplit == 1) { const float o = a / Lc; reinterpret_cast<float *>(p.dst + orow * p.nbd1)[d] = o; fin[d] = o; }
         else p.part[(orow * p.nsplit + split) * (2 + DV) + 2 + d] = a;
+    }
+    if constexpr (DV == 128) {
+        if (p.xq && p.nsplit == 1) {             // head iq2 = blocks 4*iq2 .. 4*iq2+3 of row iq1 in the GEMV's activation layout
+            __syncthreads();
+            if (warp == 0) quant_block_store(*reinterpret_cast<const float4 *>(&fin[4 * lane]), 4 * iq2 + (lane >> 3), lane & 7, true, p.xq + (size_t)iq1 * p.xq_acs);
+        }
     }
     if (p.nsplit > 1 && tid == 0) {
         p.part[(orow * p.nsplit + split) * (2 + DV)] = Mc;
@@ -374,7 +382,8 @@ __global__ void __launch_bounds__(128) fattn_vec_gqa_kernel(const fa_params p) {
 
 // merge the split-KV partials: one warp per output row
 template <int DV>
-__global__ void __launch_bounds__(128) fattn_combine_kernel(const float * __restrict__ part, char * __restrict__ dst, int64_t nbd1, int64_t nrows, int nsplit) {
+__global__ void __launch_bounds__(128) fattn_combine_kernel(const float * __restrict__ part, char * __restrict__ dst, int64_t nbd1, int64_t nrows, int nsplit,
+                                                            uint8_t * __restrict__ xq, uint32_t xq_acs, int n_head) {
     pdl_trigger(); pdl_wait();
     const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -395,7 +404,13 @@ __global__ void __launch_bounds__(128) fattn_combine_kernel(const float * __rest
     }
     float * out = reinterpret_cast<float *>(dst + r * nbd1);
 #pragma unroll
-    for (int e = 0; e < DV / 32; ++e) out[(DV / 32) * lane + e] = a[e] / Lc;
+    for (int e = 0; e < DV / 32; ++e) { a[e] = a[e] / Lc; out[(DV / 32) * lane + e] = a[e]; }
+    if constexpr (DV == 128) {
+        if (xq) {                                // r = row * n_head + head (ne3 = 1); the warp is uniform in r
+            const int head = (int)(r % n_head);
+            quant_block_store(make_float4(a[0], a[1], a[2], a[3]), 4 * head + (lane >> 3), lane & 7, true, xq + (size_t)(r / n_head) * xq_acs);
+        }
+    }
 }
 
 static int fa_splits(int64_t rows_heads, int ntiles) {
@@ -419,7 +434,7 @@ static int fa_launch(const fa_params & p, dim3 grid, cudaStream_t st) {
     if (p.nsplit > 1) {
         const int64_t nrows = (int64_t)p.N * p.n_head * p.ne3;
         lc.gridDim = dim3((unsigned)((nrows * 32 + 127) / 128));
-        B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_combine_kernel<D>, (const float *)p.part, p.dst, p.nbd1, nrows, p.nsplit));
+        B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_combine_kernel<D>, (const float *)p.part, p.dst, p.nbd1, nrows, p.nsplit, p.xq, p.xq_acs, p.n_head));
         ++g_launches;
     }
     return 0;
@@ -438,7 +453,7 @@ static int fa_launch_gqa(const fa_params & p, dim3 grid, cudaStream_t st) {
     if (p.nsplit > 1) {
         const int64_t nrows = (int64_t)p.N * p.n_head * p.ne3;
         lc.gridDim = dim3((unsigned)((nrows * 32 + 127) / 128));
-        B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_combine_kernel<D>, (const float *)p.part, p.dst, p.nbd1, nrows, p.nsplit));
+        B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_combine_kernel<D>, (const float *)p.part, p.dst, p.nbd1, nrows, p.nsplit, p.xq, p.xq_acs, p.n_head));
         ++g_launches;
     }
     return 0;
@@ -476,6 +491,17 @@ extern "C" int64_t b200_flash_attn_scratch_bytes(const b200_tensor * q, const b2
 extern "C" int b200_op_flash_attn_ext(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
                                       const b200_tensor * dst, float scale, float max_bias, float logit_softcap,
                                       void * scratch, int64_t scratch_bytes, void * stream) {
+    return b200_op_flash_attn_ext_xq(q, k, v, mask, dst, scale, max_bias, logit_softcap, scratch, scratch_bytes, nullptr, stream);
+}
+
+extern "C" int b200_flash_attn_xq_supported(const b200_tensor * q, const b200_tensor * k) {
+    return q->ne[0] == 128 && q->ne[3] == 1 && q->ne[1] >= 1 && q->ne[1] <= 8 && (k->type == T_F16 || k->type == T_Q8_0);
+}
+
+extern "C" int b200_op_flash_attn_ext_xq(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
+                                         const b200_tensor * dst, float scale, float max_bias, float logit_softcap,
+                                         void * scratch, int64_t scratch_bytes, void * xq, void * stream) {
+    if (xq && !b200_flash_attn_xq_supported(q, k)) return -1;
     if (!b200_flash_attn_supported(k->type, v->type, k->ne[0], v->ne[0]) || q->type != T_F32 || dst->type != T_F32) return -1;
     if (q->ne[0] != k->ne[0] || q->nb[0] != 4 || dst->nb[0] != 4 || k->ne[1] != v->ne[1]) return -1;
     if (mask && (mask->type != T_F16 || mask->nb[0] != 2 || mask->ne[0] < k->ne[1])) return -1;
@@ -497,6 +523,7 @@ extern "C" int b200_op_flash_attn_ext(const b200_tensor * q, const b200_tensor *
     p.scale = scale; p.max_bias = max_bias; p.softcap = logit_softcap;
     p.n_head_log2 = 1u << (unsigned)floorf(log2f((float)p.n_head));
     p.m0 = powf(2.0f, -max_bias / p.n_head_log2); p.m1 = powf(2.0f, -(max_bias / 2.0f) / p.n_head_log2);
+    p.xq = (uint8_t *)xq; p.xq_acs = (uint32_t)(((q->ne[0] * q->ne[2] + 255) / 256) * ACT_ITEM);
     const int ntiles = (p.n_kv + 31) / 32;
     const int64_t rows_heads = q->ne[1] * q->ne[2] * q->ne[3];
     // long context, several queries per KV head (GQA and / or a few rows): the grouped kernel reads the cache once per group
@@ -508,6 +535,7 @@ extern "C" int b200_op_flash_attn_ext(const b200_tensor * q, const b200_tensor *
         int ns = (int)std::min<int64_t>(std::max<int64_t>(1, (4 * 148 + ctas - 1) / ctas), std::max(1, ntiles / 4));
         ns = std::max(1, std::min(ns, 128));
         if (ns > 1 && (!scratch || scratch_bytes < rows_heads * ns * (2 + q->ne[0]) * 4)) ns = 1;
+        if (xq && ns == 1) return -1;              // (the grouped kernel writes activations through the combine kernel only)
         p.nsplit = ns;
         p.tiles_per_split = (ntiles + ns - 1) / ns;
         p.part = (float *)scratch;
