@@ -131,6 +131,8 @@ static int mmvq_dispatch(int type, const mmvq_params & p, const mmvq_launch_cfg 
 }
 
 int g_launches = 0;
+int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * const * dst, const int * N, cudaStream_t stream);   // mmvq_r.cu
+constexpr int MMVQR_SKIP = -777;
 int pdl_default() { static const int v = [] { const char * e = getenv("B200_PDL"); return e ? atoi(e) : 1; }(); return v; }
 
 }  // namespace b200
@@ -150,6 +152,11 @@ extern "C" int b200_mul_mat_vec_q_ex(const b200_mmvq_args * a, void * stream) {
     if (a->K <= 0 || a->K % block_elems(a->type) || a->N <= 0 || a->M <= 0) return -1;
     const int mmax = max_cols_per_launch(a->K);
     if (mmax <= 0) return -2;
+    {   // batch-1 decode on pre-quantised activations: register-resident kernel (mmvq_r.cuh)
+        const void * W1[1] = { a->W }; float * D1[1] = { a->dst }; const int N1[1] = { a->N };
+        const int rc = mmvqr_try(a, 1, W1, D1, N1, (cudaStream_t)stream);
+        if (rc != MMVQR_SKIP) return rc;
+    }
     const int pdl_env = pdl_default();
     for (int m0 = 0; m0 < a->M; m0 += mmax) {
         const int mc = std::min(mmax, a->M - m0);
@@ -195,6 +202,10 @@ extern "C" int b200_mul_mat_vec_q_group(const b200_mmvq_args * a, int ng, const 
     if (std::max(1, a->ny) != 1 || std::max(1, a->nz) != 1 || a->ids || a->dbg_sumi) return -1;
     int ntot = 0;
     for (int g = 0; g < ng; ++g) { if (N[g] <= 0) return -1; ntot += N[g]; }
+    {
+        const int rc = mmvqr_try(a, ng, W, dst, N, (cudaStream_t)stream);
+        if (rc != MMVQR_SKIP) return rc;
+    }
     mmvq_params p = {};
     p.W = (const uint8_t *)W[0]; p.nb1 = a->nb1;
     p.X = a->X; p.xs = a->xs; p.Xq = (const uint8_t *)a->Xq;

@@ -1,0 +1,272 @@
+// mmvq_r.cuh -- batch-1 decode GEMV with REGISTER-RESIDENT activations (sm_100a), v3 of the decode mat-vec.
+//
+// Same operator as mmvq.cuh (reference ggml-cuda/mmvq.cu:140-224 mul_mat_vec_q + quantize.cu:4-49), for the case
+// that dominates a decode step: one activation column (M = 1), already quantised by the kernel that produced it
+// (b200_quantize_acts layout, mmvq_units.cuh), K-quant weights in whole contiguous rows.
+//
+// Why a second kernel: in mmvq.cuh every thread reads its 256-weight item (144 B) AND the matching activations
+// (400 B) from shared memory, so a 14336x4096 Q4_K GEMV moves 5x more bytes through the 128 B/clk shared-memory
+// pipe than through HBM and is bound by it (ncu: 0.5 IPC per scheduler, r01_mmvq_v2_notes.md).  Here a thread owns
+// a fixed HALF-ITEM column h of the row (128 weights: blocks 4h..4h+3 of its super-block) for the whole life of
+// the CTA, so its 128 int8 activations + 4 scales + 4 sums live in ~40 registers, loaded ONCE (one bulk copy of the column into shared memory per CTA, then 12 LDS.128 per thread); per row it
+// reads only 16 B of header + 64 B of codes from shared memory.  Shared-memory traffic drops from 688 to 304 B per
+// 256 weights, instructions from ~300 to ~2 x 120.
+//
+//   warp 0      producer + epilogue: 1-D TMA bulk copies of R whole rows per stage (issued before the PDL wait,
+//               so the weights stream while the previous kernel of the decode step is still running), then per
+//               stage the fixed-order sum of the per-warp partials and a coalesced store of dst.
+//   warps 1..8  consumers: thread (rsub, h) with h = ct % TPR, rsub = ct / TPR (TPR = threads per row = the power
+//               of two >= 2*K/256; lanes h >= 2*K/256 idle).  A pass covers 256/TPR rows; two passes are in
+//               flight per thread (independent shared loads and dp4a chains), row sums by xor-shuffle over
+//               min(TPR, 32) lanes + one partial per warp in shared memory.
+//
+// The CTA is sized for HALF an SM (<= 113 KB, 288 threads, <= 112 registers) and the default grid is one CTA per
+// SM: two consecutive GEMVs of a decode step are co-resident, the second one prefetching its weights into its own
+// stages while the first computes -- HBM does not idle at kernel boundaries.
+//
+// Integer block sums are those of vecdotq.cuh:359-381 (q4_K) and 478-498 (q6_K), bit-exact (dbg hook); the fp32
+// combination order is fixed (deterministic) but ours.
+#pragma once
+#include "mmvq_units.cuh"
+
+namespace b200 {
+
+struct mmvqr_params {
+    const uint8_t * Wg[3];   // weight matrices (contiguous 16-byte aligned rows of rb bytes)
+    float * Dg[3];           // outputs
+    int cta0[4];             // CTAs [cta0[g], cta0[g+1]) work on matrix g
+    int rows_qg[3], rows_remg[3];
+    int ngroup;
+    const uint8_t * Xq;      // quantised activations of the one column
+    int K, BPR;              // BPR = K/256 items per row
+    int TPR, lgTPR;          // threads per row (power of two >= 2*BPR, <= 256)
+    int rb;                  // bytes per row
+    int R;                   // rows per stage (multiple of 256/TPR)
+    int nstages, stage_bytes;
+    int32_t * dbg_sumi;      // parity hook: [N][K/32] int32 block sums (single matrix only)
+};
+
+struct hacts { int q[4][8]; float d8[4], dsq[4]; int m32a[4], m32b[4]; };
+
+// sp: shared address of the thread's 192 bytes (4 blocks of 48) inside the staged copy of Xq
+__device__ __forceinline__ void load_hacts(uint32_t sp, hacts & a) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int4 t0 = lds128(sp + 48 * k), t1 = lds128(sp + 48 * k + 16), t2 = lds128(sp + 48 * k + 32);
+        a.q[k][0] = t0.x; a.q[k][1] = t0.y; a.q[k][2] = t0.z; a.q[k][3] = t0.w;
+        a.q[k][4] = t1.x; a.q[k][5] = t1.y; a.q[k][6] = t1.z; a.q[k][7] = t1.w;
+        a.d8[k] = __int_as_float(t2.x); a.dsq[k] = __int_as_float(t2.y); a.m32a[k] = t2.z; a.m32b[k] = t2.w;
+    }
+}
+
+// raw half-item of weights in registers
+template <int TYPE> struct hweights;
+template <> struct hweights<T_Q4_K> { int hd[4]; int w[16]; };
+template <> struct hweights<T_Q6_K> { int ql[16]; int qh[8]; int sc[2]; uint32_t d; };
+
+// ip: shared address of the item, hh: which half
+template <int TYPE> __device__ __forceinline__ void load_hweights(uint32_t ip, int hh, hweights<TYPE> & w) {
+    if constexpr (TYPE == T_Q4_K) {
+        lds_words<4, true>(ip, w.hd);
+        lds_words<16, true>(ip + 16 + 64 * hh, w.w);
+    } else {
+        lds_words_a2<16>(ip + 64 * hh, w.ql);
+        lds_words_a2<8>(ip + 128 + 32 * hh, w.qh);
+        lds_words_a2<2>(ip + 192 + 8 * hh, w.sc);
+        w.d = lds16(ip + 208);
+    }
+}
+
+template <int TYPE, bool DBG>
+__device__ __forceinline__ float half_dot(const hweights<TYPE> & w, const hacts & a, int hh, int32_t * dbg) {
+    if constexpr (TYPE == T_Q4_K) {
+        const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&w.hd[0]));
+        const uint32_t h1 = (uint32_t)w.hd[1], h2 = (uint32_t)w.hd[2], h3 = (uint32_t)w.hd[3];
+        // 6-bit (scale, min) of blocks 4hh..4hh+3 as packed bytes (reference ggml-quants.c:625-632)
+        const uint32_t sc4 = hh ? ((h3 & 0x0F0F0F0Fu) | ((h1 >> 2) & 0x30303030u)) : (h1 & 0x3F3F3F3Fu);
+        const uint32_t mn4 = hh ? (((h3 >> 4) & 0x0F0F0F0Fu) | ((h2 >> 2) & 0x30303030u)) : (h2 & 0x3F3F3F3Fu);
+        float accd = 0.0f, accm = 0.0f;
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            int s0a = 0, s0b = 0, s1a = 0, s1b = 0;
+#pragma unroll
+            for (int j = 0; j < 8; j += 2) {
+                const uint32_t q0 = (uint32_t)w.w[8 * p + j], q1 = (uint32_t)w.w[8 * p + j + 1];
+                s0a = dp4a_us(q0 & 0x0F0F0F0Fu, a.q[2 * p][j], s0a);
+                s0b = dp4a_us(q1 & 0x0F0F0F0Fu, a.q[2 * p][j + 1], s0b);
+                s1a = dp4a_us(q0 & 0xF0F0F0F0u, a.q[2 * p + 1][j], s1a);       // 16 x nibble, divided out below
+                s1b = dp4a_us(q1 & 0xF0F0F0F0u, a.q[2 * p + 1][j + 1], s1b);
+            }
+            const int s0 = s0a + s0b, s1 = (s1a + s1b) >> 4;
+            if constexpr (DBG) { dbg[2 * p] = s0; dbg[2 * p + 1] = s1; }
+            accd = fmaf(a.d8[2 * p], i2f_small(s0) * byte2f(sc4, 2 * p), accd);
+            accd = fmaf(a.d8[2 * p + 1], i2f_small(s1) * byte2f(sc4, 2 * p + 1), accd);
+            accm = fmaf(a.dsq[2 * p], byte2f(mn4, 2 * p), accm);
+            accm = fmaf(a.dsq[2 * p + 1], byte2f(mn4, 2 * p + 1), accm);
+        }
+        return dm.x * accd - dm.y * accm;
+    } else {
+        const float d = half_bits_to_float(w.d);
+        float acc6 = 0.0f;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            int sa = a.m32a[g], sb = a.m32b[g];        // -32 * sum q: folds the -32 offset of the 6-bit code
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t l4 = (uint32_t)w.ql[8 * (g & 1) + j], h4 = (uint32_t)w.qh[j];
+                const uint32_t nib = (g < 2 ? l4 : (l4 >> 4)) & 0x0F0F0F0Fu;
+                const uint32_t top = (g == 0 ? (h4 << 4) : g == 1 ? (h4 << 2) : g == 2 ? h4 : (h4 >> 2)) & 0x30303030u;
+                if (j < 4) sa = dp4a_us(nib | top, a.q[g][j], sa); else sb = dp4a_us(nib | top, a.q[g][j], sb);
+            }
+            const int sca = (int)(int8_t)((uint32_t)w.sc[g >> 1] >> (16 * (g & 1)));
+            const int scb = (int)(int8_t)((uint32_t)w.sc[g >> 1] >> (16 * (g & 1) + 8));
+            if constexpr (DBG) dbg[g] = sa + sb;
+            acc6 = fmaf(a.d8[g], i2f_small(sa * sca + sb * scb), acc6);
+        }
+        return d * acc6;
+    }
+}
+
+template <int TYPE, int U, bool DBG>
+__global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
+    constexpr int IB = item_traits<TYPE>::BYTES;
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int NW = p.TPR > 32 ? p.TPR >> 5 : 1;            // partials per row
+    const int RPP = 256 >> p.lgTPR;                        // rows per pass
+
+    uint8_t * stages = smem_raw;
+    uint8_t * act = smem_raw + (size_t)p.nstages * p.stage_bytes;                                  // BPR items of 400 bytes
+    float * partials = reinterpret_cast<float *>(act + (size_t)p.BPR * ACT_ITEM);                  // [nstages][R][NW]
+    const int part_stage = p.R * NW;
+    uint64_t * bars = reinterpret_cast<uint64_t *>(partials + (((size_t)p.nstages * part_stage + 1) & ~(size_t)1));
+    const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * p.nstages, actbar = empty0 + 8 * p.nstages;
+
+    int cta = blockIdx.x, g = 0;
+    while (g + 1 < p.ngroup && cta >= p.cta0[g + 1]) ++g;
+    cta -= p.cta0[g];
+    const uint8_t * Wc = p.Wg[g];
+    float * Dc = p.Dg[g];
+    const int row_lo = cta * p.rows_qg[g] + min(cta, p.rows_remg[g]);
+    const int nrows = p.rows_qg[g] + (cta < p.rows_remg[g] ? 1 : 0);
+    const int row_hi = row_lo + nrows;
+    const int nst = (nrows + p.R - 1) / p.R;
+
+    if (tid == 0) {
+        for (int s = 0; s < p.nstages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 8); }
+        mbar_init(actbar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    pdl_trigger();            // the next kernel of the step may become resident and start its own weight stream
+
+    if (warp == 0) {
+        const uint64_t pol = policy_evict_first();
+        auto issue = [&](int s) {   // lane 0 only
+            const int slot = s % p.nstages;
+            const int r0 = row_lo + s * p.R, nr = min(p.R, row_hi - r0);
+            const uint32_t bytes = (uint32_t)nr * p.rb, bar = full0 + 8 * slot;
+            mbar_expect_tx(bar, bytes);
+            bulk_g2s_stream(smem_u32(stages + (size_t)slot * p.stage_bytes), Wc + (int64_t)r0 * p.rb, bytes, bar, pol);
+        };
+        if (lane == 0) for (int s = 0; s < min(nst, p.nstages); ++s) issue(s);
+        pdl_wait();           // the activations come from the previous kernel; dst may still be read by it
+        if (lane == 0) {      // one coalesced copy of the column; the consumers pick their registers out of shared memory
+            const uint32_t ab = (uint32_t)p.BPR * ACT_ITEM;
+            mbar_expect_tx(actbar, ab);
+            bulk_g2s(smem_u32(act), p.Xq, ab, actbar);
+        }
+        for (int s = 0; s < nst; ++s) {
+            const int slot = s % p.nstages;
+            mbar_wait(empty0 + 8 * slot, (s / p.nstages) & 1);
+            const int r0 = row_lo + s * p.R, nr = min(p.R, row_hi - r0);
+            const float * ps = partials + (size_t)slot * part_stage;
+            for (int o = lane; o < nr; o += 32) {
+                float sum = 0.0f;
+                for (int wv = 0; wv < NW; ++wv) sum += ps[o * NW + wv];
+                Dc[r0 + o] = sum;
+            }
+            __syncwarp();
+            if (lane == 0 && s + p.nstages < nst) issue(s + p.nstages);
+        }
+    } else {
+        const int ct = tid - 32;
+        const int h = ct & (p.TPR - 1), rsub = ct >> p.lgTPR;
+        const bool active = h < 2 * p.BPR;
+        const int b = h >> 1, hh = h & 1;
+        const int wir = h >> 5;                              // warp inside the row (TPR > 32)
+        const int red = min(p.TPR, 32);
+        hacts a;
+        mbar_wait(actbar, 0);
+        if (active) load_hacts(smem_u32(act) + (uint32_t)b * ACT_ITEM + hh * (4 * ACT_BLK), a);
+        const uint32_t ioff = (uint32_t)b * IB;
+        const int nb32 = p.K >> 5;
+        for (int s = 0; s < nst; ++s) {
+            const int slot = s % p.nstages;
+            const int r0 = row_lo + s * p.R, nr = min(p.R, row_hi - r0);
+            mbar_wait(full0 + 8 * slot, (s / p.nstages) & 1);
+            const uint32_t sbase = smem_u32(stages + (size_t)slot * p.stage_bytes) + ioff;
+            float * pw = partials + (size_t)slot * part_stage;
+            // U passes (rows rr, rr + RPP, ..) in flight per thread: independent shared loads and dp4a chains
+            for (int rr = rsub; rr - rsub < nr; rr += U * RPP) {
+                hweights<TYPE> w[U];
+                float x[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+                    if (active && rr + u * RPP < nr) load_hweights<TYPE>(sbase + (uint32_t)(rr + u * RPP) * p.rb, hh, w[u]);
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    x[u] = 0.0f;
+                    if (active && rr + u * RPP < nr)
+                        x[u] = half_dot<TYPE, DBG>(w[u], a, hh, DBG ? p.dbg_sumi + (int64_t)(r0 + rr + u * RPP) * nb32 + 8 * b + 4 * hh : nullptr);
+                }
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    if (o < red) {
+#pragma unroll
+                        for (int u = 0; u < U; ++u) x[u] += __shfl_xor_sync(0xffffffffu, x[u], o);
+                    }
+                }
+                if ((lane & (red - 1)) == 0) {
+#pragma unroll
+                    for (int u = 0; u < U; ++u)
+                        if (rr + u * RPP < nr) pw[(rr + u * RPP) * NW + wir] = x[u];
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty0 + 8 * slot);
+        }
+    }
+}
+
+constexpr int MMVQR_SKIP = -777;
+struct mmvqr_launch_cfg { dim3 grid; size_t smem; int pdl; int U; };
+template <int TYPE> int mmvqr_launch_type(const mmvqr_params & p, const mmvqr_launch_cfg & c, cudaStream_t stream);
+
+template <int TYPE, int U, bool DBG>
+static int mmvqr_launch_one(const mmvqr_params & p, const mmvqr_launch_cfg & c, cudaStream_t stream) {
+    auto kern = mmvqr_kernel<TYPE, U, DBG>;
+    static int smem_set[16] = {0};   // per device
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 16 && !smem_set[dev]) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+        smem_set[dev] = 1;
+    }
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = c.grid; lc.blockDim = dim3(288, 1, 1); lc.dynamicSmemBytes = c.smem; lc.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = c.pdl ? 1 : 0;
+    B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, kern, p));
+    return 0;
+}
+
+#define B200_MMVQR_DEFINE(TYPE_) \
+    template <> int mmvqr_launch_type<TYPE_>(const mmvqr_params & p, const mmvqr_launch_cfg & c, cudaStream_t stream) { \
+        if (p.dbg_sumi) return c.U == 2 ? mmvqr_launch_one<TYPE_, 2, true>(p, c, stream) : mmvqr_launch_one<TYPE_, 1, true>(p, c, stream); \
+        return c.U == 2 ? mmvqr_launch_one<TYPE_, 2, false>(p, c, stream) : mmvqr_launch_one<TYPE_, 1, false>(p, c, stream); \
+    }
+
+}  // namespace b200

@@ -98,6 +98,23 @@ def mul_mat_vec_q(t, W, X, N, K, nb1=None, dbg=False, pdl=-1, Xq=None):
     return (dst, sums) if dbg else dst
 
 
+def mul_mat_vec_q_group(t, Ws, Ns, X, K, Xq=None, pdl=-1):
+    """Up to three weight matrices of one type and K times the same activations in ONE launch (q/k/v, gate/up of a decode
+    step; b200_mul_mat_vec_q_group).  Ws: uint8 CUDA tensors, Ns: their row counts; X float32 [M, K].  Returns a list of
+    dst [M, N_g]."""
+    assert X.is_cuda and X.dtype == torch.float32 and X.stride(-1) == 1 and 1 <= len(Ws) <= 3
+    M, ng = X.shape[0], len(Ws)
+    dsts = [torch.empty((M, n), dtype=torch.float32, device=X.device) for n in Ns]
+    a = MmvqArgs(type=t, W=Ws[0].data_ptr(), nb1=row_bytes(t, K), X=X.data_ptr(), xs=X.stride(0), dst=dsts[0].data_ptr(), ds=Ns[0],
+                 N=Ns[0], K=K, M=M, ny=1, nz=1, pdl=pdl, Xq=Xq.data_ptr() if Xq is not None else None)
+    Wp = (C.c_void_p * ng)(*[w.data_ptr() for w in Ws])
+    Dp = (C.c_void_p * ng)(*[d.data_ptr() for d in dsts])
+    Np = (C.c_int * ng)(*Ns)
+    dsp = (C.c_int64 * ng)(*Ns)
+    _check(lib().b200_mul_mat_vec_q_group(C.byref(a), C.c_int(ng), Wp, Dp, Np, dsp, _stream()), "b200_mul_mat_vec_q_group")
+    return dsts
+
+
 def mul_mat_q(t, W, X, N, K, nb1=None):
     """Batched quantised mat-mul on the tensor cores (GGML_OP_MUL_MAT, quantised src0, M > 8 tokens).
     W: uint8 CUDA tensor of N quantised rows (16-byte aligned, a few bytes of slack after the last row);

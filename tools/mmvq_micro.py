@@ -58,8 +58,11 @@ def main():
             pool = [rand_weights(t, wbytes, dev) for _ in range(min(copies, 48))]
             X = torch.rand((M, K), device=dev) * 2 - 1
             prequant = os.environ.get("MICRO_XQ", "0") == "1"
+            xq_once = ops.quantize_acts(X) if os.environ.get("MICRO_XQ", "0") == "2" else None
 
             def run(Wm):
+                if xq_once is not None:   # activations quantised once by their producer (the decode step's normal case)
+                    return ops.mul_mat_vec_q(t, Wm, X, N, K, Xq=xq_once)
                 if prequant:   # separate quantise kernel + GEMV on pre-quantised activations
                     return ops.mul_mat_vec_q(t, Wm, X, N, K, Xq=ops.quantize_acts(X))
                 return ops.mul_mat_vec_q(t, Wm, X, N, K)
