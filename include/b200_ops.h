@@ -83,6 +83,15 @@ int b200_mul_mat_vec_q_group(const b200_mmvq_args * args, int ng, const void * c
                              const int64_t * ds, void * stream);
 int b200_mmvq_supported_type(int type);
 
+/* ---- kernel timeline trace (debug tooling, not on any product path) ----------------------------
+ * After b200_ktrace_enable() thread 0 of block 0 of every kernel of this library records the global timer at kernel
+ * entry and when it passes its programmatic-dependent-launch wait; b200_ktrace_dump writes the events as text
+ * ("<ns> <gridid> <event> <ctas> <threads>" per line).  Shows a decode step as it runs under CUDA-graph replay with PDL
+ * overlap, which a serialising profiler cannot.  The plugin enables it when B200_KTRACE=<file> is set. */
+int b200_ktrace_enable(void);
+int b200_ktrace_dump(const char * path);
+
+
 /* ---- activation quantisation as a stand-alone op ---------------------------------------------
  * Replaces quantize_row_q8_1_cuda (ggml/src/ggml-cuda/quantize.cu:4-49,145-157): x fp32 [nrows][k]
  * (row stride xs floats) -> block_q8_1 rows of k_pad/32 blocks, zero padded beyond k. */

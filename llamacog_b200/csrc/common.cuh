@@ -91,9 +91,41 @@ __device__ __forceinline__ void bulk_g2s_stream(uint32_t dst, const void * src, 
 __device__ __forceinline__ uint64_t policy_evict_first() {
     uint64_t p; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p;
 }
+// ---- kernel timeline trace (debug; b200_ktrace_enable / b200_ktrace_dump, ktrace.cu) ------------------------------
+// Every kernel of the library enters through pdl_trigger() and passes pdl_wait() before it touches what the previous
+// kernel wrote, so hooking these two gives a timeline of a whole decode step as it really runs (CUDA graph replay, PDL
+// overlap) -- which ncu, serialising the launches, cannot show.  Thread 0 of block 0 appends
+// (globaltimer, gridid, event, grid size, block size); off (null pointer in constant memory) it costs one predicate.
+// Events 0 = entry, 1 = PDL wait passed; kernels may add their own phase marks (2..15).
+static __constant__ unsigned long long * c_ktrace;      // one copy per translation unit, all set by b200_ktrace_enable
+constexpr unsigned long long KTRACE_CAP = 1ull << 20;   // events
+__device__ __forceinline__ void ktrace_event(int ev) {
+    unsigned long long * t = c_ktrace;
+    if (t != nullptr && (threadIdx.x | blockIdx.x | blockIdx.y | blockIdx.z) == 0) {
+        unsigned long long now, gid;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        asm volatile("mov.u64 %0, %%gridid;" : "=l"(gid));
+        const unsigned long long slot = atomicAdd(t, 1ull);
+        if (slot < KTRACE_CAP) {
+            t[1 + 2 * slot] = now;
+            t[2 + 2 * slot] = (gid << 32) | ((unsigned long long)(gridDim.x * gridDim.y * gridDim.z & 0x1FFFF) << 15) |
+                              ((unsigned long long)(blockDim.x & 0x7FF) << 4) | (unsigned long long)(ev & 15);
+        }
+    }
+}
+void ktrace_register(int (*setter)(unsigned long long *));
+namespace {
+struct ktrace_registrar {
+    ktrace_registrar() {
+        ktrace_register([](unsigned long long * p) -> int { return (int)cudaMemcpyToSymbol(c_ktrace, &p, sizeof(p)); });
+    }
+};
+static ktrace_registrar ktrace_registrar_instance;
+}
+
 // programmatic dependent launch: wait for the producer grid / allow the dependent grid to start
-__device__ __forceinline__ void pdl_wait()    { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait()    { asm volatile("griddepcontrol.wait;" ::: "memory"); ktrace_event(1); }
+__device__ __forceinline__ void pdl_trigger() { ktrace_event(0); asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -36,9 +36,12 @@ __device__ __forceinline__ float k_dot(const char * krow, const float * qf, cons
     float s = 0.0f;
     if constexpr (KT == T_F16) {
         const uint4 * kp = reinterpret_cast<const uint4 *>(krow);      // rows of the cache are 16-byte aligned
-#pragma unroll 4
+        uint4 kr[D / 8];                                               // the whole row in flight at once: one L2 round trip
+#pragma unroll
+        for (int i = 0; i < D / 8; ++i) kr[i] = __ldg(kp + i);
+#pragma unroll
         for (int i = 0; i < D / 8; ++i) {
-            const uint4 u = __ldg(kp + i);
+            const uint4 u = kr[i];
             const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
             const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&u.z)), d = __half22float2(*reinterpret_cast<const __half2 *>(&u.w));
             const float4 q0 = *reinterpret_cast<const float4 *>(qf + 8 * i), q1 = *reinterpret_cast<const float4 *>(qf + 8 * i + 4);
@@ -90,10 +93,49 @@ __device__ __forceinline__ void v_accum(const char * vrow, int lane, float p, fl
     }
 }
 
+// the same accumulation split into load and use, so that the loads of many KV positions can be in flight together
+struct vfrag { uint32_t a, b; };
+template <int VT, int DV>
+__device__ __forceinline__ vfrag v_load(const char * vrow, int lane) {
+    constexpr int E = DV / 32;
+    vfrag f; f.a = 0; f.b = 0;
+    if constexpr (VT == T_F16) {
+        if constexpr (E == 4) { const uint2 u = __ldg(reinterpret_cast<const uint2 *>(vrow) + lane); f.a = u.x; f.b = u.y; }
+        else f.a = __ldg(reinterpret_cast<const uint32_t *>(vrow) + lane);
+    } else {
+        const int d0 = E * lane;
+        const char * blk = vrow + 34 * (d0 >> 5);
+        f.b = ldg_u16(blk);
+        f.a = ldg_u16(blk + 2 + (d0 & 31));
+        if constexpr (E == 4) f.a |= ldg_u16(blk + 4 + (d0 & 31)) << 16;
+    }
+    return f;
+}
+template <int VT, int DV>
+__device__ __forceinline__ void v_fma(const vfrag f, float p, float (&acc)[DV / 32]) {
+    constexpr int E = DV / 32;
+    static_assert(E == 2 || E == 4, "head sizes 64 and 128");
+    if constexpr (VT == T_F16) {
+        const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&f.a));
+        acc[0] = fmaf(p, a.x, acc[0]); acc[1] = fmaf(p, a.y, acc[1]);
+        if constexpr (E == 4) {
+            const float2 b = __half22float2(*reinterpret_cast<const __half2 *>(&f.b));
+            acc[2] = fmaf(p, b.x, acc[2]); acc[3] = fmaf(p, b.y, acc[3]);
+        }
+    } else {
+        const float pd = p * __half2float(__ushort_as_half((unsigned short)f.b));
+#pragma unroll
+        for (int e = 0; e < E; ++e) acc[e] = fmaf(pd, (float)(int)(int8_t)((f.a >> (8 * e)) & 0xFF), acc[e]);
+    }
+}
+
+// Decode at short context is pure latency: 8 warps so that up to 256 positions are one tile per warp, the mask value and
+// the whole K row of a lane's position are requested together, and the V rows of 16 positions are in flight at a time
+// (kernel timeline, profiles/r01_ktrace_tg_v4.txt: 11.5 us per layer with dependent loads -> see v5).
 template <int KT, int VT, int DK, int DV>
-__global__ void __launch_bounds__(128) fattn_vec_kernel(const fa_params p) {
+__global__ void __launch_bounds__(256) fattn_vec_kernel(const fa_params p) {
     pdl_trigger(); pdl_wait();
-    constexpr int EV = DV / 32, NW = 4;
+    constexpr int EV = DV / 32, NW = 8;
     __shared__ __align__(16) float qf[DK];
     __shared__ int qi[DK / 4];
     __shared__ float qd[DK / 32];
@@ -103,7 +145,7 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fa_params p) {
     const int iq1 = blockIdx.x, iq2 = blockIdx.y % p.n_head, iq3 = blockIdx.y / p.n_head, split = blockIdx.z;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const float * qrow = reinterpret_cast<const float *>(p.q + iq1 * p.nbq1 + iq2 * p.nbq2 + iq3 * p.nbq3);
-    for (int i = tid; i < DK; i += 128) qf[i] = qrow[i];
+    for (int i = tid; i < DK; i += 32 * NW) qf[i] = qrow[i];
     __syncthreads();
     if constexpr (KT == T_Q8_0) {
         // quantise Q per 32 values (q8_0 arithmetic of the CPU path: d = amax/127, q = roundf(x/d))
@@ -118,6 +160,7 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fa_params p) {
         __syncthreads();
     }
 
+    ktrace_event(2);
     const unsigned h = iq2;
     const float slope = p.max_bias > 0.0f ? (h < p.n_head_log2 ? powf(p.m0, (float)(h + 1)) : powf(p.m1, (float)(2 * (h - p.n_head_log2) + 1))) : 1.0f;
     const char * kbase = p.k + (iq2 / p.rk2) * p.nbk2 + (iq3 / p.rk3) * p.nbk3;
@@ -134,14 +177,18 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fa_params p) {
         const int ic = 32 * t + lane;
         float s = -INFINITY;
         if (ic < p.n_kv) {
+            // the K row is requested together with the mask value (a masked position costs a wasted row read, an unmasked
+            // one saves a dependent round trip); its dot product is dropped by the select below
             const float mv = mrow ? slope * __half2float(mrow[ic]) : 0.0f;
+            const float sd = k_dot<KT, DK>(kbase + (int64_t)ic * p.nbk1, qf, qi, qd) * p.scale;
             if (mv != -INFINITY) {
-                s = k_dot<KT, DK>(kbase + (int64_t)ic * p.nbk1, qf, qi, qd) * p.scale;
+                s = sd;
                 if (p.softcap != 0.0f) s = p.softcap * tanhf(s);
                 s += mv;
             }
         }
         const float tmax = warp_max(s);
+        ktrace_event(3);
         if (tmax == -INFINITY) continue;            // whole tile masked (warp-uniform)
         const float Mn = fmaxf(M, tmax);
         const float corr = expf(M - Mn);            // M = -inf -> 0
@@ -150,14 +197,26 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fa_params p) {
 #pragma unroll
         for (int e = 0; e < EV; ++e) acc[e] *= corr;
         M = Mn;
+        ktrace_event(4);
         const int nvalid = min(32, p.n_kv - 32 * t);
-        for (int j = 0; j < nvalid; ++j) {
-            const float pv = __shfl_sync(0xffffffffu, pj, j);
-            if (pv != 0.0f) v_accum<VT, DV>(vbase + (int64_t)(32 * t + j) * p.nbv1, lane, pv, acc);
+        constexpr int VB = 16;                      // V rows in flight per lane
+        for (int j0 = 0; j0 < nvalid; j0 += VB) {
+            float pv[VB]; vfrag vf[VB];
+#pragma unroll
+            for (int jj = 0; jj < VB; ++jj) {
+                pv[jj] = __shfl_sync(0xffffffffu, pj, (j0 + jj) & 31);
+                if (j0 + jj >= nvalid) pv[jj] = 0.0f;
+                vf[jj].a = 0; vf[jj].b = 0;
+                if (pv[jj] != 0.0f) vf[jj] = v_load<VT, DV>(vbase + (int64_t)(32 * t + j0 + jj) * p.nbv1, lane);
+            }
+#pragma unroll
+            for (int jj = 0; jj < VB; ++jj)
+                if (pv[jj] != 0.0f) v_fma<VT, DV>(vf[jj], pv[jj], acc);
         }
     }
 
-    // combine the four warps
+    // combine the warps
+    ktrace_event(5);
     if (lane == 0) { wm[warp] = M; wl[warp] = L; }
 #pragma unroll
     for (int e = 0; e < EV; ++e) wacc[warp][EV * lane + e] = acc[e];
@@ -168,7 +227,7 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fa_params p) {
     for (int w = 0; w < NW; ++w) Lc += wm[w] == -INFINITY ? 0.0f : wl[w] * expf(wm[w] - Mc);
     const int64_t orow = ((int64_t)iq3 * p.N + iq1) * p.n_head + iq2;
     __shared__ __align__(16) float fin[DV];
-    for (int d = tid; d < DV; d += 128) {
+    for (int d = tid; d < DV; d += 32 * NW) {
         float a = 0.0f;
         for (int w = 0; w < NW; ++w) a += wm[w] == -INFINITY ? 0.0f : wacc[w][d] * expf(wm[w] - Mc);
         if (p.nsplit == 1) { const float o = a / Lc; reinterpret_cast<float *>(p.dst + orow * p.nbd1)[d] = o; fin[d] = o; }
@@ -184,6 +243,151 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fa_params p) {
         p.part[(orow * p.nsplit + split) * (2 + DV)] = Mc;
         p.part[(orow * p.nsplit + split) * (2 + DV) + 1] = Lc;
     }
+    ktrace_event(6);
+}
+
+// ---- staged form for an f16 cache (decode at short and medium context) ------------------------------------------------
+// The kernel above lets every lane pull its own K row straight from global memory: 16 LDG.128 per lane that touch 32
+// different lines each, 2 us of L1 tag throughput per CTA before the first dot product (kernel timeline, event marks of
+// profiles/r01_ktrace_tg_v4.txt), and the V rows follow in dependent round trips.  Here a warp pulls the K and V rows of its tile with COALESCED 16-byte loads (a row per 16
+// lanes), all 32 of them in flight as soon as the PDL wait is passed -- mask, Q and the whole tile travel in the same
+// round trip -- parks them in padded shared-memory rows, and the arithmetic then runs out of shared memory in exactly the
+// order of fattn_vec_kernel (results are bit-identical to it).  (Per-lane 1-D bulk copies were tried first: 512 TMA
+// operations per CTA take 2 us to issue.)
+template <int D>
+__global__ void __launch_bounds__(256) fattn_vec_stage_kernel(const fa_params p) {
+    constexpr int EV = D / 32, NW = 8;
+    constexpr int KROW = 2 * D + 16;              // padded: lanes reading consecutive rows with LDS.128 hit distinct banks
+    constexpr int VROW = 2 * D;
+    constexpr int WARP_BYTES = 32 * (KROW + VROW);
+    extern __shared__ __align__(128) uint8_t fa_smem[];
+    __shared__ __align__(16) float qf[D];
+    __shared__ float wm[NW], wl[NW], wsc[NW];
+    __shared__ float wacc[NW][D];
+    __shared__ __align__(16) float fin[D];
+
+    const int iq1 = blockIdx.x, iq2 = blockIdx.y % p.n_head, iq3 = blockIdx.y / p.n_head, split = blockIdx.z;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pdl_trigger(); pdl_wait();
+
+    const char * kbase = p.k + (iq2 / p.rk2) * p.nbk2 + (iq3 / p.rk3) * p.nbk3;
+    const char * vbase = p.v + (iq2 / p.rv2) * p.nbv2 + (iq3 / p.rv3) * p.nbv3;
+    uint8_t * kt = fa_smem + (size_t)warp * WARP_BYTES, * vt = kt + 32 * KROW;
+    const int ntiles = (p.n_kv + 31) / 32;
+    const int t0 = split * p.tiles_per_split, t1 = min(ntiles, t0 + p.tiles_per_split);
+    // one tile = 32 positions: coalesced 16-byte loads (a row of 2*D bytes per 2*D/16 lanes), all in flight at once, then
+    // parked in shared memory where lane j finds row j
+    constexpr int LPR = 2 * D / 16, RPI = 32 / LPR, NI = 32 / RPI;     // lanes per row, rows per instruction, instructions
+    uint4 kreg[NI], vreg[NI];
+    auto fetch = [&](int t) {
+        const int nvalid = min(32, p.n_kv - 32 * t);
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            const int r = RPI * i + lane / LPR;
+            kreg[i] = make_uint4(0, 0, 0, 0); vreg[i] = make_uint4(0, 0, 0, 0);
+            if (r < nvalid) {
+                kreg[i] = __ldg(reinterpret_cast<const uint4 *>(kbase + (int64_t)(32 * t + r) * p.nbk1) + lane % LPR);
+                vreg[i] = __ldg(reinterpret_cast<const uint4 *>(vbase + (int64_t)(32 * t + r) * p.nbv1) + lane % LPR);
+            }
+        }
+    };
+    auto park = [&]() {
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            const int r = RPI * i + lane / LPR;
+            *reinterpret_cast<uint4 *>(kt + r * KROW + 16 * (lane % LPR)) = kreg[i];
+            *reinterpret_cast<uint4 *>(vt + r * VROW + 16 * (lane % LPR)) = vreg[i];
+        }
+        __syncwarp();
+    };
+    if (t0 + warp < t1) fetch(t0 + warp);
+
+    const float * qrow = reinterpret_cast<const float *>(p.q + iq1 * p.nbq1 + iq2 * p.nbq2 + iq3 * p.nbq3);
+    for (int i = tid; i < D; i += 32 * NW) qf[i] = qrow[i];
+    const unsigned h = iq2;
+    const float slope = p.max_bias > 0.0f ? (h < p.n_head_log2 ? powf(p.m0, (float)(h + 1)) : powf(p.m1, (float)(2 * (h - p.n_head_log2) + 1))) : 1.0f;
+    const __half * mrow = p.mask ? reinterpret_cast<const __half *>(p.mask + iq1 * p.nbm1) : nullptr;
+    __syncthreads();
+    ktrace_event(2);
+
+    float M = -INFINITY, L = 0.0f, acc[EV];
+#pragma unroll
+    for (int e = 0; e < EV; ++e) acc[e] = 0.0f;
+    for (int t = t0 + warp; t < t1; t += NW) {
+        const int ic = 32 * t + lane;
+        const float mv = (ic < p.n_kv && mrow) ? slope * __half2float(mrow[ic]) : 0.0f;
+        if (t != t0 + warp) fetch(t);
+        park();
+        float s = -INFINITY;
+        if (ic < p.n_kv && mv != -INFINITY) {
+            const uint32_t kr = smem_u32(kt + lane * KROW);
+            float sd = 0.0f;
+#pragma unroll
+            for (int i = 0; i < D / 8; ++i) {
+                const int4 u = lds128(kr + 16 * i);
+                const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+                const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&u.z)), d = __half22float2(*reinterpret_cast<const __half2 *>(&u.w));
+                const float4 q0 = *reinterpret_cast<const float4 *>(qf + 8 * i), q1 = *reinterpret_cast<const float4 *>(qf + 8 * i + 4);
+                sd = fmaf(a.x, q0.x, sd); sd = fmaf(a.y, q0.y, sd); sd = fmaf(b.x, q0.z, sd); sd = fmaf(b.y, q0.w, sd);
+                sd = fmaf(c.x, q1.x, sd); sd = fmaf(c.y, q1.y, sd); sd = fmaf(d.x, q1.z, sd); sd = fmaf(d.y, q1.w, sd);
+            }
+            s = sd * p.scale;
+            if (p.softcap != 0.0f) s = p.softcap * tanhf(s);
+            s += mv;
+        }
+        const float tmax = warp_max(s);
+        ktrace_event(3);
+        if (tmax != -INFINITY) {                    // else: whole tile masked (warp-uniform)
+            const float Mn = fmaxf(M, tmax);
+            const float corr = expf(M - Mn);            // M = -inf -> 0
+            const float pj = expf(s - Mn);              // s = -inf -> 0
+            L = L * corr + warp_sum(pj);
+#pragma unroll
+            for (int e = 0; e < EV; ++e) acc[e] *= corr;
+            M = Mn;
+            const int nvalid = min(32, p.n_kv - 32 * t);
+            const uint32_t vr = smem_u32(vt) + 2 * EV * lane;
+#pragma unroll 8
+            for (int j = 0; j < nvalid; ++j) {
+                const float pv = __shfl_sync(0xffffffffu, pj, j);
+                vfrag f; f.b = 0;
+                if constexpr (EV == 4) { f.a = lds32(vr + j * VROW); f.b = lds32(vr + j * VROW + 4); } else f.a = lds32(vr + j * VROW);
+                if (pv != 0.0f) v_fma<T_F16, D>(f, pv, acc);
+            }
+        }
+        __syncwarp();
+    }
+    ktrace_event(5);
+
+    // combine the warps
+    if (lane == 0) { wm[warp] = M; wl[warp] = L; }
+#pragma unroll
+    for (int e = 0; e < EV; ++e) wacc[warp][EV * lane + e] = acc[e];
+    __syncthreads();
+    float Mc = wm[0];
+    for (int w = 1; w < NW; ++w) Mc = fmaxf(Mc, wm[w]);
+    if (tid < NW) wsc[tid] = wm[tid] == -INFINITY ? 0.0f : expf(wm[tid] - Mc);
+    __syncthreads();
+    float Lc = 0.0f;
+    for (int w = 0; w < NW; ++w) Lc += wm[w] == -INFINITY ? 0.0f : wl[w] * wsc[w];
+    const int64_t orow = ((int64_t)iq3 * p.N + iq1) * p.n_head + iq2;
+    for (int d = tid; d < D; d += 32 * NW) {
+        float a = 0.0f;
+        for (int w = 0; w < NW; ++w) a += wm[w] == -INFINITY ? 0.0f : wacc[w][d] * wsc[w];
+        if (p.nsplit == 1) { const float o = a / Lc; reinterpret_cast<float *>(p.dst + orow * p.nbd1)[d] = o; fin[d] = o; }
+        else p.part[(orow * p.nsplit + split) * (2 + D) + 2 + d] = a;
+    }
+    if constexpr (D == 128) {
+        if (p.xq && p.nsplit == 1) {             // head iq2 = blocks 4*iq2 .. 4*iq2+3 of row iq1 in the GEMV's activation layout
+            __syncthreads();
+            if (warp == 0) quant_block_store(*reinterpret_cast<const float4 *>(&fin[4 * lane]), 4 * iq2 + (lane >> 3), lane & 7, true, p.xq + (size_t)iq1 * p.xq_acs);
+        }
+    }
+    if (p.nsplit > 1 && tid == 0) {
+        p.part[(orow * p.nsplit + split) * (2 + D)] = Mc;
+        p.part[(orow * p.nsplit + split) * (2 + D) + 1] = Lc;
+    }
+    ktrace_event(6);
 }
 
 // ---- grouped form: G query vectors that share one KV head (GQA heads x the rows of a small batch) per CTA ----
@@ -424,7 +628,7 @@ static int fa_splits(int64_t rows_heads, int ntiles) {
 template <int KT, int VT, int D>
 static int fa_launch(const fa_params & p, dim3 grid, cudaStream_t st) {
     cudaLaunchConfig_t lc = {};
-    lc.gridDim = grid; lc.blockDim = dim3(128); lc.stream = st;
+    lc.gridDim = grid; lc.blockDim = dim3(256); lc.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
@@ -433,12 +637,42 @@ static int fa_launch(const fa_params & p, dim3 grid, cudaStream_t st) {
     ++g_launches;
     if (p.nsplit > 1) {
         const int64_t nrows = (int64_t)p.N * p.n_head * p.ne3;
+        lc.blockDim = dim3(128);
         lc.gridDim = dim3((unsigned)((nrows * 32 + 127) / 128));
         B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_combine_kernel<D>, (const float *)p.part, p.dst, p.nbd1, nrows, p.nsplit, p.xq, p.xq_acs, p.n_head));
         ++g_launches;
     }
     return 0;
 }
+
+template <int D>
+static int fa_launch_stage(const fa_params & p, dim3 grid, cudaStream_t st) {
+    constexpr size_t smem = 8 * 32 * (size_t)(2 * D + 16 + 2 * D);
+    static int attr_set[16] = {0};   // per device
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 16 && !attr_set[dev]) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(fattn_vec_stage_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set[dev] = 1;
+    }
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = grid; lc.blockDim = dim3(256); lc.dynamicSmemBytes = smem; lc.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+    B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_vec_stage_kernel<D>, p));
+    ++g_launches;
+    if (p.nsplit > 1) {
+        const int64_t nrows = (int64_t)p.N * p.n_head * p.ne3;
+        lc.blockDim = dim3(128); lc.dynamicSmemBytes = 0;
+        lc.gridDim = dim3((unsigned)((nrows * 32 + 127) / 128));
+        B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_combine_kernel<D>, (const float *)p.part, p.dst, p.nbd1, nrows, p.nsplit, p.xq, p.xq_acs, p.n_head));
+        ++g_launches;
+    }
+    return 0;
+}
+static int fa_stage_on() { static const int v = [] { const char * e = getenv("B200_FATTN_STAGE"); return e ? atoi(e) : 1; }();  return v; }
 
 template <int KT, int VT, int D, int G>
 static int fa_launch_gqa(const fa_params & p, dim3 grid, cudaStream_t st) {
@@ -557,6 +791,11 @@ extern "C" int b200_op_flash_attn_ext_xq(const b200_tensor * q, const b200_tenso
     const dim3 grid((unsigned)q->ne[1], (unsigned)(q->ne[2] * q->ne[3]), (unsigned)p.nsplit);
     cudaStream_t st = (cudaStream_t)stream;
     const int D = (int)q->ne[0];
-    if (k->type == T_F16) return D == 128 ? fa_launch<T_F16, T_F16, 128>(p, grid, st) : fa_launch<T_F16, T_F16, 64>(p, grid, st);
+    if (k->type == T_F16) {
+        // f16 cache with 16-byte aligned rows: K / V tiles staged through shared memory by bulk copies
+        const bool al16 = ((((uintptr_t)v->data | v->nb[1] | v->nb[2] | v->nb[3]) & 15) == 0);
+        if (fa_stage_on() && al16) return D == 128 ? fa_launch_stage<128>(p, grid, st) : fa_launch_stage<64>(p, grid, st);
+        return D == 128 ? fa_launch<T_F16, T_F16, 128>(p, grid, st) : fa_launch<T_F16, T_F16, 64>(p, grid, st);
+    }
     return D == 128 ? fa_launch<T_Q8_0, T_Q8_0, 128>(p, grid, st) : fa_launch<T_Q8_0, T_Q8_0, 64>(p, grid, st);
 }

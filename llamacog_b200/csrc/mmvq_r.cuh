@@ -188,7 +188,9 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
             }
             __syncwarp();
             if (lane == 0 && s + p.nstages < nst) issue(s + p.nstages);
+            if (s == 0) ktrace_event(2);       // first stage consumed and stored
         }
+        ktrace_event(3);                       // all rows of CTA 0 stored
     } else {
         const int ct = tid - 32;
         const int h = ct & (p.TPR - 1), rsub = ct >> p.lgTPR;
