@@ -12,7 +12,7 @@ The model is a random-init GGUF of that architecture written by tools/make_gguf.
           graph on the GPU and reads the 128256 logits back to the host (the call a user makes)
   value   tokens / device time of the graph_compute calls of the same run, taken with CUDA events on the backend's
           stream (B200_TIMING=1 makes the plugin accumulate them); inputs are resident in HBM at that point
-  roofline  the dominant kernel, mmvq_kernel<Q4_K>: algorithmic bytes (N*K*144/256 per launch) over its mean launch
+  roofline  the dominant kernel, mmvqr_kernel<Q4_K> (mmvq_r.cuh): algorithmic bytes (N*K*144/256 per launch) over its mean launch
           duration, timed live in this process with CUDA events on a CUDA graph holding exactly the 192 Q4_K
           GEMVs of one token (distinct weight matrices, 3.36 GB > L2), through the C ABI of include/b200_ops.h
   cpu_baseline  the reference CPU backend on the same GGUF (llama-bench -ngl 0, all host threads), bounded to tg16
@@ -334,11 +334,11 @@ def main():
             try:
                 k = kernel_roofline(max(20, min(args.steps, 200)), args.warmup, local)
                 peak, how = measured_peak()
-                traffic = None
-                tpath = os.path.join(ROOT, "profiles", "r01_mmvq_q4k_traffic.json")
+                traffic = None      # ncu --set full capture of the four shapes, averaged with their launch counts per token
+                tpath = os.path.join(ROOT, "profiles", "r01_mmvqr_q4k_traffic.json")
                 if os.path.exists(tpath):
-                    traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
-                line["roofline"] = {"bound": "hbm", "kernel": "mmvq_kernel<Q4_K> (192 launches per token: wq wk wv wo gate up down)",
+                    traffic = json.load(open(tpath)).get("dram_bytes_per_launch_token_mix")
+                line["roofline"] = {"bound": "hbm", "kernel": "mmvqr_kernel<Q4_K> (192 launches per token: wq wk wv wo gate up down)",
                                     "achieved": k["gbps"], "peak": peak, "unit": "GB/s", "frac": k["gbps"] / peak, "traffic": traffic,
                                     "peak_source": how, "launches": k["launches"], "us_per_launch": k["us_per_launch"],
                                     "algorithmic_bytes_per_launch": k["bytes"] / k["launches"],

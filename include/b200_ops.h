@@ -71,7 +71,22 @@ typedef struct b200_mmvq_args {
     int pf_n;               /* 0..3 */
     const void * pf_ptr[3];
     int64_t pf_bytes[3];
+    /* Decode-step fusions of the batch-1 kernel (mmvq_r.cuh); honoured only when b200_mmvq_fusable() says so for the same
+     * arguments, otherwise the call fails with -4.  A kernel hop of a decode step costs 3.5-5 us whatever it computes
+     * (profiles/r01_ktrace_tg_v5.txt), so the element-wise neighbours of a mat-vec ride along with it:
+     *  - epilogue ADD (single matrix, M = 1): fuse_sum[n] = dst[n] + fuse_resid[n]; dst is still written.
+     *    Replaces the GGML_OP_ADD that follows wo / ffn_down (reference ggml-cuda/binbcast.cu).
+     *  - prologue RMS_NORM + MUL (M = 1, K <= 4096): the activations are rms_norm(norm_x, norm_eps) * norm_w; every CTA
+     *    computes them for itself, CTA 0 also stores the normalised row (norm_y), the product (norm_out) and its
+     *    quantised form into Xq (which is then an OUTPUT of the call, for later mat-vecs on the same column).  Same
+     *    arithmetic, bit for bit, as b200_op_add_rms_norm_mul without the ADD.  norm_x must not alias the outputs. */
+    const float * fuse_resid; float * fuse_sum;
+    const float * norm_x; const float * norm_w; float * norm_y; float * norm_out; float norm_eps;
 } b200_mmvq_args;
+
+/* 1 when b200_mul_mat_vec_q_ex (ng = 1, W/N NULL) or b200_mul_mat_vec_q_group would run these arguments on the
+ * register-resident batch-1 kernel, i.e. when the fuse_* / norm_* fields may be used.  Host-side check only. */
+int b200_mmvq_fusable(const b200_mmvq_args * args, int ng, const void * const * W, const int * N);
 
 int b200_mul_mat_vec_q_ex(const b200_mmvq_args * args, void * stream);
 int b200_mul_mat_vec_q(int type, const void * W, int64_t nb1, const float * X, int64_t xs,

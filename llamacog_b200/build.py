@@ -25,6 +25,8 @@ HOST = os.path.join(ROOT, "baseline", "_ref")
 NVCC = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-I", os.path.join(ROOT, "include")]
+if os.environ.get("B200_KTRACE", "0") not in ("", "0"):      # debug build with the kernel timeline hooks (common.cuh); rebuild everything
+    NVCC_FLAGS.append("-DB200_KTRACE")
 
 
 def _newer(src_files, target):

@@ -97,11 +97,17 @@ __device__ __forceinline__ uint64_t policy_evict_first() {
 // overlap) -- which ncu, serialising the launches, cannot show.  Thread 0 of block 0 appends
 // (globaltimer, gridid, event, grid size, block size); off (null pointer in constant memory) it costs one predicate.
 // Events 0 = entry, 1 = PDL wait passed; kernels may add their own phase marks (2..15).
-static __constant__ unsigned long long * c_ktrace;      // one copy per translation unit, all set by b200_ktrace_enable
+// Compiled in only with -DB200_KTRACE (B200_KTRACE=1 python -m llamacog_b200.build): the pointer lives in a __constant__
+// bank of its own, and the first touch of that bank by every kernel is a constant-cache miss -- measured at 0.4 us per
+// launch (roofline 0.53 -> 0.49 on the 192 GEMVs of a token), too much for a hook that is normally off.
 constexpr unsigned long long KTRACE_CAP = 1ull << 20;   // events
-__device__ __forceinline__ void ktrace_event(int ev) {
+#ifndef B200_KTRACE
+__device__ __forceinline__ void ktrace_event(int, int = 0) {}
+#else
+static __constant__ unsigned long long * c_ktrace;      // one copy per translation unit, all set by b200_ktrace_enable
+__device__ __forceinline__ void ktrace_event(int ev, int thread = 0) {     // recorded by `thread` of block 0
     unsigned long long * t = c_ktrace;
-    if (t != nullptr && (threadIdx.x | blockIdx.x | blockIdx.y | blockIdx.z) == 0) {
+    if (t != nullptr && ((threadIdx.x ^ thread) | blockIdx.x | blockIdx.y | blockIdx.z) == 0) {
         unsigned long long now, gid;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
         asm volatile("mov.u64 %0, %%gridid;" : "=l"(gid));
@@ -122,6 +128,7 @@ struct ktrace_registrar {
 };
 static ktrace_registrar ktrace_registrar_instance;
 }
+#endif
 
 // programmatic dependent launch: wait for the producer grid / allow the dependent grid to start
 __device__ __forceinline__ void pdl_wait()    { asm volatile("griddepcontrol.wait;" ::: "memory"); ktrace_event(1); }

@@ -8,7 +8,7 @@
 //   b200_op_unary_mul        : UNARY(silu|gelu) -> MUL(other)     (+ activations of the result)
 // Reference: the same chains are fused in ggml-cuda (RMS_NORM+MUL in norm.cu / ggml-cuda.cu graph fusion; GLU kernels in
 // unary.cu); semantics of each step follow ggml-cpu/ops.cpp (rms_norm 3285-3312) and unary-ops.cpp (silu, gelu).
-#include "mmvq_units.cuh"
+#include "mmvq_r.cuh"        // sumsq4 / rms_scale: the norm arithmetic shared with the GEMV's fused prologue
 #include "../../include/b200_ops.h"
 
 #include <algorithm>
@@ -39,14 +39,14 @@ __global__ void __launch_bounds__(1024) add_rms_norm_mul_kernel(const float * __
     }
     float s = 0.0f;
 #pragma unroll
-    for (int k = 0; k < VPT; ++k) s += v[k].x * v[k].x + v[k].y * v[k].y + v[k].z * v[k].z + v[k].w * v[k].w;
+    for (int k = 0; k < VPT; ++k) s += sumsq4(v[k]);
     s = warp_sum(s);
     __shared__ float part[32];
     if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
     __syncthreads();
     float tot = 0.0f;
     for (int wi = 0; wi < (int)(blockDim.x >> 5); ++wi) tot += part[wi];
-    const float scale = rsqrtf(tot / (float)K + eps);
+    const float scale = rms_scale(tot, K, eps);
     const float4 * w4 = reinterpret_cast<const float4 *>(w);
     float4 * n4p = reinterpret_cast<float4 *>(norm + (int64_t)r * ns);
     float4 * o4 = reinterpret_cast<float4 *>(out + (int64_t)r * os);

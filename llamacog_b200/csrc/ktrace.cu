@@ -6,6 +6,10 @@
 #include <cstdio>
 #include <vector>
 
+#ifndef B200_KTRACE
+extern "C" int b200_ktrace_enable(void) { return -1; }            // not compiled in (see common.cuh)
+extern "C" int b200_ktrace_dump(const char *) { return -1; }
+#else
 namespace b200 {
 static std::vector<int (*)(unsigned long long *)> & setters() { static std::vector<int (*)(unsigned long long *)> v; return v; }
 void ktrace_register(int (*setter)(unsigned long long *)) { setters().push_back(setter); }
@@ -41,3 +45,4 @@ extern "C" int b200_ktrace_dump(const char * path) {
     fclose(f);
     return 0;
 }
+#endif

@@ -23,12 +23,30 @@ static int sm_count() {
     return n[dev] > 0 ? n[dev] : 148;
 }
 
-// returns MMVQR_SKIP when the call is not eligible (the caller falls through to the general kernel), 0 when launched, else an error
+static bool al16(const void * p) { return ((uintptr_t)p & 15) == 0; }
+// the fused prologue / epilogue of this launch, if any, are ones the kernel can do
+static bool fuse_ok(const b200_mmvq_args * a, int ng) {
+    if (a->fuse_resid || a->fuse_sum) {
+        if (!a->fuse_resid || !a->fuse_sum || ng != 1) return false;
+    }
+    if (a->norm_x) {
+        if (!a->norm_w || !a->norm_y || !a->norm_out || a->K > 4096 || a->dbg_sumi) return false;
+        if (!al16(a->norm_x) || !al16(a->norm_w) || !al16(a->norm_y) || !al16(a->norm_out)) return false;
+    }
+    return true;
+}
+
+// returns MMVQR_SKIP when the call is not eligible (the caller falls through to the general kernel), 0 when launched, else an error.
+// stream == (cudaStream_t)-1: eligibility check only (returns 0 when the call would be launched)
 int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * const * dst, const int * N, cudaStream_t stream) {
+    const bool probe = stream == (cudaStream_t)-1;
     static const int on = env_i("B200_MMVQR", 1), cps = std::max(1, std::min(2, env_i("B200_MMVQR_CPS", 2))),
-                     smem_kb = env_i("B200_MMVQR_SMEM_KB", 110), stage_kb = env_i("B200_MMVQR_STAGE_KB", 36),
-                     max_stages = std::max(1, std::min(8, env_i("B200_MMVQR_NS", 8))), eU = env_i("B200_MMVQR_U", 0);
-    if (!on || a->M != 1 || !a->Xq || a->ids || std::max(1, a->ny) != 1 || std::max(1, a->nz) != 1) return MMVQR_SKIP;
+                     smem_kb = env_i("B200_MMVQR_SMEM_KB", 112), stage_kb = env_i("B200_MMVQR_STAGE_KB", 36),
+                     max_stages = std::max(1, std::min(8, env_i("B200_MMVQR_NS", 8))), eU = env_i("B200_MMVQR_U", 0),
+                     ramp = env_i("B200_MMVQR_RAMP", 0),          // short first stages: measured slower (per-stage hand-over cost), kept for tuning runs
+                     small_mb = env_i("B200_MMVQR_SMALL_MB", 0), stagger = env_i("B200_MMVQR_STAGGER", 0);
+    if (!fuse_ok(a, ng)) return MMVQR_SKIP;
+    if (!on || a->M != 1 || (!a->Xq && !a->norm_x) || a->ids || std::max(1, a->ny) != 1 || std::max(1, a->nz) != 1) return MMVQR_SKIP;
     if (a->type != T_Q4_K && a->type != T_Q6_K) return MMVQR_SKIP;
     if (a->dbg_sumi && ng != 1) return MMVQR_SKIP;
     const int K = a->K;
@@ -46,7 +64,10 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
         ntot += N[g];
     }
     const int rpp = 256 / tpr, nw = tpr > 32 ? tpr / 32 : 1;
-    const int gx_max = std::max(ng, std::min(sm_count() * cps, (ntot + rpp - 1) / rpp));
+    // Tuning knob (B200_MMVQR_SMALL_MB, default 0 = off): a matrix below the threshold takes one CTA per SM only, leaving the
+    // other register/thread slot of the SM to the mat-vec that follows under PDL.  No effect on tg128 (471-474 tok/s either way).
+    const int cps_eff = (int64_t)ntot * rb <= (int64_t)small_mb << 20 ? 1 : cps;
+    const int gx_max = std::max(ng, std::min(sm_count() * cps_eff, (ntot + rpp - 1) / rpp));
 
     mmvqr_params p = {};
     p.ngroup = ng;
@@ -55,7 +76,7 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
         int share = g + 1 == ng ? std::max(1, gx_max - used) : std::max(1, (int)((int64_t)gx_max * N[g] / ntot));
         share = std::max(1, std::min(share, (N[g] + rpp - 1) / rpp));
         p.cta0[g] = used; used += share;
-        p.Wg[g] = (const uint8_t *)W[g]; p.Dg[g] = dst[g];
+        p.Wg[g] = (const uint8_t *)W[g]; p.Dg[g] = probe ? nullptr : dst[g];
         p.rows_qg[g] = N[g] / share; p.rows_remg[g] = N[g] % share;
         rows_per_cta = std::max(rows_per_cta, (N[g] + share - 1) / share);
     }
@@ -73,18 +94,25 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     const int stage_bytes = round_up(R * rb + 16, 128);     // slack: the 2-byte aligned loads of Q6_K over-read 4 bytes
     const size_t budget = (size_t)smem_kb * 1024;
     const size_t per_stage = (size_t)stage_bytes + (size_t)R * nw * 4 + 16;
-    const size_t act_bytes = (size_t)bpr * ACT_ITEM;
-    if (budget < act_bytes + 128 + per_stage) return MMVQR_SKIP;
-    int nstages = (int)std::min<size_t>(max_stages, (budget - act_bytes - 128) / per_stage);
-    nstages = std::min(nstages, (rows_per_cta + R - 1) / R);
+    const size_t act_bytes = (size_t)bpr * ACT_ITEM + (a->norm_x ? (size_t)K * 8 : 0);      // + the fp32 row of the fused norm and the norm weights
+    const size_t tail_bytes = 16 + 128 + (a->fuse_resid ? (size_t)rows_per_cta * 4 : 0) + 16;   // act barrier, norm partials, residual rows
+    if (budget < act_bytes + tail_bytes + 128 + per_stage) return MMVQR_SKIP;
+    int nstages = (int)std::min<size_t>(max_stages, (budget - act_bytes - tail_bytes - 128) / per_stage);
+    const int q0 = ramp ? std::max(1, R >> 3) : R, q1 = ramp ? std::max(1, R >> 2) : R, q2 = ramp ? std::max(1, R >> 1) : R;
+    const int need = rows_per_cta <= q0 ? 1 : rows_per_cta <= q0 + q1 ? 2 : rows_per_cta <= q0 + q1 + q2 ? 3 : 3 + (rows_per_cta - q0 - q1 - q2 + R - 1) / R;
+    nstages = std::min(nstages, need);
     if (nstages < 1) return MMVQR_SKIP;
+    if (probe) return 0;
 
+    p.nx = a->norm_x; p.nw = a->norm_w; p.nnorm = a->norm_y; p.nout = a->norm_out; p.nxq = a->norm_x ? (uint8_t *)a->Xq : nullptr; p.neps = a->norm_eps;
+    p.resid = a->fuse_resid; p.dsum = a->fuse_sum; p.resid_rows = a->fuse_resid ? rows_per_cta : 0;
     p.Xq = (const uint8_t *)a->Xq; p.K = K; p.BPR = bpr; p.TPR = tpr; p.lgTPR = lg; p.rb = rb;
     p.R = R; p.nstages = nstages; p.stage_bytes = stage_bytes;
+    p.r0 = q0; p.r1 = q1; p.r2 = q2; p.stagger = stagger;
     p.dbg_sumi = a->dbg_sumi;
     mmvqr_launch_cfg c;
     c.grid = dim3(used, 1, 1);
-    c.smem = (size_t)nstages * stage_bytes + act_bytes + (((size_t)nstages * R * nw + 1) & ~(size_t)1) * 4 + (size_t)nstages * 16 + 16;
+    c.smem = (size_t)nstages * stage_bytes + act_bytes + (((size_t)nstages * R * nw + 1) & ~(size_t)1) * 4 + (size_t)nstages * 16 + tail_bytes;
     c.U = U;
     c.pdl = a->pdl >= 0 ? a->pdl : pdl_default();
     const int rc = a->type == T_Q4_K ? mmvqr_launch_type<T_Q4_K>(p, c, stream) : mmvqr_launch_type<T_Q6_K>(p, c, stream);
@@ -94,3 +122,14 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
 }
 
 }  // namespace b200
+
+extern "C" int b200_mmvq_fusable(const b200_mmvq_args * a, int ng, const void * const * W, const int * N) {
+    if (!a) return 0;
+    const void * W1[1] = { a->W }; const int N1[1] = { a->N };
+    if (!W || !N) { W = W1; N = N1; ng = 1; }
+    if (ng < 1 || ng > 3) return 0;
+    b200_mmvq_args t = *a;
+    static const char dummy[16] __attribute__((aligned(16))) = {0};
+    if (!t.Xq && !t.norm_x) t.Xq = dummy;                  // asked before the activations exist: only the shape matters
+    return b200::mmvqr_try(&t, ng, W, nullptr, N, (cudaStream_t)-1) == 0 ? 1 : 0;
+}

@@ -42,9 +42,20 @@ struct mmvqr_params {
     int TPR, lgTPR;          // threads per row (power of two >= 2*BPR, <= 256)
     int rb;                  // bytes per row
     int R;                   // rows per stage (multiple of 256/TPR)
+    int r0, r1, r2;          // rows of the first three stages of a CTA (ramp: <= R)
+    int stagger;             // tuning: stages 1.. are requested only when stage 0 has landed
     int nstages, stage_bytes;
     int32_t * dbg_sumi;      // parity hook: [N][K/32] int32 block sums (single matrix only)
+    // fused RMS_NORM + MUL prologue (NORM kernels): the activations are rms_norm(nx) * nw, computed by every CTA for itself;
+    // CTA 0 also writes the two tensors of the original nodes and the quantised column (for later mat-muls that read it)
+    const float * nx; const float * nw; float * nnorm; float * nout; uint8_t * nxq; float neps;
+    // fused residual ADD epilogue (single matrix): dsum[n] = dst[n] + resid[n]
+    const float * resid; float * dsum; int resid_rows;
 };
+
+// rms_norm arithmetic shared with add_rms_norm_mul_kernel (fused.cu): same expressions, same order, bit-identical results
+__device__ __forceinline__ float sumsq4(const float4 v) { return v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w; }
+__device__ __forceinline__ float rms_scale(float tot, int K, float eps) { return rsqrtf(tot / (float)K + eps); }
 
 struct hacts { int q[4][8]; float d8[4], dsq[4]; int m32a[4], m32b[4]; };
 
@@ -127,7 +138,7 @@ __device__ __forceinline__ float half_dot(const hweights<TYPE> & w, const hacts 
     }
 }
 
-template <int TYPE, int U, bool DBG>
+template <int TYPE, int U, bool DBG, bool NORM>
 __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
     constexpr int IB = item_traits<TYPE>::BYTES;
     extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -137,10 +148,14 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
 
     uint8_t * stages = smem_raw;
     uint8_t * act = smem_raw + (size_t)p.nstages * p.stage_bytes;                                  // BPR items of 400 bytes
-    float * partials = reinterpret_cast<float *>(act + (size_t)p.BPR * ACT_ITEM);                  // [nstages][R][NW]
+    float * xs = reinterpret_cast<float *>(act + (size_t)p.BPR * ACT_ITEM);                        // NORM: the K floats to normalise
+    float * ws = xs + (NORM ? p.K : 0);                                                            // NORM: the norm weights
+    float * partials = ws + (NORM ? p.K : 0);                                                      // [nstages][R][NW]
     const int part_stage = p.R * NW;
     uint64_t * bars = reinterpret_cast<uint64_t *>(partials + (((size_t)p.nstages * part_stage + 1) & ~(size_t)1));
-    const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * p.nstages, actbar = empty0 + 8 * p.nstages;
+    const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * p.nstages, actbar = empty0 + 8 * p.nstages, wbar = actbar + 8;
+    float * npart = reinterpret_cast<float *>(bars + 2 * p.nstages + 2);     // 32 floats: sums of squares per 32 float4s
+    float * rsd = npart + 32;                                                // resid_rows floats: this CTA's residual values
 
     int cta = blockIdx.x, g = 0;
     while (g + 1 < p.ngroup && cta >= p.cta0[g + 1]) ++g;
@@ -149,12 +164,19 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
     float * Dc = p.Dg[g];
     const int row_lo = cta * p.rows_qg[g] + min(cta, p.rows_remg[g]);
     const int nrows = p.rows_qg[g] + (cta < p.rows_remg[g] ? 1 : 0);
-    const int row_hi = row_lo + nrows;
-    const int nst = (nrows + p.R - 1) / p.R;
+    // Stage s of this CTA covers rows [srow(s), srow(s) + snr(s)) of its range.  The first three stages are short (r0, r1,
+    // r2 rows): bulk copies in flight share the SM's bandwidth, so equal stages all land together after the whole batch
+    // has streamed (the first dot product of a 66 MB gate/up GEMV started 5-8 us after its loads were issued,
+    // profiles/r01_ktrace_tg_v5.txt); with a ramp the first rows arrive after ~1 us and the multiply overlaps the rest.
+    const int rampC = p.r0 + p.r1 + p.r2;
+    auto srow = [&](int s) { return s == 0 ? 0 : s == 1 ? p.r0 : s == 2 ? p.r0 + p.r1 : rampC + (s - 3) * p.R; };
+    auto snr = [&](int s) { return min(s == 0 ? p.r0 : s == 1 ? p.r1 : s == 2 ? p.r2 : p.R, nrows - srow(s)); };
+    const int nst = nrows <= p.r0 ? 1 : nrows <= p.r0 + p.r1 ? 2 : nrows <= rampC ? 3 : 3 + (nrows - rampC + p.R - 1) / p.R;
 
     if (tid == 0) {
         for (int s = 0; s < p.nstages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 8); }
         mbar_init(actbar, 1);
+        mbar_init(wbar, 1);
         mbar_fence_init();
     }
     __syncthreads();
@@ -164,27 +186,41 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
         const uint64_t pol = policy_evict_first();
         auto issue = [&](int s) {   // lane 0 only
             const int slot = s % p.nstages;
-            const int r0 = row_lo + s * p.R, nr = min(p.R, row_hi - r0);
+            const int r0 = row_lo + srow(s), nr = snr(s);
             const uint32_t bytes = (uint32_t)nr * p.rb, bar = full0 + 8 * slot;
             mbar_expect_tx(bar, bytes);
             bulk_g2s_stream(smem_u32(stages + (size_t)slot * p.stage_bytes), Wc + (int64_t)r0 * p.rb, bytes, bar, pol);
         };
-        if (lane == 0) for (int s = 0; s < min(nst, p.nstages); ++s) issue(s);
+        // NORM kernels follow another mat-vec directly (no early residency), so their row must not queue behind the whole
+        // weight prefetch in the SM's copy engine: norm weights and the first stage before the wait, the row right after
+        // it, the other stages behind the row.  (296 CTAs reading the same 16 KB with ordinary loads took 2-8 us, the bulk
+        // copies of the same lines about 1 us: profiles/r01_ktrace_tg_v6.txt.)
+        if (lane == 0) {
+            if (NORM) { mbar_expect_tx(wbar, (uint32_t)p.K * 4); bulk_g2s(smem_u32(ws), p.nw, (uint32_t)p.K * 4, wbar); }
+            for (int s = 0; s < min(nst, (NORM || p.stagger) ? 1 : p.nstages); ++s) issue(s);
+            if (!NORM && p.stagger && nst > 1) { mbar_wait(full0, 0); for (int s = 1; s < min(nst, p.nstages); ++s) issue(s); }
+        }
         pdl_wait();           // the activations come from the previous kernel; dst may still be read by it
         if (lane == 0) {      // one coalesced copy of the column; the consumers pick their registers out of shared memory
-            const uint32_t ab = (uint32_t)p.BPR * ACT_ITEM;
+            const uint32_t ab = NORM ? (uint32_t)p.K * 4 : (uint32_t)p.BPR * ACT_ITEM;
             mbar_expect_tx(actbar, ab);
-            bulk_g2s(smem_u32(act), p.Xq, ab, actbar);
+            bulk_g2s(NORM ? smem_u32(xs) : smem_u32(act), NORM ? (const void *)p.nx : (const void *)p.Xq, ab, actbar);
+            if (NORM) for (int s = 1; s < min(nst, p.nstages); ++s) issue(s);
+        }
+        if (p.resid) {        // this CTA's rows of the residual, fetched while the first stage is being multiplied
+            for (int o = lane; o < nrows; o += 32) rsd[o] = p.resid[row_lo + o];
+            __syncwarp();
         }
         for (int s = 0; s < nst; ++s) {
             const int slot = s % p.nstages;
             mbar_wait(empty0 + 8 * slot, (s / p.nstages) & 1);
-            const int r0 = row_lo + s * p.R, nr = min(p.R, row_hi - r0);
+            const int r0 = row_lo + srow(s), nr = snr(s);
             const float * ps = partials + (size_t)slot * part_stage;
             for (int o = lane; o < nr; o += 32) {
                 float sum = 0.0f;
                 for (int wv = 0; wv < NW; ++wv) sum += ps[o * NW + wv];
                 Dc[r0 + o] = sum;
+                if (p.resid) p.dsum[r0 + o] = sum + rsd[r0 - row_lo + o];
             }
             __syncwarp();
             if (lane == 0 && s + p.nstages < nst) issue(s + p.nstages);
@@ -199,14 +235,61 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
         const int wir = h >> 5;                              // warp inside the row (TPR > 32)
         const int red = min(p.TPR, 32);
         hacts a;
-        mbar_wait(actbar, 0);
+        if constexpr (NORM) {
+            // RMS_NORM + MUL + q8 quantisation of the column, the arithmetic of add_rms_norm_mul_kernel<1> (one float4 per
+            // thread of a 1024-thread CTA there; here thread ct takes float4s ct, ct + 256, .. so that a warp still holds
+            // 32 consecutive float4s and the butterfly sums, the order of the partials and the 8-lane quantiser groups
+            // are the same)
+            const int n4 = p.K >> 2;
+            const int cw = warp - 1;
+            float4 wv[4], v[4];
+            mbar_wait(wbar, 0);                     // norm weights: copied before the PDL wait
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (ct + 256 * k < n4) wv[k] = reinterpret_cast<const float4 *>(ws)[ct + 256 * k];
+            mbar_wait(actbar, 0);                   // the row is in shared memory (copied after the producer's PDL wait)
+            ktrace_event(4, 32);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (ct + 256 * k < n4) v[k] = reinterpret_cast<const float4 *>(xs)[ct + 256 * k];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (ct + 256 * k < n4) {
+                    float sq = 0.0f;
+                    sq += sumsq4(v[k]);
+                    sq = warp_sum(sq);
+                    if (lane == 0) npart[8 * k + cw] = sq;
+                }
+            }
+            ktrace_event(5, 32);
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            float tot = 0.0f;
+            for (int wi = 0; wi < (n4 >> 5); ++wi) tot += npart[wi];
+            const float scale = rms_scale(tot, p.K, p.neps);
+            const bool writer = blockIdx.x == 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int i = ct + 256 * k;
+                if (i < n4) {
+                    const float4 nv = make_float4(v[k].x * scale, v[k].y * scale, v[k].z * scale, v[k].w * scale);
+                    const float4 y = make_float4(nv.x * wv[k].x, nv.y * wv[k].y, nv.z * wv[k].z, nv.w * wv[k].w);
+                    if (writer) { reinterpret_cast<float4 *>(p.nnorm)[i] = nv; reinterpret_cast<float4 *>(p.nout)[i] = y; }
+                    quant_block_store(y, i >> 3, ct & 7, true, act);
+                    if (writer && p.nxq) quant_block_store(y, i >> 3, ct & 7, true, p.nxq);
+                }
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            ktrace_event(6, 32);
+        } else {
+            mbar_wait(actbar, 0);
+            ktrace_event(6, 32);
+        }
         if (active) load_hacts(smem_u32(act) + (uint32_t)b * ACT_ITEM + hh * (4 * ACT_BLK), a);
         const uint32_t ioff = (uint32_t)b * IB;
         const int nb32 = p.K >> 5;
         for (int s = 0; s < nst; ++s) {
             const int slot = s % p.nstages;
-            const int r0 = row_lo + s * p.R, nr = min(p.R, row_hi - r0);
+            const int r0 = row_lo + srow(s), nr = snr(s);
             mbar_wait(full0 + 8 * slot, (s / p.nstages) & 1);
+            if (s == 0) ktrace_event(7, 32);       // first weights have landed
             const uint32_t sbase = smem_u32(stages + (size_t)slot * p.stage_bytes) + ioff;
             float * pw = partials + (size_t)slot * part_stage;
             // U passes (rows rr, rr + RPP, ..) in flight per thread: independent shared loads and dp4a chains
@@ -245,9 +328,9 @@ constexpr int MMVQR_SKIP = -777;
 struct mmvqr_launch_cfg { dim3 grid; size_t smem; int pdl; int U; };
 template <int TYPE> int mmvqr_launch_type(const mmvqr_params & p, const mmvqr_launch_cfg & c, cudaStream_t stream);
 
-template <int TYPE, int U, bool DBG>
+template <int TYPE, int U, bool DBG, bool NORM>
 static int mmvqr_launch_one(const mmvqr_params & p, const mmvqr_launch_cfg & c, cudaStream_t stream) {
-    auto kern = mmvqr_kernel<TYPE, U, DBG>;
+    auto kern = mmvqr_kernel<TYPE, U, DBG, NORM>;
     static int smem_set[16] = {0};   // per device
     int dev = 0;
     B200_CUDA_CHECK(cudaGetDevice(&dev));
@@ -267,8 +350,9 @@ static int mmvqr_launch_one(const mmvqr_params & p, const mmvqr_launch_cfg & c, 
 
 #define B200_MMVQR_DEFINE(TYPE_) \
     template <> int mmvqr_launch_type<TYPE_>(const mmvqr_params & p, const mmvqr_launch_cfg & c, cudaStream_t stream) { \
-        if (p.dbg_sumi) return c.U == 2 ? mmvqr_launch_one<TYPE_, 2, true>(p, c, stream) : mmvqr_launch_one<TYPE_, 1, true>(p, c, stream); \
-        return c.U == 2 ? mmvqr_launch_one<TYPE_, 2, false>(p, c, stream) : mmvqr_launch_one<TYPE_, 1, false>(p, c, stream); \
+        if (p.nx) return mmvqr_launch_one<TYPE_, 1, false, true>(p, c, stream); \
+        if (p.dbg_sumi) return c.U == 2 ? mmvqr_launch_one<TYPE_, 2, true, false>(p, c, stream) : mmvqr_launch_one<TYPE_, 1, true, false>(p, c, stream); \
+        return c.U == 2 ? mmvqr_launch_one<TYPE_, 2, false, false>(p, c, stream) : mmvqr_launch_one<TYPE_, 1, false, false>(p, c, stream); \
     }
 
 }  // namespace b200

@@ -22,7 +22,9 @@ class MmvqArgs(C.Structure):
                 ("w_div_z", C.c_int), ("x_sy", C.c_int64), ("x_sz", C.c_int64), ("x_mod_y", C.c_int),
                 ("d_sy", C.c_int64), ("d_sz", C.c_int64), ("ids", C.c_void_p), ("ids_sz", C.c_int64),
                 ("pdl", C.c_int), ("dbg_sumi", C.c_void_p), ("Xq", C.c_void_p), ("xq_sy", C.c_int64), ("xq_sz", C.c_int64),
-                ("pf_n", C.c_int), ("pf_ptr", C.c_void_p * 3), ("pf_bytes", C.c_int64 * 3)]
+                ("pf_n", C.c_int), ("pf_ptr", C.c_void_p * 3), ("pf_bytes", C.c_int64 * 3),
+                ("fuse_resid", C.c_void_p), ("fuse_sum", C.c_void_p),
+                ("norm_x", C.c_void_p), ("norm_w", C.c_void_p), ("norm_y", C.c_void_p), ("norm_out", C.c_void_p), ("norm_eps", C.c_float)]
 
 
 _lib = None
@@ -57,7 +59,7 @@ EXPORTS = ["b200_flash_attn_xq_supported", "b200_op_flash_attn_ext_xq", "b200_mu
            "b200_mul_mat_supported", "b200_op_mul_mat_id", "b200_mul_mat_q", "b200_mul_mat_q_scratch_bytes",
            "b200_mul_mat_q_supported", "b200_mmq_debug_trace", "b200_acts_bf16_bytes",
            "b200_convert_acts_bf16", "b200_mul_mat_q_bf16", "b200_op_add_rms_norm_mul", "b200_op_unary_mul", "b200_op_rope_cpy_batch", "b200_op_rope_cpy_batch_check",
-           "b200_ktrace_enable", "b200_ktrace_dump"]
+           "b200_ktrace_enable", "b200_ktrace_dump", "b200_mmvq_fusable"]
 
 
 def _stream():

@@ -110,3 +110,86 @@ def test_prefill_rows_with_bf16_activations(M, K):
     torch.cuda.synchronize()
     assert torch.allclose(out, torch.nn.functional.silu(g) * u, rtol=1e-5, atol=1e-6)
     assert torch.equal(xb2, out.to(torch.bfloat16))
+
+
+def _gemv_args(ops, t, W, N, K, dst, **kw):
+    return ops.MmvqArgs(type=t, W=W.data_ptr(), nb1=ops.row_bytes(t, K), X=None, xs=K, dst=dst.data_ptr(), ds=N, N=N, K=K, M=1,
+                        ny=1, nz=1, pdl=-1, **kw)
+
+
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K"])
+@pytest.mark.parametrize("N,K", [(4096, 4096), (1024, 2048), (300, 1024), (128256, 4096)])
+def test_gemv_norm_prologue_matches_separate_launches(tname, N, K):
+    """RMS_NORM + MUL + quantisation done by the batch-1 GEMV itself (b200_mmvq_args.norm_*): the normalised row, the
+    product, the quantised column it leaves behind and the mat-vec result must equal, bit for bit, those of the stand-alone
+    fused norm kernel followed by the GEMV on its activations."""
+    import numpy as np
+    import oracle as O
+    ops = _ops(); L = ops.lib()
+    t = O.QUANT_TYPES[tname]
+    rng = np.random.default_rng(N + K)
+    W = torch.from_numpy(O.random_quant_bytes(t, N, K, rng).reshape(-1)).cuda()
+    torch.manual_seed(N + K)
+    x = torch.randn(1, K, device="cuda") * 3; w = torch.randn(K, device="cuda")
+    eps = 1e-5
+    n_ref = torch.empty_like(x); o_ref = torch.empty_like(x); q_ref = torch.zeros((1, K // 256 * 400), dtype=torch.uint8, device="cuda")
+    assert L.b200_op_add_rms_norm_mul(C.byref(ops.as_b200(x)), None, None, C.byref(ops.as_b200(n_ref)), C.byref(ops.as_b200(w)),
+                                      C.byref(ops.as_b200(o_ref)), C.c_float(eps), C.c_void_p(q_ref.data_ptr()), C.c_int(0), _st(ops)) == 0
+    d_ref = ops.mul_mat_vec_q(t, W, o_ref, N, K, Xq=q_ref)
+    n = torch.empty_like(x); o = torch.empty_like(x); q = torch.zeros_like(q_ref); d = torch.empty(1, N, device="cuda")
+    a = _gemv_args(ops, t, W, N, K, d, Xq=q.data_ptr(), norm_x=x.data_ptr(), norm_w=w.data_ptr(), norm_y=n.data_ptr(),
+                   norm_out=o.data_ptr(), norm_eps=eps)
+    if not L.b200_mmvq_fusable(C.byref(a), C.c_int(1), None, None):
+        pytest.skip("shape not taken by the register-resident kernel")
+    assert L.b200_mul_mat_vec_q_ex(C.byref(a), _st(ops)) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(n, n_ref) and torch.equal(o, o_ref)
+    assert _same_acts(q, q_ref)
+    assert torch.equal(d, d_ref)
+
+
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K"])
+@pytest.mark.parametrize("N,K", [(4096, 4096), (4096, 14336), (37, 2048), (5000, 4096)])
+def test_gemv_residual_epilogue(tname, N, K):
+    """ADD fused into the GEMV's store (b200_mmvq_args.fuse_resid / fuse_sum): dst as without it, fuse_sum = dst + resid exactly
+    (one fp32 add per element, as b200_op_binary does); also with fuse_sum aliasing dst (the graph allocator's in-place ADD)."""
+    import numpy as np
+    import oracle as O
+    ops = _ops(); L = ops.lib()
+    t = O.QUANT_TYPES[tname]
+    rng = np.random.default_rng(N * 3 + K)
+    W = torch.from_numpy(O.random_quant_bytes(t, N, K, rng).reshape(-1)).cuda()
+    torch.manual_seed(N)
+    x = torch.randn(1, K, device="cuda"); r = torch.randn(1, N, device="cuda")
+    xq = ops.quantize_acts(x)
+    d_ref = ops.mul_mat_vec_q(t, W, x, N, K, Xq=xq)
+    d = torch.empty(1, N, device="cuda"); s = torch.empty(1, N, device="cuda")
+    a = _gemv_args(ops, t, W, N, K, d, Xq=xq.data_ptr(), fuse_resid=r.data_ptr(), fuse_sum=s.data_ptr())
+    if not L.b200_mmvq_fusable(C.byref(a), C.c_int(1), None, None):
+        pytest.skip("shape not taken by the register-resident kernel")
+    assert L.b200_mul_mat_vec_q_ex(C.byref(a), _st(ops)) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(d, d_ref)
+    assert torch.equal(s, d_ref + r)
+    d2 = torch.empty(1, N, device="cuda")
+    a = _gemv_args(ops, t, W, N, K, d2, Xq=xq.data_ptr(), fuse_resid=r.data_ptr(), fuse_sum=d2.data_ptr())
+    assert L.b200_mul_mat_vec_q_ex(C.byref(a), _st(ops)) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(d2, d_ref + r)
+
+
+def test_gemv_fusion_refused_when_not_eligible():
+    """M = 2 does not run on the register-resident kernel: the fusable predicate says no and a call with fused fields fails
+    loudly (-4) instead of silently dropping the fused work."""
+    import oracle as O
+    import numpy as np
+    ops = _ops(); L = ops.lib()
+    t = O.QUANT_TYPES["q4_K"]
+    N, K = 64, 4096
+    W = torch.from_numpy(O.random_quant_bytes(t, N, K, np.random.default_rng(0)).reshape(-1)).cuda()
+    x = torch.randn(2, K, device="cuda"); r = torch.randn(2, N, device="cuda"); d = torch.empty(2, N, device="cuda"); s = torch.empty(2, N, device="cuda")
+    xq = ops.quantize_acts(x)
+    a = _gemv_args(ops, t, W, N, K, d, Xq=xq.data_ptr(), fuse_resid=r.data_ptr(), fuse_sum=s.data_ptr())
+    a.M = 2
+    assert L.b200_mmvq_fusable(C.byref(a), C.c_int(1), None, None) == 0
+    assert L.b200_mul_mat_vec_q_ex(C.byref(a), _st(ops)) == -4

@@ -21,8 +21,11 @@ def main():
         t, N, K = SHAPES[n]
         pool = [rand_weights(t, N * ops.row_bytes(t, K), dev) for _ in range(3)]
         X = torch.rand((1, K), device=dev) * 2 - 1
+        xq_once = ops.quantize_acts(X) if os.environ.get("MICRO_XQ", "0") == "2" else None
         for i in range(3):
-            if os.environ.get("MICRO_XQ", "0") == "1":
+            if xq_once is not None:      # activations quantised by their producer: the batch-1 register-resident kernel
+                ops.mul_mat_vec_q(t, pool[i], X, N, K, Xq=xq_once)
+            elif os.environ.get("MICRO_XQ", "0") == "1":
                 ops.mul_mat_vec_q(t, pool[i], X, N, K, Xq=ops.quantize_acts(X))
             else:
                 ops.mul_mat_vec_q(t, pool[i], X, N, K)
