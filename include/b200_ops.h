@@ -82,6 +82,8 @@ typedef struct b200_mmvq_args {
      *    arithmetic, bit for bit, as b200_op_add_rms_norm_mul without the ADD.  norm_x must not alias the outputs. */
     const float * fuse_resid; float * fuse_sum;
     const float * norm_x; const float * norm_w; float * norm_y; float * norm_out; float norm_eps;
+    /*  - epilogue ROPE + KV-cache store of a q/k/v launch (M = 1, see struct b200_gemv_rope below) */
+    const struct b200_gemv_rope * rope;
 } b200_mmvq_args;
 
 /* 1 when b200_mul_mat_vec_q_ex (ng = 1, W/N NULL) or b200_mul_mat_vec_q_group would run these arguments on the
@@ -165,6 +167,22 @@ typedef struct b200_rope_params {
 } b200_rope_params;
 int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst,
                  const b200_rope_params * prm, void * stream);
+/* ROPE and the KV-cache stores of a decode step inside the q/k/v mat-vec (b200_mmvq_args.rope; batch-1 kernel only, checked by
+ * b200_mmvq_fusable).  Per matrix g of the launch, with n the row index (= flat element index of the [head_dim, n_head] result):
+ *   mode 0: nothing            mode 1: out[n] = rope(dst)[n]            mode 2: mode 1 and cell[n] = convert(out[n])  (K row)
+ *   mode 3: cell[n] = convert(dst[n])  (V row)
+ * rope in mode "normal" (adjacent pairs) at position pos[0]; cell_type f32 / f16 / bf16, contiguous cell; cell_slot (optional):
+ * device address of a pointer that replaces cell when the kernel runs (CUDA-graph replay, see b200_op_cpy_indirect).  The raw
+ * dst of a roped matrix is not written.  Bit-identical to b200_op_rope_cpy_batch on the mat-vec's output; replaces the
+ * reference's rope.cu + cpy.cu launches that follow the q/k/v projections. */
+typedef struct b200_gemv_rope {
+    int mode[3];
+    float * out[3];
+    void * cell[3]; void * const * cell_slot[3]; int cell_type[3];
+    int head_dim[3];
+    const int32_t * pos; const float * ffac;
+    b200_rope_params prm;
+} b200_gemv_rope;
 /* copy with type conversion and arbitrary strides (CPY / CONT / DUP): f32,f16,bf16 -> f32,f16,bf16; f32 -> q8_0 (the
  * KV-cache store; bit-exact to quantize_row_q8_0_ref, ggml-quants.c:191-212); same-type block copies of quantised
  * data.  Replaces ggml_cuda_cpy (ggml-cuda/cpy.cu:303-). */

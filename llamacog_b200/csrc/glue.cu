@@ -4,6 +4,7 @@
 // first dependent access) so that the next GEMV can prefetch its weights while they run.
 // Semantics follow the reference CPU operators (ggml/src/ggml-cpu/ops.cpp), cited per kernel.
 #include "common.cuh"
+#include "rope_units.cuh"
 #include "../../include/b200_ops.h"
 
 #include <algorithm>
@@ -170,19 +171,6 @@ __global__ void __launch_bounds__(256) rms_norm_generic_kernel(const tens src, c
 }
 
 // ---- rope (reference ggml-cpu/ops.cpp:5080-5118, 5178-5360): modes normal and neox ----
-struct rope_dev { int n_dims, neox; float freq_scale, ext_factor, attn_factor, theta_scale, corr0, corr1; };
-// rotation of pair ip of a row at position p: returns cos/sin (already scaled)
-__device__ __forceinline__ void rope_cs(const rope_dev & p, int64_t ip, int32_t posv, const float * __restrict__ ff, float & c, float & sn) {
-    const float theta_extrap = (float)posv * powf(p.theta_scale, (float)ip) / (ff ? ff[ip] : 1.0f);
-    float theta = p.freq_scale * theta_extrap, mscale = p.attn_factor;
-    if (p.ext_factor != 0.0f) {
-        const float y = ((float)ip - p.corr0) / fmaxf(0.001f, p.corr1 - p.corr0);
-        const float ramp = (1.0f - fminf(1.0f, fmaxf(0.0f, y))) * p.ext_factor;
-        theta = theta * (1.0f - ramp) + theta_extrap * ramp;
-        mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
-    }
-    c = cosf(theta) * mscale; sn = sinf(theta) * mscale;
-}
 template <typename T>
 __global__ void __launch_bounds__(256) rope_kernel(const tens src, const tens dst, const int32_t * __restrict__ pos,
                                                    const float * __restrict__ ff, const rope_dev p) {
@@ -202,8 +190,9 @@ __global__ void __launch_bounds__(256) rope_kernel(const tens src, const tens ds
         float c, sn; rope_cs(p, ip, pos[i2], ff, c, sn);
         const int64_t ia = p.neox ? ip : i0, ib = p.neox ? ip + p.n_dims / 2 : i0 + 1;
         const float x0 = (float)((const T *)s)[ia], x1 = (float)((const T *)s)[ib];
-        ((T *)d)[ia] = (T)(x0 * c - x1 * sn);
-        ((T *)d)[ib] = (T)(x0 * sn + x1 * c);
+        float ya, yb; rope_pair(x0, x1, c, sn, ya, yb);
+        ((T *)d)[ia] = (T)ya;
+        ((T *)d)[ib] = (T)yb;
     }
 }
 
@@ -299,7 +288,7 @@ __global__ void __launch_bounds__(256) ew_batch_kernel(const __grid_constant__ e
             float c, sn; rope_cs(p, ip, t.pos[i2], t.ff, c, sn);
             ia = p.neox ? ip : i0; ib = p.neox ? ip + p.n_dims / 2 : i0 + 1;
             const float x0 = s[ia], x1 = s[ib];
-            ya = x0 * c - x1 * sn; yb = x0 * sn + x1 * c;
+            rope_pair(x0, x1, c, sn, ya, yb);
         }
         d[ia] = ya; d[ib] = yb;
         if (t.kind == 1) { store_conv(d2, t.dst2, t.d2type, row0 + ia, ya); store_conv(d2, t.dst2, t.d2type, row0 + ib, yb); }
@@ -466,12 +455,7 @@ static int ew_build(const b200_ew_desc * tasks, int n, ew_batch & b, int64_t & n
             if ((prm->mode != 0 && prm->mode != 2) || prm->n_dims % 2 || prm->n_dims > d.src->ne[0] || d.src->ne[0] % 2) EW_FAIL();
             t.dst = mk(d.dst);
             t.pos = (const int32_t *)d.pos->data; t.ff = d.ffac ? (const float *)d.ffac->data : nullptr;
-            rope_dev & p = t.rp;
-            p.n_dims = prm->n_dims; p.neox = prm->mode == 2; p.freq_scale = prm->freq_scale; p.ext_factor = prm->ext_factor;
-            p.attn_factor = prm->attn_factor; p.theta_scale = powf(prm->freq_base, -2.0f / prm->n_dims);
-            auto corr_dim = [&](float n_rot) { return prm->n_dims * logf(prm->n_ctx_orig / (n_rot * 2 * 3.14159265358979323846f)) / (2 * logf(prm->freq_base)); };
-            p.corr0 = std::max(0.0f, floorf(corr_dim(prm->beta_fast)));
-            p.corr1 = std::min((float)prm->n_dims - 1, ceilf(corr_dim(prm->beta_slow)));
+            t.rp = rope_dev_from(*prm);
             t.n = nelem(d.src) / 2;
         } else t.n = nelem(d.src);
         if (d.kind != 0) {

@@ -29,6 +29,17 @@ static bool fuse_ok(const b200_mmvq_args * a, int ng) {
     if (a->fuse_resid || a->fuse_sum) {
         if (!a->fuse_resid || !a->fuse_sum || ng != 1) return false;
     }
+    if (a->rope) {
+        const b200_gemv_rope * r = a->rope;
+        if (a->fuse_resid || a->dbg_sumi || !r->pos || r->prm.mode != 0 || r->prm.n_dims % 2 || r->prm.n_dims <= 0) return false;
+        for (int g = 0; g < ng; ++g) {
+            const int m = r->mode[g];
+            if (m < 0 || m > 3) return false;
+            if (m == 0) continue;
+            if ((m == 1 || m == 2) && (!r->out[g] || r->head_dim[g] <= 0 || r->head_dim[g] % 2 || r->prm.n_dims > r->head_dim[g])) return false;
+            if ((m == 2 || m == 3) && (!(r->cell[g] || r->cell_slot[g]) || (r->cell_type[g] != T_F16 && r->cell_type[g] != T_F32 && r->cell_type[g] != T_BF16))) return false;
+        }
+    }
     if (a->norm_x) {
         if (!a->norm_w || !a->norm_y || !a->norm_out || a->K > 4096 || a->dbg_sumi) return false;
         if (!al16(a->norm_x) || !al16(a->norm_w) || !al16(a->norm_y) || !al16(a->norm_out)) return false;
@@ -59,8 +70,10 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     const int rb = bpr * block_bytes(a->type);
     if (a->nb1 != rb || rb % 16 || ((uintptr_t)a->Xq & 15)) return MMVQR_SKIP;
     int ntot = 0;
+    const int unit = a->rope ? 2 : 1;                                 // rope epilogue: rows are dealt to the CTAs in pairs
     for (int g = 0; g < ng; ++g) {
-        if (((uintptr_t)W[g] & 15) || N[g] <= 0) return MMVQR_SKIP;
+        if (((uintptr_t)W[g] & 15) || N[g] <= 0 || N[g] % unit) return MMVQR_SKIP;
+        if (a->rope && (a->rope->mode[g] == 1 || a->rope->mode[g] == 2) && N[g] % a->rope->head_dim[g]) return MMVQR_SKIP;
         ntot += N[g];
     }
     const int rpp = 256 / tpr, nw = tpr > 32 ? tpr / 32 : 1;
@@ -74,11 +87,11 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     int used = 0, rows_per_cta = 1;
     for (int g = 0; g < ng; ++g) {
         int share = g + 1 == ng ? std::max(1, gx_max - used) : std::max(1, (int)((int64_t)gx_max * N[g] / ntot));
-        share = std::max(1, std::min(share, (N[g] + rpp - 1) / rpp));
+        share = std::max(1, std::min(share, (N[g] / unit + rpp - 1) / rpp));
         p.cta0[g] = used; used += share;
         p.Wg[g] = (const uint8_t *)W[g]; p.Dg[g] = probe ? nullptr : dst[g];
-        p.rows_qg[g] = N[g] / share; p.rows_remg[g] = N[g] % share;
-        rows_per_cta = std::max(rows_per_cta, (N[g] + share - 1) / share);
+        p.rows_qg[g] = N[g] / unit / share; p.rows_remg[g] = N[g] / unit % share;      // in units of `unit` rows
+        rows_per_cta = std::max(rows_per_cta, unit * ((N[g] / unit + share - 1) / share));
     }
     p.cta0[ng] = used;
 
@@ -91,14 +104,16 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     int R = std::max(rq, (stage_kb * 1024 / rb) / rq * rq);
     R = std::min(R, std::max(rq, round_up((rows_per_cta + 3) / 4, rq)));
     R = std::min(R, round_up(rows_per_cta, rpp));
+    if (a->rope && (R & 1)) return MMVQR_SKIP;               // pairs must not straddle stages
     const int stage_bytes = round_up(R * rb + 16, 128);     // slack: the 2-byte aligned loads of Q6_K over-read 4 bytes
     const size_t budget = (size_t)smem_kb * 1024;
     const size_t per_stage = (size_t)stage_bytes + (size_t)R * nw * 4 + 16;
     const size_t act_bytes = (size_t)bpr * ACT_ITEM + (a->norm_x ? (size_t)K * 8 : 0);      // + the fp32 row of the fused norm and the norm weights
-    const size_t tail_bytes = 16 + 128 + (a->fuse_resid ? (size_t)rows_per_cta * 4 : 0) + 16;   // act barrier, norm partials, residual rows
+    const size_t tail_bytes = 16 + 128 + ((a->fuse_resid || a->rope) ? (size_t)(rows_per_cta + 2) * 4 : 0) + 16;   // act barrier, norm partials, residual rows / rope cos-sin
     if (budget < act_bytes + tail_bytes + 128 + per_stage) return MMVQR_SKIP;
     int nstages = (int)std::min<size_t>(max_stages, (budget - act_bytes - tail_bytes - 128) / per_stage);
-    const int q0 = ramp ? std::max(1, R >> 3) : R, q1 = ramp ? std::max(1, R >> 2) : R, q2 = ramp ? std::max(1, R >> 1) : R;
+    const bool rmp = ramp && !a->rope;
+    const int q0 = rmp ? std::max(1, R >> 3) : R, q1 = rmp ? std::max(1, R >> 2) : R, q2 = rmp ? std::max(1, R >> 1) : R;
     const int need = rows_per_cta <= q0 ? 1 : rows_per_cta <= q0 + q1 ? 2 : rows_per_cta <= q0 + q1 + q2 ? 3 : 3 + (rows_per_cta - q0 - q1 - q2 + R - 1) / R;
     nstages = std::min(nstages, need);
     if (nstages < 1) return MMVQR_SKIP;
@@ -106,6 +121,15 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
 
     p.nx = a->norm_x; p.nw = a->norm_w; p.nnorm = a->norm_y; p.nout = a->norm_out; p.nxq = a->norm_x ? (uint8_t *)a->Xq : nullptr; p.neps = a->norm_eps;
     p.resid = a->fuse_resid; p.dsum = a->fuse_sum; p.resid_rows = a->fuse_resid ? rows_per_cta : 0;
+    if (a->rope) {
+        const b200_gemv_rope * r = a->rope;
+        p.rope_on = 1; p.rope_rows = rows_per_cta + 2;
+        for (int g = 0; g < ng; ++g) {
+            p.rmode[g] = r->mode[g]; p.rout[g] = r->out[g]; p.rcell[g] = (char *)r->cell[g]; p.rslot[g] = (char * const *)r->cell_slot[g];
+            p.rctype[g] = r->cell_type[g]; p.rcesz[g] = r->cell_type[g] == T_F32 ? 4 : 2; p.rhd[g] = std::max(2, r->head_dim[g]);
+        }
+        p.rpos = r->pos; p.rff = r->ffac; p.rp = rope_dev_from(r->prm);
+    }
     p.Xq = (const uint8_t *)a->Xq; p.K = K; p.BPR = bpr; p.TPR = tpr; p.lgTPR = lg; p.rb = rb;
     p.R = R; p.nstages = nstages; p.stage_bytes = stage_bytes;
     p.r0 = q0; p.r1 = q1; p.r2 = q2; p.stagger = stagger;

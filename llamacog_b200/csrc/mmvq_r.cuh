@@ -28,6 +28,7 @@
 // combination order is fixed (deterministic) but ours.
 #pragma once
 #include "mmvq_units.cuh"
+#include "rope_units.cuh"
 
 namespace b200 {
 
@@ -51,6 +52,11 @@ struct mmvqr_params {
     const float * nx; const float * nw; float * nnorm; float * nout; uint8_t * nxq; float neps;
     // fused residual ADD epilogue (single matrix): dsum[n] = dst[n] + resid[n]
     const float * resid; float * dsum; int resid_rows;
+    // fused ROPE + KV-cache store epilogue of a q/k/v launch (b200_gemv_rope): per matrix mode 0 none, 1 out = rope(row sums),
+    // 2 also cell = convert(out), 3 cell = convert(row sums).  Row ranges of the CTAs are even-aligned (pairs stay together).
+    int rope_on, rope_rows;
+    int rmode[3]; float * rout[3]; char * rcell[3]; char * const * rslot[3]; int rctype[3], rcesz[3], rhd[3];
+    const int32_t * rpos; const float * rff; rope_dev rp;
 };
 
 // rms_norm arithmetic shared with add_rms_norm_mul_kernel (fused.cu): same expressions, same order, bit-identical results
@@ -156,14 +162,16 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
     const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * p.nstages, actbar = empty0 + 8 * p.nstages, wbar = actbar + 8;
     float * npart = reinterpret_cast<float *>(bars + 2 * p.nstages + 2);     // 32 floats: sums of squares per 32 float4s
     float * rsd = npart + 32;                                                // resid_rows floats: this CTA's residual values
+    float * csn = rsd + p.resid_rows;                                        // rope_rows floats: (cos, sin) of this CTA's row pairs
 
     int cta = blockIdx.x, g = 0;
     while (g + 1 < p.ngroup && cta >= p.cta0[g + 1]) ++g;
     cta -= p.cta0[g];
     const uint8_t * Wc = p.Wg[g];
     float * Dc = p.Dg[g];
-    const int row_lo = cta * p.rows_qg[g] + min(cta, p.rows_remg[g]);
-    const int nrows = p.rows_qg[g] + (cta < p.rows_remg[g] ? 1 : 0);
+    const int unit = p.rope_on ? 2 : 1;        // rope: rows are dealt in pairs (rows_qg / rows_remg count pairs)
+    const int row_lo = unit * (cta * p.rows_qg[g] + min(cta, p.rows_remg[g]));
+    const int nrows = unit * (p.rows_qg[g] + (cta < p.rows_remg[g] ? 1 : 0));
     // Stage s of this CTA covers rows [srow(s), srow(s) + snr(s)) of its range.  The first three stages are short (r0, r1,
     // r2 rows): bulk copies in flight share the SM's bandwidth, so equal stages all land together after the whole batch
     // has streamed (the first dot product of a 66 MB gate/up GEMV started 5-8 us after its loads were issued,
@@ -200,6 +208,19 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
             for (int s = 0; s < min(nst, (NORM || p.stagger) ? 1 : p.nstages); ++s) issue(s);
             if (!NORM && p.stagger && nst > 1) { mbar_wait(full0, 0); for (int s = 1; s < min(nst, p.nstages); ++s) issue(s); }
         }
+        const int rmode = p.rope_on ? p.rmode[g] : 0;
+        if (rmode == 1 || rmode == 2) {
+            // cos / sin of this CTA's row pairs: depends on the position only (a graph input), so it is computed while the
+            // previous kernel is still running and the weights are in flight
+            const int hd = p.rhd[g], posv = p.rpos[0];
+            for (int o2 = lane; 2 * o2 < nrows; o2 += 32) {
+                const int d = (row_lo + 2 * o2) % hd;
+                float c = 1.0f, sn = 0.0f;
+                if (d < p.rp.n_dims) rope_cs(p.rp, d >> 1, posv, p.rff, c, sn);
+                csn[2 * o2] = c; csn[2 * o2 + 1] = sn;
+            }
+            __syncwarp();
+        }
         pdl_wait();           // the activations come from the previous kernel; dst may still be read by it
         if (lane == 0) {      // one coalesced copy of the column; the consumers pick their registers out of shared memory
             const uint32_t ab = NORM ? (uint32_t)p.K * 4 : (uint32_t)p.BPR * ACT_ITEM;
@@ -216,11 +237,39 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
             mbar_wait(empty0 + 8 * slot, (s / p.nstages) & 1);
             const int r0 = row_lo + srow(s), nr = snr(s);
             const float * ps = partials + (size_t)slot * part_stage;
-            for (int o = lane; o < nr; o += 32) {
-                float sum = 0.0f;
-                for (int wv = 0; wv < NW; ++wv) sum += ps[o * NW + wv];
-                Dc[r0 + o] = sum;
-                if (p.resid) p.dsum[r0 + o] = sum + rsd[r0 - row_lo + o];
+            if (rmode == 0) {
+                for (int o = lane; o < nr; o += 32) {
+                    float sum = 0.0f;
+                    for (int wv = 0; wv < NW; ++wv) sum += ps[o * NW + wv];
+                    Dc[r0 + o] = sum;
+                    if (p.resid) p.dsum[r0 + o] = sum + rsd[r0 - row_lo + o];
+                }
+            } else {
+                // q / k: rotate the adjacent pair (2i, 2i+1) -- the partner's sum sits in the neighbouring lane (r0 and nr are
+                // even) -- and store the result (f32 tensor of the ROPE node, K row of the cache); v: the row into the cache
+                char * cell = p.rslot[g] ? *p.rslot[g] : p.rcell[g];
+                for (int o0 = 0; o0 < nr; o0 += 32) {
+                    const int o = o0 + lane, n = r0 + o;
+                    const bool valid = o < nr;
+                    float sum = 0.0f;
+                    if (valid) for (int wv = 0; wv < NW; ++wv) sum += ps[o * NW + wv];
+                    if (rmode == 3) {
+                        if (valid) { Dc[n] = sum; store_as(cell + (size_t)n * p.rcesz[g], p.rctype[g], sum); }
+                        continue;
+                    }
+                    const float other = __shfl_xor_sync(0xffffffffu, sum, 1);
+                    if (valid) {
+                        float y = sum;
+                        if ((n % p.rhd[g]) < p.rp.n_dims) {
+                            const int lo = (n - row_lo) & ~1;
+                            float ya, yb;
+                            rope_pair((n & 1) ? other : sum, (n & 1) ? sum : other, csn[lo], csn[lo + 1], ya, yb);
+                            y = (n & 1) ? yb : ya;
+                        }
+                        p.rout[g][n] = y;
+                        if (rmode == 2) store_as(cell + (size_t)n * p.rcesz[g], p.rctype[g], y);
+                    }
+                }
             }
             __syncwarp();
             if (lane == 0 && s + p.nstages < nst) issue(s + p.nstages);

@@ -24,7 +24,8 @@ class MmvqArgs(C.Structure):
                 ("pdl", C.c_int), ("dbg_sumi", C.c_void_p), ("Xq", C.c_void_p), ("xq_sy", C.c_int64), ("xq_sz", C.c_int64),
                 ("pf_n", C.c_int), ("pf_ptr", C.c_void_p * 3), ("pf_bytes", C.c_int64 * 3),
                 ("fuse_resid", C.c_void_p), ("fuse_sum", C.c_void_p),
-                ("norm_x", C.c_void_p), ("norm_w", C.c_void_p), ("norm_y", C.c_void_p), ("norm_out", C.c_void_p), ("norm_eps", C.c_float)]
+                ("norm_x", C.c_void_p), ("norm_w", C.c_void_p), ("norm_y", C.c_void_p), ("norm_out", C.c_void_p), ("norm_eps", C.c_float),
+                ("rope", C.c_void_p)]
 
 
 _lib = None
