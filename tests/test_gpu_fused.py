@@ -193,3 +193,71 @@ def test_gemv_fusion_refused_when_not_eligible():
     a.M = 2
     assert L.b200_mmvq_fusable(C.byref(a), C.c_int(1), None, None) == 0
     assert L.b200_mul_mat_vec_q_ex(C.byref(a), _st(ops)) == -4
+
+
+class _RopeParams(C.Structure):
+    _fields_ = [("n_dims", C.c_int), ("mode", C.c_int), ("n_ctx_orig", C.c_int), ("freq_base", C.c_float), ("freq_scale", C.c_float),
+                ("ext_factor", C.c_float), ("attn_factor", C.c_float), ("beta_fast", C.c_float), ("beta_slow", C.c_float)]
+
+
+class _GemvRope(C.Structure):
+    _fields_ = [("mode", C.c_int * 3), ("out", C.c_void_p * 3), ("cell", C.c_void_p * 3), ("cell_slot", C.c_void_p * 3),
+                ("cell_type", C.c_int * 3), ("head_dim", C.c_int * 3), ("pos", C.c_void_p), ("ffac", C.c_void_p), ("prm", _RopeParams)]
+
+
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K"])
+@pytest.mark.parametrize("hd,n_dims,pos,ext,use_ff,slot", [(128, 128, 77, 0.0, False, False), (128, 128, 4095, 0.0, True, True),
+                                                           (64, 32, 5, 0.0, False, False), (128, 128, 300, 1.0, False, True)])
+def test_gemv_rope_epilogue_matches_rope_op(tname, hd, n_dims, pos, ext, use_ff, slot):
+    """ROPE + KV-cache stores in the q/k/v mat-vec's epilogue (b200_gemv_rope): rope(q) as f32, rope(k) as f32 and as the f16
+    cache row, v as the f16 cache row must equal, bit for bit, b200_op_rope (and a round-to-nearest f16 conversion) applied
+    to the plain grouped mat-vec's outputs; also through a device pointer slot (CUDA-graph replay), with frequency factors,
+    partial rotation (n_dims < head size) and YaRN mixing."""
+    import numpy as np
+    import oracle as O
+    ops = _ops(); L = ops.lib()
+    t = O.QUANT_TYPES[tname]
+    K, nh, nkv = 2048, 12, 4
+    Ns = [nh * hd, nkv * hd, nkv * hd]
+    rng = np.random.default_rng(hd + pos)
+    Ws = [torch.from_numpy(O.random_quant_bytes(t, n, K, rng).reshape(-1)).cuda() for n in Ns]
+    torch.manual_seed(pos)
+    X = torch.randn(1, K, device="cuda")
+    xq = ops.quantize_acts(X)
+    ref = ops.mul_mat_vec_q_group(t, Ws, Ns, X, K, Xq=xq)
+    prm = _RopeParams(n_dims=n_dims, mode=0, n_ctx_orig=8192, freq_base=500000.0, freq_scale=1.0 if ext == 0.0 else 0.25, ext_factor=ext,
+                      attn_factor=1.0, beta_fast=32.0, beta_slow=1.0)
+    posd = torch.tensor([pos], dtype=torch.int32, device="cuda")
+    ff = (torch.rand(n_dims // 2, device="cuda") + 0.5) if use_ff else None
+    want = []
+    for g in range(2):
+        src = ref[g].view(1, Ns[g] // hd, hd).contiguous(); dst = torch.empty_like(src)
+        assert L.b200_op_rope(C.byref(ops.as_b200(src)), C.byref(ops.as_b200(posd)), C.byref(ops.as_b200(ff)) if use_ff else None,
+                              C.byref(ops.as_b200(dst)), C.byref(prm), _st(ops)) == 0
+        want.append(dst.view(1, -1))
+    # fused
+    oq = torch.zeros(1, Ns[0], device="cuda"); ok_ = torch.zeros(1, Ns[1], device="cuda")
+    kc = torch.zeros(Ns[1], dtype=torch.float16, device="cuda"); vc = torch.zeros(Ns[2], dtype=torch.float16, device="cuda")
+    slots = torch.tensor([kc.data_ptr(), vc.data_ptr()], dtype=torch.int64, device="cuda")
+    gr = _GemvRope()
+    gr.mode[0], gr.mode[1], gr.mode[2] = 1, 2, 3
+    gr.out[0], gr.out[1] = oq.data_ptr(), ok_.data_ptr()
+    if slot:
+        gr.cell_slot[1], gr.cell_slot[2] = slots.data_ptr(), slots.data_ptr() + 8
+    else:
+        gr.cell[1], gr.cell[2] = kc.data_ptr(), vc.data_ptr()
+    gr.cell_type[1] = gr.cell_type[2] = 1
+    gr.head_dim[0] = gr.head_dim[1] = hd
+    gr.pos = posd.data_ptr(); gr.ffac = ff.data_ptr() if use_ff else None; gr.prm = prm
+    raw = [torch.zeros(1, n, device="cuda") for n in Ns]
+    a = ops.MmvqArgs(type=t, W=Ws[0].data_ptr(), nb1=ops.row_bytes(t, K), X=None, xs=K, dst=raw[0].data_ptr(), ds=Ns[0], N=Ns[0], K=K, M=1,
+                     ny=1, nz=1, pdl=-1, Xq=xq.data_ptr(), rope=C.addressof(gr))
+    Wp = (C.c_void_p * 3)(*[w.data_ptr() for w in Ws]); Dp = (C.c_void_p * 3)(*[d.data_ptr() for d in raw])
+    Np = (C.c_int * 3)(*Ns); dsp = (C.c_int64 * 3)(*Ns)
+    if not L.b200_mmvq_fusable(C.byref(a), C.c_int(3), Wp, Np):
+        pytest.skip("shape not taken by the register-resident kernel")
+    assert L.b200_mul_mat_vec_q_group(C.byref(a), C.c_int(3), Wp, Dp, Np, dsp, _st(ops)) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(oq, want[0]) and torch.equal(ok_, want[1])
+    assert torch.equal(kc, want[1].view(-1).half())
+    assert torch.equal(raw[2], ref[2]) and torch.equal(vc, ref[2].view(-1).half())
