@@ -145,6 +145,15 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
+// rms_norm arithmetic shared by rms_norm_kernel (glue.cu), add_rms_norm_mul_kernel (fused.cu) and the GEMV's fused prologue
+// (mmvq_r.cuh): same operations in the same order, bit-identical results
+// (explicit fused multiply-adds: left to the compiler, the same expression contracted as x*x first in one kernel and y*y
+// first in the other -- a last-bit difference in one layer of one decode step out of hundreds, found by hashing node outputs)
+__device__ __forceinline__ float sumsq4(const float4 v) {
+    return __fmaf_rn(v.w, v.w, __fmaf_rn(v.z, v.z, __fmaf_rn(v.y, v.y, __fmul_rn(v.x, v.x))));
+}
+__device__ __forceinline__ float rms_scale(float tot, int K, float eps) { return rsqrtf(tot / (float)K + eps); }
+
 extern int g_launches;   // kernels launched by this library (bench.py gpu_launches)
 int pdl_default();       // env B200_PDL (default 1): launch kernels with programmatic dependent launch
 

@@ -136,14 +136,14 @@ __global__ void __launch_bounds__(1024) rms_norm_kernel(const tens src, const te
     for (int k = 0; k < VPT; ++k) { const int i = threadIdx.x + k * blockDim.x; v[k] = i < n4 ? x[i] : make_float4(0.f, 0.f, 0.f, 0.f); }
     float s = 0.0f;
 #pragma unroll
-    for (int k = 0; k < VPT; ++k) s += v[k].x * v[k].x + v[k].y * v[k].y + v[k].z * v[k].z + v[k].w * v[k].w;
+    for (int k = 0; k < VPT; ++k) s += sumsq4(v[k]);
     s = warp_sum(s);
     __shared__ float part[32];
     if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
     __syncthreads();
     float tot = 0.0f;
     for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += part[w];
-    const float scale = rsqrtf(tot / (float)src.ne[0] + eps);
+    const float scale = rms_scale(tot, (int)src.ne[0], eps);
 #pragma unroll
     for (int k = 0; k < VPT; ++k) {
         const int i = threadIdx.x + k * blockDim.x;

@@ -59,10 +59,6 @@ struct mmvqr_params {
     const int32_t * rpos; const float * rff; rope_dev rp;
 };
 
-// rms_norm arithmetic shared with add_rms_norm_mul_kernel (fused.cu): same expressions, same order, bit-identical results
-__device__ __forceinline__ float sumsq4(const float4 v) { return v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w; }
-__device__ __forceinline__ float rms_scale(float tot, int K, float eps) { return rsqrtf(tot / (float)K + eps); }
-
 struct hacts { int q[4][8]; float d8[4], dsq[4]; int m32a[4], m32b[4]; };
 
 // sp: shared address of the thread's 192 bytes (4 blocks of 48) inside the staged copy of Xq
