@@ -40,15 +40,27 @@ __global__ void __launch_bounds__(256) mask_classify_kernel(const char * __restr
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int lim = min(128, n_kv - 128 * j);
     int any = 0, nz = 0;
-    for (int r = warp; r < 128; r += 8) {
-        const int qi = 128 * qt + r;
-        if (qi >= N) break;
-        const __half * row = reinterpret_cast<const __half *>(mask + (int64_t)qi * nbm1) + 128 * j;
-        if (vec && lim == 128) {
-            const uint2 u = __ldg(reinterpret_cast<const uint2 *>(row) + lane);
-            any |= (u.x != 0xFC00FC00u) | (u.y != 0xFC00FC00u);
-            nz |= ((u.x | u.y) & 0x7FFF7FFFu) != 0u;
-        } else {
+    if (vec && lim == 128) {
+        // all 16 rows of the warp in flight at once (a row-by-row loop paid one memory round trip per row: 16 in series)
+        uint2 u[16];
+#pragma unroll
+        for (int it = 0; it < 16; ++it) {
+            const int qi = 128 * qt + warp + 8 * it;
+            if (qi < N) u[it] = __ldg(reinterpret_cast<const uint2 *>(reinterpret_cast<const __half *>(mask + (int64_t)qi * nbm1) + 128 * j) + lane);
+        }
+#pragma unroll
+        for (int it = 0; it < 16; ++it) {
+            const int qi = 128 * qt + warp + 8 * it;
+            if (qi < N) {
+                any |= (u[it].x != 0xFC00FC00u) | (u[it].y != 0xFC00FC00u);
+                nz |= ((u[it].x | u[it].y) & 0x7FFF7FFFu) != 0u;
+            }
+        }
+    } else {
+        for (int r = warp; r < 128; r += 8) {
+            const int qi = 128 * qt + r;
+            if (qi >= N) break;
+            const __half * row = reinterpret_cast<const __half *>(mask + (int64_t)qi * nbm1) + 128 * j;
             for (int i = lane; i < lim; i += 32) {
                 const unsigned short h = __half_as_ushort(row[i]);
                 any |= h != 0xFC00u; nz |= (h & 0x7FFFu) != 0;

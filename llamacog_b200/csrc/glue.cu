@@ -196,6 +196,47 @@ __global__ void __launch_bounds__(256) rope_kernel(const tens src, const tens ds
     }
 }
 
+// Prefill shape (many tokens): one thread per (token, pair, group of ROPE_HPT heads), so the powf / sincos of rope_cs are paid once
+// per group instead of once per head, and the group's loads are all issued before the first use (the per-element kernel is bound
+// by the transcendentals, a thread that walks all the heads by load latency).  Same rope_cs / rope_pair arithmetic: bit-identical.
+constexpr int ROPE_HPT = 8;
+template <typename T>
+__global__ void __launch_bounds__(256) rope_heads_kernel(const tens src, const tens dst, const int32_t * __restrict__ pos,
+                                                         const float * __restrict__ ff, const rope_dev p, int ngrp) {
+    pdl_enter();
+    const int64_t half0 = src.ne[0] / 2;
+    const int64_t total = half0 * ngrp * src.ne[2] * src.ne[3];
+    const int nh = (int)src.ne[1];
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t ip = i % half0, r = i / half0;
+        const int h0 = (int)(r % ngrp) * ROPE_HPT;
+        const int64_t r2 = r / ngrp, i2 = r2 % src.ne[2], i3 = r2 / src.ne[2];
+        const char * s = src.d + i2 * src.nb[2] + i3 * src.nb[3] + h0 * src.nb[1];
+        char * d = dst.d + i2 * dst.nb[2] + i3 * dst.nb[3] + h0 * dst.nb[1];
+        const int64_t i0 = 2 * ip;
+        const bool tail = i0 >= p.n_dims;          // pass-through of the unrotated tail
+        const int64_t ia = tail ? i0 : (p.neox ? ip : i0), ib = tail ? i0 + 1 : (p.neox ? ip + p.n_dims / 2 : i0 + 1);
+        float x0[ROPE_HPT], x1[ROPE_HPT];
+#pragma unroll
+        for (int h = 0; h < ROPE_HPT; ++h)
+            if (h0 + h < nh) {
+                const T * sh = (const T *)(s + h * src.nb[1]);
+                x0[h] = (float)sh[ia]; x1[h] = (float)sh[ib];
+            }
+        float c = 1.0f, sn = 0.0f;
+        if (!tail) rope_cs(p, ip, pos[i2], ff, c, sn);
+#pragma unroll
+        for (int h = 0; h < ROPE_HPT; ++h)
+            if (h0 + h < nh) {
+                T * dh = (T *)(d + h * dst.nb[1]);
+                float ya = x0[h], yb = x1[h];
+                if (!tail) rope_pair(x0[h], x1[h], c, sn, ya, yb);
+                dh[ia] = (T)ya;
+                dh[ib] = (T)yb;
+            }
+    }
+}
+
 // ---- cpy / cont / dup with conversion ----
 template <typename T> __device__ __forceinline__ float to_f32(T v);
 template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
@@ -218,6 +259,19 @@ __global__ void __launch_bounds__(256) cpy_kernel(const tens src, const tens dst
     char * dd = dslot ? *dslot : dst.d;          // CUDA-graph replay: the destination (KV cache cell) comes from a pointer table
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
         *(D *)(dd + flat_off(dst, i)) = from_f32<D>(to_f32<S>(*(const S *)(src.d + flat_off(src, i))));
+}
+// four consecutive elements per thread when rows of both sides hold a multiple of four and every row start is vector aligned
+// (the K / V store of a prefill batch): one offset computation per four elements, 16-byte loads, 8- or 16-byte stores
+template <typename S, typename D>
+__global__ void __launch_bounds__(256) cpy_vec4_kernel(const tens src, const tens dst, int64_t n4) {
+    pdl_enter();
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        struct alignas(4 * sizeof(S)) sv_t { S v[4]; } sv = *(const sv_t *)(src.d + flat_off(src, 4 * i));
+        struct alignas(4 * sizeof(D)) dv_t { D v[4]; } dv;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) dv.v[j] = from_f32<D>(to_f32<S>(sv.v[j]));
+        *(dv_t *)(dst.d + flat_off(dst, 4 * i)) = dv;
+    }
 }
 // f32 -> q8_0 blocks: one warp per block of 32 consecutive source elements (the same flat order);
 // arithmetic of quantize_row_q8_0_ref (ggml-quants.c:191-212): d = amax/127, id = 1/d, q = roundf(x*id)
@@ -397,6 +451,14 @@ extern "C" int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, co
     p.corr0 = std::max(0.0f, floorf(corr_dim(prm->beta_fast)));
     p.corr1 = std::min((float)prm->n_dims - 1, ceilf(corr_dim(prm->beta_slow)));
     const float * ff = ffac ? (const float *)ffac->data : nullptr;
+    // a prefill batch: enough (token, pair) positions to fill the GPU with one thread per ROPE_HPT heads
+    const int ngrp = (int)((src->ne[1] + ROPE_HPT - 1) / ROPE_HPT);
+    const int64_t npos = src->ne[0] / 2 * src->ne[2] * src->ne[3];
+    static const bool heads_on = !getenv("B200_ROPE_HEADS") || atoi(getenv("B200_ROPE_HEADS")) != 0;
+    if (heads_on && src->ne[1] >= 4 && npos >= 8192) {
+        if (src->type == T_F32) return launch(rope_heads_kernel<float>, grid_for(npos * ngrp, 256), 256, 0, (cudaStream_t)stream, mk(src), mk(dst), (const int32_t *)pos->data, ff, p, ngrp);
+        return launch(rope_heads_kernel<__half>, grid_for(npos * ngrp, 256), 256, 0, (cudaStream_t)stream, mk(src), mk(dst), (const int32_t *)pos->data, ff, p, ngrp);
+    }
     if (src->type == T_F32) return launch(rope_kernel<float>, grid_for(n, 256), 256, 0, (cudaStream_t)stream, mk(src), mk(dst), (const int32_t *)pos->data, ff, p);
     return launch(rope_kernel<__half>, grid_for(n, 256), 256, 0, (cudaStream_t)stream, mk(src), mk(dst), (const int32_t *)pos->data, ff, p);
 }
@@ -431,6 +493,20 @@ extern "C" int b200_op_cpy_indirect(const b200_tensor * src, const b200_tensor *
         const int be = block_elems(src->type);
         if (src->ne[0] % be || dst->ne[0] % be) return -1;
         return launch(cpy_blocks_kernel, grid_for(n / be, 256), 256, 0, st, mk(src), mk(dst), n / be, block_bytes(src->type), be, dslot);
+    }
+    {   // vector path (see cpy_vec4_kernel)
+        auto vec_ok = [](const b200_tensor * t) {
+            const size_t a = 4 * type_size(t->type);
+            return t->nb[0] == type_size(t->type) && t->ne[0] % 4 == 0 && ((uintptr_t)t->data % a) == 0 &&
+                   (t->ne[1] == 1 || t->nb[1] % a == 0) && (t->ne[2] == 1 || t->nb[2] % a == 0) && (t->ne[3] == 1 || t->nb[3] % a == 0);
+        };
+        static const bool vec_on = !getenv("B200_CPY_VEC") || atoi(getenv("B200_CPY_VEC")) != 0;
+        if (vec_on && !dslot && n >= 16384 && vec_ok(src) && vec_ok(dst)) {
+#define B200_CPY_VCASE(ST, SC, DT, DC) if (src->type == ST && dst->type == DT) return launch(cpy_vec4_kernel<SC, DC>, grid_for(n / 4, 256), 256, 0, st, mk(src), mk(dst), n / 4);
+            B200_CPY_VCASE(T_F32, float, T_F16, __half) B200_CPY_VCASE(T_F32, float, B200_TYPE_BF16, __nv_bfloat16)
+            B200_CPY_VCASE(T_F16, __half, T_F32, float) B200_CPY_VCASE(T_F32, float, T_F32, float) B200_CPY_VCASE(T_F16, __half, T_F16, __half)
+#undef B200_CPY_VCASE
+        }
     }
     B200_CPY_CASE(T_F32, float, T_F32, float) B200_CPY_CASE(T_F32, float, T_F16, __half) B200_CPY_CASE(T_F32, float, B200_TYPE_BF16, __nv_bfloat16)
     B200_CPY_CASE(T_F16, __half, T_F32, float) B200_CPY_CASE(T_F16, __half, T_F16, __half) B200_CPY_CASE(T_F16, __half, B200_TYPE_BF16, __nv_bfloat16)

@@ -261,3 +261,48 @@ def test_gemv_rope_epilogue_matches_rope_op(tname, hd, n_dims, pos, ext, use_ff,
     assert torch.equal(oq, want[0]) and torch.equal(ok_, want[1])
     assert torch.equal(kc, want[1].view(-1).half())
     assert torch.equal(raw[2], ref[2]) and torch.equal(vc, ref[2].view(-1).half())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16])
+@pytest.mark.parametrize("hd,nh,n_dims,mode,T", [(128, 32, 128, 0, 512), (128, 8, 128, 0, 512), (64, 12, 32, 0, 300), (128, 16, 128, 2, 256),
+                                               (80, 5, 40, 2, 333)])
+def test_rope_prefill_kernel_matches_decode_kernel(dtype, hd, nh, n_dims, mode, T):
+    """b200_op_rope on a prefill batch takes the kernel that walks the heads per (token, pair) thread (cos/sin once per position
+    and pair); it must equal, bit for bit, the per-element kernel that small batches take (here: the same rows in chunks of 8 tokens)."""
+    ops = _ops(); L = ops.lib()
+    torch.manual_seed(T + nh)
+    src = torch.randn(T, nh, hd, device="cuda").to(dtype)
+    pos = torch.arange(1000, 1000 + T, dtype=torch.int32, device="cuda")
+    prm = _RopeParams(n_dims=n_dims, mode=mode, n_ctx_orig=8192, freq_base=500000.0, freq_scale=1.0, ext_factor=0.0, attn_factor=1.0,
+                      beta_fast=32.0, beta_slow=1.0)
+    got = torch.empty_like(src); want = torch.empty_like(src)
+    assert L.b200_op_rope(C.byref(ops.as_b200(src)), C.byref(ops.as_b200(pos)), None, C.byref(ops.as_b200(got)), C.byref(prm), _st(ops)) == 0
+    for t0 in range(0, T, 8):
+        s = src[t0:t0 + 8]; d = want[t0:t0 + 8]; p = pos[t0:t0 + 8]
+        assert L.b200_op_rope(C.byref(ops.as_b200(s)), C.byref(ops.as_b200(p)), None, C.byref(ops.as_b200(d)), C.byref(prm), _st(ops)) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(got, want)
+    if n_dims < hd:
+        assert torch.equal(got[..., n_dims:], src[..., n_dims:])
+
+
+@pytest.mark.parametrize("sd,dd", [(torch.float32, torch.float16), (torch.float32, torch.bfloat16), (torch.float16, torch.float32),
+                                   (torch.float32, torch.float32)])
+def test_cpy_vector_path_strided(sd, dd):
+    """CPY of a prefill batch into a strided destination (the K / V store: rows of the batch into rows of a wider cache) and from a
+    strided source, through the four-elements-per-thread kernel: exact round-to-nearest conversion, untouched bytes stay untouched."""
+    ops = _ops(); L = ops.lib()
+    torch.manual_seed(7)
+    T, n = 512, 1024
+    src_full = torch.randn(T, n + 64, device="cuda").to(sd)
+    src = src_full[:, 32:32 + n]                      # strided source view, 16-byte aligned rows
+    cache = torch.full((T + 8, 2 * n), 7.0, device="cuda").to(dd)
+    dst = cache[4:4 + T, n:]                          # strided destination view
+    assert L.b200_op_cpy(C.byref(ops.as_b200(src)), C.byref(ops.as_b200(dst)), _st(ops)) == 0
+    # different logical shapes with the same element count (flat order): [T, n] -> [2T, n/2]
+    flat = torch.zeros(2 * T, n // 2, device="cuda").to(dd)
+    assert L.b200_op_cpy(C.byref(ops.as_b200(src)), C.byref(ops.as_b200(flat)), _st(ops)) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(dst, src.to(dd))
+    assert torch.equal(flat.view(T, n), src.to(dd))
+    assert bool((cache[:4] == 7).all()) and bool((cache[4 + T:] == 7).all()) and bool((cache[:, :n] == 7).all())
