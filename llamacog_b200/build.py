@@ -27,6 +27,8 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-I", os.path.join(ROOT, "include")]
 if os.environ.get("B200_KTRACE", "0") not in ("", "0"):      # debug build with the kernel timeline hooks (common.cuh); rebuild everything
     NVCC_FLAGS.append("-DB200_KTRACE")
+if os.environ.get("B200_MMQ_TRACE", "0") not in ("", "0"):   # debug build: clock64 stamps inside mmq_kernel (tools/mmq_debug.py trace)
+    NVCC_FLAGS.append("-DB200_MMQ_TRACE")
 
 
 def _newer(src_files, target):

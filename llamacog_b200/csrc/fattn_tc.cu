@@ -187,7 +187,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && nact > 0) {             // tensor-core issue
+        if (nact > 0 && elect_one()) {           // tensor-core issue
             const uint32_t idesc_s = umma_idesc(0, 128, 0), idesc_o = umma_idesc(0, D, 1);
             auto issue_s = [&](int jj) {
                 const int st = jj & 1;

@@ -292,6 +292,7 @@ struct mmq_params {
     int tn;                      // tokens per tile: 32, 64, 128 or 256
     int nb;                      // depth of the activation-tile ring in shared memory (<= NB_MAX)
     int na;                      // depth of the A ring in tensor memory: 4 or 8 (even)
+    int nr;                      // depth of the raw weight-block ring in shared memory: 2 or 4
     int tmem_cols;               // 256 or 512
     long long * trace;           // debug: clock64 stamps of CTA (0,0), [event][index] (b200_mmq_debug_trace)
     // MUL_MAT_ID (expert = blockIdx.z): activation rows sorted by expert; rows [off[e], off[e] + cnt[e]) belong to expert e,
@@ -320,8 +321,9 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
     const int tn = p.tn, nb = p.nb, na = p.na;
     const uint32_t b_slot = (uint32_t)tn * 128u;
-    const uint32_t sB = base, sR = sB + (uint32_t)nb * b_slot, sBar = sR + 2 * RAW;
-    const uint32_t raw_full = sBar, raw_empty = sBar + 16, a_full = sBar + 32, a_empty = a_full + 8 * NA_MAX,
+    const int nr = p.nr, lg_nr = nr == 4 ? 2 : 1;
+    const uint32_t sB = base, sR = sB + (uint32_t)nb * b_slot, sBar = sR + (uint32_t)nr * RAW;
+    const uint32_t raw_full = sBar, raw_empty = sBar + 32, a_full = sBar + 64, a_empty = a_full + 8 * NA_MAX,
                    b_full = a_empty + 8 * NA_MAX, b_empty = b_full + 8 * NB_MAX, tmem_full = b_empty + 8 * NB_MAX, tmem_slot = tmem_full + 8;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -338,7 +340,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
     const uint32_t a_col0 = (uint32_t)p.tmem_cols - 32u * (uint32_t)na;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 2; ++i) { mbar_init(raw_full + 8 * i, 1); mbar_init(raw_empty + 8 * i, 8); }
+        for (int i = 0; i < 4; ++i) { mbar_init(raw_full + 8 * i, 1); mbar_init(raw_empty + 8 * i, 8); }
         for (int i = 0; i < NA_MAX; ++i) { mbar_init(a_full + 8 * i, 4); mbar_init(a_empty + 8 * i, 1); }
         for (int i = 0; i < NB_MAX; ++i) { mbar_init(b_full + 8 * i, 1); mbar_init(b_empty + 8 * i, 1); }
         mbar_init(tmem_full, 1);
@@ -356,8 +358,8 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
     if (warp == 0) {
         if (lane == 0) {                         // raw weight blocks: one 128-row box per 256-K block
             for (int kb = 0; kb < nkb; ++kb) {
-                const int s = kb & 1;
-                mbar_wait_b(raw_empty + 8 * s, ((kb >> 1) & 1) ^ 1);
+                const int s = kb & (nr - 1);
+                mbar_wait_b(raw_empty + 8 * s, ((kb >> lg_nr) & 1) ^ 1);
                 trace(p, 0, kb);
                 mbar_expect_tx(raw_full + 8 * s, RAW);
                 tma_load_2d(sR + s * RAW, &wmap, (kb * DQ::STEP16) & ~7, w_row0, raw_full + 8 * s);     // 16-byte aligned start
@@ -376,7 +378,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {                         // tensor-core issue: one thread, so every instruction between two MMAs counts
+        if (elect_one()) {                       // tensor-core issue: one thread, so every instruction between two MMAs counts
             const uint32_t idesc = umma_idesc(1, tn, 0);
             const uint32_t a0 = tmem_base + a_col0;
             const uint64_t bd0 = umma_desc_sw128(sB);
@@ -410,10 +412,10 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
         DQ q;
         auto block = [&](auto shift, int kb) {
             constexpr int S = decltype(shift)::value;
-            const int s = kb & 1;
+            const int s = kb & (nr - 1);
             const bool tr = lane == 0 && (dw & 3) == 0;
             if (tr) trace(p, 8 + 8 * h, kb);
-            mbar_wait_b(raw_full + 8 * s, (kb >> 1) & 1);
+            mbar_wait_b(raw_full + 8 * s, (kb >> lg_nr) & 1);
             if (tr) trace(p, 9 + 8 * h, kb);
             const uint32_t row = sR + s * RAW + r * DQ::PITCH;
             q.template prep<S>(row, h);
@@ -450,16 +452,29 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
         mbar_wait_b(tmem_full, 0);
         tc_fence_after();
         if (lane == 0 && dw == 0) trace(p, 6, 0);
+        // (addresses are stepped, not recomputed: with the row-table test inside the store loop every store paid a chain of
+        // constant loads and 64-bit multiplies, and the epilogue was a fifth of the kernel at K = 4096)
         const int n = n0 + r;
+        float * const dbase = p.dst; const int64_t ds = p.ds; const int64_t * const mrow = p.moe_row;
         for (int c0 = h * 32; c0 < tn; c0 += 64) {
             uint32_t v[32];
             tmem_ld32(lane_base + (uint32_t)c0, v);
             tmem_ld_wait();
-            if (n < p.N) {
+            const int mb = m0 + c0, cnt = m_end - mb;          // tokens of this column group that exist
+            if (n < p.N && cnt > 0) {
+                if (mrow) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int m = m0 + c0 + j;
-                    if (m < m_end) p.dst[(p.moe_row ? p.moe_row[m] : (int64_t)m * p.ds) + n] = __uint_as_float(v[j]);
+                    for (int j = 0; j < 32; ++j)
+                        if (j < cnt) dbase[mrow[mb + j] + n] = __uint_as_float(v[j]);
+                } else {
+                    float * d = dbase + (int64_t)mb * ds + n;
+                    if (cnt >= 32) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) { *d = __uint_as_float(v[j]); d += ds; }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) { if (j < cnt) *d = __uint_as_float(v[j]); d += ds; }
+                    }
                 }
             }
         }
@@ -549,7 +564,15 @@ static int raw_pitch(int type) {
                     case T_Q5_K: return pitch_of<T_Q5_K>(); case T_Q6_K: return pitch_of<T_Q6_K>(); }
     return 0;
 }
-static size_t mmq_smem(int type, int tn, int nb) { return 1024 + (size_t)nb * tn * 128 + 2 * 128 * (size_t)raw_pitch(type) + 512; }
+static size_t mmq_smem(int type, int tn, int nb, int nr) { return 1024 + (size_t)nb * tn * 128 + (size_t)nr * 128 * (size_t)raw_pitch(type) + 512; }
+// ring depths: a deeper raw-block ring (more weight bytes in flight per SM) is worth more than the last activation slots
+static void choose_rings(int type, mmq_params & p) {
+    static const int want_nr = env_int("B200_MMQ_NR", 4) >= 4 ? 4 : 2, min_nb = std::max(2, std::min(NB_MAX, env_int("B200_MMQ_MIN_NB", 3)));
+    p.nr = want_nr; p.nb = NB_MAX;
+    while (p.nb > min_nb && mmq_smem(type, p.tn, p.nb, p.nr) > 232448) --p.nb;
+    if (mmq_smem(type, p.tn, p.nb, p.nr) > 232448) { p.nr = 2; p.nb = NB_MAX; }
+    while (p.nb > 2 && mmq_smem(type, p.tn, p.nb, p.nr) > 232448) --p.nb;
+}
 
 // tokens per tile: fill the 148 SMs first, then prefer the wider tile (weights are dequantised once per tile)
 static int choose_tn(int N, int M) {
@@ -640,13 +663,12 @@ extern "C" int b200_mul_mat_q_bf16(int type, const void * W, int64_t nb1, const 
     p.dst = dst; p.ds = ds; p.N = N; p.M = M; p.K = K;
     p.tn = choose_tn(N, M);
     p.trace = g_mmq_trace;
-    p.nb = NB_MAX;
-    while (p.nb > 2 && mmq_smem(type, p.tn, p.nb) > 232448) --p.nb;
+    choose_rings(type, p);
     // tensor memory: accumulator columns + A ring; narrow tiles take half of it so that two CTAs can share an SM
     p.na = p.tn <= 128 ? 4 : NA_MAX;
     p.tmem_cols = p.tn <= 128 ? 256 : 512;
-    if (mmq_smem(type, p.tn, p.nb) > 232448) return -3;
-    const size_t smem = mmq_smem(type, p.tn, p.nb);
+    if (mmq_smem(type, p.tn, p.nb, p.nr) > 232448) return -3;
+    const size_t smem = mmq_smem(type, p.tn, p.nb, p.nr);
 
     CUtensorMap wmap, xmap;
     {   // weights as a [N][nb1/2] array of 16-bit words; box = one 256-K block (padded to the raw pitch) x 128 rows
@@ -720,12 +742,11 @@ extern "C" int b200_mul_mat_id_q(int type, const void * W, int64_t nb1, int n_ex
     p.tn = env_int("B200_MMQ_ID_TN", 0);
     if (p.tn != 32 && p.tn != 64 && p.tn != 128 && p.tn != 256) p.tn = avg <= 32 ? 32 : avg <= 64 ? 64 : avg <= 192 ? 128 : 256;
     p.trace = nullptr;
-    p.nb = NB_MAX;
-    while (p.nb > 2 && mmq_smem(type, p.tn, p.nb) > 232448) --p.nb;
+    choose_rings(type, p);
     p.na = p.tn <= 128 ? 4 : NA_MAX;
     p.tmem_cols = p.tn <= 128 ? 256 : 512;
-    if (mmq_smem(type, p.tn, p.nb) > 232448) return -3;
-    const size_t smem = mmq_smem(type, p.tn, p.nb);
+    if (mmq_smem(type, p.tn, p.nb, p.nr) > 232448) return -3;
+    const size_t smem = mmq_smem(type, p.tn, p.nb, p.nr);
     p.moe_cnt = cnt; p.moe_off = off; p.moe_row = row_off;
 
     CUtensorMap wmap, xmap;

@@ -137,10 +137,10 @@ def main():
         for name in names:
             for tn in ("256", "128"):
                 os.environ["B200_MMQ_TN"] = tn
-                trace(name, 14336, 4096, 512)
+                trace(name, int(os.environ.get("TRACE_N", "14336")), 4096, 512)
     else:
         for name in names:
-            for (N, K, M) in [(4096, 4096, 512), (14336, 4096, 512), (4096, 14336, 512), (4096, 4096, 128), (14336, 4096, 2048)]:
+            for (N, K, M) in [(1024, 4096, 512), (4096, 4096, 512), (14336, 4096, 512), (4096, 14336, 512), (4096, 4096, 128), (14336, 4096, 2048)]:
                 for tn in ("128", "256"):
                     os.environ["B200_MMQ_TN"] = tn
                     timing(name, N, K, M)
