@@ -281,8 +281,8 @@ template <> struct dq<T_Q8_0> {
 };
 
 // ------------------------------------------------------------------------------------------------
-// The kernel.  Step i = 4*kb + j covers the 64-K sub-chunk c = {0,2,1,3}[j] of block kb, so that the two
-// dequantiser groups (h = 0: sub-chunks 0,1; h = 1: sub-chunks 2,3) alternate: group = i & 1.
+// The kernel.  Step i = 4*kb + j covers the 64-K sub-chunk c = {0,2,1,3}[j] of block kb; dequantiser group g (four warps,
+// one per TMEM lane quarter) owns sub-chunk c = g of every block, i.e. step 4*kb + 2*(g & 1) + (g >> 1).
 // Tensor memory: columns [0, tn) hold the f32 accumulator, columns [a_col0, a_col0 + 32*na) the ring of
 // `na` A slots (128 lanes x 32 columns = 128 rows x 64 bf16 each).
 // ------------------------------------------------------------------------------------------------
@@ -308,7 +308,7 @@ __device__ __forceinline__ void trace(const mmq_params & p, int ev, int idx) {
 __device__ __forceinline__ void trace(const mmq_params &, int, int) {}
 #endif
 
-constexpr int MMQ_THREADS = 384;
+constexpr int MMQ_THREADS = 640;            // TMA x2, MMA issue, TMEM allocator warps + 16 dequantiser warps
 constexpr int NA_MAX = 8;
 constexpr int NB_MAX = 6;
 
@@ -340,7 +340,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
     const uint32_t a_col0 = (uint32_t)p.tmem_cols - 32u * (uint32_t)na;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 4; ++i) { mbar_init(raw_full + 8 * i, 1); mbar_init(raw_empty + 8 * i, 8); }
+        for (int i = 0; i < 4; ++i) { mbar_init(raw_full + 8 * i, 1); mbar_init(raw_empty + 8 * i, 16); }
         for (int i = 0; i < NA_MAX; ++i) { mbar_init(a_full + 8 * i, 4); mbar_init(a_empty + 8 * i, 1); }
         for (int i = 0; i < NB_MAX; ++i) { mbar_init(b_full + 8 * i, 1); mbar_init(b_empty + 8 * i, 1); }
         mbar_init(tmem_full, 1);
@@ -406,21 +406,24 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
             tc_commit(tmem_full);
         }
     } else if (warp >= 4) {
-        const int dw = warp - 4, h = dw >> 2, r = (dw & 3) * 32 + lane;
+        // sixteen dequantiser warps: warp quarter (dw & 3) = 32 weight rows = its TMEM lane quarter, group g = dw >> 2 = the 64-K
+        // sub-chunk (h = g >> 1, t = g & 1) it expands in every block.  (Eight warps doing two sub-chunks each left the kernel
+        // bound by their issue rate for tiles of <= 128 tokens: 1800 cycles per block against 1024 of tensor-pipe time.)
+        const int dw = warp - 4, g = dw >> 2, h = g >> 1, r = (dw & 3) * 32 + lane;
         const uint32_t lane_base = tmem_base + ((uint32_t)((dw & 3) * 32) << 16);      // this warp's TMEM lane quarter
         const int na_shift = na == 8 ? 3 : 2;
-        DQ q;
-        auto block = [&](auto shift, int kb) {
-            constexpr int S = decltype(shift)::value;
-            const int s = kb & (nr - 1);
-            const bool tr = lane == 0 && (dw & 3) == 0;
-            if (tr) trace(p, 8 + 8 * h, kb);
-            mbar_wait_b(raw_full + 8 * s, (kb >> lg_nr) & 1);
-            if (tr) trace(p, 9 + 8 * h, kb);
-            const uint32_t row = sR + s * RAW + r * DQ::PITCH;
-            q.template prep<S>(row, h);
-#pragma unroll
-            for (int t = 0; t < 2; ++t) {
+        auto run = [&](auto tc) {
+            constexpr int t = decltype(tc)::value;
+            DQ q;
+            auto block = [&](auto shift, int kb) {
+                constexpr int S = decltype(shift)::value;
+                const int s = kb & (nr - 1);
+                const bool tr = lane == 0 && (dw & 3) == 0;
+                if (tr && t == 0) trace(p, 8 + 8 * h, kb);
+                mbar_wait_b(raw_full + 8 * s, (kb >> lg_nr) & 1);
+                if (tr && t == 0) trace(p, 9 + 8 * h, kb);
+                const uint32_t row = sR + s * RAW + r * DQ::PITCH;
+                q.template prep<S>(row, h);
                 const int i = 4 * kb + 2 * t + h, slot = i & (na - 1);
                 uint32_t out[32];
                 q.emit(row, h, t, out);
@@ -433,22 +436,21 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
                 tc_fence_before();
                 if (tr) trace(p, 12 + 8 * h + 3 * t, kb);
                 __syncwarp();
-                if (lane == 0) mbar_arrive(a_full + 8 * slot);
+                if (lane == 0) { mbar_arrive(a_full + 8 * slot); mbar_arrive(raw_empty + 8 * s); }
+            };
+            if constexpr (DQ::SHIFTED) {         // block kb sits 2*(kb % 8) bytes into its raw row: unroll the period
+                for (int kb = 0; kb < nkb; kb += 8) {
+                    block(std::integral_constant<int, 0>{}, kb);      block(std::integral_constant<int, 2>{}, kb + 1);
+                    block(std::integral_constant<int, 4>{}, kb + 2);  block(std::integral_constant<int, 6>{}, kb + 3);
+                    block(std::integral_constant<int, 8>{}, kb + 4);  block(std::integral_constant<int, 10>{}, kb + 5);
+                    block(std::integral_constant<int, 12>{}, kb + 6); block(std::integral_constant<int, 14>{}, kb + 7);
+                }
+            } else {
+                for (int kb = 0; kb < nkb; ++kb) block(std::integral_constant<int, 0>{}, kb);
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(raw_empty + 8 * s);
         };
-        if constexpr (DQ::SHIFTED) {             // block kb sits 2*(kb % 8) bytes into its raw row: unroll the period
-            for (int kb = 0; kb < nkb; kb += 8) {
-                block(std::integral_constant<int, 0>{}, kb);      block(std::integral_constant<int, 2>{}, kb + 1);
-                block(std::integral_constant<int, 4>{}, kb + 2);  block(std::integral_constant<int, 6>{}, kb + 3);
-                block(std::integral_constant<int, 8>{}, kb + 4);  block(std::integral_constant<int, 10>{}, kb + 5);
-                block(std::integral_constant<int, 12>{}, kb + 6); block(std::integral_constant<int, 14>{}, kb + 7);
-            }
-        } else {
-            for (int kb = 0; kb < nkb; ++kb) block(std::integral_constant<int, 0>{}, kb);
-        }
-        // epilogue: TMEM lane = weight row (this warp's quarter), column = token; group h takes every other 32 columns
+        if (g & 1) run(std::integral_constant<int, 1>{}); else run(std::integral_constant<int, 0>{});
+        // epilogue: TMEM lane = weight row (this warp's quarter), column = token; group g takes every fourth 32 columns
         mbar_wait_b(tmem_full, 0);
         tc_fence_after();
         if (lane == 0 && dw == 0) trace(p, 6, 0);
@@ -456,7 +458,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
         // constant loads and 64-bit multiplies, and the epilogue was a fifth of the kernel at K = 4096)
         const int n = n0 + r;
         float * const dbase = p.dst; const int64_t ds = p.ds; const int64_t * const mrow = p.moe_row;
-        for (int c0 = h * 32; c0 < tn; c0 += 64) {
+        for (int c0 = g * 32; c0 < tn; c0 += 128) {
             uint32_t v[32];
             tmem_ld32(lane_base + (uint32_t)c0, v);
             tmem_ld_wait();
