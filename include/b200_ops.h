@@ -242,6 +242,11 @@ int64_t b200_acts_bf16_bytes(int K, int M);
 int b200_convert_acts_bf16(const float * X, int64_t xs, void * out, int K, int M, void * stream);
 int b200_mul_mat_q_bf16(int type, const void * W, int64_t nb1, const void * Xb, float * dst, int64_t ds,
                         int N, int K, int M, void * stream);
+/* Up to three weight matrices of one type, K and row stride times the same bf16 activations in ONE grid (q/k/v of a prefill
+ * batch: the k / v projections alone are 8 row tiles, a fraction of the SMs).  dst[g][m * ds[g] + n], N[g] rows each.
+ * No reference counterpart: ggml-cuda launches one mul_mat_q per MUL_MAT node (ggml-cuda.cu:1936-2005). */
+int b200_mul_mat_q_bf16_group(int type, int ng, const void * const * W, int64_t nb1, const void * Xb, float * const * dst,
+                              const int64_t * ds, const int * N, int K, int M, void * stream);
 /* debug hook: device buffer of (return value) int64 slots that CTA (0,0) of later b200_mul_mat_q launches fills with
  * clock64 stamps of its pipeline events (tools/mmq_debug.py trace); NULL switches it off. */
 int b200_mmq_debug_trace(void * dev_buf);

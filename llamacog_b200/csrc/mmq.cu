@@ -298,6 +298,9 @@ struct mmq_params {
     // MUL_MAT_ID (expert = blockIdx.z): activation rows sorted by expert; rows [off[e], off[e] + cnt[e]) belong to expert e,
     // row m of the sorted list goes to dst + row_off[m]; the weight map stacks the experts' matrices (N rows each)
     const int * moe_cnt; const int * moe_off; const int64_t * moe_row;
+    // grouped launch (matrices of one type and K that read the same activations, e.g. q/k/v): group g owns the row tiles
+    // [gy[g], gy[g+1]) of grid.y, its own tensor map (wmap / wmap1 / wmap2), destination and row count
+    int ngroup; int gy[4]; float * gdst[3]; int64_t gds[3]; int gN[3];
 };
 constexpr int TRACE_N = 512;
 #ifdef B200_MMQ_TRACE
@@ -314,7 +317,8 @@ constexpr int NB_MAX = 6;
 
 template <int TYPE>
 __global__ void __launch_bounds__(MMQ_THREADS, 1)
-mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUtensorMap xmap, const mmq_params p) {
+mmq_kernel(const __grid_constant__ CUtensorMap wmap0, const __grid_constant__ CUtensorMap xmap, const mmq_params p,
+           const __grid_constant__ CUtensorMap wmap1, const __grid_constant__ CUtensorMap wmap2) {
     using DQ = dq<TYPE>;
     constexpr int RAW = 128 * DQ::PITCH;
     extern __shared__ uint8_t smem_dyn[];
@@ -327,8 +331,16 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
                    b_full = a_empty + 8 * NA_MAX, b_empty = b_full + 8 * NB_MAX, tmem_full = b_empty + 8 * NB_MAX, tmem_slot = tmem_full + 8;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int m0 = blockIdx.x * tn, m_end = p.M, w_row0 = blockIdx.y * 128;
-    const int n0 = blockIdx.y * 128;
+    const CUtensorMap * wm = &wmap0;
+    float * dst_g = p.dst; int64_t ds_g = p.ds; int N_g = p.N; int by = blockIdx.y;
+    if (p.ngroup > 1) {
+        const int g = by >= p.gy[2] ? 2 : by >= p.gy[1] ? 1 : 0;
+        by -= p.gy[g];
+        wm = g == 0 ? &wmap0 : g == 1 ? &wmap1 : &wmap2;
+        dst_g = p.gdst[g]; ds_g = p.gds[g]; N_g = p.gN[g];
+    }
+    int m0 = blockIdx.x * tn, m_end = p.M, w_row0 = by * 128;
+    const int n0 = by * 128;
     if (p.moe_cnt) {                             // (launched without PDL: the routing tables are complete)
         const int cnt = p.moe_cnt[blockIdx.z];
         if (m0 >= cnt) return;                   // this expert has fewer tokens than the worst case the grid was sized for
@@ -345,7 +357,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
         for (int i = 0; i < NB_MAX; ++i) { mbar_init(b_full + 8 * i, 1); mbar_init(b_empty + 8 * i, 1); }
         mbar_init(tmem_full, 1);
         mbar_fence_init();
-        tma_prefetch_desc(&wmap); tma_prefetch_desc(&xmap);
+        tma_prefetch_desc(wm); tma_prefetch_desc(&xmap);
     }
     if (warp == 2) { tmem_alloc(tmem_slot, (uint32_t)p.tmem_cols); tmem_relinquish(); }
     tc_fence_before();
@@ -362,7 +374,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
                 mbar_wait_b(raw_empty + 8 * s, ((kb >> lg_nr) & 1) ^ 1);
                 trace(p, 0, kb);
                 mbar_expect_tx(raw_full + 8 * s, RAW);
-                tma_load_2d(sR + s * RAW, &wmap, (kb * DQ::STEP16) & ~7, w_row0, raw_full + 8 * s);     // 16-byte aligned start
+                tma_load_2d(sR + s * RAW, wm, (kb * DQ::STEP16) & ~7, w_row0, raw_full + 8 * s);     // 16-byte aligned start
             }
         }
     } else if (warp == 3) {
@@ -457,13 +469,13 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUt
         // (addresses are stepped, not recomputed: with the row-table test inside the store loop every store paid a chain of
         // constant loads and 64-bit multiplies, and the epilogue was a fifth of the kernel at K = 4096)
         const int n = n0 + r;
-        float * const dbase = p.dst; const int64_t ds = p.ds; const int64_t * const mrow = p.moe_row;
+        float * const dbase = dst_g; const int64_t ds = ds_g; const int64_t * const mrow = p.moe_row;
         for (int c0 = g * 32; c0 < tn; c0 += 128) {
             uint32_t v[32];
             tmem_ld32(lane_base + (uint32_t)c0, v);
             tmem_ld_wait();
             const int mb = m0 + c0, cnt = m_end - mb;          // tokens of this column group that exist
-            if (n < p.N && cnt > 0) {
+            if (n < N_g && cnt > 0) {
                 if (mrow) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
@@ -594,7 +606,8 @@ static int choose_tn(int N, int M) {
 }
 
 template <int TYPE>
-static int mmq_launch(const CUtensorMap & wmap, const CUtensorMap & xmap, const mmq_params & p, size_t smem, cudaStream_t st, int n_expert = 0) {
+static int mmq_launch(const CUtensorMap & wmap, const CUtensorMap & xmap, const mmq_params & p, size_t smem, cudaStream_t st, int n_expert = 0,
+                      const CUtensorMap * wmap1 = nullptr, const CUtensorMap * wmap2 = nullptr) {
     static size_t configured[16] = {0};  // per device
     int dev = 0;
     B200_CUDA_CHECK(cudaGetDevice(&dev));
@@ -603,12 +616,12 @@ static int mmq_launch(const CUtensorMap & wmap, const CUtensorMap & xmap, const 
         configured[dev & 15] = smem;
     }
     cudaLaunchConfig_t lc = {};
-    lc.gridDim = dim3((p.M + p.tn - 1) / p.tn, (p.N + 127) / 128, n_expert > 0 ? n_expert : 1); lc.blockDim = dim3(MMQ_THREADS); lc.dynamicSmemBytes = smem; lc.stream = st;
+    lc.gridDim = dim3((p.M + p.tn - 1) / p.tn, p.ngroup > 1 ? p.gy[p.ngroup] : (p.N + 127) / 128, n_expert > 0 ? n_expert : 1); lc.blockDim = dim3(MMQ_THREADS); lc.dynamicSmemBytes = smem; lc.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = at; lc.numAttrs = pdl_default() && n_expert == 0 ? 1 : 0;       // the expert tables are read before griddepcontrol.wait
-    B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, mmq_kernel<TYPE>, wmap, xmap, p));
+    B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, mmq_kernel<TYPE>, wmap, xmap, p, wmap1 ? *wmap1 : wmap, wmap2 ? *wmap2 : wmap));
     ++g_launches;
     return 0;
 }
@@ -695,6 +708,64 @@ extern "C" int b200_mul_mat_q_bf16(int type, const void * W, int64_t nb1, const 
         case T_Q4_K: return mmq_launch<T_Q4_K>(wmap, xmap, p, smem, st);
         case T_Q5_K: return mmq_launch<T_Q5_K>(wmap, xmap, p, smem, st);
         case T_Q6_K: return mmq_launch<T_Q6_K>(wmap, xmap, p, smem, st);
+    }
+    return -1;
+}
+
+// Up to three weight matrices of one type, K and row stride that read the same activations (q/k/v of a prefill batch) in one
+// grid: 8 + 8 + 32 row tiles fill the SMs where the k and v launches alone ran on 32 CTAs each.
+extern "C" int b200_mul_mat_q_bf16_group(int type, int ng, const void * const * W, int64_t nb1, const void * Xb, float * const * dst,
+                                         const int64_t * ds, const int * N, int K, int M, void * stream) {
+    if (ng < 1 || ng > 3 || !W || !dst || !ds || !N) return -1;
+    if (ng == 1) return b200_mul_mat_q_bf16(type, W[0], nb1, Xb, dst[0], ds[0], N[0], K, M, stream);
+    if (M <= 0 || ((uintptr_t)Xb & 127)) return -1;
+    int ntot = 0;
+    for (int g = 0; g < ng; ++g) {
+        if (!b200_mul_mat_q_supported(type, W[g], nb1, K) || N[g] <= 0 || !dst[g]) return -1;
+        ntot += (N[g] + 127) / 128 * 128;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    mmq_params p = {};
+    p.dst = dst[0]; p.ds = ds[0]; p.N = N[0]; p.M = M; p.K = K;
+    p.tn = choose_tn(ntot, M);
+    p.trace = nullptr;
+    choose_rings(type, p);
+    p.na = p.tn <= 128 ? 4 : NA_MAX;
+    p.tmem_cols = p.tn <= 128 ? 256 : 512;
+    if (mmq_smem(type, p.tn, p.nb, p.nr) > 232448) return -3;
+    const size_t smem = mmq_smem(type, p.tn, p.nb, p.nr);
+    p.ngroup = ng;
+    CUtensorMap wmap[3], xmap;
+    int y = 0;
+    for (int g = 0; g < 3; ++g) {
+        p.gy[g] = y;
+        if (g >= ng) continue;
+        p.gdst[g] = dst[g]; p.gds[g] = ds[g]; p.gN[g] = N[g];
+        y += (N[g] + 127) / 128;
+        const cuuint64_t dims[2] = {(cuuint64_t)((int64_t)(K / block_elems(type)) * block_bytes(type) / 2), (cuuint64_t)N[g]};
+        const cuuint64_t strides[1] = {(cuuint64_t)nb1};
+        const cuuint32_t box[2] = {(cuuint32_t)(raw_pitch(type) / 2), 128};
+        const cuuint32_t es[2] = {1, 1};
+        if (encode_tiled()(&wmap[g], CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void *>(W[g]), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return -4;
+    }
+    p.gy[3] = y;
+    for (int g = ng; g < 3; ++g) p.gy[g] = y;
+    {
+        const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)M};
+        const cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+        const cuuint32_t box[2] = {64, (cuuint32_t)p.tn};
+        const cuuint32_t es[2] = {1, 1};
+        if (encode_tiled()(&xmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(Xb), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return -5;
+    }
+    const CUtensorMap * w1 = &wmap[1], * w2 = ng > 2 ? &wmap[2] : &wmap[1];
+    switch (type) {
+        case T_Q4_0: return mmq_launch<T_Q4_0>(wmap[0], xmap, p, smem, st, 0, w1, w2);
+        case T_Q8_0: return mmq_launch<T_Q8_0>(wmap[0], xmap, p, smem, st, 0, w1, w2);
+        case T_Q4_K: return mmq_launch<T_Q4_K>(wmap[0], xmap, p, smem, st, 0, w1, w2);
+        case T_Q5_K: return mmq_launch<T_Q5_K>(wmap[0], xmap, p, smem, st, 0, w1, w2);
+        case T_Q6_K: return mmq_launch<T_Q6_K>(wmap[0], xmap, p, smem, st, 0, w1, w2);
     }
     return -1;
 }

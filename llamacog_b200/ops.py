@@ -59,7 +59,7 @@ EXPORTS = ["b200_flash_attn_xq_supported", "b200_op_flash_attn_ext_xq", "b200_mu
            "b200_flash_attn_scratch_bytes", "b200_flash_attn_supported", "b200_op_mul_mat", "b200_mul_mat_scratch_bytes",
            "b200_mul_mat_supported", "b200_op_mul_mat_id", "b200_mul_mat_q", "b200_mul_mat_q_scratch_bytes",
            "b200_mul_mat_q_supported", "b200_mmq_debug_trace", "b200_acts_bf16_bytes",
-           "b200_convert_acts_bf16", "b200_mul_mat_q_bf16", "b200_op_add_rms_norm_mul", "b200_op_unary_mul", "b200_op_rope_cpy_batch", "b200_op_rope_cpy_batch_check",
+           "b200_convert_acts_bf16", "b200_mul_mat_q_bf16", "b200_mul_mat_q_bf16_group", "b200_op_add_rms_norm_mul", "b200_op_unary_mul", "b200_op_rope_cpy_batch", "b200_op_rope_cpy_batch_check",
            "b200_ktrace_enable", "b200_ktrace_dump", "b200_mmvq_fusable"]
 
 
@@ -135,6 +135,23 @@ def mul_mat_q(t, W, X, N, K, nb1=None):
                                 C.c_void_p(dst.data_ptr()), C.c_int64(N), C.c_int(N), C.c_int(K), C.c_int(M),
                                 C.c_void_p(scratch.data_ptr()), C.c_int64(need), _stream()), "b200_mul_mat_q")
     return dst
+
+
+def mul_mat_q_group(t, Ws, Ns, X, K):
+    """Several weight matrices of one type times the same activations in one tensor-core grid (b200_mul_mat_q_bf16_group)."""
+    M = X.shape[0]
+    nb1 = row_bytes(t, K)
+    xb = torch.empty(lib().b200_acts_bf16_bytes(C.c_int(K), C.c_int(M)) + 128, dtype=torch.uint8, device=X.device)
+    xp = (xb.data_ptr() + 127) & ~127
+    _check(lib().b200_convert_acts_bf16(C.c_void_p(X.data_ptr()), C.c_int64(X.stride(0)), C.c_void_p(xp), C.c_int(K), C.c_int(M), _stream()),
+           "b200_convert_acts_bf16")
+    ng = len(Ws)
+    outs = [torch.empty((M, n), dtype=torch.float32, device=X.device) for n in Ns]
+    Wp = (C.c_void_p * ng)(*[w.data_ptr() for w in Ws]); Dp = (C.c_void_p * ng)(*[o.data_ptr() for o in outs])
+    Np = (C.c_int * ng)(*Ns); dsp = (C.c_int64 * ng)(*Ns)
+    _check(lib().b200_mul_mat_q_bf16_group(C.c_int(t), C.c_int(ng), Wp, C.c_int64(nb1), C.c_void_p(xp), Dp, dsp, Np, C.c_int(K), C.c_int(M),
+                                           _stream()), "b200_mul_mat_q_bf16_group")
+    return outs
 
 
 def mul_mat_id(t, W, X, ids, N, K, n_expert):

@@ -115,3 +115,21 @@ def test_unsupported_shapes_are_refused():
         ops.mul_mat_q(O.QUANT_TYPES["q4_0"], W, X, 4, 128)              # K % 256 != 0
     with pytest.raises(RuntimeError):
         ops.mul_mat_q(O.QUANT_TYPES["q6_K"], W, torch.zeros(16, 256, device="cuda"), 4, 256)      # 210-byte row stride
+
+
+@pytest.mark.parametrize("name", ["q4_K", "q6_K", "q8_0"])
+@pytest.mark.parametrize("Ns,M", [((4096, 1024, 1024), 512), ((512, 200), 77), ((1024, 1024, 384), 300)])
+def test_group_launch_equals_single_launches(name, Ns, M):
+    """q/k/v of a prefill batch in one grid (b200_mul_mat_q_bf16_group): each matrix's result must equal, bit for bit, its own
+    launch (same K-order of the f32 accumulation whatever the token tile), ragged last row tiles included."""
+    ops = _ops()
+    t = O.QUANT_TYPES[name]
+    K = 2048
+    rng = np.random.default_rng(len(Ns) * 1000 + M)
+    Ws = [_dev(O.random_quant_bytes(t, n, K, rng)) for n in Ns]
+    torch.manual_seed(M)
+    X = torch.randn(M, K, device="cuda")
+    got = ops.mul_mat_q_group(t, Ws, list(Ns), X, K)
+    for g, n in enumerate(Ns):
+        want = ops.mul_mat_q(t, Ws[g], X, n, K)
+        assert torch.equal(got[g], want), "matrix %d of the group differs" % g
