@@ -215,6 +215,12 @@ int b200_flash_attn_xq_supported(const b200_tensor * q, const b200_tensor * k);
 int b200_op_flash_attn_ext_xq(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
                               const b200_tensor * dst, float scale, float max_bias, float logit_softcap,
                               void * scratch, int64_t scratch_bytes, void * xq, void * stream);
+/* prefill: same, and the result also as the bf16 activation rows [rows][D * n_head] of the MMQ that consumes it (the output
+ * projection): saves the activation conversion launch.  -1 when the tensor-core kernel does not take the shape. */
+int b200_flash_attn_xb_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * dst);
+int b200_op_flash_attn_ext_xb(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
+                              const b200_tensor * dst, float scale, float max_bias, float logit_softcap,
+                              void * scratch, int64_t scratch_bytes, void * xb, void * stream);
 int64_t b200_flash_attn_scratch_bytes(const b200_tensor * q, const b200_tensor * k);
 int b200_flash_attn_supported(int k_type, int v_type, int64_t dk, int64_t dv);
 /* MUL_MAT: dst[N, M, b2, b3] = src0[K, N, a2, a3] x src1[K, M, b2, b3], src0 broadcast over dims 2,3.

@@ -696,11 +696,11 @@ static int fa_gqa_min_kv() { static const int v = [] { const char * e = getenv("
 
 // tensor-core kernel for batches of query rows (fattn_tc.cu); returns 0 when the shape is not its to take
 int fattn_tc_try(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst,
-                 float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc);
+                 float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc, void * xb = nullptr);
 int64_t fattn_tc_flag_bytes(const b200_tensor * q, const b200_tensor * k);
 int64_t fattn_tc_q8_scratch(const b200_tensor * q, const b200_tensor * k);
 int fattn_tc_try_q8(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst,
-                    float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc);
+                    float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc, void * xb = nullptr);
 
 }  // namespace b200
 
@@ -730,6 +730,27 @@ extern "C" int b200_op_flash_attn_ext(const b200_tensor * q, const b200_tensor *
 
 extern "C" int b200_flash_attn_xq_supported(const b200_tensor * q, const b200_tensor * k) {
     return q->ne[0] == 128 && q->ne[3] == 1 && q->ne[1] >= 1 && q->ne[1] <= 8 && (k->type == T_F16 || k->type == T_Q8_0);
+}
+
+// Prefill: the tensor-core kernel also stores its result as the bf16 activation rows of the output projection's MMQ (xb:
+// b200_acts_bf16_bytes(D * n_head, rows), 128-byte aligned).  -1 when the tensor-core kernel does not take the shape.
+extern "C" int b200_flash_attn_xb_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * dst) {
+    if (q->ne[3] != 1 || (q->ne[0] != 64 && q->ne[0] != 128) || (k->type != T_F16 && k->type != T_Q8_0)) return 0;
+    if (dst->nb[1] != q->ne[0] * 4 || dst->nb[2] != dst->nb[1] * q->ne[2]) return 0;       // [D, n_head, rows] contiguous
+    return fattn_tc_flag_bytes(q, k) > 0;
+}
+extern "C" int b200_op_flash_attn_ext_xb(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,
+                                         const b200_tensor * dst, float scale, float max_bias, float logit_softcap,
+                                         void * scratch, int64_t scratch_bytes, void * xb, void * stream) {
+    if (!xb || ((uintptr_t)xb & 15) || !b200_flash_attn_xb_supported(q, k, dst)) return -1;
+    if (!b200_flash_attn_supported(k->type, v->type, k->ne[0], v->ne[0]) || q->type != T_F32 || dst->type != T_F32) return -1;
+    if (q->ne[0] != k->ne[0] || q->nb[0] != 4 || dst->nb[0] != 4 || k->ne[1] != v->ne[1]) return -1;
+    if (mask && (mask->type != T_F16 || mask->nb[0] != 2 || mask->ne[0] < k->ne[1])) return -1;
+    if (q->ne[1] == 0 || k->ne[1] == 0) return -1;
+    int rc = 0;
+    if (fattn_tc_try(q, k, v, mask, dst, scale, max_bias, logit_softcap, scratch, scratch_bytes, (cudaStream_t)stream, &rc, xb)) return rc;
+    if (k->type == T_Q8_0 && fattn_tc_try_q8(q, k, v, mask, dst, scale, max_bias, logit_softcap, scratch, scratch_bytes, (cudaStream_t)stream, &rc, xb)) return rc;
+    return -1;
 }
 
 extern "C" int b200_op_flash_attn_ext_xq(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask,

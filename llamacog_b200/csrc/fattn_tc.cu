@@ -28,6 +28,7 @@ struct fat_params {
     float scale, softcap, max_bias, m0, m1;
     unsigned n_head_log2;
     const uint8_t * flags;       // [q tiles][kv tiles] from mask_classify_kernel: 0 nothing to attend, 1 mixed, 2 mask is all zero
+    uint32_t * xb;               // optional: the result also as bf16 rows [token][n_head * D] (the activations of the output projection's MMQ)
 };
 
 // ---- one pass over the mask for all heads: which 128 x 128 tiles are empty, which need no mask at all ----
@@ -331,6 +332,12 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
                     o.x = nact > 0 ? __uint_as_float(v[i]) * inv : 0.0f; o.y = nact > 0 ? __uint_as_float(v[i + 1]) * inv : 0.0f;
                     o.z = nact > 0 ? __uint_as_float(v[i + 2]) * inv : 0.0f; o.w = nact > 0 ? __uint_as_float(v[i + 3]) * inv : 0.0f;
                     *reinterpret_cast<float4 *>(out + 32 * c + i) = o;
+                    if (p.xb) {                  // same values, rounded as x_to_bf16_kernel rounds them
+                        uint2 w;                 // cvt.rn.bf16x2.f32 {hi, lo}, as pack_bf16 of mmq.cu
+                        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w.x) : "f"(o.y), "f"(o.x));
+                        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w.y) : "f"(o.w), "f"(o.z));
+                        *reinterpret_cast<uint2 *>(p.xb + ((((int64_t)iq3 * p.N + qi) * p.n_head + iq2) * D + 32 * c + i) / 2) = w;
+                    }
                 }
             }
         }
@@ -371,7 +378,7 @@ int64_t fattn_tc_flag_bytes(const b200_tensor * q, const b200_tensor * k) {
     return ((((q->ne[1] + 127) / 128) * ((k->ne[1] + 127) / 128) + 255) & ~(int64_t)255) + 256;
 }
 int fattn_tc_try(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst,
-                 float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc) {
+                 float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc, void * xb) {
     *rc = 0;
     const int D = (int)q->ne[0];
     if (k->type != T_F16 || v->type != T_F16 || (D != 64 && D != 128) || v->ne[0] != D) return 0;
@@ -391,6 +398,7 @@ int fattn_tc_try(const b200_tensor * q, const b200_tensor * k, const b200_tensor
     }
     fat_params p = {};
     p.q = (const char *)q->data; p.mask = mask ? (const char *)mask->data : nullptr; p.dst = (char *)dst->data;
+    p.xb = (uint32_t *)xb;
     p.nbq1 = q->nb[1]; p.nbq2 = q->nb[2]; p.nbq3 = q->nb[3]; p.nbm1 = mask ? mask->nb[1] : 0; p.nbd1 = dst->nb[1];
     p.N = (int)q->ne[1]; p.n_head = (int)q->ne[2]; p.n_kv = (int)k->ne[1];
     p.rk2 = (int)(q->ne[2] / k->ne[2]); p.rk3 = (int)(q->ne[3] / k->ne[3]);
@@ -450,7 +458,7 @@ int64_t fattn_tc_q8_scratch(const b200_tensor * q, const b200_tensor * k) {
 
 // q8_0 K and V: dequantise into scratch, then the f16 kernel.  Returns 1 when it ran (rc = its status).
 int fattn_tc_try_q8(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst,
-                    float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc) {
+                    float scale, float max_bias, float logit_softcap, void * scratch, int64_t scratch_bytes, cudaStream_t st, int * rc, void * xb) {
     *rc = 0;
     const int64_t need = fattn_tc_q8_scratch(q, k);
     if (need == 0 || v->type != T_Q8_0 || !scratch || scratch_bytes < need || v->ne[0] != k->ne[0] || v->ne[1] != k->ne[1] || v->ne[2] != k->ne[2] || v->ne[3] != k->ne[3]) return 0;
@@ -474,7 +482,7 @@ int fattn_tc_try_q8(const b200_tensor * q, const b200_tensor * k, const b200_ten
         f.ne[0] = D; f.ne[1] = n_kv; f.ne[2] = t->ne[2]; f.ne[3] = t->ne[3];
         f.nb[0] = 2; f.nb[1] = 2 * D; f.nb[2] = f.nb[1] * n_kv; f.nb[3] = f.nb[2] * t->ne[2];
     }
-    return fattn_tc_try(q, &kv[0], &kv[1], mask, dst, scale, max_bias, logit_softcap, scratch, fattn_tc_flag_bytes(q, k), st, rc);
+    return fattn_tc_try(q, &kv[0], &kv[1], mask, dst, scale, max_bias, logit_softcap, scratch, fattn_tc_flag_bytes(q, k), st, rc, xb);
 }
 
 }  // namespace b200

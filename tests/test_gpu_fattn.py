@@ -111,3 +111,36 @@ def test_q8_0_kv_cache(D, N, n_kv, n_past):
     out = _ops().flash_attn_ext(q, k8, v8, mask, scale)
     ref = _ref(q, kd, vd, mask, scale)
     assert _nmse(out, ref) < 5e-4, _nmse(out, ref)
+
+
+@pytest.mark.parametrize("D,N,n_kv,n_past", [(128, 512, 512, 0), (64, 200, 200, 0), (128, 130, 700, 570), (128, 35, 1024, 100)])
+def test_prefill_bf16_rows_for_the_output_projection(D, N, n_kv, n_past):
+    """b200_op_flash_attn_ext_xb: the tensor-core kernel also stores its result as the bf16 activation rows of the MMQ that reads
+    it; dst must equal the plain call bit for bit and the rows must be the round-to-nearest bf16 of dst (what
+    b200_convert_acts_bf16 would have produced)."""
+    import ctypes as C
+    ops = _ops(); L = ops.lib()
+    torch.manual_seed(N + n_kv + D)
+    n_head, n_head_kv = 8, 2
+    q = torch.randn(1, n_head, N, D, device="cuda")
+    k = torch.randn(1, n_head_kv, n_kv, D, device="cuda").half()
+    v = torch.randn(1, n_head_kv, n_kv, D, device="cuda").half()
+    mask = _causal_mask(N, n_kv, n_past)
+    scale = 1.0 / math.sqrt(D)
+    want = ops.flash_attn_ext(q, k, v, mask, scale)
+    dst = torch.zeros_like(want)
+    xb = torch.zeros(N, n_head * D, dtype=torch.bfloat16, device="cuda")
+    tq, tk, tv, tm, td = ops.as_b200(q), ops.as_b200(k), ops.as_b200(v), ops.as_b200(mask), ops.as_b200(dst)
+    assert L.b200_flash_attn_xb_supported(C.byref(tq), C.byref(tk), C.byref(td)) == 1
+    need = L.b200_flash_attn_scratch_bytes(C.byref(tq), C.byref(tk))
+    scratch = torch.empty(max(int(need), 16), dtype=torch.uint8, device="cuda")
+    rc = L.b200_op_flash_attn_ext_xb(C.byref(tq), C.byref(tk), C.byref(tv), C.byref(tm), C.byref(td), C.c_float(scale), C.c_float(0.0), C.c_float(0.0),
+                                     C.c_void_p(scratch.data_ptr()), C.c_int64(scratch.numel()), C.c_void_p(xb.data_ptr()),
+                                     C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert torch.equal(dst, want)
+    assert torch.equal(xb.view(torch.int16), dst.view(N, n_head * D).to(torch.bfloat16).view(torch.int16))
+    # decode shapes are not this entry point's
+    q1 = torch.randn(1, n_head, 1, D, device="cuda"); d1 = torch.zeros(1, 1, n_head, D, device="cuda")
+    assert L.b200_flash_attn_xb_supported(C.byref(ops.as_b200(q1)), C.byref(tk), C.byref(ops.as_b200(d1))) == 0
