@@ -348,9 +348,9 @@ def main():
         if not args.no_roofline and world == 1:
             # the prefill side of the headline metric: pp512 through the same unmodified llama-bench, and the MMQ tensor-pipe fraction
             try:
-                resp, _ = llama_bench(model, ["-ngl", "99", "-fa", "1", "-p", "512", "-n", "0", "-r", "5"], plugin=True, device=device)
+                resp, _ = llama_bench(model, ["-ngl", "99", "-fa", "1", "-p", "512", "-n", "0", "-r", "9"], plugin=True, device=device)
                 samples = sorted(float(x) for x in resp[-1].get("samples_ts", [])) or [float(resp[-1]["avg_ts"])]
-                pre = {"pp512_tokens_per_s": samples[len(samples) // 2],      # median of 5 passes: a fresh box occasionally stalls one pass
+                pre = {"pp512_tokens_per_s": samples[len(samples) // 2],      # median of 9 passes (12 ms each): the first passes of a process run 6 % below the rest, a fresh box occasionally stalls one
                        "pp512_samples": samples,
                        "workload": "llama3-8b-q4_k_m pp512, llama-bench -ngl 99 -fa 1 (MMQ tcgen05 + tensor-core flash attention)"}
                 m = mmq_roofline(20, args.warmup, local)

@@ -103,11 +103,27 @@ __device__ __forceinline__ uint64_t policy_evict_first() {
 constexpr unsigned long long KTRACE_CAP = 1ull << 20;   // events
 #ifndef B200_KTRACE
 __device__ __forceinline__ void ktrace_event(int, int = 0) {}
+__device__ __forceinline__ void ktrace_event_at(int, int, int) {}
 #else
 static __constant__ unsigned long long * c_ktrace;      // one copy per translation unit, all set by b200_ktrace_enable
 __device__ __forceinline__ void ktrace_event(int ev, int thread = 0) {     // recorded by `thread` of block 0
     unsigned long long * t = c_ktrace;
     if (t != nullptr && ((threadIdx.x ^ thread) | blockIdx.x | blockIdx.y | blockIdx.z) == 0) {
+        unsigned long long now, gid;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        asm volatile("mov.u64 %0, %%gridid;" : "=l"(gid));
+        const unsigned long long slot = atomicAdd(t, 1ull);
+        if (slot < KTRACE_CAP) {
+            t[1 + 2 * slot] = now;
+            t[2 + 2 * slot] = (gid << 32) | ((unsigned long long)(gridDim.x * gridDim.y * gridDim.z & 0x1FFFF) << 15) |
+                              ((unsigned long long)(blockDim.x & 0x7FF) << 4) | (unsigned long long)(ev & 15);
+        }
+    }
+}
+// same, recorded by `thread` of block (bx, 0, 0): phase marks of a CTA other than the first (the longest one of a causal attention grid)
+__device__ __forceinline__ void ktrace_event_at(int ev, int thread, int bx) {
+    unsigned long long * t = c_ktrace;
+    if (t != nullptr && ((threadIdx.x ^ thread) | (blockIdx.x ^ bx) | blockIdx.y | blockIdx.z) == 0) {
         unsigned long long now, gid;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
         asm volatile("mov.u64 %0, %%gridid;" : "=l"(gid));

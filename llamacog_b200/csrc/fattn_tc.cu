@@ -139,6 +139,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
             sts128(sQ + (u >> 3) * ATOM + row * 128 + (((u & 7) ^ (row & 7)) << 4), w[0], w[1], w[2], w[3]);
         }
         fence_proxy_async();
+        ktrace_event_at(2, 64, gridDim.x - 1);
         // ---- which KV tiles have anything to attend to? ----
         if (p.mask && p.flags) {
             for (int j = threadIdx.x - 64; j < nt; j += FAT_THREADS - 64) act[j] = p.flags[(int64_t)blockIdx.x * nt + j];
@@ -170,6 +171,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
     }
     __syncthreads();
     const int nact = *nact_p;
+    ktrace_event_at(3, 64, gridDim.x - 1);
 
     if (warp == 0) {
         if (lane == 0) {                         // TMA producer: K and V tiles of the active KV tiles, two stages each
@@ -228,8 +230,18 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
         for (int jj = 0; jj < nact; ++jj) {
             const int j = tiles[jj] & 0x7FFF, st = jj & 1;
             const bool nomask = (tiles[jj] & 0x8000) != 0;
+            // a tile that needs its mask: the 16 loads of this thread's mask row go out before the wait for S (they do not depend on it);
+            // issued one per use inside the loop below they were 16 memory round trips in series, 5 us of a 17 us CTA
+            const int lim = p.n_kv - 128 * j;
+            const bool mvec = !nomask && mrow && p.mask_vec && lim >= 128;
+            uint4 mreg[16];
+            if (mvec) {
+#pragma unroll
+                for (int g = 0; g < 16; ++g) mreg[g] = __ldg(reinterpret_cast<const uint4 *>(mrow + 128 * j) + g);
+            }
             mbar_wait_b(s_full + 8 * st, (jj >> 1) & 1);
             tc_fence_after();
+            ktrace_event_at(4, 64, gridDim.x - 1);
             float s[128];
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
@@ -242,8 +254,8 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(s_empty + 8 * st);
+            ktrace_event_at(5, 64, gridDim.x - 1);
             // scale, softcap, mask (all in the log2 domain), positions past n_kv and rows past N are -inf
-            const int lim = p.n_kv - 128 * j;
             float rmax = -INFINITY;
             if (nomask) {                        // a whole tile, every row attends to every position: scale (and softcap) only
 #pragma unroll
@@ -258,8 +270,8 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
 #pragma unroll
             for (int g = 0; g < 16; ++g) {
                 float mv[8];
-                if (mrow && p.mask_vec && lim >= 128) {
-                    const uint4 u = __ldg(reinterpret_cast<const uint4 *>(mrow + 128 * j) + g);
+                if (mvec) {
+                    const uint4 u = mreg[g];
                     const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
                     const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&u.z)), d = __half22float2(*reinterpret_cast<const __half2 *>(&u.w));
                     mv[0] = a.x; mv[1] = a.y; mv[2] = b.x; mv[3] = b.y; mv[4] = c.x; mv[5] = c.y; mv[6] = d.x; mv[7] = d.y;
@@ -294,7 +306,9 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
             }
             l = l * alpha + sum;
             m = mn;
+            ktrace_event_at(6, 64, gridDim.x - 1);
             if (jj > 0) { mbar_wait_b(o_done, (jj - 1) & 1); tc_fence_after(); }       // previous P V finished: P is free, O is complete
+            ktrace_event_at(7, 64, gridDim.x - 1);
             {
                 uint32_t (&lo)[32] = *reinterpret_cast<uint32_t (*)[32]>(&pk[0]);
                 uint32_t (&hi)[32] = *reinterpret_cast<uint32_t (*)[32]>(&pk[32]);
@@ -316,10 +330,12 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(p_full);
+            ktrace_event_at(8, 64, gridDim.x - 1);
         }
         // ---- epilogue: O / l -> dst[(iq3*N + q)*n_head + head][D] ----
         float * out = reinterpret_cast<float *>(p.dst + (((int64_t)iq3 * p.N + qi) * p.n_head + iq2) * p.nbd1);
         if (nact > 0) { mbar_wait_b(o_done, (nact - 1) & 1); tc_fence_after(); }
+        ktrace_event_at(9, 64, gridDim.x - 1);
         const float inv = l > 0.0f ? 1.0f / l : 0.0f;
 #pragma unroll
         for (int c = 0; c < D / 32; ++c) {
@@ -342,6 +358,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant_
             }
         }
     }
+    ktrace_event_at(10, 64, gridDim.x - 1);
     tc_fence_before();
     __syncthreads();
     if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, 512); }
