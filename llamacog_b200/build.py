@@ -38,6 +38,20 @@ def _newer(src_files, target):
     return any(os.path.getmtime(s) > t for s in src_files)
 
 
+def _flags_changed():
+    """Objects are reused by mtime; a different flag set (B200_KTRACE / B200_MMQ_TRACE debug builds) must rebuild all of them."""
+    stamp = os.path.join(OBJ, "nvcc_flags.txt")
+    want = " ".join(NVCC_FLAGS)
+    have = open(stamp).read() if os.path.exists(stamp) else None
+    if have == want:
+        return False
+    os.makedirs(OBJ, exist_ok=True)
+    for o in glob.glob(os.path.join(OBJ, "*.o")):
+        os.remove(o)
+    open(stamp, "w").write(want)
+    return True
+
+
 def _compile(src, extra=()):
     obj = os.path.join(OBJ, os.path.basename(src) + ".o")
     deps = glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(CSRC, "backend", "*.h")) + glob.glob(os.path.join(CSRC, "backend", "*.inc")) + \
@@ -54,6 +68,7 @@ def _compile(src, extra=()):
 
 def build_ops(verbose=False):
     os.makedirs(OBJ, exist_ok=True)
+    _flags_changed()
     srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
     extra = ["-Xptxas", "-v"] if verbose else []
     with cf.ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:
