@@ -310,7 +310,8 @@ __global__ void __launch_bounds__(256) cpy_blocks_kernel(const tens src, const t
 
 // ---- several rope / KV-store nodes of a decode step in one launch (blockIdx.y = task) ----
 // kind 0: dst = rope(src);  kind 1: dst = rope(src) and dst2 = convert(dst) in cpy's flat element order;  kind 2: dst2 = convert(src)
-struct ew_task { int kind, d2type; tens src, dst, dst2; const int32_t * pos; const float * ff; rope_dev rp; char * const * dslot; int64_t n; };
+struct ew_task { int kind, d2type; tens src, dst, dst2; const int32_t * pos; const float * ff; rope_dev rp; char * const * dslot; int64_t n;
+                 int vec4, ngrp; int64_t nwide; };      // prefill form: 4-wide copy possible, head groups per (token, pair), threads needed
 struct ew_batch { ew_task t[4]; };
 __device__ __forceinline__ void store_conv(char * base, const tens & d2, int d2type, int64_t flat, float v) {
     char * p = base + flat_off(d2, flat);
@@ -346,6 +347,65 @@ __global__ void __launch_bounds__(256) ew_batch_kernel(const __grid_constant__ e
         }
         d[ia] = ya; d[ib] = yb;
         if (t.kind == 1) { store_conv(d2, t.dst2, t.d2type, row0 + ia, ya); store_conv(d2, t.dst2, t.d2type, row0 + ib, yb); }
+    }
+}
+
+// The same tasks for a prefill batch (thousands of tokens): rope walks ROPE_HPT heads per thread (rope_heads_kernel's mapping: cos/sin
+// once per head group), the plain store moves four elements per thread (cpy_vec4_kernel's) -- one launch for rope(q), rope(k) -> K
+// cache and v -> V cache instead of four.  Same arithmetic and roundings as the kernels it stands for.
+__global__ void __launch_bounds__(256) ew_batch_wide_kernel(const __grid_constant__ ew_batch b) {
+    pdl_enter();
+    const ew_task & t = b.t[blockIdx.y];
+    char * d2 = t.kind ? (t.dslot ? *t.dslot : t.dst2.d) : nullptr;
+    if (t.kind == 2) {
+        if (t.vec4) {
+            for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < t.nwide; i += (int64_t)gridDim.x * blockDim.x) {
+                const float4 v = *(const float4 *)(t.src.d + flat_off(t.src, 4 * i));
+                char * o = d2 + flat_off(t.dst2, 4 * i);
+                if (t.d2type == T_F16) { __half2 a = __floats2half2_rn(v.x, v.y), c = __floats2half2_rn(v.z, v.w); uint2 w; w.x = *(uint32_t *)&a; w.y = *(uint32_t *)&c; *(uint2 *)o = w; }
+                else if (t.d2type == T_BF16) { __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), c = __floats2bfloat162_rn(v.z, v.w); uint2 w; w.x = *(uint32_t *)&a; w.y = *(uint32_t *)&c; *(uint2 *)o = w; }
+                else *(float4 *)o = v;
+            }
+        } else {
+            for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < t.n; i += (int64_t)gridDim.x * blockDim.x)
+                store_conv(d2, t.dst2, t.d2type, i, *(const float *)(t.src.d + flat_off(t.src, i)));
+        }
+        return;
+    }
+    const tens & src = t.src; const tens & dst = t.dst; const rope_dev & p = t.rp;
+    const int64_t half0 = src.ne[0] / 2;
+    const int nh = (int)src.ne[1], ngrp = t.ngrp;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < t.nwide; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t ip = i % half0, r = i / half0;
+        const int h0 = (int)(r % ngrp) * ROPE_HPT;
+        const int64_t r2 = r / ngrp, i2 = r2 % src.ne[2], i3 = r2 / src.ne[2];
+        const char * sb = src.d + i2 * src.nb[2] + i3 * src.nb[3] + h0 * src.nb[1];
+        char * db = dst.d + i2 * dst.nb[2] + i3 * dst.nb[3] + h0 * dst.nb[1];
+        const int64_t row0 = ((i3 * src.ne[2] + i2) * nh + h0) * src.ne[0];      // flat index of head h0's first element (cpy order)
+        const int64_t i0 = 2 * ip;
+        const bool tail = i0 >= p.n_dims;
+        const int64_t ia = tail ? i0 : (p.neox ? ip : i0), ib = tail ? i0 + 1 : (p.neox ? ip + p.n_dims / 2 : i0 + 1);
+        float x0[ROPE_HPT], x1[ROPE_HPT];
+#pragma unroll
+        for (int h = 0; h < ROPE_HPT; ++h)
+            if (h0 + h < nh) {
+                const float * sh = (const float *)(sb + h * src.nb[1]);
+                x0[h] = sh[ia]; x1[h] = sh[ib];
+            }
+        float c = 1.0f, sn = 0.0f;
+        if (!tail) rope_cs(p, ip, t.pos[i2], t.ff, c, sn);
+#pragma unroll
+        for (int h = 0; h < ROPE_HPT; ++h)
+            if (h0 + h < nh) {
+                float * dh = (float *)(db + h * dst.nb[1]);
+                float ya = x0[h], yb = x1[h];
+                if (!tail) rope_pair(x0[h], x1[h], c, sn, ya, yb);
+                dh[ia] = ya; dh[ib] = yb;
+                if (t.kind == 1) {
+                    store_conv(d2, t.dst2, t.d2type, row0 + h * src.ne[0] + ia, ya);
+                    store_conv(d2, t.dst2, t.d2type, row0 + h * src.ne[0] + ib, yb);
+                }
+            }
     }
 }
 
@@ -533,12 +593,22 @@ static int ew_build(const b200_ew_desc * tasks, int n, ew_batch & b, int64_t & n
             t.pos = (const int32_t *)d.pos->data; t.ff = d.ffac ? (const float *)d.ffac->data : nullptr;
             t.rp = rope_dev_from(*prm);
             t.n = nelem(d.src) / 2;
-        } else t.n = nelem(d.src);
+            t.ngrp = (int)((d.src->ne[1] + ROPE_HPT - 1) / ROPE_HPT);
+            t.nwide = d.src->ne[0] / 2 * t.ngrp * d.src->ne[2] * d.src->ne[3];
+        } else { t.n = nelem(d.src); t.nwide = t.n / 4; }
         if (d.kind != 0) {
             if (!d.dst2 || nelem(d.dst2) != nelem(d.src)) EW_FAIL();
             if (d.dst2->type != T_F16 && d.dst2->type != T_F32 && d.dst2->type != T_BF16) EW_FAIL();
             if (d.dst2->nb[0] != type_size(d.dst2->type)) EW_FAIL();
             t.dst2 = mk(d.dst2); t.d2type = d.dst2->type; t.dslot = (char * const *)d.dst2_slot;
+            if (d.kind == 2) {
+                auto vec_ok = [](const b200_tensor * x) {
+                    const size_t a = 4 * type_size(x->type);
+                    return x->nb[0] == type_size(x->type) && x->ne[0] % 4 == 0 && ((uintptr_t)x->data % a) == 0 &&
+                           (x->ne[1] == 1 || x->nb[1] % a == 0) && (x->ne[2] == 1 || x->nb[2] % a == 0) && (x->ne[3] == 1 || x->nb[3] % a == 0);
+                };
+                t.vec4 = !d.dst2_slot && vec_ok(d.src) && vec_ok(d.dst2);
+            }
         }
         nmax = std::max(nmax, t.n);
     }
@@ -553,5 +623,13 @@ extern "C" int b200_op_rope_cpy_batch(const b200_ew_desc * tasks, int n, void * 
     const int rc = ew_build(tasks, n, b, nmax);
     if (rc) return rc;
     if (nmax == 0) return 0;
+    // a prefill batch: enough (token, pair) positions that the per-head-group mapping fills the GPU
+    int64_t wide = 0; bool all_wide = true;
+    for (int i = 0; i < n; ++i) {
+        const ew_task & t = b.t[i];
+        if (t.kind != 2 && (t.src.ne[1] < 4 || t.src.ne[0] / 2 * t.src.ne[2] * t.src.ne[3] < 8192)) all_wide = false;
+        wide = std::max(wide, t.kind == 2 && !t.vec4 ? t.n : t.nwide);
+    }
+    if (all_wide && nmax >= 16384) return launch(ew_batch_wide_kernel, dim3(grid_for(wide, 256), (unsigned)n), 256, 0, (cudaStream_t)stream, b);
     return launch(ew_batch_kernel, dim3(grid_for(nmax, 256), (unsigned)n), 256, 0, (cudaStream_t)stream, b);
 }

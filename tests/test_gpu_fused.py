@@ -306,3 +306,48 @@ def test_cpy_vector_path_strided(sd, dd):
     assert torch.equal(dst, src.to(dd))
     assert torch.equal(flat.view(T, n), src.to(dd))
     assert bool((cache[:4] == 7).all()) and bool((cache[4 + T:] == 7).all()) and bool((cache[:, :n] == 7).all())
+
+
+class _EwDesc(C.Structure):
+    _fields_ = [("kind", C.c_int), ("src", C.c_void_p), ("dst", C.c_void_p), ("dst2", C.c_void_p), ("pos", C.c_void_p), ("ffac", C.c_void_p),
+                ("rope", C.c_void_p), ("dst2_slot", C.c_void_p)]
+
+
+@pytest.mark.parametrize("T,cache_dtype,mode", [(512, torch.float16, 0), (300, torch.float16, 2), (512, torch.bfloat16, 0), (6, torch.float16, 0)])
+def test_rope_store_batch_prefill_matches_separate_ops(T, cache_dtype, mode):
+    """b200_op_rope_cpy_batch on a prefill batch (the wide kernel: 8 heads per thread, 4-wide V store) and on a decode batch: rope(q),
+    rope(k) + K-cache rows, V-cache rows in one launch must equal b200_op_rope / b200_op_cpy run one after the other, bit for bit;
+    the cache views are strided (rows of a larger cache)."""
+    ops = _ops(); L = ops.lib()
+    hd, nh, nkv, n_ctx = 128, 32, 8, 1024
+    torch.manual_seed(T)
+    q = torch.randn(T, nh, hd, device="cuda"); k = torch.randn(T, nkv, hd, device="cuda"); v = torch.randn(T, nkv * hd, device="cuda")
+    pos = torch.arange(100, 100 + T, dtype=torch.int32, device="cuda")
+    prm = _RopeParams(n_dims=hd, mode=mode, n_ctx_orig=8192, freq_base=500000.0, freq_scale=1.0, ext_factor=0.0, attn_factor=1.0, beta_fast=32.0, beta_slow=1.0)
+
+    def run(batched):
+        oq = torch.zeros_like(q); ok_ = torch.zeros_like(k)
+        kc = torch.zeros(n_ctx, nkv * hd, device="cuda").to(cache_dtype); vc = torch.zeros(n_ctx, nkv * hd, device="cuda").to(cache_dtype)
+        kview = kc[17:17 + T]; vview = vc[17:17 + T]
+        tq, toq, tk, tok, tv, tpos = (ops.as_b200(x) for x in (q, oq, k, ok_, v, pos))
+        tkc, tvc = ops.as_b200(kview), ops.as_b200(vview)
+        if batched:
+            d = (_EwDesc * 3)()
+            d[0].kind = 0; d[0].src = C.addressof(tq); d[0].dst = C.addressof(toq); d[0].pos = C.addressof(tpos); d[0].rope = C.addressof(prm)
+            d[1].kind = 1; d[1].src = C.addressof(tk); d[1].dst = C.addressof(tok); d[1].pos = C.addressof(tpos); d[1].rope = C.addressof(prm); d[1].dst2 = C.addressof(tkc)
+            d[2].kind = 2; d[2].src = C.addressof(tv); d[2].dst2 = C.addressof(tvc)
+            assert L.b200_op_rope_cpy_batch_check(d, 3) == 0
+            assert L.b200_op_rope_cpy_batch(d, 3, _st(ops)) == 0
+        else:
+            assert L.b200_op_rope(C.byref(tq), C.byref(tpos), None, C.byref(toq), C.byref(prm), _st(ops)) == 0
+            assert L.b200_op_rope(C.byref(tk), C.byref(tpos), None, C.byref(tok), C.byref(prm), _st(ops)) == 0
+            tok2 = ops.as_b200(ok_.view(T, nkv * hd))
+            assert L.b200_op_cpy(C.byref(tok2), C.byref(tkc), _st(ops)) == 0
+            assert L.b200_op_cpy(C.byref(tv), C.byref(tvc), _st(ops)) == 0
+        torch.cuda.synchronize()
+        return oq, ok_, kc, vc
+
+    a = run(True); b = run(False)
+    for x, y, what in zip(a, b, ("rope(q)", "rope(k)", "K cache", "V cache")):
+        assert torch.equal(x.view(torch.int16) if x.dtype != torch.float32 else x, y.view(torch.int16) if y.dtype != torch.float32 else y), what
+    assert bool((a[2][:17] == 0).all()) and bool((a[2][17 + T:] == 0).all())
