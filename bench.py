@@ -360,6 +360,9 @@ def main():
                                        "peak": tpeak, "unit": "TFLOP/s", "frac": m["tflops"] / tpeak,
                                        "peak_source": "measured bf16 burst (MEASURED_PEAKS.json)" if peaks else "fallback 1.59 PFLOP/s",
                                        "ms_per_layer": m["ms_per_layer"]}
+                tp = os.path.join(ROOT, "profiles", "r01_mmq_traffic.json")      # ncu --set full of the three large shapes: DRAM bytes per launch
+                if os.path.exists(tp):
+                    pre["mmq_roofline"]["traffic"] = {x["shape"]: x["dram_read_bytes"] + x["dram_write_bytes"] for x in json.load(open(tp))["launches"]}
                 line["prefill"] = pre
             except Exception as e:  # noqa: BLE001
                 line["prefill"] = {"error": str(e)[:200]}
