@@ -253,6 +253,17 @@ int b200_mul_mat_q_bf16(int type, const void * W, int64_t nb1, const void * Xb, 
  * No reference counterpart: ggml-cuda launches one mul_mat_q per MUL_MAT node (ggml-cuda.cu:1936-2005). */
 int b200_mul_mat_q_bf16_group(int type, int ng, const void * const * W, int64_t nb1, const void * Xb, float * const * dst,
                               const int64_t * ds, const int * N, int K, int M, void * stream);
+/* b200_mul_mat_q for callers that cannot allocate device memory (CUDA-graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.  Same arguments and
+ * results (bit for bit) as b200_mul_mat_q without the scratch: the bf16 activation rows go to a static __device__ array of
+ * B200_NOALLOC_SCRATCH_BYTES inside the library (each GPU that loads the library holds it until exit), so the call needs
+ * K * M * 2 <= B200_NOALLOC_SCRATCH_BYTES and returns B200_ERR_NOALLOC_TOO_LARGE (with a line on stderr) beyond that.
+ * The call itself performs no cudaMalloc / cudaFree.  All calls on a device share the array: calls that overlap on the
+ * GPU (two streams, concurrent graph replays) race -- serialise them.  Nothing in the array needs clearing between calls. */
+#define B200_NOALLOC_SCRATCH_BYTES (8 << 20)
+#define B200_ERR_NOALLOC_TOO_LARGE (-7)
+int b200_mul_mat_q_noalloc(int type, const void * W, int64_t nb1, const float * X, int64_t xs, float * dst, int64_t ds,
+                           int N, int K, int M, void * stream);
 /* debug hook: device buffer of (return value) int64 slots that CTA (0,0) of later b200_mul_mat_q launches fills with
  * clock64 stamps of its pipeline events (tools/mmq_debug.py trace); NULL switches it off. */
 int b200_mmq_debug_trace(void * dev_buf);

@@ -60,7 +60,7 @@ EXPORTS = ["b200_flash_attn_xq_supported", "b200_op_flash_attn_ext_xq", "b200_fl
            "b200_mul_mat_supported", "b200_op_mul_mat_id", "b200_mul_mat_q", "b200_mul_mat_q_scratch_bytes",
            "b200_mul_mat_q_supported", "b200_mmq_debug_trace", "b200_acts_bf16_bytes",
            "b200_convert_acts_bf16", "b200_mul_mat_q_bf16", "b200_mul_mat_q_bf16_group", "b200_op_add_rms_norm_mul", "b200_op_unary_mul", "b200_op_rope_cpy_batch", "b200_op_rope_cpy_batch_check",
-           "b200_ktrace_enable", "b200_ktrace_dump", "b200_mmvq_fusable"]
+           "b200_ktrace_enable", "b200_ktrace_dump", "b200_mmvq_fusable", "b200_mul_mat_q_noalloc"]
 
 
 def _stream():
@@ -135,6 +135,19 @@ def mul_mat_q(t, W, X, N, K, nb1=None):
                                 C.c_void_p(dst.data_ptr()), C.c_int64(N), C.c_int(N), C.c_int(K), C.c_int(M),
                                 C.c_void_p(scratch.data_ptr()), C.c_int64(need), _stream()), "b200_mul_mat_q")
     return dst
+
+
+def mul_mat_q_noalloc(t, W, X, N, K, nb1=None, dst=None):
+    """b200_mul_mat_q_noalloc: mul_mat_q with the activation scratch in the library's static device array (no allocation inside
+    the call; pass `dst` to keep the binding allocation-free as well).  Returns (rc, dst): rc is the library's code."""
+    assert W.is_cuda and X.is_cuda and X.dtype == torch.float32 and X.stride(-1) == 1
+    M = X.shape[0]
+    nb1 = nb1 or row_bytes(t, K)
+    if dst is None:
+        dst = torch.empty((M, N), dtype=torch.float32, device=X.device)
+    rc = lib().b200_mul_mat_q_noalloc(C.c_int(t), C.c_void_p(W.data_ptr()), C.c_int64(nb1), C.c_void_p(X.data_ptr()), C.c_int64(X.stride(0)),
+                                      C.c_void_p(dst.data_ptr()), C.c_int64(dst.stride(0)), C.c_int(N), C.c_int(K), C.c_int(M), _stream())
+    return rc, dst
 
 
 def mul_mat_q_group(t, Ws, Ns, X, K):
