@@ -17,9 +17,17 @@ The model is a random-init GGUF of that architecture written by tools/make_gguf.
           GEMVs of one token (distinct weight matrices, 3.36 GB > L2), through the C ABI of include/b200_ops.h
   cpu_baseline  the reference CPU backend on the same GGUF (llama-bench -ngl 0, all host threads), bounded to tg16
 
+  value   tokens / device time of the REPLAYED graph_compute calls of the same workload (CUDA events on the backend's
+          stream; the plugin keeps the first eager run and the capture + instantiate call of a graph out of this sum)
+
 `--impl reference` times the reference's own CPU implementation (same llama-bench, no plugin) on the same model.
-N > 1 (torchrun): the decode path of an 8B model does not shard at this level (row split is SURVEY 8e, next):
-replicas only -- every rank runs the same workload on its own GPU, value = tokens of all ranks / max time.
+
+N > 1 (torchrun, one rank per GPU): the path shards by WEIGHT ROWS (--split-mode row): rank 0, with all N GPUs
+visible, runs the north-star multi-GPU workload -- Llama-3-70B Q4_K_M through unmodified llama-bench with -sm row -ts 1/../1
+(and -sm layer, and -sm none on one GPU as the reference point) -- after checking IN THE SAME RUN that split and single-GPU
+logits of the 1B model are bit-identical (tests/host/build/logits_check); the other ranks take part in the replica side
+measurement and then wait at the barrier (libllama drives all GPUs of a split model from one process: the ggml backend ABI has
+one host thread per model, not one per GPU).  value / e2e = 70B row-split tg tokens/s, scaling "strong".
 """
 import argparse
 import json
@@ -130,7 +138,10 @@ def ensure_model(preset="llama3-8b", ftype="q4_k_m"):
     return path
 
 
-def llama_bench(model, extra, plugin, timing=False, device=None, timeout=1800):
+GPU_ARM_THREADS = 4      # host threads of a GPU-arm llama-bench (-t): libllama's CPU work per token is tiny; the default (all cores) makes replicas fight
+
+
+def llama_bench(model, extra, plugin, timing=False, device=None, timeout=3600):
     """Run the reference's llama-bench; returns (list of json results, stats dict from the plugin)."""
     exe = os.path.join(REF_BIN, "llama-bench")
     if not os.path.exists(exe):
@@ -146,14 +157,24 @@ def llama_bench(model, extra, plugin, timing=False, device=None, timeout=1800):
             env["B200_TIMING"] = "1"
         if device is not None:
             env["CUDA_VISIBLE_DEVICES"] = str(device)
+    if plugin and "-t" not in extra:
+        extra = extra + ["-t", str(GPU_ARM_THREADS)]
     r = subprocess.run([exe, "-m", model, "-o", "json"] + extra, capture_output=True, text=True, env=env, timeout=timeout)
+    logdir = os.environ.get("B200_BENCH_LOGDIR")            # keep the raw llama-bench output (profiles/ evidence)
+    if logdir and int(os.environ.get("RANK", "0")) == 0:
+        os.makedirs(logdir, exist_ok=True)
+        with open(os.path.join(logdir, "llama_bench_calls.log"), "a") as f:
+            f.write("$ %s%s\n%s\n--- stderr (tail) ---\n%s\n\n" % ("GGML_BACKEND_PATH=libggml-b200.so " if plugin else "", " ".join([os.path.basename(exe), "-m", os.path.basename(model), "-o", "json"] + extra),
+                                                                 r.stdout[-6000:], r.stderr[-1500:]))
     if r.returncode != 0:
         raise RuntimeError("llama-bench failed (%d): %s" % (r.returncode, r.stderr[-2000:]))
     res = json.loads(r.stdout[r.stdout.index("["):])
     stats = {}
-    m = re.search(r"ggml-b200: stats graphs=(\d+) device_ms=([0-9.]+) kernel_launches=(\d+)", r.stderr)
+    m = re.search(r"ggml-b200: stats graphs=(\d+) device_ms=([0-9.]+) kernel_launches=(\d+) host_enqueue_ms=([0-9.]+) replay_graphs=(\d+) replay_ms=([0-9.]+)", r.stderr)
     if m:
-        stats = {"graphs": int(m.group(1)), "device_ms": float(m.group(2)), "launches": int(m.group(3))}
+        stats = {"graphs": int(m.group(1)), "device_ms": float(m.group(2)), "launches": int(m.group(3)), "host_ms": float(m.group(4)),
+                 "replay_graphs": int(m.group(5)), "replay_ms": float(m.group(6))}
+    stats["stderr_tail"] = r.stderr[-1500:]
     if plugin and "B200" not in r.stdout + r.stderr:
         raise RuntimeError("llama-bench did not load the B200 backend: " + r.stderr[-1000:])
     return res, stats
@@ -239,22 +260,100 @@ def cpu_reference_run(model, n_tokens, threads):
     return float(res[-1]["avg_ts"])
 
 
+WORKLOAD_1 = "llama3-8b-q4_k_m tg, batch 1"          # config.workload: the same string in both arms
+WORKLOAD_N = "llama3-70b-q4_k_m tg, batch 1"
+
+
 def reference_arm(args):
     """The reference's own CPU implementation of the path on the host cores (unmodified llama-bench, no plugin)."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
-    model = ensure_model()
+    multi = args.gpus > 1
+    model = ensure_model("llama3-70b") if multi else ensure_model()
     threads = os.cpu_count() or 1
-    n = max(4, min(args.steps, 64))
+    n = max(4, min(args.steps, 8 if multi else 64))          # bounded sample: 70B on the host cores runs at ~2 tokens/s
     v = cpu_reference_run(model, n, threads)
-    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "tokens/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 / v, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "q4_K/q6_K weights x q8_K activations (int8 dot, f32 accumulate)", "data": "synthetic",
-            "config": {"workload": "llama3-8b-q4_k_m tg, batch 1, reference ggml CPU backend via llama-bench -ngl 0"},
+    line = {"impl": "reference", "metric": METRIC_N if multi else METRIC, "value": v, "unit": "tokens/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 / v, "higher_is_better": True, "scaling": "strong" if multi else "weak", "vs_baseline": None,
+            "dtype": "q4_K/q5_K/q6_K weights x q8_K activations (int8 dot, f32 accumulate)", "data": "synthetic",
+            "config": {"workload": WORKLOAD_N if multi else WORKLOAD_1,
+                       "harness": "reference ggml CPU backend via llama-bench -ngl 0 (no GPU is used by this arm)"},
             "cpu_baseline": {"value": v, "unit": "tokens/s", "cores": threads, "kind": "reference",
                              "sample": "llama-bench -ngl 0 -p 0 -n %d -r 1 -t %d (after its 1-token warm-up)" % (n, threads)},
             "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+METRIC_N = "llama-bench tg tokens/s, Llama-3-70B Q4_K_M --split-mode row over N GPUs (batch-1 decode)"
+
+
+def device_step_ms(stats, n_tok):
+    """ms of device time per decoded token from the plugin's B200_TIMING line: replayed CUDA-graph calls only (the first eager
+    sighting of a graph and its capture + instantiate call carry host milliseconds and are left out)."""
+    if not stats or stats.get("graphs", 0) <= 0:
+        raise RuntimeError("the plugin reported no graph_compute calls: the CUDA path did not run")
+    gpt = stats["graphs"] / n_tok                      # graph_compute calls per token (one per backend that owns layers)
+    if stats.get("replay_graphs", 0) > 0:
+        return stats["replay_ms"] / stats["replay_graphs"] * gpt, gpt, "replayed graphs only"
+    return stats["device_ms"] / stats["graphs"] * gpt, gpt, "all calls (no graph was replayed)"
+
+
+def split_parity(n_gpus):
+    """--split-mode row / layer against the single-GPU run of the same model (Llama-3.2-1B Q4_K_M, prefill 40 + 8 decode steps):
+    a weight row's dot product does not depend on the device that holds it, so the logits must be bit-identical."""
+    import numpy as np
+    exe = os.path.join(ROOT, "tests", "host", "build", "logits_check")
+    if not os.path.exists(exe):
+        return "not run (tests/host/build/logits_check missing)"
+    model = ensure_model("llama3.2-1b")
+    env = dict(os.environ)
+    env["LD_LIBRARY_PATH"] = REF_LIB + ":" + os.path.join(ROOT, "llamacog_b200") + ":" + env.get("LD_LIBRARY_PATH", "")
+    env["GGML_BACKEND_PATH"] = PLUGIN
+    env["CUDA_VISIBLE_DEVICES"] = visible_devices(n_gpus)
+    outs = {}
+    # row-all: every matrix sharded (B200_SPLIT_MIN_MB=0); row: the default placement (small matrices stay whole on the main device)
+    for name, mode, extra in (("none", "none", {}), ("row", "row", {}), ("row-all", "row", {"B200_SPLIT_MIN_MB": "0"}), ("layer", "layer", {})):
+        out = os.path.join(MODEL_DIR, "parity_%s_%d.bin" % (name, os.getpid()))
+        r = subprocess.run([exe, model, out, "99", "1", "40", "8", "512", mode], capture_output=True, text=True, env=dict(env, **extra), timeout=900)
+        if r.returncode != 0:
+            return "FAILED to run (%s): %s" % (name, r.stderr[-300:])
+        outs[name] = np.fromfile(out, dtype=np.uint8)
+        os.remove(out)
+    bad = [m for m in ("row", "row-all", "layer") if not np.array_equal(outs[m], outs["none"])]
+    return "bit-identical" if not bad else "MISMATCH: " + ",".join(bad)
+
+
+def visible_devices(n):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    ids = vis.split(",") if vis else [str(i) for i in range(64)]
+    return ",".join(ids[:n])
+
+
+def split_arm(args, world, sampler):
+    """Rank 0, all `world` GPUs visible: Llama-3-70B Q4_K_M over unmodified llama-bench, -sm none (one GPU) / row / layer."""
+    model = ensure_model("llama3-70b")
+    dev = visible_devices(world)
+    ts = "/".join(["1"] * world)
+    common = ["-ngl", "99", "-fa", "1", "-r", "1", "-mg", "0"]
+    out = {"model": "llama3-70b-q4_k_m (random init, tools/make_gguf.py)", "tensor_split": ts, "logs": {}}
+    t0 = time.time()
+    # e2e: tg K (after W untimed tokens) and pp512, the three placements in one llama-bench invocation each
+    def run(sm, extra, timing=False):
+        return llama_bench(model, common + ["-sm", sm] + (["-ts", ts] if sm != "none" else []) + extra, plugin=True, timing=timing, device=dev)
+    res = {}
+    for sm in ("none", "row", "layer"):
+        r, st = run(sm, ["-p", "0", "-n", "%d,%d" % (args.warmup, args.steps)])
+        rp, _ = run(sm, ["-p", "512", "-n", "0", "-r", "2"])
+        res[sm] = {"tg_tokens_per_s": float(r[-1]["avg_ts"]), "pp512_tokens_per_s": float(rp[-1]["avg_ts"])}
+    t1 = time.time()
+    # device time of the row-split decode step (B200_TIMING adds an event synchronisation per graph: its own run)
+    _, st = run("row", ["-p", "0", "-n", "%d,%d" % (args.warmup, args.steps)], timing=True)
+    n_tok = args.warmup + args.steps + 2
+    ms_step, gpt, how = device_step_ms(st, n_tok)
+    out.update({"one_gpu": res["none"], "row": res["row"], "layer": res["layer"],
+                "row_tg_speedup_vs_one_gpu": res["row"]["tg_tokens_per_s"] / res["none"]["tg_tokens_per_s"],
+                "row_device_ms_per_token": ms_step, "device_time": how, "launches_per_token": st["launches"] / n_tok})
+    return out, ms_step, (t0, t1)
 
 
 def main():
@@ -265,6 +364,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-split", action="store_true", help="N > 1: replicas only (skip the 70B row-split arm)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
@@ -275,10 +375,12 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     dist = None
     if world > 1:
+        import datetime
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # rank 0 spends minutes in the split arm while the others wait at a barrier: no 10-minute watchdog
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(hours=3))
     if rank == 0:
         model = ensure_model()
     if world > 1:
@@ -298,14 +400,9 @@ def main():
     t1 = time.time()
     clocks = sampler.summary(t0, t1)
     res_t, stats = llama_bench(model, lb, plugin=True, timing=True, device=device)    # device time of graph_compute
-    sampler.stop_flag = True
     e2e_rank = float(res[-1]["avg_ts"])
     n_tok = args.warmup + args.steps + 2            # llama-bench decodes one warm-up token in front of each test
-    if not stats or stats["graphs"] <= 0:
-        raise RuntimeError("the plugin reported no graph_compute calls: the CUDA path did not run")
-    dev_ms_per_graph = stats["device_ms"] / stats["graphs"]
-    graphs_per_tok = stats["graphs"] / n_tok
-    ms_step = dev_ms_per_graph * graphs_per_tok
+    ms_step, graphs_per_tok, dev_how = device_step_ms(stats, n_tok)
     launches_per_step = stats["launches"] / n_tok
 
     if world > 1:
@@ -323,13 +420,37 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "q4_K/q6_K weights x q8_1 activations (int8 dp4a, f32 accumulate), f16 KV", "data": "synthetic",
-                "config": {"workload": "llama3-8b-q4_k_m tg%d: unmodified reference llama-bench -ngl 99 -fa 1 -p 0 over the "
-                                       "libggml-b200.so plugin; random-init GGUF (tools/make_gguf.py, reference quantiser, no_vocab)" % args.steps,
+                "config": {"workload": WORKLOAD_1,
+                           "harness": "tg%d: unmodified reference llama-bench -ngl 99 -fa 1 -p 0 -t %d over the libggml-b200.so plugin; random-init GGUF "
+                                      "(tools/make_gguf.py, reference quantiser, no_vocab)" % (args.steps, GPU_ARM_THREADS),
                            "l2": "inputs larger than L2 (4.6 GB of weights streamed per step)",
-                           "parallelism": "replicas x%d" % world, "graph_compute_calls_per_token": graphs_per_tok},
+                           "parallelism": "replicas x%d" % world, "graph_compute_calls_per_token": graphs_per_tok,
+                           "device_time": dev_how},
                 "clocks": clocks,
                 "e2e": {"value": e2e_val, "unit": "tokens/s", "h2d_bytes_per_step": 12 + n_kv * 64 * 4, "d2h_bytes_per_step": N_VOCAB * 4},
                 "gpu_launches": int(round(launches_per_step * args.steps))}
+        if world > 1 and not args.no_split:
+            # the north-star multi-GPU workload replaces the replica figures as the headline; they stay as a side key
+            replicas = {"metric": METRIC, "value": value, "e2e": e2e_val, "ms_per_step": ms_step, "parallelism": "replicas x%d" % world}
+            try:
+                parity = split_parity(world)
+                sp, ms_row, (s0, s1) = split_arm(args, world, sampler)
+                line.update({"metric": METRIC_N, "value": 1e3 / ms_row, "ms_per_step": ms_row, "scaling": "strong",
+                             "dtype": "q4_K/q5_K/q6_K weights x q8_1 activations (int8 dp4a, f32 accumulate), f16 KV",
+                             "clocks": sampler.summary(s0, s1),
+                             "e2e": {"value": sp["row"]["tg_tokens_per_s"], "unit": "tokens/s", "h2d_bytes_per_step": 12 + n_kv * 64 * 4,
+                                     "d2h_bytes_per_step": N_VOCAB * 4},
+                             "gpu_launches": int(round(sp["launches_per_token"] * args.steps)),
+                             "split": sp, "split_parity": parity, "replicas": replicas})
+                line["config"] = {"workload": WORKLOAD_N,
+                                  "harness": "tg%d: unmodified reference llama-bench -ngl 99 -fa 1 -p 0 -sm row -ts %s -t %d over the libggml-b200.so plugin, "
+                                             "driven from rank 0 with %d GPUs visible; random-init GGUF" % (args.steps, sp["tensor_split"], GPU_ARM_THREADS, world),
+                                  "l2": "inputs larger than L2 (42 GB of weights streamed per step)",
+                                  "parallelism": "row split x%d" % world, "device_time": sp["device_time"]}
+            except Exception as e:  # noqa: BLE001
+                line["split"] = {"error": str(e)[-600:]}
+                line["replicas"] = replicas
+        sampler.stop_flag = True
         if not args.no_roofline:
             try:
                 k = kernel_roofline(max(20, min(args.steps, 200)), args.warmup, local)
@@ -342,7 +463,7 @@ def main():
                                     "achieved": k["gbps"], "peak": peak, "unit": "GB/s", "frac": k["gbps"] / peak, "traffic": traffic,
                                     "peak_source": how, "launches": k["launches"], "us_per_launch": k["us_per_launch"],
                                     "algorithmic_bytes_per_launch": k["bytes"] / k["launches"],
-                                    "whole_step_GBps": plan_bytes(step_plan()) / (ms_step * 1e-3) / 1e9}
+                                    "whole_step_GBps": plan_bytes(step_plan()) / (ms_step * 1e-3) / 1e9 if world == 1 else None}
             except Exception as e:  # noqa: BLE001
                 line["roofline"] = {"error": str(e)[:200]}
         if not args.no_roofline and world == 1:

@@ -84,6 +84,19 @@ typedef struct b200_mmvq_args {
     const float * norm_x; const float * norm_w; float * norm_y; float * norm_out; float norm_eps;
     /*  - epilogue ROPE + KV-cache store of a q/k/v launch (M = 1, see struct b200_gemv_rope below) */
     const struct b200_gemv_rope * rope;
+    /* Row-split hand-over folded into the launch (all optional; protocol of csrc/peer.cu, flags are 32-bit words, zero when idle,
+     * in memory the launching device can reach).  Replaces the wait / signal launches around a shard's mat-vec, i.e. the
+     * cudaStreamWaitEvent / cudaEventRecord pairs of the reference's split MUL_MAT (ggml-cuda/ggml-cuda.cu:1628-1630, :1724-1745).
+     * Needs pre-quantised activations (Xq).
+     *   hs_wait    every CTA spins until *hs_wait != 0 before it reads Xq            (peer: "the activations have arrived")
+     *   hs_counter zeroed word in the launching device's memory; elects the CTA that finishes last, which then, in this order,
+     *   hs_join    waits for hs_join[t * hs_join_stride], t in hs_join_mask, and lowers them  (main: "every peer's slice is written")
+     *   hs_clear   stores 0 to *hs_clear                                             (peer: lowers the wait flag)
+     *   hs_signal  system-scope fence, then *hs_signal = 1                           (peer: "my slice of dst is written")
+     *   hs_timeout_ms / hs_error: spin budget (0 = none); on expiry *hs_error = 1 and the kernel carries on */
+    const uint32_t * hs_wait; uint32_t * hs_clear; uint32_t * hs_signal;
+    uint32_t * hs_join; int hs_join_stride; uint32_t hs_join_mask;
+    unsigned * hs_counter; unsigned hs_timeout_ms; uint32_t * hs_error;
 } b200_mmvq_args;
 
 /* 1 when b200_mul_mat_vec_q_ex (ng = 1, W/N NULL) or b200_mul_mat_vec_q_group would run these arguments on the
@@ -328,6 +341,11 @@ int b200_kernel_launch_add(int n);
 int b200_peer_bcast(const void * src, void * const * dsts, uint32_t * const * flags, int n_peers, int64_t bytes,
                     unsigned * counter, void * stream);
 int b200_peer_wait(uint32_t * flags, int stride, uint32_t mask, void * stream);
+/* same with an explicit spin budget (0 = none) and an error word (device-visible, e.g. mapped host memory) that is set to 1
+ * when the budget runs out; the kernel then carries on instead of trapping.  b200_peer_timeout_ms: env B200_SPLIT_TIMEOUT_MS,
+ * default 30000. */
+int b200_peer_wait_ex(uint32_t * flags, int stride, uint32_t mask, unsigned timeout_ms, uint32_t * error, void * stream);
+unsigned b200_peer_timeout_ms(void);
 int b200_peer_signal(uint32_t * remote_flag, void * stream);
 
 #ifdef __cplusplus

@@ -170,7 +170,69 @@ __device__ __forceinline__ float sumsq4(const float4 v) {
 }
 __device__ __forceinline__ float rms_scale(float tot, int K, float eps) { return rsqrtf(tot / (float)K + eps); }
 
+// ---- row-split hand-over folded into a kernel (protocol of csrc/peer.cu; b200_mmvq_args.hs_*) ---------------------------
+// A launch on a peer device waits for "the activations have arrived" in the prologue of every CTA and, from the CTA that
+// finishes last, lowers that flag and raises "my slice of dst is written" in the main device's memory; the main device's own
+// launch waits for those flags in its last CTA, so that the completion of its kernel means every slice is there.  Replaces
+// three dependent launches per hand-over (wait kernel -> GEMV -> signal kernel) of the first version.
+struct hs_params {
+    const uint32_t * wait;               // every CTA: spin until != 0 before the activations are read
+    uint32_t * clear;                    // last CTA: store 0 (the wait flag, once nobody reads it any more)
+    uint32_t * signal;                   // last CTA: system fence, then store 1 (remote)
+    uint32_t * join; int join_stride; uint32_t join_mask;      // last CTA: wait for join[t * stride], t in mask; lower them
+    unsigned * counter;                  // ticket that elects the last CTA; returns to 0 by itself
+    unsigned long long timeout_ns;       // spin budget (0: none); expiry sets *error and goes on (results are then garbage)
+    uint32_t * error;
+};
+__device__ __forceinline__ uint32_t hs_ld_acquire_sys(const uint32_t * p) {
+    uint32_t v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v;
+}
+__device__ __forceinline__ void hs_st_release_sys(uint32_t * p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void hs_spin(const uint32_t * f, const hs_params & h) {
+    unsigned long long t0 = 0;
+    if (h.timeout_ns) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    int n = 0;
+    while (hs_ld_acquire_sys(f) == 0u) {
+        if (++n > 64) __nanosleep(32);
+        if (h.timeout_ns && (n & 255) == 0) {
+            unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t - t0 > h.timeout_ns) { if (h.error) *(volatile uint32_t *)h.error = 1u; break; }
+        }
+    }
+}
+// one thread per CTA, before the activations are fetched (generic loads or a bulk copy issued by the same thread)
+__device__ __forceinline__ void hs_wait_acts(const hs_params & h) {
+    if (!h.wait) return;
+    hs_spin(h.wait, h);
+    asm volatile("fence.proxy.async;" ::: "memory");        // the bulk copy that follows reads what the flag guards
+}
+// one thread per CTA, after the threads of the CTA that stored results have synchronised with it (__syncwarp / bar.sync);
+// total = CTAs of the launch.  Fences, measured between two B200s (tools/p2p_pingpong.cu, profiles/r02_p2p_pingpong.log): a
+// system-scope fence after remote stores costs 1.9 us and 296 CTAs issuing one each serialise (29 us per hand-over); a gpu-scope
+// fence costs 0.5 us.  So every CTA orders its stores before its ticket at gpu scope, and only the CTA that draws the last
+// ticket -- whose atomic has observed all the others -- pays for the system-scope fence in front of the flag (9 us per hand-over
+// with 296 CTAs, no stale reads): the fence is cumulative over the writes that happen-before it.
+__device__ __forceinline__ void hs_finish(const hs_params & h, unsigned total) {
+    if (!h.counter) return;
+    __threadfence();
+    if (atomicInc(h.counter, total - 1) != total - 1) return;
+    for (uint32_t m = h.join_mask, t = 0; m; m >>= 1, ++t) {
+        if (!(m & 1u)) continue;
+        uint32_t * f = h.join + (size_t)t * h.join_stride;
+        hs_spin(f, h);
+        *(volatile uint32_t *)f = 0u;
+    }
+    if (h.clear) *(volatile uint32_t *)h.clear = 0u;
+    __threadfence_system();
+    if (h.signal) asm volatile("st.relaxed.sys.global.u32 [%0], %1;" :: "l"(h.signal), "r"(1u) : "memory");
+}
+
 extern int g_launches;   // kernels launched by this library (bench.py gpu_launches)
+#define B200_HS_FROM_ARGS(h, a) do { (h).wait = (a)->hs_wait; (h).clear = (a)->hs_clear; (h).signal = (a)->hs_signal; (h).join = (a)->hs_join; \
+    (h).join_stride = (a)->hs_join_stride; (h).join_mask = (a)->hs_join ? (a)->hs_join_mask : 0u; (h).counter = (a)->hs_counter; \
+    (h).timeout_ns = (unsigned long long)(a)->hs_timeout_ms * 1000000ull; (h).error = (a)->hs_error; } while (0)
 int pdl_default();       // env B200_PDL (default 1): launch kernels with programmatic dependent launch
 
 }  // namespace b200

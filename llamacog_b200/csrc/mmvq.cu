@@ -152,6 +152,7 @@ extern "C" int b200_mul_mat_vec_q_ex(const b200_mmvq_args * a, void * stream) {
     if (a->K <= 0 || a->K % block_elems(a->type) || a->N <= 0 || a->M <= 0) return -1;
     const int mmax = max_cols_per_launch(a->K);
     if (mmax <= 0) return -2;
+    if ((a->hs_wait || a->hs_counter) && (!a->Xq || a->ids || a->M > mmax)) return -1;      // the hand-over hooks guard Xq, one launch
     {   // batch-1 decode on pre-quantised activations: register-resident kernel (mmvq_r.cuh)
         const void * W1[1] = { a->W }; float * D1[1] = { a->dst }; const int N1[1] = { a->N };
         const int rc = mmvqr_try(a, 1, W1, D1, N1, (cudaStream_t)stream);
@@ -174,6 +175,7 @@ extern "C" int b200_mul_mat_vec_q_ex(const b200_mmvq_args * a, void * stream) {
         p.vec_ok = ((((uintptr_t)p.X) | ((uintptr_t)a->xs * 4) | ((uintptr_t)a->x_sy * 4) | ((uintptr_t)a->x_sz * 4)) & 15) == 0;
         p.dbg_sumi = a->dbg_sumi ? a->dbg_sumi + (int64_t)m0 * a->N * (a->K / 32) : nullptr;
         if (m0 + mmax >= a->M) set_prefetch(p, a);
+        B200_HS_FROM_ARGS(p.hs, a);
         mmvq_launch_cfg c = {};
         int rc = configure(a->type, a->N, a->K, mc, *a, p, c);
         if (rc) return rc;
@@ -201,6 +203,7 @@ extern "C" int b200_mul_mat_vec_q_group(const b200_mmvq_args * a, int ng, const 
     if (!a || ng < 1 || ng > 3 || !b200_mmvq_supported_type(a->type)) return -1;
     if (a->K <= 0 || a->K % block_elems(a->type) || a->M <= 0 || a->M > max_cols_per_launch(a->K)) return -1;
     if (std::max(1, a->ny) != 1 || std::max(1, a->nz) != 1 || a->ids || a->dbg_sumi) return -1;
+    if ((a->hs_wait || a->hs_counter) && !a->Xq) return -1;
     int ntot = 0;
     for (int g = 0; g < ng; ++g) { if (N[g] <= 0) return -1; ntot += N[g]; }
     {
@@ -216,6 +219,7 @@ extern "C" int b200_mul_mat_vec_q_group(const b200_mmvq_args * a, int ng, const 
     p.w_div_y = 1; p.w_div_z = 1; p.x_mod_y = 1 << 30;
     p.vec_ok = ((((uintptr_t)p.X) | ((uintptr_t)a->xs * 4)) & 15) == 0;
     set_prefetch(p, a);
+    B200_HS_FROM_ARGS(p.hs, a);
     b200_mmvq_args cfg = *a;
     uintptr_t align = 0;
     for (int g = 0; g < ng; ++g) align |= (uintptr_t)W[g];

@@ -63,6 +63,7 @@ struct mmvq_params {
     int cta0[4], rows_qg[3], rows_remg[3];
     // trailing L2 prefetch of the next matmul's weights (b200_mmvq_args.pf_*)
     int pf_n; const uint8_t * pf_ptr[3]; int64_t pf_bytes[3];
+    hs_params hs;            // row-split hand-over folded into the launch (common.cuh); needs Xq
 };
 
 template <int TYPE, int M, bool A16, bool DBG>
@@ -166,6 +167,7 @@ __global__ void __launch_bounds__(288, (M <= 4 ? 2 : 1)) mmvq_kernel(const mmvq_
             if (p.pf_n && ngroups <= p.nstages) prefetch_next();
         }
         pdl_wait();   // dst may still be read by the previous grid; Xq is written by it
+        if (lane == 0) hs_wait_acts(p.hs);      // row split, peer side: the main device's broadcast has landed
         if (p.Xq && lane == 0) {
             const uint8_t * xq = Xqc;
             mbar_expect_tx(actbar, (uint32_t)M * acs);
@@ -187,6 +189,10 @@ __global__ void __launch_bounds__(288, (M <= 4 ? 2 : 1)) mmvq_kernel(const mmvq_
                 issue(g + p.nstages);
                 if (p.pf_n && g + p.nstages == ngroups - 1) prefetch_next();
             }
+        }
+        if (p.hs.counter) {                    // row split: the last CTA of the launch lowers / raises / awaits the hand-over flags
+            __syncwarp();
+            if (lane == 0) hs_finish(p.hs, gridDim.x * gridDim.y * gridDim.z);
         }
     } else {
         // ================= consumer warps =================

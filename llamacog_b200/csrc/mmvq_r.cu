@@ -134,6 +134,7 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     p.R = R; p.nstages = nstages; p.stage_bytes = stage_bytes;
     p.r0 = q0; p.r1 = q1; p.r2 = q2; p.stagger = stagger;
     p.dbg_sumi = a->dbg_sumi;
+    B200_HS_FROM_ARGS(p.hs, a);
     mmvqr_launch_cfg c;
     c.grid = dim3(used, 1, 1);
     c.smem = (size_t)nstages * stage_bytes + act_bytes + (((size_t)nstages * R * nw + 1) & ~(size_t)1) * 4 + (size_t)nstages * 16 + tail_bytes;

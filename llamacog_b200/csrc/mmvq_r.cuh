@@ -57,6 +57,7 @@ struct mmvqr_params {
     int rope_on, rope_rows;
     int rmode[3]; float * rout[3]; char * rcell[3]; char * const * rslot[3]; int rctype[3], rcesz[3], rhd[3];
     const int32_t * rpos; const float * rff; rope_dev rp;
+    hs_params hs;            // row-split hand-over folded into the launch (common.cuh)
 };
 
 struct hacts { int q[4][8]; float d8[4], dsq[4]; int m32a[4], m32b[4]; };
@@ -218,6 +219,7 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
             __syncwarp();
         }
         pdl_wait();           // the activations come from the previous kernel; dst may still be read by it
+        if (lane == 0) hs_wait_acts(p.hs);      // row split, peer side: the main device's broadcast has landed
         if (lane == 0) {      // one coalesced copy of the column; the consumers pick their registers out of shared memory
             const uint32_t ab = NORM ? (uint32_t)p.K * 4 : (uint32_t)p.BPR * ACT_ITEM;
             mbar_expect_tx(actbar, ab);
@@ -272,6 +274,10 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
             if (s == 0) ktrace_event(2);       // first stage consumed and stored
         }
         ktrace_event(3);                       // all rows of CTA 0 stored
+        if (p.hs.counter) {                    // row split: the last CTA of the launch lowers / raises / awaits the hand-over flags
+            __syncwarp();
+            if (lane == 0) hs_finish(p.hs, gridDim.x);
+        }
     } else {
         const int ct = tid - 32;
         const int h = ct & (p.TPR - 1), rsub = ct >> p.lgTPR;

@@ -14,9 +14,16 @@
 //   main:  ... its own shard, then b200_peer_wait on the done flags of all peers
 //
 // The flags return to 0 after every hand-over, so a captured CUDA graph replays the same protocol.  Every spin is
-// bounded by a 2 s wall-clock budget and traps: a protocol bug surfaces as a launch failure, not as a hung GPU.
+// bounded by a wall-clock budget (B200_SPLIT_TIMEOUT_MS, default 30 s: tools that serialise kernels, time slicing or a long
+// backlog on the other device must not trip it).  On expiry b200_peer_wait_ex sets the caller's error word and carries on --
+// the plugin then fails the backend cleanly; the plain b200_peer_wait has nowhere to report to and traps.
+//
+// For decode the wait and the signal no longer are launches of their own: the mat-vec kernels take the flags as arguments
+// (b200_mmvq_args.hs_*, common.cuh hs_params) -- wait in the prologue of every CTA, signal / join from the CTA that finishes last.
 #include "common.cuh"
 #include "../../include/b200_ops.h"
+
+#include <cstdlib>
 
 namespace b200 {
 
@@ -50,25 +57,31 @@ __global__ void __launch_bounds__(512) peer_bcast_kernel(const bcast_args a) {
         dst[i] = v0; dst[i + step] = v1; dst[i + 2 * step] = v2; dst[i + 3 * step] = v3;
     }
     for (; i < a.n16; i += step) dst[i] = a.src[i];
-    __threadfence_system();
     __syncthreads();
     if (threadIdx.x == 0) {
+        // gpu-scope fence per block, ONE system-scope fence by the block that draws the last ticket (it has observed all the
+        // others; the fence is cumulative): 512 threads x 128 blocks fencing at system scope serialise for tens of microseconds
+        __threadfence();
         const unsigned total = gridDim.x * gridDim.y;
         if (atomicInc(a.counter, total - 1) == total - 1) {        // every block's stores are ordered before its increment
             __threadfence_system();
-            for (int q = 0; q < a.n_peers; ++q) st_release_sys(a.flag[q], 1u);
+            for (int q = 0; q < a.n_peers; ++q) asm volatile("st.relaxed.sys.global.u32 [%0], %1;" :: "l"(a.flag[q]), "r"(1u) : "memory");
         }
     }
 }
 
 // thread t (if its bit is set in mask) waits for flags[t * stride] to be raised and lowers it
-__global__ void peer_wait_kernel(uint32_t * flags, int stride, uint32_t mask) {
+__global__ void peer_wait_kernel(uint32_t * flags, int stride, uint32_t mask, unsigned long long timeout_ns, uint32_t * error) {
     if (!((mask >> threadIdx.x) & 1u)) return;
     uint32_t * f = flags + (size_t)threadIdx.x * stride;
     const unsigned long long t0 = globaltimer_ns();
     while (ld_acquire_sys(f) == 0u) {
         __nanosleep(40);
-        if (globaltimer_ns() - t0 > 2000000000ull) __trap();
+        if (timeout_ns && globaltimer_ns() - t0 > timeout_ns) {
+            if (!error) __trap();
+            *(volatile uint32_t *)error = 1u;
+            break;
+        }
     }
     *f = 0u;
     __threadfence_system();
@@ -76,7 +89,7 @@ __global__ void peer_wait_kernel(uint32_t * flags, int stride, uint32_t mask) {
 
 __global__ void peer_signal_kernel(uint32_t * remote_flag) {
     __threadfence_system();
-    st_release_sys(remote_flag, 1u);
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" :: "l"(remote_flag), "r"(1u) : "memory");
 }
 
 }  // namespace b200
@@ -101,12 +114,19 @@ extern "C" int b200_peer_bcast(const void * src, void * const * dsts, uint32_t *
     return 0;
 }
 
-extern "C" int b200_peer_wait(uint32_t * flags, int stride, uint32_t mask, void * stream) {
+extern "C" unsigned b200_peer_timeout_ms(void) {
+    static const unsigned v = [] { const char * e = getenv("B200_SPLIT_TIMEOUT_MS"); return e ? (unsigned)atol(e) : 30000u; }();
+    return v;
+}
+extern "C" int b200_peer_wait_ex(uint32_t * flags, int stride, uint32_t mask, unsigned timeout_ms, uint32_t * error, void * stream) {
     if (mask == 0) return 0;
-    peer_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(flags, stride, mask);
+    peer_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(flags, stride, mask, (unsigned long long)timeout_ms * 1000000ull, error);
     B200_CUDA_CHECK(cudaGetLastError());
     ++g_launches;
     return 0;
+}
+extern "C" int b200_peer_wait(uint32_t * flags, int stride, uint32_t mask, void * stream) {
+    return b200_peer_wait_ex(flags, stride, mask, b200_peer_timeout_ms(), nullptr, stream);
 }
 
 extern "C" int b200_peer_signal(uint32_t * remote_flag, void * stream) {

@@ -25,7 +25,10 @@ class MmvqArgs(C.Structure):
                 ("pf_n", C.c_int), ("pf_ptr", C.c_void_p * 3), ("pf_bytes", C.c_int64 * 3),
                 ("fuse_resid", C.c_void_p), ("fuse_sum", C.c_void_p),
                 ("norm_x", C.c_void_p), ("norm_w", C.c_void_p), ("norm_y", C.c_void_p), ("norm_out", C.c_void_p), ("norm_eps", C.c_float),
-                ("rope", C.c_void_p)]
+                ("rope", C.c_void_p),
+                ("hs_wait", C.c_void_p), ("hs_clear", C.c_void_p), ("hs_signal", C.c_void_p), ("hs_join", C.c_void_p),
+                ("hs_join_stride", C.c_int), ("hs_join_mask", C.c_uint32), ("hs_counter", C.c_void_p), ("hs_timeout_ms", C.c_uint),
+                ("hs_error", C.c_void_p)]
 
 
 _lib = None
@@ -60,7 +63,7 @@ EXPORTS = ["b200_flash_attn_xq_supported", "b200_op_flash_attn_ext_xq", "b200_fl
            "b200_mul_mat_supported", "b200_op_mul_mat_id", "b200_mul_mat_q", "b200_mul_mat_q_scratch_bytes",
            "b200_mul_mat_q_supported", "b200_mmq_debug_trace", "b200_acts_bf16_bytes",
            "b200_convert_acts_bf16", "b200_mul_mat_q_bf16", "b200_mul_mat_q_bf16_group", "b200_op_add_rms_norm_mul", "b200_op_unary_mul", "b200_op_rope_cpy_batch", "b200_op_rope_cpy_batch_check",
-           "b200_ktrace_enable", "b200_ktrace_dump", "b200_mmvq_fusable", "b200_mul_mat_q_noalloc"]
+           "b200_ktrace_enable", "b200_ktrace_dump", "b200_mmvq_fusable", "b200_mul_mat_q_noalloc", "b200_peer_wait_ex", "b200_peer_timeout_ms"]
 
 
 def _stream():

@@ -106,13 +106,18 @@ def test_logits_match_reference_cpu_backend(tmp_path, preset, fa, n_prompt):
         assert nmse(got[i], ref[i]) < bar, (i, nmse(got[i], ref[i]), bar)
 
 
-@pytest.mark.parametrize("mode,env", [("layer", {}), ("row", {}), ("row", {"B200_SPLIT_FLAGS": "0"}), ("row", {"B200_SPLIT_P2P": "0"}),
-                                      ("row", {"B200_CUDA_GRAPHS": "0"})])
+ALL = {"B200_SPLIT_MIN_MB": "0"}      # shard every matrix (the default leaves matrices below ~72 MB whole on the main device: most of a 1B model)
+
+
+@pytest.mark.parametrize("mode,env", [("layer", {}), ("row", {}), ("row", ALL), ("row", dict(ALL, B200_SPLIT_FOLD="0")), ("row", dict(ALL, B200_SPLIT_FLAGS="0")),
+                                      ("row", dict(ALL, B200_SPLIT_P2P="0")), ("row", dict(ALL, B200_CUDA_GRAPHS="0"))])
 def test_row_split_logits_equal_single_gpu(tmp_path, mode, env):
     """--split-mode layer / row over every visible B200 against the single-GPU run of the same model: prefill + 8 decode steps.
-    A weight row's dot product does not depend on which device holds it, so the logits must be bit-identical -- through the
-    flag hand-over in peer memory (default), the event fork/join (B200_SPLIT_FLAGS=0), the staged path without peer mappings
-    (B200_SPLIT_P2P=0) and without CUDA graphs.  The reference has no test for its split buffers: this is the pin."""
+    A weight row's dot product does not depend on which device holds it, so the logits must be bit-identical -- with the default
+    placement (small matrices whole on the main device), with every matrix sharded, through the flag hand-over folded into the
+    mat-vec kernels (default), as wait / signal launches (B200_SPLIT_FOLD=0), the event fork/join (B200_SPLIT_FLAGS=0), the staged
+    path without peer mappings (B200_SPLIT_P2P=0) and without CUDA graphs.  The reference has no test for its split buffers: this is
+    the pin."""
     import numpy as np
     import torch
     _need()

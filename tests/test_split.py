@@ -3,9 +3,11 @@
   * the shard geometry the plugin's split buffer type uses (ggml_backend_b200_split_rows) against the rule the
     reference states in get_row_split (ggml-cuda.cu:768-781): boundaries proportional to tensor_split, rounded
     down to 128 rows, the last device takes the remainder;
-  * the algorithm itself with two gloo ranks standing in for two devices: every rank multiplies its row shard
-    with the oracle's MMVQ restatement, the slices are gathered, and the result must equal the unsplit product
-    bit for bit (rows are independent: no reduction crosses the shard boundary).
+  * the algorithm itself with two gloo ranks standing in for two devices: every rank takes its row range from the PLUGIN's
+    geometry export, multiplies its shard, the slices are gathered, and the result must equal the unsplit product bit for bit
+    (rows are independent: no reduction crosses the shard boundary).  The shard product is the product code -- the CUDA mat-vec
+    through the C ABI (b200_mul_mat_vec_q) -- in the `gpu` variant (both ranks share cuda:0, so it runs on a one-GPU box too);
+    without a GPU the oracle's restatement stands in for the kernel and only the geometry + gather logic is product code.
 
 The reference holds no test for its split buffers ("parity unpinned by the reference"); the GPU side
 is pinned by tests/test_gpu_plugin.py::test_row_split_logits_equal_single_gpu on a multi-GPU box."""
@@ -69,7 +71,7 @@ def test_split_rows_geometry(n_rows, split):
             assert got[d + 1] == got[d]
 
 
-def _rank_main(rank, world, port, t, N, K, M, split, ret):
+def _rank_main(rank, world, port, t, N, K, M, split, ret, use_gpu=False):
     import torch.distributed as dist
     import oracle as O
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -79,11 +81,23 @@ def _rank_main(rank, world, port, t, N, K, M, split, ret):
     rng = np.random.default_rng(7)                                    # same seed on every rank: same W and X
     W = O.random_quant_bytes(t, N, K, rng)
     X = rng.standard_normal((M, K)).astype(np.float32)
-    rows = _split_rows_ref(N, split)
+    rows = _split_rows(_plugin(), N, split) if os.path.exists(PLUGIN) else _split_rows_ref(N, split)      # the plugin's own geometry
     r0, r1 = rows[rank], rows[rank + 1]
     rb = O.row_bytes(t, K)
     Wb = np.ascontiguousarray(W).reshape(N, rb)
-    mine = O.mul_mat_vec_q(t, Wb[r0:r1].copy(), X, r1 - r0, K, M) if r1 > r0 else np.zeros((M, 0), np.float32)
+
+    def product(Wrows, n):
+        if n == 0:
+            return np.zeros((M, 0), np.float32)
+        if use_gpu:                                                   # product code: the CUDA mat-vec through the C ABI
+            from llamacog_b200 import ops
+            Wd = torch.zeros(Wrows.size + 256, dtype=torch.uint8, device="cuda")
+            Wd[:Wrows.size] = torch.from_numpy(np.ascontiguousarray(Wrows).reshape(-1)).cuda()
+            out = ops.mul_mat_vec_q(t, Wd, torch.from_numpy(X).cuda(), n, K)
+            torch.cuda.synchronize()
+            return out.cpu().numpy()
+        return O.mul_mat_vec_q(t, Wrows.copy(), X, n, K, M)
+    mine = product(Wb[r0:r1], r1 - r0)
     # the gather: every rank contributes its [M, rows] slice (padded to the widest shard for all_gather)
     width = max(rows[d + 1] - rows[d] for d in range(world))
     pad = np.zeros((M, width), np.float32)
@@ -92,24 +106,38 @@ def _rank_main(rank, world, port, t, N, K, M, split, ret):
     dist.all_gather(parts, torch.from_numpy(pad))
     full = np.concatenate([parts[d].numpy()[:, :rows[d + 1] - rows[d]] for d in range(world)], axis=1)
     if rank == 0:
-        want = O.mul_mat_vec_q(t, Wb, X, N, K, M)
-        ret.put((bool(np.array_equal(full.view(np.uint32), want.view(np.uint32))), full.shape))
+        want = product(Wb, N)                                         # the unsplit product by the same code
+        ok = bool(np.array_equal(full.view(np.uint32), want.view(np.uint32)))
+        if use_gpu:                                                   # ... which itself is held to the oracle
+            ref = O.mul_mat_vec_q(t, Wb, X, N, K, M).astype(np.float64)
+            ok = ok and float(np.abs(want - ref).max()) <= 2e-5 * float(np.sqrt((ref ** 2).mean()) + 1e-30) * 4
+        ret.put((ok, full.shape))
     dist.barrier()
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("tname,N,K,M,split", [("q4_K", 384, 512, 1, [1.0, 1.0]), ("q6_K", 640, 256, 3, [3.0, 1.0]), ("q4_0", 256, 256, 2, [1.0, 0.0])])
-def test_row_sharded_matmul_two_ranks_gloo(tname, N, K, M, split):
+CASES = [("q4_K", 384, 512, 1, [1.0, 1.0]), ("q6_K", 640, 256, 3, [3.0, 1.0]), ("q4_0", 256, 256, 2, [1.0, 0.0])]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tname,N,K,M,split", CASES + [("q4_K", 4096, 4096, 1, [1.0, 1.0]), ("q5_K", 1024, 8192, 1, [1.0, 1.0])])
+def test_row_sharded_matmul_two_ranks_gloo_cuda_kernels(tname, N, K, M, split):
+    """The same with the CUDA mat-vec of the product as every rank's shard multiply (C ABI, both ranks on cuda:0)."""
+    test_row_sharded_matmul_two_ranks_gloo(tname, N, K, M, split, use_gpu=True)
+
+
+@pytest.mark.parametrize("tname,N,K,M,split", CASES)
+def test_row_sharded_matmul_two_ranks_gloo(tname, N, K, M, split, use_gpu=False):
     import torch.multiprocessing as mp
     import oracle as O
     t = O.TYPES[tname] if hasattr(O, "TYPES") else {"q4_0": 2, "q8_0": 8, "q4_K": 12, "q5_K": 13, "q6_K": 14}[tname]
     ctx = mp.get_context("spawn")
     ret = ctx.Queue()
     port = 29500 + (os.getpid() % 2000)
-    procs = [ctx.Process(target=_rank_main, args=(r, 2, port, t, N, K, M, split, ret)) for r in range(2)]
+    procs = [ctx.Process(target=_rank_main, args=(r, 2, port, t, N, K, M, split, ret, use_gpu)) for r in range(2)]
     for p in procs:
         p.start()
-    ok, shape = ret.get(timeout=120)
+    ok, shape = ret.get(timeout=300)
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
