@@ -381,6 +381,10 @@ def main():
         torch.cuda.set_device(local)
         # rank 0 spends minutes in the split arm while the others wait at a barrier: no 10-minute watchdog
         dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(hours=3))
+        # The long wait (rank 0 alone drives all GPUs through the split arm) must be a HOST-side wait: a rank parked in an NCCL
+        # barrier keeps a spinning kernel resident on its GPU, the split model's kernels on that GPU are then time-sliced against it
+        # and every device-to-device hand-over takes milliseconds (seen: the 30 s spin budget of a hand-over ran out).
+        cpu_group = dist.new_group(backend="gloo", timeout=datetime.timedelta(hours=3))
     if rank == 0:
         model = ensure_model()
     if world > 1:
@@ -451,6 +455,8 @@ def main():
                 line["split"] = {"error": str(e)[-600:]}
                 line["replicas"] = replicas
         sampler.stop_flag = True
+        if world > 1:
+            dist.barrier(group=cpu_group)
         if not args.no_roofline:
             try:
                 k = kernel_roofline(max(20, min(args.steps, 200)), args.warmup, local)
@@ -496,6 +502,9 @@ def main():
             except Exception as e:  # noqa: BLE001
                 line["cpu_baseline"] = {"error": str(e)[:200]}
         print(json.dumps(line), flush=True)
+    elif world > 1:
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu_group)            # parked on the host until rank 0 is through with the split arm
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -324,6 +324,39 @@ typedef struct b200_ew_desc {
 int b200_op_rope_cpy_batch(const b200_ew_desc * tasks, int n, void * stream);
 int b200_op_rope_cpy_batch_check(const b200_ew_desc * tasks, int n);      /* 0 when the batch would be accepted; launches nothing */
 
+/* ---- the mat-vec chain of a decode step as ONE persistent launch (csrc/dchain.cu) -----------------------------------------
+ * Between two attentions a batch-1 decode step of a Llama layer is
+ *     wo mat-vec (+ residual) -> RMS_NORM * w -> gate / up mat-vecs -> act(gate) * up -> down mat-vec (+ residual)
+ *     [ -> RMS_NORM * w -> up to two groups of mat-vecs on the same row: q / k / v of the next layer (rope + KV store), or lm_head ]
+ * which the reference runs as 12-14 kernels (ggml-cuda/ggml-cuda.cu:2150-2400: mul_mat_vec_q + quantize_q8_1 per MUL_MAT, norm.cu,
+ * binbcast.cu, unary.cu, rope.cu, cpy.cu).  Here the CTAs stay resident across the chain, the weight stream never stops at a node
+ * boundary and the phases hand over through counters in L2.  Every tensor gets the bits the node-by-node entry points of this
+ * header give it.  All weights Q4_K or Q6_K, K multiples of 256, norm rows <= 4096 floats, M = 1.
+ *   gemv.epi: 0 dst[n] = row sum; 1 also sum[n] = dst[n] + resid[n] (ng = 1); 2 rope / KV-cache store as b200_mmvq_args.rope */
+typedef struct b200_chain_gemv {
+    int type, ng, K, epi;
+    const void * W[3]; int N[3]; float * dst[3];
+    const float * resid; float * sum;
+    const struct b200_gemv_rope * rope;
+} b200_chain_gemv;
+typedef struct b200_chain_norm { const float * x; const float * w; float * y; float * out; float eps; int K; } b200_chain_norm;   /* y = rms_norm(x), out = y * w */
+typedef struct b200_chain_args {
+    b200_chain_gemv wo; const void * xq_attn;        /* xq_attn: the attention output as pre-quantised activations (b200_op_flash_attn_ext_xq) */
+    b200_chain_norm norm1;                           /* x = wo.sum */
+    b200_chain_gemv gate_up;                         /* ng = 2: dst[0] = gate, dst[1] = up (N[0] == N[1]) */
+    int act_op; float * act; float * act_out;        /* act = unary(gate) (B200_UNARY_SILU / _GELU), act_out = act * up */
+    void * xq_ffn;                                   /* scratch, b200_quantized_acts_bytes(N_ff, 1): act_out as the down projection reads it */
+    b200_chain_gemv down;                            /* K = N_ff, resid = wo.sum */
+    int tail;                                        /* 1: norm2 (x = down.sum) + t1 (+ t2 when t2.ng > 0, same activations) */
+    b200_chain_norm norm2;
+    b200_chain_gemv t1, t2;
+    uint32_t * barriers;                             /* 128 zeroed 32-bit words of device memory; shared by every chain launch of a stream (they leave it zeroed) */
+    uint32_t * error; unsigned timeout_ms;           /* bounded spins: *error = 2 on expiry (device-visible word, may be NULL), 0 = unbounded */
+    int pdl;                                         /* as b200_mmvq_args.pdl */
+} b200_chain_args;
+int b200_decode_chain_supported(const b200_chain_args * args);      /* host-side check only */
+int b200_decode_chain(const b200_chain_args * args, void * stream);
+
 /* number of kernels launched by this library so far in this process (bench.py gpu_launches) */
 int b200_kernel_launch_count(void);
 /* account for kernels launched through a replayed CUDA graph (the plugin captures decode steps) */

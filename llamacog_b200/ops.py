@@ -63,7 +63,7 @@ EXPORTS = ["b200_flash_attn_xq_supported", "b200_op_flash_attn_ext_xq", "b200_fl
            "b200_mul_mat_supported", "b200_op_mul_mat_id", "b200_mul_mat_q", "b200_mul_mat_q_scratch_bytes",
            "b200_mul_mat_q_supported", "b200_mmq_debug_trace", "b200_acts_bf16_bytes",
            "b200_convert_acts_bf16", "b200_mul_mat_q_bf16", "b200_mul_mat_q_bf16_group", "b200_op_add_rms_norm_mul", "b200_op_unary_mul", "b200_op_rope_cpy_batch", "b200_op_rope_cpy_batch_check",
-           "b200_ktrace_enable", "b200_ktrace_dump", "b200_mmvq_fusable", "b200_mul_mat_q_noalloc", "b200_peer_wait_ex", "b200_peer_timeout_ms"]
+           "b200_ktrace_enable", "b200_ktrace_dump", "b200_mmvq_fusable", "b200_mul_mat_q_noalloc", "b200_peer_wait_ex", "b200_peer_timeout_ms", "b200_decode_chain", "b200_decode_chain_supported"]
 
 
 def _stream():
