@@ -353,6 +353,7 @@ typedef struct b200_chain_args {
     uint32_t * barriers;                             /* 128 zeroed 32-bit words of device memory; shared by every chain launch of a stream (they leave it zeroed) */
     uint32_t * error; unsigned timeout_ms;           /* bounded spins: *error = 2 on expiry (device-visible word, may be NULL), 0 = unbounded */
     int pdl;                                         /* as b200_mmvq_args.pdl */
+    void * trace;                                    /* debug: 128 uint64 slots that receive %globaltimer stamps of the first and the last CTA (tools/chain_micro.py); NULL = off */
 } b200_chain_args;
 int b200_decode_chain_supported(const b200_chain_args * args);      /* host-side check only */
 int b200_decode_chain(const b200_chain_args * args, void * stream);

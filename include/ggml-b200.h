@@ -17,6 +17,11 @@
  *                                             ggml-cuda.cu:753-1084, :3476-3478; consumer src/llama-model.cpp:342-360).
  *                                             Weight rows are sharded over the devices in proportion to tensor_split,
  *                                             boundaries rounded down to 128 rows; MUL_MAT is the only op accepted on it.
+ *                                             Matrices too small for a cross-device hand-over to pay (below ~36 MB * n/(n-1),
+ *                                             B200_SPLIT_MIN_MB) stay whole on the main device.
+ *   "ggml_backend_register_host_buffer"    -> bool (*)(void * buffer, size_t size): pin a host range for DMA uploads
+ *   "ggml_backend_unregister_host_buffer"  -> void (*)(void * buffer)      (reference ggml-cuda.cu:2894-2927, :3480-3486; same
+ *                                             opt-in: only when GGML_CUDA_REGISTER_HOST or B200_REGISTER_HOST is set)
  */
 #ifndef GGML_B200_H
 #define GGML_B200_H

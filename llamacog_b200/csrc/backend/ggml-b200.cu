@@ -78,9 +78,60 @@ void buf_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, uint8
     B200_CHECK(cudaMemsetAsync((char *)tensor->data + offset, value, size, cudaStreamPerThread));
     B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
 }
+// ---- weight upload (reference set_tensor: one synchronous cudaMemcpyAsync from pageable memory per tensor,
+// ggml-cuda.cu:604-611) ----
+// The loader hands us pointers into the mmap'd GGUF (pageable, often not yet faulted in).  A pageable cudaMemcpy makes the driver
+// copy through its own small bounce buffers with the CPU copy and the DMA taking turns.  Here: two pinned staging buffers per device
+// and an upload stream; while the DMA engine drains one buffer the calling thread fills the other (that memcpy is also what faults
+// the file pages in), so disk/page-cache reads and PCIe transfers overlap.  Still synchronous at the interface: the call returns
+// when the last chunk has landed.  B200_STAGED_UPLOAD=0 restores the plain copy; B200_UPLOAD_CHUNK_MB sets the chunk (default 16).
+struct upload_lane {
+    std::mutex mu;
+    void * pin[2] = {nullptr, nullptr};
+    cudaEvent_t done[2] = {nullptr, nullptr};
+    cudaStream_t stream = nullptr;
+    size_t chunk = 0;
+    bool failed = false;
+};
+upload_lane g_upload[B200_MAX_DEVICES];
+std::atomic<long long> g_upload_bytes{0}, g_upload_us{0};
+
+bool staged_upload(int device, void * dst, const void * src, size_t size) {
+    static const bool on = [] { const char * e = getenv("B200_STAGED_UPLOAD"); return !e || atoi(e) != 0; }();
+    static const size_t chunk_mb = [] { const char * e = getenv("B200_UPLOAD_CHUNK_MB"); const long v = e ? atol(e) : 16; return (size_t)(v < 1 ? 1 : v > 256 ? 256 : v); }();
+    if (!on || size < (size_t)4 << 20 || device < 0 || device >= B200_MAX_DEVICES) return false;
+    upload_lane & L = g_upload[device];
+    std::lock_guard<std::mutex> lock(L.mu);
+    if (L.failed) return false;
+    if (!L.stream) {
+        L.chunk = chunk_mb << 20;
+        if (cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking) != cudaSuccess || cudaMallocHost(&L.pin[0], L.chunk) != cudaSuccess ||
+            cudaMallocHost(&L.pin[1], L.chunk) != cudaSuccess || cudaEventCreateWithFlags(&L.done[0], cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&L.done[1], cudaEventDisableTiming) != cudaSuccess) {
+            cudaGetLastError();
+            L.failed = true;      // no pinned memory to be had: the plain path still works
+            return false;
+        }
+    }
+    size_t off = 0;
+    int b = 0;
+    bool used[2] = {false, false};
+    while (off < size) {
+        const size_t n = size - off < L.chunk ? size - off : L.chunk;
+        if (used[b]) B200_CHECK(cudaEventSynchronize(L.done[b]));      // the DMA out of this buffer has finished
+        memcpy(L.pin[b], (const char *)src + off, n);
+        B200_CHECK(cudaMemcpyAsync((char *)dst + off, L.pin[b], n, cudaMemcpyHostToDevice, L.stream));
+        B200_CHECK(cudaEventRecord(L.done[b], L.stream));
+        used[b] = true;
+        off += n; b ^= 1;
+    }
+    B200_CHECK(cudaStreamSynchronize(L.stream));
+    return true;
+}
 void buf_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
     buf_ctx * c = (buf_ctx *)buffer->context;
     set_device(c->device);
+    if (staged_upload(c->device, (char *)tensor->data + offset, data, size)) return;
     B200_CHECK(cudaMemcpyAsync((char *)tensor->data + offset, data, size, cudaMemcpyHostToDevice, cudaStreamPerThread));
     B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
 }

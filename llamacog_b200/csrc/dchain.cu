@@ -54,7 +54,13 @@ struct chain_params {
     uint32_t * bars;                                     // CH_NBAR counters, 128 bytes apart, zero between launches
     uint32_t * error; unsigned long long timeout_ns;
     int nstages, stage_bytes, act_bytes, wn_bytes, rsd_rows, csn_rows;
+    unsigned long long * trace;                          // debug: globaltimer stamps of the first and the last CTA, 64 slots each (tools/chain_micro.py)
 };
+__device__ __forceinline__ void ch_stamp(const chain_params & p, int ev) {      // call from ONE thread of the warp
+    if (!p.trace || (blockIdx.x != 0 && blockIdx.x != gridDim.x - 1)) return;
+    unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.trace[(blockIdx.x ? 64 : 0) + ev] = t;
+}
 
 __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t * p) {
     uint32_t v; asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v;
@@ -184,6 +190,7 @@ __global__ void __launch_bounds__(288, 2) chain_kernel(const __grid_constant__ c
             for (int s = 0; s < c.nst; ++s, ++gs) {
                 const int slot = gs % p.nstages;
                 mbar_wait(empty0 + 8 * slot, (gs / p.nstages) & 1);
+                if (s == 0 && lane == 0) ch_stamp(p, 32 + 2 * ph);
                 if (s == 0 && q.epi == 1) {                // this CTA's rows of the residual (written before the barrier the consumers passed)
                     for (int o = lane; o < c.nrows; o += 32) rsd[o] = __ldcg(q.resid + c.row_lo + o);
                     __syncwarp();
@@ -225,6 +232,7 @@ __global__ void __launch_bounds__(288, 2) chain_kernel(const __grid_constant__ c
                 __syncwarp();
                 if (lane == 0) {
                     if (s == c.nst - 1 && q.arrive_bar >= 0) grid_arrive(p, q.arrive_bar);
+                    if (s == c.nst - 1) ch_stamp(p, 33 + 2 * ph);
                     issue_next();
                 }
             }
@@ -242,9 +250,10 @@ __global__ void __launch_bounds__(288, 2) chain_kernel(const __grid_constant__ c
         for (int ph = 0; ph < p.nph; ++ph) {
             const ch_gemv & q = p.ph[ph];
             const ph_cta c = phase_rows(q);
+            if (ct == 0 && ph == 0) ch_stamp(p, 0);
             if (q.silu_before) {
                 // ---- act = unary(g), out = act * u, quantised column of `out`: 32-blocks dealt round-robin to the CTAs, 8 threads each ----
-                if (ct == 0) grid_wait(p, p.silu_wait);
+                if (ct == 0) { grid_wait(p, p.silu_wait); ch_stamp(p, 28); }
                 asm volatile("bar.sync 1, 256;" ::: "memory");
                 const int nblk = p.sn >> 5, sub = ct & 7;
                 for (int base = 0; base < nblk; base += gridDim.x * 32) {      // (uniform trip count: quant_block_store shuffles over the full warp)
@@ -264,7 +273,7 @@ __global__ void __launch_bounds__(288, 2) chain_kernel(const __grid_constant__ c
                 }
                 __threadfence();
                 asm volatile("bar.sync 1, 256;" ::: "memory");
-                if (ct == 0) grid_arrive(p, p.silu_arrive);
+                if (ct == 0) { ch_stamp(p, 29); grid_arrive(p, p.silu_arrive); }
             }
             if (c.nst == 0 && !(q.pre == 1 && blockIdx.x == 0)) {      // nothing to multiply in this phase: only keep the barrier count right
                 if (ct == 0 && q.arrive_bar >= 0) grid_arrive(p, q.arrive_bar);
@@ -275,6 +284,7 @@ __global__ void __launch_bounds__(288, 2) chain_kernel(const __grid_constant__ c
                 if (ct == 0) {
                     if (q.wait_bar >= 0) grid_wait(p, q.wait_bar);
                     else if (first_read) pdl_wait();       // the column comes from the previous kernel
+                    ch_stamp(p, 1 + 4 * ph);
                     asm volatile("fence.proxy.async;" ::: "memory");
                     if (q.pre == 0) {
                         mbar_expect_tx(actbar, (uint32_t)q.BPR * ACT_ITEM);
@@ -343,11 +353,13 @@ __global__ void __launch_bounds__(288, 2) chain_kernel(const __grid_constant__ c
                 // the next phase's column may overwrite `act` only when every thread has its registers
                 asm volatile("bar.sync 1, 256;" ::: "memory");
             }
+            if (ct == 0) ch_stamp(p, 2 + 4 * ph);
             const uint32_t ioff = (uint32_t)b * (q.type == T_Q4_K ? (uint32_t)item_traits<T_Q4_K>::BYTES : (uint32_t)item_traits<T_Q6_K>::BYTES);
             for (int s = 0; s < c.nst; ++s, ++gs) {
                 const int slot = gs % p.nstages;
                 const int nr = min(q.R, c.nrows - s * q.R);
                 mbar_wait(full0 + 8 * slot, (gs / p.nstages) & 1);
+                if (s == 0 && ct == 0) ch_stamp(p, 3 + 4 * ph);
                 const uint32_t sbase = smem_u32(stages + (size_t)slot * p.stage_bytes) + ioff;
                 float * pw = partials + (size_t)slot * CH_PART;
                 if (q.type == T_Q4_K) chain_stage<T_Q4_K>(q, a, sbase, pw, nr, rsub, RPP, active, hh, NW, wir, red, lane);
@@ -355,6 +367,7 @@ __global__ void __launch_bounds__(288, 2) chain_kernel(const __grid_constant__ c
                 __syncwarp();
                 if (lane == 0) mbar_arrive(empty0 + 8 * slot);
             }
+            if (ct == 0) ch_stamp(p, 4 + 4 * ph);
         }
         if (w_issued > w_waited) mbar_wait(wbar, w_par);      // a CTA that sat out the last norm: no bulk copy may be in flight into shared memory when it exits
     }
@@ -508,6 +521,7 @@ int ch_build(const b200_chain_args * a, chain_params & p, dim3 * grid_out, size_
     }
     p.sg = a->gate_up.dst[0]; p.su = a->gate_up.dst[1]; p.sact = a->act; p.sout = a->act_out; p.sxq = (uint8_t *)a->xq_ffn; p.sn = a->gate_up.N[0]; p.sop = a->act_op;
     p.bars = a->barriers; p.error = a->error; p.timeout_ns = (unsigned long long)a->timeout_ms * 1000000ull;
+    p.trace = (unsigned long long *)a->trace;
     // shared memory
     const int act_bytes = round_up(std::max((act_k / 256) * ACT_ITEM, (a->norm1.K / 256) * ACT_ITEM + a->norm1.K * 4), 128);
     const int wn_bytes = round_up(a->norm1.K * 4, 128);

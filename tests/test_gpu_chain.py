@@ -40,7 +40,7 @@ class ChainArgs(C.Structure):
     _fields_ = [("wo", ChainGemv), ("xq_attn", C.c_void_p), ("norm1", ChainNorm), ("gate_up", ChainGemv), ("act_op", C.c_int),
                 ("act", C.c_void_p), ("act_out", C.c_void_p), ("xq_ffn", C.c_void_p), ("down", ChainGemv), ("tail", C.c_int),
                 ("norm2", ChainNorm), ("t1", ChainGemv), ("t2", ChainGemv), ("barriers", C.c_void_p), ("error", C.c_void_p),
-                ("timeout_ms", C.c_uint), ("pdl", C.c_int)]
+                ("timeout_ms", C.c_uint), ("pdl", C.c_int), ("trace", C.c_void_p)]
 
 
 def _ops():

@@ -47,3 +47,9 @@ def test_plugin_registry_without_gpu():
     name = C.CFUNCTYPE(C.c_char_p, C.c_void_p)(reg.contents.get_name)
     assert name(C.cast(reg, C.c_void_p)) == b"B200"
     assert lib.ggml_backend_init() and C.addressof(lib.ggml_backend_init().contents) == C.addressof(reg.contents)   # idempotent
+    # the names the host asks the registry for (reference ggml-cuda.cu:3474-3496): answered; anything else: NULL
+    proc = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_char_p)(reg.contents.get_proc_address)
+    for n in (b"ggml_backend_split_buffer_type", b"ggml_backend_get_features", b"ggml_backend_register_host_buffer",
+              b"ggml_backend_unregister_host_buffer"):
+        assert proc(C.cast(reg, C.c_void_p), n), n
+    assert not proc(C.cast(reg, C.c_void_p), b"ggml_backend_no_such_thing")
