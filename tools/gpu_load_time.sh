@@ -9,9 +9,9 @@ f=/tmp/b200_models/$m-q4_k_m.gguf
 ls -la $f
 for rep in 1 2; do
   for mode in 1 0; do
-    s=$(date +%s.%N)
+    s=$(date +%s%N)
     B200_STAGED_UPLOAD=$mode baseline/_ref/bin/llama-bench -m $f -ngl 99 -fa 1 -p 0 -n 1 -r 1 -t 4 > /dev/null 2>&1
-    e=$(date +%s.%N)
-    echo "rep $rep B200_STAGED_UPLOAD=$mode : $(echo "$e - $s" | bc) s wall (load + 2 tokens)"
+    e=$(date +%s%N)
+    echo "rep $rep B200_STAGED_UPLOAD=$mode : $(( (e - s) / 1000000 )) ms wall (process start, load, 2 tokens)"
   done
 done
