@@ -29,6 +29,9 @@ struct fa_params {
 };
 
 __device__ __forceinline__ uint32_t ldg_u16(const void * p) { return *reinterpret_cast<const unsigned short *>(p); }
+__device__ __forceinline__ uint2 lds64(uint32_t saddr) {
+    uint2 v; asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(saddr)); return v;
+}
 
 // dot product of one K row with Q (shared memory); D elements
 template <int KT, int D>
@@ -395,21 +398,32 @@ __global__ void __launch_bounds__(256) fattn_vec_stage_kernel(const fa_params p)
 // holds.  Here lane j still owns KV position j of a 32-position tile, but its K row is loaded once and dotted with all G
 // queries (Q in shared memory, broadcast reads), and every V row chunk is loaded once and accumulated into G outputs.
 // Query g of CTA x: flat index x * G + g over (row, head-in-group), row-major.
-template <int KT, int VT, int D, int G>
-__global__ void __launch_bounds__(128) fattn_vec_gqa_kernel(const fa_params p) {
+// STAGE (f16 cache, 16-byte aligned rows): the K rows of a warp's tile reach shared memory through cp.async, a row per 2D/16 lanes
+// (whole 128-byte lines per request instead of 32 scattered 16-byte pieces per load instruction), double buffered per warp so the
+// next tile is in flight while this one is multiplied; lane j then reads row j from padded shared-memory rows (conflict-free
+// LDS.128).  Same arithmetic in the same order as the direct form: results are bit-identical to it.
+// ncu (profiles/r02_fattn_gqa_32k_ncu.md): with K alone staged and V read straight from global memory the kernel ran at 1.67 TB/s
+// with 8 warps per SM, 28 % issue slots, stalled on the scoreboard: too few bytes in flight.  So V goes through the same
+// cp.async pipeline, a CTA is 6 warps that own a whole SM (one K + V tile of 16 KB in flight per warp while the previous one is
+// multiplied), and the per-warp combine buffers live in the staging memory once the tiles are done.
+template <int KT, int VT, int D, int G, bool STAGE = false>
+__global__ void __launch_bounds__(STAGE ? 192 : 128) fattn_vec_gqa_kernel(const fa_params p) {
     pdl_trigger(); pdl_wait();
-    constexpr int EV = D / 32, NW = 4;
+    constexpr int EV = D / 32, NW = STAGE ? 6 : 4, NT = 32 * NW;
+    constexpr int KROW = 2 * D + 16, VROW = 2 * D, TILEB = 32 * (KROW + VROW);
+    extern __shared__ __align__(128) uint8_t gqa_smem[];
     __shared__ __align__(16) float qf[G][D];
     __shared__ int qi[G][D / 4];
     __shared__ float qd[G][D / 32];
     __shared__ float wm[NW][G], wl[NW][G];
-    __shared__ float wacc[NW][G][D];
+    __shared__ float wacc_s[STAGE ? 1 : NW][STAGE ? 1 : G][STAGE ? 1 : D];
+    float (*wacc)[G][D] = STAGE ? reinterpret_cast<float (*)[G][D]>(gqa_smem) : reinterpret_cast<float (*)[G][D]>(&wacc_s[0][0][0]);
 
     const int ikv = blockIdx.y % (p.n_head / p.rk2), iq3 = blockIdx.y / (p.n_head / p.rk2), split = blockIdx.z;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int ngq = p.N * p.rk2;                                  // queries that share this KV head
     const int g0 = blockIdx.x * G;
-    for (int i = tid; i < G * D; i += 128) {
+    for (int i = tid; i < G * D; i += NT) {
         const int g = i / D, d = i % D, gq = g0 + g;
         float x = 0.0f;
         if (gq < ngq) x = reinterpret_cast<const float *>(p.q + (int64_t)(gq / p.rk2) * p.nbq1 + (int64_t)(ikv * p.rk2 + gq % p.rk2) * p.nbq2 + (int64_t)iq3 * p.nbq3)[d];
@@ -449,12 +463,57 @@ __global__ void __launch_bounds__(128) fattn_vec_gqa_kernel(const fa_params p) {
     }
     const int ntiles = (p.n_kv + 31) / 32;
     const int t0 = split * p.tiles_per_split, t1 = min(ntiles, t0 + p.tiles_per_split);
-    for (int t = t0 + warp; t < t1; t += NW) {
+    constexpr int LPR = 2 * D / 16, RPI = 32 / LPR, NI = 32 / RPI;      // lanes per row, rows per instruction, instructions per tile
+    uint8_t * kbuf = gqa_smem + (size_t)warp * 2 * TILEB;      // per warp: two tiles of (32 padded K rows, 32 V rows)
+    auto prefetch = [&](int t, int b) {
+        if constexpr (STAGE) {
+            const int nvalid = min(32, p.n_kv - 32 * t);
+#pragma unroll
+            for (int i = 0; i < NI; ++i) {
+                const int r = RPI * i + lane / LPR;
+                if (r < nvalid) {
+                    const uint32_t dk = smem_u32(kbuf + (size_t)b * TILEB + r * KROW + 16 * (lane % LPR));
+                    const uint32_t dv = smem_u32(kbuf + (size_t)b * TILEB + 32 * KROW + r * VROW + 16 * (lane % LPR));
+                    const char * sk = kbase + (int64_t)(32 * t + r) * p.nbk1 + 16 * (lane % LPR);
+                    const char * sv = vbase + (int64_t)(32 * t + r) * p.nbv1 + 16 * (lane % LPR);
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dk), "l"(sk) : "memory");
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dv), "l"(sv) : "memory");
+                }
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        }
+    };
+    int kb = 0;
+    if (t0 + warp < t1) prefetch(t0 + warp, 0);
+    for (int t = t0 + warp; t < t1; t += NW, kb ^= 1) {
         const int ic = 32 * t + lane;
         float s[G];
 #pragma unroll
         for (int g = 0; g < G; ++g) s[g] = 0.0f;
         const bool in = ic < p.n_kv;
+        if constexpr (STAGE) {
+            __syncwarp();                               // every lane is through with the tile whose buffer the next copy overwrites
+            if (t + NW < t1) { prefetch(t + NW, kb ^ 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+            else asm volatile("cp.async.wait_group 0;" ::: "memory");
+            __syncwarp();
+            if (in) {
+                const uint32_t kr = smem_u32(kbuf + (size_t)kb * TILEB + lane * KROW);
+#pragma unroll 4
+                for (int i = 0; i < D / 8; ++i) {
+                    const int4 u = lds128(kr + 16 * i);
+                    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+                    const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&u.z)), d = __half22float2(*reinterpret_cast<const __half2 *>(&u.w));
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        const float4 q0 = *reinterpret_cast<const float4 *>(&qf[g][8 * i]), q1 = *reinterpret_cast<const float4 *>(&qf[g][8 * i + 4]);
+                        float x = s[g];
+                        x = fmaf(a.x, q0.x, x); x = fmaf(a.y, q0.y, x); x = fmaf(b.x, q0.z, x); x = fmaf(b.y, q0.w, x);
+                        x = fmaf(c.x, q1.x, x); x = fmaf(c.y, q1.y, x); x = fmaf(d.x, q1.z, x); x = fmaf(d.y, q1.w, x);
+                        s[g] = x;
+                    }
+                }
+            }
+        } else
         if (in) {
             const char * krow = kbase + (int64_t)ic * p.nbk1;
             if constexpr (KT == T_F16) {
@@ -520,7 +579,18 @@ __global__ void __launch_bounds__(128) fattn_vec_gqa_kernel(const fa_params p) {
         auto vstep = [&](int j) {
             float vv[EV];
             const char * vrow = vbase + (int64_t)(32 * t + j) * p.nbv1;
-            if constexpr (VT == T_F16) {
+            if constexpr (STAGE) {
+                const uint32_t vr = smem_u32(kbuf + (size_t)kb * TILEB + 32 * KROW + j * VROW) + 2 * EV * lane;
+                if constexpr (EV == 4) {
+                    const uint2 u = lds64(vr);
+                    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+                    vv[0] = a.x; vv[1] = a.y; vv[2] = b.x; vv[3] = b.y;
+                } else {
+                    const uint32_t u = lds32(vr);
+                    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u));
+                    vv[0] = a.x; vv[1] = a.y;
+                }
+            } else if constexpr (VT == T_F16) {
                 const __half * vp = reinterpret_cast<const __half *>(vrow) + EV * lane;
                 if constexpr (EV == 4) {
                     const uint2 u = __ldg(reinterpret_cast<const uint2 *>(vp));
@@ -555,7 +625,8 @@ __global__ void __launch_bounds__(128) fattn_vec_gqa_kernel(const fa_params p) {
         }
     }
 
-    // combine the four warps, one query at a time
+    // combine the warps, one query at a time
+    if constexpr (STAGE) __syncthreads();             // the combine buffers take the place of the staged tiles
 #pragma unroll
     for (int g = 0; g < G; ++g) {
         if (lane == 0) { wm[warp][g] = M[g]; wl[warp][g] = L[g]; }
@@ -563,7 +634,7 @@ __global__ void __launch_bounds__(128) fattn_vec_gqa_kernel(const fa_params p) {
         for (int e = 0; e < EV; ++e) wacc[warp][g][EV * lane + e] = acc[g][e];
     }
     __syncthreads();
-    for (int i = tid; i < G * D; i += 128) {
+    for (int i = tid; i < G * D; i += NT) {
         const int g = i / D, d = i % D, gq = g0 + g;
         if (gq >= ngq) continue;
         float Mc = wm[0][g];
@@ -674,15 +745,37 @@ static int fa_launch_stage(const fa_params & p, dim3 grid, cudaStream_t st) {
 }
 static int fa_stage_on() { static const int v = [] { const char * e = getenv("B200_FATTN_STAGE"); return e ? atoi(e) : 1; }();  return v; }
 
+// off by default: measured SLOWER than the direct form (32k context, 32/8 heads: 0.132 vs 0.119 ms per call).  The ncu capture
+// (profiles/r02_fattn_gqa_32k_ncu.md) shows why staging cannot help: DRAM traffic already equals the cache bytes and the kernel
+// issues 2900 warp instructions per 16 KB tile (0.18 per byte) -- at 44 KB/us per SM that would need 4.1 IPC.  It is bound by its
+// scalar FMA / LDS stream, not by how K arrives; the way on is QK^T and PV on mma tiles (G queries x 32 positions), not staging.
+static int fa_gqa_stage_on() { static const int v = [] { const char * e = getenv("B200_FATTN_GQA_STAGE"); return e ? atoi(e) : 0; }();  return v; }
 template <int KT, int VT, int D, int G>
-static int fa_launch_gqa(const fa_params & p, dim3 grid, cudaStream_t st) {
+static int fa_launch_gqa(const fa_params & p, dim3 grid, cudaStream_t st, bool want_stage) {
     cudaLaunchConfig_t lc = {};
     lc.gridDim = grid; lc.blockDim = dim3(128); lc.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
-    B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_vec_gqa_kernel<KT, VT, D, G>, p));
+    bool staged = false;
+    if constexpr (KT == T_F16) {
+        if (want_stage) {                 // K and V tiles through cp.async + shared memory (f16 rows are 16-byte aligned: checked by the caller)
+            constexpr size_t smem = 6 * 2 * 32 * (size_t)(2 * D + 16 + 2 * D);
+            static int attr_set[16] = {0};   // per device
+            int dev = 0;
+            B200_CUDA_CHECK(cudaGetDevice(&dev));
+            if (dev < 16 && !attr_set[dev]) {
+                B200_CUDA_CHECK(cudaFuncSetAttribute(fattn_vec_gqa_kernel<KT, VT, D, G, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                attr_set[dev] = 1;
+            }
+            lc.dynamicSmemBytes = smem; lc.blockDim = dim3(192);
+            B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_vec_gqa_kernel<KT, VT, D, G, true>, p));
+            lc.dynamicSmemBytes = 0; lc.blockDim = dim3(128);
+            staged = true;
+        }
+    }
+    if (!staged) B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_vec_gqa_kernel<KT, VT, D, G>, p));
     ++g_launches;
     if (p.nsplit > 1) {
         const int64_t nrows = (int64_t)p.N * p.n_head * p.ne3;
@@ -787,7 +880,11 @@ extern "C" int b200_op_flash_attn_ext_xq(const b200_tensor * q, const b200_tenso
         const int G = ngq <= 4 ? 4 : 8;
         const int nx = (ngq + G - 1) / G;
         const int64_t ctas = (int64_t)nx * (q->ne[2] / p.rk2) * q->ne[3];
-        int ns = (int)std::min<int64_t>(std::max<int64_t>(1, (4 * 148 + ctas - 1) / ctas), std::max(1, ntiles / 4));
+        // f16 cache at long context: the staged form, CTAs of 6 warps that own an SM each, one wave of them
+        static const int stage_min_kv = [] { const char * e = getenv("B200_FATTN_GQA_STAGE_MIN_KV"); return e ? atoi(e) : 4096; }();
+        const bool staged = k->type == T_F16 && fa_gqa_stage_on() && p.n_kv >= stage_min_kv;
+        int ns = staged ? (int)std::min<int64_t>(std::max<int64_t>(1, (148 + ctas - 1) / ctas), std::max(1, ntiles / 12))
+                        : (int)std::min<int64_t>(std::max<int64_t>(1, (4 * 148 + ctas - 1) / ctas), std::max(1, ntiles / 4));
         ns = std::max(1, std::min(ns, 128));
         if (ns > 1 && (!scratch || scratch_bytes < rows_heads * ns * (2 + q->ne[0]) * 4)) ns = 1;
         if (xq && ns == 1) return -1;              // (the grouped kernel writes activations through the combine kernel only)
@@ -799,11 +896,11 @@ extern "C" int b200_op_flash_attn_ext_xq(const b200_tensor * q, const b200_tenso
         const int D = (int)q->ne[0];
         const bool f16 = k->type == T_F16;
         if (G == 4) {
-            if (D == 128) return f16 ? fa_launch_gqa<T_F16, T_F16, 128, 4>(p, grid, st) : fa_launch_gqa<T_Q8_0, T_Q8_0, 128, 4>(p, grid, st);
-            return f16 ? fa_launch_gqa<T_F16, T_F16, 64, 4>(p, grid, st) : fa_launch_gqa<T_Q8_0, T_Q8_0, 64, 4>(p, grid, st);
+            if (D == 128) return f16 ? fa_launch_gqa<T_F16, T_F16, 128, 4>(p, grid, st, staged) : fa_launch_gqa<T_Q8_0, T_Q8_0, 128, 4>(p, grid, st, false);
+            return f16 ? fa_launch_gqa<T_F16, T_F16, 64, 4>(p, grid, st, staged) : fa_launch_gqa<T_Q8_0, T_Q8_0, 64, 4>(p, grid, st, false);
         }
-        if (D == 128) return f16 ? fa_launch_gqa<T_F16, T_F16, 128, 8>(p, grid, st) : fa_launch_gqa<T_Q8_0, T_Q8_0, 128, 8>(p, grid, st);
-        return f16 ? fa_launch_gqa<T_F16, T_F16, 64, 8>(p, grid, st) : fa_launch_gqa<T_Q8_0, T_Q8_0, 64, 8>(p, grid, st);
+        if (D == 128) return f16 ? fa_launch_gqa<T_F16, T_F16, 128, 8>(p, grid, st, staged) : fa_launch_gqa<T_Q8_0, T_Q8_0, 128, 8>(p, grid, st, false);
+        return f16 ? fa_launch_gqa<T_F16, T_F16, 64, 8>(p, grid, st, staged) : fa_launch_gqa<T_Q8_0, T_Q8_0, 64, 8>(p, grid, st, false);
     }
     p.nsplit = fa_splits(rows_heads, ntiles);
     if (p.nsplit > 1 && (!scratch || scratch_bytes < rows_heads * p.nsplit * (2 + q->ne[0]) * 4)) p.nsplit = 1;

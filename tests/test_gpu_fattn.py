@@ -57,6 +57,39 @@ def test_causal_gqa(D, N, n_kv, n_past):
     assert _nmse(out, _ref(q, k, v, mask, scale)) < 1e-5
 
 
+@pytest.mark.parametrize("cache", ["f16", "q8_0"])
+@pytest.mark.parametrize("N,n_kv,n_head,n_head_kv", [(1, 32768, 32, 8), (1, 32768, 8, 1), (3, 32768, 8, 4), (1, 28672 + 129, 32, 8), (8, 16384, 8, 2)])
+def test_decode_at_32k_context(cache, N, n_kv, n_head, n_head_kv):
+    """Config 3 of BASELINE.json (32k context): the grouped split-KV decode kernel (K tiles staged through cp.async for an f16 cache,
+    up to 128 KV splits + combine) on the shapes of Llama-3-8B and on groups of 8 / 2 queries per KV head, f16 and q8_0 cache,
+    against the fp32 reference on the values the cache really holds."""
+    import numpy as np
+    import oracle as O
+    D = 128
+    torch.manual_seed(n_kv + N)
+    q = torch.randn(1, n_head, N, D, device="cuda")
+    kf = torch.randn(1, n_head_kv, n_kv, D); vf = torch.randn(1, n_head_kv, n_kv, D)
+    mask = torch.full(((N + 63) // 64 * 64, (n_kv + 255) // 256 * 256), float("-inf"), dtype=torch.float16, device="cuda")
+    for i in range(N):
+        mask[i, : n_kv - N + i + 1] = 0
+    scale = 1.0 / math.sqrt(D)
+    if cache == "f16":
+        k = kf.half().cuda(); v = vf.half().cuda()
+        out = _ops().flash_attn_ext(q, k, v, mask, scale)
+        ref = _ref(q, k, v, mask, scale)
+        bar = 1e-5
+    else:
+        t = O.QUANT_TYPES["q8_0"]
+        kq = O.quantize_row_q8_0_ref(kf.numpy().reshape(-1)); vq = O.quantize_row_q8_0_ref(vf.numpy().reshape(-1))
+        kd = torch.from_numpy(O.dequantize(t, kq, n_head_kv * n_kv, D)).reshape(1, n_head_kv, n_kv, D).cuda()
+        vd = torch.from_numpy(O.dequantize(t, vq, n_head_kv * n_kv, D)).reshape(1, n_head_kv, n_kv, D).cuda()
+        k8 = torch.from_numpy(kq).reshape(1, n_head_kv, n_kv, D // 32 * 34).cuda(); v8 = torch.from_numpy(vq).reshape(1, n_head_kv, n_kv, D // 32 * 34).cuda()
+        out = _ops().flash_attn_ext(q, k8, v8, mask, scale)
+        ref = _ref(q, kd, vd, mask, scale)
+        bar = 5e-4                      # Q is quantised to int8 for the q8_0 K dot (as the reference does): the op's own bar
+    assert _nmse(out, ref) < bar, _nmse(out, ref)
+
+
 @pytest.mark.parametrize("N", [4, 48, 256])
 def test_no_mask_softcap_and_batch(N):
     torch.manual_seed(N)
