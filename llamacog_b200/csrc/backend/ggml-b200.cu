@@ -61,9 +61,11 @@ void set_device(int device) {
 // ------------------------------------------------------------------------------------------------
 struct buf_ctx { int device; void * base; };
 
+void upload_fence(int device, cudaStream_t stream, bool host_wait);
 void buf_free(ggml_backend_buffer_t buffer) {
     buf_ctx * c = (buf_ctx *)buffer->context;
     set_device(c->device);
+    upload_fence(c->device, nullptr, true);
     cudaFree(c->base);
     delete c;
 }
@@ -72,9 +74,11 @@ enum ggml_status buf_init_tensor(ggml_backend_buffer_t buffer, ggml_tensor * ten
     (void)buffer; (void)tensor;      // no extras: kernels read GGUF blocks in place; rows are never over-read
     return GGML_STATUS_SUCCESS;
 }
+void upload_fence(int device, cudaStream_t stream, bool host_wait);
 void buf_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, uint8_t value, size_t offset, size_t size) {
     buf_ctx * c = (buf_ctx *)buffer->context;
     set_device(c->device);
+    upload_fence(c->device, nullptr, true);
     B200_CHECK(cudaMemsetAsync((char *)tensor->data + offset, value, size, cudaStreamPerThread));
     B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
 }
@@ -128,9 +132,44 @@ bool staged_upload(int device, void * dst, const void * src, size_t size) {
     B200_CHECK(cudaStreamSynchronize(L.stream));
     return true;
 }
+// Small uploads (the token ids, positions and the mask of every decode step: 3-5 set_tensor calls per token) need not wait for
+// their DMA.  A copy from pageable memory returns once the driver has taken the bytes into its own staging area -- the caller's
+// buffer is free, which is all "synchronous" means to the caller -- so the stream synchronisation that followed it (10-20 us each,
+// with the GPU idle) is replaced by ordering: the copies go to one upload stream per device, and whatever touches the device next
+// on a backend stream or reads a tensor back first waits for that stream's last event (upload_fence).  B200_ASYNC_SMALL_UPLOAD=0
+// restores the synchronising copy.
+struct small_lane { std::mutex mu; cudaStream_t stream = nullptr; cudaEvent_t ev = nullptr; std::atomic<bool> pending{false}; bool failed = false; };
+small_lane g_small[B200_MAX_DEVICES];
+bool small_upload(int device, void * dst, const void * src, size_t size) {
+    static const bool on = [] { const char * e = getenv("B200_ASYNC_SMALL_UPLOAD"); return !e || atoi(e) != 0; }();
+    if (!on || size > ((size_t)256 << 10) || device < 0 || device >= B200_MAX_DEVICES) return false;
+    small_lane & L = g_small[device];
+    std::lock_guard<std::mutex> lock(L.mu);
+    if (L.failed) return false;
+    if (!L.stream) {
+        if (cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&L.ev, cudaEventDisableTiming) != cudaSuccess) {
+            cudaGetLastError(); L.failed = true; return false;
+        }
+    }
+    B200_CHECK(cudaMemcpyAsync(dst, src, size, cudaMemcpyHostToDevice, L.stream));      // pageable source: staged by the driver before this returns
+    B200_CHECK(cudaEventRecord(L.ev, L.stream));
+    L.pending.store(true, std::memory_order_release);
+    return true;
+}
+// make `stream` (nullptr: the calling host thread) wait for the uploads still in flight to this device
+void upload_fence(int device, cudaStream_t stream, bool host_wait) {
+    if (device < 0 || device >= B200_MAX_DEVICES) return;
+    small_lane & L = g_small[device];
+    if (!L.pending.load(std::memory_order_acquire)) return;
+    std::lock_guard<std::mutex> lock(L.mu);
+    if (host_wait) { B200_CHECK(cudaEventSynchronize(L.ev)); L.pending.store(false, std::memory_order_release); }
+    else B200_CHECK(cudaStreamWaitEvent(stream, L.ev, 0));
+}
 void buf_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
     buf_ctx * c = (buf_ctx *)buffer->context;
     set_device(c->device);
+    if (small_upload(c->device, (char *)tensor->data + offset, data, size)) return;
+    upload_fence(c->device, nullptr, true);
     if (staged_upload(c->device, (char *)tensor->data + offset, data, size)) return;
     B200_CHECK(cudaMemcpyAsync((char *)tensor->data + offset, data, size, cudaMemcpyHostToDevice, cudaStreamPerThread));
     B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
@@ -138,6 +177,7 @@ void buf_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const vo
 void buf_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
     buf_ctx * c = (buf_ctx *)buffer->context;
     set_device(c->device);
+    upload_fence(c->device, nullptr, true);
     B200_CHECK(cudaMemcpyAsync(data, (const char *)tensor->data + offset, size, cudaMemcpyDeviceToHost, cudaStreamPerThread));
     B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
 }
@@ -146,7 +186,9 @@ bool buf_cpy_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * src, ggml_
     if (!src->buffer || !buffer_is_b200(src->buffer)) return false;
     buf_ctx * sc = (buf_ctx *)src->buffer->context;
     buf_ctx * dc = (buf_ctx *)buffer->context;
+    upload_fence(sc->device, nullptr, true);
     set_device(dc->device);
+    upload_fence(dc->device, nullptr, true);
     if (sc->device == dc->device) {
         B200_CHECK(cudaMemcpyAsync(dst->data, src->data, ggml_nbytes(src), cudaMemcpyDeviceToDevice, cudaStreamPerThread));
     } else {
@@ -158,6 +200,7 @@ bool buf_cpy_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * src, ggml_
 void buf_clear(ggml_backend_buffer_t buffer, uint8_t value) {
     buf_ctx * c = (buf_ctx *)buffer->context;
     set_device(c->device);
+    upload_fence(c->device, nullptr, true);
     B200_CHECK(cudaMemsetAsync(c->base, value, buffer->size, cudaStreamPerThread));
     B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
 }
