@@ -301,38 +301,47 @@ __global__ void __launch_bounds__(288, 2) chain_kernel(const __grid_constant__ c
                     const ch_norm & nm = p.norms[q.norm];
                     const float * xs = reinterpret_cast<const float *>(act + (size_t)q.BPR * ACT_ITEM);
                     const int n4 = nm.K >> 2;
-                    float4 wv[4], v[4];
                     mbar_wait(wbar, w_par); w_par ^= 1; ++w_waited;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) if (ct + 256 * k < n4) wv[k] = reinterpret_cast<const float4 *>(wn)[ct + 256 * k];
                     mbar_wait(actbar, act_par); act_par ^= 1;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) if (ct + 256 * k < n4) v[k] = reinterpret_cast<const float4 *>(xs)[ct + 256 * k];
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        if (ct + 256 * k < n4) {
-                            float sq = 0.0f;
-                            sq += sumsq4(v[k]);
-                            sq = warp_sum(sq);
+                    if (ct == 0) ch_stamp(p, 44 + 4 * q.norm);
+#pragma unroll 1
+                    for (int k = 0; k < 4; ++k) {                                  // rolled: see mmvq_r.cuh (cold instruction cache)
+                        const int i = ct + 256 * k;
+                        if (i < n4) {
+                            const float sq = warp_sum(sumsq4(reinterpret_cast<const float4 *>(xs)[i]));
                             if (lane == 0) npart[8 * k + cw] = sq;
                         }
                     }
                     asm volatile("bar.sync 1, 256;" ::: "memory");
+                    if (ct == 0) ch_stamp(p, 45 + 4 * q.norm);
                     float tot = 0.0f;
+#pragma unroll 4
                     for (int wi = 0; wi < (n4 >> 5); ++wi) tot += npart[wi];
                     const float scale = rms_scale(tot, nm.K, nm.eps);
                     const bool writer = blockIdx.x == 0;
+#pragma unroll 1
+                    for (int k = 0; k < 4; k += 2) {                        // two blocks per pass: their dependent chains overlap, the code stays small
+                        float4 y[2];
+                        int jb[2];
+                        bool in[2];
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const int i = ct + 256 * k;
-                        if (i < n4) {
-                            const float4 nv = make_float4(v[k].x * scale, v[k].y * scale, v[k].z * scale, v[k].w * scale);
-                            const float4 y = make_float4(nv.x * wv[k].x, nv.y * wv[k].y, nv.z * wv[k].z, nv.w * wv[k].w);
-                            if (writer) { reinterpret_cast<float4 *>(nm.y)[i] = nv; reinterpret_cast<float4 *>(nm.out)[i] = y; }
-                            quant_block_store(y, i >> 3, ct & 7, true, act);
+                        for (int u = 0; u < 2; ++u) {
+                            const int i = ct + 256 * (k + u);
+                            in[u] = i < n4;
+                            jb[u] = in[u] ? i >> 3 : 0;
+                            y[u] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                            if (in[u]) {
+                                const float4 v = reinterpret_cast<const float4 *>(xs)[i], wv = reinterpret_cast<const float4 *>(wn)[i];
+                                const float4 nv = make_float4(v.x * scale, v.y * scale, v.z * scale, v.w * scale);
+                                y[u] = make_float4(nv.x * wv.x, nv.y * wv.y, nv.z * wv.z, nv.w * wv.w);
+                                if (writer) { reinterpret_cast<float4 *>(nm.y)[i] = nv; reinterpret_cast<float4 *>(nm.out)[i] = y[u]; }
+                            }
                         }
+                        quant_block_store_n<2>(y, jb, ct & 7, in, act);
                     }
+                    if (ct == 0) ch_stamp(p, 46 + 4 * q.norm);
                     asm volatile("bar.sync 1, 256;" ::: "memory");
+                    if (ct == 0) ch_stamp(p, 47 + 4 * q.norm);
                     ++norms_done;
                     if (norms_done < 2 && p.norms[norms_done].x) ++w_issued;
                     if (ct == 0 && norms_done < 2 && p.norms[norms_done].x) {      // the weights of the next norm take this one's place

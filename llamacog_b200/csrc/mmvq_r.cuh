@@ -293,39 +293,46 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
             // are the same)
             const int n4 = p.K >> 2;
             const int cw = warp - 1;
-            float4 wv[4], v[4];
+            // Rolled loops on purpose: this code runs once per launch out of a cold instruction cache while the weight copies
+            // saturate L2, so its cost is its SIZE (the unrolled form, 1600 instructions between the two barriers, took 7 us;
+            // see profiles/r02_norm_prologue.md); the row and the weights are re-read from shared memory instead of kept in registers.
             mbar_wait(wbar, 0);                     // norm weights: copied before the PDL wait
-#pragma unroll
-            for (int k = 0; k < 4; ++k) if (ct + 256 * k < n4) wv[k] = reinterpret_cast<const float4 *>(ws)[ct + 256 * k];
             mbar_wait(actbar, 0);                   // the row is in shared memory (copied after the producer's PDL wait)
             ktrace_event(4, 32);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) if (ct + 256 * k < n4) v[k] = reinterpret_cast<const float4 *>(xs)[ct + 256 * k];
-#pragma unroll
+#pragma unroll 1
             for (int k = 0; k < 4; ++k) {
-                if (ct + 256 * k < n4) {
-                    float sq = 0.0f;
-                    sq += sumsq4(v[k]);
-                    sq = warp_sum(sq);
+                const int i = ct + 256 * k;
+                if (i < n4) {
+                    const float sq = warp_sum(sumsq4(reinterpret_cast<const float4 *>(xs)[i]));
                     if (lane == 0) npart[8 * k + cw] = sq;
                 }
             }
             ktrace_event(5, 32);
             asm volatile("bar.sync 1, 256;" ::: "memory");
             float tot = 0.0f;
+#pragma unroll 4
             for (int wi = 0; wi < (n4 >> 5); ++wi) tot += npart[wi];
             const float scale = rms_scale(tot, p.K, p.neps);
             const bool writer = blockIdx.x == 0;
+#pragma unroll 1
+            for (int k = 0; k < 4; k += 2) {                        // two blocks per pass: their dependent chains overlap, the code stays small
+                float4 y[2];
+                int jb[2];
+                bool in[2];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const int i = ct + 256 * k;
-                if (i < n4) {
-                    const float4 nv = make_float4(v[k].x * scale, v[k].y * scale, v[k].z * scale, v[k].w * scale);
-                    const float4 y = make_float4(nv.x * wv[k].x, nv.y * wv[k].y, nv.z * wv[k].z, nv.w * wv[k].w);
-                    if (writer) { reinterpret_cast<float4 *>(p.nnorm)[i] = nv; reinterpret_cast<float4 *>(p.nout)[i] = y; }
-                    quant_block_store(y, i >> 3, ct & 7, true, act);
-                    if (writer && p.nxq) quant_block_store(y, i >> 3, ct & 7, true, p.nxq);
+                for (int u = 0; u < 2; ++u) {
+                    const int i = ct + 256 * (k + u);
+                    in[u] = i < n4;
+                    jb[u] = in[u] ? i >> 3 : 0;
+                    y[u] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                    if (in[u]) {
+                        const float4 v = reinterpret_cast<const float4 *>(xs)[i], wv = reinterpret_cast<const float4 *>(ws)[i];
+                        const float4 nv = make_float4(v.x * scale, v.y * scale, v.z * scale, v.w * scale);
+                        y[u] = make_float4(nv.x * wv.x, nv.y * wv.y, nv.z * wv.z, nv.w * wv.w);
+                        if (writer) { reinterpret_cast<float4 *>(p.nnorm)[i] = nv; reinterpret_cast<float4 *>(p.nout)[i] = y[u]; }
+                    }
                 }
+                quant_block_store_n<2>(y, jb, ct & 7, in, act, writer ? p.nxq : nullptr);
             }
             asm volatile("bar.sync 1, 256;" ::: "memory");
             ktrace_event(6, 32);

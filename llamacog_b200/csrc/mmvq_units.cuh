@@ -237,22 +237,32 @@ __device__ __forceinline__ int q8_round(float x, float d, float inv, bool exact_
     if (exact_only || !(fabsf(u) <= 0.4999f)) return (int)roundf(__fdiv_rn(x, d));
     return __float_as_int(fm) - 0x4B400000;
 }
+// The same decision for the four elements of a lane with ONE branch: the fast roundings are straight-line code (sixteen of them
+// interleave freely in quant_block_store_n), the exact division runs only when one of the four asks for it (about 1 lane in 1000).
+__device__ __forceinline__ int q8_round4(const float4 x, float d, float inv, bool exact_only) {
+    const float r0 = x.x * inv, r1 = x.y * inv, r2 = x.z * inv, r3 = x.w * inv;
+    const float f0 = r0 + 12582912.0f, f1 = r1 + 12582912.0f, f2 = r2 + 12582912.0f, f3 = r3 + 12582912.0f;
+    const float u0 = r0 - (f0 - 12582912.0f), u1 = r1 - (f1 - 12582912.0f), u2 = r2 - (f2 - 12582912.0f), u3 = r3 - (f3 - 12582912.0f);
+    int q0 = __float_as_int(f0) - 0x4B400000, q1 = __float_as_int(f1) - 0x4B400000;
+    int q2 = __float_as_int(f2) - 0x4B400000, q3 = __float_as_int(f3) - 0x4B400000;
+    const bool ok = fabsf(u0) <= 0.4999f && fabsf(u1) <= 0.4999f && fabsf(u2) <= 0.4999f && fabsf(u3) <= 0.4999f;
+    if (exact_only || !ok) {
+        q0 = q8_round(x.x, d, inv, exact_only); q1 = q8_round(x.y, d, inv, exact_only);
+        q2 = q8_round(x.z, d, inv, exact_only); q3 = q8_round(x.w, d, inv, exact_only);
+    }
+    return (int)__byte_perm(__byte_perm(q0, q1, 0x0040), __byte_perm(q2, q3, 0x0040), 0x5410);
+}
 
 // One 32-block held by 8 consecutive lanes (lane `sub` of the group has elements 4*sub..4*sub+3): quantise it with q8_1
 // arithmetic and store it as block jb of the activation layout at `am` (see ACT_ITEM / ACT_BLK).  All 8 lanes must call.
-__device__ __forceinline__ void quant_block_store(const float4 x, int jb, int sub, bool in_range, uint8_t * am) {
+__device__ __forceinline__ void quant_block_store(const float4 x, int jb, int sub, bool in_range, uint8_t * am, uint8_t * am2 = nullptr) {
     float amax = fmaxf(fmaxf(fabsf(x.x), fabsf(x.y)), fmaxf(fabsf(x.z), fabsf(x.w)));
 #pragma unroll
     for (int o = 1; o < 8; o <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
     const float d = __fdiv_rn(amax, 127.0f);
-    int q0 = 0, q1 = 0, q2 = 0, q3 = 0;
-    if (amax != 0.0f) {
-        const bool tiny = amax < 1e-20f;
-        float inv; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(d));
-        q0 = q8_round(x.x, d, inv, tiny); q1 = q8_round(x.y, d, inv, tiny);
-        q2 = q8_round(x.z, d, inv, tiny); q3 = q8_round(x.w, d, inv, tiny);
-    }
-    const int word = (int)__byte_perm(__byte_perm(q0, q1, 0x0040), __byte_perm(q2, q3, 0x0040), 0x5410);
+    float inv; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(d));
+    if (amax == 0.0f) inv = 0.0f;                                                  // an all-zero block: every q is 0, no branch
+    const int word = q8_round4(x, d, inv, amax < 1e-20f && amax != 0.0f);
     int s = __dp4a(word, 0x01010101, 0);
     s += __shfl_xor_sync(0xffffffffu, s, 1);
     s += __shfl_xor_sync(0xffffffffu, s, 2);          // sum of 16 elements (lanes 0-3 / 4-7)
@@ -260,12 +270,64 @@ __device__ __forceinline__ void quant_block_store(const float4 x, int jb, int su
     s += __shfl_xor_sync(0xffffffffu, s, 4);          // sum of the 32-block
     const int s16b = __shfl_down_sync(0xffffffffu, s16, 4);
     if (in_range) {
-        uint8_t * blk = am + (size_t)(jb >> 3) * ACT_ITEM + (jb & 7) * ACT_BLK;
-        reinterpret_cast<int *>(blk)[sub] = word;
+        const size_t off = (size_t)(jb >> 3) * ACT_ITEM + (jb & 7) * ACT_BLK;
+        reinterpret_cast<int *>(am + off)[sub] = word;
+        if (am2) reinterpret_cast<int *>(am2 + off)[sub] = word;
         if (sub == 0) {
             const float d8 = __half2float(__float2half_rn(d));   // q8_1 stores d as binary16 (quantize.cu:47)
             int4 t; t.x = __float_as_int(d8); t.y = __float_as_int(d8 * (float)s); t.z = -32 * s16; t.w = -32 * s16b;
-            *reinterpret_cast<int4 *>(blk + 32) = t;
+            *reinterpret_cast<int4 *>(am + off + 32) = t;
+            if (am2) *reinterpret_cast<int4 *>(am2 + off + 32) = t;
+        }
+    }
+}
+
+// NB independent 32-blocks per 8-lane group, the same arithmetic per block as quant_block_store, written so that the NB dependent
+// chains (3 + 4 shuffles, an IEEE division, a reciprocal, four roundings: ~1500 cycles of latency each) advance in lockstep instead
+// of one after the other.  The fused norm prologue of the batch-1 GEMV runs 4 blocks per thread with 2 warps per scheduler: called
+// four times in a row the quantiser alone took 3.6 us of the prologue's 6 (timeline of the chain kernel, profiles/r02_chain_timeline.log).
+// in[n] must be uniform over the 8 lanes of a group; all lanes of the warp must call.
+template <int NB>
+__device__ __forceinline__ void quant_block_store_n(const float4 (&x)[NB], const int (&jb)[NB], int sub, const bool (&in)[NB], uint8_t * am, uint8_t * am2 = nullptr) {
+    float amax[NB], d[NB], inv[NB];
+    int word[NB], s[NB], s16[NB], s16b[NB];
+#pragma unroll
+    for (int n = 0; n < NB; ++n) amax[n] = fmaxf(fmaxf(fabsf(x[n].x), fabsf(x[n].y)), fmaxf(fabsf(x[n].z), fabsf(x[n].w)));
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+#pragma unroll
+        for (int n = 0; n < NB; ++n) amax[n] = fmaxf(amax[n], __shfl_xor_sync(0xffffffffu, amax[n], o));
+    }
+#pragma unroll
+    for (int n = 0; n < NB; ++n) d[n] = __fdiv_rn(amax[n], 127.0f);
+#pragma unroll
+    for (int n = 0; n < NB; ++n) asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv[n]) : "f"(d[n]));
+#pragma unroll
+    for (int n = 0; n < NB; ++n) {
+        if (amax[n] == 0.0f) inv[n] = 0.0f;
+        word[n] = q8_round4(x[n], d[n], inv[n], amax[n] < 1e-20f && amax[n] != 0.0f);
+        s[n] = __dp4a(word[n], 0x01010101, 0);
+    }
+#pragma unroll
+    for (int n = 0; n < NB; ++n) s[n] += __shfl_xor_sync(0xffffffffu, s[n], 1);
+#pragma unroll
+    for (int n = 0; n < NB; ++n) s[n] += __shfl_xor_sync(0xffffffffu, s[n], 2);
+#pragma unroll
+    for (int n = 0; n < NB; ++n) { s16[n] = s[n]; s[n] += __shfl_xor_sync(0xffffffffu, s[n], 4); }
+#pragma unroll
+    for (int n = 0; n < NB; ++n) s16b[n] = __shfl_down_sync(0xffffffffu, s16[n], 4);
+#pragma unroll
+    for (int n = 0; n < NB; ++n) {
+        if (in[n]) {
+            const size_t off = (size_t)(jb[n] >> 3) * ACT_ITEM + (jb[n] & 7) * ACT_BLK;
+            reinterpret_cast<int *>(am + off)[sub] = word[n];
+            if (am2) reinterpret_cast<int *>(am2 + off)[sub] = word[n];
+            if (sub == 0) {
+                const float d8 = __half2float(__float2half_rn(d[n]));
+                int4 t; t.x = __float_as_int(d8); t.y = __float_as_int(d8 * (float)s[n]); t.z = -32 * s16[n]; t.w = -32 * s16b[n];
+                *reinterpret_cast<int4 *>(am + off + 32) = t;
+                if (am2) *reinterpret_cast<int4 *>(am2 + off + 32) = t;
+            }
         }
     }
 }

@@ -186,6 +186,9 @@ for ph, nm in enumerate(["wo", "gate/up", "down", "q/k", "v"]):
     names[1 + 4 * ph] = nm + ": wait passed"; names[2 + 4 * ph] = nm + ": activations in registers"
     names[3 + 4 * ph] = nm + ": first stage landed"; names[4 + 4 * ph] = nm + ": last stage multiplied"
     names[32 + 2 * ph] = nm + ": [w0] first stage epilogue"; names[33 + 2 * ph] = nm + ": [w0] last epilogue + arrive"
+for nn in range(2):
+    names[44 + 4 * nn] = "norm %d: row in shared memory" % nn; names[45 + 4 * nn] = "norm %d: sums of squares done (barrier)" % nn
+    names[46 + 4 * nn] = "norm %d: thread 0 quantised its blocks" % nn; names[47 + 4 * nn] = "norm %d: all threads done (barrier)" % nn
 for base, who in ((0, "CTA 0"), (64, "last CTA")):
     t0 = tr[base + 0]
     ev = sorted((int(tr[base + i]), i) for i in range(64) if tr[base + i] != 0)

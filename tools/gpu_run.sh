@@ -1,0 +1,52 @@
+#!/bin/bash
+# gpu_run.sh <task> [args] -- the recurring GPU-box procedures of this repo in one place (run through gpurun; outputs under gpurun_out/).
+#   tests [pytest args]     the -m gpu suite
+#   bench [bench.py args]   bench.py (N = 1)
+#   benchn <N> [args]       bench.py under torchrun on N GPUs (70B row split arm)
+#   launches [tg|pp]        ncu launch list of a decode step / a pp512 pass (graphs off: every kernel is a launch) -> gpurun_out/launches_*.csv
+#   ncu <regex> <cmd...>    one `ncu --set full` capture of the kernels matching <regex> while <cmd> runs -> gpurun_out/ncu_<regex>.ncu-rep
+#   tbo                     the reference's test-backend-ops against the plugin, all ops -> gpurun_out/tbo_all.log
+#   bitident                logits with every fusion on / off (must be identical)
+#   ktrace                  kernel timeline of a decode step (needs a B200_KTRACE=1 build)
+#   split [models]          llama-bench -sm row variants on the visible GPUs (tools/gpu_split.sh)
+#   refcuda [models]        the reference's own ggml-cuda (sm_100 build) next to the plugin (tools/gpu_ref_cuda.sh)
+#   loadtime                model load wall time, staged vs plain upload (tools/gpu_load_time.sh)
+set -u
+export LD_LIBRARY_PATH=$PWD/baseline/_ref/lib:$PWD/llamacog_b200:${LD_LIBRARY_PATH:-}
+PLUGIN=$PWD/llamacog_b200/libggml-b200.so
+B=baseline/_ref/bin
+mkdir -p gpurun_out
+task=${1:-tests}; shift || true
+model() { python -c "import bench; print(bench.ensure_model())"; }
+case $task in
+  tests)   python -m pytest tests -m gpu -x -q "$@" ;;
+  bench)   python bench.py "$@" ;;
+  benchn)  n=$1; shift; python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29555 bench.py --gpus $n "$@" ;;
+  launches)
+    M=$(model); export GGML_BACKEND_PATH=$PLUGIN
+    if [ "${1:-tg}" = pp ]; then A="-p 512 -n 0"; else A="-p 0 -n 3"; fi
+    B200_CUDA_GRAPHS=0 timeout 300 $B/llama-bench -m $M -ngl 99 -fa 1 $A -r 1 -t 4 > gpurun_out/launches_${1:-tg}_plain.log 2>&1 || exit 1
+    B200_CUDA_GRAPHS=0 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/launches_${1:-tg}.csv \
+        $B/llama-bench -m $M -ngl 99 -fa 1 $A -r 1 -t 4 > gpurun_out/launches_${1:-tg}_ncu.log 2>&1
+    python tools/launch_agg.py gpurun_out/launches_${1:-tg}.csv | head -n 30 ;;
+  ncu)     re=$1; shift; "$@" > gpurun_out/ncu_plain.log 2>&1 || exit 1
+           timeout 900 ncu --set full --clock-control none --import-source on -k regex:$re -c ${NCU_COUNT:-4} -f -o gpurun_out/ncu_$re "$@" > gpurun_out/ncu_$re.log 2>&1; tail -n 3 gpurun_out/ncu_$re.log ;;
+  tbo)     export GGML_BACKEND_PATH=$PLUGIN; timeout 900 $B/test-backend-ops test -b B200_0 > gpurun_out/tbo_all.log 2>&1; echo "exit $?" >> gpurun_out/tbo_all.log
+           sed 's/\x1b\[[0-9;]*m//g' gpurun_out/tbo_all.log | grep -E "FAIL|not supported|exit|backends passed|tests passed" | awk '{print $1, $NF}' | sort | uniq -c | sort -rn | head -n 20 ;;
+  bitident)
+    M=$(model); export GGML_BACKEND_PATH=$PLUGIN; L=tests/host/build/logits_check
+    run() { name=$1; shift; env "$@" timeout 600 $L $M /tmp/$name.bin 99 1 $NP $ND > /dev/null 2>&1 || echo "$name failed"; }
+    for cfg in "20 8" "600 12" "1100 6"; do
+      set -- $cfg; NP=$1; ND=$2
+      run base B200_FUSE=0; run fused B200_FUSE=1; run nogemv B200_FUSE=1 B200_FUSE_GEMV=0 B200_FUSE_ROPE=0 B200_FUSE_HOIST=0
+      echo "== n_prompt=$NP n_decode=$ND"
+      for v in fused nogemv; do cmp -s /tmp/base.bin /tmp/$v.bin && echo "  $v == unfused" || { echo "  $v DIFFERS from unfused"; python tools/cmp_bins.py /tmp/base.bin /tmp/$v.bin; }; done
+    done ;;
+  ktrace)  M=$(model); export GGML_BACKEND_PATH=$PLUGIN
+           B200_KTRACE=/tmp/ktrace.txt timeout 600 $B/llama-bench -m $M -ngl 99 -fa 1 -p 0 -n 64 -r 1 -t 4 > gpurun_out/kt_lb.log 2>&1
+           python tools/ktrace_report.py /tmp/ktrace.txt 0 ${KT_N:-20} | tee gpurun_out/ktrace_report.txt ;;
+  split)   MODELS="${*:-llama3-8b llama3-70b}" bash tools/gpu_split.sh ;;
+  refcuda) MODELS="${*:-llama3-8b}" bash tools/gpu_ref_cuda.sh ;;
+  loadtime) bash tools/gpu_load_time.sh ;;
+  *) echo "unknown task $task"; exit 2 ;;
+esac

@@ -1,25 +1,20 @@
-# 2+ GPUs: row split / layer split against the single-GPU run (logits and llama-bench)
-export LD_LIBRARY_PATH=$PWD/baseline/_ref/lib:$PWD/llamacog_b200:$LD_LIBRARY_PATH
-mkdir -p gpurun_out
-B=baseline/_ref/bin
+#!/bin/bash
+# row-split debug: llama-bench -sm row, stderr kept; B200_TIMING=1 prints the graph capture / replay counts
+export LD_LIBRARY_PATH=baseline/_ref/lib:llamacog_b200
 export GGML_BACKEND_PATH=$PWD/llamacog_b200/libggml-b200.so
-nvidia-smi topo -m > gpurun_out/topo.log 2>&1
-python tools/make_gguf.py llama3.2-1b q4_k_m /tmp/l1b.gguf > gpurun_out/gen1b.log 2>&1
-python tools/make_gguf.py llama3-8b q4_k_m /tmp/l8b-q4km.gguf > gpurun_out/gen8b.log 2>&1
-L=tests/host/build/logits_check
-for m in l1b l8b-q4km; do
-  for sm in none layer row; do
-    B200_TIMING=1 timeout 300 $L /tmp/$m.gguf /tmp/$m.$sm.bin 99 1 40 8 512 $sm > gpurun_out/split_$m.$sm.log 2>&1; echo "$m $sm exit $?"
-    grep -E "row-split|B200_Split|error|failed" gpurun_out/split_$m.$sm.log | head -5
-  done
-  python tools/cmp_logits.py /tmp/$m.none.bin /tmp/$m.layer.bin
-  python tools/cmp_logits.py /tmp/$m.none.bin /tmp/$m.row.bin
+mkdir -p /tmp/b200_models
+for m in ${MODELS:-llama3-8b}; do
+  [ -f /tmp/b200_models/$m-q4_k_m.gguf ] || python tools/make_gguf.py $m q4_k_m /tmp/b200_models/$m-q4_k_m.gguf > /dev/null
+  echo "=== $m row n=5,32 (B200_TIMING=1)"
+  B200_TIMING=1 baseline/_ref/bin/llama-bench -m /tmp/b200_models/$m-q4_k_m.gguf -ngl 99 -fa 1 -r 1 -mg 0 -sm row -ts ${TS:-1/1} -p 0 -n 5,32 -t 4 2>&1 | grep -v "^$" | tail -n 14
+  echo "=== $m row n=64"
+  baseline/_ref/bin/llama-bench -m /tmp/b200_models/$m-q4_k_m.gguf -ngl 99 -fa 1 -r 1 -mg 0 -sm row -ts ${TS:-1/1} -p 0 -n 64 -t 4 2>&1 | grep "tg64\|error\|ggml-b200:"
+  echo "=== $m row, events instead of flags"
+  B200_SPLIT_FLAGS=0 baseline/_ref/bin/llama-bench -m /tmp/b200_models/$m-q4_k_m.gguf -ngl 99 -fa 1 -r 1 -mg 0 -sm row -ts ${TS:-1/1} -p 0 -n 64 -t 4 2>&1 | grep "tg64\|error\|ggml-b200:"
+  echo "=== $m row, unfolded flags"
+  B200_SPLIT_FOLD=0 baseline/_ref/bin/llama-bench -m /tmp/b200_models/$m-q4_k_m.gguf -ngl 99 -fa 1 -r 1 -mg 0 -sm row -ts ${TS:-1/1} -p 0 -n 64 -t 4 2>&1 | grep "tg64\|error\|ggml-b200:"
+  echo "=== $m row, shard everything"
+  B200_SPLIT_MIN_MB=0 baseline/_ref/bin/llama-bench -m /tmp/b200_models/$m-q4_k_m.gguf -ngl 99 -fa 1 -r 1 -mg 0 -sm row -ts ${TS:-1/1} -p 0 -n 64 -t 4 2>&1 | grep "tg64\|error\|ggml-b200:"
+  echo "=== $m none n=64"
+  baseline/_ref/bin/llama-bench -m /tmp/b200_models/$m-q4_k_m.gguf -ngl 99 -fa 1 -r 1 -mg 0 -sm none -p 0 -n 64 -t 4 2>&1 | grep "tg64\|error"
 done
-B200_SPLIT_P2P=0 timeout 300 $L /tmp/l1b.gguf /tmp/l1b.row_nop2p.bin 99 1 40 8 512 row > gpurun_out/split_l1b.row_nop2p.log 2>&1; echo "row without p2p exit $?"
-python tools/cmp_logits.py /tmp/l1b.none.bin /tmp/l1b.row_nop2p.bin
-for sm in none layer row; do
-  timeout 600 $B/llama-bench -m /tmp/l8b-q4km.gguf -ngl 99 -fa 1 -sm $sm -p 512 -n 128 -r 3 > gpurun_out/lb_8b_sm_$sm.log 2>&1; echo "exit $?" >> gpurun_out/lb_8b_sm_$sm.log
-  grep -E "pp512|tg128|error|exit" gpurun_out/lb_8b_sm_$sm.log
-done
-B200_SPLIT_XCOPY=1 timeout 600 $B/llama-bench -m /tmp/l8b-q4km.gguf -ngl 99 -fa 1 -sm row -p 0 -n 128 -r 3 > gpurun_out/lb_8b_sm_row_xcopy.log 2>&1
-grep -E "tg128|error" gpurun_out/lb_8b_sm_row_xcopy.log
