@@ -315,29 +315,40 @@ __global__ void __launch_bounds__(288, 2) chain_kernel(const __grid_constant__ c
                     asm volatile("bar.sync 1, 256;" ::: "memory");
                     if (ct == 0) ch_stamp(p, 45 + 4 * q.norm);
                     float tot = 0.0f;
-#pragma unroll 4
-                    for (int wi = 0; wi < (n4 >> 5); ++wi) tot += npart[wi];
+                    if ((n4 >> 5) == 32) {                                     // K = 4096: loads batched, the same sequential order of additions
+#pragma unroll
+                        for (int w2 = 0; w2 < 16; ++w2) { const float2 t2 = reinterpret_cast<const float2 *>(npart)[w2]; tot += t2.x; tot += t2.y; }
+                    } else {
+                        for (int wi = 0; wi < (n4 >> 5); ++wi) tot += npart[wi];
+                    }
+                    if (ct == 0 && tot != -1.0f) ch_stamp(p, 52 + 4 * q.norm);
                     const float scale = rms_scale(tot, nm.K, nm.eps);
+                    if (ct == 0 && scale != -1.0f) ch_stamp(p, 53 + 4 * q.norm);
                     const bool writer = blockIdx.x == 0;
-#pragma unroll 1
-                    for (int k = 0; k < 4; k += 2) {                        // two blocks per pass: their dependent chains overlap, the code stays small
-                        float4 y[2];
+                    {                                                          // eight consecutive elements per thread and pass: four lanes per 32-block
+                        float4 y0[2], y1[2];
                         int jb[2];
                         bool in[2];
 #pragma unroll
-                        for (int u = 0; u < 2; ++u) {
-                            const int i = ct + 256 * (k + u);
-                            in[u] = i < n4;
-                            jb[u] = in[u] ? i >> 3 : 0;
-                            y[u] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-                            if (in[u]) {
-                                const float4 v = reinterpret_cast<const float4 *>(xs)[i], wv = reinterpret_cast<const float4 *>(wn)[i];
-                                const float4 nv = make_float4(v.x * scale, v.y * scale, v.z * scale, v.w * scale);
-                                y[u] = make_float4(nv.x * wv.x, nv.y * wv.y, nv.z * wv.z, nv.w * wv.w);
-                                if (writer) { reinterpret_cast<float4 *>(nm.y)[i] = nv; reinterpret_cast<float4 *>(nm.out)[i] = y[u]; }
+                        for (int k = 0; k < 2; ++k) {
+                            const int t = ct + 256 * k, i = 2 * t;
+                            in[k] = i < n4;
+                            jb[k] = in[k] ? t >> 2 : 0;
+                            y0[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); y1[k] = y0[k];
+                            if (in[k]) {
+                                const float4 v0 = reinterpret_cast<const float4 *>(xs)[i], v1 = reinterpret_cast<const float4 *>(xs)[i + 1];
+                                const float4 w0 = reinterpret_cast<const float4 *>(wn)[i], w1 = reinterpret_cast<const float4 *>(wn)[i + 1];
+                                const float4 n0 = make_float4(v0.x * scale, v0.y * scale, v0.z * scale, v0.w * scale);
+                                const float4 n1 = make_float4(v1.x * scale, v1.y * scale, v1.z * scale, v1.w * scale);
+                                y0[k] = make_float4(n0.x * w0.x, n0.y * w0.y, n0.z * w0.z, n0.w * w0.w);
+                                y1[k] = make_float4(n1.x * w1.x, n1.y * w1.y, n1.z * w1.z, n1.w * w1.w);
+                                if (writer) {
+                                    reinterpret_cast<float4 *>(nm.y)[i] = n0; reinterpret_cast<float4 *>(nm.y)[i + 1] = n1;
+                                    reinterpret_cast<float4 *>(nm.out)[i] = y0[k]; reinterpret_cast<float4 *>(nm.out)[i + 1] = y1[k];
+                                }
                             }
                         }
-                        quant_block_store_n<2>(y, jb, ct & 7, in, act);
+                        quant_block_store8<2>(y0, y1, jb, ct & 3, in, act);
                     }
                     if (ct == 0) ch_stamp(p, 46 + 4 * q.norm);
                     asm volatile("bar.sync 1, 256;" ::: "memory");

@@ -282,6 +282,78 @@ __device__ __forceinline__ void quant_block_store(const float4 x, int jb, int su
     }
 }
 
+// Straight-line part of q8_round4: the word of fast roundings and whether all four are trustworthy (no branch in here).
+__device__ __forceinline__ int q8_fast4(const float4 x, float inv, bool & ok) {
+    const float r0 = x.x * inv, r1 = x.y * inv, r2 = x.z * inv, r3 = x.w * inv;
+    const float f0 = r0 + 12582912.0f, f1 = r1 + 12582912.0f, f2 = r2 + 12582912.0f, f3 = r3 + 12582912.0f;
+    const float u0 = r0 - (f0 - 12582912.0f), u1 = r1 - (f1 - 12582912.0f), u2 = r2 - (f2 - 12582912.0f), u3 = r3 - (f3 - 12582912.0f);
+    ok = ok && fabsf(u0) <= 0.4999f && fabsf(u1) <= 0.4999f && fabsf(u2) <= 0.4999f && fabsf(u3) <= 0.4999f;
+    const int q0 = __float_as_int(f0) - 0x4B400000, q1 = __float_as_int(f1) - 0x4B400000;
+    const int q2 = __float_as_int(f2) - 0x4B400000, q3 = __float_as_int(f3) - 0x4B400000;
+    return (int)__byte_perm(__byte_perm(q0, q1, 0x0040), __byte_perm(q2, q3, 0x0040), 0x5410);
+}
+static __device__ __noinline__ int q8_exact4(const float4 x, float d, float inv, bool tiny) {      // the rare path, kept out of line
+    const int q0 = q8_round(x.x, d, inv, tiny), q1 = q8_round(x.y, d, inv, tiny), q2 = q8_round(x.z, d, inv, tiny), q3 = q8_round(x.w, d, inv, tiny);
+    return (int)__byte_perm(__byte_perm(q0, q1, 0x0040), __byte_perm(q2, q3, 0x0040), 0x5410);
+}
+
+// NP 32-blocks, each held by FOUR consecutive lanes with eight consecutive elements per lane (a = 8*sub4 .. +3, b = 8*sub4+4 .. +7):
+// the same q8_1 arithmetic as quant_block_store (max, integer sums and per-element roundings do not depend on which lane holds
+// what), with 2.4x fewer instructions per element (two butterfly rounds instead of three, one division / reciprocal per eight
+// elements) and ONE branch for all the roundings, so the NP dependent chains overlap.  Used where every CTA of a launch repeats
+// the quantisation (the norm prologue of the batch-1 GEMV), see profiles/r02_norm_prologue.md.  in[n] uniform over the 4 lanes.
+template <int NP>
+__device__ __forceinline__ void quant_block_store8(const float4 (&a)[NP], const float4 (&b)[NP], const int (&jb)[NP], int sub4, const bool (&in)[NP],
+                                                   uint8_t * am, uint8_t * am2 = nullptr) {
+    float amax[NP], d[NP], inv[NP];
+    int w0[NP], w1[NP], s[NP], s16[NP], s16b[NP];
+    bool ok = true;
+#pragma unroll
+    for (int n = 0; n < NP; ++n)
+        amax[n] = fmaxf(fmaxf(fmaxf(fabsf(a[n].x), fabsf(a[n].y)), fmaxf(fabsf(a[n].z), fabsf(a[n].w))),
+                        fmaxf(fmaxf(fabsf(b[n].x), fabsf(b[n].y)), fmaxf(fabsf(b[n].z), fabsf(b[n].w))));
+#pragma unroll
+    for (int n = 0; n < NP; ++n) amax[n] = fmaxf(amax[n], __shfl_xor_sync(0xffffffffu, amax[n], 1));
+#pragma unroll
+    for (int n = 0; n < NP; ++n) amax[n] = fmaxf(amax[n], __shfl_xor_sync(0xffffffffu, amax[n], 2));
+#pragma unroll
+    for (int n = 0; n < NP; ++n) {
+        d[n] = __fdiv_rn(amax[n], 127.0f);
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv[n]) : "f"(d[n]));
+        if (amax[n] == 0.0f) inv[n] = 0.0f;                            // an all-zero block: every q is 0
+        ok = ok && !(amax[n] < 1e-20f && amax[n] != 0.0f);             // denormal scales take the exact division
+    }
+#pragma unroll
+    for (int n = 0; n < NP; ++n) { w0[n] = q8_fast4(a[n], inv[n], ok); w1[n] = q8_fast4(b[n], inv[n], ok); }
+    if (!ok) {
+#pragma unroll
+        for (int n = 0; n < NP; ++n) {
+            const bool tiny = amax[n] < 1e-20f && amax[n] != 0.0f;
+            w0[n] = q8_exact4(a[n], d[n], inv[n], tiny); w1[n] = q8_exact4(b[n], d[n], inv[n], tiny);
+        }
+    }
+#pragma unroll
+    for (int n = 0; n < NP; ++n) s[n] = __dp4a(w1[n], 0x01010101, __dp4a(w0[n], 0x01010101, 0));
+#pragma unroll
+    for (int n = 0; n < NP; ++n) { s[n] += __shfl_xor_sync(0xffffffffu, s[n], 1); s16[n] = s[n]; }      // 16 elements (lanes 0-1 / 2-3)
+#pragma unroll
+    for (int n = 0; n < NP; ++n) { s[n] += __shfl_xor_sync(0xffffffffu, s[n], 2); s16b[n] = __shfl_down_sync(0xffffffffu, s16[n], 2); }
+#pragma unroll
+    for (int n = 0; n < NP; ++n) {
+        if (in[n]) {
+            const size_t off = (size_t)(jb[n] >> 3) * ACT_ITEM + (jb[n] & 7) * ACT_BLK;
+            reinterpret_cast<int2 *>(am + off)[sub4] = make_int2(w0[n], w1[n]);
+            if (am2) reinterpret_cast<int2 *>(am2 + off)[sub4] = make_int2(w0[n], w1[n]);
+            if (sub4 == 0) {
+                const float d8 = __half2float(__float2half_rn(d[n]));
+                int4 t; t.x = __float_as_int(d8); t.y = __float_as_int(d8 * (float)s[n]); t.z = -32 * s16[n]; t.w = -32 * s16b[n];
+                *reinterpret_cast<int4 *>(am + off + 32) = t;
+                if (am2) *reinterpret_cast<int4 *>(am2 + off + 32) = t;
+            }
+        }
+    }
+}
+
 // NB independent 32-blocks per 8-lane group, the same arithmetic per block as quant_block_store, written so that the NB dependent
 // chains (3 + 4 shuffles, an IEEE division, a reciprocal, four roundings: ~1500 cycles of latency each) advance in lockstep instead
 // of one after the other.  The fused norm prologue of the batch-1 GEMV runs 4 blocks per thread with 2 warps per scheduler: called

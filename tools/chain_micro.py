@@ -188,6 +188,8 @@ for ph, nm in enumerate(["wo", "gate/up", "down", "q/k", "v"]):
     names[32 + 2 * ph] = nm + ": [w0] first stage epilogue"; names[33 + 2 * ph] = nm + ": [w0] last epilogue + arrive"
 for nn in range(2):
     names[44 + 4 * nn] = "norm %d: row in shared memory" % nn; names[45 + 4 * nn] = "norm %d: sums of squares done (barrier)" % nn
+    names[52 + 4 * nn] = "norm %d: partials summed" % nn; names[53 + 4 * nn] = "norm %d: scale known" % nn
+    names[54 + 4 * nn] = "norm %d: first pass of the quantiser done" % nn
     names[46 + 4 * nn] = "norm %d: thread 0 quantised its blocks" % nn; names[47 + 4 * nn] = "norm %d: all threads done (barrier)" % nn
 for base, who in ((0, "CTA 0"), (64, "last CTA")):
     t0 = tr[base + 0]
