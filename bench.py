@@ -127,6 +127,25 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def tc_issue_peaks():
+    """tcgen05.mma issue-rate peaks (bf16 / int8 / fp8): measured live with tools/tc_peak.bin when it is there (0.1 s), else the
+    committed measurement of the same program on this pool's B200 (profiles/r02_tc_peak.log)."""
+    def parse(out):
+        return json.loads([l for l in out.split("\n") if l.startswith('{"tc_peak"')][-1])["tc_peak"]
+    try:
+        d = parse(subprocess.run([os.path.join(ROOT, "tools", "tc_peak.bin")], capture_output=True, text=True, timeout=120).stdout)
+        d["source"] = "measured in this run (tools/tc_peak.bin)"
+        return d
+    except Exception:  # noqa: BLE001
+        pass
+    try:
+        d = parse(open(os.path.join(ROOT, "profiles", "r02_tc_peak.log")).read())
+        d["source"] = "profiles/r02_tc_peak.log"
+        return d
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def ensure_model(preset="llama3-8b", ftype="q4_k_m"):
     os.makedirs(MODEL_DIR, exist_ok=True)
     path = os.path.join(MODEL_DIR, "%s-%s.gguf" % (preset, ftype))
@@ -487,6 +506,10 @@ def main():
                                        "peak": tpeak, "unit": "TFLOP/s", "frac": m["tflops"] / tpeak,
                                        "peak_source": "measured bf16 burst (MEASURED_PEAKS.json)" if peaks else "fallback 1.59 PFLOP/s",
                                        "ms_per_layer": m["ms_per_layer"]}
+                tc = tc_issue_peaks()      # tcgen05 issue-rate ceilings of this box (tools/tc_peak.cu): what an int8 / fp8 operand route could reach at most
+                if tc:
+                    pre["mmq_roofline"].update({"frac_int8_peak": m["tflops"] / tc["int8_tops"], "frac_fp8_peak": m["tflops"] / tc["fp8_tflops"],
+                                                "frac_bf16_issue_peak": m["tflops"] / tc["bf16_tflops"], "tc_issue_peaks": tc})
                 tp = os.path.join(ROOT, "profiles", "r01_mmq_traffic.json")      # ncu --set full of the three large shapes: DRAM bytes per launch
                 if os.path.exists(tp):
                     pre["mmq_roofline"]["traffic"] = {x["shape"]: x["dram_read_bytes"] + x["dram_write_bytes"] for x in json.load(open(tp))["launches"]}

