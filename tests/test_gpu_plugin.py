@@ -106,6 +106,47 @@ def test_logits_match_reference_cpu_backend(tmp_path, preset, fa, n_prompt):
         assert nmse(got[i], ref[i]) < bar, (i, nmse(got[i], ref[i]), bar)
 
 
+def _nodes(path):
+    import struct
+    raw = open(path, "rb").read()
+    out, o = [], 0
+    while o < len(raw):
+        name = raw[o:o + 64].split(b"\0")[0].decode()
+        op, ne1, n = struct.unpack_from("<iiq", raw, o + 64)
+        nmse, = struct.unpack_from("<d", raw, o + 80)
+        out.append((name, op, ne1, n, nmse))
+        o += 88
+    return out
+
+
+@pytest.mark.parametrize("preset,n_prompt", [("tiny", 70), ("tiny-moe", 40), ("llama3.2-1b", 40)])
+def test_per_node_parity_with_reference_cpu_backend(tmp_path, preset, n_prompt):
+    """The fixed-seed twin of the end-to-end logits test, node by node.  The model runs on the plugin with the scheduler's eval
+    callback (ggml-backend.cpp:1415-1447) handing out every MUL_MAT / MUL_MAT_ID / FLASH_ATTN_EXT node of the prefill graph (MMQ +
+    tensor-core attention) and of two decode graphs (MMVQ + vector attention); tests/host/logits_check.cpp re-evaluates each node
+    on the reference CPU backend FROM THE SAME INPUT BYTES (read back from the device, strides kept) and records the NMSE.  That is
+    ggml_backend_compare_graph_backend (ggml-backend.cpp:1829-1865) with the inputs re-synchronised per node, so nothing drifts and
+    the bar is the reference's own per-op bar: 5e-4 (tests/test-backend-ops.cpp:1049), for every node of every layer.  (The
+    callback splits the graph per observed node: this is the unfused path; fused == unfused bit for bit is test_gpu_fused.py.)"""
+    _need()
+    model = str(tmp_path / (preset + ".gguf"))
+    subprocess.check_call([sys.executable, os.path.join(ROOT, "tools", "make_gguf.py"), preset, "q4_k_m", model], stdout=subprocess.DEVNULL)
+    exe = os.path.join(ROOT, "tests", "host", "build", "logits_check")
+    nodes = str(tmp_path / "nodes.bin")
+    r = subprocess.run([exe, model, str(tmp_path / "gpu.bin"), "99", "1", str(n_prompt), "2", "512", "none", nodes],
+                       capture_output=True, text=True, env=_env(), timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    recs = _nodes(nodes)
+    n_layer = {"tiny": 2, "tiny-moe": 2, "llama3.2-1b": 16}[preset]
+    mm = [x for x in recs if x[1] != 64]
+    fa = [x for x in recs if x[1] == 64]
+    assert len(fa) == 3 * n_layer and len(mm) >= 3 * (7 * n_layer + 1), (len(fa), len(mm))      # prefill + 2 decode graphs
+    worst = max(recs, key=lambda x: x[4])
+    print("per-node twin: %d nodes, worst %s (ne1 = %d) NMSE %.3g" % (len(recs), worst[0], worst[2], worst[4]))
+    for name, op, ne1, n, nmse in recs:
+        assert nmse < 5e-4, (name, op, ne1, n, nmse)
+
+
 ALL = {"B200_SPLIT_MIN_MB": "0"}      # shard every matrix (the default leaves matrices below ~72 MB whole on the main device: most of a 1B model)
 
 
