@@ -785,6 +785,41 @@ static int fa_launch_gqa(const fa_params & p, dim3 grid, cudaStream_t st, bool w
     }
     return 0;
 }
+}  // namespace b200
+#include "fattn_mma.cuh"
+namespace b200 {
+
+// warp-level tensor-core tiles for an f16 cache (fattn_mma.cuh): one CTA per SM, grid (groups of 16 queries, KV heads x ne3, splits)
+template <int D, bool Q8>
+static int fa_launch_mma(const fa_params & p, dim3 grid, cudaStream_t st) {
+    constexpr size_t smem = fmma_smem_bytes<D, Q8>();
+    static int attr_set[16] = {0};   // per device
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 16 && !attr_set[dev]) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(fattn_mma_gqa_kernel<D, Q8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set[dev] = 1;
+    }
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = grid; lc.blockDim = dim3(32 * FMMA_NW); lc.dynamicSmemBytes = smem; lc.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+    B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_mma_gqa_kernel<D, Q8>, p));
+    ++g_launches;
+    if (p.nsplit > 1) {
+        const int64_t nrows = (int64_t)p.N * p.n_head * p.ne3;
+        lc.dynamicSmemBytes = 0; lc.blockDim = dim3(128);
+        lc.gridDim = dim3((unsigned)((nrows * 32 + 127) / 128));
+        B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, fattn_combine_kernel<D>, (const float *)p.part, p.dst, p.nbd1, nrows, p.nsplit, p.xq, p.xq_acs, p.n_head));
+        ++g_launches;
+    }
+    return 0;
+}
+static int fa_mma_min_kv() { static const int v = [] { const char * e = getenv("B200_FATTN_MMA_MIN_KV"); return e ? atoi(e) : 512; }();  return v; }
+static bool fa_mma_on() { static const bool v = [] { const char * e = getenv("B200_FATTN_MMA"); return !e || atoi(e) != 0; }();  return v; }
+
 static int fa_gqa_min_kv() { static const int v = [] { const char * e = getenv("B200_FATTN_GQA_MIN_KV"); return e ? atoi(e) : 512; }();  return v; }
 
 // tensor-core kernel for batches of query rows (fattn_tc.cu); returns 0 when the shape is not its to take
@@ -877,6 +912,27 @@ extern "C" int b200_op_flash_attn_ext_xq(const b200_tensor * q, const b200_tenso
     // long context, several queries per KV head (GQA and / or a few rows): the grouped kernel reads the cache once per group
     if (p.n_kv >= fa_gqa_min_kv() && p.N * p.rk2 >= 2 && p.rk2 == p.rv2 && p.rk3 == p.rv3 && q->ne[2] % p.rk2 == 0) {
         const int ngq = p.N * p.rk2;
+        // (f16 rows must be 16-byte aligned for the copies; q8_0 rows of D = 128 / 64 are 8- / 4-byte aligned whenever the cache is)
+        const uintptr_t kval = (uintptr_t)k->data | (uintptr_t)v->data | k->nb[1] | k->nb[2] | k->nb[3] | v->nb[1] | v->nb[2] | v->nb[3];
+        const bool al16 = (kval & (k->type == T_F16 ? 15 : q->ne[0] == 128 ? 7 : 3)) == 0;
+        if (al16 && fa_mma_on() && p.n_kv >= fa_mma_min_kv() && q->nb[1] % 16 == 0 && q->nb[2] % 16 == 0 && q->nb[3] % 16 == 0 &&
+            ((uintptr_t)q->data & 15) == 0 && (!mask || ((((uintptr_t)mask->data | mask->nb[1]) & 15) == 0))) {
+            // f16 cache, long context: m16n8k16 tiles, the whole group (up to 16 queries) per CTA, one CTA per SM, one wave
+            const int nx = (ngq + 15) / 16;
+            const int64_t ctas = (int64_t)nx * (q->ne[2] / p.rk2) * q->ne[3];
+            int ns = (int)std::min<int64_t>(std::max<int64_t>(1, 148 / ctas), std::max(1, ntiles / 4));
+            ns = std::max(1, std::min(ns, 128));
+            if (ns > 1 && (!scratch || scratch_bytes < rows_heads * ns * (2 + q->ne[0]) * 4)) ns = 1;
+            if (!(xq && ns == 1)) {
+                p.nsplit = ns;
+                p.tiles_per_split = (ntiles + ns - 1) / ns;
+                p.part = (float *)scratch;
+                const dim3 grid((unsigned)nx, (unsigned)((q->ne[2] / p.rk2) * q->ne[3]), (unsigned)ns);
+                cudaStream_t st = (cudaStream_t)stream;
+                if (k->type == T_F16) return q->ne[0] == 128 ? fa_launch_mma<128, false>(p, grid, st) : fa_launch_mma<64, false>(p, grid, st);
+                return q->ne[0] == 128 ? fa_launch_mma<128, true>(p, grid, st) : fa_launch_mma<64, true>(p, grid, st);
+            }
+        }
         const int G = ngq <= 4 ? 4 : 8;
         const int nx = (ngq + G - 1) / G;
         const int64_t ctas = (int64_t)nx * (q->ne[2] / p.rk2) * q->ne[3];

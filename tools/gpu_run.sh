@@ -11,6 +11,8 @@
 #   split [models]          llama-bench -sm row variants on the visible GPUs (tools/gpu_split.sh)
 #   refcuda [models]        the reference's own ggml-cuda (sm_100 build) next to the plugin (tools/gpu_ref_cuda.sh)
 #   loadtime                model load wall time, staged vs plain upload (tools/gpu_load_time.sh)
+#   config3                 Llama-3-8B Q8_0 with f16 and q8_0 KV cache: pp512 / tg128 at depth 0 and at 28672
+#   moe                     Mixtral-8x7B Q4_K_M pp512 / tg128 and llama-batched-bench
 set -u
 export LD_LIBRARY_PATH=$PWD/baseline/_ref/lib:$PWD/llamacog_b200:${LD_LIBRARY_PATH:-}
 PLUGIN=$PWD/llamacog_b200/libggml-b200.so
@@ -48,5 +50,17 @@ case $task in
   split)   MODELS="${*:-llama3-8b llama3-70b}" bash tools/gpu_split.sh ;;
   refcuda) MODELS="${*:-llama3-8b}" bash tools/gpu_ref_cuda.sh ;;
   loadtime) bash tools/gpu_load_time.sh ;;
+  config3)
+    export GGML_BACKEND_PATH=$PLUGIN; mkdir -p /tmp/b200_models; f=/tmp/b200_models/llama3-8b-q8_0.gguf
+    [ -f $f ] || python tools/make_gguf.py llama3-8b q8_0 $f > /dev/null
+    for kv in f16 q8_0; do
+      echo "=== Llama-3-8B Q8_0, $kv KV cache"
+      timeout 600 $B/llama-bench -m $f -ngl 99 -fa 1 -ctk $kv -ctv $kv -p 512 -n 128 -d 0,28672 -r 2 -t 4 2>&1 | grep -E "pp512|tg128|error"
+    done ;;
+  moe)
+    export GGML_BACKEND_PATH=$PLUGIN; mkdir -p /tmp/b200_models; f=/tmp/b200_models/mixtral-8x7b-q4_k_m.gguf
+    [ -f $f ] || python tools/make_gguf.py mixtral-8x7b q4_k_m $f > /dev/null
+    timeout 600 $B/llama-bench -m $f -ngl 99 -fa 1 -p 512 -n 128 -r 2 -t 4 2>&1 | grep -E "pp512|tg128|error"
+    timeout 600 $B/llama-batched-bench -m $f -ngl 99 -fa 1 -npp 128 -ntg 32 -npl 1,2,4,8,16,32,64 -c 16384 2>&1 | grep -E "^\|" ;;
   *) echo "unknown task $task"; exit 2 ;;
 esac
