@@ -54,19 +54,22 @@ __global__ void __launch_bounds__(256) mm_dense_kernel(const mm_params p) {
 
 // ---- few token columns (M <= 8): one CTA per weight row, K spread over the threads ----
 // (the router of a MoE layer: [n_embd] x [n_expert] in f32; K.Q and V.P of the non-flash attention path at decode)
-template <typename TA, typename TB>
-__global__ void __launch_bounds__(128) mv_dense_kernel(const mm_params p) {
+// NT threads per row: the MoE router (K = 4096, 8 rows, 8 CTAs in all) is pure latency -- with 128 threads each lane walked 32
+// dependent-looking iterations (21 us per call, 11 % of a Mixtral decode step); 512 threads and four loads in flight: ~4 us.
+template <typename TA, typename TB, int NT>
+__global__ void __launch_bounds__(NT) mv_dense_kernel(const mm_params p) {
     pdl_trigger(); pdl_wait();
     const int i12 = blockIdx.z % p.ne12, i13 = blockIdx.z / p.ne12;
     const char * A = p.a + (int64_t)(i12 / p.r2) * p.nba2 + (int64_t)(i13 / p.r3) * p.nba3 + (int64_t)blockIdx.x * p.nba1;
     const char * B = p.b + (int64_t)i12 * p.nbb2 + (int64_t)i13 * p.nbb3;
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int k = threadIdx.x; k < p.K; k += 128) {
+#pragma unroll 4
+    for (int k = threadIdx.x; k < p.K; k += NT) {
         const float av = ld_f<TA>(A + (int64_t)k * p.nba0);
 #pragma unroll
         for (int m = 0; m < 8; ++m) if (m < p.M) acc[m] = fmaf(av, ld_f<TB>(B + (int64_t)m * p.nbb1 + (int64_t)k * p.nbb0), acc[m]);
     }
-    __shared__ float part[4][8];
+    __shared__ float part[NT / 32][8];
 #pragma unroll
     for (int m = 0; m < 8; ++m) {
         float v = acc[m];
@@ -75,21 +78,26 @@ __global__ void __launch_bounds__(128) mv_dense_kernel(const mm_params p) {
         if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5][m] = v;
     }
     __syncthreads();
-    if (threadIdx.x < p.M)
-        *(float *)(p.d + (int64_t)threadIdx.x * p.nbd1 + (int64_t)i12 * p.nbd2 + (int64_t)i13 * p.nbd3 + (int64_t)blockIdx.x * 4) =
-            part[0][threadIdx.x] + part[1][threadIdx.x] + part[2][threadIdx.x] + part[3][threadIdx.x];
+    if (threadIdx.x < p.M) {
+        float v = 0.0f;
+#pragma unroll
+        for (int w = 0; w < NT / 32; ++w) v += part[w][threadIdx.x];
+        *(float *)(p.d + (int64_t)threadIdx.x * p.nbd1 + (int64_t)i12 * p.nbd2 + (int64_t)i13 * p.nbd3 + (int64_t)blockIdx.x * 4) = v;
+    }
 }
 
 template <typename TA, typename TB>
 static int mm_dense_launch(const mm_params & p, int nz, cudaStream_t st) {
     if (p.M <= 8 && p.N <= 2147483647 / 1) {
         cudaLaunchConfig_t lc = {};
-        lc.gridDim = dim3(p.N, 1, nz); lc.blockDim = dim3(128); lc.stream = st;
+        const bool wide = p.K >= 2048 && (int64_t)p.N * nz <= 1024;       // few long rows: more threads per row
+        lc.gridDim = dim3(p.N, 1, nz); lc.blockDim = dim3(wide ? 512 : 128); lc.stream = st;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[0].val.programmaticStreamSerializationAllowed = 1;
         lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
-        B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, mv_dense_kernel<TA, TB>, p));
+        if (wide) B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, mv_dense_kernel<TA, TB, 512>, p));
+        else B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, mv_dense_kernel<TA, TB, 128>, p));
         ++g_launches;
         return 0;
     }
@@ -190,8 +198,17 @@ static bool use_mmq_id(const b200_tensor * as, const b200_tensor * b, const b200
     if (ids->ne[1] < mmq_id_min_t() || as->nb[2] != as->ne[1] * as->nb[1] || as->ne[2] > 4096 || (ids->nb[1] & 3) || ids->nb[0] != 4) return false;
     return b200_mul_mat_q_supported(as->type, as->data, as->nb[1], (int)as->ne[0]) != 0 && (b->nb[1] & 3) == 0 && (b->nb[2] & 3) == 0;
 }
+// one token, K-quant experts: the register-resident GEMV takes the (up to 3) chosen experts as a group launch; it needs the
+// activation columns quantised first (scratch: one 400-byte item per 256 values and column)
+static bool use_mmvqr_id(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids) {
+    static const bool on = [] { const char * e = getenv("B200_MMVQR_ID"); return !e || atoi(e) != 0; }();
+    return on && (as->type == T_Q4_K || as->type == T_Q6_K) && ids->ne[1] == 1 && ids->ne[0] <= 3 && as->ne[0] % 256 == 0 && (b->nb[1] & 15) == 0 &&
+           ((uintptr_t)b->data & 15) == 0 && (as->nb[2] & 15) == 0;
+}
 extern "C" int64_t b200_mul_mat_id_scratch_bytes(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids) {
-    if (!is_quant(as->type) || !use_mmq_id(as, b, ids)) return 0;
+    if (!is_quant(as->type)) return 0;
+    if (use_mmvqr_id(as, b, ids)) return b->ne[1] * (as->ne[0] / 256) * ACT_ITEM + 256;
+    if (!use_mmq_id(as, b, ids)) return 0;
     return b200_mul_mat_id_q_scratch_bytes((int)as->ne[0], (int)ids->ne[0], (int)ids->ne[1], (int)as->ne[2]);
 }
 
@@ -224,5 +241,16 @@ extern "C" int b200_op_mul_mat_id(const b200_tensor * as, const b200_tensor * b,
     g.d_sy = dst->nb[1] / 4; g.d_sz = dst->nb[2] / 4;
     g.ids = (const int32_t *)ids->data; g.ids_sz = ids->nb[1] / 4;
     g.pdl = -1;
+    if (use_mmvqr_id(as, b, ids) && scratch && scratch_bytes >= b->ne[1] * (K / 256) * ACT_ITEM + 256) {
+        // quantise the activation column(s) once, then one group launch of the register-resident kernel over the chosen experts
+        void * xq = (void *)(((uintptr_t)scratch + 255) & ~(uintptr_t)255);
+        b200_mmvq_args h = g;
+        h.Xq = xq;
+        if (b200_mmvq_fusable(&h, 0, nullptr, nullptr)) {
+            const int rc = b200_quantize_acts((const float *)b->data, b->nb[1] / 4, xq, K, (int)b->ne[1], stream);
+            if (rc) return rc;
+            return b200_mul_mat_vec_q_ex(&h, stream);
+        }
+    }
     return b200_mul_mat_vec_q_ex(&g, stream);
 }

@@ -51,13 +51,24 @@ static bool fuse_ok(const b200_mmvq_args * a, int ng) {
 // stream == (cudaStream_t)-1: eligibility check only (returns 0 when the call would be launched)
 int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * const * dst, const int * N, cudaStream_t stream) {
     const bool probe = stream == (cudaStream_t)-1;
+    // MUL_MAT_ID for one token: slot y of the router's choice becomes matrix y of a group launch; the kernel adds ids[y] * w_sy to
+    // the base of the expert stack after its PDL wait (mmvq_r.cuh)
+    const void * Wid[3]; float * Did[3]; int Nid[3];
+    const bool by_id = a->ids != nullptr;
+    if (by_id) {
+        const int ny = std::max(1, a->ny);
+        if (ng != 1 || ny > 3 || std::max(1, a->nz) != 1 || !a->Xq || a->fuse_resid || a->fuse_sum || a->norm_x || a->rope || a->dbg_sumi ||
+            a->hs_wait || a->hs_counter || std::max(1, a->w_div_y) != 1 || a->xq_sy || (a->w_sy & 15)) return MMVQR_SKIP;
+        for (int y = 0; y < ny; ++y) { Wid[y] = W[0]; Did[y] = probe ? nullptr : dst[0] + (int64_t)y * a->d_sy; Nid[y] = N[0]; }
+        W = Wid; dst = Did; N = Nid; ng = ny;
+    }
     static const int on = env_i("B200_MMVQR", 1), cps = std::max(1, std::min(2, env_i("B200_MMVQR_CPS", 2))),
                      smem_kb = env_i("B200_MMVQR_SMEM_KB", 112), stage_kb = env_i("B200_MMVQR_STAGE_KB", 36),
                      max_stages = std::max(1, std::min(8, env_i("B200_MMVQR_NS", 8))), eU = env_i("B200_MMVQR_U", 0),
                      ramp = env_i("B200_MMVQR_RAMP", 0),          // short first stages: measured slower (per-stage hand-over cost), kept for tuning runs
                      small_mb = env_i("B200_MMVQR_SMALL_MB", 0), stagger = env_i("B200_MMVQR_STAGGER", 0);
     if (!fuse_ok(a, ng)) return MMVQR_SKIP;
-    if (!on || a->M != 1 || (!a->Xq && !a->norm_x) || a->ids || std::max(1, a->ny) != 1 || std::max(1, a->nz) != 1) return MMVQR_SKIP;
+    if (!on || a->M != 1 || (!a->Xq && !a->norm_x) || (!by_id && std::max(1, a->ny) != 1) || std::max(1, a->nz) != 1) return MMVQR_SKIP;
     if (a->type != T_Q4_K && a->type != T_Q6_K) return MMVQR_SKIP;
     if (a->dbg_sumi && ng != 1) return MMVQR_SKIP;
     const int K = a->K;
@@ -134,6 +145,10 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     p.R = R; p.nstages = nstages; p.stage_bytes = stage_bytes;
     p.r0 = q0; p.r1 = q1; p.r2 = q2; p.stagger = stagger;
     p.dbg_sumi = a->dbg_sumi;
+    if (by_id) {
+        p.ids = a->ids; p.w_expert = a->w_sy;
+        for (int g = 0; g < ng; ++g) p.xq_col[g] = a->x_mod_y > 0 ? g % a->x_mod_y : g;
+    }
     B200_HS_FROM_ARGS(p.hs, a);
     mmvqr_launch_cfg c;
     c.grid = dim3(used, 1, 1);

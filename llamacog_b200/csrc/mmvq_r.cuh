@@ -58,6 +58,10 @@ struct mmvqr_params {
     int rmode[3]; float * rout[3]; char * rcell[3]; char * const * rslot[3]; int rctype[3], rcesz[3], rhd[3];
     const int32_t * rpos; const float * rff; rope_dev rp;
     hs_params hs;            // row-split hand-over folded into the launch (common.cuh)
+    // MUL_MAT_ID at batch 1 (reference mmvq.cu:161-164 ids_dst path): matrix g is expert ids[g] of the stack at Wg[g] (w_expert bytes per
+    // expert), read on the device after the PDL wait (the ids come out of the router kernels of the same step); its activations
+    // are column xq_col[g] of Xq
+    const int32_t * ids; int64_t w_expert; int xq_col[3];
 };
 
 struct hacts { int q[4][8]; float d8[4], dsq[4]; int m32a[4], m32b[4]; };
@@ -200,7 +204,7 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
         // weight prefetch in the SM's copy engine: norm weights and the first stage before the wait, the row right after
         // it, the other stages behind the row.  (296 CTAs reading the same 16 KB with ordinary loads took 2-8 us, the bulk
         // copies of the same lines about 1 us: profiles/r01_ktrace_tg_v6.txt.)
-        if (lane == 0) {
+        if (lane == 0 && !p.ids) {
             if (NORM) { mbar_expect_tx(wbar, (uint32_t)p.K * 4); bulk_g2s(smem_u32(ws), p.nw, (uint32_t)p.K * 4, wbar); }
             for (int s = 0; s < min(nst, (NORM || p.stagger) ? 1 : p.nstages); ++s) issue(s);
             if (!NORM && p.stagger && nst > 1) { mbar_wait(full0, 0); for (int s = 1; s < min(nst, p.nstages); ++s) issue(s); }
@@ -220,11 +224,13 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
         }
         pdl_wait();           // the activations come from the previous kernel; dst may still be read by it
         if (lane == 0) hs_wait_acts(p.hs);      // row split, peer side: the main device's broadcast has landed
+        if (p.ids) Wc += (int64_t)p.ids[g] * p.w_expert;      // the expert the router chose for slot g (known only now)
         if (lane == 0) {      // one coalesced copy of the column; the consumers pick their registers out of shared memory
             const uint32_t ab = NORM ? (uint32_t)p.K * 4 : (uint32_t)p.BPR * ACT_ITEM;
             mbar_expect_tx(actbar, ab);
-            bulk_g2s(NORM ? smem_u32(xs) : smem_u32(act), NORM ? (const void *)p.nx : (const void *)p.Xq, ab, actbar);
+            bulk_g2s(NORM ? smem_u32(xs) : smem_u32(act), NORM ? (const void *)p.nx : (const void *)(p.Xq + (size_t)(p.ids ? p.xq_col[g] : 0) * ab), ab, actbar);
             if (NORM) for (int s = 1; s < min(nst, p.nstages); ++s) issue(s);
+            if (p.ids) for (int s = 0; s < min(nst, p.nstages); ++s) issue(s);
         }
         if (p.resid) {        // this CTA's rows of the residual, fetched while the first stage is being multiplied
             for (int o = lane; o < nrows; o += 32) rsd[o] = p.resid[row_lo + o];

@@ -12,6 +12,7 @@
 #   refcuda [models]        the reference's own ggml-cuda (sm_100 build) next to the plugin (tools/gpu_ref_cuda.sh)
 #   loadtime                model load wall time, staged vs plain upload (tools/gpu_load_time.sh)
 #   config3                 Llama-3-8B Q8_0 with f16 and q8_0 KV cache: pp512 / tg128 at depth 0 and at 28672
+#   cpu                     the reference CPU backend on the box's host cores: 1B Q4_0 pp512 / tg128 (config 1), 8B Q4_K_M pp64 / tg16
 #   moe                     Mixtral-8x7B Q4_K_M pp512 / tg128 and llama-batched-bench
 set -u
 export LD_LIBRARY_PATH=$PWD/baseline/_ref/lib:$PWD/llamacog_b200:${LD_LIBRARY_PATH:-}
@@ -57,10 +58,15 @@ case $task in
       echo "=== Llama-3-8B Q8_0, $kv KV cache"
       timeout 600 $B/llama-bench -m $f -ngl 99 -fa 1 -ctk $kv -ctv $kv -p 512 -n 128 -d 0,28672 -r 2 -t 4 2>&1 | grep -E "pp512|tg128|error"
     done ;;
+  cpu)
+    unset GGML_BACKEND_PATH; mkdir -p /tmp/b200_models; T=$(nproc)
+    f=/tmp/b200_models/llama3.2-1b-q4_0.gguf; [ -f $f ] || python tools/make_gguf.py llama3.2-1b q4_0 $f > /dev/null
+    echo "=== reference CPU backend, $T threads"; timeout 900 $B/llama-bench -m $f -ngl 0 -p 512 -n 128 -r 2 -t $T 2>&1 | grep -E "pp512|tg128|error"
+    f=$(model); timeout 900 $B/llama-bench -m $f -ngl 0 -p 64 -n 16 -r 1 -t $T 2>&1 | grep -E "pp64|tg16|error" ;;
   moe)
     export GGML_BACKEND_PATH=$PLUGIN; mkdir -p /tmp/b200_models; f=/tmp/b200_models/mixtral-8x7b-q4_k_m.gguf
     [ -f $f ] || python tools/make_gguf.py mixtral-8x7b q4_k_m $f > /dev/null
     timeout 600 $B/llama-bench -m $f -ngl 99 -fa 1 -p 512 -n 128 -r 2 -t 4 2>&1 | grep -E "pp512|tg128|error"
-    timeout 600 $B/llama-batched-bench -m $f -ngl 99 -fa 1 -npp 128 -ntg 32 -npl 1,2,4,8,16,32,64 -c 16384 2>&1 | grep -E "^\|" ;;
+    timeout 600 $B/llama-batched-bench -m $f -ngl 99 -fa -npp 128 -ntg 32 -npl 1,2,4,8,16,32,64 -c 16384 2>&1 | grep -E "^\|" ;;
   *) echo "unknown task $task"; exit 2 ;;
 esac
