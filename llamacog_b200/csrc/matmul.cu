@@ -193,7 +193,7 @@ extern "C" int b200_op_mul_mat(const b200_tensor * a, const b200_tensor * b, con
 }
 
 // batches: rows sorted by expert + tensor-core MMQ (mmq.cu); a few tokens: one GEMV per (token, expert) pair
-static int mmq_id_min_t() { static const int v = [] { const char * e = getenv("B200_MMQ_ID_MIN_T"); return e ? atoi(e) : 9; }(); return v; }
+static int mmq_id_min_t() { static const int v = [] { const char * e = getenv("B200_MMQ_ID_MIN_T"); return e ? atoi(e) : 3; }(); return v; }
 static bool use_mmq_id(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids) {
     if (ids->ne[1] < mmq_id_min_t() || as->nb[2] != as->ne[1] * as->nb[1] || as->ne[2] > 4096 || (ids->nb[1] & 3) || ids->nb[0] != 4) return false;
     return b200_mul_mat_q_supported(as->type, as->data, as->nb[1], (int)as->ne[0]) != 0 && (b->nb[1] & 3) == 0 && (b->nb[2] & 3) == 0;

@@ -8,7 +8,10 @@
 // {char name[64]; int op; int ne1; int64 n; double nmse} is written per node: the per-node parity twin
 // (tests/test_gpu_plugin.py::test_per_node_parity_with_reference_cpu_backend).
 //
-// usage: logits_check <model.gguf> <out.bin> <ngl> <flash_attn 0|1> <n_prompt> <n_decode> [n_ubatch] [none|layer|row|-] [nodes.bin]
+// An eleventh argument sets the tokens per decode step (default 1): steps of 9 .. 64 tokens repeat their shapes like single-token
+// decode does, which is what the plugin's CUDA-graph replay of batched decode relies on (the logits of a step's last token are written).
+//
+// usage: logits_check <model.gguf> <out.bin> <ngl> <flash_attn 0|1> <n_prompt> <n_decode> [n_ubatch] [none|layer|row|-] [nodes.bin|-] [step]
 #include "llama.h"
 #include "ggml-backend.h"
 #include "ggml.h"
@@ -102,9 +105,10 @@ int main(int argc, char ** argv) {
     llama_model * model = llama_model_load_from_file(path, mp);
     if (!model) { fprintf(stderr, "cannot load %s\n", path); return 1; }
     llama_context_params cp = llama_context_default_params();
-    cp.n_ctx = n_prompt + n_decode + 8; cp.n_batch = n_prompt > n_ubatch ? n_prompt : n_ubatch; cp.n_ubatch = n_ubatch;
+    cp.n_ctx = n_prompt + n_decode * (argc > 10 ? atoi(argv[10]) : 1) + 8; cp.n_batch = n_prompt > n_ubatch ? n_prompt : n_ubatch; cp.n_ubatch = n_ubatch;
     cp.flash_attn = fa != 0; cp.n_threads = 16; cp.n_threads_batch = 16;
-    if (argc > 9) {
+    const int step = argc > 10 ? atoi(argv[10]) : 1;
+    if (argc > 9 && strcmp(argv[9], "-") != 0) {
         g_nodes = fopen(argv[9], "wb");
         if (!g_nodes) return 1;
         g_cpu = ggml_backend_init_by_type(GGML_BACKEND_DEVICE_TYPE_CPU, nullptr);
@@ -114,7 +118,7 @@ int main(int argc, char ** argv) {
     llama_context * ctx = llama_init_from_model(model, cp);
     if (!ctx) { fprintf(stderr, "cannot create the context\n"); return 1; }
     const int n_vocab = llama_vocab_n_tokens(llama_model_get_vocab(model));
-    std::vector<llama_token> toks(n_prompt + n_decode);
+    std::vector<llama_token> toks(n_prompt + n_decode * step);
     for (size_t i = 0; i < toks.size(); ++i) toks[i] = (llama_token)((i * 7919u + 13u) % (unsigned)n_vocab);
     FILE * f = fopen(out, "wb");
     if (!f) return 1;
@@ -122,7 +126,7 @@ int main(int argc, char ** argv) {
     if (llama_decode(ctx, llama_batch_get_one(toks.data(), n_prompt)) != 0) { fprintf(stderr, "prefill failed\n"); return 1; }
     fwrite(llama_get_logits_ith(ctx, -1), sizeof(float), n_vocab, f);
     for (int d = 0; d < n_decode; ++d) {
-        if (llama_decode(ctx, llama_batch_get_one(&toks[n_prompt + d], 1)) != 0) { fprintf(stderr, "decode failed\n"); return 1; }
+        if (llama_decode(ctx, llama_batch_get_one(&toks[n_prompt + d * step], step)) != 0) { fprintf(stderr, "decode failed\n"); return 1; }
         fwrite(llama_get_logits_ith(ctx, -1), sizeof(float), n_vocab, f);
     }
     fclose(f);

@@ -65,7 +65,7 @@ def test_llama_bench_tiny_model_runs_on_plugin(tmp_path):
             assert all(x["avg_ts"] > 0 for x in res)
 
 
-def _logits(model, out, ngl, fa, n_prompt, n_decode, plugin, split=None, extra_env=None):
+def _logits(model, out, ngl, fa, n_prompt, n_decode, plugin, split=None, extra_env=None, step=None):
     import numpy as np
     env = _env()
     env.update(extra_env or {})
@@ -75,6 +75,8 @@ def _logits(model, out, ngl, fa, n_prompt, n_decode, plugin, split=None, extra_e
     if not os.path.exists(exe):
         pytest.fail("tests/host/build/logits_check missing: run __graft_entry__.build() in the build container")
     cmd = [exe, model, out, str(ngl), str(fa), str(n_prompt), str(n_decode)] + (["512", split] if split else [])
+    if step:
+        cmd = [exe, model, out, str(ngl), str(fa), str(n_prompt), str(n_decode), "512", split or "-", "-", str(step)]
     r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     raw = np.fromfile(out, dtype=np.uint8)
@@ -104,6 +106,26 @@ def test_logits_match_reference_cpu_backend(tmp_path, preset, fa, n_prompt):
     for i in range(ref.shape[0]):
         bar = 4.0 * nmse(self_[i], ref[i]) + 1e-3
         assert nmse(got[i], ref[i]) < bar, (i, nmse(got[i], ref[i]), bar)
+
+
+@pytest.mark.parametrize("preset,step", [("tiny", 12), ("tiny-moe", 12), ("tiny-moe", 4), ("llama3.2-1b", 24)])
+def test_batched_decode_graph_replay_matches_eager(tmp_path, preset, step):
+    """Decode steps of 4 .. 64 tokens (llama-batched-bench, servers) repeat their shapes; the plugin captures them into a CUDA graph on
+    the second sighting and replays it (B200_GRAPH_MAX_TOKENS, default 64): tensor-core MMQ, sorted MUL_MAT_ID, tensor-core
+    attention and the K/V stores through the pointer table, all under replay.  Six steps: logits bit-identical to the eager run
+    (B200_CUDA_GRAPHS=0), and within the end-to-end bar of the reference CPU backend."""
+    import numpy as np
+    _need()
+    model = str(tmp_path / (preset + ".gguf"))
+    subprocess.check_call([sys.executable, os.path.join(ROOT, "tools", "make_gguf.py"), preset, "q4_k_m", model], stdout=subprocess.DEVNULL)
+    got = _logits(model, str(tmp_path / "g.bin"), 99, 1, 40, 6, plugin=True, step=step, extra_env={"B200_TIMING": "1"})
+    eager = _logits(model, str(tmp_path / "e.bin"), 99, 1, 40, 6, plugin=True, step=step, extra_env={"B200_CUDA_GRAPHS": "0"})
+    assert got.shape == eager.shape and got.shape[0] == 7
+    assert np.array_equal(got.view(np.uint32), eager.view(np.uint32))
+    ref = _logits(model, str(tmp_path / "c.bin"), 0, 1, 40, 6, plugin=False, step=step)
+    for i in range(7):
+        e = float(((got[i].astype(np.float64) - ref[i]) ** 2).sum() / (ref[i].astype(np.float64) ** 2).sum())
+        assert e < 2e-2, (i, e)
 
 
 def _nodes(path):
