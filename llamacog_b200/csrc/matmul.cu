@@ -61,13 +61,14 @@ __global__ void __launch_bounds__(NT) mv_dense_kernel(const mm_params p) {
     pdl_trigger(); pdl_wait();
     const int i12 = blockIdx.z % p.ne12, i13 = blockIdx.z / p.ne12;
     const char * A = p.a + (int64_t)(i12 / p.r2) * p.nba2 + (int64_t)(i13 / p.r3) * p.nba3 + (int64_t)blockIdx.x * p.nba1;
-    const char * B = p.b + (int64_t)i12 * p.nbb2 + (int64_t)i13 * p.nbb3;
+    const int m0 = 8 * blockIdx.y, mc = min(8, p.M - m0);        // this CTA's chunk of (up to 8) token columns
+    const char * B = p.b + (int64_t)i12 * p.nbb2 + (int64_t)i13 * p.nbb3 + (int64_t)m0 * p.nbb1;
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll 4
     for (int k = threadIdx.x; k < p.K; k += NT) {
         const float av = ld_f<TA>(A + (int64_t)k * p.nba0);
 #pragma unroll
-        for (int m = 0; m < 8; ++m) if (m < p.M) acc[m] = fmaf(av, ld_f<TB>(B + (int64_t)m * p.nbb1 + (int64_t)k * p.nbb0), acc[m]);
+        for (int m = 0; m < 8; ++m) if (m < mc) acc[m] = fmaf(av, ld_f<TB>(B + (int64_t)m * p.nbb1 + (int64_t)k * p.nbb0), acc[m]);
     }
     __shared__ float part[NT / 32][8];
 #pragma unroll
@@ -78,20 +79,22 @@ __global__ void __launch_bounds__(NT) mv_dense_kernel(const mm_params p) {
         if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5][m] = v;
     }
     __syncthreads();
-    if (threadIdx.x < p.M) {
+    if (threadIdx.x < mc) {
         float v = 0.0f;
 #pragma unroll
         for (int w = 0; w < NT / 32; ++w) v += part[w][threadIdx.x];
-        *(float *)(p.d + (int64_t)threadIdx.x * p.nbd1 + (int64_t)i12 * p.nbd2 + (int64_t)i13 * p.nbd3 + (int64_t)blockIdx.x * 4) = v;
+        *(float *)(p.d + (int64_t)(m0 + threadIdx.x) * p.nbd1 + (int64_t)i12 * p.nbd2 + (int64_t)i13 * p.nbd3 + (int64_t)blockIdx.x * 4) = v;
     }
 }
 
 template <typename TA, typename TB>
 static int mm_dense_launch(const mm_params & p, int nz, cudaStream_t st) {
-    if (p.M <= 8 && p.N <= 2147483647 / 1) {
+    // few token columns, or a few rows x a modest batch (the MoE router of a batched decode step: 8 rows x 9 .. 64 tokens went to the
+    // 32 x 32 tile kernel as ONE CTA, 276 us per call -- most of the gap between 8 and 12 sequences in llama-batched-bench)
+    if (p.M <= 8 || (p.N <= 64 && p.M <= 512)) {
         cudaLaunchConfig_t lc = {};
-        const bool wide = p.K >= 2048 && (int64_t)p.N * nz <= 1024;       // few long rows: more threads per row
-        lc.gridDim = dim3(p.N, 1, nz); lc.blockDim = dim3(wide ? 512 : 128); lc.stream = st;
+        const bool wide = p.K >= 2048 && (int64_t)p.N * nz * ((p.M + 7) / 8) <= 1024;       // few long rows: more threads per row
+        lc.gridDim = dim3(p.N, (p.M + 7) / 8, nz); lc.blockDim = dim3(wide ? 512 : 128); lc.stream = st;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[0].val.programmaticStreamSerializationAllowed = 1;

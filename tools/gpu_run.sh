@@ -56,7 +56,7 @@ case $task in
     [ -f $f ] || python tools/make_gguf.py llama3-8b q8_0 $f > /dev/null
     for kv in f16 q8_0; do
       echo "=== Llama-3-8B Q8_0, $kv KV cache"
-      timeout 600 $B/llama-bench -m $f -ngl 99 -fa 1 -ctk $kv -ctv $kv -p 512 -n 128 -d 0,28672 -r 2 -t 4 2>&1 | grep -E "pp512|tg128|error"
+      timeout 600 $B/llama-bench -m $f -ngl 99 -fa 1 -ctk $kv -ctv $kv -p 512 -n 128 -d 0,28672 -r 4 -t 4 2>&1 | grep -E "pp512|tg128|error"
     done ;;
   cpu)
     unset GGML_BACKEND_PATH; mkdir -p /tmp/b200_models; T=$(nproc)
