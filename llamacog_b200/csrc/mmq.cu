@@ -301,6 +301,10 @@ struct mmq_params {
     // grouped launch (matrices of one type and K that read the same activations, e.g. q/k/v): group g owns the row tiles
     // [gy[g], gy[g+1]) of grid.y, its own tensor map (wmap / wmap1 / wmap2), destination and row count
     int ngroup; int gy[4]; float * gdst[3]; int64_t gds[3]; int gN[3];
+    // split along K for launches of one token tile (M <= tn: batched decode, short prompts), whose grid would otherwise be N / 128
+    // CTAs (32 for a 4096-row matrix on 148 SMs): CTA z multiplies K blocks [z * nkb, (z + 1) * nkb) into part[z][M][part_ds]
+    // (group g at column gcol[g]); ksplit_reduce_kernel adds the slices in fixed order.  ksplit <= 1: off.
+    int ksplit; float * part; int part_ds; int gcol[3];
 };
 constexpr int TRACE_N = 512;
 #ifdef B200_MMQ_TRACE
@@ -332,13 +336,15 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap0, const __grid_constant__ CU
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const CUtensorMap * wm = &wmap0;
-    float * dst_g = p.dst; int64_t ds_g = p.ds; int N_g = p.N; int by = blockIdx.y;
+    float * dst_g = p.dst; int64_t ds_g = p.ds; int N_g = p.N; int by = blockIdx.y; int gcol = 0;
     if (p.ngroup > 1) {
         const int g = by >= p.gy[2] ? 2 : by >= p.gy[1] ? 1 : 0;
         by -= p.gy[g];
         wm = g == 0 ? &wmap0 : g == 1 ? &wmap1 : &wmap2;
-        dst_g = p.gdst[g]; ds_g = p.gds[g]; N_g = p.gN[g];
+        dst_g = p.gdst[g]; ds_g = p.gds[g]; N_g = p.gN[g]; gcol = p.gcol[g];
     }
+    const int ks = p.ksplit > 1 ? p.ksplit : 1;
+    if (ks > 1) { dst_g = p.part + (int64_t)blockIdx.z * p.M * p.part_ds + gcol; ds_g = p.part_ds; }
     int m0 = blockIdx.x * tn, m_end = p.M, w_row0 = by * 128;
     const int n0 = by * 128;
     if (p.moe_cnt) {                             // (launched without PDL: the routing tables are complete)
@@ -348,7 +354,8 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap0, const __grid_constant__ CU
         m_end = p.moe_off[blockIdx.z] + cnt;
         w_row0 += blockIdx.z * p.N;
     }
-    const int nkb = p.K >> 8, nsteps = nkb * 4;
+    const int nkb = (p.K >> 8) / ks, nsteps = nkb * 4;      // this CTA's K blocks: [kb0, kb0 + nkb)
+    const int kb0 = ks > 1 ? (int)blockIdx.z * nkb : 0;
     const uint32_t a_col0 = (uint32_t)p.tmem_cols - 32u * (uint32_t)na;
 
     if (threadIdx.x == 0) {
@@ -374,7 +381,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap0, const __grid_constant__ CU
                 mbar_wait_b(raw_empty + 8 * s, ((kb >> lg_nr) & 1) ^ 1);
                 trace(p, 0, kb);
                 mbar_expect_tx(raw_full + 8 * s, RAW);
-                tma_load_2d(sR + s * RAW, wm, (kb * DQ::STEP16) & ~7, w_row0, raw_full + 8 * s);     // 16-byte aligned start
+                tma_load_2d(sR + s * RAW, wm, ((kb0 + kb) * DQ::STEP16) & ~7, w_row0, raw_full + 8 * s);     // 16-byte aligned start
             }
         }
     } else if (warp == 3) {
@@ -385,7 +392,7 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap0, const __grid_constant__ CU
                 mbar_wait(b_empty + 8 * s, ph);
                 trace(p, 1, i);
                 mbar_expect_tx(b_full + 8 * s, b_slot);
-                tma_load_2d(sB + s * b_slot, &xmap, (i >> 2) * 256 + c * 64, m0, b_full + 8 * s);
+                tma_load_2d(sB + s * b_slot, &xmap, (kb0 + (i >> 2)) * 256 + c * 64, m0, b_full + 8 * s);
                 if (++s == nb) { s = 0; ph ^= 1; }
             }
         }
@@ -616,12 +623,69 @@ static int mmq_launch(const CUtensorMap & wmap, const CUtensorMap & xmap, const 
         configured[dev & 15] = smem;
     }
     cudaLaunchConfig_t lc = {};
-    lc.gridDim = dim3((p.M + p.tn - 1) / p.tn, p.ngroup > 1 ? p.gy[p.ngroup] : (p.N + 127) / 128, n_expert > 0 ? n_expert : 1); lc.blockDim = dim3(MMQ_THREADS); lc.dynamicSmemBytes = smem; lc.stream = st;
+    lc.gridDim = dim3((p.M + p.tn - 1) / p.tn, p.ngroup > 1 ? p.gy[p.ngroup] : (p.N + 127) / 128, n_expert > 0 ? n_expert : std::max(1, p.ksplit)); lc.blockDim = dim3(MMQ_THREADS); lc.dynamicSmemBytes = smem; lc.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = at; lc.numAttrs = pdl_default() && n_expert == 0 ? 1 : 0;       // the expert tables are read before griddepcontrol.wait
     B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, mmq_kernel<TYPE>, wmap, xmap, p, wmap1 ? *wmap1 : wmap, wmap2 ? *wmap2 : wmap));
+    ++g_launches;
+    return 0;
+}
+
+// ---- split along K for one-token-tile launches ----
+__global__ void __launch_bounds__(256) ksplit_reduce_kernel(const float * __restrict__ part, int ks, int M, int part_ds, int ng,
+                                                            int c0, int c1, int c2, int n0, int n1, int n2,
+                                                            float * d0, float * d1, float * d2, int64_t s0, int64_t s1, int64_t s2) {
+    pdl_trigger(); pdl_wait();
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= (int64_t)M * part_ds) return;
+    const int m = (int)(i / part_ds), c = (int)(i % part_ds);
+    const int g = ng > 2 && c >= c2 ? 2 : ng > 1 && c >= c1 ? 1 : 0;
+    const int n = c - (g == 0 ? c0 : g == 1 ? c1 : c2);
+    if (n >= (g == 0 ? n0 : g == 1 ? n1 : n2)) return;
+    float v = 0.0f;
+    for (int z = 0; z < ks; ++z) v += part[((int64_t)z * M + m) * part_ds + c];      // fixed order: deterministic
+    float * d = g == 0 ? d0 : g == 1 ? d1 : d2;
+    d[(int64_t)m * (g == 0 ? s0 : g == 1 ? s1 : s2) + n] = v;
+}
+// One buffer per device, allocated once (a replayed CUDA graph keeps its address) at the first use outside stream capture.
+constexpr size_t KSPLIT_BYTES = (size_t)64 << 20;
+static float * ksplit_buffer(cudaStream_t st) {
+    static float * buf[16] = {nullptr};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
+    if (!buf[dev]) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return nullptr;
+        if (cudaMalloc((void **)&buf[dev], KSPLIT_BYTES) != cudaSuccess) { cudaGetLastError(); buf[dev] = nullptr; }
+    }
+    return buf[dev];
+}
+// how many slices: fill the SMs, keep at least 4 blocks per CTA, Q6_K slices in whole 8-block alignment periods
+static int plan_ksplit(int type, int K, int M, int tn, int ctas, int part_ds, cudaStream_t st, float ** part) {
+    static const int on = env_int("B200_MMQ_KSPLIT", 1);
+    *part = nullptr;
+    if (!on || M > tn || M > 32 || ctas <= 0 || ctas > 74) return 1;      // (one 32-token tile: batched decode steps, short prompts)
+    const int nkb = K >> 8, unit = type == T_Q6_K ? 8 : 1;
+    int ks = std::min(8, 148 / ctas);
+    while (ks > 1 && (nkb % (ks * unit) != 0 || nkb / ks < 4)) --ks;
+    if (ks < 2 || (size_t)ks * M * part_ds * 4 > KSPLIT_BYTES) return 1;
+    *part = ksplit_buffer(st);
+    return *part ? ks : 1;
+}
+static int ksplit_reduce(const mmq_params & p, cudaStream_t st) {
+    const int ng = std::max(1, p.ngroup);
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)(((int64_t)p.M * p.part_ds + 255) / 256)); lc.blockDim = dim3(256); lc.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
+    if (ng == 1) B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, ksplit_reduce_kernel, (const float *)p.part, p.ksplit, p.M, p.part_ds, 1, 0, 0, 0, p.N, 0, 0,
+                                                    p.dst, (float *)nullptr, (float *)nullptr, p.ds, (int64_t)0, (int64_t)0));
+    else B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, ksplit_reduce_kernel, (const float *)p.part, p.ksplit, p.M, p.part_ds, ng, p.gcol[0], p.gcol[1], p.gcol[2],
+                                            p.gN[0], p.gN[1], p.gN[2], p.gdst[0], p.gdst[1], p.gdst[2], p.gds[0], p.gds[1], p.gds[2]));
     ++g_launches;
     return 0;
 }
@@ -702,14 +766,18 @@ extern "C" int b200_mul_mat_q_bf16(int type, const void * W, int64_t nb1, const 
         if (encode_tiled()(&xmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, xb, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return -5;
     }
+    p.part_ds = N;
+    p.ksplit = plan_ksplit(type, K, M, p.tn, (N + 127) / 128, p.part_ds, st, &p.part);
+    int rc = -1;
     switch (type) {
-        case T_Q4_0: return mmq_launch<T_Q4_0>(wmap, xmap, p, smem, st);
-        case T_Q8_0: return mmq_launch<T_Q8_0>(wmap, xmap, p, smem, st);
-        case T_Q4_K: return mmq_launch<T_Q4_K>(wmap, xmap, p, smem, st);
-        case T_Q5_K: return mmq_launch<T_Q5_K>(wmap, xmap, p, smem, st);
-        case T_Q6_K: return mmq_launch<T_Q6_K>(wmap, xmap, p, smem, st);
+        case T_Q4_0: rc = mmq_launch<T_Q4_0>(wmap, xmap, p, smem, st); break;
+        case T_Q8_0: rc = mmq_launch<T_Q8_0>(wmap, xmap, p, smem, st); break;
+        case T_Q4_K: rc = mmq_launch<T_Q4_K>(wmap, xmap, p, smem, st); break;
+        case T_Q5_K: rc = mmq_launch<T_Q5_K>(wmap, xmap, p, smem, st); break;
+        case T_Q6_K: rc = mmq_launch<T_Q6_K>(wmap, xmap, p, smem, st); break;
     }
-    return -1;
+    if (rc == 0 && p.ksplit > 1) rc = ksplit_reduce(p, st);
+    return rc;
 }
 
 // Up to three weight matrices of one type, K and row stride that read the same activations (q/k/v of a prefill batch) in one
@@ -760,14 +828,22 @@ extern "C" int b200_mul_mat_q_bf16_group(int type, int ng, const void * const * 
                            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return -5;
     }
     const CUtensorMap * w1 = &wmap[1], * w2 = ng > 2 ? &wmap[2] : &wmap[1];
-    switch (type) {
-        case T_Q4_0: return mmq_launch<T_Q4_0>(wmap[0], xmap, p, smem, st, 0, w1, w2);
-        case T_Q8_0: return mmq_launch<T_Q8_0>(wmap[0], xmap, p, smem, st, 0, w1, w2);
-        case T_Q4_K: return mmq_launch<T_Q4_K>(wmap[0], xmap, p, smem, st, 0, w1, w2);
-        case T_Q5_K: return mmq_launch<T_Q5_K>(wmap[0], xmap, p, smem, st, 0, w1, w2);
-        case T_Q6_K: return mmq_launch<T_Q6_K>(wmap[0], xmap, p, smem, st, 0, w1, w2);
+    {   // one token tile: slices along K (columns of the slices: the groups side by side)
+        int col = 0;
+        for (int g = 0; g < 3; ++g) { p.gcol[g] = col; if (g < ng) col += N[g]; }
+        p.part_ds = col;
+        p.ksplit = plan_ksplit(type, K, M, p.tn, y, p.part_ds, st, &p.part);
     }
-    return -1;
+    int rc = -1;
+    switch (type) {
+        case T_Q4_0: rc = mmq_launch<T_Q4_0>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
+        case T_Q8_0: rc = mmq_launch<T_Q8_0>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
+        case T_Q4_K: rc = mmq_launch<T_Q4_K>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
+        case T_Q5_K: rc = mmq_launch<T_Q5_K>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
+        case T_Q6_K: rc = mmq_launch<T_Q6_K>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
+    }
+    if (rc == 0 && p.ksplit > 1) rc = ksplit_reduce(p, st);
+    return rc;
 }
 
 extern "C" int b200_mul_mat_q(int type, const void * W, int64_t nb1, const float * X, int64_t xs, float * dst, int64_t ds,

@@ -117,6 +117,41 @@ def test_unsupported_shapes_are_refused():
         ops.mul_mat_q(O.QUANT_TYPES["q6_K"], W, torch.zeros(16, 256, device="cuda"), 4, 256)      # 210-byte row stride
 
 
+@pytest.mark.parametrize("name", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K"])
+@pytest.mark.parametrize("N,K,M", [(4096, 4096, 9), (1024, 14336, 32), (300, 8192, 17), (2048, 2048, 24)])
+def test_k_split_single_token_tile(name, N, K, M):
+    """Launches of one 32-token tile (batched decode steps, short prompts) whose grid would leave most SMs idle are split along K
+    (mmq.cu: plan_ksplit, slices summed in fixed order by ksplit_reduce_kernel): 2 .. 8 slices here, Q6_K in whole 8-block periods."""
+    t = O.QUANT_TYPES[name]
+    K = _k_for(name, K)
+    rng = np.random.default_rng(N + K + M)
+    W = O.random_quant_bytes(t, N, K, rng)
+    X = rng.uniform(-1, 1, (M, K)).astype(np.float32)
+    ops = _ops()
+    got = ops.mul_mat_q(t, _dev(W), torch.from_numpy(X).cuda(), N, K).cpu().numpy()
+    again = ops.mul_mat_q(t, _dev(W), torch.from_numpy(X).cuda(), N, K).cpu().numpy()
+    assert np.array_equal(got.view(np.uint32), again.view(np.uint32))      # deterministic
+    rows = rng.choice(N, min(N, 96), replace=False)                        # the oracle on a sample of the rows
+    ref = O.mul_mat_f32(t, np.ascontiguousarray(W.reshape(N, -1)[rows]), X, len(rows), K, M)
+    assert _nmse(got[:, rows], ref) < NMSE_BAR, _nmse(got[:, rows], ref)
+
+
+@pytest.mark.parametrize("name", ["q4_K", "q6_K"])
+def test_k_split_group_launch(name):
+    """q/k/v of a 12-token step in one split grid: every matrix against the oracle."""
+    ops = _ops()
+    t = O.QUANT_TYPES[name]
+    K, M, Ns = 4096, 12, (2048, 512, 512)
+    rng = np.random.default_rng(5)
+    Wn = [O.random_quant_bytes(t, n, K, rng) for n in Ns]
+    X = rng.uniform(-1, 1, (M, K)).astype(np.float32)
+    got = ops.mul_mat_q_group(t, [_dev(w) for w in Wn], list(Ns), torch.from_numpy(X).cuda(), K)
+    for g, n in enumerate(Ns):
+        rows = np.arange(0, n, 7)
+        ref = O.mul_mat_f32(t, np.ascontiguousarray(Wn[g].reshape(n, -1)[rows]), X, len(rows), K, M)
+        assert _nmse(got[g].cpu().numpy()[:, rows], ref) < NMSE_BAR, g
+
+
 @pytest.mark.parametrize("name", ["q4_K", "q6_K", "q8_0"])
 @pytest.mark.parametrize("Ns,M", [((4096, 1024, 1024), 512), ((512, 200), 77), ((1024, 1024, 384), 300)])
 def test_group_launch_equals_single_launches(name, Ns, M):
