@@ -70,7 +70,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     uint32_t d; asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo)); return d;
 }
 template <int OP> __device__ __forceinline__ float act_fn(float x) {
-    if constexpr (OP == B200_UNARY_SILU) return x / (1.0f + expf(-x));
+    if constexpr (OP == B200_UNARY_SILU) return silu_fn(x);
     else { const float c = 0.044715f, s = 0.79788456080286535587989211986876f; return 0.5f * x * (1.0f + tanhf(s * x * (1.0f + c * x * x))); }
 }
 // rows of K floats, flat over (row, float4); 8 consecutive threads = one 32-block of one row (K % 32 == 0)

@@ -157,7 +157,7 @@ extern "C" int b200_mul_mat_vec_q_ex(const b200_mmvq_args * a, void * stream) {
         const void * W1[1] = { a->W }; float * D1[1] = { a->dst }; const int N1[1] = { a->N };
         const int rc = mmvqr_try(a, 1, W1, D1, N1, (cudaStream_t)stream);
         if (rc != MMVQR_SKIP) return rc;
-        if (a->fuse_resid || a->fuse_sum || a->norm_x || a->rope) return -4;     // only that kernel has the fused prologue / epilogue
+        if (a->fuse_resid || a->fuse_sum || a->norm_x || a->rope || a->sm_act) return -4;     // only that kernel has the fused prologue / epilogue
     }
     const int pdl_env = pdl_default();
     for (int m0 = 0; m0 < a->M; m0 += mmax) {
@@ -209,7 +209,7 @@ extern "C" int b200_mul_mat_vec_q_group(const b200_mmvq_args * a, int ng, const 
     {
         const int rc = mmvqr_try(a, ng, W, dst, N, (cudaStream_t)stream);
         if (rc != MMVQR_SKIP) return rc;
-        if (a->fuse_resid || a->fuse_sum || a->norm_x || a->rope) return -4;
+        if (a->fuse_resid || a->fuse_sum || a->norm_x || a->rope || a->sm_act) return -4;
     }
     mmvq_params p = {};
     p.W = (const uint8_t *)W[0]; p.nb1 = a->nb1;

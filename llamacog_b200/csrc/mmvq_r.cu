@@ -44,6 +44,11 @@ static bool fuse_ok(const b200_mmvq_args * a, int ng) {
         if (!a->norm_w || !a->norm_y || !a->norm_out || a->K > 4096 || a->dbg_sumi) return false;
         if (!al16(a->norm_x) || !al16(a->norm_w) || !al16(a->norm_y) || !al16(a->norm_out)) return false;
     }
+    if (a->sm_act) {      // silu(gate) * up in the epilogue of a gate / up launch
+        if (ng != 2 || a->sm_op != B200_UNARY_SILU || !a->sm_out || !a->sm_counters || a->fuse_resid || a->rope || a->dbg_sumi || a->ids ||
+            a->hs_wait || a->hs_counter) return false;
+        if (!al16(a->sm_act) || !al16(a->sm_out) || !al16(a->sm_xq)) return false;
+    }
     return true;
 }
 
@@ -82,6 +87,7 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     if (a->nb1 != rb || rb % 16 || ((uintptr_t)a->Xq & 15)) return MMVQR_SKIP;
     int ntot = 0;
     const int unit = a->rope ? 2 : 1;                                 // rope epilogue: rows are dealt to the CTAs in pairs
+    if (a->sm_act && (N[0] != N[1] || N[0] % 32)) return MMVQR_SKIP;
     for (int g = 0; g < ng; ++g) {
         if (((uintptr_t)W[g] & 15) || N[g] <= 0 || N[g] % unit) return MMVQR_SKIP;
         if (a->rope && (a->rope->mode[g] == 1 || a->rope->mode[g] == 2) && N[g] % a->rope->head_dim[g]) return MMVQR_SKIP;
@@ -145,6 +151,10 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     p.R = R; p.nstages = nstages; p.stage_bytes = stage_bytes;
     p.r0 = q0; p.r1 = q1; p.r2 = q2; p.stagger = stagger;
     p.dbg_sumi = a->dbg_sumi;
+    if (a->sm_act) {
+        if (!al16(dst[0]) || !al16(dst[1])) return MMVQR_SKIP;
+        p.sm_act = a->sm_act; p.sm_out = a->sm_out; p.sm_xq = (uint8_t *)a->sm_xq; p.sm_cnt = a->sm_counters;
+    }
     if (by_id) {
         p.ids = a->ids; p.w_expert = a->w_sy;
         for (int g = 0; g < ng; ++g) p.xq_col[g] = a->x_mod_y > 0 ? g % a->x_mod_y : g;

@@ -62,7 +62,17 @@ struct mmvqr_params {
     // expert), read on the device after the PDL wait (the ids come out of the router kernels of the same step); its activations
     // are column xq_col[g] of Xq
     const int32_t * ids; int64_t w_expert; int xq_col[3];
+    // gate (matrix 0) / up (matrix 1) launch: the CTA that completes a 32-row block of both results computes silu(gate) * up and its
+    // q8 activations for that block (the arithmetic of unary_mul_kernel<SILU>, fused.cu): sm_cnt[b] counts the (matrix, CTA) pieces
+    // of block b that have been stored; the last one does the block and leaves the counter at zero for the next launch
+    float * sm_act; float * sm_out; uint8_t * sm_xq; unsigned * sm_cnt;
 };
+
+// the CTA (within its matrix' range of CTAs) that owns row n: the first `rem` CTAs have q + 1 rows, the others q
+__device__ __forceinline__ int sm_cta_of(int n, int q, int rem) {
+    const int cut = rem * (q + 1);
+    return n < cut ? n / (q + 1) : rem + (n - cut) / q;
+}
 
 struct hacts { int q[4][8]; float d8[4], dsq[4]; int m32a[4], m32b[4]; };
 
@@ -280,6 +290,37 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
             if (s == 0) ktrace_event(2);       // first stage consumed and stored
         }
         ktrace_event(3);                       // all rows of CTA 0 stored
+        if (p.sm_act) {
+            // gate / up: count this CTA's piece into every 32-row block it touched; whoever completes a block multiplies it out
+            __syncwarp();
+            __threadfence();                   // this warp's stores of Dc are visible before the count
+            const int b_lo = row_lo >> 5, b_hi = (row_lo + nrows - 1) >> 5;
+            for (int b = b_lo; b <= b_hi; ++b) {
+                int last = 0;
+                if (lane == 0) {
+                    int expect = 0;
+#pragma unroll
+                    for (int m = 0; m < 2; ++m)
+                        expect += sm_cta_of(32 * b + 31, p.rows_qg[m], p.rows_remg[m]) - sm_cta_of(32 * b, p.rows_qg[m], p.rows_remg[m]) + 1;
+                    last = atomicAdd(&p.sm_cnt[b], 1u) + 1u == (unsigned)expect;
+                    if (last) p.sm_cnt[b] = 0u;
+                }
+                last = __shfl_sync(0xffffffffu, last, 0);
+                if (!last) continue;           // (warp-uniform)
+                __threadfence();               // the other pieces' stores are visible after the count
+                float4 y = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                const bool in = lane < 8;
+                if (in) {
+                    const int i = 8 * b + lane;
+                    const float4 x = __ldcg(reinterpret_cast<const float4 *>(p.Dg[0]) + i), u = __ldcg(reinterpret_cast<const float4 *>(p.Dg[1]) + i);
+                    const float4 a = make_float4(silu_fn(x.x), silu_fn(x.y), silu_fn(x.z), silu_fn(x.w));
+                    y = make_float4(a.x * u.x, a.y * u.y, a.z * u.z, a.w * u.w);
+                    reinterpret_cast<float4 *>(p.sm_act)[i] = a;
+                    reinterpret_cast<float4 *>(p.sm_out)[i] = y;
+                }
+                if (p.sm_xq) quant_block_store(y, in ? b : 0, lane & 7, in, p.sm_xq);
+            }
+        }
         if (p.hs.counter) {                    // row split: the last CTA of the launch lowers / raises / awaits the hand-over flags
             __syncwarp();
             if (lane == 0) hs_finish(p.hs, gridDim.x);

@@ -282,6 +282,10 @@ __device__ __forceinline__ void quant_block_store(const float4 x, int jb, int su
     }
 }
 
+// SILU as every kernel that fuses it computes it (unary_mul_kernel, the gate / up epilogue of the batch-1 mat-vec): one expf, one
+// IEEE division, nothing the compiler could contract differently from one kernel to the next
+__device__ __forceinline__ float silu_fn(float x) { return x / (1.0f + expf(-x)); }
+
 // Straight-line part of q8_round4: the word of fast roundings and whether all four are trustworthy (no branch in here).
 __device__ __forceinline__ int q8_fast4(const float4 x, float inv, bool & ok) {
     const float r0 = x.x * inv, r1 = x.y * inv, r2 = x.z * inv, r3 = x.w * inv;

@@ -178,6 +178,48 @@ def test_gemv_residual_epilogue(tname, N, K):
     assert torch.equal(d2, d_ref + r)
 
 
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K"])
+@pytest.mark.parametrize("N,K,inplace", [(14336, 4096, False), (14336, 4096, True), (28672, 4096, False), (2048, 2048, True), (96, 1024, False), (8192, 2048, False)])
+def test_gemv_gate_up_silu_mul_epilogue(tname, N, K, inplace):
+    """silu(gate) * up and its q8 activations computed by the gate / up group launch itself (b200_mmvq_args.sm_*): the CTA that completes
+    a 32-row block of both results multiplies it out.  gate, up, act, out and the quantised column must equal, bit for bit, the group
+    launch followed by b200_op_unary_mul -- also with act / out written in place over gate / up (the graph allocator's choice), with the
+    norm prologue in the same launch, and on a second launch over the same counters (they must come back to zero)."""
+    import numpy as np
+    import oracle as O
+    ops = _ops(); L = ops.lib()
+    t = O.QUANT_TYPES[tname]
+    rng = np.random.default_rng(N + K)
+    Wg = torch.from_numpy(O.random_quant_bytes(t, N, K, rng).reshape(-1)).cuda()
+    Wu = torch.from_numpy(O.random_quant_bytes(t, N, K, rng).reshape(-1)).cuda()
+    torch.manual_seed(N + K)
+    x = torch.randn(1, K, device="cuda")
+    xq = ops.quantize_acts(x)
+    g_ref, u_ref = ops.mul_mat_vec_q_group(t, [Wg, Wu], [N, N], x, K, Xq=xq)
+    a_ref = torch.empty_like(g_ref); o_ref = torch.empty_like(g_ref); q_ref = torch.zeros((1, (N + 255) // 256 * 400), dtype=torch.uint8, device="cuda")
+    assert L.b200_op_unary_mul(C.c_int(10), C.byref(ops.as_b200(g_ref)), C.byref(ops.as_b200(a_ref)), C.byref(ops.as_b200(u_ref)), C.byref(ops.as_b200(o_ref)),
+                               C.c_void_p(q_ref.data_ptr()), C.c_int(0), _st(ops)) == 0
+    cnt = torch.zeros(2048, dtype=torch.int32, device="cuda")
+    for rep in range(2):
+        g = torch.empty(1, N, device="cuda"); u = torch.empty(1, N, device="cuda")
+        act = g if inplace else torch.empty(1, N, device="cuda")
+        out = u if inplace else torch.empty(1, N, device="cuda")
+        q = torch.zeros_like(q_ref)
+        a = _gemv_args(ops, t, Wg, N, K, g, Xq=xq.data_ptr(), sm_op=10, sm_act=act.data_ptr(), sm_out=out.data_ptr(), sm_xq=q.data_ptr(),
+                       sm_counters=cnt.data_ptr())
+        Wp = (C.c_void_p * 2)(Wg.data_ptr(), Wu.data_ptr()); Dp = (C.c_void_p * 2)(g.data_ptr(), u.data_ptr())
+        Np = (C.c_int * 2)(N, N); dsp = (C.c_int64 * 2)(N, N)
+        if not L.b200_mmvq_fusable(C.byref(a), C.c_int(2), Wp, Np):
+            pytest.skip("shape not taken by the register-resident kernel")
+        assert L.b200_mul_mat_vec_q_group(C.byref(a), C.c_int(2), Wp, Dp, Np, dsp, _st(ops)) == 0
+        torch.cuda.synchronize()
+        if not inplace:
+            assert torch.equal(g, g_ref) and torch.equal(u, u_ref)
+        assert torch.equal(act, a_ref) and torch.equal(out, o_ref)
+        assert _same_acts(q, q_ref)
+        assert int(cnt.abs().sum().item()) == 0
+
+
 def test_gemv_fusion_refused_when_not_eligible():
     """M = 2 does not run on the register-resident kernel: the fusable predicate says no and a call with fused fields fails
     loudly (-4) instead of silently dropping the fused work."""
