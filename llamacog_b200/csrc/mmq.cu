@@ -304,7 +304,9 @@ struct mmq_params {
     // split along K for launches of one token tile (M <= tn: batched decode, short prompts), whose grid would otherwise be N / 128
     // CTAs (32 for a 4096-row matrix on 148 SMs): CTA z multiplies K blocks [z * nkb, (z + 1) * nkb) into part[z][M][part_ds]
     // (group g at column gcol[g]); ksplit_reduce_kernel adds the slices in fixed order.  ksplit <= 1: off.
-    int ksplit; float * part; int part_ds; int gcol[3];
+    // In a grouped launch every matrix keeps the slice count its own launch would have (gks[g]; CTAs with z >= gks[g] leave at
+    // once): grouped and single launches add in the same order, so fused and unfused graphs stay bit-identical.
+    int ksplit; float * part; int part_ds; int gcol[3]; int gks[3];
 };
 constexpr int TRACE_N = 512;
 #ifdef B200_MMQ_TRACE
@@ -314,6 +316,8 @@ __device__ __forceinline__ void trace(const mmq_params & p, int ev, int idx) {
 #else
 __device__ __forceinline__ void trace(const mmq_params &, int, int) {}
 #endif
+
+__device__ __forceinline__ int by_group(const mmq_params & p, int by) { return by >= p.gy[2] ? 2 : by >= p.gy[1] ? 1 : 0; }
 
 constexpr int MMQ_THREADS = 640;            // TMA x2, MMA issue, TMEM allocator warps + 16 dequantiser warps
 constexpr int NA_MAX = 8;
@@ -343,7 +347,8 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap0, const __grid_constant__ CU
         wm = g == 0 ? &wmap0 : g == 1 ? &wmap1 : &wmap2;
         dst_g = p.gdst[g]; ds_g = p.gds[g]; N_g = p.gN[g]; gcol = p.gcol[g];
     }
-    const int ks = p.ksplit > 1 ? p.ksplit : 1;
+    const int ks = p.ksplit > 1 ? (p.ngroup > 1 ? p.gks[by_group(p, blockIdx.y)] : p.ksplit) : 1;
+    if (p.ksplit > 1 && !p.moe_cnt && (int)blockIdx.z >= ks) return;      // (before any barrier: the whole CTA leaves)
     if (ks > 1) { dst_g = p.part + (int64_t)blockIdx.z * p.M * p.part_ds + gcol; ds_g = p.part_ds; }
     int m0 = blockIdx.x * tn, m_end = p.M, w_row0 = by * 128;
     const int n0 = by * 128;
@@ -634,7 +639,7 @@ static int mmq_launch(const CUtensorMap & wmap, const CUtensorMap & xmap, const 
 }
 
 // ---- split along K for one-token-tile launches ----
-__global__ void __launch_bounds__(256) ksplit_reduce_kernel(const float * __restrict__ part, int ks, int M, int part_ds, int ng,
+__global__ void __launch_bounds__(256) ksplit_reduce_kernel(const float * __restrict__ part, int ks0, int ks1, int ks2, int M, int part_ds, int ng,
                                                             int c0, int c1, int c2, int n0, int n1, int n2,
                                                             float * d0, float * d1, float * d2, int64_t s0, int64_t s1, int64_t s2) {
     pdl_trigger(); pdl_wait();
@@ -644,6 +649,8 @@ __global__ void __launch_bounds__(256) ksplit_reduce_kernel(const float * __rest
     const int g = ng > 2 && c >= c2 ? 2 : ng > 1 && c >= c1 ? 1 : 0;
     const int n = c - (g == 0 ? c0 : g == 1 ? c1 : c2);
     if (n >= (g == 0 ? n0 : g == 1 ? n1 : n2)) return;
+    const int ks = g == 0 ? ks0 : g == 1 ? ks1 : ks2;
+    if (ks <= 1) return;                          // this matrix was not split: its CTAs wrote dst themselves
     float v = 0.0f;
     for (int z = 0; z < ks; ++z) v += part[((int64_t)z * M + m) * part_ds + c];      // fixed order: deterministic
     float * d = g == 0 ? d0 : g == 1 ? d1 : d2;
@@ -682,9 +689,9 @@ static int ksplit_reduce(const mmq_params & p, cudaStream_t st) {
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = at; lc.numAttrs = pdl_default() ? 1 : 0;
-    if (ng == 1) B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, ksplit_reduce_kernel, (const float *)p.part, p.ksplit, p.M, p.part_ds, 1, 0, 0, 0, p.N, 0, 0,
+    if (ng == 1) B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, ksplit_reduce_kernel, (const float *)p.part, p.ksplit, 0, 0, p.M, p.part_ds, 1, 0, 0, 0, p.N, 0, 0,
                                                     p.dst, (float *)nullptr, (float *)nullptr, p.ds, (int64_t)0, (int64_t)0));
-    else B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, ksplit_reduce_kernel, (const float *)p.part, p.ksplit, p.M, p.part_ds, ng, p.gcol[0], p.gcol[1], p.gcol[2],
+    else B200_CUDA_CHECK(cudaLaunchKernelEx(&lc, ksplit_reduce_kernel, (const float *)p.part, p.gks[0], p.gks[1], p.gks[2], p.M, p.part_ds, ng, p.gcol[0], p.gcol[1], p.gcol[2],
                                             p.gN[0], p.gN[1], p.gN[2], p.gdst[0], p.gdst[1], p.gdst[2], p.gds[0], p.gds[1], p.gds[2]));
     ++g_launches;
     return 0;
@@ -832,7 +839,14 @@ extern "C" int b200_mul_mat_q_bf16_group(int type, int ng, const void * const * 
         int col = 0;
         for (int g = 0; g < 3; ++g) { p.gcol[g] = col; if (g < ng) col += N[g]; }
         p.part_ds = col;
-        p.ksplit = plan_ksplit(type, K, M, p.tn, y, p.part_ds, st, &p.part);
+        p.ksplit = 1;
+        for (int g = 0; g < ng; ++g) {            // each matrix: the slice count of its own launch (8 slices of the whole width fit the buffer or nothing is split)
+            float * pb = nullptr;
+            p.gks[g] = plan_ksplit(type, K, M, p.tn, (N[g] + 127) / 128, N[g], st, &pb);
+            if ((size_t)8 * M * p.part_ds * 4 > KSPLIT_BYTES) p.gks[g] = 1;
+            if (p.gks[g] > 1) { p.part = pb; p.ksplit = std::max(p.ksplit, p.gks[g]); }
+        }
+        if (p.ksplit <= 1) { p.ksplit = 0; p.part = nullptr; }
     }
     int rc = -1;
     switch (type) {

@@ -141,15 +141,19 @@ def test_k_split_group_launch(name):
     """q/k/v of a 12-token step in one split grid: every matrix against the oracle."""
     ops = _ops()
     t = O.QUANT_TYPES[name]
-    K, M, Ns = 4096, 12, (2048, 512, 512)
+    K, M, Ns = 4096, 12, (4096, 1024, 512)
     rng = np.random.default_rng(5)
     Wn = [O.random_quant_bytes(t, n, K, rng) for n in Ns]
     X = rng.uniform(-1, 1, (M, K)).astype(np.float32)
-    got = ops.mul_mat_q_group(t, [_dev(w) for w in Wn], list(Ns), torch.from_numpy(X).cuda(), K)
+    Wd = [_dev(w) for w in Wn]
+    Xd = torch.from_numpy(X).cuda()
+    got = ops.mul_mat_q_group(t, Wd, list(Ns), Xd, K)
     for g, n in enumerate(Ns):
         rows = np.arange(0, n, 7)
         ref = O.mul_mat_f32(t, np.ascontiguousarray(Wn[g].reshape(n, -1)[rows]), X, len(rows), K, M)
         assert _nmse(got[g].cpu().numpy()[:, rows], ref) < NMSE_BAR, g
+        # every matrix keeps the slice count of its own launch: grouped == single, bit for bit (fused and unfused graphs agree)
+        assert torch.equal(got[g], ops.mul_mat_q(t, Wd[g], Xd, n, K)), g
 
 
 @pytest.mark.parametrize("name", ["q4_K", "q6_K", "q8_0"])
