@@ -29,11 +29,14 @@
 #define QK_K 256  /* elements per K-quant super-block          (ggml-common.h:89) */
 
 /* ---- ggml type ids (ggml/include/ggml.h:352-366) ---- */
-enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q8_0 = 8, T_Q8_1 = 9, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
+enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q8_1 = 9, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
 
-/* ---- block layouts (ggml-common.h:167-172, 209-214, 216-227, 285-296, 302-314, 320-326) ---- */
+/* ---- block layouts (ggml-common.h:167-172, 177-207 (q4_1 q5_0 q5_1), 209-214, 216-227, 285-296, 302-314, 320-326) ---- */
 #pragma pack(push, 1)
 typedef struct { uint16_t d; uint8_t qs[16]; } blk_q4_0;                                  /* 18 B */
+typedef struct { uint16_t d; uint16_t m; uint8_t qs[16]; } blk_q4_1;                      /* 20 B */
+typedef struct { uint16_t d; uint8_t qh[4]; uint8_t qs[16]; } blk_q5_0;                   /* 22 B */
+typedef struct { uint16_t d; uint16_t m; uint8_t qh[4]; uint8_t qs[16]; } blk_q5_1;       /* 24 B */
 typedef struct { uint16_t d; int8_t qs[32]; } blk_q8_0;                                   /* 34 B */
 typedef struct { uint16_t d; uint16_t s; int8_t qs[32]; } blk_q8_1;                       /* 36 B */
 typedef struct { uint16_t d; uint16_t dmin; uint8_t scales[12]; uint8_t qs[128]; } blk_q4_K;              /* 144 B */
@@ -44,6 +47,7 @@ typedef struct { uint8_t ql[128]; uint8_t qh[64]; int8_t scales[16]; uint16_t d;
 int64_t oracle_block_bytes(int type) {
     switch (type) {
         case T_Q4_0: return 18; case T_Q8_0: return 34; case T_Q8_1: return 36;
+        case T_Q4_1: return 20; case T_Q5_0: return 22; case T_Q5_1: return 24;
         case T_Q4_K: return 144; case T_Q5_K: return 176; case T_Q6_K: return 210;
         case T_F32: return 4; case T_F16: return 2;
     }
@@ -51,7 +55,7 @@ int64_t oracle_block_bytes(int type) {
 }
 int64_t oracle_block_elems(int type) {
     switch (type) {
-        case T_Q4_0: case T_Q8_0: case T_Q8_1: return 32;
+        case T_Q4_0: case T_Q8_0: case T_Q8_1: case T_Q4_1: case T_Q5_0: case T_Q5_1: return 32;
         case T_Q4_K: case T_Q5_K: case T_Q6_K: return 256;
         case T_F32: case T_F16: return 1;
     }
@@ -104,6 +108,38 @@ static void deq_q4_0(const blk_q4_0 *x, float *y, int64_t k) {
         for (int j = 0; j < 16; j++) {
             y[i * QK + j]      = (float)((x[i].qs[j] & 0x0F) - 8) * d;
             y[i * QK + j + 16] = (float)((x[i].qs[j] >> 4) - 8) * d;
+        }
+    }
+}
+/* q4_1 (ggml-quants.c:269-288): nibble * d + m;  q5_0 (:290-314): (5-bit code - 16) * d, bit j / j + 16 of qh is the fifth bit of
+ * element j / j + 16;  q5_1 (:316-341): 5-bit code * d + m.  Product and sum are two roundings (-ffp-contract=off). */
+static uint32_t qh_word(const uint8_t *qh) { uint32_t v; memcpy(&v, qh, 4); return v; }
+static void deq_q4_1(const blk_q4_1 *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK; i++) {
+        float d = oracle_fp16_to_fp32(x[i].d), m = oracle_fp16_to_fp32(x[i].m);
+        for (int j = 0; j < 16; j++) {
+            y[i * QK + j]      = (float)(x[i].qs[j] & 0x0F) * d + m;
+            y[i * QK + j + 16] = (float)(x[i].qs[j] >> 4) * d + m;
+        }
+    }
+}
+static void deq_q5_0(const blk_q5_0 *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK; i++) {
+        float d = oracle_fp16_to_fp32(x[i].d);
+        uint32_t qh = qh_word(x[i].qh);
+        for (int j = 0; j < 16; j++) {
+            y[i * QK + j]      = (float)((int)((x[i].qs[j] & 0x0F) | (((qh >> j) & 1) << 4)) - 16) * d;
+            y[i * QK + j + 16] = (float)((int)((x[i].qs[j] >> 4) | (((qh >> (j + 16)) & 1) << 4)) - 16) * d;
+        }
+    }
+}
+static void deq_q5_1(const blk_q5_1 *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK; i++) {
+        float d = oracle_fp16_to_fp32(x[i].d), m = oracle_fp16_to_fp32(x[i].m);
+        uint32_t qh = qh_word(x[i].qh);
+        for (int j = 0; j < 16; j++) {
+            y[i * QK + j]      = (float)((x[i].qs[j] & 0x0F) | (((qh >> j) & 1) << 4)) * d + m;
+            y[i * QK + j + 16] = (float)((x[i].qs[j] >> 4) | (((qh >> (j + 16)) & 1) << 4)) * d + m;
         }
     }
 }
@@ -166,6 +202,9 @@ int oracle_dequantize_row(int type, const void *x, float *y, int64_t k) {
     switch (type) {
         case T_Q4_0: deq_q4_0((const blk_q4_0 *)x, y, k); return 0;
         case T_Q8_0: deq_q8_0((const blk_q8_0 *)x, y, k); return 0;
+        case T_Q4_1: deq_q4_1((const blk_q4_1 *)x, y, k); return 0;
+        case T_Q5_0: deq_q5_0((const blk_q5_0 *)x, y, k); return 0;
+        case T_Q5_1: deq_q5_1((const blk_q5_1 *)x, y, k); return 0;
         case T_Q4_K: deq_q4_K((const blk_q4_K *)x, y, k); return 0;
         case T_Q5_K: deq_q5_K((const blk_q5_K *)x, y, k); return 0;
         case T_Q6_K: deq_q6_K((const blk_q6_K *)x, y, k); return 0;
@@ -240,6 +279,21 @@ static void int_codes(int type, const void *row, int64_t k, int *w) {
         for (int64_t i = 0; i < k / QK; i++) for (int j = 0; j < 16; j++) {
             w[i * QK + j] = b[i].qs[j] & 0xF; w[i * QK + j + 16] = b[i].qs[j] >> 4;
         }
+    } else if (type == T_Q4_1) {      /* nibble 0..15 (vecdotq.cuh:49-80) */
+        const blk_q4_1 *b = (const blk_q4_1 *)row;
+        for (int64_t i = 0; i < k / QK; i++) for (int j = 0; j < 16; j++) {
+            w[i * QK + j] = b[i].qs[j] & 0xF; w[i * QK + j + 16] = b[i].qs[j] >> 4;
+        }
+    } else if (type == T_Q5_0 || type == T_Q5_1) {      /* 5-bit code 0..31, the -16 of q5_0 folded into the s8 term (vecdotq.cuh:82-150) */
+        for (int64_t i = 0; i < k / QK; i++) {
+            const uint8_t *blk = (const uint8_t *)row + i * (type == T_Q5_0 ? 22 : 24);
+            const uint8_t *qs = blk + (type == T_Q5_0 ? 6 : 8);
+            const uint32_t qh = qh_word(blk + (type == T_Q5_0 ? 2 : 4));
+            for (int j = 0; j < 16; j++) {
+                w[i * QK + j]      = (int)((qs[j] & 0xF) | (((qh >> j) & 1) << 4));
+                w[i * QK + j + 16] = (int)((qs[j] >> 4)  | (((qh >> (j + 16)) & 1) << 4));
+            }
+        }
     } else if (type == T_Q8_0) {
         const blk_q8_0 *b = (const blk_q8_0 *)row;
         for (int64_t i = 0; i < k / QK; i++) for (int j = 0; j < QK; j++) w[i * QK + j] = b[i].qs[j];
@@ -302,6 +356,14 @@ int oracle_mul_mat_vec_q(int type, const void *W, int64_t row_stride_bytes, cons
                 if (type == T_Q4_0) {
                     const double d = oracle_fp16_to_fp32(((const blk_q4_0 *)row)[b].d);
                     acc += use_s8 ? d * (si[b] * d8 - 8.0 * s8) : d * d8 * (si[b] - 8.0 * sq[b]);
+                } else if (type == T_Q4_1 || type == T_Q5_1) {
+                    /* d * d8 * sumi + m * s8 (vecdotq.cuh:76-79, 146-149): s8 = fp16(sum x) in the reference; exact m * d8 * sumq here */
+                    const uint8_t *blk = row + b * (type == T_Q4_1 ? 20 : 24);
+                    const double d = oracle_fp16_to_fp32(((const uint16_t *)blk)[0]), mm = oracle_fp16_to_fp32(((const uint16_t *)blk)[1]);
+                    acc += use_s8 ? d * d8 * si[b] + mm * s8 : d * d8 * si[b] + mm * d8 * sq[b];
+                } else if (type == T_Q5_0) {
+                    const double d = oracle_fp16_to_fp32(((const blk_q5_0 *)row)[b].d);
+                    acc += use_s8 ? d * (si[b] * d8 - 16.0 * s8) : d * d8 * (si[b] - 16.0 * sq[b]);
                 } else if (type == T_Q8_0) {
                     acc += (double)oracle_fp16_to_fp32(((const blk_q8_0 *)row)[b].d) * d8 * si[b];
                 } else if (type == T_Q4_K || type == T_Q5_K) {

@@ -58,7 +58,7 @@ def p(a):
 def ref_dequant(name, data, n, k):
     fn = getattr(ref, "dequantize_row_" + name)
     out = np.empty((n, k), dtype=np.float32)
-    rb = O.row_bytes(O.QUANT_TYPES[name], k)
+    rb = O.row_bytes(O.ALL_QUANT_TYPES[name], k)
     data = np.ascontiguousarray(data).reshape(n, rb)
     for i in range(n):
         row = np.ascontiguousarray(data[i])
@@ -92,18 +92,24 @@ def q8_1_cuda_numpy(x, k_pad):
 
 def int_codes_from_dequant(name, data, deq, n, k):
     """Recover the integer code of every weight from the reference's dequantised floats."""
-    t = O.QUANT_TYPES[name]
+    t = O.ALL_QUANT_TYPES[name]
     rb = O.row_bytes(t, k)
     raw = np.ascontiguousarray(data).reshape(n, rb)
     codes = np.zeros((n, k), dtype=np.int64)
     for i in range(n):
         blocks = raw[i].reshape(-1, O.BLOCK_BYTES[t])
         for b, blk in enumerate(blocks):
-            if name in ("q4_0", "q8_0"):
+            if name in ("q4_0", "q8_0", "q5_0"):
                 d = np.float64(blk[0:2].view(np.float16)[0])
                 y = deq[i, 32 * b: 32 * b + 32].astype(np.float64)
-                c = np.rint(y / d) + (8 if name == "q4_0" else 0)
+                c = np.rint(y / d) + {"q4_0": 8, "q8_0": 0, "q5_0": 16}[name]
                 codes[i, 32 * b: 32 * b + 32] = c
+            elif name in ("q4_1", "q5_1"):
+                d = np.float64(blk[0:2].view(np.float16)[0])
+                m = np.float64(blk[2:4].view(np.float16)[0])
+                assert d != 0
+                y = deq[i, 32 * b: 32 * b + 32].astype(np.float64)
+                codes[i, 32 * b: 32 * b + 32] = np.rint((y - m) / d)
             elif name in ("q4_K", "q5_K"):
                 d = np.float32(blk[0:2].view(np.float16)[0])
                 dm = np.float32(blk[2:4].view(np.float16)[0])
@@ -179,5 +185,34 @@ def main():
     print("wrote quant_golden.npz:", {k: v.shape for k, v in out.items()})
 
 
+def main_legacy():
+    """quant_golden_legacy.npz: the same vectors for q4_1 / q5_0 / q5_1, over the activations X of quant_golden.npz so
+    that q81cuda / sumq are shared.  A file of its own: quant_golden.npz stays byte-identical."""
+    G = np.load(os.path.join(HERE, "quant_golden.npz"))
+    X = G["X"]
+    qx = np.stack([q8_1_cuda_numpy(X[m], 512)[1] for m in range(M)]).astype(np.int64)
+    rng = np.random.default_rng(20261105)
+    out = {}
+    Wf = G["Wf"]
+    for name, t in O.LEGACY_TYPES.items():
+        rb = O.row_bytes(t, K)
+        data = np.zeros(N * rb, dtype=np.uint8)
+        sz = ref.ggml_quantize_chunk(t, p(Wf), p(data), 0, N, K, None)
+        assert sz == N * rb
+        deq = ref_dequant(name, data, N, K)
+        out["W_" + name], out["deq_" + name] = data.reshape(N, rb), deq.view(np.uint32)
+        rnd = O.random_quant_bytes(t, N, K, rng)
+        rdeq = ref_dequant(name, rnd, N, K)
+        out["R_" + name], out["rdeq_" + name] = rnd, rdeq.view(np.uint32)
+        codes = int_codes_from_dequant(name, data, deq, N, K)
+        assert codes.min() >= 0 and codes.max() <= (15 if name == "q4_1" else 31)
+        out["sumi_" + name] = np.einsum("nbk,mbk->mnb", codes.reshape(N, K // 32, 32), qx.reshape(M, K // 32, 32)).astype(np.int32)
+    np.savez_compressed(os.path.join(HERE, "quant_golden_legacy.npz"), **out)
+    print("wrote quant_golden_legacy.npz:", {k: v.shape for k, v in out.items()})
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "legacy":
+        main_legacy()
+    else:
+        main()

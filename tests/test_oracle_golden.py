@@ -9,9 +9,10 @@ import pytest
 
 import oracle as O
 
-G = np.load(os.path.join(os.path.dirname(__file__), "golden", "quant_golden.npz"))
+G = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "quant_golden.npz")))
+G.update(np.load(os.path.join(os.path.dirname(__file__), "golden", "quant_golden_legacy.npz")))     # q4_1 / q5_0 / q5_1 (make_golden.py legacy)
 K, N, M = 512, 4, 2
-NAMES = list(O.QUANT_TYPES)
+NAMES = list(O.ALL_QUANT_TYPES)
 
 
 def test_fp16_to_fp32_all_codes():
@@ -29,7 +30,7 @@ def test_fp32_to_fp16():
 @pytest.mark.parametrize("name", NAMES)
 @pytest.mark.parametrize("src", ["W_", "R_"])
 def test_dequantize_bit_exact(name, src):
-    t = O.QUANT_TYPES[name]
+    t = O.ALL_QUANT_TYPES[name]
     got = O.dequantize(t, G[src + name], N, K).view(np.uint32)
     want = G[("deq_" if src == "W_" else "rdeq_") + name]
     assert np.array_equal(got, want)
@@ -89,7 +90,7 @@ def test_q8_1_cuda_padding_and_ragged():
 
 @pytest.mark.parametrize("name", NAMES)
 def test_block_sums_exact(name):
-    t = O.QUANT_TYPES[name]
+    t = O.ALL_QUANT_TYPES[name]
     for m in range(M):
         for n in range(N):
             si, sq = O.block_sums(t, G["W_" + name][n], G["q81cuda"][m], K)
@@ -103,12 +104,12 @@ def test_mmvq_reference_close_to_f32_matmul(name):
     reference's MUL_MAT bar (tests/test-backend-ops.cpp:1990-1992: 5e-4).  Only 8 outputs and an
     injected activation outlier (X[1,200]=37.5) here, so the bound is 2e-3; the 5e-4 bar itself is
     enforced on the GPU path at full sizes (tests/test_gpu_*.py, test-backend-ops)."""
-    t = O.QUANT_TYPES[name]
+    t = O.ALL_QUANT_TYPES[name]
     a = O.mul_mat_vec_q(t, G["W_" + name], G["X"], N, K, M)
     b = O.mul_mat_f32(t, G["W_" + name], G["X"], N, K, M)
     nmse = float(((a - b) ** 2).sum() / (b ** 2).sum())
     assert nmse < 2e-3
-    if name == "q4_0":  # literal s8 formula (vecdotq.cuh:43): differs only by the fp16 rounding of s=sum(x)
+    if name in ("q4_0", "q4_1", "q5_0", "q5_1"):  # literal s8 formula (vecdotq.cuh:43,79,114,149): differs only by the fp16 rounding of s=sum(x)
         c = O.mul_mat_vec_q(t, G["W_" + name], G["X"], N, K, M, use_s8=True)
         assert float(((a - c) ** 2).sum() / (b ** 2).sum()) < 1e-2
 
@@ -124,7 +125,7 @@ def test_dequantize_live_against_reference(name):
     ref.ggml_init.restype = C.c_void_p
     ref.ggml_init.argtypes = [InitParams]
     assert ref.ggml_init(InitParams(1 << 20, None, False))  # fills the fp16 table (ggml.c:1419-1433)
-    t = O.QUANT_TYPES[name]
+    t = O.ALL_QUANT_TYPES[name]
     rng = np.random.default_rng(7)
     k, n = 2048, 8
     raw = O.random_quant_bytes(t, n, k, rng)
