@@ -12,7 +12,7 @@ The model is a random-init GGUF of that architecture written by tools/make_gguf.
           graph on the GPU and reads the 128256 logits back to the host (the call a user makes)
   value   tokens / device time of the graph_compute calls of the same run, taken with CUDA events on the backend's
           stream (B200_TIMING=1 makes the plugin accumulate them); inputs are resident in HBM at that point
-  roofline  the dominant kernel, mmvqr_kernel<Q4_K> (mmvq_r.cuh): algorithmic bytes (N*K*144/256 per launch) over its mean launch
+  roofline  the dominant kernel, mmvqr_kernel<Q4_K> (mmvq_r.cuh): algorithmic bytes (N*K*144/256 per matrix) over its mean launch
           duration, timed live in this process with CUDA events on a CUDA graph holding exactly the 192 Q4_K
           GEMVs of one token (distinct weight matrices, 3.36 GB > L2), through the C ABI of include/b200_ops.h
   cpu_baseline  the reference CPU backend on the same GGUF (llama-bench -ngl 0, all host threads), bounded to tg16
@@ -199,28 +199,55 @@ def llama_bench(model, extra, plugin, timing=False, device=None, timeout=3600):
     return res, stats
 
 
-def kernel_roofline(steps, warmup, dev_index):
-    """Dominant kernel timed live: the 192 Q4_K GEMVs of one token from a CUDA graph, CUDA events on its stream."""
+def issue_groups(plan):
+    """The Q4_K mat-vecs of a token as the plugin issues them (ggml-b200-compute.inc: try_attn_frontend / try_group_gemv): consecutive
+    matrices of one type over the same activations share a launch (q/k/v -- v only when it is Q4_K too --, gate/up); wo and down
+    are launches of their own."""
+    groups = []
+    for e in plan:
+        if groups and groups[-1][-1][4] == e[4] and groups[-1][-1][3] == e[3] and len(groups[-1]) < 3 and groups[-1][-1][0] != "wo":
+            groups[-1].append(e)
+        else:
+            groups.append([e])
+    return groups
+
+
+def kernel_roofline(steps, warmup, dev_index, grouped=True):
+    """Dominant kernel timed live: the Q4_K GEMVs of one token from a CUDA graph, CUDA events on its stream.  grouped: the launches
+    the plugin issues in the timed region (128: q/k/v and gate/up share a launch); else every matrix as a launch of its own (192,
+    the round-1 form of this figure)."""
     import ctypes as C
     import torch
     from llamacog_b200 import ops
     from tools.mmvq_micro import rand_weights
     torch.cuda.set_device(dev_index)
     dev = torch.device("cuda", dev_index)
-    ops.lib()
+    L = ops.lib()
     plan = [p for p in step_plan() if p[1] == Q4_K]
     weights = [rand_weights(t, N * ops.row_bytes(t, K), dev) for _, t, N, K, _, _ in plan]
     X = {4096: torch.rand(1, 4096, device=dev) * 2 - 1, 14336: torch.rand(1, 14336, device=dev) * 2 - 1}
-    out = {N: torch.zeros(1, N, device=dev) for N in (4096, 1024, 14336)}
     xq = {K: ops.quantize_acts(x) for K, x in X.items()}
+    launches = []
+    i = 0
+    for g in (issue_groups(plan) if grouped else [[e] for e in plan]):
+        ws = weights[i:i + len(g)]
+        i += len(g)
+        launches.append((g, ws, [torch.zeros(1, e[2], device=dev) for e in g]))
 
     def run():
-        for (_, t, N, K, _, _), W in zip(plan, weights):
-            a = ops.MmvqArgs(type=t, W=W.data_ptr(), nb1=ops.row_bytes(t, K), X=X[K].data_ptr(), xs=K, dst=out[N].data_ptr(),
-                             ds=N, N=N, K=K, M=1, ny=1, nz=1, pdl=-1, dbg_sumi=None, Xq=xq[K].data_ptr())
-            rc = ops.lib().b200_mul_mat_vec_q_ex(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        for g, ws, outs in launches:
+            t, K, ng = g[0][1], g[0][3], len(g)
+            a = ops.MmvqArgs(type=t, W=ws[0].data_ptr(), nb1=ops.row_bytes(t, K), X=X[K].data_ptr(), xs=K, dst=outs[0].data_ptr(),
+                             ds=g[0][2], N=g[0][2], K=K, M=1, ny=1, nz=1, pdl=-1, dbg_sumi=None, Xq=xq[K].data_ptr())
+            if ng == 1:
+                rc = L.b200_mul_mat_vec_q_ex(C.byref(a), st)
+            else:
+                Wp = (C.c_void_p * ng)(*[w.data_ptr() for w in ws]); Dp = (C.c_void_p * ng)(*[o.data_ptr() for o in outs])
+                Np = (C.c_int * ng)(*[e[2] for e in g]); dsp = (C.c_int64 * ng)(*[e[2] for e in g])
+                rc = L.b200_mul_mat_vec_q_group(C.byref(a), C.c_int(ng), Wp, Dp, Np, dsp, st)
             if rc:
-                raise RuntimeError("b200_mul_mat_vec_q_ex rc=%d" % rc)
+                raise RuntimeError("b200_mul_mat_vec_q rc=%d" % rc)
 
     st = torch.cuda.Stream()
     with torch.cuda.stream(st):
@@ -240,7 +267,7 @@ def kernel_roofline(steps, warmup, dev_index):
         torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
     nbytes = plan_bytes(plan)
-    return {"launches": len(plan), "us_per_launch": ms * 1e3 / len(plan), "bytes": nbytes, "gbps": nbytes / (ms * 1e-3) / 1e9}
+    return {"launches": len(launches), "us_per_launch": ms * 1e3 / len(launches), "bytes": nbytes, "gbps": nbytes / (ms * 1e-3) / 1e9}
 
 
 def mmq_roofline(steps, warmup, dev_index):
@@ -484,10 +511,15 @@ def main():
                 tpath = os.path.join(ROOT, "profiles", "r01_mmvqr_q4k_traffic.json")
                 if os.path.exists(tpath):
                     traffic = json.load(open(tpath)).get("dram_bytes_per_launch_token_mix")
-                line["roofline"] = {"bound": "hbm", "kernel": "mmvqr_kernel<Q4_K> (192 launches per token: wq wk wv wo gate up down)",
+                k1 = kernel_roofline(max(20, min(args.steps, 200)), args.warmup, local, grouped=False)
+                line["roofline"] = {"bound": "hbm", "kernel": "mmvqr_kernel<Q4_K> as the plugin issues it in the timed region (%d launches per token: q/k/v group, wo, gate/up group, down)" % k["launches"],
                                     "achieved": k["gbps"], "peak": peak, "unit": "GB/s", "frac": k["gbps"] / peak, "traffic": traffic,
                                     "peak_source": how, "launches": k["launches"], "us_per_launch": k["us_per_launch"],
                                     "algorithmic_bytes_per_launch": k["bytes"] / k["launches"],
+                                    "traffic_note": "ncu DRAM bytes per launch of the single-matrix launches (profiles/r01_mmvqr_q4k_traffic.json): 1.002 x algorithmic",
+                                    "single_launches": {"note": "the same matrices, every one a launch of its own (the round-1 form of this figure; the step never issues wk / wv alone)",
+                                                        "launches": k1["launches"], "us_per_launch": k1["us_per_launch"], "achieved": k1["gbps"], "frac": k1["gbps"] / peak,
+                                                        "algorithmic_bytes_per_launch": k1["bytes"] / k1["launches"]},
                                     "whole_step_GBps": plan_bytes(step_plan()) / (ms_step * 1e-3) / 1e9 if world == 1 else None}
             except Exception as e:  # noqa: BLE001
                 line["roofline"] = {"error": str(e)[:200]}

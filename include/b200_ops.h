@@ -98,11 +98,11 @@ typedef struct b200_mmvq_args {
     uint32_t * hs_join; int hs_join_stride; uint32_t hs_join_mask;
     unsigned * hs_counter; unsigned hs_timeout_ms; uint32_t * hs_error;
     /* gate / up of a decode step as a group launch (b200_mul_mat_vec_q_group, ng = 2: matrix 0 = gate, 1 = up, equal N, N % 32 == 0,
-     * batch-1 kernel only, see b200_mmvq_fusable): the CTA that completes a 32-row block of BOTH results also computes
+     * batch-1 kernel only, see b200_mmvq_fusable): every CTA takes the same whole 32-row blocks of BOTH matrices and also computes
      *   sm_act[n] = unary(gate[n]),  sm_out[n] = sm_act[n] * up[n],  and (sm_xq != NULL) the q8 activations of sm_out
      * with the arithmetic of b200_op_unary_mul (bit-identical); replaces that launch (reference: unary.cu silu + binbcast.cu mul).
-     * sm_act == NULL: off.  sm_op: B200_UNARY_SILU only.  sm_counters: N / 32 words of device memory, zero before the first use
-     * (the kernel leaves them zero), not shared by launches that may overlap.  sm_act / sm_out may alias the gate / up results. */
+     * sm_act == NULL: off.  sm_op: B200_UNARY_SILU only.  sm_act / sm_out may alias the gate / up results.
+     * sm_counters: unused (the first version counted blocks across CTAs there; kept so that the struct layout stays). */
     int sm_op; float * sm_act; float * sm_out; void * sm_xq; unsigned * sm_counters;
 } b200_mmvq_args;
 

@@ -1,5 +1,5 @@
 // dequant.cuh -- element-wise dequantisation of GGUF blocks, bit-exact to the reference's
-// dequantize_row_* (ggml/src/ggml-quants.c:249-267, 343-357, 1274-1296, 1480-1503, 1684-1713).
+// dequantize_row_* (ggml/src/ggml-quants.c:249-267, 269-341 (q4_1 q5_0 q5_1), 343-357, 1274-1296, 1480-1503, 1684-1713).
 #pragma once
 #include "common.cuh"
 
@@ -22,6 +22,17 @@ template <int TYPE> __device__ __forceinline__ float dequant_elem(const uint8_t 
         const uint8_t * b = row + (e >> 5) * 18; const int j = e & 31;
         const int q = j < 16 ? (b[2 + j] & 0xF) : (b[2 + j - 16] >> 4);
         return __fmul_rn((float)(q - 8), ldh(b));
+    } else if constexpr (TYPE == T_Q4_1) {
+        const uint8_t * b = row + (e >> 5) * 20; const int j = e & 31;
+        const int q = j < 16 ? (b[4 + j] & 0xF) : (b[4 + j - 16] >> 4);
+        return __fadd_rn(__fmul_rn((float)q, ldh(b)), ldh(b + 2));
+    } else if constexpr (TYPE == T_Q5_0 || TYPE == T_Q5_1) {
+        constexpr int BB = TYPE == T_Q5_0 ? 22 : 24, QH = TYPE == T_Q5_0 ? 2 : 4;
+        const uint8_t * b = row + (e >> 5) * BB; const int j = e & 31;
+        const int nib = j < 16 ? (b[QH + 4 + j] & 0xF) : (b[QH + 4 + j - 16] >> 4);
+        const int q = nib | (((b[QH + (j >> 3)] >> (j & 7)) & 1) << 4);          // bit j of the little-endian qh word
+        if constexpr (TYPE == T_Q5_0) return __fmul_rn((float)(q - 16), ldh(b));
+        else return __fadd_rn(__fmul_rn((float)q, ldh(b)), ldh(b + 2));
     } else if constexpr (TYPE == T_Q8_0) {
         const uint8_t * b = row + (e >> 5) * 34;
         return __fmul_rn((float)(int8_t)b[2 + (e & 31)], ldh(b));

@@ -115,7 +115,7 @@ static int mm_dense_launch(const mm_params & p, int nz, cudaStream_t st) {
     return 0;
 }
 
-static bool is_quant(int t) { return t == T_Q4_0 || t == T_Q8_0 || t == T_Q4_K || t == T_Q5_K || t == T_Q6_K; }
+static bool is_quant(int t) { return b200_mmvq_supported_type(t) != 0; }
 static bool is_dense(int t) { return t == T_F32 || t == T_F16 || t == T_BF16; }
 
 static int mmq_min_m() { static const int v = [] { const char * e = getenv("B200_MMQ_MIN_M"); return e ? atoi(e) : 9; }(); return v; }

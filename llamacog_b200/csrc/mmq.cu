@@ -249,6 +249,89 @@ template <> struct dq<T_Q4_0> {
     }
 };
 
+// ---- Q4_1: 8 blocks of {d, m (f16), qs[16]} per 256 K; nibble * d + m = ((1 + q/16) - 1.5) * 16d + (8d + m)   (round 2)
+template <> struct dq<T_Q4_1> {
+    static constexpr int PITCH = 160;
+    static constexpr int STEP16 = 80;
+    static constexpr bool SHIFTED = false;
+    template <int S> __device__ __forceinline__ void prep(uint32_t, int) {}
+    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t (&out)[32]) const {
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            const uint32_t blk = row + 20 * (2 * (2 * h + t) + b);                          // 4-byte aligned
+            const uint32_t dm = lds32(blk);
+            uint32_t s2, c2;
+            make_sb(16.0f * half_bits_to_float(dm & 0xFFFFu), -half_bits_to_float(dm >> 16), s2, c2);
+            uint32_t w[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) w[j] = lds32(blk + 4 + 4 * j);
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                uint32_t o[4], p[4];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const uint32_t x = w[2 * u + i];
+                    expand4(((x << 3) & 0x78787878u) | 0x80808080u, s2, c2, o[2 * i], o[2 * i + 1]);
+                    expand4(((x >> 1) & 0x78787878u) | 0x80808080u, s2, c2, p[2 * i], p[2 * i + 1]);
+                }
+                { out[4 * ((4 * b + u))] = o[0]; out[4 * ((4 * b + u)) + 1] = o[1]; out[4 * ((4 * b + u)) + 2] = o[2]; out[4 * ((4 * b + u)) + 3] = o[3]; }
+                { out[4 * ((4 * b + u + 2))] = p[0]; out[4 * ((4 * b + u + 2)) + 1] = p[1]; out[4 * ((4 * b + u + 2)) + 2] = p[2]; out[4 * ((4 * b + u + 2)) + 3] = p[3]; }
+            }
+        }
+    }
+};
+
+// four bits of x (bits 0..3) to bit 6 of four bytes: x * 0x00204081 puts bit k at bit 8k (the four shifted copies do not overlap)
+__device__ __forceinline__ uint32_t spread4_bit6(uint32_t x) { return (((x & 0xFu) * 0x00204081u) & 0x01010101u) << 6; }
+
+// ---- Q5_0 / Q5_1: 8 blocks of {d [, m], qh[4], qs[16]}; 5-bit code q = nibble | bit j of qh << 4 (element j; the high nibbles are
+//      elements 16..31).  Q5_0: (q - 16) d = ((1 + q/32) - 1.5) * 32d;  Q5_1: q d + m = ((1 + q/32) - 1.5) * 32d + (16d + m).
+//      Code byte 0x80 | q << 2: nibble at bits 2..5, fifth bit at bit 6.
+template <int TYPE> struct dq5 {
+    static constexpr int BB = TYPE == T_Q5_0 ? 22 : 24;
+    static constexpr int PITCH = 8 * BB;
+    static constexpr int STEP16 = 4 * BB;
+    static constexpr bool SHIFTED = false;
+    template <int S> __device__ __forceinline__ void prep(uint32_t, int) {}
+    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t (&out)[32]) const {
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            const uint32_t blk = row + BB * (2 * (2 * h + t) + b);                          // Q5_0: 2-byte aligned, Q5_1: 8-byte aligned
+            uint32_t s2, c2 = 0, qh, w[4];
+            if constexpr (TYPE == T_Q5_0) {
+                s2 = pack_bf16_dup(32.0f * half_bits_to_float(lds16(blk)));
+                int v[5]; lds_words_a2<5>(blk + 2, v);
+                qh = (uint32_t)v[0];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) w[j] = (uint32_t)v[1 + j];
+            } else {
+                const uint32_t dm = lds32(blk);
+                make_sb(32.0f * half_bits_to_float(dm & 0xFFFFu), -half_bits_to_float(dm >> 16), s2, c2);
+                qh = lds32(blk + 4);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) w[j] = lds32(blk + 8 + 4 * j);
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                uint32_t o[4], p[4];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const int e = 4 * (2 * u + i);                                          // first element of this word's low nibbles
+                    const uint32_t x = w[2 * u + i];
+                    const uint32_t lo = ((x << 2) & 0x3C3C3C3Cu) | 0x80808080u | spread4_bit6(qh >> e);
+                    const uint32_t hi = ((x >> 2) & 0x3C3C3C3Cu) | 0x80808080u | spread4_bit6(qh >> (16 + e));
+                    if constexpr (TYPE == T_Q5_0) { expand4_sym(lo, s2, o[2 * i], o[2 * i + 1]); expand4_sym(hi, s2, p[2 * i], p[2 * i + 1]); }
+                    else { expand4(lo, s2, c2, o[2 * i], o[2 * i + 1]); expand4(hi, s2, c2, p[2 * i], p[2 * i + 1]); }
+                }
+                { out[4 * ((4 * b + u))] = o[0]; out[4 * ((4 * b + u)) + 1] = o[1]; out[4 * ((4 * b + u)) + 2] = o[2]; out[4 * ((4 * b + u)) + 3] = o[3]; }
+                { out[4 * ((4 * b + u + 2))] = p[0]; out[4 * ((4 * b + u + 2)) + 1] = p[1]; out[4 * ((4 * b + u + 2)) + 2] = p[2]; out[4 * ((4 * b + u + 2)) + 3] = p[3]; }
+            }
+        }
+    }
+};
+template <> struct dq<T_Q5_0> : dq5<T_Q5_0> {};
+template <> struct dq<T_Q5_1> : dq5<T_Q5_1> {};
+
 // ---- Q8_0: 8 blocks of {d (f16), qs int8[32]} per 256 K; q * d.  Codes go through f16 (1024 + (q ^ 0x80) is
 //      exact, minus 1152 gives q, times the f16 scale) and are then rounded to bf16.
 template <> struct dq<T_Q8_0> {
@@ -587,6 +670,7 @@ static int env_int(const char * name, int def) { const char * e = getenv(name); 
 template <int TYPE> static int pitch_of() { return dq<TYPE>::PITCH; }
 static int raw_pitch(int type) {
     switch (type) { case T_Q4_0: return pitch_of<T_Q4_0>(); case T_Q8_0: return pitch_of<T_Q8_0>(); case T_Q4_K: return pitch_of<T_Q4_K>();
+                    case T_Q4_1: return pitch_of<T_Q4_1>(); case T_Q5_0: return pitch_of<T_Q5_0>(); case T_Q5_1: return pitch_of<T_Q5_1>();
                     case T_Q5_K: return pitch_of<T_Q5_K>(); case T_Q6_K: return pitch_of<T_Q6_K>(); }
     return 0;
 }
@@ -779,6 +863,9 @@ extern "C" int b200_mul_mat_q_bf16(int type, const void * W, int64_t nb1, const 
     switch (type) {
         case T_Q4_0: rc = mmq_launch<T_Q4_0>(wmap, xmap, p, smem, st); break;
         case T_Q8_0: rc = mmq_launch<T_Q8_0>(wmap, xmap, p, smem, st); break;
+        case T_Q4_1: rc = mmq_launch<T_Q4_1>(wmap, xmap, p, smem, st); break;
+        case T_Q5_0: rc = mmq_launch<T_Q5_0>(wmap, xmap, p, smem, st); break;
+        case T_Q5_1: rc = mmq_launch<T_Q5_1>(wmap, xmap, p, smem, st); break;
         case T_Q4_K: rc = mmq_launch<T_Q4_K>(wmap, xmap, p, smem, st); break;
         case T_Q5_K: rc = mmq_launch<T_Q5_K>(wmap, xmap, p, smem, st); break;
         case T_Q6_K: rc = mmq_launch<T_Q6_K>(wmap, xmap, p, smem, st); break;
@@ -852,6 +939,9 @@ extern "C" int b200_mul_mat_q_bf16_group(int type, int ng, const void * const * 
     switch (type) {
         case T_Q4_0: rc = mmq_launch<T_Q4_0>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
         case T_Q8_0: rc = mmq_launch<T_Q8_0>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
+        case T_Q4_1: rc = mmq_launch<T_Q4_1>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
+        case T_Q5_0: rc = mmq_launch<T_Q5_0>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
+        case T_Q5_1: rc = mmq_launch<T_Q5_1>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
         case T_Q4_K: rc = mmq_launch<T_Q4_K>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
         case T_Q5_K: rc = mmq_launch<T_Q5_K>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
         case T_Q6_K: rc = mmq_launch<T_Q6_K>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
@@ -932,6 +1022,9 @@ extern "C" int b200_mul_mat_id_q(int type, const void * W, int64_t nb1, int n_ex
     switch (type) {
         case T_Q4_0: return mmq_launch<T_Q4_0>(wmap, xmap, p, smem, st, n_expert);
         case T_Q8_0: return mmq_launch<T_Q8_0>(wmap, xmap, p, smem, st, n_expert);
+        case T_Q4_1: return mmq_launch<T_Q4_1>(wmap, xmap, p, smem, st, n_expert);
+        case T_Q5_0: return mmq_launch<T_Q5_0>(wmap, xmap, p, smem, st, n_expert);
+        case T_Q5_1: return mmq_launch<T_Q5_1>(wmap, xmap, p, smem, st, n_expert);
         case T_Q4_K: return mmq_launch<T_Q4_K>(wmap, xmap, p, smem, st, n_expert);
         case T_Q5_K: return mmq_launch<T_Q5_K>(wmap, xmap, p, smem, st, n_expert);
         case T_Q6_K: return mmq_launch<T_Q6_K>(wmap, xmap, p, smem, st, n_expert);

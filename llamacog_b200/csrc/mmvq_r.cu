@@ -11,6 +11,7 @@ namespace b200 {
 
 B200_MMVQR_DEFINE(T_Q4_K)
 B200_MMVQR_DEFINE(T_Q6_K)
+B200_MMVQR_DEFINE(T_Q8_0)
 
 static int env_i(const char * name, int dflt) { const char * e = getenv(name); return e ? atoi(e) : dflt; }
 
@@ -45,7 +46,7 @@ static bool fuse_ok(const b200_mmvq_args * a, int ng) {
         if (!al16(a->norm_x) || !al16(a->norm_w) || !al16(a->norm_y) || !al16(a->norm_out)) return false;
     }
     if (a->sm_act) {      // silu(gate) * up in the epilogue of a gate / up launch
-        if (ng != 2 || a->sm_op != B200_UNARY_SILU || !a->sm_out || !a->sm_counters || a->fuse_resid || a->rope || a->dbg_sumi || a->ids ||
+        if (ng != 2 || a->sm_op != B200_UNARY_SILU || !a->sm_out || a->fuse_resid || a->rope || a->dbg_sumi || a->ids ||
             a->hs_wait || a->hs_counter) return false;
         if (!al16(a->sm_act) || !al16(a->sm_out) || !al16(a->sm_xq)) return false;
     }
@@ -74,7 +75,8 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
                      small_mb = env_i("B200_MMVQR_SMALL_MB", 0), stagger = env_i("B200_MMVQR_STAGGER", 0);
     if (!fuse_ok(a, ng)) return MMVQR_SKIP;
     if (!on || a->M != 1 || (!a->Xq && !a->norm_x) || (!by_id && std::max(1, a->ny) != 1) || std::max(1, a->nz) != 1) return MMVQR_SKIP;
-    if (a->type != T_Q4_K && a->type != T_Q6_K) return MMVQR_SKIP;
+    static const int q8_on = env_i("B200_MMVQR_Q8_0", 1);
+    if (a->type != T_Q4_K && a->type != T_Q6_K && !(a->type == T_Q8_0 && q8_on)) return MMVQR_SKIP;
     if (a->dbg_sumi && ng != 1) return MMVQR_SKIP;
     const int K = a->K;
     if (K <= 0 || K % 256) return MMVQR_SKIP;
@@ -86,7 +88,8 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     const int rb = bpr * block_bytes(a->type);
     if (a->nb1 != rb || rb % 16 || ((uintptr_t)a->Xq & 15)) return MMVQR_SKIP;
     int ntot = 0;
-    const int unit = a->rope ? 2 : 1;                                 // rope epilogue: rows are dealt to the CTAs in pairs
+    const bool pair = a->sm_act != nullptr;                           // gate / up pair mode: every CTA owns whole 32-row blocks of both matrices
+    const int unit = pair ? 32 : a->rope ? 2 : 1;                     // rope epilogue: rows are dealt to the CTAs in pairs
     if (a->sm_act && (N[0] != N[1] || N[0] % 32)) return MMVQR_SKIP;
     for (int g = 0; g < ng; ++g) {
         if (((uintptr_t)W[g] & 15) || N[g] <= 0 || N[g] % unit) return MMVQR_SKIP;
@@ -100,8 +103,17 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     const int gx_max = std::max(ng, std::min(sm_count() * cps_eff, (ntot + rpp - 1) / rpp));
 
     mmvqr_params p = {};
-    p.ngroup = ng;
+    p.ngroup = pair ? 1 : ng;
     int used = 0, rows_per_cta = 1;
+    if (pair) {
+        // the same number of blocks for every CTA where possible: CTAs share HBM evenly, so the launch ends with its largest CTA
+        // (448 blocks of a 14336-row pair: 224 CTAs of two blocks, not 152 of two and 144 of one)
+        const int units = N[0] / 32, cap = std::max(1, sm_count() * cps_eff), per = (units + cap - 1) / cap, share = (units + per - 1) / per;
+        p.cta0[0] = 0; used = share;
+        for (int g = 0; g < 2; ++g) { p.Wg[g] = (const uint8_t *)W[g]; p.Dg[g] = probe ? nullptr : dst[g]; }
+        p.rows_qg[0] = units / share; p.rows_remg[0] = units % share;
+        rows_per_cta = 32 * ((units + share - 1) / share);
+    } else
     for (int g = 0; g < ng; ++g) {
         int share = g + 1 == ng ? std::max(1, gx_max - used) : std::max(1, (int)((int64_t)gx_max * N[g] / ntot));
         share = std::max(1, std::min(share, (N[g] / unit + rpp - 1) / rpp));
@@ -110,7 +122,7 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
         p.rows_qg[g] = N[g] / unit / share; p.rows_remg[g] = N[g] / unit % share;      // in units of `unit` rows
         rows_per_cta = std::max(rows_per_cta, unit * ((N[g] / unit + share - 1) / share));
     }
-    p.cta0[ng] = used;
+    p.cta0[p.ngroup] = used;
 
     // rows per stage: about stage_kb of weights, at least four stages per CTA when it has the rows for them
     auto round_up = [](int x, int m) { return (x + m - 1) / m * m; };
@@ -126,18 +138,18 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     const size_t budget = (size_t)smem_kb * 1024;
     const size_t per_stage = (size_t)stage_bytes + (size_t)R * nw * 4 + 16;
     const size_t act_bytes = (size_t)bpr * ACT_ITEM + (a->norm_x ? (size_t)K * 8 : 0);      // + the fp32 row of the fused norm and the norm weights
-    const size_t tail_bytes = 16 + 128 + ((a->fuse_resid || a->rope) ? (size_t)(rows_per_cta + 2) * 4 : 0) + 16;   // act barrier, norm partials, residual rows / rope cos-sin
+    const size_t tail_bytes = 16 + 128 + ((a->fuse_resid || a->rope) ? (size_t)(rows_per_cta + 2) * 4 : 0) + (pair ? (size_t)rows_per_cta * 8 : 0) + 16;   // act barrier, norm partials, residual rows / rope cos-sin
     if (budget < act_bytes + tail_bytes + 128 + per_stage) return MMVQR_SKIP;
     int nstages = (int)std::min<size_t>(max_stages, (budget - act_bytes - tail_bytes - 128) / per_stage);
     const bool rmp = ramp && !a->rope;
     const int q0 = rmp ? std::max(1, R >> 3) : R, q1 = rmp ? std::max(1, R >> 2) : R, q2 = rmp ? std::max(1, R >> 1) : R;
     const int need = rows_per_cta <= q0 ? 1 : rows_per_cta <= q0 + q1 ? 2 : rows_per_cta <= q0 + q1 + q2 ? 3 : 3 + (rows_per_cta - q0 - q1 - q2 + R - 1) / R;
-    nstages = std::min(nstages, need);
+    nstages = std::min(nstages, pair ? 2 * need : need);
     if (nstages < 1) return MMVQR_SKIP;
     if (probe) return 0;
 
     p.nx = a->norm_x; p.nw = a->norm_w; p.nnorm = a->norm_y; p.nout = a->norm_out; p.nxq = a->norm_x ? (uint8_t *)a->Xq : nullptr; p.neps = a->norm_eps;
-    p.resid = a->fuse_resid; p.dsum = a->fuse_sum; p.resid_rows = a->fuse_resid ? rows_per_cta : 0;
+    p.resid = a->fuse_resid; p.dsum = a->fuse_sum; p.resid_rows = (a->fuse_resid || pair) ? rows_per_cta : 0;      // pair mode: the CTA's gate sums live there
     if (a->rope) {
         const b200_gemv_rope * r = a->rope;
         p.rope_on = 1; p.rope_rows = rows_per_cta + 2;
@@ -153,7 +165,8 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     p.dbg_sumi = a->dbg_sumi;
     if (a->sm_act) {
         if (!al16(dst[0]) || !al16(dst[1])) return MMVQR_SKIP;
-        p.sm_act = a->sm_act; p.sm_out = a->sm_out; p.sm_xq = (uint8_t *)a->sm_xq; p.sm_cnt = a->sm_counters;
+        p.sm_act = a->sm_act; p.sm_out = a->sm_out; p.sm_xq = (uint8_t *)a->sm_xq;
+        p.rope_rows = rows_per_cta;                       // ... and its products behind them (the rope slot of the tail: never both)
     }
     if (by_id) {
         p.ids = a->ids; p.w_expert = a->w_sy;
@@ -165,7 +178,7 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     c.smem = (size_t)nstages * stage_bytes + act_bytes + (((size_t)nstages * R * nw + 1) & ~(size_t)1) * 4 + (size_t)nstages * 16 + tail_bytes;
     c.U = U;
     c.pdl = a->pdl >= 0 ? a->pdl : pdl_default();
-    const int rc = a->type == T_Q4_K ? mmvqr_launch_type<T_Q4_K>(p, c, stream) : mmvqr_launch_type<T_Q6_K>(p, c, stream);
+    const int rc = a->type == T_Q4_K ? mmvqr_launch_type<T_Q4_K>(p, c, stream) : a->type == T_Q6_K ? mmvqr_launch_type<T_Q6_K>(p, c, stream) : mmvqr_launch_type<T_Q8_0>(p, c, stream);
     if (rc) return rc;
     ++g_launches;
     return 0;

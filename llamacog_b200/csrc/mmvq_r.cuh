@@ -62,17 +62,13 @@ struct mmvqr_params {
     // expert), read on the device after the PDL wait (the ids come out of the router kernels of the same step); its activations
     // are column xq_col[g] of Xq
     const int32_t * ids; int64_t w_expert; int xq_col[3];
-    // gate (matrix 0) / up (matrix 1) launch: the CTA that completes a 32-row block of both results computes silu(gate) * up and its
-    // q8 activations for that block (the arithmetic of unary_mul_kernel<SILU>, fused.cu): sm_cnt[b] counts the (matrix, CTA) pieces
-    // of block b that have been stored; the last one does the block and leaves the counter at zero for the next launch
-    float * sm_act; float * sm_out; uint8_t * sm_xq; unsigned * sm_cnt;
+    // gate (matrix 0) / up (matrix 1) launch in PAIR mode: every CTA owns the same whole 32-row blocks of BOTH matrices (it streams its
+    // gate rows, then its up rows: 2 * nst stages), keeps its gate sums in shared memory and, as the up sums arrive, stores
+    // silu(gate), silu(gate) * up and finally the q8 activations of its blocks (the arithmetic of unary_mul_kernel<SILU>, fused.cu).
+    // No cross-CTA traffic.  (The first version dealt gate and up rows to different CTAs and counted 32-row blocks with atomics:
+    // two fences, an atomic and a dependent load on the tail of every CTA cost what the removed launch had cost.)
+    float * sm_act; float * sm_out; uint8_t * sm_xq;
 };
-
-// the CTA (within its matrix' range of CTAs) that owns row n: the first `rem` CTAs have q + 1 rows, the others q
-__device__ __forceinline__ int sm_cta_of(int n, int q, int rem) {
-    const int cut = rem * (q + 1);
-    return n < cut ? n / (q + 1) : rem + (n - cut) / q;
-}
 
 struct hacts { int q[4][8]; float d8[4], dsq[4]; int m32a[4], m32b[4]; };
 
@@ -91,12 +87,20 @@ __device__ __forceinline__ void load_hacts(uint32_t sp, hacts & a) {
 template <int TYPE> struct hweights;
 template <> struct hweights<T_Q4_K> { int hd[4]; int w[16]; };
 template <> struct hweights<T_Q6_K> { int ql[16]; int qh[8]; int sc[2]; uint32_t d; };
+template <> struct hweights<T_Q8_0> { int w[34]; };      // four blocks of {d (f16), qs int8[32]}: 136 bytes, 8-byte aligned
 
 // ip: shared address of the item, hh: which half
 template <int TYPE> __device__ __forceinline__ void load_hweights(uint32_t ip, int hh, hweights<TYPE> & w) {
     if constexpr (TYPE == T_Q4_K) {
         lds_words<4, true>(ip, w.hd);
         lds_words<16, true>(ip + 16 + 64 * hh, w.w);
+    } else if constexpr (TYPE == T_Q8_0) {
+#pragma unroll
+        for (int i = 0; i < 17; ++i) {
+            uint32_t lo, hi;
+            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(ip + 136 * hh + 8 * i));
+            w.w[2 * i] = (int)lo; w.w[2 * i + 1] = (int)hi;
+        }
     } else {
         lds_words_a2<16>(ip + 64 * hh, w.ql);
         lds_words_a2<8>(ip + 128 + 32 * hh, w.qh);
@@ -133,6 +137,17 @@ __device__ __forceinline__ float half_dot(const hweights<TYPE> & w, const hacts 
             accm = fmaf(a.dsq[2 * p + 1], byte2f(mn4, 2 * p + 1), accm);
         }
         return dm.x * accd - dm.y * accm;
+    } else if constexpr (TYPE == T_Q8_0) {         // vecdotq.cuh:153-165: d_w * d8 * sum q_w q_x per 32-block
+        float acc = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int s = 0;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s = dp4a_ss(word_at_half<34>(w.w, 17 * j + 1 + 2 * k), a.q[j][k], s);
+            if constexpr (DBG) dbg[j] = s;
+            acc = fmaf(half_bits_to_float(halfword<34>(w.w, 17 * j)) * a.d8[j], i2f_small(s), acc);
+        }
+        return acc;
     } else {
         const float d = half_bits_to_float(w.d);
         float acc6 = 0.0f;
@@ -180,7 +195,8 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
     cta -= p.cta0[g];
     const uint8_t * Wc = p.Wg[g];
     float * Dc = p.Dg[g];
-    const int unit = p.rope_on ? 2 : 1;        // rope: rows are dealt in pairs (rows_qg / rows_remg count pairs)
+    const bool pair = p.sm_act != nullptr;     // gate / up pair mode: this CTA's rows of matrix 0, then the same rows of matrix 1
+    const int unit = pair ? 32 : p.rope_on ? 2 : 1;        // rope: rows are dealt in pairs, pair mode: in 32-row blocks (rows_qg / rows_remg count units)
     const int row_lo = unit * (cta * p.rows_qg[g] + min(cta, p.rows_remg[g]));
     const int nrows = unit * (p.rows_qg[g] + (cta < p.rows_remg[g] ? 1 : 0));
     // Stage s of this CTA covers rows [srow(s), srow(s) + snr(s)) of its range.  The first three stages are short (r0, r1,
@@ -191,6 +207,7 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
     auto srow = [&](int s) { return s == 0 ? 0 : s == 1 ? p.r0 : s == 2 ? p.r0 + p.r1 : rampC + (s - 3) * p.R; };
     auto snr = [&](int s) { return min(s == 0 ? p.r0 : s == 1 ? p.r1 : s == 2 ? p.r2 : p.R, nrows - srow(s)); };
     const int nst = nrows <= p.r0 ? 1 : nrows <= p.r0 + p.r1 ? 2 : nrows <= rampC ? 3 : 3 + (nrows - rampC + p.R - 1) / p.R;
+    const int nsv = pair ? 2 * nst : nst;      // stages this CTA streams (pair mode: sv < nst matrix 0, else matrix 1)
 
     if (tid == 0) {
         for (int s = 0; s < p.nstages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 8); }
@@ -203,12 +220,13 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
 
     if (warp == 0) {
         const uint64_t pol = policy_evict_first();
-        auto issue = [&](int s) {   // lane 0 only
-            const int slot = s % p.nstages;
+        auto issue = [&](int sv) {   // lane 0 only
+            const int slot = sv % p.nstages;
+            const int m = pair && sv >= nst ? 1 : 0, s = sv - m * nst;
             const int r0 = row_lo + srow(s), nr = snr(s);
             const uint32_t bytes = (uint32_t)nr * p.rb, bar = full0 + 8 * slot;
             mbar_expect_tx(bar, bytes);
-            bulk_g2s_stream(smem_u32(stages + (size_t)slot * p.stage_bytes), Wc + (int64_t)r0 * p.rb, bytes, bar, pol);
+            bulk_g2s_stream(smem_u32(stages + (size_t)slot * p.stage_bytes), (m ? p.Wg[1] : Wc) + (int64_t)r0 * p.rb, bytes, bar, pol);
         };
         // NORM kernels follow another mat-vec directly (no early residency), so their row must not queue behind the whole
         // weight prefetch in the SM's copy engine: norm weights and the first stage before the wait, the row right after
@@ -216,8 +234,8 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
         // copies of the same lines about 1 us: profiles/r01_ktrace_tg_v6.txt.)
         if (lane == 0 && !p.ids) {
             if (NORM) { mbar_expect_tx(wbar, (uint32_t)p.K * 4); bulk_g2s(smem_u32(ws), p.nw, (uint32_t)p.K * 4, wbar); }
-            for (int s = 0; s < min(nst, (NORM || p.stagger) ? 1 : p.nstages); ++s) issue(s);
-            if (!NORM && p.stagger && nst > 1) { mbar_wait(full0, 0); for (int s = 1; s < min(nst, p.nstages); ++s) issue(s); }
+            for (int s = 0; s < min(nsv, (NORM || p.stagger) ? 1 : p.nstages); ++s) issue(s);
+            if (!NORM && p.stagger && nsv > 1) { mbar_wait(full0, 0); for (int s = 1; s < min(nsv, p.nstages); ++s) issue(s); }
         }
         const int rmode = p.rope_on ? p.rmode[g] : 0;
         if (rmode == 1 || rmode == 2) {
@@ -239,19 +257,34 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
             const uint32_t ab = NORM ? (uint32_t)p.K * 4 : (uint32_t)p.BPR * ACT_ITEM;
             mbar_expect_tx(actbar, ab);
             bulk_g2s(NORM ? smem_u32(xs) : smem_u32(act), NORM ? (const void *)p.nx : (const void *)(p.Xq + (size_t)(p.ids ? p.xq_col[g] : 0) * ab), ab, actbar);
-            if (NORM) for (int s = 1; s < min(nst, p.nstages); ++s) issue(s);
-            if (p.ids) for (int s = 0; s < min(nst, p.nstages); ++s) issue(s);
+            if (NORM) for (int s = 1; s < min(nsv, p.nstages); ++s) issue(s);
+            if (p.ids) for (int s = 0; s < min(nsv, p.nstages); ++s) issue(s);
         }
         if (p.resid) {        // this CTA's rows of the residual, fetched while the first stage is being multiplied
             for (int o = lane; o < nrows; o += 32) rsd[o] = p.resid[row_lo + o];
             __syncwarp();
         }
-        for (int s = 0; s < nst; ++s) {
-            const int slot = s % p.nstages;
-            mbar_wait(empty0 + 8 * slot, (s / p.nstages) & 1);
+        for (int sv = 0; sv < nsv; ++sv) {
+            const int slot = sv % p.nstages;
+            mbar_wait(empty0 + 8 * slot, (sv / p.nstages) & 1);
+            const int mtx = pair && sv >= nst ? 1 : 0, s = sv - mtx * nst;
             const int r0 = row_lo + srow(s), nr = snr(s);
             const float * ps = partials + (size_t)slot * part_stage;
-            if (rmode == 0) {
+            if (pair) {
+                // rsd: this CTA's gate sums, csn: its products (both nrows floats of shared memory)
+                for (int o = lane; o < nr; o += 32) {
+                    float sum = 0.0f;
+                    for (int wv = 0; wv < NW; ++wv) sum += ps[o * NW + wv];
+                    const int n = r0 + o, l = n - row_lo;
+                    if (mtx == 0) { p.Dg[0][n] = sum; rsd[l] = sum; }
+                    else {
+                        const float av = silu_fn(rsd[l]), y = av * sum;
+                        p.Dg[1][n] = sum;              // act / out may sit on the gate / up results: these stores come last, act before out
+                        p.sm_act[n] = av; p.sm_out[n] = y;
+                        csn[l] = y;
+                    }
+                }
+            } else if (rmode == 0) {
                 for (int o = lane; o < nr; o += 32) {
                     float sum = 0.0f;
                     for (int wv = 0; wv < NW; ++wv) sum += ps[o * NW + wv];
@@ -286,39 +319,19 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
                 }
             }
             __syncwarp();
-            if (lane == 0 && s + p.nstages < nst) issue(s + p.nstages);
-            if (s == 0) ktrace_event(2);       // first stage consumed and stored
+            if (lane == 0 && sv + p.nstages < nsv) issue(sv + p.nstages);
+            if (sv == 0) ktrace_event(2);       // first stage consumed and stored
         }
         ktrace_event(3);                       // all rows of CTA 0 stored
-        if (p.sm_act) {
-            // gate / up: count this CTA's piece into every 32-row block it touched; whoever completes a block multiplies it out
+        if (pair && p.sm_xq) {
+            // the q8 activations of this CTA's 32-row blocks, four blocks per pass (an 8-lane group each)
             __syncwarp();
-            __threadfence();                   // this warp's stores of Dc are visible before the count
-            const int b_lo = row_lo >> 5, b_hi = (row_lo + nrows - 1) >> 5;
-            for (int b = b_lo; b <= b_hi; ++b) {
-                int last = 0;
-                if (lane == 0) {
-                    int expect = 0;
-#pragma unroll
-                    for (int m = 0; m < 2; ++m)
-                        expect += sm_cta_of(32 * b + 31, p.rows_qg[m], p.rows_remg[m]) - sm_cta_of(32 * b, p.rows_qg[m], p.rows_remg[m]) + 1;
-                    last = atomicAdd(&p.sm_cnt[b], 1u) + 1u == (unsigned)expect;
-                    if (last) p.sm_cnt[b] = 0u;
-                }
-                last = __shfl_sync(0xffffffffu, last, 0);
-                if (!last) continue;           // (warp-uniform)
-                __threadfence();               // the other pieces' stores are visible after the count
+            for (int b0 = 0; 32 * b0 < nrows; b0 += 4) {
+                const int bl = b0 + (lane >> 3);
+                const bool in = 32 * bl < nrows;
                 float4 y = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-                const bool in = lane < 8;
-                if (in) {
-                    const int i = 8 * b + lane;
-                    const float4 x = __ldcg(reinterpret_cast<const float4 *>(p.Dg[0]) + i), u = __ldcg(reinterpret_cast<const float4 *>(p.Dg[1]) + i);
-                    const float4 a = make_float4(silu_fn(x.x), silu_fn(x.y), silu_fn(x.z), silu_fn(x.w));
-                    y = make_float4(a.x * u.x, a.y * u.y, a.z * u.z, a.w * u.w);
-                    reinterpret_cast<float4 *>(p.sm_act)[i] = a;
-                    reinterpret_cast<float4 *>(p.sm_out)[i] = y;
-                }
-                if (p.sm_xq) quant_block_store(y, in ? b : 0, lane & 7, in, p.sm_xq);
+                if (in) { const float * yp = csn + 32 * bl + 4 * (lane & 7); y = make_float4(yp[0], yp[1], yp[2], yp[3]); }
+                quant_block_store(y, in ? (row_lo >> 5) + bl : 0, lane & 7, in, p.sm_xq);
             }
         }
         if (p.hs.counter) {                    // row split: the last CTA of the launch lowers / raises / awaits the hand-over flags
@@ -399,11 +412,12 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
         if (active) load_hacts(smem_u32(act) + (uint32_t)b * ACT_ITEM + hh * (4 * ACT_BLK), a);
         const uint32_t ioff = (uint32_t)b * IB;
         const int nb32 = p.K >> 5;
-        for (int s = 0; s < nst; ++s) {
-            const int slot = s % p.nstages;
+        for (int sv = 0; sv < nsv; ++sv) {
+            const int slot = sv % p.nstages;
+            const int s = pair && sv >= nst ? sv - nst : sv;
             const int r0 = row_lo + srow(s), nr = snr(s);
-            mbar_wait(full0 + 8 * slot, (s / p.nstages) & 1);
-            if (s == 0) ktrace_event(7, 32);       // first weights have landed
+            mbar_wait(full0 + 8 * slot, (sv / p.nstages) & 1);
+            if (sv == 0) ktrace_event(7, 32);       // first weights have landed
             const uint32_t sbase = smem_u32(stages + (size_t)slot * p.stage_bytes) + ioff;
             float * pw = partials + (size_t)slot * part_stage;
             // U passes (rows rr, rr + RPP, ..) in flight per thread: independent shared loads and dp4a chains

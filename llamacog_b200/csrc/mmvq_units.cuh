@@ -19,8 +19,9 @@
 // take pre-quantised activations (large K, small N: per-CTA re-quantisation would cost more than
 // the dot products there).
 // The integer dot products are those of reference ggml-cuda/vecdotq.cuh:25-44 (q4_0), 153-165
-// (q8_0), 359-381 (q4_K), 415-444 (q5_K), 478-498 (q6_K); integer sums are order independent and
-// therefore bit-exact; the fp32 combination order is ours.
+// (q8_0), 359-381 (q4_K), 415-444 (q5_K), 478-498 (q6_K), 49-80 (q4_1), 82-115 (q5_0), 117-150 (q5_1); integer sums are order
+// independent and therefore bit-exact; the fp32 combination order is ours.  Where the reference multiplies a block minimum or
+// offset with s8 = fp16(sum of the unquantised x) (q4_0, q4_1, q5_0, q5_1) we use the exact d8 * sum q of the layout's tail.
 #pragma once
 #include "common.cuh"
 
@@ -29,6 +30,9 @@ namespace b200 {
 template <int TYPE> struct item_traits;
 template <> struct item_traits<T_Q4_0> { static constexpr int BYTES = 144; };
 template <> struct item_traits<T_Q8_0> { static constexpr int BYTES = 272; };
+template <> struct item_traits<T_Q4_1> { static constexpr int BYTES = 160; };   // 8 x {d, m, qs[16]}
+template <> struct item_traits<T_Q5_0> { static constexpr int BYTES = 176; };   // 8 x {d, qh[4], qs[16]}
+template <> struct item_traits<T_Q5_1> { static constexpr int BYTES = 192; };   // 8 x {d, m, qh[4], qs[16]}
 template <> struct item_traits<T_Q4_K> { static constexpr int BYTES = 144; };
 template <> struct item_traits<T_Q5_K> { static constexpr int BYTES = 176; };
 template <> struct item_traits<T_Q6_K> { static constexpr int BYTES = 210; };
@@ -111,6 +115,70 @@ __device__ __forceinline__ void item_dot(uint32_t wp, uint32_t ap, uint32_t acs,
                     const int s = s0 + (s1 >> 4);
                     if constexpr (DBG) dbg[m * dms + i] = s;
                     acc[m] = fmaf(dw * a.d8, i2f_small(s + ((a.m32a + a.m32b) >> 2)), acc[m]);
+                }
+            }
+        }
+    } else if constexpr (TYPE == T_Q4_1) {
+        int w[40];                                       // block i = words 5i .. 5i+4: (d, m) | qs[16]
+        lds_words<40, A16>(wp, w);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (i < nblk) {
+                const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&w[5 * i]));
+                uint32_t lo[4], hi[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { lo[j] = (uint32_t)w[5 * i + 1 + j] & 0x0F0F0F0Fu; hi[j] = (uint32_t)w[5 * i + 1 + j] & 0xF0F0F0F0u; }
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    act_blk a; lds_act(ap + m * acs + i * ACT_BLK, a);
+                    int s0 = 0, s1 = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { s0 = dp4a_us(lo[j], a.q[j], s0); s1 = dp4a_us(hi[j], a.q[4 + j], s1); }
+                    const int s = s0 + (s1 >> 4);
+                    if constexpr (DBG) dbg[m * dms + i] = s;
+                    acc[m] = fmaf(dm.x * a.d8, i2f_small(s), fmaf(dm.y, a.dsq, acc[m]));
+                }
+            }
+        }
+    } else if constexpr (TYPE == T_Q5_0 || TYPE == T_Q5_1) {
+        // fifth bits: bit j of qh belongs to element j; the four bits of a word of low (high) nibbles are spread to bit 4 of its
+        // bytes by one multiply (x * 0x00204081 puts bit k of x at bit 8k: the four shifted copies do not overlap)
+        constexpr int NW = TYPE == T_Q5_0 ? 44 : 48;
+        int w[NW];
+        lds_words<NW, A16>(wp, w);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (i < nblk) {
+                float dw, mw = 0.0f; uint32_t qh, qs[4];
+                if constexpr (TYPE == T_Q5_0) {          // block i = halfwords 11i .. 11i+10: d | qh[4] | qs[16]
+                    dw = half_bits_to_float(halfword<NW>(w, 11 * i));
+                    qh = (uint32_t)word_at_half<NW>(w, 11 * i + 1);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) qs[j] = (uint32_t)word_at_half<NW>(w, 11 * i + 3 + 2 * j);
+                } else {                                 // block i = words 6i .. 6i+5: (d, m) | qh | qs[16]
+                    const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&w[6 * i]));
+                    dw = dm.x; mw = dm.y;
+                    qh = (uint32_t)w[6 * i + 1];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) qs[j] = (uint32_t)w[6 * i + 2 + j];
+                }
+                uint32_t lo[4], hi[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t b0 = ((((qh >> (4 * j)) & 0xFu) * 0x00204081u) & 0x01010101u) << 4;
+                    const uint32_t b1 = ((((qh >> (16 + 4 * j)) & 0xFu) * 0x00204081u) & 0x01010101u) << 4;
+                    lo[j] = (qs[j] & 0x0F0F0F0Fu) | b0;
+                    hi[j] = ((qs[j] >> 4) & 0x0F0F0F0Fu) | b1;
+                }
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    act_blk a; lds_act(ap + m * acs + i * ACT_BLK, a);
+                    int s = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { s = dp4a_us(lo[j], a.q[j], s); s = dp4a_us(hi[j], a.q[4 + j], s); }
+                    if constexpr (DBG) dbg[m * dms + i] = s;
+                    if constexpr (TYPE == T_Q5_0) acc[m] = fmaf(dw * a.d8, i2f_small(s + ((a.m32a + a.m32b) >> 1)), acc[m]);   // (q - 16): -16 * sum q
+                    else acc[m] = fmaf(dw * a.d8, i2f_small(s), fmaf(mw, a.dsq, acc[m]));
                 }
             }
         }

@@ -141,18 +141,20 @@ def _nodes(path):
     return out
 
 
-@pytest.mark.parametrize("preset,n_prompt", [("tiny", 70), ("tiny-moe", 40), ("llama3.2-1b", 40)])
-def test_per_node_parity_with_reference_cpu_backend(tmp_path, preset, n_prompt):
+@pytest.mark.parametrize("preset,n_prompt,ftype", [("tiny", 70, "q4_k_m"), ("tiny-moe", 40, "q4_k_m"), ("llama3.2-1b", 40, "q4_k_m"),
+                                                   ("tiny", 70, "q4_1"), ("tiny", 70, "q5_0"), ("tiny", 70, "q5_1"), ("tiny-moe", 40, "q5_0")])
+def test_per_node_parity_with_reference_cpu_backend(tmp_path, preset, n_prompt, ftype):
     """The fixed-seed twin of the end-to-end logits test, node by node.  The model runs on the plugin with the scheduler's eval
     callback (ggml-backend.cpp:1415-1447) handing out every MUL_MAT / MUL_MAT_ID / FLASH_ATTN_EXT node of the prefill graph (MMQ +
     tensor-core attention) and of two decode graphs (MMVQ + vector attention); tests/host/logits_check.cpp re-evaluates each node
     on the reference CPU backend FROM THE SAME INPUT BYTES (read back from the device, strides kept) and records the NMSE.  That is
     ggml_backend_compare_graph_backend (ggml-backend.cpp:1829-1865) with the inputs re-synchronised per node, so nothing drifts and
-    the bar is the reference's own per-op bar: 5e-4 (tests/test-backend-ops.cpp:1049), for every node of every layer.  (The
+    the bar is the reference's own per-op bar: 5e-4 (tests/test-backend-ops.cpp:1049), for every node of every layer; q4_1 / q5_0 /
+    q5_1 models (round-2 widening) go through the same twin.  (The
     callback splits the graph per observed node: this is the unfused path; fused == unfused bit for bit is test_gpu_fused.py.)"""
     _need()
     model = str(tmp_path / (preset + ".gguf"))
-    subprocess.check_call([sys.executable, os.path.join(ROOT, "tools", "make_gguf.py"), preset, "q4_k_m", model], stdout=subprocess.DEVNULL)
+    subprocess.check_call([sys.executable, os.path.join(ROOT, "tools", "make_gguf.py"), preset, ftype, model], stdout=subprocess.DEVNULL)
     exe = os.path.join(ROOT, "tests", "host", "build", "logits_check")
     nodes = str(tmp_path / "nodes.bin")
     r = subprocess.run([exe, model, str(tmp_path / "gpu.bin"), "99", "1", str(n_prompt), "2", "512", "none", nodes],
