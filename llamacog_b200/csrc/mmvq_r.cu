@@ -85,7 +85,7 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     int tpr = 1, lg = 0;
     while (tpr < hpr) { tpr <<= 1; ++lg; }
     if (hpr * 10 < tpr * 6) return MMVQR_SKIP;                       // more than 40 % of the lanes would idle
-    const int rb = bpr * block_bytes(a->type);
+    const int rb = K / block_elems(a->type) * block_bytes(a->type);     // (Q8_0: eight 34-byte blocks per 256-weight item)
     if (a->nb1 != rb || rb % 16 || ((uintptr_t)a->Xq & 15)) return MMVQR_SKIP;
     int ntot = 0;
     const bool pair = a->sm_act != nullptr;                           // gate / up pair mode: every CTA owns whole 32-row blocks of both matrices
