@@ -513,10 +513,11 @@ def main():
                     traffic = json.load(open(tpath)).get("dram_bytes_per_launch_token_mix")
                 k1 = kernel_roofline(max(20, min(args.steps, 200)), args.warmup, local, grouped=False)
                 line["roofline"] = {"bound": "hbm", "kernel": "mmvqr_kernel<Q4_K> as the plugin issues it in the timed region (%d launches per token: q/k/v group, wo, gate/up group, down)" % k["launches"],
-                                    "achieved": k["gbps"], "peak": peak, "unit": "GB/s", "frac": k["gbps"] / peak, "traffic": traffic,
+                                    "achieved": k["gbps"], "peak": peak, "unit": "GB/s", "frac": k["gbps"] / peak,
+                                    "traffic": int(traffic * k1["launches"] / k["launches"]) if traffic else None,
                                     "peak_source": how, "launches": k["launches"], "us_per_launch": k["us_per_launch"],
                                     "algorithmic_bytes_per_launch": k["bytes"] / k["launches"],
-                                    "traffic_note": "ncu DRAM bytes per launch of the single-matrix launches (profiles/r01_mmvqr_q4k_traffic.json): 1.002 x algorithmic",
+                                    "traffic_note": "ncu --set full of the four Q4_K shapes as single-matrix launches (profiles/r01_mmvqr_q4k_traffic.json: DRAM bytes = 1.002 x algorithmic, weights are read once however the matrices are grouped), re-expressed per issued launch",
                                     "single_launches": {"note": "the same matrices, every one a launch of its own (the round-1 form of this figure; the step never issues wk / wv alone)",
                                                         "launches": k1["launches"], "us_per_launch": k1["us_per_launch"], "achieved": k1["gbps"], "frac": k1["gbps"] / peak,
                                                         "algorithmic_bytes_per_launch": k1["bytes"] / k1["launches"]},

@@ -219,8 +219,20 @@ int b200_op_soft_max(const b200_tensor * src, const b200_tensor * mask, const b2
                      void * stream);
 /* row-wise argsort (order 0 ascending, 1 descending), dst i32; ne0 <= 1024.  Replaces ggml-cuda/argsort.cu:11-. */
 int b200_op_argsort(const b200_tensor * src, const b200_tensor * dst, int order, void * stream);
+/* probs = SOFT_MAX(src * scale) (no mask), order = ARGSORT(probs) in one launch: the router of a MoE layer (reference
+ * src/llama-graph.cpp:663-693; ggml-cuda softmax.cu + argsort.cu).  Rows of <= 1024 contiguous f32; both outputs bit-identical to the
+ * two operators. */
+int b200_op_soft_max_argsort(const b200_tensor * src, const b200_tensor * probs, const b200_tensor * order, float scale, int desc, void * stream);
 /* dst[0, r] = sum over row r.  Replaces ggml-cuda/sumrows.cu. */
 int b200_op_sum_rows(const b200_tensor * src, const b200_tensor * dst, void * stream);
+/* The tail of a MoE layer for a few tokens (reference src/llama-graph.cpp:696-775 build_moe_ffn; run there as ggml-cuda getrows.cu,
+ * sumrows.cu, binbcast.cu x (2 + n_used - 1)) in one launch:
+ *   w = GET_ROWS(probs [1, n_expert, T], ids [n_used, T]); wsum = SUM_ROWS(w); wnorm = w / wsum;
+ *   weighted = experts [n_embd, n_used, T] * wnorm; adds[k] = (k ? adds[k - 1] : weighted[:, 0]) + weighted[:, k + 1]
+ * Every output holds the bits the single operators give it.  2 <= n_used <= 8; w / wnorm [n_used, T], wsum [T], weighted like
+ * experts (may be the same memory), adds[0 .. n_used - 2] [n_embd, T], all contiguous f32. */
+int b200_op_moe_combine(const b200_tensor * probs, const b200_tensor * ids, const b200_tensor * experts, float * w, float * wsum, float * wnorm,
+                        float * weighted, float * const * adds, void * stream);
 /* softmax(scale * Q K^T + slope * mask [softcap]) V with online softmax and GQA broadcast; Q f32 [D, n_batch, n_head],
  * K/V f16 or q8_0 [D, n_kv, n_head_kv] (strided views of the KV cache), mask f16 [n_kv, >= n_batch], dst f32
  * [D, n_head, n_batch].  Replaces ggml_cuda_flash_attn_ext (ggml-cuda/fattn.cu:271-346); op contract

@@ -12,6 +12,8 @@ namespace b200 {
 B200_MMVQR_DEFINE(T_Q4_K)
 B200_MMVQR_DEFINE(T_Q6_K)
 B200_MMVQR_DEFINE(T_Q8_0)
+B200_MMVQR_DEFINE(T_Q4_0)
+B200_MMVQR_DEFINE(T_Q5_K)
 
 static int env_i(const char * name, int dflt) { const char * e = getenv(name); return e ? atoi(e) : dflt; }
 
@@ -75,8 +77,8 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
                      small_mb = env_i("B200_MMVQR_SMALL_MB", 0), stagger = env_i("B200_MMVQR_STAGGER", 0);
     if (!fuse_ok(a, ng)) return MMVQR_SKIP;
     if (!on || a->M != 1 || (!a->Xq && !a->norm_x) || (!by_id && std::max(1, a->ny) != 1) || std::max(1, a->nz) != 1) return MMVQR_SKIP;
-    static const int q8_on = env_i("B200_MMVQR_Q8_0", 1);
-    if (a->type != T_Q4_K && a->type != T_Q6_K && !(a->type == T_Q8_0 && q8_on)) return MMVQR_SKIP;
+    static const int more_on = env_i("B200_MMVQR_MORE", 1);      // Q8_0 / Q4_0 / Q5_K (round 2); 0: only Q4_K and Q6_K take this kernel
+    if (a->type != T_Q4_K && a->type != T_Q6_K && !((a->type == T_Q8_0 || a->type == T_Q4_0 || a->type == T_Q5_K) && more_on)) return MMVQR_SKIP;
     if (a->dbg_sumi && ng != 1) return MMVQR_SKIP;
     const int K = a->K;
     if (K <= 0 || K % 256) return MMVQR_SKIP;
@@ -178,7 +180,14 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     c.smem = (size_t)nstages * stage_bytes + act_bytes + (((size_t)nstages * R * nw + 1) & ~(size_t)1) * 4 + (size_t)nstages * 16 + tail_bytes;
     c.U = U;
     c.pdl = a->pdl >= 0 ? a->pdl : pdl_default();
-    const int rc = a->type == T_Q4_K ? mmvqr_launch_type<T_Q4_K>(p, c, stream) : a->type == T_Q6_K ? mmvqr_launch_type<T_Q6_K>(p, c, stream) : mmvqr_launch_type<T_Q8_0>(p, c, stream);
+    int rc = -1;
+    switch (a->type) {
+        case T_Q4_K: rc = mmvqr_launch_type<T_Q4_K>(p, c, stream); break;
+        case T_Q6_K: rc = mmvqr_launch_type<T_Q6_K>(p, c, stream); break;
+        case T_Q8_0: rc = mmvqr_launch_type<T_Q8_0>(p, c, stream); break;
+        case T_Q4_0: rc = mmvqr_launch_type<T_Q4_0>(p, c, stream); break;
+        case T_Q5_K: rc = mmvqr_launch_type<T_Q5_K>(p, c, stream); break;
+    }
     if (rc) return rc;
     ++g_launches;
     return 0;

@@ -88,19 +88,26 @@ template <int TYPE> struct hweights;
 template <> struct hweights<T_Q4_K> { int hd[4]; int w[16]; };
 template <> struct hweights<T_Q6_K> { int ql[16]; int qh[8]; int sc[2]; uint32_t d; };
 template <> struct hweights<T_Q8_0> { int w[34]; };      // four blocks of {d (f16), qs int8[32]}: 136 bytes, 8-byte aligned
+template <> struct hweights<T_Q4_0> { int w[18]; };      // four blocks of {d (f16), qs[16]}: 72 bytes, 8-byte aligned
+template <> struct hweights<T_Q5_K> { int hd[4]; int qh[8]; int w[16]; };      // header, the fifth bits of all 256 weights, this half's 64 code bytes
 
 // ip: shared address of the item, hh: which half
 template <int TYPE> __device__ __forceinline__ void load_hweights(uint32_t ip, int hh, hweights<TYPE> & w) {
     if constexpr (TYPE == T_Q4_K) {
         lds_words<4, true>(ip, w.hd);
         lds_words<16, true>(ip + 16 + 64 * hh, w.w);
-    } else if constexpr (TYPE == T_Q8_0) {
+    } else if constexpr (TYPE == T_Q8_0 || TYPE == T_Q4_0) {
+        constexpr int HB = TYPE == T_Q8_0 ? 136 : 72;
 #pragma unroll
-        for (int i = 0; i < 17; ++i) {
+        for (int i = 0; i < HB / 8; ++i) {
             uint32_t lo, hi;
-            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(ip + 136 * hh + 8 * i));
+            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(ip + HB * hh + 8 * i));
             w.w[2 * i] = (int)lo; w.w[2 * i + 1] = (int)hi;
         }
+    } else if constexpr (TYPE == T_Q5_K) {
+        lds_words<4, true>(ip, w.hd);
+        lds_words<8, true>(ip + 16, w.qh);
+        lds_words<16, true>(ip + 48 + 64 * hh, w.w);
     } else {
         lds_words_a2<16>(ip + 64 * hh, w.ql);
         lds_words_a2<8>(ip + 128 + 32 * hh, w.qh);
@@ -137,6 +144,46 @@ __device__ __forceinline__ float half_dot(const hweights<TYPE> & w, const hacts 
             accm = fmaf(a.dsq[2 * p + 1], byte2f(mn4, 2 * p + 1), accm);
         }
         return dm.x * accd - dm.y * accm;
+    } else if constexpr (TYPE == T_Q5_K) {         // vecdotq.cuh:415-444: as Q4_K with bit (sub-block) of qh[l] as the code's fifth bit
+        const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&w.hd[0]));
+        const uint32_t h1 = (uint32_t)w.hd[1], h2 = (uint32_t)w.hd[2], h3 = (uint32_t)w.hd[3];
+        const uint32_t sc4 = hh ? ((h3 & 0x0F0F0F0Fu) | ((h1 >> 2) & 0x30303030u)) : (h1 & 0x3F3F3F3Fu);
+        const uint32_t mn4 = hh ? (((h3 >> 4) & 0x0F0F0F0Fu) | ((h2 >> 2) & 0x30303030u)) : (h2 & 0x3F3F3F3Fu);
+        float accd = 0.0f, accm = 0.0f;
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            int s0 = 0, s1 = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t q = (uint32_t)w.w[8 * p + j];
+                const uint32_t hb = hh ? ((uint32_t)w.qh[j] >> 4) : (uint32_t)w.qh[j];        // this half's four sub-block bits at bits 0..3
+                const uint32_t b0 = (hb << (4 - 2 * p)) & 0x10101010u, b1 = (hb << (3 - 2 * p)) & 0x10101010u;
+                s0 = dp4a_us((q & 0x0F0F0F0Fu) | b0, a.q[2 * p][j], s0);
+                s1 = dp4a_us(((q >> 4) & 0x0F0F0F0Fu) | b1, a.q[2 * p + 1][j], s1);
+            }
+            if constexpr (DBG) { dbg[2 * p] = s0; dbg[2 * p + 1] = s1; }
+            accd = fmaf(a.d8[2 * p], i2f_small(s0) * byte2f(sc4, 2 * p), accd);
+            accd = fmaf(a.d8[2 * p + 1], i2f_small(s1) * byte2f(sc4, 2 * p + 1), accd);
+            accm = fmaf(a.dsq[2 * p], byte2f(mn4, 2 * p), accm);
+            accm = fmaf(a.dsq[2 * p + 1], byte2f(mn4, 2 * p + 1), accm);
+        }
+        return dm.x * accd - dm.y * accm;
+    } else if constexpr (TYPE == T_Q4_0) {         // vecdotq.cuh:25-44: d_w * d8 * (sum nibble q_x - 8 sum q_x) per 32-block
+        float acc = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int s0 = 0, s1 = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t q = (uint32_t)word_at_half<18>(w.w, 9 * j + 1 + 2 * k);
+                s0 = dp4a_us(q & 0x0F0F0F0Fu, a.q[j][k], s0);
+                s1 = dp4a_us(q & 0xF0F0F0F0u, a.q[j][4 + k], s1);          // 16 x nibble, divided out below
+            }
+            const int s = s0 + (s1 >> 4);
+            if constexpr (DBG) dbg[j] = s;
+            acc = fmaf(half_bits_to_float(halfword<18>(w.w, 9 * j)) * a.d8[j], i2f_small(s + ((a.m32a[j] + a.m32b[j]) >> 2)), acc);
+        }
+        return acc;
     } else if constexpr (TYPE == T_Q8_0) {         // vecdotq.cuh:153-165: d_w * d8 * sum q_w q_x per 32-block
         float acc = 0.0f;
 #pragma unroll

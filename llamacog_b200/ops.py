@@ -60,7 +60,7 @@ def lib():
 EXPORTS = ["b200_flash_attn_xq_supported", "b200_op_flash_attn_ext_xq", "b200_flash_attn_xb_supported", "b200_op_flash_attn_ext_xb", "b200_mul_mat_id_q", "b200_mul_mat_id_q_scratch_bytes", "b200_mul_mat_id_scratch_bytes", "b200_peer_bcast", "b200_peer_wait", "b200_peer_signal", "b200_mul_mat_vec_q_ex", "b200_mul_mat_vec_q", "b200_mul_mat_vec_q_group", "b200_mmvq_supported_type", "b200_quantize_q8_1",
            "b200_dequantize_rows", "b200_kernel_launch_count", "b200_kernel_launch_add", "b200_quantize_acts", "b200_quantized_acts_bytes",
            "b200_op_binary", "b200_op_unary", "b200_op_scale", "b200_op_rms_norm", "b200_op_rope", "b200_op_cpy", "b200_op_cpy_indirect", "b200_op_cpy_supported",
-           "b200_op_get_rows", "b200_op_soft_max", "b200_op_argsort", "b200_op_sum_rows", "b200_op_flash_attn_ext",
+           "b200_op_get_rows", "b200_op_soft_max", "b200_op_argsort", "b200_op_sum_rows", "b200_op_moe_combine", "b200_op_soft_max_argsort", "b200_op_flash_attn_ext",
            "b200_flash_attn_scratch_bytes", "b200_flash_attn_supported", "b200_op_mul_mat", "b200_mul_mat_scratch_bytes",
            "b200_mul_mat_supported", "b200_op_mul_mat_id", "b200_mul_mat_q", "b200_mul_mat_q_scratch_bytes",
            "b200_mul_mat_q_supported", "b200_mmq_debug_trace", "b200_acts_bf16_bytes",

@@ -117,7 +117,7 @@ def _gemv_args(ops, t, W, N, K, dst, **kw):
                         ny=1, nz=1, pdl=-1, **kw)
 
 
-@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0"])
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K"])
 @pytest.mark.parametrize("N,K", [(4096, 4096), (1024, 2048), (300, 1024), (128256, 4096)])
 def test_gemv_norm_prologue_matches_separate_launches(tname, N, K):
     """RMS_NORM + MUL + quantisation done by the batch-1 GEMV itself (b200_mmvq_args.norm_*): the normalised row, the
@@ -148,7 +148,7 @@ def test_gemv_norm_prologue_matches_separate_launches(tname, N, K):
     assert torch.equal(d, d_ref)
 
 
-@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0"])
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K"])
 @pytest.mark.parametrize("N,K", [(4096, 4096), (4096, 14336), (37, 2048), (5000, 4096)])
 def test_gemv_residual_epilogue(tname, N, K):
     """ADD fused into the GEMV's store (b200_mmvq_args.fuse_resid / fuse_sum): dst as without it, fuse_sum = dst + resid exactly
@@ -178,11 +178,12 @@ def test_gemv_residual_epilogue(tname, N, K):
     assert torch.equal(d2, d_ref + r)
 
 
-@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0"])
-@pytest.mark.parametrize("N,K,inplace", [(14336, 4096, False), (14336, 4096, True), (28672, 4096, False), (2048, 2048, True), (96, 1024, False), (8192, 2048, False)])
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K"])
+@pytest.mark.parametrize("N,K,inplace", [(14336, 4096, False), (14336, 4096, True), (28672, 4096, False), (2048, 2048, True), (96, 1024, False), (8192, 2048, False),
+                                          (28672, 8192, True), (11008, 4096, False), (9472, 2048, True)])      # Llama-3-70B, Llama-2-7B (344 blocks: uneven CTAs), 296 blocks
 def test_gemv_gate_up_silu_mul_epilogue(tname, N, K, inplace):
-    """silu(gate) * up and its q8 activations computed by the gate / up group launch itself (b200_mmvq_args.sm_*): the CTA that completes
-    a 32-row block of both results multiplies it out.  gate, up, act, out and the quantised column must equal, bit for bit, the group
+    """silu(gate) * up and its q8 activations computed by the gate / up group launch itself (b200_mmvq_args.sm_*, pair mode: every CTA
+    owns the same 32-row blocks of both matrices).  gate, up, act, out and the quantised column must equal, bit for bit, the group
     launch followed by b200_op_unary_mul -- also with act / out written in place over gate / up (the graph allocator's choice), with the
     norm prologue in the same launch, and on a second launch over the same counters (they must come back to zero)."""
     import numpy as np
@@ -247,7 +248,7 @@ class _GemvRope(C.Structure):
                 ("cell_type", C.c_int * 3), ("head_dim", C.c_int * 3), ("pos", C.c_void_p), ("ffac", C.c_void_p), ("prm", _RopeParams)]
 
 
-@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0"])
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K"])
 @pytest.mark.parametrize("hd,n_dims,pos,ext,use_ff,slot", [(128, 128, 77, 0.0, False, False), (128, 128, 4095, 0.0, True, True),
                                                            (64, 32, 5, 0.0, False, False), (128, 128, 300, 1.0, False, True)])
 def test_gemv_rope_epilogue_matches_rope_op(tname, hd, n_dims, pos, ext, use_ff, slot):

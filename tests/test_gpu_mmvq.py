@@ -171,8 +171,8 @@ def test_prequantised_path_matches_fused(name, N, K, M):
     d1, s1 = ops.mul_mat_vec_q(t, W, X, N, K, dbg=True, Xq=ops.quantize_acts(X))
     torch.cuda.synchronize()
     assert torch.equal(s0, s1)
-    if M == 1 and name in ("q4_K", "q6_K", "q8_0"):
-        # batch-1 K-quant GEMVs on pre-quantised activations run the register-resident kernel (mmvq_r.cuh): same
+    if M == 1 and name in ("q4_K", "q6_K", "q8_0", "q4_0", "q5_K"):
+        # batch-1 GEMVs of these formats on pre-quantised activations run the register-resident kernel (mmvq_r.cuh): same
         # integer sums, its own (fixed) fp32 summation order
         _close(d1.cpu().numpy(), d0.cpu().numpy().astype(np.float64))
     else:
@@ -183,7 +183,7 @@ RR_SHAPES = [(257, 4096), (130, 14336), (33, 8192), (7, 28672), (40, 1024), (64,
              (1500, 4096), (3, 2560)]
 
 
-@pytest.mark.parametrize("name", ["q4_K", "q6_K", "q8_0"])
+@pytest.mark.parametrize("name", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K"])
 @pytest.mark.parametrize("N,K", RR_SHAPES)
 def test_register_resident_kernel_vs_oracle(name, N, K):
     """mmvq_r.cuh (M = 1, pre-quantised activations; one thread per 128-weight half item with its activations in
@@ -210,7 +210,7 @@ def test_register_resident_kernel_vs_oracle(name, N, K):
     assert torch.equal(dst, dst2)          # parity-hook build == production build of the kernel
 
 
-@pytest.mark.parametrize("name", ["q4_K", "q6_K", "q8_0"])
+@pytest.mark.parametrize("name", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K"])
 @pytest.mark.parametrize("Ns,K", [((4096, 1024, 1024), 4096), ((1432, 1432), 4096), ((5, 300), 14336), ((1, 1, 1), 512)])
 def test_group_launch_matches_single(name, Ns, K):
     """q/k/v and gate/up share one launch (b200_mul_mat_vec_q_group): every matrix must come out bit-identical to its own

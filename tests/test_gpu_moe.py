@@ -86,3 +86,78 @@ def test_batched_equals_per_pair_rows(monkeypatch):
     a8 = a[::8]
     nmse = float(((a8.astype(np.float64) - b) ** 2).sum() / (b.astype(np.float64) ** 2).sum())
     assert nmse < 5e-4, nmse
+
+
+@pytest.mark.parametrize("n_expert,n_used,T,n_embd,inplace", [(8, 2, 1, 4096, False), (8, 2, 1, 4096, True), (8, 2, 3, 512, False), (16, 4, 2, 300, False),
+                                                              (32, 8, 1, 1000, True), (4, 3, 8, 64, False)])
+def test_moe_combine_matches_single_operators(n_expert, n_used, T, n_embd, inplace):
+    """b200_op_moe_combine (the tail of build_moe_ffn in one launch: GET_ROWS, SUM_ROWS, DIV, MUL, ADD x (n_used - 1)) must leave in
+    every tensor the bits of the single operators run one after the other -- also with DIV in place on the weights, MUL in place on
+    the experts and the ADDs on the running sum (what the graph allocator does)."""
+    import ctypes as C
+    from llamacog_b200 import ops
+    L = ops.lib()
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    torch.manual_seed(n_expert * 100 + n_used * 10 + T)
+    probs = torch.softmax(torch.randn(T, n_expert, device="cuda"), dim=-1).contiguous()
+    order = torch.argsort(probs, dim=-1, descending=True).to(torch.int32).contiguous()        # [T, n_expert]: top-k = a view of its first columns
+    ids = order[:, :n_used]
+    experts = torch.randn(T, n_used, n_embd, device="cuda")
+    B = lambda t: C.byref(ops.as_b200(t))
+    # the single operators, as the plugin runs them node by node
+    w_ref = torch.empty(T, n_used, 1, device="cuda")
+    assert L.b200_op_get_rows(B(probs.view(T, n_expert, 1)), B(ids), B(w_ref), st) == 0
+    s_ref = torch.empty(T, 1, device="cuda")
+    assert L.b200_op_sum_rows(B(w_ref.view(T, n_used)), B(s_ref), st) == 0
+    n_ref = torch.empty(T, n_used, device="cuda")
+    assert L.b200_op_binary(C.c_int(3), B(w_ref.view(T, n_used)), B(s_ref), B(n_ref), st) == 0
+    m_ref = torch.empty_like(experts)
+    assert L.b200_op_binary(C.c_int(2), B(experts), B(n_ref.view(T, n_used, 1)), B(m_ref), st) == 0
+    a_ref, acc = [], m_ref[:, 0, :]
+    for k in range(1, n_used):
+        o = torch.empty(T, n_embd, device="cuda")
+        assert L.b200_op_binary(C.c_int(0), B(acc), B(m_ref[:, k, :]), B(o), st) == 0
+        a_ref.append(o); acc = o
+    torch.cuda.synchronize()
+    # one launch
+    ex = experts.clone()
+    w = torch.empty(T, n_used, device="cuda"); s = torch.empty(T, device="cuda")
+    wn = w if inplace else torch.empty(T, n_used, device="cuda")
+    m = ex if inplace else torch.empty_like(ex)
+    adds = []
+    for k in range(1, n_used):
+        adds.append(adds[-1] if (inplace and adds) else torch.empty(T, n_embd, device="cuda"))
+    ap = (C.c_void_p * 7)(*([a.data_ptr() for a in adds] + [None] * (7 - len(adds))))
+    assert L.b200_op_moe_combine(B(probs.view(T, n_expert, 1)), B(ids), B(ex), C.c_void_p(w.data_ptr()), C.c_void_p(s.data_ptr()), C.c_void_p(wn.data_ptr()),
+                                 C.c_void_p(m.data_ptr()), ap, st) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(s, s_ref.view(T)) and torch.equal(wn, n_ref)
+    if not inplace:
+        assert torch.equal(w, w_ref.view(T, n_used)) and torch.equal(m, m_ref)
+        for a, r in zip(adds, a_ref):
+            assert torch.equal(a, r)
+    assert torch.equal(adds[-1], a_ref[-1])
+
+
+@pytest.mark.parametrize("n_expert,T", [(8, 1), (8, 5), (16, 2), (60, 3), (128, 1), (1000, 2)])
+def test_soft_max_argsort_matches_the_two_operators(n_expert, T):
+    """The router's SOFT_MAX + ARGSORT (ggml_top_k) in one launch: probabilities and order bit-identical to b200_op_soft_max followed by
+    b200_op_argsort, also with the probabilities written in place over the logits."""
+    import ctypes as C
+    from llamacog_b200 import ops
+    L = ops.lib()
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    torch.manual_seed(n_expert + T)
+    logits = torch.randn(T, n_expert, device="cuda") * 3
+    logits[0, : min(4, n_expert)] = 1.25                      # ties: the order of equal keys must match as well
+    B = lambda t: C.byref(ops.as_b200(t))
+    p_ref = torch.empty_like(logits); o_ref = torch.empty(T, n_expert, dtype=torch.int32, device="cuda")
+    assert L.b200_op_soft_max(B(logits), None, B(p_ref), C.c_float(1.0), C.c_float(0.0), st) == 0
+    assert L.b200_op_argsort(B(p_ref), B(o_ref), C.c_int(1), st) == 0
+    for inplace in (False, True):
+        x = logits.clone()
+        p = x if inplace else torch.empty_like(x)
+        o = torch.empty_like(o_ref)
+        assert L.b200_op_soft_max_argsort(B(x), B(p), B(o), C.c_float(1.0), C.c_int(1), st) == 0
+        torch.cuda.synchronize()
+        assert torch.equal(p, p_ref) and torch.equal(o, o_ref)

@@ -20,7 +20,7 @@ PLUGIN=$PWD/llamacog_b200/libggml-b200.so
 B=baseline/_ref/bin
 mkdir -p gpurun_out
 task=${1:-tests}; shift || true
-model() { python -c "import bench; print(bench.ensure_model('llama3-8b', '${MODEL_FTYPE:-q4_k_m}'))"; }      # MODEL_FTYPE=q8_0 ...: another quantisation of the 8B model
+model() { python -c "import bench; print(bench.ensure_model('${MODEL_PRESET:-llama3-8b}', '${MODEL_FTYPE:-q4_k_m}'))"; }      # MODEL_FTYPE=q8_0 / MODEL_PRESET=mixtral-8x7b ...: another quantisation / model
 case $task in
   tests)   python -m pytest tests -m gpu -x -q "$@" ;;
   bench)   python bench.py "$@" ;;
