@@ -104,6 +104,11 @@ typedef struct b200_mmvq_args {
      * sm_act == NULL: off.  sm_op: B200_UNARY_SILU only.  sm_act / sm_out may alias the gate / up results.
      * sm_counters: unused (the first version counted blocks across CTAs there; kept so that the struct layout stays). */
     int sm_op; float * sm_act; float * sm_out; void * sm_xq; unsigned * sm_counters;
+    /* the same for the chosen experts of ONE token of a MoE layer (b200_mul_mat_vec_q_ex with ids, ny = n_used <= 3; reference
+     * ggml-cuda.cu:2007-2148 mul_mat_id x 2 + unary.cu + binbcast.cu): W = the gate stack, sm_up_W = the up stack (same geometry),
+     * dst / sm_up_dst = the gate / up results [N, ny] (slot stride d_sy), sm_act / sm_out likewise, sm_xq = ny q8 columns of N / 256
+     * items (N % 256 == 0).  One launch instead of three. */
+    const void * sm_up_W; float * sm_up_dst;
 } b200_mmvq_args;
 
 /* 1 when b200_mul_mat_vec_q_ex (ng = 1, W/N NULL) or b200_mul_mat_vec_q_group would run these arguments on the

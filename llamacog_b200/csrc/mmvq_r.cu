@@ -48,8 +48,8 @@ static bool fuse_ok(const b200_mmvq_args * a, int ng) {
         if (!al16(a->norm_x) || !al16(a->norm_w) || !al16(a->norm_y) || !al16(a->norm_out)) return false;
     }
     if (a->sm_act) {      // silu(gate) * up in the epilogue of a gate / up launch
-        if (ng != 2 || a->sm_op != B200_UNARY_SILU || !a->sm_out || a->fuse_resid || a->rope || a->dbg_sumi || a->ids ||
-            a->hs_wait || a->hs_counter) return false;
+        if (a->sm_op != B200_UNARY_SILU || !a->sm_out || a->fuse_resid || a->rope || a->dbg_sumi || a->hs_wait || a->hs_counter) return false;
+        if (a->ids ? (ng != 1 || !a->sm_up_W || !a->sm_up_dst || ((uintptr_t)a->sm_up_W & 15) || a->norm_x) : ng != 2) return false;
         if (!al16(a->sm_act) || !al16(a->sm_out) || !al16(a->sm_xq)) return false;
     }
     return true;
@@ -63,6 +63,7 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     // the base of the expert stack after its PDL wait (mmvq_r.cuh)
     const void * Wid[3]; float * Did[3]; int Nid[3];
     const bool by_id = a->ids != nullptr;
+    if (by_id && a->sm_act && !fuse_ok(a, ng)) return MMVQR_SKIP;        // (asked with ng = 1 here: the slots become groups below)
     if (by_id) {
         const int ny = std::max(1, a->ny);
         if (ng != 1 || ny > 3 || std::max(1, a->nz) != 1 || !a->Xq || a->fuse_resid || a->fuse_sum || a->norm_x || a->rope || a->dbg_sumi ||
@@ -75,7 +76,7 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
                      max_stages = std::max(1, std::min(8, env_i("B200_MMVQR_NS", 8))), eU = env_i("B200_MMVQR_U", 0),
                      ramp = env_i("B200_MMVQR_RAMP", 0),          // short first stages: measured slower (per-stage hand-over cost), kept for tuning runs
                      small_mb = env_i("B200_MMVQR_SMALL_MB", 0), stagger = env_i("B200_MMVQR_STAGGER", 0);
-    if (!fuse_ok(a, ng)) return MMVQR_SKIP;
+    if (!(by_id && a->sm_act) && !fuse_ok(a, ng)) return MMVQR_SKIP;
     if (!on || a->M != 1 || (!a->Xq && !a->norm_x) || (!by_id && std::max(1, a->ny) != 1) || std::max(1, a->nz) != 1) return MMVQR_SKIP;
     static const int more_on = env_i("B200_MMVQR_MORE", 1);      // Q8_0 / Q4_0 / Q5_K (round 2); 0: only Q4_K and Q6_K take this kernel
     if (a->type != T_Q4_K && a->type != T_Q6_K && !((a->type == T_Q8_0 || a->type == T_Q4_0 || a->type == T_Q5_K) && more_on)) return MMVQR_SKIP;
@@ -92,7 +93,7 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     int ntot = 0;
     const bool pair = a->sm_act != nullptr;                           // gate / up pair mode: every CTA owns whole 32-row blocks of both matrices
     const int unit = pair ? 32 : a->rope ? 2 : 1;                     // rope epilogue: rows are dealt to the CTAs in pairs
-    if (a->sm_act && (N[0] != N[1] || N[0] % 32)) return MMVQR_SKIP;
+    if (a->sm_act && ((!by_id && N[0] != N[1]) || N[0] % 32 || (by_id && a->sm_xq && N[0] % 256))) return MMVQR_SKIP;
     for (int g = 0; g < ng; ++g) {
         if (((uintptr_t)W[g] & 15) || N[g] <= 0 || N[g] % unit) return MMVQR_SKIP;
         if (a->rope && (a->rope->mode[g] == 1 || a->rope->mode[g] == 2) && N[g] % a->rope->head_dim[g]) return MMVQR_SKIP;
@@ -105,15 +106,23 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     const int gx_max = std::max(ng, std::min(sm_count() * cps_eff, (ntot + rpp - 1) / rpp));
 
     mmvqr_params p = {};
-    p.ngroup = pair ? 1 : ng;
+    p.ngroup = pair && !by_id ? 1 : ng;
     int used = 0, rows_per_cta = 1;
     if (pair) {
         // the same number of blocks for every CTA where possible: CTAs share HBM evenly, so the launch ends with its largest CTA
-        // (448 blocks of a 14336-row pair: 224 CTAs of two blocks, not 152 of two and 144 of one)
-        const int units = N[0] / 32, cap = std::max(1, sm_count() * cps_eff), per = (units + cap - 1) / cap, share = (units + per - 1) / per;
-        p.cta0[0] = 0; used = share;
-        for (int g = 0; g < 2; ++g) { p.Wg[g] = (const uint8_t *)W[g]; p.Dg[g] = probe ? nullptr : dst[g]; }
-        p.rows_qg[0] = units / share; p.rows_remg[0] = units % share;
+        // (448 blocks of a 14336-row pair: 224 CTAs of two blocks, not 152 of two and 144 of one).  MoE: one such group per slot.
+        const int ngr = by_id ? ng : 1;
+        const int units = N[0] / 32, cap = std::max(1, sm_count() * cps_eff / ngr), per = (units + cap - 1) / cap, share = (units + per - 1) / per;
+        for (int g = 0; g < ngr; ++g) {
+            p.cta0[g] = used; used += share;
+            p.rows_qg[g] = units / share; p.rows_remg[g] = units % share;
+        }
+        if (by_id) {
+            for (int g = 0; g < ngr; ++g) { p.Wg[g] = (const uint8_t *)W[g]; p.Dg[g] = probe ? nullptr : dst[g]; p.Du[g] = probe ? nullptr : a->sm_up_dst + (int64_t)g * a->d_sy; }
+            p.Wup = (const uint8_t *)a->sm_up_W; p.sm_slot = a->d_sy; p.sm_xq_col = (int64_t)(N[0] / 256) * ACT_ITEM;
+        } else {
+            for (int g = 0; g < 2; ++g) { p.Wg[g] = (const uint8_t *)W[g]; p.Dg[g] = probe ? nullptr : dst[g]; }
+        }
         rows_per_cta = 32 * ((units + share - 1) / share);
     } else
     for (int g = 0; g < ng; ++g) {
@@ -166,7 +175,7 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     p.r0 = q0; p.r1 = q1; p.r2 = q2; p.stagger = stagger;
     p.dbg_sumi = a->dbg_sumi;
     if (a->sm_act) {
-        if (!al16(dst[0]) || !al16(dst[1])) return MMVQR_SKIP;
+        if (!al16(dst[0]) || (by_id ? (!al16(a->sm_up_dst) || (a->d_sy & 3)) : !al16(dst[1]))) return MMVQR_SKIP;
         p.sm_act = a->sm_act; p.sm_out = a->sm_out; p.sm_xq = (uint8_t *)a->sm_xq;
         p.rope_rows = rows_per_cta;                       // ... and its products behind them (the rope slot of the tail: never both)
     }

@@ -68,6 +68,10 @@ struct mmvqr_params {
     // No cross-CTA traffic.  (The first version dealt gate and up rows to different CTAs and counted 32-row blocks with atomics:
     // two fences, an atomic and a dependent load on the tail of every CTA cost what the removed launch had cost.)
     float * sm_act; float * sm_out; uint8_t * sm_xq;
+    // pair mode over the chosen experts of a MoE layer (ids != nullptr): group g = slot g; Wg[g] is the gate stack and Wup the up stack
+    // (the expert offset ids[g] * w_expert goes on both), Dg[g] / Du[g] the gate / up results of the slot, sm_act / sm_out advance by
+    // sm_slot floats and the q8 column by sm_xq_col bytes per slot
+    const uint8_t * Wup; float * Du[3]; int64_t sm_slot, sm_xq_col;
 };
 
 struct hacts { int q[4][8]; float d8[4], dsq[4]; int m32a[4], m32b[4]; };
@@ -242,6 +246,11 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
     cta -= p.cta0[g];
     const uint8_t * Wc = p.Wg[g];
     float * Dc = p.Dg[g];
+    const bool pair_ids = p.sm_act != nullptr && p.ids != nullptr;
+    const uint8_t * Wc1 = pair_ids ? p.Wup : p.Wg[1];                         // pair mode: the second matrix of this CTA
+    float * Dc1 = pair_ids ? p.Du[g] : p.Dg[1];
+    float * act_o = p.sm_act ? p.sm_act + (pair_ids ? g * p.sm_slot : 0) : nullptr, * out_o = p.sm_out ? p.sm_out + (pair_ids ? g * p.sm_slot : 0) : nullptr;
+    uint8_t * xq_o = p.sm_xq ? p.sm_xq + (pair_ids ? g * p.sm_xq_col : 0) : nullptr;
     const bool pair = p.sm_act != nullptr;     // gate / up pair mode: this CTA's rows of matrix 0, then the same rows of matrix 1
     const int unit = pair ? 32 : p.rope_on ? 2 : 1;        // rope: rows are dealt in pairs, pair mode: in 32-row blocks (rows_qg / rows_remg count units)
     const int row_lo = unit * (cta * p.rows_qg[g] + min(cta, p.rows_remg[g]));
@@ -273,7 +282,7 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
             const int r0 = row_lo + srow(s), nr = snr(s);
             const uint32_t bytes = (uint32_t)nr * p.rb, bar = full0 + 8 * slot;
             mbar_expect_tx(bar, bytes);
-            bulk_g2s_stream(smem_u32(stages + (size_t)slot * p.stage_bytes), (m ? p.Wg[1] : Wc) + (int64_t)r0 * p.rb, bytes, bar, pol);
+            bulk_g2s_stream(smem_u32(stages + (size_t)slot * p.stage_bytes), (m ? Wc1 : Wc) + (int64_t)r0 * p.rb, bytes, bar, pol);
         };
         // NORM kernels follow another mat-vec directly (no early residency), so their row must not queue behind the whole
         // weight prefetch in the SM's copy engine: norm weights and the first stage before the wait, the row right after
@@ -299,7 +308,7 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
         }
         pdl_wait();           // the activations come from the previous kernel; dst may still be read by it
         if (lane == 0) hs_wait_acts(p.hs);      // row split, peer side: the main device's broadcast has landed
-        if (p.ids) Wc += (int64_t)p.ids[g] * p.w_expert;      // the expert the router chose for slot g (known only now)
+        if (p.ids) { Wc += (int64_t)p.ids[g] * p.w_expert; Wc1 += (int64_t)p.ids[g] * p.w_expert; }      // the expert the router chose for slot g (known only now)
         if (lane == 0) {      // one coalesced copy of the column; the consumers pick their registers out of shared memory
             const uint32_t ab = NORM ? (uint32_t)p.K * 4 : (uint32_t)p.BPR * ACT_ITEM;
             mbar_expect_tx(actbar, ab);
@@ -323,11 +332,11 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
                     float sum = 0.0f;
                     for (int wv = 0; wv < NW; ++wv) sum += ps[o * NW + wv];
                     const int n = r0 + o, l = n - row_lo;
-                    if (mtx == 0) { p.Dg[0][n] = sum; rsd[l] = sum; }
+                    if (mtx == 0) { Dc[n] = sum; rsd[l] = sum; }
                     else {
                         const float av = silu_fn(rsd[l]), y = av * sum;
-                        p.Dg[1][n] = sum;              // act / out may sit on the gate / up results: these stores come last, act before out
-                        p.sm_act[n] = av; p.sm_out[n] = y;
+                        Dc1[n] = sum;                  // act / out may sit on the gate / up results: these stores come last, act before out
+                        act_o[n] = av; out_o[n] = y;
                         csn[l] = y;
                     }
                 }
@@ -370,7 +379,7 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
             if (sv == 0) ktrace_event(2);       // first stage consumed and stored
         }
         ktrace_event(3);                       // all rows of CTA 0 stored
-        if (pair && p.sm_xq) {
+        if (pair && xq_o) {
             // the q8 activations of this CTA's 32-row blocks, four blocks per pass (an 8-lane group each)
             __syncwarp();
             for (int b0 = 0; 32 * b0 < nrows; b0 += 4) {
@@ -378,7 +387,7 @@ __global__ void __launch_bounds__(288, 2) mmvqr_kernel(const mmvqr_params p) {
                 const bool in = 32 * bl < nrows;
                 float4 y = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                 if (in) { const float * yp = csn + 32 * bl + 4 * (lane & 7); y = make_float4(yp[0], yp[1], yp[2], yp[3]); }
-                quant_block_store(y, in ? (row_lo >> 5) + bl : 0, lane & 7, in, p.sm_xq);
+                quant_block_store(y, in ? (row_lo >> 5) + bl : 0, lane & 7, in, xq_o);
             }
         }
         if (p.hs.counter) {                    // row split: the last CTA of the launch lowers / raises / awaits the hand-over flags

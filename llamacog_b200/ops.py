@@ -30,7 +30,8 @@ class MmvqArgs(C.Structure):
                 ("hs_wait", C.c_void_p), ("hs_clear", C.c_void_p), ("hs_signal", C.c_void_p), ("hs_join", C.c_void_p),
                 ("hs_join_stride", C.c_int), ("hs_join_mask", C.c_uint32), ("hs_counter", C.c_void_p), ("hs_timeout_ms", C.c_uint),
                 ("hs_error", C.c_void_p),
-                ("sm_op", C.c_int), ("sm_act", C.c_void_p), ("sm_out", C.c_void_p), ("sm_xq", C.c_void_p), ("sm_counters", C.c_void_p)]
+                ("sm_op", C.c_int), ("sm_act", C.c_void_p), ("sm_out", C.c_void_p), ("sm_xq", C.c_void_p), ("sm_counters", C.c_void_p),
+                ("sm_up_W", C.c_void_p), ("sm_up_dst", C.c_void_p)]
 
 
 _lib = None

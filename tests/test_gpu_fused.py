@@ -221,6 +221,51 @@ def test_gemv_gate_up_silu_mul_epilogue(tname, N, K, inplace):
         assert int(cnt.abs().sum().item()) == 0
 
 
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0"])
+@pytest.mark.parametrize("N,K,n_expert,n_used,inplace", [(14336, 4096, 8, 2, False), (14336, 4096, 8, 2, True), (512, 1024, 4, 3, False), (2048, 2048, 4, 1, True)])
+def test_moe_gate_up_pair_launch(tname, N, K, n_expert, n_used, inplace):
+    """The gate and up expert mat-vecs of one token, silu(gate) * up and its q8 activations in ONE launch (b200_mmvq_args.sm_up_*, pair
+    mode over the chosen experts): every tensor equals, bit for bit, what the per-expert launches followed by b200_op_unary_mul leave."""
+    import numpy as np
+    import oracle as O
+    ops = _ops(); L = ops.lib()
+    t = O.QUANT_TYPES[tname]
+    rng = np.random.default_rng(N + K + n_used)
+    rb = ops.row_bytes(t, K)
+    Wg = torch.from_numpy(O.random_quant_bytes(t, N * n_expert, K, rng).reshape(-1)).cuda()
+    Wu = torch.from_numpy(O.random_quant_bytes(t, N * n_expert, K, rng).reshape(-1)).cuda()
+    torch.manual_seed(N + K)
+    x = torch.randn(1, K, device="cuda")
+    xq = ops.quantize_acts(x)
+    ids = torch.from_numpy(rng.choice(n_expert, n_used, replace=False).astype(np.int32)).cuda()
+    g_ref = torch.empty(n_used, N, device="cuda"); u_ref = torch.empty(n_used, N, device="cuda")
+    for y in range(n_used):
+        e = int(ids[y].item())
+        g_ref[y] = ops.mul_mat_vec_q(t, Wg[e * N * rb:(e + 1) * N * rb], x, N, K, Xq=xq)[0]
+        u_ref[y] = ops.mul_mat_vec_q(t, Wu[e * N * rb:(e + 1) * N * rb], x, N, K, Xq=xq)[0]
+    a_ref = torch.empty_like(g_ref); o_ref = torch.empty_like(g_ref)
+    q_ref = torch.zeros((n_used, (N + 255) // 256 * 400), dtype=torch.uint8, device="cuda")
+    assert L.b200_op_unary_mul(C.c_int(10), C.byref(ops.as_b200(g_ref)), C.byref(ops.as_b200(a_ref)), C.byref(ops.as_b200(u_ref)), C.byref(ops.as_b200(o_ref)),
+                               C.c_void_p(q_ref.data_ptr()), C.c_int(0), _st(ops)) == 0
+    for rep in range(2):
+        g = torch.empty(n_used, N, device="cuda"); u = torch.empty(n_used, N, device="cuda")
+        act = g if inplace else torch.empty_like(g)
+        out = u if inplace else torch.empty_like(g)
+        q = torch.zeros_like(q_ref)
+        a = _gemv_args(ops, t, Wg, N, K, g, Xq=xq.data_ptr(), sm_op=10, sm_act=act.data_ptr(), sm_out=out.data_ptr(), sm_xq=q.data_ptr() if N % 256 == 0 else None,
+                       sm_up_W=Wu.data_ptr(), sm_up_dst=u.data_ptr(), ids=ids.data_ptr(), ids_sz=n_used, w_sy=N * rb, d_sy=N, x_mod_y=1)
+        a.ny = n_used
+        if not L.b200_mmvq_fusable(C.byref(a), C.c_int(0), None, None):
+            pytest.skip("shape not taken by the register-resident kernel")
+        assert L.b200_mul_mat_vec_q_ex(C.byref(a), _st(ops)) == 0
+        torch.cuda.synchronize()
+        if not inplace:
+            assert torch.equal(g, g_ref) and torch.equal(u, u_ref)
+        assert torch.equal(act, a_ref) and torch.equal(out, o_ref)
+        if N % 256 == 0:
+            assert _same_acts(q, q_ref)
+
+
 def test_gemv_fusion_refused_when_not_eligible():
     """M = 2 does not run on the register-resident kernel: the fusable predicate says no and a call with fused fields fails
     loudly (-4) instead of silently dropping the fused work."""

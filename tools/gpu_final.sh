@@ -12,5 +12,10 @@ bash tools/gpu_run.sh launches pp > gpurun_out/${R}_launches_pp.txt 2>&1; head -
 bash tools/gpu_run.sh tbo > gpurun_out/${R}_tbo_summary.txt 2>&1; tail -n 6 gpurun_out/${R}_tbo_summary.txt
 bash tools/gpu_run.sh config3 > gpurun_out/${R}_config3_q8_0.log 2>&1; cat gpurun_out/${R}_config3_q8_0.log
 bash tools/gpu_run.sh moe > gpurun_out/${R}_mixtral.log 2>&1; cat gpurun_out/${R}_mixtral.log
+MODEL_PRESET=mixtral-8x7b bash tools/gpu_run.sh launches tg > gpurun_out/${R}_launches_tg_mixtral_final.txt 2>&1; head -n 8 gpurun_out/${R}_launches_tg_mixtral_final.txt
+# one full ncu capture of the dominant launch as the plugin issues it (gate / up pair mode): DRAM traffic per launch
+bash tools/gpu_run.sh ncu mmvqr python tools/prof_mmvq.py pair4k; python tools/ncu_traffic.py gpurun_out/ncu_mmvqr.ncu-rep > gpurun_out/${R}_mmvqr_pair_traffic.json 2>&1; cat gpurun_out/${R}_mmvqr_pair_traffic.json
+if [ "${FULL:-0}" = 1 ]; then
 bash tools/gpu_run.sh cpu > gpurun_out/${R}_cpu_baseline.log 2>&1; cat gpurun_out/${R}_cpu_baseline.log
 bash tools/gpu_run.sh loadtime > gpurun_out/${R}_load_time_8b.log 2>&1; tail -n 4 gpurun_out/${R}_load_time_8b.log
+fi
