@@ -232,14 +232,20 @@ def kernel_roofline(steps, warmup, dev_index, grouped=True):
     for g in (issue_groups(plan) if grouped else [[e] for e in plan]):
         ws = weights[i:i + len(g)]
         i += len(g)
-        launches.append((g, ws, [torch.zeros(1, e[2], device=dev) for e in g]))
+        extra = None
+        if grouped and len(g) == 2 and g[0][0] == "gate":      # as issued: pair mode, SILU(gate) * up and its q8 activations in the same launch
+            N = g[0][2]
+            extra = (torch.zeros(1, N, device=dev), torch.zeros(1, N, device=dev), torch.zeros(N // 256 * 400, dtype=torch.uint8, device=dev))
+        launches.append((g, ws, [torch.zeros(1, e[2], device=dev) for e in g], extra))
 
     def run():
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        for g, ws, outs in launches:
+        for g, ws, outs, extra in launches:
             t, K, ng = g[0][1], g[0][3], len(g)
             a = ops.MmvqArgs(type=t, W=ws[0].data_ptr(), nb1=ops.row_bytes(t, K), X=X[K].data_ptr(), xs=K, dst=outs[0].data_ptr(),
                              ds=g[0][2], N=g[0][2], K=K, M=1, ny=1, nz=1, pdl=-1, dbg_sumi=None, Xq=xq[K].data_ptr())
+            if extra is not None:
+                a.sm_op, a.sm_act, a.sm_out, a.sm_xq = 10, extra[0].data_ptr(), extra[1].data_ptr(), extra[2].data_ptr()
             if ng == 1:
                 rc = L.b200_mul_mat_vec_q_ex(C.byref(a), st)
             else:
@@ -512,12 +518,20 @@ def main():
                 if os.path.exists(tpath):
                     traffic = json.load(open(tpath)).get("dram_bytes_per_launch_token_mix")
                 k1 = kernel_roofline(max(20, min(args.steps, 200)), args.warmup, local, grouped=False)
-                line["roofline"] = {"bound": "hbm", "kernel": "mmvqr_kernel<Q4_K> as the plugin issues it in the timed region (%d launches per token: q/k/v group, wo, gate/up group, down)" % k["launches"],
+                pair = None         # the gate / up pair launch itself under ncu --set full (tools/prof_mmvq.py pair4k, round 2)
+                ppath = os.path.join(ROOT, "profiles", "r02_mmvqr_pair_traffic.json")
+                if os.path.exists(ppath):
+                    pl = json.load(open(ppath)).get("launches", [])
+                    if pl:
+                        pair = {"dram_bytes_per_launch": int(sorted(x["dram_read_bytes"] + x["dram_write_bytes"] for x in pl)[len(pl) // 2]),
+                                "algorithmic_bytes": 2 * N_FF * N_EMBD * 144 // 256, "source": "profiles/r02_mmvqr_pair_traffic.json"}
+                line["roofline"] = {"bound": "hbm", "kernel": "mmvqr_kernel<Q4_K> as the plugin issues it in the timed region (%d launches per token: q/k/v group, wo, gate/up pair launch with SILU*up, down)" % k["launches"],
                                     "achieved": k["gbps"], "peak": peak, "unit": "GB/s", "frac": k["gbps"] / peak,
                                     "traffic": int(traffic * k1["launches"] / k["launches"]) if traffic else None,
                                     "peak_source": how, "launches": k["launches"], "us_per_launch": k["us_per_launch"],
                                     "algorithmic_bytes_per_launch": k["bytes"] / k["launches"],
                                     "traffic_note": "ncu --set full of the four Q4_K shapes as single-matrix launches (profiles/r01_mmvqr_q4k_traffic.json: DRAM bytes = 1.002 x algorithmic, weights are read once however the matrices are grouped), re-expressed per issued launch",
+                                    "traffic_gate_up_pair_launch": pair,
                                     "single_launches": {"note": "the same matrices, every one a launch of its own (the round-1 form of this figure; the step never issues wk / wv alone)",
                                                         "launches": k1["launches"], "us_per_launch": k1["us_per_launch"], "achieved": k1["gbps"], "frac": k1["gbps"] / peak,
                                                         "algorithmic_bytes_per_launch": k1["bytes"] / k1["launches"]},

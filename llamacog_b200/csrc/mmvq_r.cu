@@ -112,7 +112,11 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
         // the same number of blocks for every CTA where possible: CTAs share HBM evenly, so the launch ends with its largest CTA
         // (448 blocks of a 14336-row pair: 224 CTAs of two blocks, not 152 of two and 144 of one).  MoE: one such group per slot.
         const int ngr = by_id ? ng : 1;
-        const int units = N[0] / 32, cap = std::max(1, sm_count() * cps_eff / ngr), per = (units + cap - 1) / cap, share = (units + per - 1) / per;
+        // B200_PAIR_GEOM=1 (tuning): all the CTAs the SMs hold, the first ones a block more than the rest -- CTA i and CTA i + #SMs land
+        // on one SM, so the SMs (not the CTAs) come out even
+        static const int geom = env_i("B200_PAIR_GEOM", 0);
+        const int units = N[0] / 32, cap = std::max(1, sm_count() * cps_eff / ngr), per = (units + cap - 1) / cap,
+                  share = geom == 1 ? std::min(cap, units) : (units + per - 1) / per;
         for (int g = 0; g < ngr; ++g) {
             p.cta0[g] = used; used += share;
             p.rows_qg[g] = units / share; p.rows_remg[g] = units % share;

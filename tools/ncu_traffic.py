@@ -23,5 +23,5 @@ for r in rows[2:]:
     scale_w = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit_w, 1)
     res.append({"kernel": r[col["Kernel Name"]][:60], "grid": r[col["Grid Size"]] if "Grid Size" in col else None,
                 "dram_read_bytes": (f("dram__bytes_read.sum") or 0) * scale, "dram_write_bytes": (f("dram__bytes_write.sum") or 0) * scale_w,
-                "duration_ns_under_ncu": f("gpu__time_duration.sum")})
+                "duration_under_ncu (unit of the report, us)": f("gpu__time_duration.sum")})
 print(json.dumps({"source": sys.argv[1], "launches": res}, indent=1))
