@@ -112,9 +112,13 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
         // the same number of blocks for every CTA where possible: CTAs share HBM evenly, so the launch ends with its largest CTA
         // (448 blocks of a 14336-row pair: 224 CTAs of two blocks, not 152 of two and 144 of one).  MoE: one such group per slot.
         const int ngr = by_id ? ng : 1;
-        // B200_PAIR_GEOM=1 (tuning): all the CTAs the SMs hold, the first ones a block more than the rest -- CTA i and CTA i + #SMs land
-        // on one SM, so the SMs (not the CTAs) come out even
-        static const int geom = env_i("B200_PAIR_GEOM", 0);
+        // Two geometries, measured A/B on tg128 (profiles/r02_ab_pair_geometry.log).  0: every CTA the same number of blocks (448 blocks of
+        // an 8B gate/up pair: 224 CTAs of two) -- CTAs share HBM evenly, so a launch ends with its largest CTA; better for the dense pair
+        // (8B: 1.685 vs 1.717 ms per token).  1: all the CTAs the SMs hold, the first ones a block more than the rest (CTA i and CTA i + #SMs
+        // land on one SM: the SMs come out even) -- better for the MoE form, whose groups would otherwise leave a quarter of the CTA slots
+        // empty (Mixtral: 2.77 vs 2.81 ms per token).  B200_PAIR_GEOM=0/1 forces one.
+        static const int geom_env = env_i("B200_PAIR_GEOM", -1);
+        const int geom = geom_env >= 0 ? geom_env : (by_id ? 1 : 0);
         const int units = N[0] / 32, cap = std::max(1, sm_count() * cps_eff / ngr), per = (units + cap - 1) / cap,
                   share = geom == 1 ? std::min(cap, units) : (units + per - 1) / per;
         for (int g = 0; g < ngr; ++g) {
