@@ -33,6 +33,18 @@ template <int TYPE> __device__ __forceinline__ float dequant_elem(const uint8_t 
         const int q = nib | (((b[QH + (j >> 3)] >> (j & 7)) & 1) << 4);          // bit j of the little-endian qh word
         if constexpr (TYPE == T_Q5_0) return __fmul_rn((float)(q - 16), ldh(b));
         else return __fadd_rn(__fmul_rn((float)q, ldh(b)), ldh(b + 2));
+    } else if constexpr (TYPE == T_Q2_K) {         // ggml-quants.c:706-736
+        const uint8_t * b = row + (e >> 8) * 84; const int r = e & 255, n = r >> 7, j = (r >> 5) & 3, l = r & 31;
+        const uint8_t sc = b[8 * n + 2 * j + (l >> 4)];
+        const float dl = __fmul_rn(ldh(b + 80), (float)(sc & 0xF)), ml = __fmul_rn(ldh(b + 82), (float)(sc >> 4));
+        return __fsub_rn(__fmul_rn(dl, (float)((b[16 + 32 * n + l] >> (2 * j)) & 3)), ml);
+    } else if constexpr (TYPE == T_Q3_K) {         // ggml-quants.c:1050-1098
+        const uint8_t * b = row + (e >> 8) * 110; const int r = e & 255, n = r >> 7, j = (r >> 5) & 3, l = r & 31;
+        const int is = r >> 4, sb = is & 3, sg = is >> 2;
+        const int lo = sg < 2 ? (b[96 + 4 * sg + sb] & 0xF) : (b[96 + 4 * (sg - 2) + sb] >> 4);
+        const int sc = (lo | (((b[104 + sb] >> (2 * sg)) & 3) << 4)) - 32;
+        const int q = (int)((b[32 + 32 * n + l] >> (2 * j)) & 3) - ((b[l] & (1 << (4 * n + j))) ? 0 : 4);
+        return __fmul_rn(__fmul_rn(ldh(b + 108), (float)sc), (float)q);
     } else if constexpr (TYPE == T_Q8_0) {
         const uint8_t * b = row + (e >> 5) * 34;
         return __fmul_rn((float)(int8_t)b[2 + (e & 31)], ldh(b));

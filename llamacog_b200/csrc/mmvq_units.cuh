@@ -30,6 +30,8 @@ namespace b200 {
 template <int TYPE> struct item_traits;
 template <> struct item_traits<T_Q4_0> { static constexpr int BYTES = 144; };
 template <> struct item_traits<T_Q8_0> { static constexpr int BYTES = 272; };
+template <> struct item_traits<T_Q2_K> { static constexpr int BYTES = 84; };    // scales[16] | qs[64] | d | dmin
+template <> struct item_traits<T_Q3_K> { static constexpr int BYTES = 110; };   // hmask[32] | qs[64] | scales[12] | d
 template <> struct item_traits<T_Q4_1> { static constexpr int BYTES = 160; };   // 8 x {d, m, qs[16]}
 template <> struct item_traits<T_Q5_0> { static constexpr int BYTES = 176; };   // 8 x {d, qh[4], qs[16]}
 template <> struct item_traits<T_Q5_1> { static constexpr int BYTES = 192; };   // 8 x {d, m, qh[4], qs[16]}
@@ -203,6 +205,80 @@ __device__ __forceinline__ void item_dot(uint32_t wp, uint32_t ap, uint32_t acs,
                 }
             }
         }
+    } else if constexpr (TYPE == T_Q2_K) {
+        // vecdotq.cuh:218-243.  32-block 4n + j: bits 2j..2j+1 of qs[32n .. 32n+31], a 4-bit scale / 4-bit min pair per 16 elements
+        int sc[4], q[8], dmw[1];
+        lds_words_a2<4>(wp, sc);
+        lds_words_a2<1>(wp + 80, dmw);
+        const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&dmw[0]));
+        float accd[M], accm[M];
+#pragma unroll
+        for (int m = 0; m < M; ++m) { accd[m] = 0.0f; accm[m] = 0.0f; }
+#pragma unroll
+        for (int n = 0; n < 2; ++n) {
+            lds_words_a2<8>(wp + 16 + 32 * n, q);           // qs[32n .. 32n+31]: every byte serves the four j
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t scw = (uint32_t)sc[2 * n + (j >> 1)] >> (16 * (j & 1));       // bytes 8n + 2j, 8n + 2j + 1
+                const int sa = scw & 0xF, ma = (scw >> 4) & 0xF, sb = (scw >> 8) & 0xF, mb = (scw >> 12) & 0xF;
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    act_blk a; lds_act(ap + m * acs + (4 * n + j) * ACT_BLK, a);
+                    int s0 = 0, s1 = 0;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        s0 = dp4a_us(((uint32_t)q[k] >> (2 * j)) & 0x03030303u, a.q[k], s0);
+                        s1 = dp4a_us(((uint32_t)q[4 + k] >> (2 * j)) & 0x03030303u, a.q[4 + k], s1);
+                    }
+                    if constexpr (DBG) dbg[m * dms + 4 * n + j] = s0 + s1;
+                    accd[m] = fmaf(a.d8, i2f_small(s0 * sa + s1 * sb), accd[m]);
+                    accm[m] = fmaf(a.d8, i2f_small(-(a.m32a >> 5) * ma - (a.m32b >> 5) * mb), accm[m]);      // m32a = -32 * sum of the first 16 q8
+                }
+            }
+        }
+#pragma unroll
+        for (int m = 0; m < M; ++m) acc[m] += dm.x * accd[m] - dm.y * accm[m];
+    } else if constexpr (TYPE == T_Q3_K) {
+        // vecdotq.cuh:301-331.  code = 2 low bits | hmask bit << 2, minus 4 (folded: -4 * sum q8 = m32 >> 3); 6-bit scales minus 32
+        int hm[8], q[8], scw[3];
+        lds_words_a2<8>(wp, hm);
+        lds_words_a2<3>(wp + 96, scw);
+        const float d = half_bits_to_float(lds16(wp + 108));
+        float acc3[M];
+#pragma unroll
+        for (int m = 0; m < M; ++m) acc3[m] = 0.0f;
+#pragma unroll
+        for (int n = 0; n < 2; ++n) {
+            lds_words_a2<8>(wp + 32 + 32 * n, q);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                // scale indices 8n + 2j, 8n + 2j + 1: low nibble from scales[is % 8] (>> 4 for is >= 8), high pair from scales[8 + is % 4] >> 2 (is / 4)
+                int scv[2];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int is = 8 * n + 2 * j + h, b = is & 3, g = is >> 2;
+                    const uint32_t lo = ((uint32_t)scw[(g & 1)] >> (8 * b + (g >= 2 ? 4 : 0))) & 0xFu;
+                    const uint32_t hi = ((uint32_t)scw[2] >> (8 * b + 2 * g)) & 3u;
+                    scv[h] = (int)(lo | (hi << 4)) - 32;
+                }
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    act_blk a; lds_act(ap + m * acs + (4 * n + j) * ACT_BLK, a);
+                    int s0 = a.m32a >> 3, s1 = a.m32b >> 3;      // -4 * sum q8 of each half
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t v0 = (((uint32_t)q[k] >> (2 * j)) & 0x03030303u) | ((((uint32_t)hm[k] >> (4 * n + j)) & 0x01010101u) << 2);
+                        const uint32_t v1 = (((uint32_t)q[4 + k] >> (2 * j)) & 0x03030303u) | ((((uint32_t)hm[4 + k] >> (4 * n + j)) & 0x01010101u) << 2);
+                        s0 = dp4a_us(v0, a.q[k], s0);
+                        s1 = dp4a_us(v1, a.q[4 + k], s1);
+                    }
+                    if constexpr (DBG) dbg[m * dms + 4 * n + j] = s0 + s1;
+                    acc3[m] = fmaf(a.d8, i2f_small(s0 * scv[0] + s1 * scv[1]), acc3[m]);
+                }
+            }
+        }
+#pragma unroll
+        for (int m = 0; m < M; ++m) acc[m] = fmaf(d, acc3[m], acc[m]);
     } else if constexpr (TYPE == T_Q4_K || TYPE == T_Q5_K) {
         constexpr int QS0 = (TYPE == T_Q4_K) ? 16 : 48;
         int hd[4];

@@ -29,7 +29,7 @@
 #define QK_K 256  /* elements per K-quant super-block          (ggml-common.h:89) */
 
 /* ---- ggml type ids (ggml/include/ggml.h:352-366) ---- */
-enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q8_1 = 9, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
+enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q8_1 = 9, T_Q2_K = 10, T_Q3_K = 11, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
 
 /* ---- block layouts (ggml-common.h:167-172, 177-207 (q4_1 q5_0 q5_1), 209-214, 216-227, 285-296, 302-314, 320-326) ---- */
 #pragma pack(push, 1)
@@ -39,6 +39,8 @@ typedef struct { uint16_t d; uint8_t qh[4]; uint8_t qs[16]; } blk_q5_0;         
 typedef struct { uint16_t d; uint16_t m; uint8_t qh[4]; uint8_t qs[16]; } blk_q5_1;       /* 24 B */
 typedef struct { uint16_t d; int8_t qs[32]; } blk_q8_0;                                   /* 34 B */
 typedef struct { uint16_t d; uint16_t s; int8_t qs[32]; } blk_q8_1;                       /* 36 B */
+typedef struct { uint8_t scales[16]; uint8_t qs[64]; uint16_t d; uint16_t dmin; } blk_q2_K;                 /* 84 B  (ggml-common.h:250-267) */
+typedef struct { uint8_t hmask[32]; uint8_t qs[64]; uint8_t scales[12]; uint16_t d; } blk_q3_K;            /* 110 B (ggml-common.h:273-279) */
 typedef struct { uint16_t d; uint16_t dmin; uint8_t scales[12]; uint8_t qs[128]; } blk_q4_K;              /* 144 B */
 typedef struct { uint16_t d; uint16_t dmin; uint8_t scales[12]; uint8_t qh[32]; uint8_t qs[128]; } blk_q5_K; /* 176 B */
 typedef struct { uint8_t ql[128]; uint8_t qh[64]; int8_t scales[16]; uint16_t d; } blk_q6_K;              /* 210 B */
@@ -48,7 +50,7 @@ int64_t oracle_block_bytes(int type) {
     switch (type) {
         case T_Q4_0: return 18; case T_Q8_0: return 34; case T_Q8_1: return 36;
         case T_Q4_1: return 20; case T_Q5_0: return 22; case T_Q5_1: return 24;
-        case T_Q4_K: return 144; case T_Q5_K: return 176; case T_Q6_K: return 210;
+        case T_Q4_K: return 144; case T_Q5_K: return 176; case T_Q6_K: return 210; case T_Q2_K: return 84; case T_Q3_K: return 110;
         case T_F32: return 4; case T_F16: return 2;
     }
     return 0;
@@ -56,7 +58,7 @@ int64_t oracle_block_bytes(int type) {
 int64_t oracle_block_elems(int type) {
     switch (type) {
         case T_Q4_0: case T_Q8_0: case T_Q8_1: case T_Q4_1: case T_Q5_0: case T_Q5_1: return 32;
-        case T_Q4_K: case T_Q5_K: case T_Q6_K: return 256;
+        case T_Q4_K: case T_Q5_K: case T_Q6_K: case T_Q2_K: case T_Q3_K: return 256;
         case T_F32: case T_F16: return 1;
     }
     return 0;
@@ -198,6 +200,41 @@ static void deq_q6_K(const blk_q6_K *x, float *y, int64_t k) {
     }
 }
 
+/* q2_K (ggml-quants.c:706-736): element e = 128 n + 32 j + l uses bits 2j..2j+1 of qs[32 n + l] and the 4-bit scale / 4-bit min pair
+ * scales[8 n + 2 j + l / 16]:  y = (d * sc) * q - (dmin * mn), every product and the difference rounded on its own. */
+static void deq_q2_K(const blk_q2_K *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK_K; i++) {
+        const float d = oracle_fp16_to_fp32(x[i].d), mn = oracle_fp16_to_fp32(x[i].dmin);
+        for (int e = 0; e < QK_K; e++) {
+            const int n = e >> 7, j = (e >> 5) & 3, l = e & 31;
+            const uint8_t sc = x[i].scales[8 * n + 2 * j + (l >> 4)];
+            const float dl = d * (float)(sc & 0xF), ml = mn * (float)(sc >> 4);
+            y[i * QK_K + e] = dl * (float)((x[i].qs[32 * n + l] >> (2 * j)) & 3) - ml;
+        }
+    }
+}
+/* q3_K (ggml-quants.c:1050-1098): 6-bit scales (low nibbles in scales[0..7], high pairs in scales[8..11]) minus 32; code = 2 low bits of
+ * qs minus 4 unless bit (4 n + j) of hmask[l] is set, -4..3;  y = (d * (sc - 32)) * code. */
+static int q3_scale(const uint8_t *sc, int is) {
+    const int b = is & 3, g = is >> 2;
+    const int lo = g < 2 ? (sc[4 * g + b] & 0xF) : (sc[4 * (g - 2) + b] >> 4);
+    const int hi = (sc[8 + b] >> (2 * g)) & 3;
+    return (lo | (hi << 4)) - 32;
+}
+static int q3_code(const blk_q3_K *b, int e) {
+    const int n = e >> 7, j = (e >> 5) & 3, l = e & 31;
+    return (int)((b->qs[32 * n + l] >> (2 * j)) & 3) - ((b->hmask[l] & (1 << (4 * n + j))) ? 0 : 4);
+}
+static void deq_q3_K(const blk_q3_K *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK_K; i++) {
+        const float d = oracle_fp16_to_fp32(x[i].d);
+        for (int e = 0; e < QK_K; e++) {
+            const float dl = d * (float)q3_scale(x[i].scales, e >> 4);
+            y[i * QK_K + e] = dl * (float)q3_code(&x[i], e);
+        }
+    }
+}
+
 int oracle_dequantize_row(int type, const void *x, float *y, int64_t k) {
     switch (type) {
         case T_Q4_0: deq_q4_0((const blk_q4_0 *)x, y, k); return 0;
@@ -208,6 +245,8 @@ int oracle_dequantize_row(int type, const void *x, float *y, int64_t k) {
         case T_Q4_K: deq_q4_K((const blk_q4_K *)x, y, k); return 0;
         case T_Q5_K: deq_q5_K((const blk_q5_K *)x, y, k); return 0;
         case T_Q6_K: deq_q6_K((const blk_q6_K *)x, y, k); return 0;
+        case T_Q2_K: deq_q2_K((const blk_q2_K *)x, y, k); return 0;
+        case T_Q3_K: deq_q3_K((const blk_q3_K *)x, y, k); return 0;
         case T_F32: memcpy(y, x, (size_t)k * 4); return 0;
         case T_F16: for (int64_t i = 0; i < k; i++) y[i] = oracle_fp16_to_fp32(((const uint16_t *)x)[i]); return 0;
     }
@@ -311,6 +350,13 @@ static void int_codes(int type, const void *row, int64_t k, int *w) {
     } else if (type == T_Q6_K) {
         const blk_q6_K *b = (const blk_q6_K *)row;
         for (int64_t i = 0; i < k / QK_K; i++) for (int e = 0; e < QK_K; e++) w[i * QK_K + e] = q6_val(&b[i], e);
+    } else if (type == T_Q2_K) {      /* 0..3 (vecdotq.cuh:218-243) */
+        const blk_q2_K *b = (const blk_q2_K *)row;
+        for (int64_t i = 0; i < k / QK_K; i++) for (int e = 0; e < QK_K; e++)
+            w[i * QK_K + e] = (b[i].qs[32 * (e >> 7) + (e & 31)] >> (2 * ((e >> 5) & 3))) & 3;
+    } else if (type == T_Q3_K) {      /* -4..3 after __vsubss4 (vecdotq.cuh:301-331) */
+        const blk_q3_K *b = (const blk_q3_K *)row;
+        for (int64_t i = 0; i < k / QK_K; i++) for (int e = 0; e < QK_K; e++) w[i * QK_K + e] = q3_code(&b[i], e);
     }
 }
 
@@ -371,6 +417,22 @@ int oracle_mul_mat_vec_q(int type, const void *W, int64_t row_stride_bytes, cons
                     const double d = oracle_fp16_to_fp32(((const uint16_t *)blk)[0]), dm = oracle_fp16_to_fp32(((const uint16_t *)blk)[1]);
                     int sc, mn; scale_min_k4((int)(b % 8), blk + 4, &sc, &mn);
                     acc += d * d8 * ((double)si[b] * sc) - dm * d8 * ((double)sq[b] * mn);
+                } else if (type == T_Q2_K || type == T_Q3_K) {
+                    /* two 16-element scale groups per 32 sub-block, as q6_K */
+                    for (int g = 0; g < 2; g++) {
+                        int32_t sw = 0, sx = 0;
+                        const int e0 = (int)(b % 8) * 32 + g * 16;
+                        if (type == T_Q2_K) {
+                            const blk_q2_K *blk = (const blk_q2_K *)row + b / 8;
+                            for (int j = 0; j < 16; j++) { const int e = e0 + j; sw += (int)((blk->qs[32 * (e >> 7) + (e & 31)] >> (2 * ((e >> 5) & 3))) & 3) * y[b].qs[g * 16 + j]; sx += y[b].qs[g * 16 + j]; }
+                            const uint8_t sc = blk->scales[e0 >> 4];
+                            acc += (double)oracle_fp16_to_fp32(blk->d) * d8 * ((double)sw * (sc & 0xF)) - (double)oracle_fp16_to_fp32(blk->dmin) * d8 * ((double)sx * (sc >> 4));
+                        } else {
+                            const blk_q3_K *blk = (const blk_q3_K *)row + b / 8;
+                            for (int j = 0; j < 16; j++) sw += q3_code(blk, e0 + j) * y[b].qs[g * 16 + j];
+                            acc += (double)oracle_fp16_to_fp32(blk->d) * d8 * ((double)sw * q3_scale(blk->scales, e0 >> 4));
+                        }
+                    }
                 } else if (type == T_Q6_K) {
                     /* two 16-element scale groups per 32 sub-block: redo the split */
                     const blk_q6_K *blk = (const blk_q6_K *)row + b / 8;

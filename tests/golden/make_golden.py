@@ -125,6 +125,25 @@ def int_codes_from_dequant(name, data, deq, n, k):
                     ms = np.float64(np.float32(dm * np.float32(mn)))
                     assert sc != 0, "golden weights must have non-zero sub-scales for code recovery"
                     codes[i, 256 * b + 32 * j: 256 * b + 32 * j + 32] = np.rint((y + ms) / ds)
+            elif name == "q2_K":
+                d = np.float32(blk[80:82].view(np.float16)[0]); dm = np.float32(blk[82:84].view(np.float16)[0])
+                for g in range(16):
+                    sc = blk[g]
+                    assert (sc & 0xF) != 0, "golden weights must have non-zero sub-scales for code recovery"
+                    dl = np.float64(np.float32(d * np.float32(sc & 0xF))); ml = np.float64(np.float32(dm * np.float32(sc >> 4)))
+                    y = deq[i, 256 * b + 16 * g: 256 * b + 16 * g + 16].astype(np.float64)
+                    codes[i, 256 * b + 16 * g: 256 * b + 16 * g + 16] = np.rint((y + ml) / dl)
+            elif name == "q3_K":
+                d = np.float32(blk[108:110].view(np.float16)[0])
+                sc12 = blk[96:108]
+                for g in range(16):
+                    bb, gg = g & 3, g >> 2
+                    lo = (sc12[4 * gg + bb] & 0xF) if gg < 2 else (sc12[4 * (gg - 2) + bb] >> 4)
+                    scv = int(lo | (((sc12[8 + bb] >> (2 * gg)) & 3) << 4)) - 32
+                    assert scv != 0, "golden weights must have non-zero sub-scales for code recovery"
+                    dl = np.float64(np.float32(d * np.float32(scv)))
+                    y = deq[i, 256 * b + 16 * g: 256 * b + 16 * g + 16].astype(np.float64)
+                    codes[i, 256 * b + 16 * g: 256 * b + 16 * g + 16] = np.rint(y / dl)
             elif name == "q6_K":
                 d = np.float32(blk[208:210].view(np.float16)[0])
                 scs = blk[192:208].view(np.int8)
@@ -186,7 +205,7 @@ def main():
 
 
 def main_legacy():
-    """quant_golden_legacy.npz: the same vectors for q4_1 / q5_0 / q5_1, over the activations X of quant_golden.npz so
+    """quant_golden_legacy.npz: the same vectors for q4_1 / q5_0 / q5_1 and q2_K / q3_K, over the activations X of quant_golden.npz so
     that q81cuda / sumq are shared.  A file of its own: quant_golden.npz stays byte-identical."""
     G = np.load(os.path.join(HERE, "quant_golden.npz"))
     X = G["X"]
@@ -194,7 +213,7 @@ def main_legacy():
     rng = np.random.default_rng(20261105)
     out = {}
     Wf = G["Wf"]
-    for name, t in O.LEGACY_TYPES.items():
+    for name, t in {**O.LEGACY_TYPES, **O.SMALL_K_TYPES}.items():
         rb = O.row_bytes(t, K)
         data = np.zeros(N * rb, dtype=np.uint8)
         sz = ref.ggml_quantize_chunk(t, p(Wf), p(data), 0, N, K, None)
@@ -205,7 +224,8 @@ def main_legacy():
         rdeq = ref_dequant(name, rnd, N, K)
         out["R_" + name], out["rdeq_" + name] = rnd, rdeq.view(np.uint32)
         codes = int_codes_from_dequant(name, data, deq, N, K)
-        assert codes.min() >= 0 and codes.max() <= (15 if name == "q4_1" else 31)
+        lo, hi = {"q4_1": (0, 15), "q5_0": (0, 31), "q5_1": (0, 31), "q2_K": (0, 3), "q3_K": (-4, 3)}[name]
+        assert codes.min() >= lo and codes.max() <= hi
         out["sumi_" + name] = np.einsum("nbk,mbk->mnb", codes.reshape(N, K // 32, 32), qx.reshape(M, K // 32, 32)).astype(np.int32)
     np.savez_compressed(os.path.join(HERE, "quant_golden_legacy.npz"), **out)
     print("wrote quant_golden_legacy.npz:", {k: v.shape for k, v in out.items()})

@@ -1,4 +1,5 @@
-"""GPU parity of the round-2 format widening: q4_1 / q5_0 / q5_1 through the C ABI against the CPU oracle, to the
+"""GPU parity of the round-2 format widening: q4_1 / q5_0 / q5_1 (every path) and q2_K / q3_K (decode mat-vec,
+dequantisation; reference ggml-quants.c:706-736, 1050-1098, vecdotq.cuh:218-243, 301-331) through the C ABI against the CPU oracle, to the
 bars of test_gpu_mmvq.py / test_gpu_mmq.py: int32 block sums bit-exact (reference ggml-cuda/vecdotq.cuh:49-150), dequantised
 rows bit-exact (ggml-quants.c:269-341), fp32 mat-vec within summation-order noise of the oracle's double accumulation, the
 tensor-core mat-mul within NMSE 1e-4 of dequantise-then-f32 (the reference's bar for MUL_MAT is 5e-4)."""
@@ -13,7 +14,9 @@ import oracle as O
 pytestmark = pytest.mark.gpu
 G = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "quant_golden.npz")))
 G.update(np.load(os.path.join(os.path.dirname(__file__), "golden", "quant_golden_legacy.npz")))
-NAMES = list(O.LEGACY_TYPES)
+NAMES = list(O.LEGACY_TYPES)                                   # every path, tensor-core MMQ included
+NAMES_MV = list(O.LEGACY_TYPES) + list(O.SMALL_K_TYPES)        # decode mat-vec, dequantisation, GET_ROWS (q2_K / q3_K: prefill runs as mat-vec passes)
+TYPES = {**O.LEGACY_TYPES, **O.SMALL_K_TYPES}
 
 
 def _ops():
@@ -40,18 +43,18 @@ def _nmse(got, ref):
     return float(((got.astype(np.float64) - ref) ** 2).sum() / (ref.astype(np.float64) ** 2).sum())
 
 
-@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("name", NAMES_MV)
 def test_golden_block_sums_bit_exact(name):
-    t = O.LEGACY_TYPES[name]
+    t = TYPES[name]
     dst, sums = _run(t, G["W_" + name], G["X"], 4, 512, dbg=True)
     assert np.array_equal(sums.cpu().numpy(), G["sumi_" + name])
     _close(dst.cpu().numpy(), O.mul_mat_vec_q(t, G["W_" + name], G["X"], 4, 512, 2))
 
 
-@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("name", NAMES_MV)
 @pytest.mark.parametrize("M", [1, 2, 3, 5, 8])
 def test_small_shapes_vs_oracle(name, M):
-    t = O.LEGACY_TYPES[name]
+    t = TYPES[name]
     rng = np.random.default_rng(200 + M)
     N, K = 16, 256
     W = O.random_quant_bytes(t, N, K, rng)
@@ -65,12 +68,14 @@ def test_small_shapes_vs_oracle(name, M):
     _close(dst.cpu().numpy(), O.mul_mat_vec_q(t, W, X, N, K, M))
 
 
-@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("name", NAMES_MV)
 @pytest.mark.parametrize("N,K,M", [(257, 4096, 1), (130, 14336, 1), (96, 4096, 4), (64, 2048, 8), (40, 1024, 7), (33, 8192, 2), (1, 512, 1),
                                    (19, 160, 3), (5, 32, 1)])
 def test_model_shapes_vs_oracle(name, N, K, M):
     """K = 160 and 32: rows that end inside a 256-weight item (the tail item holds fewer than 8 blocks)."""
-    t = O.LEGACY_TYPES[name]
+    t = TYPES[name]
+    if K % O.BLOCK_ELEMS[t]:
+        pytest.skip("K is not a multiple of the super-block")
     rng = np.random.default_rng(N * 7 + K + M)
     W = O.random_quant_bytes(t, N, K, rng)
     X = rng.uniform(-1, 1, (M, K)).astype(np.float32)
@@ -82,10 +87,10 @@ def test_model_shapes_vs_oracle(name, N, K, M):
         assert _nmse(dst, f32) < 5e-4
 
 
-@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("name", NAMES_MV)
 def test_strided_unaligned_rows(name):
     ops = _ops()
-    t = O.LEGACY_TYPES[name]
+    t = TYPES[name]
     rng = np.random.default_rng(5)
     N, K, M = 19, 512, 2
     rb = O.row_bytes(t, K)
@@ -102,10 +107,10 @@ def test_strided_unaligned_rows(name):
     _close(dst.cpu().numpy(), O.mul_mat_vec_q(t, Wrows, X, N, K, M))
 
 
-@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("name", NAMES_MV)
 def test_dequantize_bit_exact(name):
     ops = _ops()
-    t = O.LEGACY_TYPES[name]
+    t = TYPES[name]
     for src, ref in (("W_", "deq_"), ("R_", "rdeq_")):
         got = ops.dequantize_rows(t, torch.from_numpy(G[src + name].reshape(-1).copy()).cuda(), 4, 512).cpu().numpy()
         assert np.array_equal(got.view(np.uint32), G[ref + name])
@@ -115,10 +120,10 @@ def test_dequantize_bit_exact(name):
     assert np.array_equal(got.view(np.uint32), O.dequantize(t, raw, 8, 4096).view(np.uint32))
 
 
-@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("name", NAMES_MV)
 def test_prequantised_path_matches_fused(name):
     ops = _ops()
-    t = O.LEGACY_TYPES[name]
+    t = TYPES[name]
     N, K, M = 37, 14336, 2
     rng = np.random.default_rng(K + M)
     W = torch.from_numpy(O.random_quant_bytes(t, N, K, rng).reshape(-1)).cuda()
@@ -140,7 +145,7 @@ def _dev(Wnp):
 @pytest.mark.parametrize("tn", [32, 64, 128, 256])
 def test_mmq_one_hot_reads_back_dequantised_weights(name, tn, monkeypatch):
     """One-hot activations read every dequantised weight back through the tensor-core path, element by element."""
-    t = O.LEGACY_TYPES[name]
+    t = TYPES[name]
     N, K = 130, 512
     rng = np.random.default_rng(11)
     W = O.random_quant_bytes(t, N, K, rng)
@@ -154,7 +159,7 @@ def test_mmq_one_hot_reads_back_dequantised_weights(name, tn, monkeypatch):
 @pytest.mark.parametrize("name", NAMES)
 @pytest.mark.parametrize("N,K,M", [(16, 256, 9), (16, 256, 32), (128, 512, 33), (257, 1024, 100), (129, 4096, 129), (512, 2048, 300), (96, 14336, 64)])
 def test_mmq_shapes_vs_oracle(name, N, K, M):
-    t = O.LEGACY_TYPES[name]
+    t = TYPES[name]
     rng = np.random.default_rng(N * 3 + K + M)
     W = O.random_quant_bytes(t, N, K, rng)
     X = rng.uniform(-1, 1, (M, K)).astype(np.float32)
@@ -166,7 +171,7 @@ def test_mmq_shapes_vs_oracle(name, N, K, M):
 @pytest.mark.parametrize("name", NAMES)
 def test_mmq_on_quantiser_output(name):
     """Weights as the reference's quantiser writes them (tests/golden: ggml_quantize_chunk), tiled to a full row tile."""
-    t = O.LEGACY_TYPES[name]
+    t = TYPES[name]
     N, K, M = 4, 512, 40
     W = G["W_" + name]
     rng = np.random.default_rng(1)
