@@ -9,7 +9,7 @@
 namespace b200 {
 
 // ggml type ids (reference ggml/include/ggml.h:352-366)
-enum : int { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q8_1 = 9, T_Q2_K = 10, T_Q3_K = 11, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14, T_I32 = 26, T_BF16 = 30 };
+enum : int { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q8_1 = 9, T_Q2_K = 10, T_Q3_K = 11, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14, T_IQ4_NL = 20, T_IQ4_XS = 23, T_I32 = 26, T_BF16 = 30 };
 
 template <int TYPE> struct fmt;   // bytes per block, elements per block
 template <> struct fmt<T_Q4_0> { static constexpr int BB = 18,  BE = 32;  };
@@ -21,16 +21,18 @@ template <> struct fmt<T_Q8_1> { static constexpr int BB = 36,  BE = 32;  };
 template <> struct fmt<T_Q2_K> { static constexpr int BB = 84,  BE = 256; };
 template <> struct fmt<T_Q3_K> { static constexpr int BB = 110, BE = 256; };
 template <> struct fmt<T_Q4_K> { static constexpr int BB = 144, BE = 256; };
+template <> struct fmt<T_IQ4_NL> { static constexpr int BB = 18,  BE = 32;  };
+template <> struct fmt<T_IQ4_XS> { static constexpr int BB = 136, BE = 256; };
 template <> struct fmt<T_Q5_K> { static constexpr int BB = 176, BE = 256; };
 template <> struct fmt<T_Q6_K> { static constexpr int BB = 210, BE = 256; };
 
 __host__ __device__ inline int block_bytes(int t) {
-    switch (t) { case T_Q4_0: return 18; case T_Q4_1: return 20; case T_Q5_0: return 22; case T_Q5_1: return 24; case T_Q8_0: return 34; case T_Q8_1: return 36; case T_Q2_K: return 84; case T_Q3_K: return 110; case T_Q4_K: return 144;
+    switch (t) { case T_IQ4_NL: return 18; case T_IQ4_XS: return 136; case T_Q4_0: return 18; case T_Q4_1: return 20; case T_Q5_0: return 22; case T_Q5_1: return 24; case T_Q8_0: return 34; case T_Q8_1: return 36; case T_Q2_K: return 84; case T_Q3_K: return 110; case T_Q4_K: return 144;
                  case T_Q5_K: return 176; case T_Q6_K: return 210; case T_F32: return 4; case T_F16: return 2; case T_I32: return 4; case T_BF16: return 2; }
     return 0;
 }
 __host__ __device__ inline int block_elems(int t) {
-    switch (t) { case T_Q4_0: case T_Q4_1: case T_Q5_0: case T_Q5_1: case T_Q8_0: case T_Q8_1: return 32; case T_Q2_K: case T_Q3_K: case T_Q4_K: case T_Q5_K: case T_Q6_K: return 256;
+    switch (t) { case T_IQ4_NL: case T_Q4_0: case T_Q4_1: case T_Q5_0: case T_Q5_1: case T_Q8_0: case T_Q8_1: return 32; case T_IQ4_XS: case T_Q2_K: case T_Q3_K: case T_Q4_K: case T_Q5_K: case T_Q6_K: return 256;
                  case T_F32: case T_F16: case T_I32: case T_BF16: return 1; }
     return 0;
 }

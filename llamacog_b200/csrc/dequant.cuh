@@ -15,6 +15,9 @@ __device__ __forceinline__ float ldh(const uint8_t * p) {   // 2-byte aligned ha
     return __half2float(__ushort_as_half(*reinterpret_cast<const unsigned short *>(p)));
 }
 
+// the table of the 4-bit non-linear formats (reference ggml-common.h:1077-1079)
+__device__ const int8_t iq4_values[16] = { -127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113 };
+
 // One element per thread; every product/difference is an explicit single rounding so the result is
 // bit-identical to the reference's unfused CPU arithmetic (ggml-quants.c dequantize_row_*).
 template <int TYPE> __device__ __forceinline__ float dequant_elem(const uint8_t * row, int64_t e) {
@@ -33,6 +36,16 @@ template <int TYPE> __device__ __forceinline__ float dequant_elem(const uint8_t 
         const int q = nib | (((b[QH + (j >> 3)] >> (j & 7)) & 1) << 4);          // bit j of the little-endian qh word
         if constexpr (TYPE == T_Q5_0) return __fmul_rn((float)(q - 16), ldh(b));
         else return __fadd_rn(__fmul_rn((float)q, ldh(b)), ldh(b + 2));
+    } else if constexpr (TYPE == T_IQ4_NL) {       // ggml-quants.c:2428-2444
+        const uint8_t * b = row + (e >> 5) * 18; const int j = e & 31;
+        const int idx = j < 16 ? (b[2 + j] & 0xF) : (b[2 + j - 16] >> 4);
+        return __fmul_rn(ldh(b), (float)iq4_values[idx]);
+    } else if constexpr (TYPE == T_IQ4_XS) {       // ggml-quants.c:2446-2467
+        const uint8_t * b = row + (e >> 8) * 136; const int r = e & 255, ib = r >> 5, j = r & 31;
+        const unsigned sh = b[2] | (b[3] << 8);
+        const int ls = (int)(((b[4 + ib / 2] >> (4 * (ib % 2))) & 0xF) | (((sh >> (2 * ib)) & 3) << 4)) - 32;
+        const int idx = j < 16 ? (b[8 + 16 * ib + j] & 0xF) : (b[8 + 16 * ib + j - 16] >> 4);
+        return __fmul_rn(__fmul_rn(ldh(b), (float)ls), (float)iq4_values[idx]);
     } else if constexpr (TYPE == T_Q2_K) {         // ggml-quants.c:706-736
         const uint8_t * b = row + (e >> 8) * 84; const int r = e & 255, n = r >> 7, j = (r >> 5) & 3, l = r & 31;
         const uint8_t sc = b[8 * n + 2 * j + (l >> 4)];

@@ -220,7 +220,7 @@ extern "C" int b200_op_get_rows(const b200_tensor * src, const b200_tensor * ids
     const int threads = src->ne[0] >= 1024 ? 256 : 64;
     switch (src->type) {
         B200_GR_CASE(T_F32) B200_GR_CASE(T_F16) B200_GR_CASE(T_BF16) B200_GR_CASE(T_Q4_0) B200_GR_CASE(T_Q8_0)
-        B200_GR_CASE(T_Q4_K) B200_GR_CASE(T_Q5_K) B200_GR_CASE(T_Q6_K) B200_GR_CASE(T_Q4_1) B200_GR_CASE(T_Q5_0) B200_GR_CASE(T_Q5_1) B200_GR_CASE(T_Q2_K) B200_GR_CASE(T_Q3_K)
+        B200_GR_CASE(T_Q4_K) B200_GR_CASE(T_Q5_K) B200_GR_CASE(T_Q6_K) B200_GR_CASE(T_Q4_1) B200_GR_CASE(T_Q5_0) B200_GR_CASE(T_Q5_1) B200_GR_CASE(T_Q2_K) B200_GR_CASE(T_Q3_K) B200_GR_CASE(T_IQ4_NL) B200_GR_CASE(T_IQ4_XS)
     }
     return -1;
 }

@@ -14,6 +14,8 @@ template <> int mmvq_launch_type<T_Q4_0>(const mmvq_params &, const mmvq_launch_
 template <> int mmvq_launch_type<T_Q8_0>(const mmvq_params &, const mmvq_launch_cfg &, cudaStream_t);
 template <> int mmvq_launch_type<T_Q4_1>(const mmvq_params &, const mmvq_launch_cfg &, cudaStream_t);
 template <> int mmvq_launch_type<T_Q2_K>(const mmvq_params &, const mmvq_launch_cfg &, cudaStream_t);
+template <> int mmvq_launch_type<T_IQ4_NL>(const mmvq_params &, const mmvq_launch_cfg &, cudaStream_t);
+template <> int mmvq_launch_type<T_IQ4_XS>(const mmvq_params &, const mmvq_launch_cfg &, cudaStream_t);
 template <> int mmvq_launch_type<T_Q3_K>(const mmvq_params &, const mmvq_launch_cfg &, cudaStream_t);
 template <> int mmvq_launch_type<T_Q5_0>(const mmvq_params &, const mmvq_launch_cfg &, cudaStream_t);
 template <> int mmvq_launch_type<T_Q5_1>(const mmvq_params &, const mmvq_launch_cfg &, cudaStream_t);
@@ -44,7 +46,7 @@ static int max_cols_per_launch(int K) {
 }
 
 static int item_bytes(int type) {
-    switch (type) { case T_Q4_0: return 144; case T_Q2_K: return 84; case T_Q3_K: return 110; case T_Q4_1: return 160; case T_Q5_0: return 176; case T_Q5_1: return 192; case T_Q8_0: return 272; case T_Q4_K: return 144; case T_Q5_K: return 176; case T_Q6_K: return 210; }
+    switch (type) { case T_Q4_0: return 144; case T_Q2_K: return 84; case T_Q3_K: return 110; case T_IQ4_NL: return 144; case T_IQ4_XS: return 136; case T_Q4_1: return 160; case T_Q5_0: return 176; case T_Q5_1: return 192; case T_Q8_0: return 272; case T_Q4_K: return 144; case T_Q5_K: return 176; case T_Q6_K: return 210; }
     return 0;
 }
 
@@ -130,6 +132,8 @@ static int mmvq_dispatch(int type, const mmvq_params & p, const mmvq_launch_cfg 
         case T_Q8_0: return mmvq_launch_type<T_Q8_0>(p, c, s);
         case T_Q4_1: return mmvq_launch_type<T_Q4_1>(p, c, s);
         case T_Q2_K: return mmvq_launch_type<T_Q2_K>(p, c, s);
+        case T_IQ4_NL: return mmvq_launch_type<T_IQ4_NL>(p, c, s);
+        case T_IQ4_XS: return mmvq_launch_type<T_IQ4_XS>(p, c, s);
         case T_Q3_K: return mmvq_launch_type<T_Q3_K>(p, c, s);
         case T_Q5_0: return mmvq_launch_type<T_Q5_0>(p, c, s);
         case T_Q5_1: return mmvq_launch_type<T_Q5_1>(p, c, s);
@@ -150,7 +154,7 @@ int pdl_default() { static const int v = [] { const char * e = getenv("B200_PDL"
 using namespace b200;
 
 extern "C" int b200_mmvq_supported_type(int type) {
-    return type == T_Q4_0 || type == T_Q8_0 || type == T_Q4_K || type == T_Q5_K || type == T_Q6_K || type == T_Q4_1 || type == T_Q5_0 || type == T_Q5_1 || type == T_Q2_K || type == T_Q3_K;
+    return type == T_Q4_0 || type == T_Q8_0 || type == T_Q4_K || type == T_Q5_K || type == T_Q6_K || type == T_Q4_1 || type == T_Q5_0 || type == T_Q5_1 || type == T_Q2_K || type == T_Q3_K || type == T_IQ4_NL || type == T_IQ4_XS;
 }
 
 extern "C" int b200_kernel_launch_count(void) { return g_launches; }

@@ -42,7 +42,7 @@ static int mmvq_launch_one(const mmvq_params & p, const mmvq_launch_cfg & c, cud
 #define B200_MMVQ_DEFINE(TYPE_) \
     template <> int mmvq_launch_type<TYPE_>(const mmvq_params & p, const mmvq_launch_cfg & c, cudaStream_t stream) { \
         constexpr int TYPE = TYPE_; \
-        constexpr bool A16_OK = (TYPE_ != T_Q6_K && TYPE_ != T_Q2_K && TYPE_ != T_Q3_K); \
+        constexpr bool A16_OK = (TYPE_ != T_Q6_K && TYPE_ != T_Q2_K && TYPE_ != T_Q3_K && TYPE_ != T_IQ4_XS); \
         B200_MMVQ_CASE(1) B200_MMVQ_CASE(2) B200_MMVQ_CASE(3) B200_MMVQ_CASE(4) \
         B200_MMVQ_CASE(5) B200_MMVQ_CASE(6) B200_MMVQ_CASE(7) B200_MMVQ_CASE(8) \
         return -1; \

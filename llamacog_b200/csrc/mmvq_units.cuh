@@ -32,6 +32,8 @@ template <> struct item_traits<T_Q4_0> { static constexpr int BYTES = 144; };
 template <> struct item_traits<T_Q8_0> { static constexpr int BYTES = 272; };
 template <> struct item_traits<T_Q2_K> { static constexpr int BYTES = 84; };    // scales[16] | qs[64] | d | dmin
 template <> struct item_traits<T_Q3_K> { static constexpr int BYTES = 110; };   // hmask[32] | qs[64] | scales[12] | d
+template <> struct item_traits<T_IQ4_NL> { static constexpr int BYTES = 144; };  // 8 x {d, qs[16]}: 4-bit indices into a fixed table
+template <> struct item_traits<T_IQ4_XS> { static constexpr int BYTES = 136; };  // d | scales_h | scales_l[4] | qs[128]
 template <> struct item_traits<T_Q4_1> { static constexpr int BYTES = 160; };   // 8 x {d, m, qs[16]}
 template <> struct item_traits<T_Q5_0> { static constexpr int BYTES = 176; };   // 8 x {d, qh[4], qs[16]}
 template <> struct item_traits<T_Q5_1> { static constexpr int BYTES = 192; };   // 8 x {d, m, qh[4], qs[16]}
@@ -85,6 +87,24 @@ template <int NW> __device__ __forceinline__ uint32_t halfword(const int (&w)[NW
 // 32-bit word starting at halfword h (static index)
 template <int NW> __device__ __forceinline__ int word_at_half(const int (&w)[NW], int h) {
     return (h & 1) ? (int)__funnelshift_r((uint32_t)w[h >> 1], (uint32_t)w[(h >> 1) + 1], 16) : w[h >> 1];
+}
+
+// The 4-bit table formats (IQ4_NL, IQ4_XS; table: reference ggml-common.h:1077-1079): eight indices of a word -> the table's int8
+// values of its four low nibbles (elements j .. j+3 of a block) and of its four high nibbles (elements j+16 ..).  PRMT picks any of
+// eight bytes per selector nibble, so a 16-entry table is two picks (entries 0-7, entries 8-15, on index & 7) and a third that
+// chooses between them on bit 3 of the index; two consecutive bytes of the word (four nibbles) are looked up at a time, and the
+// results are de-interleaved into the low-nibble and the high-nibble word.
+__device__ __forceinline__ void iq4_lookup8(uint32_t q, int & vlo, int & vhi) {
+    constexpr uint32_t T0 = 0xbfad9881u, T1 = 0xf6eaddcfu, T2 = 0x26190d01u, T3 = 0x71594535u;      // -127 -104 -83 -65 | -49 -35 -22 -10 | 1 13 25 38 | 53 69 89 113
+    uint32_t r[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const uint32_t idx = q >> (16 * i);                       // four indices: byte 2i low, high, byte 2i+1 low, high
+        const uint32_t a = __byte_perm(T0, T1, idx & 0x7777u), b = __byte_perm(T2, T3, idx & 0x7777u);
+        r[i] = __byte_perm(a, b, 0x3210u | ((idx & 0x8888u) >> 1));
+    }
+    vlo = (int)__byte_perm(r[0], r[1], 0x6420u);
+    vhi = (int)__byte_perm(r[0], r[1], 0x7531u);
 }
 
 // ---- the per-format item dot products ---------------------------------------------------------
@@ -205,6 +225,54 @@ __device__ __forceinline__ void item_dot(uint32_t wp, uint32_t ap, uint32_t acs,
                 }
             }
         }
+    } else if constexpr (TYPE == T_IQ4_NL) {
+        int w[36];                                       // block i = halfwords 9i .. 9i+8: d | qs[16]
+        lds_words<36, A16>(wp, w);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (i < nblk) {
+                const float dw = half_bits_to_float(halfword<36>(w, 9 * i));
+                int vlo[4], vhi[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) iq4_lookup8((uint32_t)word_at_half<36>(w, 9 * i + 1 + 2 * j), vlo[j], vhi[j]);
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    act_blk a; lds_act(ap + m * acs + i * ACT_BLK, a);
+                    int s = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { s = dp4a_ss(vlo[j], a.q[j], s); s = dp4a_ss(vhi[j], a.q[4 + j], s); }
+                    if constexpr (DBG) dbg[m * dms + i] = s;
+                    acc[m] = fmaf(dw * a.d8, i2f_small(s), acc[m]);
+                }
+            }
+        }
+    } else if constexpr (TYPE == T_IQ4_XS) {
+        int hd[2];
+        lds_words_a2<2>(wp, hd);                         // d | scales_h, scales_l[4]
+        const float d = half_bits_to_float((uint32_t)hd[0] & 0xFFFFu);
+        const uint32_t sh = (uint32_t)hd[0] >> 16, sl = (uint32_t)hd[1];
+        float accx[M];
+#pragma unroll
+        for (int m = 0; m < M; ++m) accx[m] = 0.0f;
+#pragma unroll
+        for (int ib = 0; ib < 8; ++ib) {
+            int q[4], vlo[4], vhi[4];
+            lds_words_a2<4>(wp + 8 + 16 * ib, q);
+            const int ls = (int)(((sl >> (4 * ib)) & 0xFu) | (((sh >> (2 * ib)) & 3u) << 4)) - 32;      // scales_l[ib / 2] >> 4 (ib % 2)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) iq4_lookup8((uint32_t)q[j], vlo[j], vhi[j]);
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+                act_blk a; lds_act(ap + m * acs + ib * ACT_BLK, a);
+                int s = 0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { s = dp4a_ss(vlo[j], a.q[j], s); s = dp4a_ss(vhi[j], a.q[4 + j], s); }
+                if constexpr (DBG) dbg[m * dms + ib] = s;
+                accx[m] = fmaf(a.d8 * (float)ls, i2f_small(s), accx[m]);
+            }
+        }
+#pragma unroll
+        for (int m = 0; m < M; ++m) acc[m] = fmaf(d, accx[m], acc[m]);
     } else if constexpr (TYPE == T_Q2_K) {
         // vecdotq.cuh:218-243.  32-block 4n + j: bits 2j..2j+1 of qs[32n .. 32n+31], a 4-bit scale / 4-bit min pair per 16 elements
         int sc[4], q[8], dmw[1];

@@ -103,6 +103,8 @@ extern "C" int b200_dequantize_rows(int type, const void * src, int64_t src_nb1,
         case T_Q8_0: return dequant_launch<T_Q8_0>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);
         case T_Q4_1: return dequant_launch<T_Q4_1>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);
         case T_Q2_K: return dequant_launch<T_Q2_K>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);
+        case T_IQ4_NL: return dequant_launch<T_IQ4_NL>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);
+        case T_IQ4_XS: return dequant_launch<T_IQ4_XS>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);
         case T_Q3_K: return dequant_launch<T_Q3_K>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);
         case T_Q5_0: return dequant_launch<T_Q5_0>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);
         case T_Q5_1: return dequant_launch<T_Q5_1>(src, src_nb1, dst, dst_type, dst_stride, k, nrows, st);

@@ -13,8 +13,9 @@ from . import build as _build
 F32, F16, Q4_0, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K, I32 = 0, 1, 2, 8, 9, 12, 13, 14, 26
 Q4_1, Q5_0, Q5_1 = 3, 6, 7
 Q2_K, Q3_K = 10, 11
-BLOCK_BYTES = {Q2_K: 84, Q3_K: 110, Q4_1: 20, Q5_0: 22, Q5_1: 24, Q4_0: 18, Q8_0: 34, Q8_1: 36, Q4_K: 144, Q5_K: 176, Q6_K: 210, F32: 4, F16: 2}
-BLOCK_ELEMS = {Q2_K: 256, Q3_K: 256, Q4_1: 32, Q5_0: 32, Q5_1: 32, Q4_0: 32, Q8_0: 32, Q8_1: 32, Q4_K: 256, Q5_K: 256, Q6_K: 256, F32: 1, F16: 1}
+IQ4_NL, IQ4_XS = 20, 23
+BLOCK_BYTES = {IQ4_NL: 18, IQ4_XS: 136, Q2_K: 84, Q3_K: 110, Q4_1: 20, Q5_0: 22, Q5_1: 24, Q4_0: 18, Q8_0: 34, Q8_1: 36, Q4_K: 144, Q5_K: 176, Q6_K: 210, F32: 4, F16: 2}
+BLOCK_ELEMS = {IQ4_NL: 32, IQ4_XS: 256, Q2_K: 256, Q3_K: 256, Q4_1: 32, Q5_0: 32, Q5_1: 32, Q4_0: 32, Q8_0: 32, Q8_1: 32, Q4_K: 256, Q5_K: 256, Q6_K: 256, F32: 1, F16: 1}
 
 
 class MmvqArgs(C.Structure):

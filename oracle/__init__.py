@@ -17,14 +17,15 @@ REF_LIB_PATH = os.path.join(HERE, "_ref", "libggml-ref.so")
 F32, F16, Q4_0, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K = 0, 1, 2, 8, 9, 12, 13, 14
 Q4_1, Q5_0, Q5_1 = 3, 6, 7
 Q2_K, Q3_K = 10, 11
+IQ4_NL, IQ4_XS = 20, 23
 QUANT_TYPES = {"q4_0": Q4_0, "q8_0": Q8_0, "q4_K": Q4_K, "q5_K": Q5_K, "q6_K": Q6_K}
 # the round-2 widening: the remaining 32-element block formats
 LEGACY_TYPES = {"q4_1": Q4_1, "q5_0": Q5_0, "q5_1": Q5_1}
 # ... and the two small K-quants (decode mat-vec, dequantisation and GET_ROWS; prefill runs as mat-vec passes)
-SMALL_K_TYPES = {"q2_K": Q2_K, "q3_K": Q3_K}
+SMALL_K_TYPES = {"q2_K": Q2_K, "q3_K": Q3_K, "iq4_nl": IQ4_NL, "iq4_xs": IQ4_XS}      # ... and the two 4-bit table formats
 ALL_QUANT_TYPES = {**QUANT_TYPES, **LEGACY_TYPES, **SMALL_K_TYPES}
-BLOCK_BYTES = {Q2_K: 84, Q3_K: 110, Q4_1: 20, Q5_0: 22, Q5_1: 24, Q4_0: 18, Q8_0: 34, Q8_1: 36, Q4_K: 144, Q5_K: 176, Q6_K: 210, F32: 4, F16: 2}
-BLOCK_ELEMS = {Q2_K: 256, Q3_K: 256, Q4_1: 32, Q5_0: 32, Q5_1: 32, Q4_0: 32, Q8_0: 32, Q8_1: 32, Q4_K: 256, Q5_K: 256, Q6_K: 256, F32: 1, F16: 1}
+BLOCK_BYTES = {IQ4_NL: 18, IQ4_XS: 136, Q2_K: 84, Q3_K: 110, Q4_1: 20, Q5_0: 22, Q5_1: 24, Q4_0: 18, Q8_0: 34, Q8_1: 36, Q4_K: 144, Q5_K: 176, Q6_K: 210, F32: 4, F16: 2}
+BLOCK_ELEMS = {IQ4_NL: 32, IQ4_XS: 256, Q2_K: 256, Q3_K: 256, Q4_1: 32, Q5_0: 32, Q5_1: 32, Q4_0: 32, Q8_0: 32, Q8_1: 32, Q4_K: 256, Q5_K: 256, Q6_K: 256, F32: 1, F16: 1}
 
 
 def row_bytes(t, k):
@@ -150,6 +151,10 @@ def random_quant_bytes(t, n, k, rng, scale=0.02):
     elif t == Q2_K:
         put_half(80, rng.uniform(0.2, 1.0, nb) * scale / 16)
         put_half(82, rng.uniform(0.2, 1.0, nb) * scale / 16)
+    elif t == IQ4_NL:
+        put_half(0, rng.uniform(0.2, 1.0, nb) * scale / 64 * rng.choice([-1.0, 1.0], nb))
+    elif t == IQ4_XS:
+        put_half(0, rng.uniform(0.2, 1.0, nb) * scale / 1024 * rng.choice([-1.0, 1.0], nb))
     elif t == Q3_K:
         put_half(108, rng.uniform(0.2, 1.0, nb) * scale / 64 * rng.choice([-1.0, 1.0], nb))
     return raw.reshape(n, rb)

@@ -29,7 +29,7 @@
 #define QK_K 256  /* elements per K-quant super-block          (ggml-common.h:89) */
 
 /* ---- ggml type ids (ggml/include/ggml.h:352-366) ---- */
-enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q8_1 = 9, T_Q2_K = 10, T_Q3_K = 11, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
+enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q8_1 = 9, T_Q2_K = 10, T_Q3_K = 11, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14, T_IQ4_NL = 20, T_IQ4_XS = 23 };
 
 /* ---- block layouts (ggml-common.h:167-172, 177-207 (q4_1 q5_0 q5_1), 209-214, 216-227, 285-296, 302-314, 320-326) ---- */
 #pragma pack(push, 1)
@@ -42,6 +42,8 @@ typedef struct { uint16_t d; uint16_t s; int8_t qs[32]; } blk_q8_1;             
 typedef struct { uint8_t scales[16]; uint8_t qs[64]; uint16_t d; uint16_t dmin; } blk_q2_K;                 /* 84 B  (ggml-common.h:250-267) */
 typedef struct { uint8_t hmask[32]; uint8_t qs[64]; uint8_t scales[12]; uint16_t d; } blk_q3_K;            /* 110 B (ggml-common.h:273-279) */
 typedef struct { uint16_t d; uint16_t dmin; uint8_t scales[12]; uint8_t qs[128]; } blk_q4_K;              /* 144 B */
+typedef struct { uint16_t d; uint8_t qs[16]; } blk_iq4_nl;                                                  /* 18 B  (ggml-common.h:405-410) */
+typedef struct { uint16_t d; uint16_t scales_h; uint8_t scales_l[4]; uint8_t qs[128]; } blk_iq4_xs;         /* 136 B (ggml-common.h:412-418) */
 typedef struct { uint16_t d; uint16_t dmin; uint8_t scales[12]; uint8_t qh[32]; uint8_t qs[128]; } blk_q5_K; /* 176 B */
 typedef struct { uint8_t ql[128]; uint8_t qh[64]; int8_t scales[16]; uint16_t d; } blk_q6_K;              /* 210 B */
 #pragma pack(pop)
@@ -51,14 +53,15 @@ int64_t oracle_block_bytes(int type) {
         case T_Q4_0: return 18; case T_Q8_0: return 34; case T_Q8_1: return 36;
         case T_Q4_1: return 20; case T_Q5_0: return 22; case T_Q5_1: return 24;
         case T_Q4_K: return 144; case T_Q5_K: return 176; case T_Q6_K: return 210; case T_Q2_K: return 84; case T_Q3_K: return 110;
+        case T_IQ4_NL: return 18; case T_IQ4_XS: return 136;
         case T_F32: return 4; case T_F16: return 2;
     }
     return 0;
 }
 int64_t oracle_block_elems(int type) {
     switch (type) {
-        case T_Q4_0: case T_Q8_0: case T_Q8_1: case T_Q4_1: case T_Q5_0: case T_Q5_1: return 32;
-        case T_Q4_K: case T_Q5_K: case T_Q6_K: case T_Q2_K: case T_Q3_K: return 256;
+        case T_Q4_0: case T_Q8_0: case T_Q8_1: case T_Q4_1: case T_Q5_0: case T_Q5_1: case T_IQ4_NL: return 32;
+        case T_Q4_K: case T_Q5_K: case T_Q6_K: case T_Q2_K: case T_Q3_K: case T_IQ4_XS: return 256;
         case T_F32: case T_F16: return 1;
     }
     return 0;
@@ -235,6 +238,35 @@ static void deq_q3_K(const blk_q3_K *x, float *y, int64_t k) {
     }
 }
 
+/* iq4_nl / iq4_xs (ggml-quants.c:2428-2467): 4-bit indices into a fixed non-linear table (ggml-common.h:1077-1079); iq4_nl has one
+ * f16 scale per 32 elements, iq4_xs a super-block scale times a 6-bit block scale minus 32.  Low nibbles are elements 0..15 of a
+ * block, high nibbles 16..31. */
+static const int8_t iq4_table[16] = { -127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113 };
+static void deq_iq4_nl(const blk_iq4_nl *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK; i++) {
+        const float d = oracle_fp16_to_fp32(x[i].d);
+        for (int j = 0; j < 16; j++) {
+            y[i * QK + j]      = d * (float)iq4_table[x[i].qs[j] & 0xF];
+            y[i * QK + j + 16] = d * (float)iq4_table[x[i].qs[j] >> 4];
+        }
+    }
+}
+static int iq4_xs_scale(const blk_iq4_xs *b, int ib) {
+    return (((b->scales_l[ib / 2] >> (4 * (ib % 2))) & 0xF) | (((b->scales_h >> (2 * ib)) & 3) << 4)) - 32;
+}
+static void deq_iq4_xs(const blk_iq4_xs *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK_K; i++) {
+        const float d = oracle_fp16_to_fp32(x[i].d);
+        for (int ib = 0; ib < 8; ib++) {
+            const float dl = d * (float)iq4_xs_scale(&x[i], ib);
+            for (int j = 0; j < 16; j++) {
+                y[i * QK_K + 32 * ib + j]      = dl * (float)iq4_table[x[i].qs[16 * ib + j] & 0xF];
+                y[i * QK_K + 32 * ib + j + 16] = dl * (float)iq4_table[x[i].qs[16 * ib + j] >> 4];
+            }
+        }
+    }
+}
+
 int oracle_dequantize_row(int type, const void *x, float *y, int64_t k) {
     switch (type) {
         case T_Q4_0: deq_q4_0((const blk_q4_0 *)x, y, k); return 0;
@@ -247,6 +279,8 @@ int oracle_dequantize_row(int type, const void *x, float *y, int64_t k) {
         case T_Q6_K: deq_q6_K((const blk_q6_K *)x, y, k); return 0;
         case T_Q2_K: deq_q2_K((const blk_q2_K *)x, y, k); return 0;
         case T_Q3_K: deq_q3_K((const blk_q3_K *)x, y, k); return 0;
+        case T_IQ4_NL: deq_iq4_nl((const blk_iq4_nl *)x, y, k); return 0;
+        case T_IQ4_XS: deq_iq4_xs((const blk_iq4_xs *)x, y, k); return 0;
         case T_F32: memcpy(y, x, (size_t)k * 4); return 0;
         case T_F16: for (int64_t i = 0; i < k; i++) y[i] = oracle_fp16_to_fp32(((const uint16_t *)x)[i]); return 0;
     }
@@ -354,6 +388,16 @@ static void int_codes(int type, const void *row, int64_t k, int *w) {
         const blk_q2_K *b = (const blk_q2_K *)row;
         for (int64_t i = 0; i < k / QK_K; i++) for (int e = 0; e < QK_K; e++)
             w[i * QK_K + e] = (b[i].qs[32 * (e >> 7) + (e & 31)] >> (2 * ((e >> 5) & 3))) & 3;
+    } else if (type == T_IQ4_NL) {    /* table values (vecdotq.cuh: vec_dot_iq4_nl_q8_1) */
+        const blk_iq4_nl *b = (const blk_iq4_nl *)row;
+        for (int64_t i = 0; i < k / QK; i++) for (int j = 0; j < 16; j++) {
+            w[i * QK + j] = iq4_table[b[i].qs[j] & 0xF]; w[i * QK + j + 16] = iq4_table[b[i].qs[j] >> 4];
+        }
+    } else if (type == T_IQ4_XS) {
+        const blk_iq4_xs *b = (const blk_iq4_xs *)row;
+        for (int64_t i = 0; i < k / QK_K; i++) for (int ib = 0; ib < 8; ib++) for (int j = 0; j < 16; j++) {
+            w[i * QK_K + 32 * ib + j] = iq4_table[b[i].qs[16 * ib + j] & 0xF]; w[i * QK_K + 32 * ib + j + 16] = iq4_table[b[i].qs[16 * ib + j] >> 4];
+        }
     } else if (type == T_Q3_K) {      /* -4..3 after __vsubss4 (vecdotq.cuh:301-331) */
         const blk_q3_K *b = (const blk_q3_K *)row;
         for (int64_t i = 0; i < k / QK_K; i++) for (int e = 0; e < QK_K; e++) w[i * QK_K + e] = q3_code(&b[i], e);
@@ -410,6 +454,11 @@ int oracle_mul_mat_vec_q(int type, const void *W, int64_t row_stride_bytes, cons
                 } else if (type == T_Q5_0) {
                     const double d = oracle_fp16_to_fp32(((const blk_q5_0 *)row)[b].d);
                     acc += use_s8 ? d * (si[b] * d8 - 16.0 * s8) : d * d8 * (si[b] - 16.0 * sq[b]);
+                } else if (type == T_IQ4_NL) {
+                    acc += (double)oracle_fp16_to_fp32(((const blk_iq4_nl *)row)[b].d) * d8 * si[b];
+                } else if (type == T_IQ4_XS) {
+                    const blk_iq4_xs *blk = (const blk_iq4_xs *)row + b / 8;
+                    acc += (double)oracle_fp16_to_fp32(blk->d) * iq4_xs_scale(blk, (int)(b % 8)) * d8 * si[b];
                 } else if (type == T_Q8_0) {
                     acc += (double)oracle_fp16_to_fp32(((const blk_q8_0 *)row)[b].d) * d8 * si[b];
                 } else if (type == T_Q4_K || type == T_Q5_K) {

@@ -125,6 +125,17 @@ def int_codes_from_dequant(name, data, deq, n, k):
                     ms = np.float64(np.float32(dm * np.float32(mn)))
                     assert sc != 0, "golden weights must have non-zero sub-scales for code recovery"
                     codes[i, 256 * b + 32 * j: 256 * b + 32 * j + 32] = np.rint((y + ms) / ds)
+            elif name == "iq4_nl":
+                d = np.float64(blk[0:2].view(np.float16)[0])
+                assert d != 0
+                codes[i, 32 * b: 32 * b + 32] = np.rint(deq[i, 32 * b: 32 * b + 32].astype(np.float64) / d)
+            elif name == "iq4_xs":
+                d = np.float32(blk[0:2].view(np.float16)[0]); sh = int(blk[2:4].view(np.uint16)[0]); sl = blk[4:8]
+                for ib in range(8):
+                    ls = (((int(sl[ib // 2]) >> (4 * (ib % 2))) & 0xF) | (((sh >> (2 * ib)) & 3) << 4)) - 32
+                    assert ls != 0 and d != 0, "golden weights must have non-zero block scales for code recovery"
+                    dl = np.float64(np.float32(d * np.float32(ls)))
+                    codes[i, 256 * b + 32 * ib: 256 * b + 32 * ib + 32] = np.rint(deq[i, 256 * b + 32 * ib: 256 * b + 32 * ib + 32].astype(np.float64) / dl)
             elif name == "q2_K":
                 d = np.float32(blk[80:82].view(np.float16)[0]); dm = np.float32(blk[82:84].view(np.float16)[0])
                 for g in range(16):
@@ -224,7 +235,7 @@ def main_legacy():
         rdeq = ref_dequant(name, rnd, N, K)
         out["R_" + name], out["rdeq_" + name] = rnd, rdeq.view(np.uint32)
         codes = int_codes_from_dequant(name, data, deq, N, K)
-        lo, hi = {"q4_1": (0, 15), "q5_0": (0, 31), "q5_1": (0, 31), "q2_K": (0, 3), "q3_K": (-4, 3)}[name]
+        lo, hi = {"q4_1": (0, 15), "q5_0": (0, 31), "q5_1": (0, 31), "q2_K": (0, 3), "q3_K": (-4, 3), "iq4_nl": (-127, 113), "iq4_xs": (-127, 113)}[name]
         assert codes.min() >= lo and codes.max() <= hi
         out["sumi_" + name] = np.einsum("nbk,mbk->mnb", codes.reshape(N, K // 32, 32), qx.reshape(M, K // 32, 32)).astype(np.int32)
     np.savez_compressed(os.path.join(HERE, "quant_golden_legacy.npz"), **out)

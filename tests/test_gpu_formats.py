@@ -1,5 +1,5 @@
-"""GPU parity of the round-2 format widening: q4_1 / q5_0 / q5_1 (every path) and q2_K / q3_K (decode mat-vec,
-dequantisation; reference ggml-quants.c:706-736, 1050-1098, vecdotq.cuh:218-243, 301-331) through the C ABI against the CPU oracle, to the
+"""GPU parity of the round-2 format widening: q4_1 / q5_0 / q5_1 (every path) and q2_K / q3_K / iq4_nl / iq4_xs (decode mat-vec,
+dequantisation; reference ggml-quants.c:706-736, 1050-1098, 2428-2467, vecdotq.cuh:218-243, 301-331) through the C ABI against the CPU oracle, to the
 bars of test_gpu_mmvq.py / test_gpu_mmq.py: int32 block sums bit-exact (reference ggml-cuda/vecdotq.cuh:49-150), dequantised
 rows bit-exact (ggml-quants.c:269-341), fp32 mat-vec within summation-order noise of the oracle's double accumulation, the
 tensor-core mat-mul within NMSE 1e-4 of dequantise-then-f32 (the reference's bar for MUL_MAT is 5e-4)."""

@@ -142,7 +142,7 @@ def _nodes(path):
 
 
 @pytest.mark.parametrize("preset,n_prompt,ftype", [("tiny", 70, "q4_k_m"), ("tiny-moe", 40, "q4_k_m"), ("llama3.2-1b", 40, "q4_k_m"),
-                                                   ("tiny", 70, "q4_1"), ("tiny", 70, "q5_0"), ("tiny", 70, "q5_1"), ("tiny-moe", 40, "q5_0"), ("tiny", 70, "q2_k"), ("tiny", 70, "q3_k")])
+                                                   ("tiny", 70, "q4_1"), ("tiny", 70, "q5_0"), ("tiny", 70, "q5_1"), ("tiny-moe", 40, "q5_0"), ("tiny", 70, "q2_k"), ("tiny", 70, "q3_k"), ("tiny", 70, "iq4_nl"), ("tiny", 70, "iq4_xs")])
 def test_per_node_parity_with_reference_cpu_backend(tmp_path, preset, n_prompt, ftype):
     """The fixed-seed twin of the end-to-end logits test, node by node.  The model runs on the plugin with the scheduler's eval
     callback (ggml-backend.cpp:1415-1447) handing out every MUL_MAT / MUL_MAT_ID / FLASH_ATTN_EXT node of the prefill graph (MMQ +

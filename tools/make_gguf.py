@@ -14,7 +14,7 @@ only draws random token ids (tools/llama-bench/llama-bench.cpp:1760-1792); the l
 BASELINE.json names is absent from the reference mount (.MISSING_LARGE_BLOBS).
 
 usage: make_gguf.py <preset> <ftype> <out.gguf>     presets: llama3-8b llama3.2-1b llama3-70b mixtral-8x7b tiny tiny-moe
-                                                     ftypes:  q4_k_m q4_0 q4_1 q5_0 q5_1 q8_0 q2_k q3_k f16   (q2_k / q3_k: every 2-D tensor of that type, output Q6_K)
+                                                     ftypes:  q4_k_m q4_0 q4_1 q5_0 q5_1 q8_0 q2_k q3_k iq4_nl iq4_xs f16   (q2_k ... iq4_xs: every 2-D tensor of that type, output Q6_K)
 """
 import concurrent.futures as cf
 import ctypes as C
@@ -37,7 +37,8 @@ PRESETS = {
 F32, F16, Q4_0, Q8_0, Q4_K, Q5_K, Q6_K = 0, 1, 2, 8, 12, 13, 14
 Q4_1, Q5_0, Q5_1 = 3, 6, 7
 Q2_K, Q3_K = 10, 11
-FTYPE_ID = {"f16": 1, "q4_0": 2, "q4_1": 3, "q8_0": 7, "q5_0": 8, "q5_1": 9, "q2_k": 10, "q3_k": 11, "q4_k_m": 15}      # llama_ftype (include/llama.h)
+IQ4_NL, IQ4_XS = 20, 23
+FTYPE_ID = {"f16": 1, "q4_0": 2, "q4_1": 3, "q8_0": 7, "q5_0": 8, "q5_1": 9, "q2_k": 10, "q3_k": 11, "q4_k_m": 15, "iq4_nl": 25, "iq4_xs": 30}      # llama_ftype (include/llama.h)
 
 
 def use_more_bits(i, n):
@@ -49,7 +50,7 @@ def tensor_type(name, il, n_layer, ftype, n_expert, is_70b, tied):
         return F32
     if ftype == "f16":
         return F16
-    base = {"q4_0": Q4_0, "q4_1": Q4_1, "q5_0": Q5_0, "q5_1": Q5_1, "q8_0": Q8_0, "q2_k": Q2_K, "q3_k": Q3_K, "q4_k_m": Q4_K}[ftype]
+    base = {"q4_0": Q4_0, "q4_1": Q4_1, "q5_0": Q5_0, "q5_1": Q5_1, "q8_0": Q8_0, "q2_k": Q2_K, "q3_k": Q3_K, "iq4_nl": IQ4_NL, "iq4_xs": IQ4_XS, "q4_k_m": Q4_K}[ftype]
     if name == "output.weight" or (tied and name == "token_embd.weight"):
         return Q8_0 if ftype == "q8_0" else Q6_K
     if ftype != "q4_k_m":
@@ -140,7 +141,8 @@ def main():
     qt = {F32: gguf.GGMLQuantizationType.F32, F16: gguf.GGMLQuantizationType.F16, Q4_0: gguf.GGMLQuantizationType.Q4_0,
           Q8_0: gguf.GGMLQuantizationType.Q8_0, Q4_K: gguf.GGMLQuantizationType.Q4_K, Q5_K: gguf.GGMLQuantizationType.Q5_K,
           Q6_K: gguf.GGMLQuantizationType.Q6_K, Q4_1: gguf.GGMLQuantizationType.Q4_1, Q5_0: gguf.GGMLQuantizationType.Q5_0,
-          Q5_1: gguf.GGMLQuantizationType.Q5_1, Q2_K: gguf.GGMLQuantizationType.Q2_K, Q3_K: gguf.GGMLQuantizationType.Q3_K}
+          Q5_1: gguf.GGMLQuantizationType.Q5_1, Q2_K: gguf.GGMLQuantizationType.Q2_K, Q3_K: gguf.GGMLQuantizationType.Q3_K,
+          IQ4_NL: gguf.GGMLQuantizationType.IQ4_NL, IQ4_XS: gguf.GGMLQuantizationType.IQ4_XS}
 
     def add(full, short, il, rows, k, salt, experts=0):
         t = tensor_type(short, il, n_layer, ftype, n_expert, is_70b, tied)
