@@ -63,6 +63,24 @@ __device__ __forceinline__ float half_bits_to_float(uint32_t h16) {
     return __half2float(__ushort_as_half((unsigned short)h16));
 }
 
+// The 4-bit table formats (IQ4_NL, IQ4_XS; table: reference ggml-common.h:1077-1079): eight indices of a word -> the table's int8
+// values of its four low nibbles (elements j .. j+3 of a block) and of its four high nibbles (elements j+16 ..).  PRMT picks any of
+// eight bytes per selector nibble, so a 16-entry table is two picks (entries 0-7, entries 8-15, on index & 7) and a third that
+// chooses between them on bit 3 of the index; two consecutive bytes of the word (four nibbles) are looked up at a time, and the
+// results are de-interleaved into the low-nibble and the high-nibble word.
+__device__ __forceinline__ void iq4_lookup8(uint32_t q, int & vlo, int & vhi) {
+    constexpr uint32_t T0 = 0xbfad9881u, T1 = 0xf6eaddcfu, T2 = 0x26190d01u, T3 = 0x71594535u;      // -127 -104 -83 -65 | -49 -35 -22 -10 | 1 13 25 38 | 53 69 89 113
+    uint32_t r[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const uint32_t idx = q >> (16 * i);                       // four indices: byte 2i low, high, byte 2i+1 low, high
+        const uint32_t a = __byte_perm(T0, T1, idx & 0x7777u), b = __byte_perm(T2, T3, idx & 0x7777u);
+        r[i] = __byte_perm(a, b, 0x3210u | ((idx & 0x8888u) >> 1));
+    }
+    vlo = (int)__byte_perm(r[0], r[1], 0x6420u);
+    vhi = (int)__byte_perm(r[0], r[1], 0x7531u);
+}
+
 // ---- mbarrier + bulk async copy (TMA 1-D) ----------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {

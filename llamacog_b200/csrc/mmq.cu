@@ -181,6 +181,7 @@ template <int NW, int S> __device__ __forceinline__ void lds_shifted(uint32_t a1
 //      A 210-byte block is not a multiple of 16: TMA fetches the enclosing 16-byte aligned 240-byte window, so block
 //      kb starts S = (210 kb) mod 16 = 2 (kb mod 8) bytes into its row of the raw stage (compile-time per unrolled kb).
 template <> struct dq<T_Q6_K> {
+    static constexpr int BB = 210;        // bytes per block: block kb of a row starts (BB * kb) % 16 bytes into its 16-byte aligned window
     static constexpr int PITCH = 240;
     static constexpr int STEP16 = 105;
     static constexpr bool SHIFTED = true;
@@ -216,6 +217,166 @@ template <> struct dq<T_Q6_K> {
                     expand4_sym(code, s2[si], o[2 * i], o[2 * i + 1]);
                 }
                 { out[4 * ((4 * g + u))] = o[0]; out[4 * ((4 * g + u)) + 1] = o[1]; out[4 * ((4 * g + u)) + 2] = o[2]; out[4 * ((4 * g + u)) + 3] = o[3]; }
+            }
+        }
+    }
+};
+
+// ---- Q2_K (round 2): scales[16] (4-bit scale | 4-bit min per 16 elements) | qs[64] | d | dmin; element 128n + 32j + l: bits 2j..2j+1 of
+//      qs[32n + l]; q*d*sc - dmin*mn = ((1 + q/4) - 1.5) * 4 d sc + (2 d sc - dmin mn).  84-byte blocks: window of 96 bytes, shift (84 kb) % 16.
+template <> struct dq<T_Q2_K> {
+    static constexpr int BB = 84;
+    static constexpr int PITCH = 96;
+    static constexpr int STEP16 = 42;
+    static constexpr bool SHIFTED = true;
+    uint32_t s2[8], b2[8], qs[8];          // the eight 16-element scale groups and the 32 code bytes of this half
+    template <int S> __device__ __forceinline__ void prep(uint32_t row, int h) {
+        uint32_t dmw[1]; lds_shifted<1, S>(row + 80, dmw);
+        const float d = half_bits_to_float(dmw[0] & 0xFFFFu), dmin = half_bits_to_float(dmw[0] >> 16);
+        uint32_t sc[4]; lds_shifted<4, S>(row, sc);
+        const uint32_t sx = h ? sc[2] : sc[0], sy = h ? sc[3] : sc[1];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint32_t b = ((j < 4 ? sx : sy) >> (8 * (j & 3))) & 0xFFu;
+            make_sb(4.0f * d * (float)(b & 0xFu), dmin * (float)(b >> 4), s2[j], b2[j]);
+        }
+        lds_shifted<8, S>(row + 16 + 32 * h, qs);
+    }
+    __device__ __forceinline__ void emit(uint32_t, int, int t, uint32_t (&out)[32]) const {
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {   // 32 elements each: bit pair j = 2t + jj of every code byte
+            const int j = 2 * t + jj;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                uint32_t o[4];
+                const int si = 2 * j + (u >> 1);
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const uint32_t code = (((qs[2 * u + i] >> (2 * j)) & 0x03030303u) << 5) | 0x80808080u;
+                    expand4(code, s2[si], b2[si], o[2 * i], o[2 * i + 1]);
+                }
+                { out[4 * ((4 * jj + u))] = o[0]; out[4 * ((4 * jj + u)) + 1] = o[1]; out[4 * ((4 * jj + u)) + 2] = o[2]; out[4 * ((4 * jj + u)) + 3] = o[3]; }
+            }
+        }
+    }
+};
+
+// ---- Q3_K (round 2): hmask[32] | qs[64] | scales[12] (6 bit) | d; code q3 = 2 low bits | hmask bit (4n + j) << 2, value (q3 - 4) d (sc - 32)
+//      = ((1 + q3/8) - 1.5) * 8 d (sc - 32).  110-byte blocks: window of 128 bytes, shift (110 kb) % 16.
+template <> struct dq<T_Q3_K> {
+    static constexpr int BB = 110;
+    static constexpr int PITCH = 128;
+    static constexpr int STEP16 = 55;
+    static constexpr bool SHIFTED = true;
+    uint32_t s2[8], hm[8], qs[8];
+    template <int S> __device__ __forceinline__ void prep(uint32_t row, int h) {
+        const float d = half_bits_to_float(lds16(row + 108 + S));
+        uint32_t sc[3]; lds_shifted<3, S>(row + 96, sc);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {      // scale 8h + j: low nibble from scales[(8h + j) % 8] (high nibble for the second half), high pair from scales[8 + j % 4]
+            const uint32_t lo = (sc[j >> 2] >> (8 * (j & 3) + 4 * h)) & 0xFu;
+            const uint32_t hi = (sc[2] >> (8 * (j & 3) + 2 * (2 * h + (j >> 2)))) & 3u;
+            s2[j] = pack_bf16_dup(8.0f * d * (float)((int)(lo | (hi << 4)) - 32));
+        }
+        lds_shifted<8, S>(row, hm);
+        lds_shifted<8, S>(row + 32 + 32 * h, qs);
+    }
+    __device__ __forceinline__ void emit(uint32_t, int h, int t, uint32_t (&out)[32]) const {
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+            const int j = 2 * t + jj;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                uint32_t o[4];
+                const int si = 2 * j + (u >> 1);
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const uint32_t code = (((qs[2 * u + i] >> (2 * j)) & 0x03030303u) << 4) | (((hm[2 * u + i] >> (4 * h + j)) & 0x01010101u) << 6) | 0x80808080u;
+                    expand4_sym(code, s2[si], o[2 * i], o[2 * i + 1]);
+                }
+                { out[4 * ((4 * jj + u))] = o[0]; out[4 * ((4 * jj + u)) + 1] = o[1]; out[4 * ((4 * jj + u)) + 2] = o[2]; out[4 * ((4 * jj + u)) + 3] = o[3]; }
+            }
+        }
+    }
+};
+
+// int8 x 4 (a word of table values) times an f16 scale -> two packed bf16 pairs.  As for Q8_0: 1024 + (v ^ 0x80) is exact in f16,
+// minus 1152 gives v, times the scale, rounded to bf16.
+__device__ __forceinline__ void i8x4_scaled(uint32_t v, __half2 d2, uint32_t & o01, uint32_t & o23) {
+    const __half2 off = __float2half2_rn(1152.0f);
+    const uint32_t x = v ^ 0x80808080u;
+    const uint32_t a = __byte_perm(x, 0x64646464u, PRMT_01), c = __byte_perm(x, 0x64646464u, PRMT_23);
+    const float2 fa = __half22float2(__hmul2(__hsub2(*reinterpret_cast<const __half2 *>(&a), off), d2));
+    const float2 fc = __half22float2(__hmul2(__hsub2(*reinterpret_cast<const __half2 *>(&c), off), d2));
+    o01 = pack_bf16(fa.x, fa.y); o23 = pack_bf16(fc.x, fc.y);
+}
+
+// ---- IQ4_NL (round 2): 8 blocks of {d (f16), qs[16]} per 256 K; table[nibble] * d (table: common.cuh iq4_lookup8)
+template <> struct dq<T_IQ4_NL> {
+    static constexpr int PITCH = 144;
+    static constexpr int STEP16 = 72;
+    static constexpr bool SHIFTED = false;
+    template <int S> __device__ __forceinline__ void prep(uint32_t, int) {}
+    __device__ __forceinline__ void emit(uint32_t row, int h, int t, uint32_t (&out)[32]) const {
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            const uint32_t blk = row + 18 * (2 * (2 * h + t) + b);
+            const __half2 d2 = __half2half2(__ushort_as_half((unsigned short)lds16(blk)));
+            int w[4]; lds_words_a2<4>(blk + 2, w);
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                uint32_t o[4], p[4];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    int vlo, vhi; iq4_lookup8((uint32_t)w[2 * u + i], vlo, vhi);
+                    i8x4_scaled((uint32_t)vlo, d2, o[2 * i], o[2 * i + 1]);
+                    i8x4_scaled((uint32_t)vhi, d2, p[2 * i], p[2 * i + 1]);
+                }
+                { out[4 * ((4 * b + u))] = o[0]; out[4 * ((4 * b + u)) + 1] = o[1]; out[4 * ((4 * b + u)) + 2] = o[2]; out[4 * ((4 * b + u)) + 3] = o[3]; }
+                { out[4 * ((4 * b + u + 2))] = p[0]; out[4 * ((4 * b + u + 2)) + 1] = p[1]; out[4 * ((4 * b + u + 2)) + 2] = p[2]; out[4 * ((4 * b + u + 2)) + 3] = p[3]; }
+            }
+        }
+    }
+};
+
+// ---- IQ4_XS (round 2): d | scales_h | scales_l[4] | qs[128]; block ib: table[nibble] * d * (ls - 32), ls = 6 bits.  136-byte blocks:
+//      window of 144 bytes, shift (136 kb) % 16 = 0 / 8; the codes of a block sit 8 bytes further (shift 8 / 0 of the next 16 bytes).
+template <> struct dq<T_IQ4_XS> {
+    static constexpr int BB = 136;
+    static constexpr int PITCH = 144;
+    static constexpr int STEP16 = 68;
+    static constexpr bool SHIFTED = true;
+    uint32_t dl[4], qs[16];                // this half's four block scales (f16 pairs) and 64 code bytes
+    template <int S> __device__ __forceinline__ void prep(uint32_t row, int h) {
+        uint32_t hd[2]; lds_shifted<2, S>(row, hd);
+        const float d = half_bits_to_float(hd[0] & 0xFFFFu);
+        const uint32_t sh = hd[0] >> 16, sl = hd[1];
+#pragma unroll
+        for (int bb = 0; bb < 4; ++bb) {
+            const int ib = 4 * h + bb;
+            const int ls = (int)(((sl >> (4 * ib)) & 0xFu) | (((sh >> (2 * ib)) & 3u) << 4)) - 32;
+            const __half2 d2 = __float2half2_rn(d * (float)ls);
+            dl[bb] = *reinterpret_cast<const uint32_t *>(&d2);
+            uint32_t w[4];
+            lds_shifted<4, (S + 8) % 16>(row + 16 * ib + ((S + 8) & ~15), w);
+            qs[4 * bb] = w[0]; qs[4 * bb + 1] = w[1]; qs[4 * bb + 2] = w[2]; qs[4 * bb + 3] = w[3];
+        }
+    }
+    __device__ __forceinline__ void emit(uint32_t, int, int t, uint32_t (&out)[32]) const {
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            const __half2 d2 = *reinterpret_cast<const __half2 *>(&dl[2 * t + b]);
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                uint32_t o[4], p[4];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    int vlo, vhi; iq4_lookup8(qs[4 * (2 * t + b) + 2 * u + i], vlo, vhi);
+                    i8x4_scaled((uint32_t)vlo, d2, o[2 * i], o[2 * i + 1]);
+                    i8x4_scaled((uint32_t)vhi, d2, p[2 * i], p[2 * i + 1]);
+                }
+                { out[4 * ((4 * b + u))] = o[0]; out[4 * ((4 * b + u)) + 1] = o[1]; out[4 * ((4 * b + u)) + 2] = o[2]; out[4 * ((4 * b + u)) + 3] = o[3]; }
+                { out[4 * ((4 * b + u + 2))] = p[0]; out[4 * ((4 * b + u + 2)) + 1] = p[1]; out[4 * ((4 * b + u + 2)) + 2] = p[2]; out[4 * ((4 * b + u + 2)) + 3] = p[3]; }
             }
         }
     }
@@ -545,12 +706,13 @@ mmq_kernel(const __grid_constant__ CUtensorMap wmap0, const __grid_constant__ CU
                 __syncwarp();
                 if (lane == 0) { mbar_arrive(a_full + 8 * slot); mbar_arrive(raw_empty + 8 * s); }
             };
-            if constexpr (DQ::SHIFTED) {         // block kb sits 2*(kb % 8) bytes into its raw row: unroll the period
+            if constexpr (DQ::SHIFTED) {         // block kb sits (BB * kb) % 16 bytes into its raw row (Q6_K: 2 * (kb % 8)): unroll the period of 8
+                constexpr int BBs = DQ::BB;
                 for (int kb = 0; kb < nkb; kb += 8) {
-                    block(std::integral_constant<int, 0>{}, kb);      block(std::integral_constant<int, 2>{}, kb + 1);
-                    block(std::integral_constant<int, 4>{}, kb + 2);  block(std::integral_constant<int, 6>{}, kb + 3);
-                    block(std::integral_constant<int, 8>{}, kb + 4);  block(std::integral_constant<int, 10>{}, kb + 5);
-                    block(std::integral_constant<int, 12>{}, kb + 6); block(std::integral_constant<int, 14>{}, kb + 7);
+                    block(std::integral_constant<int, 0>{}, kb);                    block(std::integral_constant<int, (BBs * 1) % 16>{}, kb + 1);
+                    block(std::integral_constant<int, (BBs * 2) % 16>{}, kb + 2);  block(std::integral_constant<int, (BBs * 3) % 16>{}, kb + 3);
+                    block(std::integral_constant<int, (BBs * 4) % 16>{}, kb + 4);  block(std::integral_constant<int, (BBs * 5) % 16>{}, kb + 5);
+                    block(std::integral_constant<int, (BBs * 6) % 16>{}, kb + 6);  block(std::integral_constant<int, (BBs * 7) % 16>{}, kb + 7);
                 }
             } else {
                 for (int kb = 0; kb < nkb; ++kb) block(std::integral_constant<int, 0>{}, kb);
@@ -668,10 +830,16 @@ encode_tiled_fn encode_tiled() {
 static int env_int(const char * name, int def) { const char * e = getenv(name); return e ? atoi(e) : def; }
 
 template <int TYPE> static int pitch_of() { return dq<TYPE>::PITCH; }
+// Q2_K / Q3_K / IQ4_NL / IQ4_XS on the tensor-core path (round 2; B200_MMQ_MORE=0: those types run prefill as mat-vec passes)
+static bool mmq_more() { static const bool v = [] { const char * e = getenv("B200_MMQ_MORE"); return !e || atoi(e) != 0; }(); return v; }
+// formats whose blocks are not multiples of 16 bytes: shifted windows, whole periods of 8 blocks per row
+static bool mmq_shifted(int type) { return type == T_Q6_K || type == T_Q2_K || type == T_Q3_K || type == T_IQ4_XS; }
 static int raw_pitch(int type) {
     switch (type) { case T_Q4_0: return pitch_of<T_Q4_0>(); case T_Q8_0: return pitch_of<T_Q8_0>(); case T_Q4_K: return pitch_of<T_Q4_K>();
                     case T_Q4_1: return pitch_of<T_Q4_1>(); case T_Q5_0: return pitch_of<T_Q5_0>(); case T_Q5_1: return pitch_of<T_Q5_1>();
-                    case T_Q5_K: return pitch_of<T_Q5_K>(); case T_Q6_K: return pitch_of<T_Q6_K>(); }
+                    case T_Q5_K: return pitch_of<T_Q5_K>(); case T_Q6_K: return pitch_of<T_Q6_K>();
+                    case T_Q2_K: return mmq_more() ? pitch_of<T_Q2_K>() : 0; case T_Q3_K: return mmq_more() ? pitch_of<T_Q3_K>() : 0;
+                    case T_IQ4_NL: return mmq_more() ? pitch_of<T_IQ4_NL>() : 0; case T_IQ4_XS: return mmq_more() ? pitch_of<T_IQ4_XS>() : 0; }
     return 0;
 }
 static size_t mmq_smem(int type, int tn, int nb, int nr) { return 1024 + (size_t)nb * tn * 128 + (size_t)nr * 128 * (size_t)raw_pitch(type) + 512; }
@@ -758,7 +926,7 @@ static int plan_ksplit(int type, int K, int M, int tn, int ctas, int part_ds, cu
     static const int on = env_int("B200_MMQ_KSPLIT", 1);
     *part = nullptr;
     if (!on || M > tn || M > 32 || ctas <= 0 || ctas > 74) return 1;      // (one 32-token tile: batched decode steps, short prompts)
-    const int nkb = K >> 8, unit = type == T_Q6_K ? 8 : 1;
+    const int nkb = K >> 8, unit = mmq_shifted(type) ? 8 : 1;
     int ks = std::min(8, 148 / ctas);
     while (ks > 1 && (nkb % (ks * unit) != 0 || nkb / ks < 4)) --ks;
     if (ks < 2 || (size_t)ks * M * part_ds * 4 > KSPLIT_BYTES) return 1;
@@ -787,7 +955,7 @@ using namespace b200;
 
 extern "C" int b200_mul_mat_q_supported(int type, const void * W, int64_t nb1, int K) {
     if (!raw_pitch(type) || K <= 0 || K % 256) return 0;
-    if (type == T_Q6_K && K % 2048) return 0;                     // the 210-byte blocks realign with 16 bytes every 8 blocks
+    if (mmq_shifted(type) && K % 2048) return 0;                  // the 210-byte (84, 110, 136) blocks realign with 16 bytes every 8 blocks at the latest
     if (((uintptr_t)W & 15) || (nb1 & 15)) return 0;              // TMA: 16-byte aligned base and row stride
     if (nb1 < (int64_t)(K / block_elems(type)) * block_bytes(type)) return 0;
     return encode_tiled() != nullptr;
@@ -869,6 +1037,10 @@ extern "C" int b200_mul_mat_q_bf16(int type, const void * W, int64_t nb1, const 
         case T_Q4_K: rc = mmq_launch<T_Q4_K>(wmap, xmap, p, smem, st); break;
         case T_Q5_K: rc = mmq_launch<T_Q5_K>(wmap, xmap, p, smem, st); break;
         case T_Q6_K: rc = mmq_launch<T_Q6_K>(wmap, xmap, p, smem, st); break;
+        case T_Q2_K: rc = mmq_launch<T_Q2_K>(wmap, xmap, p, smem, st); break;
+        case T_Q3_K: rc = mmq_launch<T_Q3_K>(wmap, xmap, p, smem, st); break;
+        case T_IQ4_NL: rc = mmq_launch<T_IQ4_NL>(wmap, xmap, p, smem, st); break;
+        case T_IQ4_XS: rc = mmq_launch<T_IQ4_XS>(wmap, xmap, p, smem, st); break;
     }
     if (rc == 0 && p.ksplit > 1) rc = ksplit_reduce(p, st);
     return rc;
@@ -945,6 +1117,10 @@ extern "C" int b200_mul_mat_q_bf16_group(int type, int ng, const void * const * 
         case T_Q4_K: rc = mmq_launch<T_Q4_K>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
         case T_Q5_K: rc = mmq_launch<T_Q5_K>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
         case T_Q6_K: rc = mmq_launch<T_Q6_K>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
+        case T_Q2_K: rc = mmq_launch<T_Q2_K>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
+        case T_Q3_K: rc = mmq_launch<T_Q3_K>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
+        case T_IQ4_NL: rc = mmq_launch<T_IQ4_NL>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
+        case T_IQ4_XS: rc = mmq_launch<T_IQ4_XS>(wmap[0], xmap, p, smem, st, 0, w1, w2); break;
     }
     if (rc == 0 && p.ksplit > 1) rc = ksplit_reduce(p, st);
     return rc;
@@ -1028,6 +1204,10 @@ extern "C" int b200_mul_mat_id_q(int type, const void * W, int64_t nb1, int n_ex
         case T_Q4_K: return mmq_launch<T_Q4_K>(wmap, xmap, p, smem, st, n_expert);
         case T_Q5_K: return mmq_launch<T_Q5_K>(wmap, xmap, p, smem, st, n_expert);
         case T_Q6_K: return mmq_launch<T_Q6_K>(wmap, xmap, p, smem, st, n_expert);
+        case T_Q2_K: return mmq_launch<T_Q2_K>(wmap, xmap, p, smem, st, n_expert);
+        case T_Q3_K: return mmq_launch<T_Q3_K>(wmap, xmap, p, smem, st, n_expert);
+        case T_IQ4_NL: return mmq_launch<T_IQ4_NL>(wmap, xmap, p, smem, st, n_expert);
+        case T_IQ4_XS: return mmq_launch<T_IQ4_XS>(wmap, xmap, p, smem, st, n_expert);
     }
     return -1;
 }

@@ -14,8 +14,12 @@ import oracle as O
 pytestmark = pytest.mark.gpu
 G = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "quant_golden.npz")))
 G.update(np.load(os.path.join(os.path.dirname(__file__), "golden", "quant_golden_legacy.npz")))
-NAMES = list(O.LEGACY_TYPES)                                   # every path, tensor-core MMQ included
-NAMES_MV = list(O.LEGACY_TYPES) + list(O.SMALL_K_TYPES)        # decode mat-vec, dequantisation, GET_ROWS (q2_K / q3_K: prefill runs as mat-vec passes)
+NAMES = list(O.LEGACY_TYPES) + list(O.SMALL_K_TYPES)          # tensor-core MMQ (q2_K / q3_K / iq4_xs: shifted 16-byte windows, K % 2048 == 0)
+NAMES_MV = NAMES                                               # decode mat-vec, dequantisation, GET_ROWS
+
+
+def _k_for(name, k):
+    return (k + 2047) // 2048 * 2048 if name in ("q2_K", "q3_K", "iq4_xs") else k
 TYPES = {**O.LEGACY_TYPES, **O.SMALL_K_TYPES}
 
 
@@ -146,7 +150,7 @@ def _dev(Wnp):
 def test_mmq_one_hot_reads_back_dequantised_weights(name, tn, monkeypatch):
     """One-hot activations read every dequantised weight back through the tensor-core path, element by element."""
     t = TYPES[name]
-    N, K = 130, 512
+    N, K = 130, _k_for(name, 512)
     rng = np.random.default_rng(11)
     W = O.random_quant_bytes(t, N, K, rng)
     want = O.dequantize(t, W, N, K)
@@ -160,6 +164,7 @@ def test_mmq_one_hot_reads_back_dequantised_weights(name, tn, monkeypatch):
 @pytest.mark.parametrize("N,K,M", [(16, 256, 9), (16, 256, 32), (128, 512, 33), (257, 1024, 100), (129, 4096, 129), (512, 2048, 300), (96, 14336, 64)])
 def test_mmq_shapes_vs_oracle(name, N, K, M):
     t = TYPES[name]
+    K = _k_for(name, K)
     rng = np.random.default_rng(N * 3 + K + M)
     W = O.random_quant_bytes(t, N, K, rng)
     X = rng.uniform(-1, 1, (M, K)).astype(np.float32)
@@ -172,6 +177,8 @@ def test_mmq_shapes_vs_oracle(name, N, K, M):
 def test_mmq_on_quantiser_output(name):
     """Weights as the reference's quantiser writes them (tests/golden: ggml_quantize_chunk), tiled to a full row tile."""
     t = TYPES[name]
+    if _k_for(name, 512) != 512:
+        pytest.skip("the golden rows hold two blocks; this format's tensor-core path takes rows of whole 8-block periods")
     N, K, M = 4, 512, 40
     W = G["W_" + name]
     rng = np.random.default_rng(1)
