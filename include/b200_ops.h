@@ -22,11 +22,18 @@ extern "C" {
 #define B200_TYPE_F32   0
 #define B200_TYPE_F16   1
 #define B200_TYPE_Q4_0  2
+#define B200_TYPE_Q4_1  3
+#define B200_TYPE_Q5_0  6
+#define B200_TYPE_Q5_1  7
 #define B200_TYPE_Q8_0  8
 #define B200_TYPE_Q8_1  9
+#define B200_TYPE_Q2_K 10
+#define B200_TYPE_Q3_K 11
 #define B200_TYPE_Q4_K 12
 #define B200_TYPE_Q5_K 13
 #define B200_TYPE_Q6_K 14
+#define B200_TYPE_IQ4_NL 20
+#define B200_TYPE_IQ4_XS 23
 #define B200_TYPE_I32  26
 
 /* ---- MUL_MAT, decode regime (activation columns M small) ----------------------------------------
@@ -261,7 +268,8 @@ int b200_op_flash_attn_ext_xb(const b200_tensor * q, const b200_tensor * k, cons
 int64_t b200_flash_attn_scratch_bytes(const b200_tensor * q, const b200_tensor * k);
 int b200_flash_attn_supported(int k_type, int v_type, int64_t dk, int64_t dv);
 /* MUL_MAT: dst[N, M, b2, b3] = src0[K, N, a2, a3] x src1[K, M, b2, b3], src0 broadcast over dims 2,3.
- * Quantised src0 (Q4_0, Q8_0, Q4_K, Q5_K, Q6_K) with f32 src1 goes to the MMVQ GEMV for M <= 8 and to the MMQ GEMM
+ * Quantised src0 (Q4_0, Q4_1, Q5_0, Q5_1, Q8_0, Q2_K, Q3_K, Q4_K, Q5_K, Q6_K, IQ4_NL, IQ4_XS: b200_mmvq_supported_type) with f32 src1
+ * goes to the MMVQ GEMV for M <= 8 and to the MMQ GEMM (b200_mul_mat_q_supported: K % 256 == 0; K % 2048 == 0 for Q6_K, Q2_K, Q3_K, IQ4_XS)
  * beyond; f16/bf16/f32 src0 to a plain tiled kernel.  Replaces ggml_cuda_mul_mat (ggml-cuda/ggml-cuda.cu:1936-2005).
  * scratch: device memory for the quantised activations (b200_mul_mat_scratch_bytes). */
 int b200_op_mul_mat(const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst,

@@ -14,6 +14,11 @@
 #   config3                 Llama-3-8B Q8_0 with f16 and q8_0 KV cache: pp512 / tg128 at depth 0 and at 28672
 #   cpu                     the reference CPU backend on the box's host cores: 1B Q4_0 pp512 / tg128 (config 1), 8B Q4_K_M pp64 / tg16
 #   moe                     Mixtral-8x7B Q4_K_M pp512 / tg128 and llama-batched-bench
+#   ab <VAR> [args]         A/B of one plugin switch on tg128 (VAR=1 / VAR=0, twice): tok/s and replayed-graph device time (tools/gpu_ab.sh)
+#   moedebug                why the MoE fusions match or not on the Mixtral model (B200_DEBUG_FUSE lines of a 4-token decode)
+#   check70b                Llama-3-70B on one GPU: fused == unfused logits, tg128 / pp512 with the gate/up pair mode on and off
+#   final                   the round's evidence in one box session (tools/gpu_final.sh)
+# MODEL_PRESET / MODEL_FTYPE select the model of bitident / launches / ab (tools/make_gguf.py presets and ftypes).
 set -u
 export LD_LIBRARY_PATH=$PWD/baseline/_ref/lib:$PWD/llamacog_b200:${LD_LIBRARY_PATH:-}
 PLUGIN=$PWD/llamacog_b200/libggml-b200.so
@@ -68,5 +73,9 @@ case $task in
     [ -f $f ] || python tools/make_gguf.py mixtral-8x7b q4_k_m $f > /dev/null
     timeout 600 $B/llama-bench -m $f -ngl 99 -fa 1 -p 512 -n 128 -r 2 -t 4 2>&1 | grep -E "pp512|tg128|error"
     timeout 600 $B/llama-batched-bench -m $f -ngl 99 -fa -npp 128 -ntg 32 -npl 1,2,4,8,16,32,64 -c 16384 2>&1 | grep -E "^\|" ;;
+  ab)      bash tools/gpu_ab.sh "$@" ;;
+  moedebug) bash tools/gpu_moe_debug.sh ;;
+  check70b) bash tools/gpu_70b_check.sh ;;
+  final)   bash tools/gpu_final.sh ;;
   *) echo "unknown task $task"; exit 2 ;;
 esac
