@@ -205,7 +205,7 @@ static bool use_mmq_id(const b200_tensor * as, const b200_tensor * b, const b200
 // activation columns quantised first (scratch: one 400-byte item per 256 values and column)
 static bool use_mmvqr_id(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids) {
     static const bool on = [] { const char * e = getenv("B200_MMVQR_ID"); return !e || atoi(e) != 0; }();
-    return on && (as->type == T_Q4_K || as->type == T_Q6_K || as->type == T_Q8_0 || as->type == T_Q4_0 || as->type == T_Q5_K) && ids->ne[1] == 1 && ids->ne[0] <= 3 && as->ne[0] % 256 == 0 && (b->nb[1] & 15) == 0 &&
+    return on && is_quant(as->type) && ids->ne[1] == 1 && ids->ne[0] <= 3 && as->ne[0] % 256 == 0 && (b->nb[1] & 15) == 0 &&
            ((uintptr_t)b->data & 15) == 0 && (as->nb[2] & 15) == 0;
 }
 extern "C" int64_t b200_mul_mat_id_scratch_bytes(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids) {

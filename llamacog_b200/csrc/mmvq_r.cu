@@ -14,6 +14,13 @@ B200_MMVQR_DEFINE(T_Q6_K)
 B200_MMVQR_DEFINE(T_Q8_0)
 B200_MMVQR_DEFINE(T_Q4_0)
 B200_MMVQR_DEFINE(T_Q5_K)
+B200_MMVQR_DEFINE(T_Q4_1)
+B200_MMVQR_DEFINE(T_Q5_0)
+B200_MMVQR_DEFINE(T_Q5_1)
+B200_MMVQR_DEFINE(T_IQ4_NL)
+B200_MMVQR_DEFINE(T_Q2_K)
+B200_MMVQR_DEFINE(T_Q3_K)
+B200_MMVQR_DEFINE(T_IQ4_XS)
 
 static int env_i(const char * name, int dflt) { const char * e = getenv(name); return e ? atoi(e) : dflt; }
 
@@ -79,7 +86,10 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
     if (!(by_id && a->sm_act) && !fuse_ok(a, ng)) return MMVQR_SKIP;
     if (!on || a->M != 1 || (!a->Xq && !a->norm_x) || (!by_id && std::max(1, a->ny) != 1) || std::max(1, a->nz) != 1) return MMVQR_SKIP;
     static const int more_on = env_i("B200_MMVQR_MORE", 1);      // Q8_0 / Q4_0 / Q5_K (round 2); 0: only Q4_K and Q6_K take this kernel
-    if (a->type != T_Q4_K && a->type != T_Q6_K && !((a->type == T_Q8_0 || a->type == T_Q4_0 || a->type == T_Q5_K) && more_on)) return MMVQR_SKIP;
+    static const int wide_on = env_i("B200_MMVQR_WIDE", 1);      // the formats of the round-2 widening
+    const bool more_t = a->type == T_Q8_0 || a->type == T_Q4_0 || a->type == T_Q5_K;
+    const bool wide_t = a->type == T_Q4_1 || a->type == T_Q5_0 || a->type == T_Q5_1 || a->type == T_IQ4_NL || a->type == T_Q2_K || a->type == T_Q3_K || a->type == T_IQ4_XS;
+    if (a->type != T_Q4_K && a->type != T_Q6_K && !(more_t && more_on) && !(wide_t && wide_on)) return MMVQR_SKIP;
     if (a->dbg_sumi && ng != 1) return MMVQR_SKIP;
     const int K = a->K;
     if (K <= 0 || K % 256) return MMVQR_SKIP;
@@ -204,6 +214,13 @@ int mmvqr_try(const b200_mmvq_args * a, int ng, const void * const * W, float * 
         case T_Q8_0: rc = mmvqr_launch_type<T_Q8_0>(p, c, stream); break;
         case T_Q4_0: rc = mmvqr_launch_type<T_Q4_0>(p, c, stream); break;
         case T_Q5_K: rc = mmvqr_launch_type<T_Q5_K>(p, c, stream); break;
+        case T_Q4_1: rc = mmvqr_launch_type<T_Q4_1>(p, c, stream); break;
+        case T_Q5_0: rc = mmvqr_launch_type<T_Q5_0>(p, c, stream); break;
+        case T_Q5_1: rc = mmvqr_launch_type<T_Q5_1>(p, c, stream); break;
+        case T_IQ4_NL: rc = mmvqr_launch_type<T_IQ4_NL>(p, c, stream); break;
+        case T_Q2_K: rc = mmvqr_launch_type<T_Q2_K>(p, c, stream); break;
+        case T_Q3_K: rc = mmvqr_launch_type<T_Q3_K>(p, c, stream); break;
+        case T_IQ4_XS: rc = mmvqr_launch_type<T_IQ4_XS>(p, c, stream); break;
     }
     if (rc) return rc;
     ++g_launches;

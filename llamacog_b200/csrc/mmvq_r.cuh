@@ -94,14 +94,22 @@ template <> struct hweights<T_Q6_K> { int ql[16]; int qh[8]; int sc[2]; uint32_t
 template <> struct hweights<T_Q8_0> { int w[34]; };      // four blocks of {d (f16), qs int8[32]}: 136 bytes, 8-byte aligned
 template <> struct hweights<T_Q4_0> { int w[18]; };      // four blocks of {d (f16), qs[16]}: 72 bytes, 8-byte aligned
 template <> struct hweights<T_Q5_K> { int hd[4]; int qh[8]; int w[16]; };      // header, the fifth bits of all 256 weights, this half's 64 code bytes
+// the formats of the round-2 widening (a half item = four 32-blocks, or half a super-block):
+template <> struct hweights<T_Q4_1> { int w[20]; };      // 4 x {d, m, qs[16]}: 80 bytes, 16-byte aligned
+template <> struct hweights<T_Q5_0> { int w[22]; };      // 4 x {d, qh[4], qs[16]}: 88 bytes, 8-byte aligned
+template <> struct hweights<T_Q5_1> { int w[24]; };      // 4 x {d, m, qh[4], qs[16]}: 96 bytes, 16-byte aligned
+template <> struct hweights<T_IQ4_NL> { int w[18]; };    // as Q4_0
+template <> struct hweights<T_Q2_K> { int sc[2]; int q[8]; int dm; };                 // this half's 8 scale bytes and 32 code bytes, d | dmin
+template <> struct hweights<T_Q3_K> { int hm[8]; int q[8]; int sc[3]; uint32_t d; };   // hmask (all of it), this half's 32 code bytes, the 12 scale bytes, d
+template <> struct hweights<T_IQ4_XS> { int hd[2]; int q[16]; };                       // d | scales_h, scales_l; this half's 64 code bytes
 
 // ip: shared address of the item, hh: which half
 template <int TYPE> __device__ __forceinline__ void load_hweights(uint32_t ip, int hh, hweights<TYPE> & w) {
     if constexpr (TYPE == T_Q4_K) {
         lds_words<4, true>(ip, w.hd);
         lds_words<16, true>(ip + 16 + 64 * hh, w.w);
-    } else if constexpr (TYPE == T_Q8_0 || TYPE == T_Q4_0) {
-        constexpr int HB = TYPE == T_Q8_0 ? 136 : 72;
+    } else if constexpr (TYPE == T_Q8_0 || TYPE == T_Q4_0 || TYPE == T_IQ4_NL || TYPE == T_Q4_1 || TYPE == T_Q5_0 || TYPE == T_Q5_1) {
+        constexpr int HB = TYPE == T_Q8_0 ? 136 : TYPE == T_Q4_1 ? 80 : TYPE == T_Q5_0 ? 88 : TYPE == T_Q5_1 ? 96 : 72;      // 8-byte aligned halves
 #pragma unroll
         for (int i = 0; i < HB / 8; ++i) {
             uint32_t lo, hi;
@@ -112,6 +120,22 @@ template <int TYPE> __device__ __forceinline__ void load_hweights(uint32_t ip, i
         lds_words<4, true>(ip, w.hd);
         lds_words<8, true>(ip + 16, w.qh);
         lds_words<16, true>(ip + 48 + 64 * hh, w.w);
+    } else if constexpr (TYPE == T_Q2_K) {         // 84-byte items: 4-byte aligned
+#pragma unroll
+        for (int i = 0; i < 2; ++i) w.sc[i] = (int)lds32(ip + 8 * hh + 4 * i);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) w.q[i] = (int)lds32(ip + 16 + 32 * hh + 4 * i);
+        w.dm = (int)lds32(ip + 80);
+    } else if constexpr (TYPE == T_Q3_K) {         // 110-byte items: 2-byte aligned
+        lds_words_a2<8>(ip, w.hm);
+        lds_words_a2<8>(ip + 32 + 32 * hh, w.q);
+        lds_words_a2<3>(ip + 96, w.sc);
+        w.d = lds16(ip + 108);
+    } else if constexpr (TYPE == T_IQ4_XS) {       // 136-byte items: 8-byte aligned
+#pragma unroll
+        for (int i = 0; i < 2; ++i) w.hd[i] = (int)lds32(ip + 4 * i);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) w.q[i] = (int)lds32(ip + 8 + 64 * hh + 4 * i);
     } else {
         lds_words_a2<16>(ip + 64 * hh, w.ql);
         lds_words_a2<8>(ip + 128 + 32 * hh, w.qh);
@@ -188,6 +212,128 @@ __device__ __forceinline__ float half_dot(const hweights<TYPE> & w, const hacts 
             acc = fmaf(half_bits_to_float(halfword<18>(w.w, 9 * j)) * a.d8[j], i2f_small(s + ((a.m32a[j] + a.m32b[j]) >> 2)), acc);
         }
         return acc;
+    } else if constexpr (TYPE == T_Q4_1) {         // vecdotq.cuh:49-80 (the block minimum times d8 * sum q from the layout's tail)
+        float acc = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&w.w[5 * j]));
+            int s0 = 0, s1 = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t q = (uint32_t)w.w[5 * j + 1 + k];
+                s0 = dp4a_us(q & 0x0F0F0F0Fu, a.q[j][k], s0);
+                s1 = dp4a_us(q & 0xF0F0F0F0u, a.q[j][4 + k], s1);
+            }
+            const int s = s0 + (s1 >> 4);
+            if constexpr (DBG) dbg[j] = s;
+            acc = fmaf(dm.x * a.d8[j], i2f_small(s), fmaf(dm.y, a.dsq[j], acc));
+        }
+        return acc;
+    } else if constexpr (TYPE == T_Q5_0 || TYPE == T_Q5_1) {      // vecdotq.cuh:82-150
+        float acc = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float dw, mw = 0.0f; uint32_t qh, qs[4];
+            if constexpr (TYPE == T_Q5_0) {
+                dw = half_bits_to_float(halfword<22>(w.w, 11 * j));
+                qh = (uint32_t)word_at_half<22>(w.w, 11 * j + 1);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) qs[k] = (uint32_t)word_at_half<22>(w.w, 11 * j + 3 + 2 * k);
+            } else {
+                const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&w.w[6 * j]));
+                dw = dm.x; mw = dm.y;
+                qh = (uint32_t)w.w[6 * j + 1];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) qs[k] = (uint32_t)w.w[6 * j + 2 + k];
+            }
+            int s = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t b0 = ((((qh >> (4 * k)) & 0xFu) * 0x00204081u) & 0x01010101u) << 4;
+                const uint32_t b1 = ((((qh >> (16 + 4 * k)) & 0xFu) * 0x00204081u) & 0x01010101u) << 4;
+                s = dp4a_us((qs[k] & 0x0F0F0F0Fu) | b0, a.q[j][k], s);
+                s = dp4a_us(((qs[k] >> 4) & 0x0F0F0F0Fu) | b1, a.q[j][4 + k], s);
+            }
+            if constexpr (DBG) dbg[j] = s;
+            if constexpr (TYPE == T_Q5_0) acc = fmaf(dw * a.d8[j], i2f_small(s + ((a.m32a[j] + a.m32b[j]) >> 1)), acc);
+            else acc = fmaf(dw * a.d8[j], i2f_small(s), fmaf(mw, a.dsq[j], acc));
+        }
+        return acc;
+    } else if constexpr (TYPE == T_IQ4_NL) {
+        float acc = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int s = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                int vlo, vhi; iq4_lookup8((uint32_t)word_at_half<18>(w.w, 9 * j + 1 + 2 * k), vlo, vhi);
+                s = dp4a_ss(vlo, a.q[j][k], s); s = dp4a_ss(vhi, a.q[j][4 + k], s);
+            }
+            if constexpr (DBG) dbg[j] = s;
+            acc = fmaf(half_bits_to_float(halfword<18>(w.w, 9 * j)) * a.d8[j], i2f_small(s), acc);
+        }
+        return acc;
+    } else if constexpr (TYPE == T_IQ4_XS) {
+        const float d = half_bits_to_float((uint32_t)w.hd[0] & 0xFFFFu);
+        const uint32_t sh = (uint32_t)w.hd[0] >> 16, sl = (uint32_t)w.hd[1];
+        float accx = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int ib = 4 * hh + j;
+            const int ls = (int)(((sl >> (4 * ib)) & 0xFu) | (((sh >> (2 * ib)) & 3u) << 4)) - 32;
+            int s = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                int vlo, vhi; iq4_lookup8((uint32_t)w.q[4 * j + k], vlo, vhi);
+                s = dp4a_ss(vlo, a.q[j][k], s); s = dp4a_ss(vhi, a.q[j][4 + k], s);
+            }
+            if constexpr (DBG) dbg[j] = s;
+            accx = fmaf(a.d8[j] * (float)ls, i2f_small(s), accx);
+        }
+        return d * accx;
+    } else if constexpr (TYPE == T_Q2_K) {         // vecdotq.cuh:218-243: this half's blocks j = 0..3 use bit pair j of the 32 code bytes
+        const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&w.dm));
+        float accd = 0.0f, accm = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t scw = (uint32_t)w.sc[j >> 1] >> (16 * (j & 1));
+            const int sa = scw & 0xF, ma = (scw >> 4) & 0xF, sb = (scw >> 8) & 0xF, mb = (scw >> 12) & 0xF;
+            int s0 = 0, s1 = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                s0 = dp4a_us(((uint32_t)w.q[k] >> (2 * j)) & 0x03030303u, a.q[j][k], s0);
+                s1 = dp4a_us(((uint32_t)w.q[4 + k] >> (2 * j)) & 0x03030303u, a.q[j][4 + k], s1);
+            }
+            if constexpr (DBG) dbg[j] = s0 + s1;
+            accd = fmaf(a.d8[j], i2f_small(s0 * sa + s1 * sb), accd);
+            accm = fmaf(a.d8[j], i2f_small(-(a.m32a[j] >> 5) * ma - (a.m32b[j] >> 5) * mb), accm);
+        }
+        return dm.x * accd - dm.y * accm;
+    } else if constexpr (TYPE == T_Q3_K) {         // vecdotq.cuh:301-331
+        const float d = half_bits_to_float(w.d);
+        float acc3 = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int scv[2];
+#pragma unroll
+            for (int h2 = 0; h2 < 2; ++h2) {       // scale 8hh + 2j + h2: low nibble word (2j + h2) / 4, byte (2j + h2) % 4, second half: high nibbles
+                const int il = 2 * j + h2;
+                const uint32_t lo = ((uint32_t)w.sc[il >> 2] >> (8 * (il & 3) + 4 * hh)) & 0xFu;
+                const uint32_t hi = ((uint32_t)w.sc[2] >> (8 * (il & 3) + 2 * (2 * hh + (il >> 2)))) & 3u;
+                scv[h2] = (int)(lo | (hi << 4)) - 32;
+            }
+            int s0 = a.m32a[j] >> 3, s1 = a.m32b[j] >> 3;      // -4 * sum q8 of each half
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t v0 = (((uint32_t)w.q[k] >> (2 * j)) & 0x03030303u) | ((((uint32_t)w.hm[k] >> (4 * hh + j)) & 0x01010101u) << 2);
+                const uint32_t v1 = (((uint32_t)w.q[4 + k] >> (2 * j)) & 0x03030303u) | ((((uint32_t)w.hm[4 + k] >> (4 * hh + j)) & 0x01010101u) << 2);
+                s0 = dp4a_us(v0, a.q[j][k], s0);
+                s1 = dp4a_us(v1, a.q[j][4 + k], s1);
+            }
+            if constexpr (DBG) dbg[j] = s0 + s1;
+            acc3 = fmaf(a.d8[j], i2f_small(s0 * scv[0] + s1 * scv[1]), acc3);
+        }
+        return d * acc3;
     } else if constexpr (TYPE == T_Q8_0) {         // vecdotq.cuh:153-165: d_w * d8 * sum q_w q_x per 32-block
         float acc = 0.0f;
 #pragma unroll

@@ -186,3 +186,42 @@ def test_mmq_on_quantiser_output(name):
     got = _ops().mul_mat_q(t, _dev(W), torch.from_numpy(X).cuda(), N, K).cpu().numpy()
     ref = O.mul_mat_f32(t, W, X, N, K, M)
     assert _nmse(got, ref) < 1e-4, _nmse(got, ref)
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("N,K", [(257, 4096), (130, 14336), (33, 8192), (40, 2048), (1500, 4096), (7, 28672)])
+def test_register_resident_kernel_vs_oracle(name, N, K):
+    """The batch-1 kernel with register-resident activations (mmvq_r.cuh) on the widened formats: every int32 block sum bit-exact
+    against the oracle, fp32 within summation-order noise, parity-hook build == production build."""
+    ops = _ops()
+    t = TYPES[name]
+    rng = np.random.default_rng(N * 31 + K)
+    Wnp = O.random_quant_bytes(t, N, K, rng)
+    Xnp = rng.uniform(-1, 1, (1, K)).astype(np.float32)
+    W = torch.from_numpy(Wnp.reshape(-1)).cuda()
+    X = torch.from_numpy(Xnp).cuda()
+    dst, sums = ops.mul_mat_vec_q(t, W, X, N, K, dbg=True, Xq=ops.quantize_acts(X))
+    dst2 = ops.mul_mat_vec_q(t, W, X, N, K, Xq=ops.quantize_acts(X))
+    torch.cuda.synchronize()
+    q = O.quantize_row_q8_1_cuda(Xnp[0], K)
+    sums = sums.cpu().numpy()
+    for n in range(0, N, max(1, N // 40)):
+        si, _ = O.block_sums(t, Wnp[n], q, K)
+        assert np.array_equal(sums[0, n], si), "row %d" % n
+    _close(dst.cpu().numpy(), O.mul_mat_vec_q(t, Wnp, Xnp, N, K, 1))
+    assert torch.equal(dst, dst2)
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_register_resident_kernel_is_taken(name):
+    """b200_mmvq_fusable says the register-resident kernel takes a 4096 x 4096 launch of every widened format (so the test above and the
+    fused decode paths of the plugin really run it, not the general kernel)."""
+    import ctypes as C
+    ops = _ops()
+    t = TYPES[name]
+    N = K = 4096
+    W = torch.zeros(N * ops.row_bytes(t, K), dtype=torch.uint8, device="cuda")
+    d = torch.empty(1, N, device="cuda")
+    xq = torch.zeros(K // 256 * 400, dtype=torch.uint8, device="cuda")
+    a = ops.MmvqArgs(type=t, W=W.data_ptr(), nb1=ops.row_bytes(t, K), X=None, xs=K, dst=d.data_ptr(), ds=N, N=N, K=K, M=1, ny=1, nz=1, pdl=-1, Xq=xq.data_ptr())
+    assert ops.lib().b200_mmvq_fusable(C.byref(a), C.c_int(1), None, None) == 1

@@ -117,7 +117,7 @@ def _gemv_args(ops, t, W, N, K, dst, **kw):
                         ny=1, nz=1, pdl=-1, **kw)
 
 
-@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K"])
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K", "q4_1", "q5_0", "q3_K", "iq4_xs"])
 @pytest.mark.parametrize("N,K", [(4096, 4096), (1024, 2048), (300, 1024), (128256, 4096)])
 def test_gemv_norm_prologue_matches_separate_launches(tname, N, K):
     """RMS_NORM + MUL + quantisation done by the batch-1 GEMV itself (b200_mmvq_args.norm_*): the normalised row, the
@@ -126,7 +126,7 @@ def test_gemv_norm_prologue_matches_separate_launches(tname, N, K):
     import numpy as np
     import oracle as O
     ops = _ops(); L = ops.lib()
-    t = O.QUANT_TYPES[tname]
+    t = O.ALL_QUANT_TYPES[tname]
     rng = np.random.default_rng(N + K)
     W = torch.from_numpy(O.random_quant_bytes(t, N, K, rng).reshape(-1)).cuda()
     torch.manual_seed(N + K)
@@ -148,7 +148,7 @@ def test_gemv_norm_prologue_matches_separate_launches(tname, N, K):
     assert torch.equal(d, d_ref)
 
 
-@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K"])
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K", "q4_1", "q5_0", "q3_K", "iq4_xs"])
 @pytest.mark.parametrize("N,K", [(4096, 4096), (4096, 14336), (37, 2048), (5000, 4096)])
 def test_gemv_residual_epilogue(tname, N, K):
     """ADD fused into the GEMV's store (b200_mmvq_args.fuse_resid / fuse_sum): dst as without it, fuse_sum = dst + resid exactly
@@ -156,7 +156,7 @@ def test_gemv_residual_epilogue(tname, N, K):
     import numpy as np
     import oracle as O
     ops = _ops(); L = ops.lib()
-    t = O.QUANT_TYPES[tname]
+    t = O.ALL_QUANT_TYPES[tname]
     rng = np.random.default_rng(N * 3 + K)
     W = torch.from_numpy(O.random_quant_bytes(t, N, K, rng).reshape(-1)).cuda()
     torch.manual_seed(N)
@@ -178,7 +178,7 @@ def test_gemv_residual_epilogue(tname, N, K):
     assert torch.equal(d2, d_ref + r)
 
 
-@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K"])
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K", "q4_1", "q5_0", "q3_K", "iq4_xs"])
 @pytest.mark.parametrize("N,K,inplace", [(14336, 4096, False), (14336, 4096, True), (28672, 4096, False), (2048, 2048, True), (96, 1024, False), (8192, 2048, False),
                                           (28672, 8192, True), (11008, 4096, False), (9472, 2048, True)])      # Llama-3-70B, Llama-2-7B (344 blocks: uneven CTAs), 296 blocks
 def test_gemv_gate_up_silu_mul_epilogue(tname, N, K, inplace):
@@ -189,7 +189,7 @@ def test_gemv_gate_up_silu_mul_epilogue(tname, N, K, inplace):
     import numpy as np
     import oracle as O
     ops = _ops(); L = ops.lib()
-    t = O.QUANT_TYPES[tname]
+    t = O.ALL_QUANT_TYPES[tname]
     rng = np.random.default_rng(N + K)
     Wg = torch.from_numpy(O.random_quant_bytes(t, N, K, rng).reshape(-1)).cuda()
     Wu = torch.from_numpy(O.random_quant_bytes(t, N, K, rng).reshape(-1)).cuda()
@@ -229,7 +229,7 @@ def test_moe_gate_up_pair_launch(tname, N, K, n_expert, n_used, inplace):
     import numpy as np
     import oracle as O
     ops = _ops(); L = ops.lib()
-    t = O.QUANT_TYPES[tname]
+    t = O.ALL_QUANT_TYPES[tname]
     rng = np.random.default_rng(N + K + n_used)
     rb = ops.row_bytes(t, K)
     Wg = torch.from_numpy(O.random_quant_bytes(t, N * n_expert, K, rng).reshape(-1)).cuda()
@@ -293,7 +293,7 @@ class _GemvRope(C.Structure):
                 ("cell_type", C.c_int * 3), ("head_dim", C.c_int * 3), ("pos", C.c_void_p), ("ffac", C.c_void_p), ("prm", _RopeParams)]
 
 
-@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K"])
+@pytest.mark.parametrize("tname", ["q4_K", "q6_K", "q8_0", "q4_0", "q5_K", "q4_1", "q5_0", "q3_K", "iq4_xs"])
 @pytest.mark.parametrize("hd,n_dims,pos,ext,use_ff,slot", [(128, 128, 77, 0.0, False, False), (128, 128, 4095, 0.0, True, True),
                                                            (64, 32, 5, 0.0, False, False), (128, 128, 300, 1.0, False, True)])
 def test_gemv_rope_epilogue_matches_rope_op(tname, hd, n_dims, pos, ext, use_ff, slot):
@@ -304,7 +304,7 @@ def test_gemv_rope_epilogue_matches_rope_op(tname, hd, n_dims, pos, ext, use_ff,
     import numpy as np
     import oracle as O
     ops = _ops(); L = ops.lib()
-    t = O.QUANT_TYPES[tname]
+    t = O.ALL_QUANT_TYPES[tname]
     K, nh, nkv = 2048, 12, 4
     Ns = [nh * hd, nkv * hd, nkv * hd]
     rng = np.random.default_rng(hd + pos)
